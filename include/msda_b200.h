@@ -1,0 +1,112 @@
+/*
+ * msda_b200.h -- C ABI of the B200-native multi-scale deformable attention op.
+ *
+ * This is the drop-in boundary for the reference's native extension
+ * `MultiScaleDeformableAttention` (LuisCossioUOH/Kinet,
+ * src/trackformer/models/ops/src/).  Entry points replace:
+ *
+ *   msda_b200_forward   <- ms_deform_attn_forward   (src/vision.cpp:5,
+ *                          src/ms_deform_attn.h:10-28,
+ *                          src/cuda/ms_deform_attn_cuda.cu:19-86)
+ *   msda_b200_backward  <- ms_deform_attn_backward  (src/vision.cpp:6,
+ *                          src/ms_deform_attn.h:30-49,
+ *                          src/cuda/ms_deform_attn_cuda.cu:89-168)
+ *
+ * Conventions: plain pointers and sizes only; all data pointers are DEVICE
+ * pointers on the current CUDA device; calls enqueue work on `stream`
+ * (a cudaStream_t passed as void*; NULL = legacy default stream) and return
+ * without synchronising.  Nothing is allocated; nothing throws.  Return value
+ * is 0 on success, a negative MSDA_E_* for argument errors, or a positive
+ * cudaError_t from the launch.  There is no CPU implementation: on a machine
+ * without a CUDA device every compute entry point returns a CUDA error.
+ *
+ * Tensor layouts (row-major, contiguous; same as the reference,
+ * ms_deform_attn_cuda.cu:25-27):
+ *   value            [N][S][M][D]          value_dtype
+ *   spatial_shapes   [L][2] int64 (H, W)   device memory
+ *   level_start      [L] int64 or NULL     device memory; NULL = computed from
+ *                                          spatial_shapes inside the kernel
+ *                                          (the reference recomputes it on the
+ *                                          host every call, :52-58)
+ *   sampling_loc     [N][Lq][M][L][P][2]   aux_dtype, (x, y) in [0,1]
+ *   attn_weight      [N][Lq][M][L][P]      aux_dtype
+ *   output           [N][Lq][M*D]          value_dtype
+ *   grad_output      [N][Lq][M*D]          value_dtype
+ *   grad_value       like value            value_dtype  (fully overwritten)
+ *   grad_sampling_loc, grad_attn_weight    aux_dtype    (fully overwritten)
+ */
+#ifndef MSDA_B200_H
+#define MSDA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MSDA_B200_ABI_VERSION 1
+
+/* element types */
+#define MSDA_F32 0
+#define MSDA_BF16 1
+#define MSDA_F64 2 /* parity with the reference's AT_DISPATCH_FLOATING_TYPES (gradcheck) */
+#define MSDA_F16 3
+
+/* argument errors (negative so they never collide with cudaError_t) */
+#define MSDA_E_DTYPE (-1)   /* unsupported value_dtype / aux_dtype combination */
+#define MSDA_E_SHAPE (-2)   /* non-positive or unsupported dimension */
+#define MSDA_E_NULL (-3)    /* required pointer is NULL */
+#define MSDA_E_ALIGN (-4)   /* pointer not 16-byte aligned */
+#define MSDA_E_WORKSPACE (-5) /* workspace too small */
+
+#define MSDA_MAX_LEVELS 16
+
+/* Supported (value_dtype, aux_dtype): (F32,F32) (BF16,F32) (BF16,BF16)
+ * (F16,F32) (F16,F16) (F64,F64).  D*sizeof(value) must be a multiple of 16
+ * for the vector paths (D % 4 == 0 fp32, D % 8 == 0 bf16/f16); any other D
+ * takes the scalar path.  1 <= L <= MSDA_MAX_LEVELS. */
+
+typedef struct msda_dims {
+    int32_t N;  /* batch */
+    int32_t S;  /* sum_l H_l*W_l */
+    int32_t M;  /* heads */
+    int32_t D;  /* channels per head */
+    int32_t L;  /* levels */
+    int32_t Lq; /* queries (0 allowed: no-op for outputs, grad_value zero-filled) */
+    int32_t P;  /* points per level */
+} msda_dims;
+
+int msda_b200_abi_version(void);
+
+/* Human-readable text for a return code of this library. */
+const char *msda_b200_error_string(int code);
+
+/* output = sum_{l,p} attn * bilinear(value_l, loc)   (fused, no scratch) */
+int msda_b200_forward(const void *value, int value_dtype,
+                      const int64_t *spatial_shapes, const int64_t *level_start,
+                      const void *sampling_loc, const void *attn_weight, int aux_dtype,
+                      void *output, const msda_dims *dims, void *stream);
+
+/* Bytes of device scratch msda_b200_backward needs (0 for f32/f64 value:
+ * gradients accumulate in place; bf16/f16 accumulate grad_value in fp32). */
+size_t msda_b200_backward_workspace_bytes(int value_dtype, const msda_dims *dims);
+
+/* All three gradients in one call.  grad_value/grad_sampling_loc/grad_attn_weight
+ * need not be initialised.  workspace may be NULL when the size above is 0. */
+int msda_b200_backward(const void *value, int value_dtype,
+                       const int64_t *spatial_shapes, const int64_t *level_start,
+                       const void *sampling_loc, const void *attn_weight, int aux_dtype,
+                       const void *grad_output,
+                       void *grad_value, void *grad_sampling_loc, void *grad_attn_weight,
+                       void *workspace, size_t workspace_bytes,
+                       const msda_dims *dims, void *stream);
+
+/* Number of kernels the last forward / backward call of this thread launched
+ * (bench.py's gpu_launches evidence). */
+int msda_b200_last_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MSDA_B200_H */

@@ -1,0 +1,72 @@
+"""ctypes binding of libmsda_b200.so (include/msda_b200.h).
+
+The library is the product; there is no fallback.  If it is missing, or a call
+fails, this module raises -- it never routes around the CUDA kernels.
+"""
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmsda_b200.so")
+
+MSDA_F32, MSDA_BF16, MSDA_F64, MSDA_F16 = 0, 1, 2, 3
+_DTYPE_CODE = {torch.float32: MSDA_F32, torch.bfloat16: MSDA_BF16,
+               torch.float64: MSDA_F64, torch.float16: MSDA_F16}
+
+
+class MsdaDims(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in ("N", "S", "M", "D", "L", "Lq", "P")]
+
+
+EXPORTS = ("msda_b200_abi_version", "msda_b200_error_string", "msda_b200_forward",
+           "msda_b200_backward_workspace_bytes", "msda_b200_backward",
+           "msda_b200_last_launch_count")
+
+_lib = None
+
+
+def load():
+    """Load the shared library (once).  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "kinet_b200: %s is missing -- build it with `python -m kinet_b200.build` "
+            "(there is no CPU or PyTorch fallback for MSDeformAttn)" % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    vp, i, dp = ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(MsdaDims)
+    lib.msda_b200_abi_version.restype = i
+    lib.msda_b200_error_string.restype = ctypes.c_char_p
+    lib.msda_b200_error_string.argtypes = [i]
+    lib.msda_b200_forward.restype = i
+    lib.msda_b200_forward.argtypes = [vp, i, vp, vp, vp, vp, i, vp, dp, vp]
+    lib.msda_b200_backward_workspace_bytes.restype = ctypes.c_size_t
+    lib.msda_b200_backward_workspace_bytes.argtypes = [i, dp]
+    lib.msda_b200_backward.restype = i
+    lib.msda_b200_backward.argtypes = [vp, i, vp, vp, vp, vp, i, vp, vp, vp, vp, vp,
+                                       ctypes.c_size_t, dp, vp]
+    lib.msda_b200_last_launch_count.restype = i
+    if lib.msda_b200_abi_version() != 1:
+        raise RuntimeError("kinet_b200: libmsda_b200.so ABI version mismatch")
+    _lib = lib
+    return lib
+
+
+def dtype_code(dtype):
+    try:
+        return _DTYPE_CODE[dtype]
+    except KeyError:
+        raise RuntimeError("kinet_b200: unsupported dtype %s" % dtype)
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = load().msda_b200_error_string(rc).decode()
+        raise RuntimeError("%s failed: %s (code %d)" % (what, msg, rc))
+
+
+def last_launch_count():
+    return int(load().msda_b200_last_launch_count())

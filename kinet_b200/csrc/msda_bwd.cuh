@@ -1,0 +1,242 @@
+// msda_bwd.cuh -- multi-scale deformable attention backward for sm_100a.
+//
+// Replaces the reference's two backward kernels (.cuh:239-306 grad_value with a
+// 5x5 neighbourhood scan and one scalar global atomic per channel and corner;
+// .cuh:308-378 grad_sampling_loc / grad_attn_weight with a serial, uncoalesced
+// channel loop that re-reads every corner three times) with ONE pass over the
+// samples that reads each corner row once (16-byte loads) and produces all three
+// gradients:
+//   * grad_attn_weight / grad_sampling_loc: per-lane partial sums over the lane's
+//     VEC channels, reduced across the GS lanes of the row with warp shuffles;
+//     every output element has exactly one writer (no atomics), written coalesced.
+//   * grad_value: 16-byte vector reductions (red.global.add.v4.f32, sm_90+) --
+//     one instruction per lane and corner instead of four scalar atomics.
+//     16-bit value types accumulate into an fp32 workspace that a second small
+//     kernel rounds once (accumulating in bf16 would lose the small terms).
+#pragma once
+#include "msda_common.cuh"
+
+namespace msda {
+
+// Sum across the GS lanes of a group; every lane of the group gets the total.
+template <int GS>
+__device__ __forceinline__ float group_sum(float v, int gl, int grp_base)
+{
+    if constexpr ((GS & (GS - 1)) == 0) {
+#pragma unroll
+        for (int o = GS / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        return v;
+    } else {
+        // non power-of-two group (D = 36 -> GS = 9): fold down, then broadcast lane 0
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) {
+            const float t = __shfl_down_sync(0xffffffffu, v, o);
+            if (gl < o && gl + o < GS) v += t;
+        }
+        return __shfl_sync(0xffffffffu, v, grp_base);
+    }
+}
+
+// GV is the type grad_value is accumulated in (float; the fp32 workspace for 16-bit VT).
+template <typename VT, typename AT, int VEC, int GS, int NWARPS>
+__global__ void __launch_bounds__(NWARPS * 32)
+msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ shapes,
+                     const int64_t* __restrict__ level_start, const AT* __restrict__ loc,
+                     const AT* __restrict__ attn, const VT* __restrict__ grad_out,
+                     float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
+                     AT* __restrict__ grad_attn, const KernelDims d)
+{
+    constexpr int GPW = 32 / GS;
+    constexpr int D = VEC * GS;
+    static_assert(VEC % 4 == 0, "vector reductions are 4 floats wide");
+    __shared__ LevelTable lt;
+    stage_levels(lt, shapes, level_start, d);
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int grp = lane / GS, gl = lane - grp * GS;
+    const bool lane_used = grp < GPW;
+    const int grp_base = grp * GS;
+    const int LP = d.L * d.P;
+    const int row_stride = d.M * D;
+    const int items = lt.total_tiles * d.N * d.M;
+
+    for (int item = blockIdx.x; item < items; item += gridDim.x) {
+        const int tile = item / (d.N * d.M);
+        const int bm = item - tile * (d.N * d.M);
+        const int b = bm / d.M, m = bm - b * d.M;
+        const size_t bbase = ((size_t)b * d.S * d.M + m) * D + gl * VEC;
+        const VT* vbase = value + bbase;
+        float* gvbase = grad_value_acc + bbase;
+
+        for (int i0 = warp * GPW; i0 < d.tile_q; i0 += NWARPS * GPW) {
+            const int q = (lane_used && i0 + grp < d.tile_q) ? tile_query(lt, d, tile, i0 + grp) : -1;
+            const bool row_ok = q >= 0;
+            const size_t row = ((size_t)b * d.Lq + (row_ok ? q : 0)) * d.M + m;
+            const AT* lrow = loc + row * LP * 2;
+            const AT* arow = attn + row * LP;
+
+            float g[VEC];
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) g[k] = 0.f;
+            if (row_ok) VecIO<VT, VEC>::load_stream(grad_out + row * D + gl * VEC, g);
+
+            int l = 0, p = 0;
+            int H = lt.H[0], W = lt.W[0], st = lt.start[0];
+            for (int s0 = 0; s0 < LP; s0 += GS) {
+                float2 my_xy = make_float2(-8.f, -8.f);
+                float my_a = 0.f;
+                const bool mine = row_ok && s0 + gl < LP;
+                if (mine) {
+                    my_xy = load_loc<AT>(lrow + (s0 + gl) * 2);
+                    my_a = load_attn<AT>(arow + s0 + gl);
+                }
+                float out_gx = 0.f, out_gy = 0.f, out_ga = 0.f;   // results for my sample
+                const int cnt = min(GS, LP - s0);
+#pragma unroll 2
+                for (int j = 0; j < cnt; ++j) {
+                    const float lx = __shfl_sync(0xffffffffu, my_xy.x, grp_base + j);
+                    const float ly = __shfl_sync(0xffffffffu, my_xy.y, grp_base + j);
+                    const float a = __shfl_sync(0xffffffffu, my_a, grp_base + j);
+                    const Tap t = make_tap(lx, ly, H, W, st, row_stride);
+                    const float w[4] = {t.hh * t.hw, t.hh * t.lw, t.lh * t.hw, t.lh * t.lw};
+                    float v[4][VEC];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        if (t.off[c] >= 0) {
+                            VecIO<VT, VEC>::load(vbase + t.off[c], v[c]);
+                        } else {
+#pragma unroll
+                            for (int k = 0; k < VEC; ++k) v[c][k] = 0.f;
+                        }
+                    }
+                    float sa = 0.f, sx = 0.f, sy = 0.f;
+#pragma unroll
+                    for (int k = 0; k < VEC; ++k) {
+                        const float top = v[0][k], tr = v[1][k], bl = v[2][k], br = v[3][k];
+                        sa = fmaf(g[k], w[0] * top + w[1] * tr + w[2] * bl + w[3] * br, sa);
+                        sx = fmaf(g[k], t.hh * (tr - top) + t.lh * (br - bl), sx);
+                        sy = fmaf(g[k], t.hw * (bl - top) + t.lw * (br - tr), sy);
+                    }
+                    // scatter: grad_value[corner] += w_corner * attn * grad_out
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        if (t.off[c] >= 0) {
+                            const float wa = w[c] * a;
+#pragma unroll
+                            for (int k = 0; k < VEC; k += 4)
+                                red_add_f32x4(gvbase + t.off[c] + k, wa * g[k], wa * g[k + 1],
+                                              wa * g[k + 2], wa * g[k + 3]);
+                        }
+                    }
+                    sa = group_sum<GS>(sa, gl, grp_base);
+                    sx = group_sum<GS>(sx, gl, grp_base);
+                    sy = group_sum<GS>(sy, gl, grp_base);
+                    if (gl == j) {
+                        out_ga = sa;
+                        out_gx = sx * a * (float)W;
+                        out_gy = sy * a * (float)H;
+                    }
+                    if (++p == d.P) {
+                        p = 0;
+                        ++l;
+                        if (l < d.L) { H = lt.H[l]; W = lt.W[l]; st = lt.start[l]; }
+                    }
+                }
+                if (mine) {
+                    store_loc<AT>(grad_loc + (row * LP + s0 + gl) * 2, out_gx, out_gy);
+                    grad_attn[row * LP + s0 + gl] = from_f32<AT>(out_ga);
+                }
+            }
+        }
+    }
+}
+
+// fp32 workspace -> 16-bit grad_value (one rounding of the full sum).
+template <typename VT>
+__global__ void __launch_bounds__(256)
+msda_round_grad_value_kernel(const float* __restrict__ acc, VT* __restrict__ gv, size_t n8)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8;
+         i += (size_t)gridDim.x * blockDim.x) {
+        float v[8];
+        VecIO<float, 4>::load_stream(acc + i * 8, *reinterpret_cast<float(*)[4]>(&v[0]));
+        VecIO<float, 4>::load_stream(acc + i * 8 + 4, *reinterpret_cast<float(*)[4]>(&v[4]));
+        VecIO<VT, 8>::store(gv + i * 8, v);
+    }
+}
+
+template <typename T> __device__ __forceinline__ void atomic_add_any(T* p, T v) { atomicAdd(p, v); }
+
+// Generic fallback (any D / fp64): one warp per (query, head) row.
+// GV: accumulation buffer element type (double for fp64, float otherwise).
+template <typename VT, typename AT, typename ACC>
+__global__ void __launch_bounds__(256)
+msda_backward_generic_kernel(const VT* __restrict__ value, const int64_t* __restrict__ shapes,
+                             const int64_t* __restrict__ level_start, const AT* __restrict__ loc,
+                             const AT* __restrict__ attn, const VT* __restrict__ grad_out,
+                             ACC* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
+                             AT* __restrict__ grad_attn, const KernelDims d)
+{
+    __shared__ LevelTable lt;
+    stage_levels(lt, shapes, level_start, d);
+    const int lane = threadIdx.x & 31;
+    const size_t warps = (size_t)gridDim.x * (blockDim.x >> 5);
+    const size_t rows = (size_t)d.N * d.Lq * d.M;
+    const int LP = d.L * d.P;
+    const size_t rs = (size_t)d.M * d.D;
+    for (size_t row = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows; row += warps) {
+        const int m = (int)(row % d.M);
+        const size_t b = row / ((size_t)d.Lq * d.M);
+        const size_t bbase = (b * d.S * d.M + m) * d.D;
+        for (int s = 0; s < LP; ++s) {
+            const int l = s / d.P;
+            const int H = lt.H[l], W = lt.W[l];
+            const ACC x = (ACC)loc[(row * LP + s) * 2] * (ACC)W - (ACC)0.5;
+            const ACC y = (ACC)loc[(row * LP + s) * 2 + 1] * (ACC)H - (ACC)0.5;
+            const ACC a = (ACC)attn[row * LP + s];
+            ACC sa = 0, sx = 0, sy = 0;
+            if (y > (ACC)-1 && x > (ACC)-1 && y < (ACC)H && x < (ACC)W) {
+                const ACC fy = floor(y), fx = floor(x);
+                const int y0 = (int)fy, x0 = (int)fx;
+                const ACC lh = y - fy, lw = x - fx, hh = (ACC)1 - lh, hw = (ACC)1 - lw;
+                const size_t pix = (size_t)lt.start[l] + (size_t)y0 * W + x0;
+                const bool ok[4] = {y0 >= 0 && x0 >= 0, y0 >= 0 && x0 + 1 <= W - 1,
+                                    y0 + 1 <= H - 1 && x0 >= 0, y0 + 1 <= H - 1 && x0 + 1 <= W - 1};
+                const size_t off[4] = {pix * rs, (pix + 1) * rs, (pix + W) * rs, (pix + W + 1) * rs};
+                const ACC w[4] = {hh * hw, hh * lw, lh * hw, lh * lw};
+                for (int c = lane; c < d.D; c += 32) {
+                    const ACC g = (ACC)grad_out[row * d.D + c];
+                    ACC v[4];
+                    for (int k = 0; k < 4; ++k) v[k] = ok[k] ? (ACC)value[bbase + off[k] + c] : (ACC)0;
+                    sa += g * (w[0] * v[0] + w[1] * v[1] + w[2] * v[2] + w[3] * v[3]);
+                    sx += g * (hh * (v[1] - v[0]) + lh * (v[3] - v[2]));
+                    sy += g * (hw * (v[2] - v[0]) + lw * (v[3] - v[1]));
+                    for (int k = 0; k < 4; ++k)
+                        if (ok[k]) atomic_add_any<ACC>(grad_value_acc + bbase + off[k] + c, w[k] * a * g);
+                }
+            }
+            for (int o = 16; o > 0; o >>= 1) {
+                sa += __shfl_xor_sync(0xffffffffu, sa, o);
+                sx += __shfl_xor_sync(0xffffffffu, sx, o);
+                sy += __shfl_xor_sync(0xffffffffu, sy, o);
+            }
+            if (lane == 0) {
+                grad_loc[(row * LP + s) * 2] = (AT)(sx * a * (ACC)W);
+                grad_loc[(row * LP + s) * 2 + 1] = (AT)(sy * a * (ACC)H);
+                grad_attn[row * LP + s] = (AT)sa;
+            }
+        }
+    }
+}
+
+// ACC workspace -> VT grad_value for the generic path (scalar).
+template <typename VT, typename ACC>
+__global__ void __launch_bounds__(256)
+msda_round_generic_kernel(const ACC* __restrict__ acc, VT* __restrict__ gv, size_t n)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (size_t)gridDim.x * blockDim.x)
+        gv[i] = (VT)acc[i];
+}
+
+}  // namespace msda

@@ -1,0 +1,247 @@
+// msda_common.cuh -- shared device helpers for the sm_100a MSDeformAttn kernels.
+//
+// Semantics follow the reference kernels (LuisCossioUOH/Kinet,
+// src/trackformer/models/ops/src/cuda/ms_deform_im2col_cuda.cuh): pixel-centre
+// shift x = loc_x*W - 0.5 (:227-228), open sample window -1 < x < W (:229),
+// zero contribution from corners outside [0,W-1]x[0,H-1] (:24-67).
+// Nothing here is derived from that file's code; it is a new design:
+//   * a CTA owns one (batch, head) pair and a tile of queries, so the gather
+//     footprint of a tile (one head's 64/128-byte rows) stays L1-resident;
+//   * a group of GS lanes owns one (query, head) row, each lane VEC channels
+//     (16-byte loads: fp32x4 / bf16x8), several rows per warp;
+//   * spatial shapes / level starts are staged in shared memory by the CTA
+//     prologue (level starts are computed there when the caller passes none).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/msda_b200.h"
+
+namespace msda {
+
+constexpr int kMaxLevels = MSDA_MAX_LEVELS;
+
+// Per-level geometry staged in shared memory.
+struct LevelTable {
+    int H[kMaxLevels];
+    int W[kMaxLevels];
+    int start[kMaxLevels];       // first pixel of the level in the flattened pyramid
+    int tiles_x[kMaxLevels];     // 2-D tiling (encoder form): tiles per row
+    int tile_begin[kMaxLevels];  // 2-D tiling: first tile id of the level
+    int total_tiles;
+};
+
+struct KernelDims {
+    int N, S, M, D, L, Lq, P;
+    int tile_q;   // queries per tile (1-D tiling) == tile_h * tile_w (2-D tiling)
+    int tile_h;   // 2-D tiling: tile height; 0 selects 1-D tiling over the query index
+    int tile_w;
+};
+
+// Fills the level table (all threads call; ends with __syncthreads()).
+__device__ __forceinline__ void stage_levels(LevelTable& t, const int64_t* __restrict__ shapes,
+                                             const int64_t* __restrict__ level_start,
+                                             const KernelDims& d)
+{
+    if (threadIdx.x == 0) {
+        int run = 0, trun = 0;
+        for (int l = 0; l < d.L; ++l) {
+            const int H = (int)shapes[2 * l], W = (int)shapes[2 * l + 1];
+            t.H[l] = H;
+            t.W[l] = W;
+            t.start[l] = level_start ? (int)level_start[l] : run;
+            run += H * W;
+            if (d.tile_h > 0) {
+                const int tx = (W + d.tile_w - 1) / d.tile_w;
+                const int ty = (H + d.tile_h - 1) / d.tile_h;
+                t.tiles_x[l] = tx;
+                t.tile_begin[l] = trun;
+                trun += tx * ty;
+            }
+        }
+        t.total_tiles = d.tile_h > 0 ? trun : (d.Lq + d.tile_q - 1) / d.tile_q;
+    }
+    __syncthreads();
+}
+
+// Query index of slot i of tile `tile`, or -1 when the slot is empty.
+__device__ __forceinline__ int tile_query(const LevelTable& t, const KernelDims& d, int tile, int i)
+{
+    if (d.tile_h == 0) {
+        const int q = tile * d.tile_q + i;
+        return q < d.Lq ? q : -1;
+    }
+    int l = 0;
+    while (l + 1 < d.L && tile >= t.tile_begin[l + 1]) ++l;
+    const int rel = tile - t.tile_begin[l];
+    const int ty = rel / t.tiles_x[l], tx = rel - ty * t.tiles_x[l];
+    const int iy = i / d.tile_w, ix = i - iy * d.tile_w;
+    const int y = ty * d.tile_h + iy, x = tx * d.tile_w + ix;
+    if (y >= t.H[l] || x >= t.W[l]) return -1;
+    return t.start[l] + y * t.W[l] + x;
+}
+
+// ---- element conversion -------------------------------------------------------------
+template <typename T> __device__ __forceinline__ float to_f32(T v);
+template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <> __device__ __forceinline__ float to_f32<__half>(__half v) { return __half2float(v); }
+
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
+
+// ---- vector loads of VEC consecutive channels into fp32 registers ---------------------
+// Read-only path with L1 allocation (gathered rows are re-used by neighbouring queries).
+template <typename T, int VEC> struct VecIO;
+
+template <> struct VecIO<float, 4> {
+    static __device__ __forceinline__ void load(const float* p, float (&v)[4]) {
+        const float4 r = __ldg(reinterpret_cast<const float4*>(p));
+        v[0] = r.x; v[1] = r.y; v[2] = r.z; v[3] = r.w;
+    }
+    static __device__ __forceinline__ void load_stream(const float* p, float (&v)[4]) {
+        float4 r;
+        asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+        v[0] = r.x; v[1] = r.y; v[2] = r.z; v[3] = r.w;
+    }
+    static __device__ __forceinline__ void store(float* p, const float (&v)[4]) {
+        asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};"
+                     :: "l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]) : "memory");
+    }
+};
+
+__device__ __forceinline__ void unpack_bf16x2(uint32_t w, float& lo, float& hi) {
+    lo = __uint_as_float(w << 16);
+    hi = __uint_as_float(w & 0xffff0000u);
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+__device__ __forceinline__ void unpack_f16x2(uint32_t w, float& lo, float& hi) {
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w));
+    lo = f.x; hi = f.y;
+}
+__device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
+    const __half2 h = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+template <typename T> struct Half2Codec;
+template <> struct Half2Codec<__nv_bfloat16> {
+    static __device__ __forceinline__ void unpack(uint32_t w, float& a, float& b) { unpack_bf16x2(w, a, b); }
+    static __device__ __forceinline__ uint32_t pack(float a, float b) { return pack_bf16x2(a, b); }
+};
+template <> struct Half2Codec<__half> {
+    static __device__ __forceinline__ void unpack(uint32_t w, float& a, float& b) { unpack_f16x2(w, a, b); }
+    static __device__ __forceinline__ uint32_t pack(float a, float b) { return pack_f16x2(a, b); }
+};
+
+template <typename T> struct VecIO<T, 8> {  // 16-bit types, 16-byte vectors
+    static __device__ __forceinline__ void load(const T* p, float (&v)[8]) {
+        const uint4 r = __ldg(reinterpret_cast<const uint4*>(p));
+        Half2Codec<T>::unpack(r.x, v[0], v[1]); Half2Codec<T>::unpack(r.y, v[2], v[3]);
+        Half2Codec<T>::unpack(r.z, v[4], v[5]); Half2Codec<T>::unpack(r.w, v[6], v[7]);
+    }
+    static __device__ __forceinline__ void load_stream(const T* p, float (&v)[8]) {
+        uint4 r;
+        asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+        Half2Codec<T>::unpack(r.x, v[0], v[1]); Half2Codec<T>::unpack(r.y, v[2], v[3]);
+        Half2Codec<T>::unpack(r.z, v[4], v[5]); Half2Codec<T>::unpack(r.w, v[6], v[7]);
+    }
+    static __device__ __forceinline__ void store(T* p, const float (&v)[8]) {
+        const uint32_t a = Half2Codec<T>::pack(v[0], v[1]), b = Half2Codec<T>::pack(v[2], v[3]);
+        const uint32_t c = Half2Codec<T>::pack(v[4], v[5]), d = Half2Codec<T>::pack(v[6], v[7]);
+        asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
+                     :: "l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+    }
+};
+
+template <typename T> struct VecIO<T, 4> {  // 16-bit types, 8-byte vectors (D = 36)
+    static __device__ __forceinline__ void load(const T* p, float (&v)[4]) {
+        const uint2 r = __ldg(reinterpret_cast<const uint2*>(p));
+        Half2Codec<T>::unpack(r.x, v[0], v[1]); Half2Codec<T>::unpack(r.y, v[2], v[3]);
+    }
+    static __device__ __forceinline__ void load_stream(const T* p, float (&v)[4]) {
+        uint2 r;
+        asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];"
+                     : "=r"(r.x), "=r"(r.y) : "l"(p));
+        Half2Codec<T>::unpack(r.x, v[0], v[1]); Half2Codec<T>::unpack(r.y, v[2], v[3]);
+    }
+    static __device__ __forceinline__ void store(T* p, const float (&v)[4]) {
+        const uint32_t a = Half2Codec<T>::pack(v[0], v[1]), b = Half2Codec<T>::pack(v[2], v[3]);
+        asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};"
+                     :: "l"(p), "r"(a), "r"(b) : "memory");
+    }
+};
+
+// Vector fp32 reduction into global memory (sm_90+): one instruction adds 16 bytes.
+__device__ __forceinline__ void red_add_f32x4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// Streaming scalar loads of the per-sample metadata (read exactly once).
+template <typename A> __device__ __forceinline__ float2 load_loc(const A* p);
+template <> __device__ __forceinline__ float2 load_loc<float>(const float* p) {
+    float2 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.f32 {%0,%1}, [%2];" : "=f"(r.x), "=f"(r.y) : "l"(p));
+    return r;
+}
+template <> __device__ __forceinline__ float2 load_loc<__nv_bfloat16>(const __nv_bfloat16* p) {
+    uint32_t w;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(w) : "l"(p));
+    float2 r; unpack_bf16x2(w, r.x, r.y); return r;
+}
+template <> __device__ __forceinline__ float2 load_loc<__half>(const __half* p) {
+    uint32_t w;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(w) : "l"(p));
+    float2 r; unpack_f16x2(w, r.x, r.y); return r;
+}
+template <typename A> __device__ __forceinline__ float load_attn(const A* p) { return to_f32<A>(__ldg(p)); }
+
+template <typename A> __device__ __forceinline__ void store_loc(A* p, float x, float y);
+template <> __device__ __forceinline__ void store_loc<float>(float* p, float x, float y) {
+    *reinterpret_cast<float2*>(p) = make_float2(x, y);
+}
+template <> __device__ __forceinline__ void store_loc<__nv_bfloat16>(__nv_bfloat16* p, float x, float y) {
+    *reinterpret_cast<uint32_t*>(p) = pack_bf16x2(x, y);
+}
+template <> __device__ __forceinline__ void store_loc<__half>(__half* p, float x, float y) {
+    *reinterpret_cast<uint32_t*>(p) = pack_f16x2(x, y);
+}
+
+// One bilinear tap: the four corner rows (element offsets from the (batch, head)
+// base, -1 = outside the level) and their weights.
+struct Tap {
+    int off[4];
+    float lh, lw, hh, hw;
+    bool inside;
+};
+
+__device__ __forceinline__ Tap make_tap(float lx, float ly, int H, int W, int start, int row_stride)
+{
+    Tap t;
+    const float x = fmaf(lx, (float)W, -0.5f);
+    const float y = fmaf(ly, (float)H, -0.5f);
+    t.inside = (y > -1.f) && (x > -1.f) && (y < (float)H) && (x < (float)W);
+    const float fy = floorf(y), fx = floorf(x);
+    const int y0 = (int)fy, x0 = (int)fx;
+    t.lh = y - fy; t.lw = x - fx;
+    t.hh = 1.f - t.lh; t.hw = 1.f - t.lw;
+    const bool yl = y0 >= 0, yh = y0 + 1 <= H - 1, xl = x0 >= 0, xh = x0 + 1 <= W - 1;
+    const int base = (start + y0 * W + x0) * row_stride;
+    t.off[0] = (t.inside && yl && xl) ? base : -1;
+    t.off[1] = (t.inside && yl && xh) ? base + row_stride : -1;
+    t.off[2] = (t.inside && yh && xl) ? base + W * row_stride : -1;
+    t.off[3] = (t.inside && yh && xh) ? base + (W + 1) * row_stride : -1;
+    return t;
+}
+
+}  // namespace msda

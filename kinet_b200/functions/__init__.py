@@ -1,0 +1,6 @@
+from .ms_deform_attn_func import (  # noqa: F401
+    MSDeformAttnFunction,
+    ms_deform_attn_backward,
+    ms_deform_attn_core_pytorch,
+    ms_deform_attn_forward,
+)

@@ -1,0 +1,189 @@
+"""MSDeformAttnFunction -- autograd wrapper over the sm_100a kernels.
+
+Mirrors the reference's src/trackformer/models/ops/functions/ms_deform_attn_func.py:
+``MSDeformAttnFunction.apply(value, value_spatial_shapes, sampling_locations,
+attention_weights, im2col_step)`` (:14-31, the 5-argument form the reference's
+MSDeformAttn module uses) and additionally accepts the upstream Deformable-DETR
+6-argument form with ``value_level_start_index`` in position 2.
+
+The two module-level functions ``ms_deform_attn_forward`` / ``ms_deform_attn_backward``
+have the signatures of the reference's native extension (src/vision.cpp:4-7,
+src/ms_deform_attn.h:10-49) and are what MultiScaleDeformableAttention.py (the
+drop-in shim for ``import MultiScaleDeformableAttention as MSDA``) re-exports.
+
+There is no CPU path: CPU tensors raise, like the reference (ms_deform_attn.h:27,48).
+"""
+import ctypes
+
+import torch
+import torch.nn.functional as F
+from torch.autograd import Function
+from torch.autograd.function import once_differentiable
+
+from .. import _lib
+
+
+def _dims(value, loc):
+    N, S, M, D = value.shape
+    _, Lq, M2, L, P, two = loc.shape
+    if M2 != M or two != 2 or loc.shape[0] != N:
+        raise RuntimeError("sampling_loc must be (N, Lq, M, L, P, 2) matching value (N, S, M, D)")
+    return _lib.MsdaDims(N, S, M, D, L, Lq, P)
+
+
+def _check_inputs(value, spatial_shapes, sampling_loc, attn_weight, im2col_step):
+    # same preconditions and order as ms_deform_attn_cuda.cu:29-34,46-48
+    if not value.is_cuda:
+        raise RuntimeError("Not implemented on the CPU")
+    if not value.is_contiguous():
+        raise RuntimeError("value tensor has to be contiguous")
+    if not spatial_shapes.is_cuda:
+        raise RuntimeError("spatial_shapes must be a CUDA tensor")
+    if not sampling_loc.is_cuda:
+        raise RuntimeError("sampling_loc must be a CUDA tensor")
+    if not attn_weight.is_cuda:
+        raise RuntimeError("attn_weight must be a CUDA tensor")
+    batch = value.shape[0]
+    step = min(batch, int(im2col_step))
+    if step <= 0 or batch % step != 0:
+        raise RuntimeError("batch(%d) must divide im2col_step(%d)" % (batch, step))
+    if value.dim() != 4 or sampling_loc.dim() != 6 or attn_weight.dim() != 5:
+        raise RuntimeError("expected value (N,S,M,D), sampling_loc (N,Lq,M,L,P,2), attn_weight (N,Lq,M,L,P)")
+    if spatial_shapes.dim() != 2 or spatial_shapes.shape[0] != sampling_loc.shape[3]:
+        raise RuntimeError("spatial_shapes must be (L, 2)")
+    if tuple(attn_weight.shape) != tuple(sampling_loc.shape[:5]):
+        raise RuntimeError("attn_weight shape must equal sampling_loc.shape[:5]")
+
+
+def _aux_dtype(value, sampling_loc, attn_weight):
+    """dtype the kernels read loc/attn in: the value dtype when both already have it, else fp32
+    (fp64 stays fp64).  Sampling locations in bf16 would cost ~0.3 px at W=167, so mixed
+    inputs are promoted, never demoted."""
+    if value.dtype == torch.float64:
+        return torch.float64
+    if value.dtype == torch.float32:
+        return torch.float32
+    if sampling_loc.dtype == value.dtype and attn_weight.dtype == value.dtype:
+        return value.dtype
+    return torch.float32
+
+
+def _prep(value, spatial_shapes, level_start_index, sampling_loc, attn_weight):
+    aux = _aux_dtype(value, sampling_loc, attn_weight)
+    loc = sampling_loc.to(aux).contiguous()
+    attn = attn_weight.to(aux).contiguous()
+    shapes = spatial_shapes.to(torch.int64).contiguous()
+    lsi = None
+    if level_start_index is not None:
+        lsi = level_start_index.to(device=value.device, dtype=torch.int64).contiguous()
+    return aux, loc, attn, shapes, lsi
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None and t.numel() > 0 else ctypes.c_void_p(0)
+
+
+def ms_deform_attn_forward(value, spatial_shapes, sampling_loc, attn_weight, im2col_step,
+                           level_start_index=None):
+    """-> output (N, Lq, M*D).  Reference: ms_deform_attn_cuda_forward (ms_deform_attn_cuda.cu:19-86)."""
+    _check_inputs(value, spatial_shapes, sampling_loc, attn_weight, im2col_step)
+    lib = _lib.load()
+    aux, loc, attn, shapes, lsi = _prep(value, spatial_shapes, level_start_index, sampling_loc, attn_weight)
+    dims = _dims(value, loc)
+    out = torch.empty((dims.N, dims.Lq, dims.M * dims.D), dtype=value.dtype, device=value.device)
+    with torch.cuda.device(value.device):
+        stream = torch.cuda.current_stream().cuda_stream
+        rc = lib.msda_b200_forward(_ptr(value), _lib.dtype_code(value.dtype), _ptr(shapes), _ptr(lsi),
+                                   _ptr(loc), _ptr(attn), _lib.dtype_code(aux), _ptr(out),
+                                   ctypes.byref(dims), ctypes.c_void_p(stream))
+    _lib.check(rc, "ms_deform_attn_forward")
+    return out
+
+
+def ms_deform_attn_backward(value, spatial_shapes, sampling_loc, attn_weight, grad_output, im2col_step,
+                            level_start_index=None):
+    """-> [grad_value, grad_sampling_loc, grad_attn_weight].
+    Reference: ms_deform_attn_cuda_backward (ms_deform_attn_cuda.cu:89-168)."""
+    _check_inputs(value, spatial_shapes, sampling_loc, attn_weight, im2col_step)
+    if not grad_output.is_cuda:
+        raise RuntimeError("grad_output must be a CUDA tensor")
+    lib = _lib.load()
+    aux, loc, attn, shapes, lsi = _prep(value, spatial_shapes, level_start_index, sampling_loc, attn_weight)
+    dims = _dims(value, loc)
+    go = grad_output.to(value.dtype).contiguous()
+    grad_value = torch.empty_like(value)
+    grad_loc = torch.empty_like(loc)
+    grad_attn = torch.empty_like(attn)
+    vcode = _lib.dtype_code(value.dtype)
+    ws_bytes = int(lib.msda_b200_backward_workspace_bytes(vcode, ctypes.byref(dims)))
+    ws = torch.empty(ws_bytes // 4, dtype=torch.float32, device=value.device) if ws_bytes else None
+    with torch.cuda.device(value.device):
+        stream = torch.cuda.current_stream().cuda_stream
+        rc = lib.msda_b200_backward(_ptr(value), vcode, _ptr(shapes), _ptr(lsi), _ptr(loc), _ptr(attn),
+                                    _lib.dtype_code(aux), _ptr(go), _ptr(grad_value), _ptr(grad_loc),
+                                    _ptr(grad_attn), _ptr(ws), ctypes.c_size_t(ws_bytes),
+                                    ctypes.byref(dims), ctypes.c_void_p(stream))
+    _lib.check(rc, "ms_deform_attn_backward")
+    if grad_loc.dtype != sampling_loc.dtype:
+        grad_loc = grad_loc.to(sampling_loc.dtype)
+    if grad_attn.dtype != attn_weight.dtype:
+        grad_attn = grad_attn.to(attn_weight.dtype)
+    return [grad_value, grad_loc, grad_attn]
+
+
+class MSDeformAttnFunction(Function):
+    """apply(value, spatial_shapes, sampling_locations, attention_weights, im2col_step)   [reference]
+    apply(value, spatial_shapes, level_start_index, sampling_locations, attention_weights,
+          im2col_step)                                                                   [upstream]"""
+
+    @staticmethod
+    def forward(ctx, *args):
+        if len(args) == 5:
+            value, shapes, loc, attn, im2col_step = args
+            lsi = None
+        elif len(args) == 6:
+            value, shapes, lsi, loc, attn, im2col_step = args
+        else:
+            raise TypeError("MSDeformAttnFunction.apply takes 5 (reference) or 6 (upstream) arguments, got %d"
+                            % len(args))
+        ctx.im2col_step = im2col_step
+        ctx.nargs = len(args)
+        output = ms_deform_attn_forward(value, shapes, loc, attn, im2col_step, lsi)
+        if lsi is None:
+            ctx.save_for_backward(value, shapes, loc, attn)
+        else:
+            ctx.save_for_backward(value, shapes, loc, attn, lsi)
+        return output
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, grad_output):
+        saved = ctx.saved_tensors
+        value, shapes, loc, attn = saved[:4]
+        lsi = saved[4] if len(saved) == 5 else None
+        grad_value, grad_loc, grad_attn = ms_deform_attn_backward(
+            value, shapes, loc, attn, grad_output, ctx.im2col_step, lsi)
+        if ctx.nargs == 5:
+            return grad_value, None, grad_loc, grad_attn, None
+        return grad_value, None, None, grad_loc, grad_attn, None
+
+
+def ms_deform_attn_core_pytorch(value, value_spatial_shapes, sampling_locations, attention_weights):
+    """Debug/test helper with the reference's name (ms_deform_attn_func.py:34-54): per-level
+    ``F.grid_sample`` + weighted sum in plain PyTorch.  It is NOT used by MSDeformAttn or
+    MSDeformAttnFunction -- those always run the CUDA kernels -- and exists so code that imports
+    this name from the ops package keeps working."""
+    N, S, M, D = value.shape
+    Lq, L, P = sampling_locations.shape[1], sampling_locations.shape[3], sampling_locations.shape[4]
+    sizes = [(int(h), int(w)) for h, w in value_spatial_shapes.tolist()]
+    per_head = value.permute(0, 2, 3, 1).reshape(N * M, D, S)
+    grid = (sampling_locations * 2 - 1).permute(0, 2, 1, 3, 4, 5).reshape(N * M, Lq, L, P, 2)
+    taps, off = [], 0
+    for lvl, (h, w) in enumerate(sizes):
+        img = per_head[:, :, off:off + h * w].reshape(N * M, D, h, w)
+        off += h * w
+        taps.append(F.grid_sample(img, grid[:, :, lvl], mode="bilinear", padding_mode="zeros",
+                                  align_corners=False))
+    taps = torch.cat(taps, dim=-1)
+    wts = attention_weights.permute(0, 2, 1, 3, 4).reshape(N * M, 1, Lq, L * P)
+    return (taps * wts).sum(-1).reshape(N, M * D, Lq).transpose(1, 2).contiguous()

@@ -1,0 +1,100 @@
+"""MSDeformAttn -- the operator module, mirroring the reference's
+src/trackformer/models/ops/modules/ms_deform_attn.py:15-89 (same constructor, parameter
+names/shapes/initialisation, forward signature incl. ``query_attn_mask``), so TrackFormer /
+KineTTracker checkpoints load unchanged and deformable_transformer.py can import it as is.
+
+The four Linear layers stay cuBLAS GEMMs; the sampling + weighted reduction runs in the
+sm_100a kernels through MSDeformAttnFunction.  Reference quirk kept on purpose: 2-d reference
+points are normalised by ``input_spatial_shapes`` in (H, W) order (:77-79), i.e. the x offset is
+divided by H and the y offset by W -- upstream Deformable-DETR flips to (W, H); the reference
+does not, and parity is defined against the reference.
+"""
+
+import torch
+import torch.nn.functional as F
+from torch import nn
+from torch.nn.init import constant_, xavier_uniform_
+
+from ..functions import MSDeformAttnFunction
+
+
+class MSDeformAttn(nn.Module):
+    def __init__(self, d_model=256, n_levels=4, n_heads=8, n_points=4, im2col_step=64):
+        super().__init__()
+        assert d_model % n_heads == 0
+
+        self.im2col_step = im2col_step
+        self.d_model = d_model
+        self.n_levels = n_levels
+        self.n_heads = n_heads
+        self.n_points = n_points
+
+        self.sampling_offsets = nn.Linear(d_model, n_heads * n_levels * n_points * 2)
+        self.attention_weights = nn.Linear(d_model, n_heads * n_levels * n_points)
+        self.value_proj = nn.Linear(d_model, d_model)
+        self.output_proj = nn.Linear(d_model, d_model)
+
+        self._reset_parameters()
+
+    def _reset_parameters(self):
+        # reference :34-47: zero offset weights; bias = the 8 compass directions cycled over the
+        # heads, scaled by (point index + 1); zero attention logits; xavier projections.
+        constant_(self.sampling_offsets.weight.data, 0.)
+        compass = torch.tensor([[-1., -1.], [-1., 0.], [-1., 1.], [0., -1.],
+                                [0., 1.], [1., -1.], [1., 0.], [1., 1.]])
+        # the reference's .view(n_heads, 1, 1, 2) of a 16-element tensor fixes n_heads == 8
+        assert self.n_heads == 8, "the reference initialisation (ms_deform_attn.py:36-37) requires n_heads == 8"
+        grid_init = compass.view(self.n_heads, 1, 1, 2).repeat(1, self.n_levels, self.n_points, 1)
+        scale = torch.arange(1, self.n_points + 1, dtype=torch.float32).view(1, 1, self.n_points, 1)
+        grid_init = grid_init * scale
+        with torch.no_grad():
+            self.sampling_offsets.bias = nn.Parameter(grid_init.reshape(-1))
+        constant_(self.attention_weights.weight.data, 0.)
+        constant_(self.attention_weights.bias.data, 0.)
+        xavier_uniform_(self.value_proj.weight.data)
+        constant_(self.value_proj.bias.data, 0.)
+        xavier_uniform_(self.output_proj.weight.data)
+        constant_(self.output_proj.bias.data, 0.)
+
+    def forward(self, query, reference_points, input_flatten, input_spatial_shapes,
+                input_padding_mask=None, query_attn_mask=None):
+        """
+        query (N, Lq, C); reference_points (N, Lq, L, 2) in [0,1] or (N, Lq, L, 4) boxes;
+        input_flatten (N, S, C); input_spatial_shapes (L, 2) [(H_l, W_l)];
+        input_padding_mask (N, S) True = padding; query_attn_mask (N, Lq) True = masked query.
+        -> (N, Lq, C)
+        """
+        N, Len_q, _ = query.shape
+        N, Len_in, _ = input_flatten.shape
+        assert (input_spatial_shapes[:, 0] * input_spatial_shapes[:, 1]).sum() == Len_in
+
+        value = self.value_proj(input_flatten)
+        if input_padding_mask is not None:
+            value = value.masked_fill(input_padding_mask[..., None], float(0))
+        value = value.view(N, Len_in, self.n_heads, self.d_model // self.n_heads)
+
+        sampling_offsets = self.sampling_offsets(query).view(
+            N, Len_q, self.n_heads, self.n_levels, self.n_points, 2)
+        attention_weights = self.attention_weights(query).view(
+            N, Len_q, self.n_heads, self.n_levels * self.n_points)
+        attention_weights = F.softmax(attention_weights, -1).view(
+            N, Len_q, self.n_heads, self.n_levels, self.n_points)
+
+        if query_attn_mask is not None:
+            attention_weights = attention_weights.masked_fill(
+                query_attn_mask[..., None, None, None], float(0))
+
+        if reference_points.shape[-1] == 2:
+            sampling_locations = reference_points[:, :, None, :, None, :] \
+                + sampling_offsets / input_spatial_shapes[None, None, None, :, None, :]
+        elif reference_points.shape[-1] == 4:
+            sampling_locations = reference_points[:, :, None, :, None, :2] \
+                + sampling_offsets / self.n_points * reference_points[:, :, None, :, None, 2:] * 0.5
+        else:
+            raise ValueError(
+                'Last dim of reference_points must be 2 or 4, but get {} instead.'.format(
+                    reference_points.shape[-1]))
+        output = MSDeformAttnFunction.apply(
+            value, input_spatial_shapes, sampling_locations, attention_weights, self.im2col_step)
+        output = self.output_proj(output)
+        return output

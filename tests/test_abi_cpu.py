@@ -1,0 +1,74 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads, exports every symbol that
+include/msda_b200.h declares, and refuses to compute without a CUDA device (no CPU fallback)."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from kinet_b200 import build
+    build.build()
+    from kinet_b200 import _lib
+    return _lib.load()
+
+
+def test_header_symbols_are_exported(lib):
+    hdr = open(os.path.join(ROOT, "include", "msda_b200.h")).read()
+    declared = set(re.findall(r"\b(msda_b200_\w+)\s*\(", hdr))
+    assert {"msda_b200_forward", "msda_b200_backward", "msda_b200_backward_workspace_bytes",
+            "msda_b200_error_string", "msda_b200_abi_version",
+            "msda_b200_last_launch_count"} <= declared
+    for name in declared:
+        assert hasattr(lib, name), name
+    from kinet_b200 import _lib
+    assert set(_lib.EXPORTS) == declared
+
+
+def test_abi_version_and_error_strings(lib):
+    assert lib.msda_b200_abi_version() == 1
+    assert lib.msda_b200_error_string(0) == b"success"
+    for code in (-1, -2, -3, -4, -5):
+        assert lib.msda_b200_error_string(code).startswith(b"msda_b200:")
+
+
+def test_workspace_size(lib):
+    from kinet_b200._lib import MsdaDims, MSDA_BF16, MSDA_F32
+    d = MsdaDims(2, 100, 8, 32, 4, 7, 4)
+    assert lib.msda_b200_backward_workspace_bytes(MSDA_F32, ctypes.byref(d)) == 0
+    assert lib.msda_b200_backward_workspace_bytes(MSDA_BF16, ctypes.byref(d)) == 2 * 100 * 8 * 32 * 4
+
+
+def test_argument_validation_without_gpu(lib):
+    from kinet_b200._lib import MsdaDims
+    d = MsdaDims(2, 100, 8, 32, 4, 7, 4)
+    null = ctypes.c_void_p(0)
+    assert lib.msda_b200_forward(null, 0, null, null, null, null, 0, null, ctypes.byref(d), null) == -3
+    bad = MsdaDims(2, 100, 8, 32, 99, 7, 4)
+    one = ctypes.c_void_p(16)
+    assert lib.msda_b200_forward(one, 0, one, null, one, one, 0, one, ctypes.byref(bad), null) == -2
+    assert lib.msda_b200_forward(one, 7, one, null, one, one, 0, one, ctypes.byref(d), null) == -1
+
+
+def test_cpu_tensors_raise_like_the_reference():
+    from kinet_b200.functions import MSDeformAttnFunction
+    value = torch.zeros(1, 4, 1, 4)
+    shapes = torch.tensor([[2, 2]])
+    loc = torch.zeros(1, 1, 1, 1, 1, 2)
+    attn = torch.ones(1, 1, 1, 1, 1)
+    with pytest.raises(RuntimeError, match="Not implemented on the CPU"):
+        MSDeformAttnFunction.apply(value, shapes, loc, attn, 64)
+
+
+def test_product_never_imports_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "kinet_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f
+                assert "msda_oracle" not in src, f

@@ -1,0 +1,268 @@
+"""Parity of the sm_100a kernels (called through the C ABI, libmsda_b200.so) against the CPU
+oracle and the reference's golden vectors.  All tests need a B200: ``-m gpu``.
+
+Tolerances (north_star: 1e-5 relative in fp32; bf16 tolerance stated here):
+  fp32: max|err| <= 1e-5 * max|ref| against the fp64 oracle on the same fp32 inputs
+        (grad_value: atomic summation order varies run to run; same bound holds).
+  fp64: 1e-11 relative.
+  bf16/f16 value: inputs rounded to the 16-bit type first; compared with the fp64 oracle on the
+        rounded inputs: max|err| <= 1.2e-2 * max|ref| (output rounding 2^-9 plus, for
+        grad_sampling_loc, cancellation in corner differences).
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle_backward, oracle_forward
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = ["recipe_f32", "recipe_f64", "edges_f32", "edges_f64", "l8_f32", "integer_f64"]
+
+
+def _dev():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return torch.device("cuda:0")
+
+
+def _relerr(a, ref):
+    a = np.asarray(a, dtype=np.float64)
+    ref = np.asarray(ref, dtype=np.float64)
+    scale = max(np.abs(ref).max(), 1e-30) if ref.size else 1.0
+    return (np.abs(a - ref).max() / scale) if ref.size else 0.0
+
+
+def _run_cuda(value, shapes, loc, attn, grad_out=None, level_start=None):
+    from kinet_b200.functions import ms_deform_attn_backward, ms_deform_attn_forward
+    out = ms_deform_attn_forward(value, shapes, loc, attn, 64, level_start)
+    grads = None
+    if grad_out is not None:
+        grads = ms_deform_attn_backward(value, shapes, loc, attn, grad_out, 64, level_start)
+    torch.cuda.synchronize()
+    return out, grads
+
+
+def _oracle64(value, shapes, loc, attn, grad_out=None):
+    v = value.detach().double().cpu().numpy()
+    l = loc.detach().double().cpu().numpy()
+    a = attn.detach().double().cpu().numpy()
+    s = shapes.cpu().numpy()
+    out = oracle_forward(v, s, l, a, nthreads=8)
+    grads = None
+    if grad_out is not None:
+        grads = oracle_backward(v, s, l, a, grad_out.detach().double().cpu().numpy(), nthreads=8)
+    return out, grads
+
+
+@pytest.mark.parametrize("name", GOLDEN)
+def test_golden_forward_backward(golden, name):
+    g = golden(name)
+    dev = _dev()
+    t = {k: torch.from_numpy(v).to(dev) for k, v in g.items()}
+    out, grads = _run_cuda(t["value"], t["shapes"], t["loc"], t["attn"], t["grad_out"])
+    tol = 1e-11 if name.endswith("f64") else 1e-5
+    assert out.dtype == t["value"].dtype
+    assert _relerr(out.cpu().numpy(), g["out"]) <= tol
+    assert _relerr(grads[0].cpu().numpy(), g["grad_value"]) <= tol
+    assert _relerr(grads[2].cpu().numpy(), g["grad_attn"]) <= tol
+    if name != "integer_f64":   # grad_loc is one-sided at integer coordinates (see test_oracle.py)
+        assert _relerr(grads[1].cpu().numpy(), g["grad_loc"]) <= tol
+
+
+def _random_case(dev, N, M, D, Lq, levels, P, dtype=torch.float32, aux=None, spread=1.2, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    L = len(levels)
+    S = sum(h * w for h, w in levels)
+    aux = aux or (torch.float32 if dtype != torch.float64 else torch.float64)
+    value = torch.randn(N, S, M, D, generator=g).to(dtype).to(dev)
+    shapes = torch.as_tensor(levels, dtype=torch.int64, device=dev)
+    loc = (torch.rand(N, Lq, M, L, P, 2, generator=g) * spread - (spread - 1) / 2).to(aux).to(dev)
+    attn = torch.softmax(torch.randn(N, Lq, M, L * P, generator=g), -1).view(N, Lq, M, L, P).to(aux).to(dev)
+    go = torch.randn(N, Lq, M * D, generator=g).to(dtype).to(dev)
+    return value, shapes, loc, attn, go
+
+
+VEC_CASES = [
+    # (N, M, D, Lq, levels, P)
+    (2, 8, 32, 37, [(9, 13), (5, 7), (3, 4), (2, 2)], 4),            # D=32 fast path, ragged Lq
+    (1, 8, 36, 29, [(7, 11), (4, 6)] * 4, 4),                         # D=36 (GS=9), L=8
+    (2, 4, 64, 19, [(6, 5), (3, 3)], 3),                              # D=64, P=3 (LP=6 < GS)
+    (1, 2, 16, 70, [(10, 10)], 5),                                    # D=16, L=1, P=5
+    (1, 3, 20, 11, [(4, 9), (2, 5)], 2),                              # D=20 -> generic path
+    (3, 8, 32, 1, [(3, 3)], 1),                                       # single query, single sample
+]
+
+
+@pytest.mark.parametrize("case", VEC_CASES)
+def test_fp32_matches_oracle(case):
+    dev = _dev()
+    N, M, D, Lq, levels, P = case
+    value, shapes, loc, attn, go = _random_case(dev, N, M, D, Lq, levels, P)
+    out, grads = _run_cuda(value, shapes, loc, attn, go)
+    ref_out, ref_grads = _oracle64(value, shapes, loc, attn, go)
+    assert _relerr(out.cpu().numpy(), ref_out) <= 1e-5
+    for got, ref in zip(grads, ref_grads):
+        assert got.shape == ref.shape
+        assert _relerr(got.cpu().numpy(), ref) <= 1e-5
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("aux_same", [False, True])
+@pytest.mark.parametrize("case", VEC_CASES[:5])
+def test_16bit_matches_oracle(case, dtype, aux_same):
+    dev = _dev()
+    N, M, D, Lq, levels, P = case
+    aux = dtype if aux_same else torch.float32
+    value, shapes, loc, attn, go = _random_case(dev, N, M, D, Lq, levels, P, dtype=dtype, aux=aux)
+    out, grads = _run_cuda(value, shapes, loc, attn, go)
+    assert out.dtype == dtype and grads[0].dtype == dtype
+    assert grads[1].dtype == aux and grads[2].dtype == aux
+    ref_out, ref_grads = _oracle64(value, shapes, loc, attn, go)
+    tol = 1.2e-2
+    assert _relerr(out.float().cpu().numpy(), ref_out) <= tol
+    for got, ref in zip(grads, ref_grads):
+        assert _relerr(got.float().cpu().numpy(), ref) <= tol
+
+
+def test_fp64_generic_matches_oracle():
+    dev = _dev()
+    value, shapes, loc, attn, go = _random_case(dev, 2, 2, 4, 5, [(12, 8), (6, 4), (3, 2)], 2,
+                                                dtype=torch.float64)
+    out, grads = _run_cuda(value, shapes, loc, attn, go)
+    ref_out, ref_grads = _oracle64(value, shapes, loc, attn, go)
+    assert _relerr(out.cpu().numpy(), ref_out) <= 1e-12
+    for got, ref in zip(grads, ref_grads):
+        assert _relerr(got.cpu().numpy(), ref) <= 1e-12
+
+
+def test_encoder_form_2d_tiling_matches_oracle():
+    """Lq == S switches the kernels to 2-D query tiles; result must not depend on the tiling."""
+    dev = _dev()
+    levels = [(37, 45), (19, 23), (10, 12), (5, 6)]
+    S = sum(h * w for h, w in levels)
+    value, shapes, loc, attn, go = _random_case(dev, 2, 8, 32, S, levels, 4, spread=1.1)
+    out, grads = _run_cuda(value, shapes, loc, attn, go)
+    ref_out, ref_grads = _oracle64(value, shapes, loc, attn, go)
+    assert _relerr(out.cpu().numpy(), ref_out) <= 1e-5
+    for got, ref in zip(grads, ref_grads):
+        assert _relerr(got.cpu().numpy(), ref) <= 1e-5
+
+
+def test_level_start_index_argument_and_6arg_form():
+    from kinet_b200.functions import MSDeformAttnFunction
+    dev = _dev()
+    levels = [(9, 13), (5, 7), (3, 4)]
+    value, shapes, loc, attn, go = _random_case(dev, 2, 8, 32, 21, levels, 4)
+    lsi = torch.cat([shapes.new_zeros(1), (shapes[:, 0] * shapes[:, 1]).cumsum(0)[:-1]])
+    o5 = MSDeformAttnFunction.apply(value, shapes, loc, attn, 64)
+    o6 = MSDeformAttnFunction.apply(value, shapes, lsi, loc, attn, 64)
+    assert torch.equal(o5, o6)
+
+
+def test_autograd_matches_oracle_and_reference_recipe():
+    """The reference's own check (ops/test.py:38-95): loss = |out|.sum(), three grads."""
+    from kinet_b200.functions import MSDeformAttnFunction
+    dev = _dev()
+    torch.manual_seed(3)
+    N, M, D, Lq, L, P = 2, 2, 4, 3, 3, 2
+    shapes = torch.as_tensor([(8, 8), (4, 4), (2, 2)], dtype=torch.long, device=dev)
+    S = 84
+    value = (torch.rand(N, S, M, D) * 0.01).to(dev).requires_grad_(True)
+    loc = torch.rand(N, Lq, M, L, P, 2).to(dev).requires_grad_(True)
+    attn = torch.rand(N, Lq, M, L, P) + 1e-5
+    attn = (attn / attn.sum(-1, keepdim=True).sum(-2, keepdim=True)).to(dev).requires_grad_(True)
+    out = MSDeformAttnFunction.apply(value, shapes, loc, attn, 2)
+    out.abs().sum().backward()
+    ref_out, ref_grads = _oracle64(value, shapes, loc, attn, torch.sign(out.detach()))
+    assert _relerr(out.detach().cpu().numpy(), ref_out) <= 1e-5
+    for got, ref in zip((value.grad, loc.grad, attn.grad), ref_grads):
+        assert _relerr(got.cpu().numpy(), ref) <= 1e-5
+
+
+def test_gradcheck_double():
+    """test_double_precision.py:117-119: gradcheck of the op in fp64."""
+    from kinet_b200.functions import MSDeformAttnFunction
+    dev = _dev()
+    torch.manual_seed(3)
+    shapes = torch.as_tensor([(12, 8), (6, 4), (3, 2)], dtype=torch.long, device=dev)
+    N, M, D, Lq, L, P, S = 2, 2, 4, 3, 3, 2, 126
+    value = (torch.rand(N, S, M, D, dtype=torch.float64) * 0.01).to(dev).requires_grad_(True)
+    loc = torch.rand(N, Lq, M, L, P, 2, dtype=torch.float64).to(dev).requires_grad_(True)
+    attn = torch.rand(N, Lq, M, L, P, dtype=torch.float64) + 1e-5
+    attn = (attn / attn.sum(-1, keepdim=True).sum(-2, keepdim=True)).to(dev).requires_grad_(True)
+    assert torch.autograd.gradcheck(MSDeformAttnFunction.apply, (value, shapes, loc, attn, 2))
+
+
+def test_empty_queries_and_error_behaviour():
+    from kinet_b200.functions import MSDeformAttnFunction, ms_deform_attn_backward
+    dev = _dev()
+    value, shapes, loc, attn, go = _random_case(dev, 2, 8, 32, 0, [(4, 4)], 4)
+    out = MSDeformAttnFunction.apply(value, shapes, loc, attn, 64)
+    assert out.shape == (2, 0, 256)
+    gv, gl, ga = ms_deform_attn_backward(value, shapes, loc, attn, go, 64)
+    assert not gv.any() and gl.numel() == 0 and ga.numel() == 0
+    value, shapes, loc, attn, go = _random_case(dev, 3, 8, 32, 5, [(4, 4)], 4)
+    with pytest.raises(RuntimeError):          # batch(3) % im2col_step(2) != 0, cu:46-48
+        MSDeformAttnFunction.apply(value, shapes, loc, attn, 2)
+    with pytest.raises(RuntimeError):          # value must be contiguous, cu:29
+        MSDeformAttnFunction.apply(value.transpose(2, 3).contiguous().transpose(2, 3), shapes, loc, attn, 64)
+    with pytest.raises(RuntimeError):          # CPU tensors: "Not implemented on the CPU", ms_deform_attn.h:27
+        MSDeformAttnFunction.apply(value.cpu(), shapes.cpu(), loc.cpu(), attn.cpu(), 64)
+
+
+def test_noncontiguous_loc_attn_are_handled():
+    from kinet_b200.functions import ms_deform_attn_forward
+    dev = _dev()
+    value, shapes, loc, attn, go = _random_case(dev, 2, 8, 32, 9, [(6, 7), (3, 4)], 4)
+    loc_nc = loc.permute(0, 2, 1, 3, 4, 5).contiguous().permute(0, 2, 1, 3, 4, 5)
+    assert not loc_nc.is_contiguous()
+    assert torch.equal(ms_deform_attn_forward(value, shapes, loc_nc, attn, 64),
+                       ms_deform_attn_forward(value, shapes, loc, attn, 64))
+
+
+def test_backward_run_to_run_spread():
+    """grad_value uses floating-point reductions in global memory: order varies, spread is bounded."""
+    dev = _dev()
+    levels = [(20, 30), (10, 15)]
+    value, shapes, loc, attn, go = _random_case(dev, 1, 8, 32, 600, levels, 4, spread=1.0)
+    _, g1 = _run_cuda(value, shapes, loc, attn, go)
+    _, g2 = _run_cuda(value, shapes, loc, attn, go)
+    assert torch.equal(g1[1], g2[1]) and torch.equal(g1[2], g2[2])     # single-writer outputs
+    assert _relerr(g1[0].cpu().numpy(), g2[0].cpu().numpy()) <= 2e-6
+
+
+def test_module_matches_reference_math():
+    """MSDeformAttn (module) on the GPU vs the same module with the sampling core replaced by the
+    oracle's grid_sample port -- checks the host-side arithmetic (F4 quirk, query_attn_mask)."""
+    from kinet_b200.modules import MSDeformAttn
+    from oracle import torch_port_forward
+    dev = _dev()
+    torch.manual_seed(0)
+    levels = [(12, 17), (6, 9), (3, 5), (2, 3)]
+    S = sum(h * w for h, w in levels)
+    m = MSDeformAttn(256, 4, 8, 4).to(dev)
+    with torch.no_grad():
+        m.sampling_offsets.weight.normal_(0, 0.02)
+        m.attention_weights.weight.normal_(0, 0.5)
+    N, Lq = 2, 23
+    query = torch.randn(N, Lq, 256, device=dev)
+    src = torch.randn(N, S, 256, device=dev)
+    shapes = torch.as_tensor(levels, dtype=torch.long, device=dev)
+    pad = torch.zeros(N, S, dtype=torch.bool, device=dev)
+    pad[1, -40:] = True
+    qmask = torch.zeros(N, Lq, dtype=torch.bool, device=dev)
+    qmask[0, 3] = True
+    for ref_dim in (2, 4):
+        ref = torch.rand(N, Lq, 4, ref_dim, device=dev) * 0.6 + 0.2
+        got = m(query, ref, src, shapes, pad, qmask)
+        # replay the module's host arithmetic with the oracle core
+        value = m.value_proj(src).masked_fill(pad[..., None], 0.).view(N, S, 8, 32)
+        off = m.sampling_offsets(query).view(N, Lq, 8, 4, 4, 2)
+        aw = torch.softmax(m.attention_weights(query).view(N, Lq, 8, 16), -1).view(N, Lq, 8, 4, 4)
+        aw = aw.masked_fill(qmask[..., None, None, None], 0.)
+        if ref_dim == 2:
+            loc = ref[:, :, None, :, None, :] + off / shapes[None, None, None, :, None, :]
+        else:
+            loc = ref[:, :, None, :, None, :2] + off / 4 * ref[:, :, None, :, None, 2:] * 0.5
+        want = m.output_proj(torch_port_forward(value, shapes, loc, aw))
+        assert _relerr(got.detach().cpu().numpy(), want.detach().cpu().numpy()) <= 2e-5
