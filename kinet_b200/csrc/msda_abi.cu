@@ -88,11 +88,16 @@ KernelDims make_dims(const msda_dims* d, int rows_per_pass)
 }
 
 template <typename Kern>
-int persistent_grid(Kern kern, int threads, long long items_upper)
+int query_occupancy(Kern kern, int threads)
 {
     int occ = 1;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, 0);
-    if (occ < 1) occ = 1;
+    return occ < 1 ? 1 : occ;
+}
+
+// Persistent grid: one wave of resident CTAs (or fewer when there is less work).
+int persistent_grid(int occ, long long items_upper)
+{
     const int cap = env_int("MSDA_B200_CTAS_PER_SM", 0);
     if (cap > 0 && cap < occ) occ = cap;
     const int sms = device_info().sms > 0 ? device_info().sms : 148;
@@ -123,7 +128,8 @@ int launch_forward_vec(const void* value, const int64_t* shapes, const int64_t* 
     constexpr int NW = 8;
     const KernelDims k = make_dims(d, NW * (32 / GS));
     auto kern = msda_forward_kernel<VT, AT, VEC, GS, NW>;
-    const int grid = persistent_grid(kern, NW * 32, items_upper_bound(k));
+    static const int occ = query_occupancy(kern, NW * 32);   // once per instantiation
+    const int grid = persistent_grid(occ, items_upper_bound(k));
     kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
                                    (VT*)out, k);
     ++g_last_launches;
@@ -139,7 +145,8 @@ int launch_forward_generic(const void* value, const int64_t* shapes, const int64
     k.tile_h = 0; k.tile_w = 0; k.tile_q = 8;
     const long long rows = (long long)d->N * d->Lq * d->M;
     auto kern = msda_forward_generic_kernel<VT, AT, ACC>;
-    const int grid = persistent_grid(kern, 256, (rows + 7) / 8);
+    static const int occ = query_occupancy(kern, 256);
+    const int grid = persistent_grid(occ, (rows + 7) / 8);
     kern<<<grid, 256, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
                                (VT*)out, k);
     ++g_last_launches;
@@ -183,7 +190,8 @@ int launch_backward_vec(const void* value, const int64_t* shapes, const int64_t*
     constexpr int NW = 8;
     const KernelDims k = make_dims(d, NW * (32 / GS));
     auto kern = msda_backward_kernel<VT, AT, VEC, GS, NW>;
-    const int grid = persistent_grid(kern, NW * 32, items_upper_bound(k));
+    static const int occ = query_occupancy(kern, NW * 32);   // once per instantiation
+    const int grid = persistent_grid(occ, items_upper_bound(k));
     kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
                                    (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k);
     ++g_last_launches;
@@ -199,7 +207,8 @@ int launch_backward_generic(const void* value, const int64_t* shapes, const int6
     k.tile_h = 0; k.tile_w = 0; k.tile_q = 8;
     const long long rows = (long long)d->N * d->Lq * d->M;
     auto kern = msda_backward_generic_kernel<VT, AT, ACC>;
-    const int grid = persistent_grid(kern, 256, (rows + 7) / 8);
+    static const int occ = query_occupancy(kern, 256);
+    const int grid = persistent_grid(occ, (rows + 7) / 8);
     kern<<<grid, 256, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
                                (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k);
     ++g_last_launches;

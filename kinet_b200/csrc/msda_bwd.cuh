@@ -98,29 +98,25 @@ msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ s
                     const float ly = __shfl_sync(0xffffffffu, my_xy.y, grp_base + j);
                     const float a = __shfl_sync(0xffffffffu, my_a, grp_base + j);
                     const Tap t = make_tap(lx, ly, H, W, st, row_stride);
-                    const float w[4] = {t.hh * t.hw, t.hh * t.lw, t.lh * t.hw, t.lh * t.lw};
                     float v[4][VEC];
 #pragma unroll
+                    for (int c = 0; c < 4; ++c) VecIO<VT, VEC>::load(vbase + t.off[c], v[c]);
+                    const float w[4] = {t.wy0 * t.wx0, t.wy0 * t.wx1, t.wy1 * t.wx0, t.wy1 * t.wx1};
+                    // u[c] = <grad_out row slice, corner c>; the three sums are linear in u
+                    float u[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
                     for (int c = 0; c < 4; ++c) {
-                        if (t.off[c] >= 0) {
-                            VecIO<VT, VEC>::load(vbase + t.off[c], v[c]);
-                        } else {
 #pragma unroll
-                            for (int k = 0; k < VEC; ++k) v[c][k] = 0.f;
-                        }
+                        for (int k = 0; k < VEC; ++k) u[c] = fmaf(g[k], v[c][k], u[c]);
                     }
-                    float sa = 0.f, sx = 0.f, sy = 0.f;
-#pragma unroll
-                    for (int k = 0; k < VEC; ++k) {
-                        const float top = v[0][k], tr = v[1][k], bl = v[2][k], br = v[3][k];
-                        sa = fmaf(g[k], w[0] * top + w[1] * tr + w[2] * bl + w[3] * br, sa);
-                        sx = fmaf(g[k], t.hh * (tr - top) + t.lh * (br - bl), sx);
-                        sy = fmaf(g[k], t.hw * (bl - top) + t.lw * (br - tr), sy);
-                    }
+                    float sa = w[0] * u[0] + w[1] * u[1] + w[2] * u[2] + w[3] * u[3];
+                    // d/dx: wy0*(mx1*v01 - mx0*v00) + wy1*(mx1*v11 - mx0*v10)   (.cuh:141-160)
+                    float sx = t.wy0 * (t.mx1 * u[1] - t.mx0 * u[0]) + t.wy1 * (t.mx1 * u[3] - t.mx0 * u[2]);
+                    float sy = t.wx0 * (t.my1 * u[2] - t.my0 * u[0]) + t.wx1 * (t.my1 * u[3] - t.my0 * u[1]);
                     // scatter: grad_value[corner] += w_corner * attn * grad_out
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
-                        if (t.off[c] >= 0) {
+                        if (t.ok[c]) {
                             const float wa = w[c] * a;
 #pragma unroll
                             for (int k = 0; k < VEC; k += 4)

@@ -217,12 +217,17 @@ template <> __device__ __forceinline__ void store_loc<__half>(__half* p, float x
     *reinterpret_cast<uint32_t*>(p) = pack_f16x2(x, y);
 }
 
-// One bilinear tap: the four corner rows (element offsets from the (batch, head)
-// base, -1 = outside the level) and their weights.
+// One bilinear tap.  Corner order: (y0,x0) (y0,x1) (y1,x0) (y1,x1).
+// Offsets are ALWAYS valid addresses (coordinates clamped into the level) so the four
+// corner loads are unconditional and can be issued back to back; corners outside the
+// level, and samples outside the open window (-1,H)x(-1,W), get weight 0 instead
+// (same result as the reference's guarded loads, .cuh:36-60).
 struct Tap {
-    int off[4];
-    float lh, lw, hh, hw;
-    bool inside;
+    int off[4];        // element offsets from the (batch, head) base
+    float wy0, wy1;    // (1-lh), lh   masked by row validity
+    float wx0, wx1;    // (1-lw), lw   masked by column validity
+    float my0, my1, mx0, mx1;   // 0/1 validity masks (needed by the derivatives)
+    bool ok[4];
 };
 
 __device__ __forceinline__ Tap make_tap(float lx, float ly, int H, int W, int start, int row_stride)
@@ -230,17 +235,22 @@ __device__ __forceinline__ Tap make_tap(float lx, float ly, int H, int W, int st
     Tap t;
     const float x = fmaf(lx, (float)W, -0.5f);
     const float y = fmaf(ly, (float)H, -0.5f);
-    t.inside = (y > -1.f) && (x > -1.f) && (y < (float)H) && (x < (float)W);
+    const bool inside = (y > -1.f) && (x > -1.f) && (y < (float)H) && (x < (float)W);
     const float fy = floorf(y), fx = floorf(x);
     const int y0 = (int)fy, x0 = (int)fx;
-    t.lh = y - fy; t.lw = x - fx;
-    t.hh = 1.f - t.lh; t.hw = 1.f - t.lw;
-    const bool yl = y0 >= 0, yh = y0 + 1 <= H - 1, xl = x0 >= 0, xh = x0 + 1 <= W - 1;
-    const int base = (start + y0 * W + x0) * row_stride;
-    t.off[0] = (t.inside && yl && xl) ? base : -1;
-    t.off[1] = (t.inside && yl && xh) ? base + row_stride : -1;
-    t.off[2] = (t.inside && yh && xl) ? base + W * row_stride : -1;
-    t.off[3] = (t.inside && yh && xh) ? base + (W + 1) * row_stride : -1;
+    const float lh = y - fy, lw = x - fx;
+    const bool by0 = inside && y0 >= 0, by1 = inside && y0 + 1 <= H - 1;
+    const bool bx0 = inside && x0 >= 0, bx1 = inside && x0 + 1 <= W - 1;
+    t.my0 = by0 ? 1.f : 0.f; t.my1 = by1 ? 1.f : 0.f;
+    t.mx0 = bx0 ? 1.f : 0.f; t.mx1 = bx1 ? 1.f : 0.f;
+    t.wy0 = by0 ? 1.f - lh : 0.f; t.wy1 = by1 ? lh : 0.f;
+    t.wx0 = bx0 ? 1.f - lw : 0.f; t.wx1 = bx1 ? lw : 0.f;
+    t.ok[0] = by0 && bx0; t.ok[1] = by0 && bx1; t.ok[2] = by1 && bx0; t.ok[3] = by1 && bx1;
+    const int y0c = min(max(y0, 0), H - 1), y1c = min(max(y0 + 1, 0), H - 1);
+    const int x0c = min(max(x0, 0), W - 1), x1c = min(max(x0 + 1, 0), W - 1);
+    const int r0 = (start + y0c * W) * row_stride, r1 = (start + y1c * W) * row_stride;
+    const int c0 = x0c * row_stride, c1 = x1c * row_stride;
+    t.off[0] = r0 + c0; t.off[1] = r0 + c1; t.off[2] = r1 + c0; t.off[3] = r1 + c1;
     return t;
 }
 

@@ -69,15 +69,15 @@ msda_forward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ sh
                     const float ly = __shfl_sync(0xffffffffu, my_xy.y, grp_base + j);
                     const float a = __shfl_sync(0xffffffffu, my_a, grp_base + j);
                     const Tap t = make_tap(lx, ly, H, W, st, row_stride);
-                    const float w[4] = {t.hh * t.hw * a, t.hh * t.lw * a, t.lh * t.hw * a, t.lh * t.lw * a};
+                    const float wa0 = t.wy0 * a, wa1 = t.wy1 * a;
+                    const float w[4] = {wa0 * t.wx0, wa0 * t.wx1, wa1 * t.wx0, wa1 * t.wx1};
+                    float v[4][VEC];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) VecIO<VT, VEC>::load(vbase + t.off[c], v[c]);
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
-                        if (t.off[c] >= 0) {
-                            float v[VEC];
-                            VecIO<VT, VEC>::load(vbase + t.off[c], v);
 #pragma unroll
-                            for (int k = 0; k < VEC; ++k) acc[k] = fmaf(w[c], v[k], acc[k]);
-                        }
+                        for (int k = 0; k < VEC; ++k) acc[k] = fmaf(w[c], v[c][k], acc[k]);
                     }
                     if (++p == d.P) {
                         p = 0;

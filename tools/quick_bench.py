@@ -21,6 +21,7 @@ def time_op(fn, flush, iters, warmup=3):
         flush.zero_()                       # > L2: evicts inputs
         torch.cuda.synchronize()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda._sleep(400000)           # let the host run ahead: events then bracket GPU time only
         a.record(); fn(); b.record()
         torch.cuda.synchronize()
         ts.append(a.elapsed_time(b) * 1e3)
