@@ -37,27 +37,52 @@ __device__ __forceinline__ float group_sum(float v, int gl, int grp_base)
     }
 }
 
-// GV is the type grad_value is accumulated in (float; the fp32 workspace for 16-bit VT).
-template <typename VT, typename AT, int VEC, int GS, int NWARPS>
-__global__ void __launch_bounds__(NWARPS * 32)
-msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ shapes,
-                     const int64_t* __restrict__ level_start, const AT* __restrict__ loc,
-                     const AT* __restrict__ attn, const VT* __restrict__ grad_out,
-                     float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
-                     AT* __restrict__ grad_attn, const KernelDims d)
+// Reduce-scatter over the GS lanes of a row group (GS a power of two): on entry every lane
+// holds, for each of the N samples, 4 partial dot products; on exit lane gl holds the group
+// totals of sample gl.  log2(GS) butterfly steps that halve the number of live values, i.e.
+// 4*(GS-1) shuffles per chunk instead of 4*GS*log2(GS) for per-sample all-reduces.
+template <int N>
+__device__ __forceinline__ void reduce_scatter(float (&U)[N][4], int gl, float (&out)[4])
+{
+    if constexpr (N == 1) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) out[c] = U[0][c];
+    } else {
+        constexpr int HALF = N / 2;
+        const bool upper = (gl & HALF) != 0;
+        float K[HALF][4];
+#pragma unroll
+        for (int i = 0; i < HALF; ++i) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const float keep = upper ? U[i + HALF][c] : U[i][c];
+                const float send = upper ? U[i][c] : U[i + HALF][c];
+                K[i][c] = keep + __shfl_xor_sync(0xffffffffu, send, HALF);
+            }
+        }
+        reduce_scatter<HALF>(K, gl, out);
+    }
+}
+
+// WIDE: every level has W > 1 (uniform column step of the 2x2 footprint).
+template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE>
+__device__ __forceinline__ void backward_items(const LevelTable& lt, const VT* __restrict__ value,
+                                               const AT* __restrict__ loc, const AT* __restrict__ attn,
+                                               const VT* __restrict__ grad_out,
+                                               float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
+                                               AT* __restrict__ grad_attn, const KernelDims& d)
 {
     constexpr int GPW = 32 / GS;
     constexpr int D = VEC * GS;
+    constexpr unsigned FULL = 0xffffffffu;
+    constexpr bool POW2 = (GS & (GS - 1)) == 0;
     static_assert(VEC % 4 == 0, "vector reductions are 4 floats wide");
-    __shared__ LevelTable lt;
-    stage_levels(lt, shapes, level_start, d);
-
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int grp = lane / GS, gl = lane - grp * GS;
     const bool lane_used = grp < GPW;
     const int grp_base = grp * GS;
     const int LP = d.L * d.P;
-    const int row_stride = d.M * D;
+    const int rsv = d.M * GS;
     const int items = lt.total_tiles * d.N * d.M;
 
     for (int item = blockIdx.x; item < items; item += gridDim.x) {
@@ -65,8 +90,8 @@ msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ s
         const int bm = item - tile * (d.N * d.M);
         const int b = bm / d.M, m = bm - b * d.M;
         const size_t bbase = ((size_t)b * d.S * d.M + m) * D + gl * VEC;
-        const VT* vbase = value + bbase;
-        float* gvbase = grad_value_acc + bbase;
+        const VT* lane_base = value + bbase;
+        float* gv_base = grad_value_acc + bbase;
 
         for (int i0 = warp * GPW; i0 < d.tile_q; i0 += NWARPS * GPW) {
             const int q = (lane_used && i0 + grp < d.tile_q) ? tile_query(lt, d, tile, i0 + grp) : -1;
@@ -80,71 +105,115 @@ msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ s
             for (int k = 0; k < VEC; ++k) g[k] = 0.f;
             if (row_ok) VecIO<VT, VEC>::load_stream(grad_out + row * D + gl * VEC, g);
 
-            int l = 0, p = 0;
-            int H = lt.H[0], W = lt.W[0], st = lt.start[0];
             for (int s0 = 0; s0 < LP; s0 += GS) {
-                float2 my_xy = make_float2(-8.f, -8.f);
-                float my_a = 0.f;
-                const bool mine = row_ok && s0 + gl < LP;
+                // owner phase: lane gl prepares sample s0 + gl of its row
+                const int s = s0 + gl;
+                const bool mine = row_ok && s < LP;
+                float2 xy = make_float2(0.f, 0.f);
+                float a = 0.f;
                 if (mine) {
-                    my_xy = load_loc<AT>(lrow + (s0 + gl) * 2);
-                    my_a = load_attn<AT>(arow + s0 + gl);
+                    xy = load_loc<AT>(lrow + s * 2);
+                    a = load_attn<AT>(arow + s);
                 }
-                float out_gx = 0.f, out_gy = 0.f, out_ga = 0.f;   // results for my sample
-                const int cnt = min(GS, LP - s0);
-#pragma unroll 2
-                for (int j = 0; j < cnt; ++j) {
-                    const float lx = __shfl_sync(0xffffffffu, my_xy.x, grp_base + j);
-                    const float ly = __shfl_sync(0xffffffffu, my_xy.y, grp_base + j);
-                    const float a = __shfl_sync(0xffffffffu, my_a, grp_base + j);
-                    const Tap t = make_tap(lx, ly, H, W, st, row_stride);
+                const int ls = min(s, LP - 1) / d.P;
+                const int H = lt.H[ls], W = lt.W[ls];
+                const OwnerTap t = make_owner_tap(mine, xy.x, xy.y, a, H, W, lt.start[ls], rsv);
+                const int my_o2 = t.off0 + t.dy;
+                const float wa0 = t.ay.w0 * t.a, wa1 = t.ay.w1 * t.a;
+                const float w00 = wa0 * t.ax.w0, w01 = wa0 * t.ax.w1;     // corner weight * attn
+                const float w10 = wa1 * t.ax.w0, w11 = wa1 * t.ax.w1;
+
+                // broadcast phase: every lane of the group handles its VEC channels of sample s0+j
+                float U[GS][4];
+#pragma unroll
+                for (int j = 0; j < GS; ++j) {
+                    const int src = grp_base + j;
+                    const int o0 = __shfl_sync(FULL, t.off0, src);
+                    const int o2 = __shfl_sync(FULL, my_o2, src);
+                    const int dx = WIDE ? rsv : __shfl_sync(FULL, t.dx, src);
+                    float bw[4];
+                    bw[0] = __shfl_sync(FULL, w00, src);
+                    bw[1] = __shfl_sync(FULL, w01, src);
+                    bw[2] = __shfl_sync(FULL, w10, src);
+                    bw[3] = __shfl_sync(FULL, w11, src);
+                    const unsigned o[4] = {(unsigned)o0, (unsigned)(o0 + dx), (unsigned)o2, (unsigned)(o2 + dx)};
                     float v[4][VEC];
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) VecIO<VT, VEC>::load(vbase + t.off[c], v[c]);
-                    const float w[4] = {t.wy0 * t.wx0, t.wy0 * t.wx1, t.wy1 * t.wx0, t.wy1 * t.wx1};
-                    // u[c] = <grad_out row slice, corner c>; the three sums are linear in u
-                    float u[4] = {0.f, 0.f, 0.f, 0.f};
+                    for (int c = 0; c < 4; ++c) VecIO<VT, VEC>::load(lane_base + (size_t)o[c] * VEC, v[c]);
+                    // u[c] = <grad_out slice, corner c>: all three scalar gradients are linear in u
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
+                        float acc2[2] = {0.f, 0.f};
 #pragma unroll
-                        for (int k = 0; k < VEC; ++k) u[c] = fmaf(g[k], v[c][k], u[c]);
+                        for (int k = 0; k < VEC; k += 2) {
+                            const float2 r = __ffma2_rn(make_float2(g[k], g[k + 1]),
+                                                        make_float2(v[c][k], v[c][k + 1]),
+                                                        make_float2(acc2[0], acc2[1]));
+                            acc2[0] = r.x; acc2[1] = r.y;
+                        }
+                        U[j][c] = acc2[0] + acc2[1];
                     }
-                    float sa = w[0] * u[0] + w[1] * u[1] + w[2] * u[2] + w[3] * u[3];
-                    // d/dx: wy0*(mx1*v01 - mx0*v00) + wy1*(mx1*v11 - mx0*v10)   (.cuh:141-160)
-                    float sx = t.wy0 * (t.mx1 * u[1] - t.mx0 * u[0]) + t.wy1 * (t.mx1 * u[3] - t.mx0 * u[2]);
-                    float sy = t.wx0 * (t.my1 * u[2] - t.my0 * u[0]) + t.wx1 * (t.my1 * u[3] - t.my0 * u[1]);
-                    // scatter: grad_value[corner] += w_corner * attn * grad_out
+                    // scatter: grad_value[corner] += (corner weight * attn) * grad_out
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
-                        if (t.ok[c]) {
-                            const float wa = w[c] * a;
+                        if (bw[c] != 0.f) {
+                            float* dst = gv_base + (size_t)o[c] * VEC;
 #pragma unroll
                             for (int k = 0; k < VEC; k += 4)
-                                red_add_f32x4(gvbase + t.off[c] + k, wa * g[k], wa * g[k + 1],
-                                              wa * g[k + 2], wa * g[k + 3]);
+                                red_add_f32x4(dst + k, bw[c] * g[k], bw[c] * g[k + 1], bw[c] * g[k + 2],
+                                              bw[c] * g[k + 3]);
                         }
                     }
-                    sa = group_sum<GS>(sa, gl, grp_base);
-                    sx = group_sum<GS>(sx, gl, grp_base);
-                    sy = group_sum<GS>(sy, gl, grp_base);
-                    if (gl == j) {
-                        out_ga = sa;
-                        out_gx = sx * a * (float)W;
-                        out_gy = sy * a * (float)H;
-                    }
-                    if (++p == d.P) {
-                        p = 0;
-                        ++l;
-                        if (l < d.L) { H = lt.H[l]; W = lt.W[l]; st = lt.start[l]; }
+                }
+                // bring the group totals of sample s0+gl to its owner lane
+                float u[4];
+                if constexpr (POW2) {
+                    reduce_scatter<GS>(U, gl, u);
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) u[c] = 0.f;
+#pragma unroll
+                    for (int j = 0; j < GS; ++j) {
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            const float tot = group_sum<GS>(U[j][c], gl, grp_base);
+                            if (gl == j) u[c] = tot;
+                        }
                     }
                 }
                 if (mine) {
-                    store_loc<AT>(grad_loc + (row * LP + s0 + gl) * 2, out_gx, out_gy);
-                    grad_attn[row * LP + s0 + gl] = from_f32<AT>(out_ga);
+                    // owner lane: its own (unbroadcast) tap turns u into the three gradients
+                    const float ga = t.ay.w0 * (t.ax.w0 * u[0] + t.ax.w1 * u[1]) +
+                                     t.ay.w1 * (t.ax.w0 * u[2] + t.ax.w1 * u[3]);
+                    const float gx = t.ay.w0 * (t.ax.d0 * u[0] + t.ax.d1 * u[1]) +
+                                     t.ay.w1 * (t.ax.d0 * u[2] + t.ax.d1 * u[3]);
+                    const float gy = t.ay.d0 * (t.ax.w0 * u[0] + t.ax.w1 * u[1]) +
+                                     t.ay.d1 * (t.ax.w0 * u[2] + t.ax.w1 * u[3]);
+                    // .cuh:373-374: pixel-space derivative times attn times W (x) / H (y)
+                    store_loc<AT>(grad_loc + (row * LP + s) * 2, gx * t.a * (float)W, gy * t.a * (float)H);
+                    grad_attn[row * LP + s] = from_f32<AT>(ga);
                 }
             }
         }
     }
+}
+
+template <typename VT, typename AT, int VEC, int GS, int NWARPS>
+__global__ void __launch_bounds__(NWARPS * 32)
+msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ shapes,
+                     const int64_t* __restrict__ level_start, const AT* __restrict__ loc,
+                     const AT* __restrict__ attn, const VT* __restrict__ grad_out,
+                     float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
+                     AT* __restrict__ grad_attn, const KernelDims d)
+{
+    __shared__ LevelTable lt;
+    stage_levels(lt, shapes, level_start, d);
+    if (lt.min_w > 1)
+        backward_items<VT, AT, VEC, GS, NWARPS, true>(lt, value, loc, attn, grad_out, grad_value_acc,
+                                                      grad_loc, grad_attn, d);
+    else
+        backward_items<VT, AT, VEC, GS, NWARPS, false>(lt, value, loc, attn, grad_out, grad_value_acc,
+                                                       grad_loc, grad_attn, d);
 }
 
 // fp32 workspace -> 16-bit grad_value (one rounding of the full sum).

@@ -31,6 +31,7 @@ struct LevelTable {
     int tiles_x[kMaxLevels];     // 2-D tiling (encoder form): tiles per row
     int tile_begin[kMaxLevels];  // 2-D tiling: first tile id of the level
     int total_tiles;
+    int min_w;                   // smallest level width (W == 1 levels need a per-sample column step)
 };
 
 struct KernelDims {
@@ -46,13 +47,14 @@ __device__ __forceinline__ void stage_levels(LevelTable& t, const int64_t* __res
                                              const KernelDims& d)
 {
     if (threadIdx.x == 0) {
-        int run = 0, trun = 0;
+        int run = 0, trun = 0, min_w = 1 << 30;
         for (int l = 0; l < d.L; ++l) {
             const int H = (int)shapes[2 * l], W = (int)shapes[2 * l + 1];
             t.H[l] = H;
             t.W[l] = W;
             t.start[l] = level_start ? (int)level_start[l] : run;
             run += H * W;
+            min_w = min(min_w, W);
             if (d.tile_h > 0) {
                 const int tx = (W + d.tile_w - 1) / d.tile_w;
                 const int ty = (H + d.tile_h - 1) / d.tile_h;
@@ -61,6 +63,7 @@ __device__ __forceinline__ void stage_levels(LevelTable& t, const int64_t* __res
                 trun += tx * ty;
             }
         }
+        t.min_w = min_w;
         t.total_tiles = d.tile_h > 0 ? trun : (d.Lq + d.tile_q - 1) / d.tile_q;
     }
     __syncthreads();
@@ -252,6 +255,79 @@ __device__ __forceinline__ Tap make_tap(float lx, float ly, int H, int W, int st
     const int c0 = x0c * row_stride, c1 = x1c * row_stride;
     t.off[0] = r0 + c0; t.off[1] = r0 + c1; t.off[2] = r1 + c0; t.off[3] = r1 + c1;
     return t;
+}
+
+// ---- owner-lane taps ---------------------------------------------------------------------
+// Each lane of a row group prepares ONE sample of the current chunk (instead of every lane
+// redoing the same coordinate arithmetic for every sample); the loop over the chunk then
+// only broadcasts the finished numbers with warp shuffles.
+//
+// A tap is expressed on a FIXED 2x2 footprint whose top-left pixel (yb, xb) is clamped into
+// the level (xb = clamp(floor(x), 0, W-2)), so the four corner addresses always are
+// base, base+dx, base+dy, base+dy+dx and are always valid memory.  Border handling (the
+// reference's guarded corners, .cuh:36-60, and the open window -1 < x < W, :229) moves into
+// the per-column / per-row weights: a corner that the reference skips gets weight 0, and when
+// floor(x) = -1 (or W-1) the surviving corner's weight is assigned to the footprint column
+// that holds it.
+struct Axis {
+    int b;          // clamped footprint origin along this axis
+    float w0, w1;   // weights of footprint column b and b+1
+    float d0, d1;   // d(w0)/dcoord, d(w1)/dcoord  (one-sided at the kinks, like .cuh:141-160)
+};
+
+__device__ __forceinline__ Axis make_axis(float c, int size, bool inside)
+{
+    Axis ax;
+    const float f = floorf(c);
+    const int i0 = (int)f;
+    const float frac = c - f;
+    const bool v0 = inside && i0 >= 0, v1 = inside && i0 + 1 <= size - 1;
+    const float a0 = v0 ? 1.f - frac : 0.f, a1 = v1 ? frac : 0.f;   // weights of pixels i0, i0+1
+    const float g0 = v0 ? -1.f : 0.f, g1 = v1 ? 1.f : 0.f;
+    ax.b = min(max(i0, 0), max(size - 2, 0));
+    const int sh = i0 - ax.b;                  // 0 normally, -1 at the low border, +1 at the high border
+    ax.w0 = sh == 0 ? a0 : (sh == -1 ? a1 : 0.f);
+    ax.w1 = sh == 0 ? a1 : (sh == 1 ? a0 : 0.f);
+    ax.d0 = sh == 0 ? g0 : (sh == -1 ? g1 : 0.f);
+    ax.d1 = sh == 0 ? g1 : (sh == 1 ? g0 : 0.f);
+    return ax;
+}
+
+struct OwnerTap {
+    int off0;         // offset of the footprint's top-left corner from the (batch, head) base,
+                      // in units of `row_stride` (caller's choice: elements or VEC-element vectors)
+    int dy;           // step to the second footprint row (0 when H == 1)
+    int dx;           // step to the second footprint column (0 when W == 1)
+    Axis ay, ax;
+    float a;          // attention weight (0 for lanes without a sample)
+};
+
+__device__ __forceinline__ OwnerTap make_owner_tap(bool mine, float lx, float ly, float a, int H, int W,
+                                                   int start, int row_stride)
+{
+    OwnerTap t;
+    const float x = fmaf(lx, (float)W, -0.5f);
+    const float y = fmaf(ly, (float)H, -0.5f);
+    const bool inside = mine && (y > -1.f) && (x > -1.f) && (y < (float)H) && (x < (float)W);
+    t.ay = make_axis(y, H, inside);
+    t.ax = make_axis(x, W, inside);
+    t.a = mine ? a : 0.f;
+    t.off0 = mine ? (start + t.ay.b * W + t.ax.b) * row_stride : 0;
+    t.dy = (mine && H > 1) ? W * row_stride : 0;
+    t.dx = (mine && W > 1) ? row_stride : 0;
+    return t;
+}
+
+// acc[0..VEC) += w * v[0..VEC) with packed fp32x2 FMAs (sm_100 FFMA2).
+template <int VEC>
+__device__ __forceinline__ void axpy_vec(float (&acc)[VEC], float w, const float (&v)[VEC])
+{
+    const float2 ww = make_float2(w, w);
+#pragma unroll
+    for (int k = 0; k < VEC; k += 2) {
+        const float2 r = __ffma2_rn(ww, make_float2(v[k], v[k + 1]), make_float2(acc[k], acc[k + 1]));
+        acc[k] = r.x; acc[k + 1] = r.y;
+    }
 }
 
 }  // namespace msda

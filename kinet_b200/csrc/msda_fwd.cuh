@@ -16,30 +16,45 @@
 
 namespace msda {
 
-template <typename VT, typename AT, int VEC, int GS, int NWARPS>
-__global__ void __launch_bounds__(NWARPS * 32)
-msda_forward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ shapes,
-                    const int64_t* __restrict__ level_start, const AT* __restrict__ loc,
-                    const AT* __restrict__ attn, VT* __restrict__ out, const KernelDims d)
+// One gathered sample: four 16-byte corner loads issued back to back, then 4*VEC FMAs.
+template <typename VT, int VEC>
+__device__ __forceinline__ void gather_sample(float (&acc)[VEC], const VT* lane_base, int o0, int o2, int dx,
+                                              float b00, float b01, float b10, float b11)
+{
+    float v00[VEC], v01[VEC], v10[VEC], v11[VEC];
+    // offsets are in VEC-element vectors: one IMAD.WIDE per address
+    VecIO<VT, VEC>::load(lane_base + (size_t)(unsigned)o0 * VEC, v00);
+    VecIO<VT, VEC>::load(lane_base + (size_t)(unsigned)(o0 + dx) * VEC, v01);
+    VecIO<VT, VEC>::load(lane_base + (size_t)(unsigned)o2 * VEC, v10);
+    VecIO<VT, VEC>::load(lane_base + (size_t)(unsigned)(o2 + dx) * VEC, v11);
+    axpy_vec<VEC>(acc, b00, v00);
+    axpy_vec<VEC>(acc, b01, v01);
+    axpy_vec<VEC>(acc, b10, v10);
+    axpy_vec<VEC>(acc, b11, v11);
+}
+
+// WIDE: every level has W > 1, so the column step of the 2x2 footprint is the same for all samples.
+template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE>
+__device__ __forceinline__ void forward_items(const LevelTable& lt, const VT* __restrict__ value,
+                                              const AT* __restrict__ loc, const AT* __restrict__ attn,
+                                              VT* __restrict__ out, const KernelDims& d)
 {
     constexpr int GPW = 32 / GS;           // rows per warp
     constexpr int D = VEC * GS;
-    __shared__ LevelTable lt;
-    stage_levels(lt, shapes, level_start, d);
-
+    constexpr unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int grp = lane / GS, gl = lane - grp * GS;
     const bool lane_used = grp < GPW;
     const int grp_base = grp * GS;         // first lane of this group
     const int LP = d.L * d.P;
-    const int row_stride = d.M * D;        // elements between neighbouring pixels
+    const int rsv = d.M * GS;              // vectors between neighbouring pixels
     const int items = lt.total_tiles * d.N * d.M;
 
     for (int item = blockIdx.x; item < items; item += gridDim.x) {
         const int tile = item / (d.N * d.M);
         const int bm = item - tile * (d.N * d.M);
         const int b = bm / d.M, m = bm - b * d.M;
-        const VT* vbase = value + ((size_t)b * d.S * d.M + m) * D + gl * VEC;
+        const VT* lane_base = value + ((size_t)b * d.S * d.M + m) * D + gl * VEC;
 
         for (int i0 = warp * GPW; i0 < d.tile_q; i0 += NWARPS * GPW) {
             const int q = (lane_used && i0 + grp < d.tile_q) ? tile_query(lt, d, tile, i0 + grp) : -1;
@@ -52,43 +67,56 @@ msda_forward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ sh
 #pragma unroll
             for (int k = 0; k < VEC; ++k) acc[k] = 0.f;
 
-            int l = 0, p = 0;
-            int H = lt.H[0], W = lt.W[0], st = lt.start[0];
             for (int s0 = 0; s0 < LP; s0 += GS) {
-                // each lane of the group fetches one sample's metadata
-                float2 my_xy = make_float2(-8.f, -8.f);
-                float my_a = 0.f;
-                if (row_ok && s0 + gl < LP) {
-                    my_xy = load_loc<AT>(lrow + (s0 + gl) * 2);
-                    my_a = load_attn<AT>(arow + s0 + gl);
+                // owner phase: lane gl of the group prepares sample s0 + gl of its row
+                const int s = s0 + gl;
+                const bool mine = row_ok && s < LP;
+                float2 xy = make_float2(0.f, 0.f);
+                float a = 0.f;
+                if (mine) {
+                    xy = load_loc<AT>(lrow + s * 2);
+                    a = load_attn<AT>(arow + s);
                 }
-                const int cnt = min(GS, LP - s0);
-#pragma unroll 4
-                for (int j = 0; j < cnt; ++j) {
-                    const float lx = __shfl_sync(0xffffffffu, my_xy.x, grp_base + j);
-                    const float ly = __shfl_sync(0xffffffffu, my_xy.y, grp_base + j);
-                    const float a = __shfl_sync(0xffffffffu, my_a, grp_base + j);
-                    const Tap t = make_tap(lx, ly, H, W, st, row_stride);
-                    const float wa0 = t.wy0 * a, wa1 = t.wy1 * a;
-                    const float w[4] = {wa0 * t.wx0, wa0 * t.wx1, wa1 * t.wx0, wa1 * t.wx1};
-                    float v[4][VEC];
+                const int ls = min(s, LP - 1) / d.P;
+                const OwnerTap t = make_owner_tap(mine, xy.x, xy.y, a, lt.H[ls], lt.W[ls], lt.start[ls], rsv);
+                const int my_o2 = t.off0 + t.dy;
+                const float wa0 = t.ay.w0 * t.a, wa1 = t.ay.w1 * t.a;
+                const float w00 = wa0 * t.ax.w0, w01 = wa0 * t.ax.w1;
+                const float w10 = wa1 * t.ax.w0, w11 = wa1 * t.ax.w1;
+                // broadcast phase: all lanes of the group consume sample s0 + j.  A ragged last
+                // chunk runs the full GS steps too: lanes without a sample publish weight 0 at
+                // offset 0 (valid memory), so no guards are needed inside the unrolled body.
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) VecIO<VT, VEC>::load(vbase + t.off[c], v[c]);
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-#pragma unroll
-                        for (int k = 0; k < VEC; ++k) acc[k] = fmaf(w[c], v[c][k], acc[k]);
-                    }
-                    if (++p == d.P) {
-                        p = 0;
-                        ++l;
-                        if (l < d.L) { H = lt.H[l]; W = lt.W[l]; st = lt.start[l]; }
-                    }
+                for (int j = 0; j < GS; ++j) {
+                    const int src = grp_base + j;
+                    const int o0 = __shfl_sync(FULL, t.off0, src);
+                    const int o2 = __shfl_sync(FULL, my_o2, src);
+                    const int dx = WIDE ? rsv : __shfl_sync(FULL, t.dx, src);
+                    const float b00 = __shfl_sync(FULL, w00, src);
+                    const float b01 = __shfl_sync(FULL, w01, src);
+                    const float b10 = __shfl_sync(FULL, w10, src);
+                    const float b11 = __shfl_sync(FULL, w11, src);
+                    gather_sample<VT, VEC>(acc, lane_base, o0, o2, dx, b00, b01, b10, b11);
                 }
             }
             if (row_ok) VecIO<VT, VEC>::store(out + row * D + gl * VEC, acc);
         }
     }
+}
+
+template <typename VT, typename AT, int VEC, int GS, int NWARPS>
+__global__ void __launch_bounds__(NWARPS * 32)
+msda_forward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ shapes,
+                    const int64_t* __restrict__ level_start, const AT* __restrict__ loc,
+                    const AT* __restrict__ attn, VT* __restrict__ out, const KernelDims d)
+{
+    __shared__ LevelTable lt;
+    stage_levels(lt, shapes, level_start, d);
+    // With W > 1 everywhere and at least two pixels, base + column step is always valid memory.
+    if (lt.min_w > 1)
+        forward_items<VT, AT, VEC, GS, NWARPS, true>(lt, value, loc, attn, out, d);
+    else
+        forward_items<VT, AT, VEC, GS, NWARPS, false>(lt, value, loc, attn, out, d);
 }
 
 // Generic fallback: any D, any supported type (incl. fp64).  One warp per
