@@ -66,7 +66,8 @@ __device__ __forceinline__ void reduce_scatter(float (&U)[N][4], int gl, float (
 
 // WIDE: every level has W > 1 (uniform column step of the 2x2 footprint).
 template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE>
-__device__ __forceinline__ void backward_items(const LevelTable& lt, const VT* __restrict__ value,
+__device__ __forceinline__ void backward_items(const LevelTable& lt, int4* stage_a, float4* stage_b,
+                                               const VT* __restrict__ value,
                                                const AT* __restrict__ loc, const AT* __restrict__ attn,
                                                const VT* __restrict__ grad_out,
                                                float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
@@ -74,7 +75,6 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, const VT* _
 {
     constexpr int GPW = 32 / GS;
     constexpr int D = VEC * GS;
-    constexpr unsigned FULL = 0xffffffffu;
     constexpr bool POW2 = (GS & (GS - 1)) == 0;
     static_assert(VEC % 4 == 0, "vector reductions are 4 floats wide");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -93,8 +93,9 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, const VT* _
         const VT* lane_base = value + bbase;
         float* gv_base = grad_value_acc + bbase;
 
-        for (int i0 = warp * GPW; i0 < d.tile_q; i0 += NWARPS * GPW) {
-            const int q = (lane_used && i0 + grp < d.tile_q) ? tile_query(lt, d, tile, i0 + grp) : -1;
+        const TileInfo ti = decode_tile(lt, d, tile);
+        for (int i0 = warp * GPW; i0 < ti.count; i0 += NWARPS * GPW) {
+            const int q = (lane_used && i0 + grp < ti.count) ? tile_query(ti, i0 + grp) : -1;
             const bool row_ok = q >= 0;
             const size_t row = ((size_t)b * d.Lq + (row_ok ? q : 0)) * d.M + m;
             const AT* lrow = loc + row * LP * 2;
@@ -118,24 +119,24 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, const VT* _
                 const int ls = min(s, LP - 1) / d.P;
                 const int H = lt.H[ls], W = lt.W[ls];
                 const OwnerTap t = make_owner_tap(mine, xy.x, xy.y, a, H, W, lt.start[ls], rsv);
-                const int my_o2 = t.off0 + t.dy;
                 const float wa0 = t.ay.w0 * t.a, wa1 = t.ay.w1 * t.a;
-                const float w00 = wa0 * t.ax.w0, w01 = wa0 * t.ax.w1;     // corner weight * attn
-                const float w10 = wa1 * t.ax.w0, w11 = wa1 * t.ax.w1;
+                // publish the tap (offsets; corner weight * attn) in shared memory, [sample][group]
+                __syncwarp();
+                if (lane_used) {
+                    stage_a[gl * GPW + grp] = make_int4(t.off0, t.off0 + t.dy, WIDE ? rsv : t.dx, 0);
+                    stage_b[gl * GPW + grp] = make_float4(wa0 * t.ax.w0, wa0 * t.ax.w1, wa1 * t.ax.w0, wa1 * t.ax.w1);
+                }
+                __syncwarp();
+                const int gsel = lane_used ? grp : 0;
 
                 // broadcast phase: every lane of the group handles its VEC channels of sample s0+j
                 float U[GS][4];
 #pragma unroll
                 for (int j = 0; j < GS; ++j) {
-                    const int src = grp_base + j;
-                    const int o0 = __shfl_sync(FULL, t.off0, src);
-                    const int o2 = __shfl_sync(FULL, my_o2, src);
-                    const int dx = WIDE ? rsv : __shfl_sync(FULL, t.dx, src);
-                    float bw[4];
-                    bw[0] = __shfl_sync(FULL, w00, src);
-                    bw[1] = __shfl_sync(FULL, w01, src);
-                    bw[2] = __shfl_sync(FULL, w10, src);
-                    bw[3] = __shfl_sync(FULL, w11, src);
+                    const int4 ra = stage_a[j * GPW + gsel];
+                    const float4 rb = stage_b[j * GPW + gsel];
+                    const int o0 = ra.x, o2 = ra.y, dx = WIDE ? rsv : ra.z;
+                    const float bw[4] = {rb.x, rb.y, rb.z, rb.w};
                     const unsigned o[4] = {(unsigned)o0, (unsigned)(o0 + dx), (unsigned)o2, (unsigned)(o2 + dx)};
                     float v[4][VEC];
 #pragma unroll
@@ -199,7 +200,7 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, const VT* _
 }
 
 template <typename VT, typename AT, int VEC, int GS, int NWARPS>
-__global__ void __launch_bounds__(NWARPS * 32)
+__global__ void __launch_bounds__(NWARPS * 32, 2)
 msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ shapes,
                      const int64_t* __restrict__ level_start, const AT* __restrict__ loc,
                      const AT* __restrict__ attn, const VT* __restrict__ grad_out,
@@ -208,11 +209,14 @@ msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ s
 {
     __shared__ LevelTable lt;
     stage_levels(lt, shapes, level_start, d);
+    __shared__ int4 stage_a[NWARPS][32];
+    __shared__ float4 stage_b[NWARPS][32];
+    const int warp = threadIdx.x >> 5;
     if (lt.min_w > 1)
-        backward_items<VT, AT, VEC, GS, NWARPS, true>(lt, value, loc, attn, grad_out, grad_value_acc,
+        backward_items<VT, AT, VEC, GS, NWARPS, true>(lt, stage_a[warp], stage_b[warp], value, loc, attn, grad_out, grad_value_acc,
                                                       grad_loc, grad_attn, d);
     else
-        backward_items<VT, AT, VEC, GS, NWARPS, false>(lt, value, loc, attn, grad_out, grad_value_acc,
+        backward_items<VT, AT, VEC, GS, NWARPS, false>(lt, stage_a[warp], stage_b[warp], value, loc, attn, grad_out, grad_value_acc,
                                                        grad_loc, grad_attn, d);
 }
 

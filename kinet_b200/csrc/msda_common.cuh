@@ -69,21 +69,42 @@ __device__ __forceinline__ void stage_levels(LevelTable& t, const int64_t* __res
     __syncthreads();
 }
 
-// Query index of slot i of tile `tile`, or -1 when the slot is empty.
-__device__ __forceinline__ int tile_query(const LevelTable& t, const KernelDims& d, int tile, int i)
+// A decoded query tile: `count` valid queries, enumerated densely (no empty slots for ragged
+// border tiles): query(i) = origin + (i / vw) * pitch + (i % vw).
+struct TileInfo {
+    int origin;   // query index of the tile's first query
+    int vw;       // valid width of the tile (1-D tiling: count)
+    int pitch;    // query-index step between tile rows (level width; 1-D tiling: 0)
+    int count;    // number of valid queries
+};
+
+__device__ __forceinline__ TileInfo decode_tile(const LevelTable& t, const KernelDims& d, int tile)
 {
+    TileInfo ti;
     if (d.tile_h == 0) {
-        const int q = tile * d.tile_q + i;
-        return q < d.Lq ? q : -1;
+        ti.origin = tile * d.tile_q;
+        ti.count = min(d.tile_q, d.Lq - ti.origin);
+        ti.vw = max(ti.count, 1);
+        ti.pitch = 0;
+        return ti;
     }
     int l = 0;
     while (l + 1 < d.L && tile >= t.tile_begin[l + 1]) ++l;
     const int rel = tile - t.tile_begin[l];
     const int ty = rel / t.tiles_x[l], tx = rel - ty * t.tiles_x[l];
-    const int iy = i / d.tile_w, ix = i - iy * d.tile_w;
-    const int y = ty * d.tile_h + iy, x = tx * d.tile_w + ix;
-    if (y >= t.H[l] || x >= t.W[l]) return -1;
-    return t.start[l] + y * t.W[l] + x;
+    const int y0 = ty * d.tile_h, x0 = tx * d.tile_w;
+    ti.vw = min(d.tile_w, t.W[l] - x0);
+    const int vh = min(d.tile_h, t.H[l] - y0);
+    ti.pitch = t.W[l];
+    ti.origin = t.start[l] + y0 * t.W[l] + x0;
+    ti.count = ti.vw * vh;
+    return ti;
+}
+
+__device__ __forceinline__ int tile_query(const TileInfo& ti, int i)
+{
+    const int iy = i / ti.vw;
+    return ti.origin + iy * ti.pitch + (i - iy * ti.vw);
 }
 
 // ---- element conversion -------------------------------------------------------------

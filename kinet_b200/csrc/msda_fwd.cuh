@@ -35,17 +35,16 @@ __device__ __forceinline__ void gather_sample(float (&acc)[VEC], const VT* lane_
 
 // WIDE: every level has W > 1, so the column step of the 2x2 footprint is the same for all samples.
 template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE>
-__device__ __forceinline__ void forward_items(const LevelTable& lt, const VT* __restrict__ value,
+__device__ __forceinline__ void forward_items(const LevelTable& lt, int4* stage_a, float4* stage_b,
+                                              const VT* __restrict__ value,
                                               const AT* __restrict__ loc, const AT* __restrict__ attn,
                                               VT* __restrict__ out, const KernelDims& d)
 {
     constexpr int GPW = 32 / GS;           // rows per warp
     constexpr int D = VEC * GS;
-    constexpr unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int grp = lane / GS, gl = lane - grp * GS;
     const bool lane_used = grp < GPW;
-    const int grp_base = grp * GS;         // first lane of this group
     const int LP = d.L * d.P;
     const int rsv = d.M * GS;              // vectors between neighbouring pixels
     const int items = lt.total_tiles * d.N * d.M;
@@ -56,8 +55,9 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, const VT* __
         const int b = bm / d.M, m = bm - b * d.M;
         const VT* lane_base = value + ((size_t)b * d.S * d.M + m) * D + gl * VEC;
 
-        for (int i0 = warp * GPW; i0 < d.tile_q; i0 += NWARPS * GPW) {
-            const int q = (lane_used && i0 + grp < d.tile_q) ? tile_query(lt, d, tile, i0 + grp) : -1;
+        const TileInfo ti = decode_tile(lt, d, tile);
+        for (int i0 = warp * GPW; i0 < ti.count; i0 += NWARPS * GPW) {
+            const int q = (lane_used && i0 + grp < ti.count) ? tile_query(ti, i0 + grp) : -1;
             const bool row_ok = q >= 0;
             const size_t row = ((size_t)b * d.Lq + (row_ok ? q : 0)) * d.M + m;
             const AT* lrow = loc + row * LP * 2;
@@ -79,24 +79,25 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, const VT* __
                 }
                 const int ls = min(s, LP - 1) / d.P;
                 const OwnerTap t = make_owner_tap(mine, xy.x, xy.y, a, lt.H[ls], lt.W[ls], lt.start[ls], rsv);
-                const int my_o2 = t.off0 + t.dy;
                 const float wa0 = t.ay.w0 * t.a, wa1 = t.ay.w1 * t.a;
-                const float w00 = wa0 * t.ax.w0, w01 = wa0 * t.ax.w1;
-                const float w10 = wa1 * t.ax.w0, w11 = wa1 * t.ax.w1;
+                // publish the finished tap in shared memory, laid out [sample j][group] so the
+                // broadcast reads of one step (one 16-byte record per group) are conflict-free.
+                // (Shuffles would cost one LSU data-pipe wavefront per value; this is 3 per sample.)
+                __syncwarp();
+                if (lane_used) {
+                    stage_a[gl * GPW + grp] = make_int4(t.off0, t.off0 + t.dy, WIDE ? rsv : t.dx, 0);
+                    stage_b[gl * GPW + grp] = make_float4(wa0 * t.ax.w0, wa0 * t.ax.w1, wa1 * t.ax.w0, wa1 * t.ax.w1);
+                }
+                __syncwarp();
                 // broadcast phase: all lanes of the group consume sample s0 + j.  A ragged last
                 // chunk runs the full GS steps too: lanes without a sample publish weight 0 at
                 // offset 0 (valid memory), so no guards are needed inside the unrolled body.
+                const int gsel = lane_used ? grp : 0;
 #pragma unroll
                 for (int j = 0; j < GS; ++j) {
-                    const int src = grp_base + j;
-                    const int o0 = __shfl_sync(FULL, t.off0, src);
-                    const int o2 = __shfl_sync(FULL, my_o2, src);
-                    const int dx = WIDE ? rsv : __shfl_sync(FULL, t.dx, src);
-                    const float b00 = __shfl_sync(FULL, w00, src);
-                    const float b01 = __shfl_sync(FULL, w01, src);
-                    const float b10 = __shfl_sync(FULL, w10, src);
-                    const float b11 = __shfl_sync(FULL, w11, src);
-                    gather_sample<VT, VEC>(acc, lane_base, o0, o2, dx, b00, b01, b10, b11);
+                    const int4 ra = stage_a[j * GPW + gsel];
+                    const float4 rb = stage_b[j * GPW + gsel];
+                    gather_sample<VT, VEC>(acc, lane_base, ra.x, ra.y, WIDE ? rsv : ra.z, rb.x, rb.y, rb.z, rb.w);
                 }
             }
             if (row_ok) VecIO<VT, VEC>::store(out + row * D + gl * VEC, acc);
@@ -105,7 +106,7 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, const VT* __
 }
 
 template <typename VT, typename AT, int VEC, int GS, int NWARPS>
-__global__ void __launch_bounds__(NWARPS * 32)
+__global__ void __launch_bounds__(NWARPS * 32, 3)
 msda_forward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ shapes,
                     const int64_t* __restrict__ level_start, const AT* __restrict__ loc,
                     const AT* __restrict__ attn, VT* __restrict__ out, const KernelDims d)
@@ -113,10 +114,13 @@ msda_forward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ sh
     __shared__ LevelTable lt;
     stage_levels(lt, shapes, level_start, d);
     // With W > 1 everywhere and at least two pixels, base + column step is always valid memory.
+    __shared__ int4 stage_a[NWARPS][32];
+    __shared__ float4 stage_b[NWARPS][32];
+    const int warp = threadIdx.x >> 5;
     if (lt.min_w > 1)
-        forward_items<VT, AT, VEC, GS, NWARPS, true>(lt, value, loc, attn, out, d);
+        forward_items<VT, AT, VEC, GS, NWARPS, true>(lt, stage_a[warp], stage_b[warp], value, loc, attn, out, d);
     else
-        forward_items<VT, AT, VEC, GS, NWARPS, false>(lt, value, loc, attn, out, d);
+        forward_items<VT, AT, VEC, GS, NWARPS, false>(lt, stage_a[warp], stage_b[warp], value, loc, attn, out, d);
 }
 
 // Generic fallback: any D, any supported type (incl. fp64).  One warp per
