@@ -1,0 +1,380 @@
+#!/usr/bin/env python
+"""bench.py -- MSDeformAttn forward+backward throughput on the Deformable-DETR 6+6-layer shape.
+
+Contract (see the task brief): `python bench.py --gpus N --steps K --warmup W [--impl reference]`
+prints ONE JSON line on rank 0.
+
+Workload ("detr_6enc_6dec_bf16", BASELINE.json configs[1]): one step = the MSDeformAttn calls of one
+Deformable-DETR forward+backward pass on an 800x1333 pyramid -- 6 encoder-layer calls (N=2, Lq=S=22223,
+M=8, D=32, L=4, P=4) and 6 decoder-layer calls (Lq=300), each forward AND backward, value in bf16,
+sampling locations / attention weights in fp32 (what autocast produces), every layer with its own
+input tensors (~0.7 GB per step > 126 MB L2, so no call finds its inputs in L2).
+
+metric: msda_fwd_bwd_GBps = algorithmic bytes of the step / device time.
+  value    inputs resident in HBM, calls made straight through the C ABI (libmsda_b200.so)
+  e2e      same step through the public Python API (MSDeformAttnFunction) with HOST pinned inputs:
+           H2D of every input, forward, backward, D2H of output and gradients inside the timed region
+  roofline dominant kernel = the encoder-form backward kernel, timed alone with CUDA events recorded
+           by the library around that launch (msda_b200_trace_next)
+  cpu_baseline / --impl reference: the reference's CPU-runnable path (per-level grid_sample + autograd,
+           restated in oracle/msda_oracle.py because /root/reference is absent on the GPU box) on a
+           bounded sample, all host threads.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from kinet_b200.workloads import algorithmic_bytes, make_inputs, resolve  # noqa: E402
+
+WORKLOAD = "detr_6enc_6dec_bf16"
+ENC_TAG, DEC_TAG, LAYERS = "C2_enc", "C2_dec", 6
+METRIC, UNIT = "msda_fwd_bwd_GBps", "GB/s"
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def step_bytes(e_value, e_aux):
+    """Algorithmic bytes of one step and of one encoder-form backward call."""
+    enc, dec = resolve(ENC_TAG), resolve(DEC_TAG)
+    ef, eb = algorithmic_bytes(enc, e_value, e_aux)
+    df, db = algorithmic_bytes(dec, e_value, e_aux)
+    return LAYERS * (ef + eb + df + db), eb
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
+class Call:
+    """One MSDeformAttn call site (one layer): device tensors + preallocated outputs, launched
+    straight through the C ABI (no allocation, no host sync in the timed region)."""
+
+    def __init__(self, tag, dev, seed):
+        from kinet_b200 import _lib
+        self.lib = _lib.load()
+        self._lib = _lib
+        s = resolve(tag)
+        self.shape = s
+        self.value, self.shapes, self.loc, self.attn = make_inputs(
+            tag, dev, torch.bfloat16, torch.float32, "structured", seed)
+        g = torch.Generator(device=dev).manual_seed(seed + 1000)
+        self.grad_out = torch.randn(s["N"], s["Lq"], s["M"] * s["D"], generator=g, device=dev).to(torch.bfloat16)
+        self.out = torch.empty_like(self.grad_out)
+        self.gv = torch.empty_like(self.value)
+        self.gl = torch.empty_like(self.loc)
+        self.ga = torch.empty_like(self.attn)
+        self.dims = _lib.MsdaDims(s["N"], s["S"], s["M"], s["D"], s["L"], s["Lq"], s["P"])
+        self.vcode, self.acode = _lib.dtype_code(self.value.dtype), _lib.dtype_code(self.loc.dtype)
+        nbytes = int(self.lib.msda_b200_backward_workspace_bytes(self.vcode, ctypes.byref(self.dims)))
+        self.ws_bytes = nbytes
+        self.ws = torch.empty(max(nbytes // 4, 1), dtype=torch.float32, device=dev)
+        self.launches = 0
+
+    @staticmethod
+    def _p(t):
+        return ctypes.c_void_p(t.data_ptr())
+
+    def forward(self, stream):
+        rc = self.lib.msda_b200_forward(self._p(self.value), self.vcode, self._p(self.shapes), None,
+                                        self._p(self.loc), self._p(self.attn), self.acode,
+                                        self._p(self.out), ctypes.byref(self.dims), ctypes.c_void_p(stream))
+        self._lib.check(rc, "msda_b200_forward")
+        self.launches += self.lib.msda_b200_last_launch_count()
+
+    def backward(self, stream):
+        rc = self.lib.msda_b200_backward(self._p(self.value), self.vcode, self._p(self.shapes), None,
+                                         self._p(self.loc), self._p(self.attn), self.acode,
+                                         self._p(self.grad_out), self._p(self.gv), self._p(self.gl),
+                                         self._p(self.ga), self._p(self.ws), ctypes.c_size_t(self.ws_bytes),
+                                         ctypes.byref(self.dims), ctypes.c_void_p(stream))
+        self._lib.check(rc, "msda_b200_backward")
+        self.launches += self.lib.msda_b200_last_launch_count()
+
+
+def run_ours(args, rank, world, dev):
+    from kinet_b200 import _lib
+    lib = _lib.load()
+    stream = torch.cuda.current_stream().cuda_stream
+    enc = [Call(ENC_TAG, dev, 100 * rank + i) for i in range(LAYERS)]
+    dec = [Call(DEC_TAG, dev, 100 * rank + 50 + i) for i in range(LAYERS)]
+    calls = enc + dec
+    total_bytes, enc_bwd_bytes = step_bytes(2, 4)
+
+    # events bracketing the dominant kernel (encoder-form backward), one pair per launch
+    n_tr = args.steps * LAYERS
+    tr = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_tr)]
+
+    def step(trace_base=None):
+        # forward through the 6 encoder then 6 decoder layers, backward in reverse order
+        for c in calls:
+            c.forward(stream)
+        for i, c in enumerate(reversed(calls)):
+            if trace_base is not None and c.shape["encoder"]:
+                a, b = tr[trace_base + (i - LAYERS)]
+                # torch events are created lazily: record once so the handle exists, then hand the
+                # raw cudaEvent_t to the library, which re-records it around the kernel
+                a.record(); b.record()
+                lib.msda_b200_trace_next(ctypes.c_void_p(a.cuda_event), ctypes.c_void_p(b.cuda_event))
+            c.backward(stream)
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    for c in calls:
+        c.launches = 0
+    barrier()
+    sampler = ClockSampler(dev.index or 0)
+    if rank == 0:
+        sampler.start()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for k in range(args.steps):
+        step(trace_base=k * LAYERS)
+    t1.record()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = t0.elapsed_time(t1)
+    kern_ms = [a.elapsed_time(b) for a, b in tr]
+    launches = sum(c.launches for c in calls)
+
+    # ---- e2e: public Python API, host pinned inputs, H2D + fwd + bwd + D2H per step ------------
+    from kinet_b200.functions import MSDeformAttnFunction
+    host = []
+    for c in calls:
+        host.append(tuple(t.cpu().pin_memory() for t in (c.value, c.loc, c.attn, c.grad_out)))
+    h2d = sum(t.numel() * t.element_size() for tup in host for t in tup)
+    d2h = sum(t.numel() * t.element_size() for c in calls for t in (c.out, c.gv, c.gl, c.ga))
+    sink = [tuple(torch.empty_like(t, device="cpu").pin_memory() for t in (c.out, c.gv, c.gl, c.ga)) for c in calls]
+
+    def e2e_step():
+        outs = []
+        for c, (hv, hl, ha, hg) in zip(calls, host):
+            v = hv.to(dev, non_blocking=True).requires_grad_(True)
+            l = hl.to(dev, non_blocking=True).requires_grad_(True)
+            a = ha.to(dev, non_blocking=True).requires_grad_(True)
+            g = hg.to(dev, non_blocking=True)
+            o = MSDeformAttnFunction.apply(v, c.shapes, l, a, 64)
+            outs.append((o, v, l, a, g))
+        for (o, v, l, a, g), dst in zip(reversed(outs), reversed(sink)):
+            o.backward(g)
+            for src, d in zip((o.detach(), v.grad, l.grad, a.grad), dst):
+                d.copy_(src, non_blocking=True)
+
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    e2e_step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(e2e_steps):
+        e2e_step()
+    e1.record()
+    barrier()
+    e2e_ms = e0.elapsed_time(e1) / e2e_steps
+    return dict(ms=ms, kern_ms=kern_ms, launches=launches, clocks=clocks, total_bytes=total_bytes,
+                enc_bwd_bytes=enc_bwd_bytes, e2e_ms=e2e_ms, h2d=h2d, d2h=d2h, e2e_steps=e2e_steps)
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the reference's CPU-runnable path (grid_sample per level + autograd), bounded sample
+# ---------------------------------------------------------------------------------------------
+def cpu_sample_inputs(tag, lq_cap=None):
+    s = resolve(tag)
+    value, shapes, loc, attn = make_inputs(tag, torch.device("cpu"), torch.float32, torch.float32, "structured", 7)
+    if lq_cap is not None and s["Lq"] > lq_cap:
+        loc, attn = loc[:, :lq_cap].contiguous(), attn[:, :lq_cap].contiguous()
+        s = dict(s, Lq=lq_cap)
+    go = torch.randn(s["N"], s["Lq"], s["M"] * s["D"])
+    return s, value, shapes, loc, attn, go
+
+
+def cpu_step(cases):
+    """forward + backward of every case through the oracle's torch restatement of the reference."""
+    from oracle import torch_port_forward
+    for s, value, shapes, loc, attn, go in cases:
+        v = value.clone().requires_grad_(True)
+        l = loc.clone().requires_grad_(True)
+        a = attn.clone().requires_grad_(True)
+        out = torch_port_forward(v, shapes, l, a)
+        out.backward(go)
+
+
+def cpu_cases():
+    # bounded sample of the same workload: ONE decoder-layer call (exact config-1 shape, Lq=300) and
+    # ONE encoder-layer call cut to its first 8192 queries, fp32 (the reference has no bf16)
+    cases = [cpu_sample_inputs(DEC_TAG), cpu_sample_inputs(ENC_TAG, lq_cap=8192)]
+    nbytes = 0
+    for s, *_ in cases:
+        f, b = algorithmic_bytes(s, 4, 4)
+        nbytes += f + b
+    return cases, nbytes, "1 decoder call (N=2,Lq=300) + 1 encoder call cut to Lq=8192, fwd+bwd, fp32, 800x1333 pyramid"
+
+
+def run_cpu(steps, warmup):
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cases, nbytes, sample = cpu_cases()
+    for _ in range(warmup):
+        cpu_step(cases)
+    t = time.perf_counter()
+    for _ in range(steps):
+        cpu_step(cases)
+    dt = (time.perf_counter() - t) / steps
+    return dict(value=nbytes / dt / 1e9, ms=dt * 1e3, cores=torch.get_num_threads(), sample=sample)
+
+
+def reduce_max(values, device, world):
+    """MAX over ranks of a list of floats (the contract's 'max over ranks' timing)."""
+    if world <= 1:
+        return [float(v) for v in values]
+    t = torch.tensor(values, device=device, dtype=torch.float64)
+    torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    return [float(x) for x in t.tolist()]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--cpu-steps", type=int, default=5)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    config = {"workload": WORKLOAD, "pyramid": "800x1333 -> (100,167)(50,84)(25,42)(13,21)",
+              "calls_per_step": "6 encoder-form (N=2,Lq=S=22223) + 6 decoder-form (Lq=300), fwd+bwd each",
+              "M": 8, "D": 32, "L": 4, "P": 4, "value_dtype": "bf16", "loc_attn_dtype": "f32",
+              "l2": "every layer has its own inputs: ~0.7 GB touched per step > 126 MB L2 (no flush needed)",
+              "parallelism": "replicas x%d (independent batches per GPU, no collective on the path)" % world}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        r = run_cpu(args.steps, args.warmup)
+        line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms"], "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                                 "sample": r["sample"]},
+                "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line), flush=True)
+        return
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the MSDeformAttn path has no CPU fallback "
+                         "(use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        torch.distributed.init_process_group("nccl", device_id=dev)
+    r = run_ours(args, rank, world, dev)
+    ms, e2e_ms = r["ms"], r["e2e_ms"]
+    ms, e2e_ms = reduce_max([ms, e2e_ms], dev, world)
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        ms_step = ms / args.steps
+        value = world * r["total_bytes"] / (ms_step * 1e-3) / 1e9
+        e2e = world * r["total_bytes"] / (e2e_ms * 1e-3) / 1e9
+        kms = sorted(r["kern_ms"])
+        kavg = sum(kms) / len(kms)
+        achieved = r["enc_bwd_bytes"] / (kavg * 1e-3) / 1e9
+        cpu = run_cpu(args.cpu_steps, 1)
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": config,
+                "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
+                        "ms_per_step": e2e_ms, "steps": r["e2e_steps"],
+                        "api": "kinet_b200.MSDeformAttnFunction.apply + Tensor.backward, pinned host tensors"},
+                "gpu_launches": r["launches"],
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                             "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                             "kernel": "msda_backward_kernel<bf16,f32,8,4,8> (encoder form, N=2 Lq=S=22223)",
+                             "kernel_us_avg": kavg * 1e3, "kernel_us_min": kms[0] * 1e3,
+                             "launches_timed": len(kms), "algorithmic_bytes_per_launch": r["enc_bwd_bytes"],
+                             "step_frac_of_hbm": value / world / peak,
+                             "note": "true limiter is the SM L1 data pipe / SM->L2 write path, see DESIGN.md"},
+                "cpu_baseline": {"value": cpu["value"], "unit": UNIT, "cores": cpu["cores"], "kind": "port",
+                                 "sample": cpu["sample"], "ms_per_sample": cpu["ms"]},
+                "clocks": r["clocks"]}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -106,6 +106,12 @@ int msda_b200_backward(const void *value, int value_dtype,
  * (bench.py's gpu_launches evidence). */
 int msda_b200_last_launch_count(void);
 
+/* Measurement hook: the NEXT forward or backward call of this thread records the two
+ * cudaEvent_t handles (passed as void*) on its stream immediately before and after its
+ * dominant kernel (the gather kernel / the gather+scatter kernel), so a caller can time that
+ * kernel alone inside a larger timed region.  One-shot; pass NULLs to cancel. */
+void msda_b200_trace_next(void *start_event, void *stop_event);
+
 #ifdef __cplusplus
 }
 #endif

@@ -22,7 +22,7 @@ class MsdaDims(ctypes.Structure):
 
 EXPORTS = ("msda_b200_abi_version", "msda_b200_error_string", "msda_b200_forward",
            "msda_b200_backward_workspace_bytes", "msda_b200_backward",
-           "msda_b200_last_launch_count")
+           "msda_b200_last_launch_count", "msda_b200_trace_next")
 
 _lib = None
 
@@ -49,6 +49,8 @@ def load():
     lib.msda_b200_backward.argtypes = [vp, i, vp, vp, vp, vp, i, vp, vp, vp, vp, vp,
                                        ctypes.c_size_t, dp, vp]
     lib.msda_b200_last_launch_count.restype = i
+    lib.msda_b200_trace_next.restype = None
+    lib.msda_b200_trace_next.argtypes = [vp, vp]
     if lib.msda_b200_abi_version() != 1:
         raise RuntimeError("kinet_b200: libmsda_b200.so ABI version mismatch")
     _lib = lib

@@ -16,6 +16,20 @@ namespace {
 using namespace msda;
 
 thread_local int g_last_launches = 0;
+thread_local cudaEvent_t g_trace_start = nullptr, g_trace_stop = nullptr;
+
+// One-shot event bracket around the dominant kernel (msda_b200_trace_next).
+struct TraceScope {
+    cudaStream_t st;
+    cudaEvent_t stop;
+    explicit TraceScope(cudaStream_t s) : st(s), stop(g_trace_stop)
+    {
+        if (g_trace_start) cudaEventRecord(g_trace_start, st);
+        g_trace_start = nullptr;
+        g_trace_stop = nullptr;
+    }
+    ~TraceScope() { if (stop) cudaEventRecord(stop, st); }
+};
 
 struct DeviceInfo {
     int sms = 0;
@@ -130,8 +144,11 @@ int launch_forward_vec(const void* value, const int64_t* shapes, const int64_t* 
     auto kern = msda_forward_kernel<VT, AT, VEC, GS, NW>;
     static const int occ = query_occupancy(kern, NW * 32);   // once per instantiation
     const int grid = persistent_grid(occ, items_upper_bound(k));
-    kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                                   (VT*)out, k);
+    {
+        TraceScope trace(st);
+        kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
+                                       (VT*)out, k);
+    }
     ++g_last_launches;
     return (int)cudaGetLastError();
 }
@@ -192,8 +209,11 @@ int launch_backward_vec(const void* value, const int64_t* shapes, const int64_t*
     auto kern = msda_backward_kernel<VT, AT, VEC, GS, NW>;
     static const int occ = query_occupancy(kern, NW * 32);   // once per instantiation
     const int grid = persistent_grid(occ, items_upper_bound(k));
-    kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                                   (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k);
+    {
+        TraceScope trace(st);
+        kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
+                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k);
+    }
     ++g_last_launches;
     return (int)cudaGetLastError();
 }
@@ -305,6 +325,12 @@ const char* msda_b200_error_string(int code)
 }
 
 int msda_b200_last_launch_count(void) { return g_last_launches; }
+
+void msda_b200_trace_next(void* start_event, void* stop_event)
+{
+    g_trace_start = (cudaEvent_t)start_event;
+    g_trace_stop = (cudaEvent_t)stop_event;
+}
 
 int msda_b200_forward(const void* value, int value_dtype, const int64_t* spatial_shapes,
                       const int64_t* level_start, const void* sampling_loc, const void* attn_weight,

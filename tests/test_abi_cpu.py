@@ -23,7 +23,7 @@ def test_header_symbols_are_exported(lib):
     declared = set(re.findall(r"\b(msda_b200_\w+)\s*\(", hdr))
     assert {"msda_b200_forward", "msda_b200_backward", "msda_b200_backward_workspace_bytes",
             "msda_b200_error_string", "msda_b200_abi_version",
-            "msda_b200_last_launch_count"} <= declared
+            "msda_b200_last_launch_count", "msda_b200_trace_next"} <= declared
     for name in declared:
         assert hasattr(lib, name), name
     from kinet_b200 import _lib

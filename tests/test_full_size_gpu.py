@@ -1,0 +1,75 @@
+"""Full BASELINE.json sizes on the GPU: (a) against the REFERENCE's own CUDA kernels compiled for
+sm_100a (oracle/_ref, built in the dev container from /root/reference by oracle/ref_cuda/build_ref.py)
+and (b) through size-independent properties (linearity in value / attention weights, adjointness
+<out, g> = <value, grad_value>, zero-weight idempotence).  ``-m gpu``."""
+import numpy as np
+import pytest
+import torch
+
+from kinet_b200.workloads import make_inputs, resolve
+
+pytestmark = pytest.mark.gpu
+
+TAGS = ["C1_dec", "C2_enc", "C3_enc", "C3_dec", "C5_enc", "C5_dec"]
+
+
+def _ours(value, shapes, loc, attn, go=None):
+    from kinet_b200.functions import ms_deform_attn_backward, ms_deform_attn_forward
+    out = ms_deform_attn_forward(value, shapes, loc, attn, 64)
+    grads = ms_deform_attn_backward(value, shapes, loc, attn, go, 64) if go is not None else None
+    return out, grads
+
+
+def _rel(a, b):
+    return float((a.double() - b.double()).abs().max() / b.double().abs().max().clamp_min(1e-30))
+
+
+@pytest.mark.parametrize("regime", ["structured", "uniform"])
+@pytest.mark.parametrize("tag", TAGS)
+def test_full_size_matches_reference_cuda_kernels(tag, regime):
+    from oracle import msda_ref_cuda as ref
+    if not ref.available():
+        pytest.skip("oracle/_ref/libmsda_ref_cuda.so not built (needs /root/reference at build time)")
+    dev = torch.device("cuda:0")
+    s = resolve(tag)
+    value, shapes, loc, attn = make_inputs(tag, dev, torch.float32, torch.float32, regime, seed=1)
+    go = torch.randn(s["N"], s["Lq"], s["M"] * s["D"], device=dev)
+    out, (gv, gl, ga) = _ours(value, shapes, loc, attn, go)
+    r_out = ref.ref_cuda_forward(value, shapes, loc, attn)
+    r_gv, r_gl, r_ga = ref.ref_cuda_backward(value, shapes, loc, attn, go)
+    assert _rel(out, r_out) <= 1e-5
+    assert _rel(gv, r_gv) <= 1e-5          # both sides sum in fp32 with unordered atomics
+    assert _rel(ga, r_ga) <= 1e-5
+    # grad_sampling_loc: exclude samples within 2e-4 px of a bilinear kink (one-sided derivative)
+    hw = shapes.double()
+    x = loc[..., 0].double() * hw[None, None, None, :, None, 1] - 0.5
+    y = loc[..., 1].double() * hw[None, None, None, :, None, 0] - 0.5
+    ok = (((x - x.round()).abs() > 2e-4) & ((y - y.round()).abs() > 2e-4))[..., None]
+    err = ((gl.double() - r_gl.double()).abs() * ok).max() / r_gl.double().abs().max()
+    assert float(err) <= 1e-5
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("tag", ["C2_enc", "C3_dec", "C5_enc"])
+def test_full_size_properties(tag, dtype):
+    dev = torch.device("cuda:0")
+    s = resolve(tag)
+    value, shapes, loc, attn = make_inputs(tag, dev, dtype, torch.float32, "structured", seed=2)
+    go = torch.randn(s["N"], s["Lq"], s["M"] * s["D"], device=dev).to(dtype)
+    tol = 1e-5 if dtype == torch.float32 else 1.2e-2
+    out, (gv, gl, ga) = _ours(value, shapes, loc, attn, go)
+    # linearity in the attention weights: f(v, 2a) = 2 f(v, a)   (exact in binary floating point)
+    out2, _ = _ours(value, shapes, loc, attn * 2, None)
+    assert _rel(out2.float(), out.float() * 2) <= (0 if dtype == torch.float32 else 8e-3)
+    # linearity in value: f(v1 + v2) = f(v1) + f(v2)
+    v2 = torch.randn_like(value)
+    o_sum, _ = _ours((value.float() + v2.float()).to(dtype), shapes, loc, attn)
+    o_2, _ = _ours(v2, shapes, loc, attn)
+    assert _rel(o_sum.float(), out.float() + o_2.float()) <= max(tol, 3e-5) * 3
+    # adjointness: <f(v), g> == <v, grad_value>  and  == <a, grad_attn>
+    lhs = (out.double() * go.double()).sum()
+    assert abs(float((value.double() * gv.double()).sum() / lhs) - 1) <= (1e-4 if dtype == torch.float32 else 2e-2)
+    assert abs(float((attn.double() * ga.double()).sum() / lhs) - 1) <= (1e-4 if dtype == torch.float32 else 2e-2)
+    # zero attention weights: zero output, zero grad_value, zero grad_loc
+    z_out, (z_gv, z_gl, _) = _ours(value, shapes, loc, torch.zeros_like(attn), go)
+    assert not z_out.any() and not z_gv.any() and not z_gl.any()
