@@ -5,305 +5,23 @@
 // re-designed: no allocation, no host loop over im2col_step chunks, no per-call
 // ATen ops for level_start_index, no host synchronisation.  Picks a kernel
 // instantiation from (value dtype, aux dtype, D) and a tiling from the shape.
-#include <cstdlib>
-#include <cstring>
+#include "msda_launch.cuh"
 
-#include "msda_bwd.cuh"
-#include "msda_fwd.cuh"
-
-namespace {
-
-using namespace msda;
+namespace msda {
 
 thread_local int g_last_launches = 0;
 thread_local cudaEvent_t g_trace_start = nullptr, g_trace_stop = nullptr;
 
-// One-shot event bracket around the dominant kernel (msda_b200_trace_next).
-struct TraceScope {
-    cudaStream_t st;
-    cudaEvent_t stop;
-    explicit TraceScope(cudaStream_t s) : st(s), stop(g_trace_stop)
-    {
-        if (g_trace_start) cudaEventRecord(g_trace_start, st);
-        g_trace_start = nullptr;
-        g_trace_stop = nullptr;
-    }
-    ~TraceScope() { if (stop) cudaEventRecord(stop, st); }
-};
+// instantiated in msda_inst_{f32,bf16,f16}.cu
+MSDA_DECLARE_TYPED(extern, float, float)
+MSDA_DECLARE_TYPED(extern, __nv_bfloat16, float)
+MSDA_DECLARE_TYPED(extern, __nv_bfloat16, __nv_bfloat16)
+MSDA_DECLARE_TYPED(extern, __half, float)
+MSDA_DECLARE_TYPED(extern, __half, __half)
 
-struct DeviceInfo {
-    int sms = 0;
-};
+}  // namespace msda
 
-DeviceInfo device_info()
-{
-    static thread_local int cached_dev = -1;
-    static thread_local DeviceInfo info;
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return info;
-    if (dev != cached_dev) {
-        cudaDeviceGetAttribute(&info.sms, cudaDevAttrMultiProcessorCount, dev);
-        cached_dev = dev;
-    }
-    return info;
-}
-
-int env_int(const char* name, int dflt)
-{
-    const char* v = std::getenv(name);
-    return (v && *v) ? std::atoi(v) : dflt;
-}
-
-int check_common(const void* value, const int64_t* shapes, const void* loc, const void* attn,
-                 const msda_dims* d)
-{
-    if (!d) return MSDA_E_NULL;
-    if (d->N <= 0 || d->S <= 0 || d->M <= 0 || d->D <= 0 || d->L <= 0 || d->P <= 0 || d->Lq < 0)
-        return MSDA_E_SHAPE;
-    if (d->L > MSDA_MAX_LEVELS) return MSDA_E_SHAPE;
-    // 32-bit element offsets inside one batch item
-    if ((long long)d->S * d->M * d->D >= (1ll << 31)) return MSDA_E_SHAPE;
-    if ((long long)d->L * d->P >= (1 << 20)) return MSDA_E_SHAPE;
-    if (!value || !shapes) return MSDA_E_NULL;
-    if (d->Lq > 0 && (!loc || !attn)) return MSDA_E_NULL;
-    return 0;
-}
-
-bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
-
-// Tiling choice.  Encoder form (Lq == S: queries are the pyramid's pixels, whose
-// samples cluster around the query's own position): 2-D tiles per level so the
-// gather footprint of one CTA is a compact patch.  Otherwise 1-D tiles over the
-// query index, sized so the grid still covers every SM.
-KernelDims make_dims(const msda_dims* d, int rows_per_pass)
-{
-    KernelDims k;
-    k.N = d->N; k.S = d->S; k.M = d->M; k.D = d->D; k.L = d->L; k.Lq = d->Lq; k.P = d->P;
-    const int sms = device_info().sms > 0 ? device_info().sms : 148;
-    const int force_1d = env_int("MSDA_B200_TILE_1D", 0);
-    if (d->Lq == d->S && !force_1d) {
-        k.tile_h = env_int("MSDA_B200_TILE_H", 8);
-        k.tile_w = env_int("MSDA_B200_TILE_W", 32);
-        k.tile_q = k.tile_h * k.tile_w;
-    } else {
-        k.tile_h = 0; k.tile_w = 0;
-        int tq = env_int("MSDA_B200_TILE_Q", 0);
-        if (tq <= 0) {
-            tq = 256;
-            // shrink until there are at least ~4 items per SM (or one pass per item)
-            while (tq > rows_per_pass &&
-                   (long long)d->N * d->M * ((d->Lq + tq - 1) / tq) < 4ll * sms)
-                tq >>= 1;
-            if (tq < rows_per_pass) tq = rows_per_pass;
-        }
-        k.tile_q = tq;
-    }
-    return k;
-}
-
-template <typename Kern>
-int query_occupancy(Kern kern, int threads)
-{
-    int occ = 1;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, 0);
-    return occ < 1 ? 1 : occ;
-}
-
-// Persistent grid: one wave of resident CTAs (or fewer when there is less work).
-int persistent_grid(int occ, long long items_upper)
-{
-    const int cap = env_int("MSDA_B200_CTAS_PER_SM", 0);
-    if (cap > 0 && cap < occ) occ = cap;
-    const int sms = device_info().sms > 0 ? device_info().sms : 148;
-    long long g = (long long)sms * occ;
-    if (items_upper < g) g = items_upper;
-    return (int)(g < 1 ? 1 : g);
-}
-
-// Upper bound of the number of work items without knowing the level shapes on the
-// host (they live in device memory): 2-D tiling adds at most one ragged tile row
-// and column per level, bounded by S/tile + (S/tile_w + S/tile_h + 1) per level;
-// the kernel loops `item < items` with the exact count, so a loose bound only
-// means a few idle CTAs.
-long long items_upper_bound(const KernelDims& k)
-{
-    long long tiles;
-    if (k.tile_h > 0)
-        tiles = (long long)k.S / k.tile_q + (long long)k.L * ((long long)k.S / k.tile_w + (long long)k.S / k.tile_h + 1);
-    else
-        tiles = (k.Lq + k.tile_q - 1) / k.tile_q;
-    return tiles * k.N * k.M;
-}
-
-template <typename VT, typename AT, int VEC, int GS>
-int launch_forward_vec(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
-                       const void* attn, void* out, const msda_dims* d, cudaStream_t st)
-{
-    constexpr int NW = 8;
-    const KernelDims k = make_dims(d, NW * (32 / GS));
-    auto kern = msda_forward_kernel<VT, AT, VEC, GS, NW>;
-    static const int occ = query_occupancy(kern, NW * 32);   // once per instantiation
-    const int grid = persistent_grid(occ, items_upper_bound(k));
-    {
-        TraceScope trace(st);
-        kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                                       (VT*)out, k);
-    }
-    ++g_last_launches;
-    return (int)cudaGetLastError();
-}
-
-template <typename VT, typename AT, typename ACC>
-int launch_forward_generic(const void* value, const int64_t* shapes, const int64_t* ls,
-                           const void* loc, const void* attn, void* out, const msda_dims* d,
-                           cudaStream_t st)
-{
-    KernelDims k = make_dims(d, 8);
-    k.tile_h = 0; k.tile_w = 0; k.tile_q = 8;
-    const long long rows = (long long)d->N * d->Lq * d->M;
-    auto kern = msda_forward_generic_kernel<VT, AT, ACC>;
-    static const int occ = query_occupancy(kern, 256);
-    const int grid = persistent_grid(occ, (rows + 7) / 8);
-    kern<<<grid, 256, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                               (VT*)out, k);
-    ++g_last_launches;
-    return (int)cudaGetLastError();
-}
-
-template <typename VT, typename AT>
-int forward_typed(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
-                  const void* attn, void* out, const msda_dims* d, cudaStream_t st)
-{
-    const bool al = aligned16(value) && aligned16(out) && !env_int("MSDA_B200_FORCE_GENERIC", 0);
-    if constexpr (sizeof(VT) == 4) {
-        if (al) switch (d->D) {
-            case 16: return launch_forward_vec<VT, AT, 4, 4>(value, shapes, ls, loc, attn, out, d, st);
-            case 32: return launch_forward_vec<VT, AT, 4, 8>(value, shapes, ls, loc, attn, out, d, st);
-            case 36: return launch_forward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, out, d, st);
-            case 64: return launch_forward_vec<VT, AT, 4, 16>(value, shapes, ls, loc, attn, out, d, st);
-            default: break;
-        }
-    } else {
-        if (al) switch (d->D) {
-            case 16: return launch_forward_vec<VT, AT, 8, 2>(value, shapes, ls, loc, attn, out, d, st);
-            case 32: return launch_forward_vec<VT, AT, 8, 4>(value, shapes, ls, loc, attn, out, d, st);
-            case 36: return launch_forward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, out, d, st);
-            case 64: return launch_forward_vec<VT, AT, 8, 8>(value, shapes, ls, loc, attn, out, d, st);
-            default: break;
-        }
-    }
-    return launch_forward_generic<VT, AT, float>(value, shapes, ls, loc, attn, out, d, st);
-}
-
-}  // namespace
-
-namespace {
-
-template <typename VT, typename AT, int VEC, int GS>
-int launch_backward_vec(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
-                        const void* attn, const void* go, float* gv_acc, void* gl, void* ga,
-                        const msda_dims* d, cudaStream_t st)
-{
-    constexpr int NW = 8;
-    const KernelDims k = make_dims(d, NW * (32 / GS));
-    auto kern = msda_backward_kernel<VT, AT, VEC, GS, NW>;
-    static const int occ = query_occupancy(kern, NW * 32);   // once per instantiation
-    const int grid = persistent_grid(occ, items_upper_bound(k));
-    {
-        TraceScope trace(st);
-        kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k);
-    }
-    ++g_last_launches;
-    return (int)cudaGetLastError();
-}
-
-template <typename VT, typename AT, typename ACC>
-int launch_backward_generic(const void* value, const int64_t* shapes, const int64_t* ls,
-                            const void* loc, const void* attn, const void* go, ACC* gv_acc,
-                            void* gl, void* ga, const msda_dims* d, cudaStream_t st)
-{
-    KernelDims k = make_dims(d, 8);
-    k.tile_h = 0; k.tile_w = 0; k.tile_q = 8;
-    const long long rows = (long long)d->N * d->Lq * d->M;
-    auto kern = msda_backward_generic_kernel<VT, AT, ACC>;
-    static const int occ = query_occupancy(kern, 256);
-    const int grid = persistent_grid(occ, (rows + 7) / 8);
-    kern<<<grid, 256, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                               (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k);
-    ++g_last_launches;
-    return (int)cudaGetLastError();
-}
-
-// VT = float: gradients accumulate straight into grad_value (zero-filled first).
-// 16-bit VT: accumulate in the fp32 workspace, then round once.
-template <typename VT, typename AT>
-int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
-                   const void* attn, const void* go, void* gv, void* gl, void* ga, void* ws,
-                   size_t ws_bytes, const msda_dims* d, cudaStream_t st)
-{
-    const size_t nval = (size_t)d->N * d->S * d->M * d->D;
-    float* acc;
-    if constexpr (sizeof(VT) == 4) {
-        acc = (float*)gv;
-    } else {
-        if (!ws || ws_bytes < nval * sizeof(float)) return MSDA_E_WORKSPACE;
-        if (!aligned16(ws)) return MSDA_E_ALIGN;
-        acc = (float*)ws;
-    }
-    cudaError_t e = cudaMemsetAsync(acc, 0, nval * sizeof(float), st);
-    if (e != cudaSuccess) return (int)e;
-    int rc = 0;
-    if (d->Lq > 0) {
-        const bool al = aligned16(value) && aligned16(go) && aligned16(acc) &&
-                        !env_int("MSDA_B200_FORCE_GENERIC", 0);
-        bool done = false;
-        if constexpr (sizeof(VT) == 4) {
-            if (al) switch (d->D) {
-                case 16: rc = launch_backward_vec<VT, AT, 4, 4>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                case 32: rc = launch_backward_vec<VT, AT, 4, 8>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                case 36: rc = launch_backward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                case 64: rc = launch_backward_vec<VT, AT, 4, 16>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                default: break;
-            }
-        } else {
-            if (al) switch (d->D) {
-                case 16: rc = launch_backward_vec<VT, AT, 8, 2>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                case 32: rc = launch_backward_vec<VT, AT, 8, 4>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                case 36: rc = launch_backward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                case 64: rc = launch_backward_vec<VT, AT, 8, 8>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                default: break;
-            }
-        }
-        if (!done) rc = launch_backward_generic<VT, AT, float>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st);
-        if (rc) return rc;
-    }
-    if constexpr (sizeof(VT) == 2) {
-        const int sms = device_info().sms > 0 ? device_info().sms : 148;
-        if (nval % 8 == 0 && aligned16(gv)) {
-            msda_round_grad_value_kernel<VT><<<sms * 8, 256, 0, st>>>(acc, (VT*)gv, nval / 8);
-        } else {
-            msda_round_generic_kernel<VT, float><<<sms * 8, 256, 0, st>>>(acc, (VT*)gv, nval);
-        }
-        ++g_last_launches;
-        rc = (int)cudaGetLastError();
-    }
-    return rc;
-}
-
-int backward_f64(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
-                 const void* attn, const void* go, void* gv, void* gl, void* ga,
-                 const msda_dims* d, cudaStream_t st)
-{
-    const size_t nval = (size_t)d->N * d->S * d->M * d->D;
-    cudaError_t e = cudaMemsetAsync(gv, 0, nval * sizeof(double), st);
-    if (e != cudaSuccess) return (int)e;
-    if (d->Lq == 0) return 0;
-    return launch_backward_generic<double, double, double>(value, shapes, ls, loc, attn, go,
-                                                           (double*)gv, gl, ga, d, st);
-}
-
-}  // namespace
+using namespace msda;
 
 extern "C" {
 
@@ -350,8 +68,7 @@ int msda_b200_forward(const void* value, int value_dtype, const int64_t* spatial
     if (value_dtype == MSDA_F16 && aux_dtype == MSDA_F16) MSDA_FWD(__half, __half);
 #undef MSDA_FWD
     if (value_dtype == MSDA_F64 && aux_dtype == MSDA_F64)
-        return launch_forward_generic<double, double, double>(value, spatial_shapes, level_start,
-                                                              sampling_loc, attn_weight, output, dims, st);
+        return forward_f64(value, spatial_shapes, level_start, sampling_loc, attn_weight, output, dims, st);
     return MSDA_E_DTYPE;
 }
 

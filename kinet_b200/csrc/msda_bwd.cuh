@@ -66,7 +66,7 @@ __device__ __forceinline__ void reduce_scatter(float (&U)[N][4], int gl, float (
 
 // WIDE: every level has W > 1 (uniform column step of the 2x2 footprint).
 template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE>
-__device__ __forceinline__ void backward_items(const LevelTable& lt, int4* stage_a, float4* stage_b,
+__device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage_a, int* stage_dx, float4* stage_b,
                                                const VT* __restrict__ value,
                                                const AT* __restrict__ loc, const AT* __restrict__ attn,
                                                const VT* __restrict__ grad_out,
@@ -105,6 +105,33 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int4* stage
 #pragma unroll
             for (int k = 0; k < VEC; ++k) g[k] = 0.f;
             if (row_ok) VecIO<VT, VEC>::load_stream(grad_out + row * D + gl * VEC, g);
+            // Operands of the grad_value reductions.  L2 executes a reduction per 32-byte sector, and
+            // a sector that one instruction covers only half costs as much as a full one.  With
+            // VEC = 8 a lane's 8 fp32 channels ARE one sector, which its two 16-byte reductions
+            // would each half-cover; so lane pairs swap halves: instruction A completes the even
+            // lane's sector, instruction B the odd lane's (the partner's 4 channels of grad_out are
+            // fetched once per row with 4 shuffles).
+            float gr[VEC];
+            int roff[VEC / 4];
+            if constexpr (VEC == 8) {
+                static_assert(GS % 2 == 0, "lane pairs");
+                const bool odd = (gl & 1) != 0;
+                float gp[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) gp[k] = __shfl_xor_sync(0xffffffffu, odd ? g[k] : g[4 + k], 1);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    gr[k] = odd ? gp[k] : g[k];           // A: even lane own low half | odd lane: partner's high half
+                    gr[4 + k] = odd ? g[4 + k] : gp[k];   // B: even lane: partner's low half | odd lane own high half
+                }
+                roff[0] = odd ? -4 : 0;
+                roff[1] = odd ? 4 : 8;
+            } else {
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) gr[k] = g[k];
+#pragma unroll
+                for (int k = 0; k < VEC / 4; ++k) roff[k] = 4 * k;
+            }
 
             for (int s0 = 0; s0 < LP; s0 += GS) {
                 // owner phase: lane gl prepares sample s0 + gl of its row
@@ -123,7 +150,8 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int4* stage
                 // publish the tap (offsets; corner weight * attn) in shared memory, [sample][group]
                 __syncwarp();
                 if (lane_used) {
-                    stage_a[gl * GPW + grp] = make_int4(t.off0, t.off0 + t.dy, WIDE ? rsv : t.dx, 0);
+                    stage_a[gl * GPW + grp] = make_int2(t.off0, t.off0 + t.dy);
+                    if constexpr (!WIDE) stage_dx[gl * GPW + grp] = t.dx;
                     stage_b[gl * GPW + grp] = make_float4(wa0 * t.ax.w0, wa0 * t.ax.w1, wa1 * t.ax.w0, wa1 * t.ax.w1);
                 }
                 __syncwarp();
@@ -133,9 +161,9 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int4* stage
                 float U[GS][4];
 #pragma unroll
                 for (int j = 0; j < GS; ++j) {
-                    const int4 ra = stage_a[j * GPW + gsel];
+                    const int2 ra = stage_a[j * GPW + gsel];
                     const float4 rb = stage_b[j * GPW + gsel];
-                    const int o0 = ra.x, o2 = ra.y, dx = WIDE ? rsv : ra.z;
+                    const int o0 = ra.x, o2 = ra.y, dx = WIDE ? rsv : stage_dx[j * GPW + gsel];
                     const float bw[4] = {rb.x, rb.y, rb.z, rb.w};
                     const unsigned o[4] = {(unsigned)o0, (unsigned)(o0 + dx), (unsigned)o2, (unsigned)(o2 + dx)};
                     float v[4][VEC];
@@ -161,8 +189,8 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int4* stage
                             float* dst = gv_base + (size_t)o[c] * VEC;
 #pragma unroll
                             for (int k = 0; k < VEC; k += 4)
-                                red_add_f32x4(dst + k, bw[c] * g[k], bw[c] * g[k + 1], bw[c] * g[k + 2],
-                                              bw[c] * g[k + 3]);
+                                red_add_f32x4(dst + roff[k / 4], bw[c] * gr[k], bw[c] * gr[k + 1], bw[c] * gr[k + 2],
+                                              bw[c] * gr[k + 3]);
                         }
                     }
                 }
@@ -209,15 +237,16 @@ msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ s
 {
     __shared__ LevelTable lt;
     stage_levels(lt, shapes, level_start, d);
-    __shared__ int4 stage_a[NWARPS][32];
+    __shared__ int2 stage_a[NWARPS][32];
+    __shared__ int stage_dx[NWARPS][32];
     __shared__ float4 stage_b[NWARPS][32];
     const int warp = threadIdx.x >> 5;
     if (lt.min_w > 1)
-        backward_items<VT, AT, VEC, GS, NWARPS, true>(lt, stage_a[warp], stage_b[warp], value, loc, attn, grad_out, grad_value_acc,
-                                                      grad_loc, grad_attn, d);
+        backward_items<VT, AT, VEC, GS, NWARPS, true>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc, attn,
+                                                      grad_out, grad_value_acc, grad_loc, grad_attn, d);
     else
-        backward_items<VT, AT, VEC, GS, NWARPS, false>(lt, stage_a[warp], stage_b[warp], value, loc, attn, grad_out, grad_value_acc,
-                                                       grad_loc, grad_attn, d);
+        backward_items<VT, AT, VEC, GS, NWARPS, false>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc, attn,
+                                                       grad_out, grad_value_acc, grad_loc, grad_attn, d);
 }
 
 // fp32 workspace -> 16-bit grad_value (one rounding of the full sum).

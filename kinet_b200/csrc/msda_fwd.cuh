@@ -35,7 +35,7 @@ __device__ __forceinline__ void gather_sample(float (&acc)[VEC], const VT* lane_
 
 // WIDE: every level has W > 1, so the column step of the 2x2 footprint is the same for all samples.
 template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE>
-__device__ __forceinline__ void forward_items(const LevelTable& lt, int4* stage_a, float4* stage_b,
+__device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_a, int* stage_dx, float4* stage_b,
                                               const VT* __restrict__ value,
                                               const AT* __restrict__ loc, const AT* __restrict__ attn,
                                               VT* __restrict__ out, const KernelDims& d)
@@ -85,7 +85,8 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int4* stage_
                 // (Shuffles would cost one LSU data-pipe wavefront per value; this is 3 per sample.)
                 __syncwarp();
                 if (lane_used) {
-                    stage_a[gl * GPW + grp] = make_int4(t.off0, t.off0 + t.dy, WIDE ? rsv : t.dx, 0);
+                    stage_a[gl * GPW + grp] = make_int2(t.off0, t.off0 + t.dy);
+                    if constexpr (!WIDE) stage_dx[gl * GPW + grp] = t.dx;
                     stage_b[gl * GPW + grp] = make_float4(wa0 * t.ax.w0, wa0 * t.ax.w1, wa1 * t.ax.w0, wa1 * t.ax.w1);
                 }
                 __syncwarp();
@@ -95,9 +96,10 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int4* stage_
                 const int gsel = lane_used ? grp : 0;
 #pragma unroll
                 for (int j = 0; j < GS; ++j) {
-                    const int4 ra = stage_a[j * GPW + gsel];
+                    const int2 ra = stage_a[j * GPW + gsel];
                     const float4 rb = stage_b[j * GPW + gsel];
-                    gather_sample<VT, VEC>(acc, lane_base, ra.x, ra.y, WIDE ? rsv : ra.z, rb.x, rb.y, rb.z, rb.w);
+                    gather_sample<VT, VEC>(acc, lane_base, ra.x, ra.y, WIDE ? rsv : stage_dx[j * GPW + gsel], rb.x, rb.y,
+                                           rb.z, rb.w);
                 }
             }
             if (row_ok) VecIO<VT, VEC>::store(out + row * D + gl * VEC, acc);
@@ -114,13 +116,14 @@ msda_forward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ sh
     __shared__ LevelTable lt;
     stage_levels(lt, shapes, level_start, d);
     // With W > 1 everywhere and at least two pixels, base + column step is always valid memory.
-    __shared__ int4 stage_a[NWARPS][32];
+    __shared__ int2 stage_a[NWARPS][32];
+    __shared__ int stage_dx[NWARPS][32];
     __shared__ float4 stage_b[NWARPS][32];
     const int warp = threadIdx.x >> 5;
     if (lt.min_w > 1)
-        forward_items<VT, AT, VEC, GS, NWARPS, true>(lt, stage_a[warp], stage_b[warp], value, loc, attn, out, d);
+        forward_items<VT, AT, VEC, GS, NWARPS, true>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc, attn, out, d);
     else
-        forward_items<VT, AT, VEC, GS, NWARPS, false>(lt, stage_a[warp], stage_b[warp], value, loc, attn, out, d);
+        forward_items<VT, AT, VEC, GS, NWARPS, false>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc, attn, out, d);
 }
 
 // Generic fallback: any D, any supported type (incl. fp64).  One warp per

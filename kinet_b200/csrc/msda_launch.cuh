@@ -1,0 +1,301 @@
+// msda_launch.cuh -- host-side launchers: kernel selection from (dtype, D), tiling choice and
+// persistent grid sizing.  Included by msda_abi.cu (entry points) and by the msda_inst_*.cu files,
+// which hold the explicit instantiations so the dtype families compile in parallel.
+#pragma once
+#include <cstdlib>
+#include <cstring>
+
+#include "msda_bwd.cuh"
+#include "msda_fwd.cuh"
+
+namespace msda {
+
+// per-thread call state, defined in msda_abi.cu
+extern thread_local int g_last_launches;
+extern thread_local cudaEvent_t g_trace_start, g_trace_stop;
+
+// One-shot event bracket around the dominant kernel (msda_b200_trace_next).
+struct TraceScope {
+    cudaStream_t st;
+    cudaEvent_t stop;
+    explicit TraceScope(cudaStream_t s) : st(s), stop(g_trace_stop)
+    {
+        if (g_trace_start) cudaEventRecord(g_trace_start, st);
+        g_trace_start = nullptr;
+        g_trace_stop = nullptr;
+    }
+    ~TraceScope() { if (stop) cudaEventRecord(stop, st); }
+};
+
+struct DeviceInfo {
+    int sms = 0;
+};
+
+inline DeviceInfo device_info()
+{
+    static thread_local int cached_dev = -1;
+    static thread_local DeviceInfo info;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return info;
+    if (dev != cached_dev) {
+        cudaDeviceGetAttribute(&info.sms, cudaDevAttrMultiProcessorCount, dev);
+        cached_dev = dev;
+    }
+    return info;
+}
+
+inline int env_int(const char* name, int dflt)
+{
+    const char* v = std::getenv(name);
+    return (v && *v) ? std::atoi(v) : dflt;
+}
+
+inline int check_common(const void* value, const int64_t* shapes, const void* loc, const void* attn,
+                 const msda_dims* d)
+{
+    if (!d) return MSDA_E_NULL;
+    if (d->N <= 0 || d->S <= 0 || d->M <= 0 || d->D <= 0 || d->L <= 0 || d->P <= 0 || d->Lq < 0)
+        return MSDA_E_SHAPE;
+    if (d->L > MSDA_MAX_LEVELS) return MSDA_E_SHAPE;
+    // 32-bit element offsets inside one batch item
+    if ((long long)d->S * d->M * d->D >= (1ll << 31)) return MSDA_E_SHAPE;
+    if ((long long)d->L * d->P >= (1 << 20)) return MSDA_E_SHAPE;
+    if (!value || !shapes) return MSDA_E_NULL;
+    if (d->Lq > 0 && (!loc || !attn)) return MSDA_E_NULL;
+    return 0;
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// Tiling choice.  Encoder form (Lq == S: queries are the pyramid's pixels, whose
+// samples cluster around the query's own position): 2-D tiles per level so the
+// gather footprint of one CTA is a compact patch.  Otherwise 1-D tiles over the
+// query index, sized so the grid still covers every SM.
+inline KernelDims make_dims(const msda_dims* d, int rows_per_pass)
+{
+    KernelDims k;
+    k.N = d->N; k.S = d->S; k.M = d->M; k.D = d->D; k.L = d->L; k.Lq = d->Lq; k.P = d->P;
+    const int sms = device_info().sms > 0 ? device_info().sms : 148;
+    const int force_1d = env_int("MSDA_B200_TILE_1D", 0);
+    if (d->Lq == d->S && !force_1d) {
+        k.tile_h = env_int("MSDA_B200_TILE_H", 8);
+        k.tile_w = env_int("MSDA_B200_TILE_W", 32);
+        k.tile_q = k.tile_h * k.tile_w;
+    } else {
+        k.tile_h = 0; k.tile_w = 0;
+        int tq = env_int("MSDA_B200_TILE_Q", 0);
+        if (tq <= 0) {
+            tq = 256;
+            // shrink until there are at least ~4 items per SM (or one pass per item)
+            while (tq > rows_per_pass &&
+                   (long long)d->N * d->M * ((d->Lq + tq - 1) / tq) < 4ll * sms)
+                tq >>= 1;
+            if (tq < rows_per_pass) tq = rows_per_pass;
+        }
+        k.tile_q = tq;
+    }
+    return k;
+}
+
+template <typename Kern>
+int query_occupancy(Kern kern, int threads)
+{
+    int occ = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, 0);
+    return occ < 1 ? 1 : occ;
+}
+
+// Persistent grid: one wave of resident CTAs (or fewer when there is less work).
+inline int persistent_grid(int occ, long long items_upper)
+{
+    const int cap = env_int("MSDA_B200_CTAS_PER_SM", 0);
+    if (cap > 0 && cap < occ) occ = cap;
+    const int sms = device_info().sms > 0 ? device_info().sms : 148;
+    long long g = (long long)sms * occ;
+    if (items_upper < g) g = items_upper;
+    return (int)(g < 1 ? 1 : g);
+}
+
+// Upper bound of the number of work items without knowing the level shapes on the
+// host (they live in device memory): 2-D tiling adds at most one ragged tile row
+// and column per level, bounded by S/tile + (S/tile_w + S/tile_h + 1) per level;
+// the kernel loops `item < items` with the exact count, so a loose bound only
+// means a few idle CTAs.
+inline long long items_upper_bound(const KernelDims& k)
+{
+    long long tiles;
+    if (k.tile_h > 0)
+        tiles = (long long)k.S / k.tile_q + (long long)k.L * ((long long)k.S / k.tile_w + (long long)k.S / k.tile_h + 1);
+    else
+        tiles = (k.Lq + k.tile_q - 1) / k.tile_q;
+    return tiles * k.N * k.M;
+}
+
+template <typename VT, typename AT, int VEC, int GS>
+int launch_forward_vec(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
+                       const void* attn, void* out, const msda_dims* d, cudaStream_t st)
+{
+    constexpr int NW = 8;
+    const KernelDims k = make_dims(d, NW * (32 / GS));
+    auto kern = msda_forward_kernel<VT, AT, VEC, GS, NW>;
+    static const int occ = query_occupancy(kern, NW * 32);   // once per instantiation
+    const int grid = persistent_grid(occ, items_upper_bound(k));
+    {
+        TraceScope trace(st);
+        kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
+                                       (VT*)out, k);
+    }
+    ++g_last_launches;
+    return (int)cudaGetLastError();
+}
+
+template <typename VT, typename AT, typename ACC>
+int launch_forward_generic(const void* value, const int64_t* shapes, const int64_t* ls,
+                           const void* loc, const void* attn, void* out, const msda_dims* d,
+                           cudaStream_t st)
+{
+    KernelDims k = make_dims(d, 8);
+    k.tile_h = 0; k.tile_w = 0; k.tile_q = 8;
+    const long long rows = (long long)d->N * d->Lq * d->M;
+    auto kern = msda_forward_generic_kernel<VT, AT, ACC>;
+    static const int occ = query_occupancy(kern, 256);
+    const int grid = persistent_grid(occ, (rows + 7) / 8);
+    kern<<<grid, 256, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
+                               (VT*)out, k);
+    ++g_last_launches;
+    return (int)cudaGetLastError();
+}
+
+template <typename VT, typename AT>
+int forward_typed(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
+                  const void* attn, void* out, const msda_dims* d, cudaStream_t st)
+{
+    const bool al = aligned16(value) && aligned16(out) && !env_int("MSDA_B200_FORCE_GENERIC", 0);
+    if constexpr (sizeof(VT) == 4) {
+        if (al) switch (d->D) {
+            case 16: return launch_forward_vec<VT, AT, 4, 4>(value, shapes, ls, loc, attn, out, d, st);
+            case 32: return launch_forward_vec<VT, AT, 4, 8>(value, shapes, ls, loc, attn, out, d, st);
+            case 36: return launch_forward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, out, d, st);
+            case 64: return launch_forward_vec<VT, AT, 4, 16>(value, shapes, ls, loc, attn, out, d, st);
+            default: break;
+        }
+    } else {
+        if (al) switch (d->D) {
+            case 16: return launch_forward_vec<VT, AT, 8, 2>(value, shapes, ls, loc, attn, out, d, st);
+            case 32: return launch_forward_vec<VT, AT, 8, 4>(value, shapes, ls, loc, attn, out, d, st);
+            case 36: return launch_forward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, out, d, st);
+            case 64: return launch_forward_vec<VT, AT, 8, 8>(value, shapes, ls, loc, attn, out, d, st);
+            default: break;
+        }
+    }
+    return launch_forward_generic<VT, AT, float>(value, shapes, ls, loc, attn, out, d, st);
+}
+
+template <typename VT, typename AT, int VEC, int GS>
+int launch_backward_vec(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
+                        const void* attn, const void* go, float* gv_acc, void* gl, void* ga,
+                        const msda_dims* d, cudaStream_t st)
+{
+    constexpr int NW = 8;
+    const KernelDims k = make_dims(d, NW * (32 / GS));
+    auto kern = msda_backward_kernel<VT, AT, VEC, GS, NW>;
+    static const int occ = query_occupancy(kern, NW * 32);   // once per instantiation
+    const int grid = persistent_grid(occ, items_upper_bound(k));
+    {
+        TraceScope trace(st);
+        kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
+                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k);
+    }
+    ++g_last_launches;
+    return (int)cudaGetLastError();
+}
+
+template <typename VT, typename AT, typename ACC>
+int launch_backward_generic(const void* value, const int64_t* shapes, const int64_t* ls,
+                            const void* loc, const void* attn, const void* go, ACC* gv_acc,
+                            void* gl, void* ga, const msda_dims* d, cudaStream_t st)
+{
+    KernelDims k = make_dims(d, 8);
+    k.tile_h = 0; k.tile_w = 0; k.tile_q = 8;
+    const long long rows = (long long)d->N * d->Lq * d->M;
+    auto kern = msda_backward_generic_kernel<VT, AT, ACC>;
+    static const int occ = query_occupancy(kern, 256);
+    const int grid = persistent_grid(occ, (rows + 7) / 8);
+    kern<<<grid, 256, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
+                               (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k);
+    ++g_last_launches;
+    return (int)cudaGetLastError();
+}
+
+// VT = float: gradients accumulate straight into grad_value (zero-filled first).
+// 16-bit VT: accumulate in the fp32 workspace, then round once.
+template <typename VT, typename AT>
+int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
+                   const void* attn, const void* go, void* gv, void* gl, void* ga, void* ws,
+                   size_t ws_bytes, const msda_dims* d, cudaStream_t st)
+{
+    const size_t nval = (size_t)d->N * d->S * d->M * d->D;
+    float* acc;
+    if constexpr (sizeof(VT) == 4) {
+        acc = (float*)gv;
+    } else {
+        if (!ws || ws_bytes < nval * sizeof(float)) return MSDA_E_WORKSPACE;
+        if (!aligned16(ws)) return MSDA_E_ALIGN;
+        acc = (float*)ws;
+    }
+    cudaError_t e = cudaMemsetAsync(acc, 0, nval * sizeof(float), st);
+    if (e != cudaSuccess) return (int)e;
+    int rc = 0;
+    if (d->Lq > 0) {
+        const bool al = aligned16(value) && aligned16(go) && aligned16(acc) &&
+                        !env_int("MSDA_B200_FORCE_GENERIC", 0);
+        bool done = false;
+        if constexpr (sizeof(VT) == 4) {
+            if (al) switch (d->D) {
+                case 16: rc = launch_backward_vec<VT, AT, 4, 4>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
+                case 32: rc = launch_backward_vec<VT, AT, 4, 8>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
+                case 36: rc = launch_backward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
+                case 64: rc = launch_backward_vec<VT, AT, 4, 16>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
+                default: break;
+            }
+        } else {
+            if (al) switch (d->D) {
+                case 16: rc = launch_backward_vec<VT, AT, 8, 2>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
+                case 32: rc = launch_backward_vec<VT, AT, 8, 4>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
+                case 36: rc = launch_backward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
+                case 64: rc = launch_backward_vec<VT, AT, 8, 8>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
+                default: break;
+            }
+        }
+        if (!done) rc = launch_backward_generic<VT, AT, float>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st);
+        if (rc) return rc;
+    }
+    if constexpr (sizeof(VT) == 2) {
+        const int sms = device_info().sms > 0 ? device_info().sms : 148;
+        if (nval % 8 == 0 && aligned16(gv)) {
+            msda_round_grad_value_kernel<VT><<<sms * 8, 256, 0, st>>>(acc, (VT*)gv, nval / 8);
+        } else {
+            msda_round_generic_kernel<VT, float><<<sms * 8, 256, 0, st>>>(acc, (VT*)gv, nval);
+        }
+        ++g_last_launches;
+        rc = (int)cudaGetLastError();
+    }
+    return rc;
+}
+
+// fp64 (generic kernels only; parity with the reference's AT_DISPATCH_FLOATING_TYPES), defined in
+// msda_inst_f32.cu
+int forward_f64(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
+                const void* attn, void* out, const msda_dims* d, cudaStream_t st);
+int backward_f64(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
+                 const void* attn, const void* go, void* gv, void* gl, void* ga,
+                 const msda_dims* d, cudaStream_t st);
+
+#define MSDA_DECLARE_TYPED(EXTERN, VT, AT)                                                                   \
+    EXTERN template int forward_typed<VT, AT>(const void*, const int64_t*, const int64_t*, const void*,      \
+                                              const void*, void*, const msda_dims*, cudaStream_t);           \
+    EXTERN template int backward_typed<VT, AT>(const void*, const int64_t*, const int64_t*, const void*,     \
+                                               const void*, const void*, void*, void*, void*, void*, size_t, \
+                                               const msda_dims*, cudaStream_t);
+
+}  // namespace msda

@@ -33,7 +33,8 @@ def test_full_size_matches_reference_cuda_kernels(tag, regime):
     dev = torch.device("cuda:0")
     s = resolve(tag)
     value, shapes, loc, attn = make_inputs(tag, dev, torch.float32, torch.float32, regime, seed=1)
-    go = torch.randn(s["N"], s["Lq"], s["M"] * s["D"], device=dev)
+    gen = torch.Generator(device=dev).manual_seed(4)
+    go = torch.randn(s["N"], s["Lq"], s["M"] * s["D"], generator=gen, device=dev)
     out, (gv, gl, ga) = _ours(value, shapes, loc, attn, go)
     r_out = ref.ref_cuda_forward(value, shapes, loc, attn)
     r_gv, r_gl, r_ga = ref.ref_cuda_backward(value, shapes, loc, attn, go)
@@ -55,8 +56,12 @@ def test_full_size_properties(tag, dtype):
     dev = torch.device("cuda:0")
     s = resolve(tag)
     value, shapes, loc, attn = make_inputs(tag, dev, dtype, torch.float32, "structured", seed=2)
-    go = torch.randn(s["N"], s["Lq"], s["M"] * s["D"], device=dev).to(dtype)
     tol = 1e-5 if dtype == torch.float32 else 1.2e-2
+    # grad_output correlated with the output, so <out, go> is a well-conditioned (non-cancelling) sum
+    # and the adjointness checks below measure the kernels, not the rounding noise of the output
+    out0, _ = _ours(value, shapes, loc, attn)
+    gen = torch.Generator(device=dev).manual_seed(5)
+    go = (out0.float() + 0.5 * torch.randn(out0.shape, generator=gen, device=dev)).to(dtype)
     out, (gv, gl, ga) = _ours(value, shapes, loc, attn, go)
     # linearity in the attention weights: f(v, 2a) = 2 f(v, a)   (exact in binary floating point)
     out2, _ = _ours(value, shapes, loc, attn * 2, None)
