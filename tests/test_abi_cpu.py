@@ -72,3 +72,18 @@ def test_product_never_imports_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f
                 assert "msda_oracle" not in src, f
+
+
+def test_extension_module_name_shim():
+    """`import MultiScaleDeformableAttention as MSDA` (reference ms_deform_attn_func.py:11) resolves to
+    the shim exporting the two pybind names of src/vision.cpp:5-6, and rejects CPU tensors."""
+    import MultiScaleDeformableAttention as MSDA
+    assert callable(MSDA.ms_deform_attn_forward) and callable(MSDA.ms_deform_attn_backward)
+    v = torch.zeros(1, 4, 1, 4)
+    shapes = torch.tensor([[2, 2]])
+    loc = torch.zeros(1, 1, 1, 1, 1, 2)
+    attn = torch.zeros(1, 1, 1, 1, 1)
+    with pytest.raises(RuntimeError, match="Not implemented on the CPU"):
+        MSDA.ms_deform_attn_forward(v, shapes, loc, attn, 64)
+    with pytest.raises(TypeError):
+        MSDA.ms_deform_attn_forward(v, shapes, loc)
