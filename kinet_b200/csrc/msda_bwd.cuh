@@ -76,7 +76,12 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
     constexpr int GPW = 32 / GS;
     constexpr int D = VEC * GS;
     constexpr bool POW2 = (GS & (GS - 1)) == 0;
-    static_assert(VEC % 4 == 0, "vector reductions are 4 floats wide");
+    // VEC = 4 for every value type: a lane's reduction is 16 contiguous bytes of the fp32 accumulator
+    // row, the GS lanes of a row cover it without gaps, and one warp instruction carries whole rows.
+    // The SM->L2 request port sends one packet (header + 32-byte sectors) per 128-byte line touched,
+    // so fewer, fuller lines per instruction is what sets the scatter rate: with 8
+    // channels per lane (bf16 x 8 loads) the same kernel measured 945 us instead of 538 us.
+    static_assert(VEC == 4, "one 16-byte reduction per lane and corner");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int grp = lane / GS, gl = lane - grp * GS;
     const bool lane_used = grp < GPW;
@@ -105,34 +110,6 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
 #pragma unroll
             for (int k = 0; k < VEC; ++k) g[k] = 0.f;
             if (row_ok) VecIO<VT, VEC>::load_stream(grad_out + row * D + gl * VEC, g);
-            // Operands of the grad_value reductions.  L2 executes a reduction per 32-byte sector, and
-            // a sector that one instruction covers only half costs as much as a full one.  With
-            // VEC = 8 a lane's 8 fp32 channels ARE one sector, which its two 16-byte reductions
-            // would each half-cover; so lane pairs swap halves: instruction A completes the even
-            // lane's sector, instruction B the odd lane's (the partner's 4 channels of grad_out are
-            // fetched once per row with 4 shuffles).
-            float gr[VEC];
-            int roff[VEC / 4];
-            if constexpr (VEC == 8) {
-                static_assert(GS % 2 == 0, "lane pairs");
-                const bool odd = (gl & 1) != 0;
-                float gp[4];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) gp[k] = __shfl_xor_sync(0xffffffffu, odd ? g[k] : g[4 + k], 1);
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    gr[k] = odd ? gp[k] : g[k];           // A: even lane own low half | odd lane: partner's high half
-                    gr[4 + k] = odd ? g[4 + k] : gp[k];   // B: even lane: partner's low half | odd lane own high half
-                }
-                roff[0] = odd ? -4 : 0;
-                roff[1] = odd ? 4 : 8;
-            } else {
-#pragma unroll
-                for (int k = 0; k < VEC; ++k) gr[k] = g[k];
-#pragma unroll
-                for (int k = 0; k < VEC / 4; ++k) roff[k] = 4 * k;
-            }
-
             for (int s0 = 0; s0 < LP; s0 += GS) {
                 // owner phase: lane gl prepares sample s0 + gl of its row
                 const int s = s0 + gl;
@@ -189,8 +166,8 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
                             float* dst = gv_base + (size_t)o[c] * VEC;
 #pragma unroll
                             for (int k = 0; k < VEC; k += 4)
-                                red_add_f32x4(dst + roff[k / 4], bw[c] * gr[k], bw[c] * gr[k + 1], bw[c] * gr[k + 2],
-                                              bw[c] * gr[k + 3]);
+                                red_add_f32x4(dst + k, bw[c] * g[k], bw[c] * g[k + 1], bw[c] * g[k + 2],
+                                              bw[c] * g[k + 3]);
                         }
                     }
                 }

@@ -260,10 +260,13 @@ int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, 
             }
         } else {
             if (al) switch (d->D) {
-                case 16: rc = launch_backward_vec<VT, AT, 8, 2>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                case 32: rc = launch_backward_vec<VT, AT, 8, 4>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
+                // 4 channels per lane also for 16-bit values (8-byte loads): a lane's reduction is then
+                // 16 contiguous bytes of the fp32 accumulator row and one instruction covers whole
+                // 128-byte rows, i.e. the fewest SM->L2 request packets per byte
+                case 16: rc = launch_backward_vec<VT, AT, 4, 4>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
+                case 32: rc = launch_backward_vec<VT, AT, 4, 8>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
                 case 36: rc = launch_backward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                case 64: rc = launch_backward_vec<VT, AT, 8, 8>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
+                case 64: rc = launch_backward_vec<VT, AT, 4, 16>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
                 default: break;
             }
         }
