@@ -58,7 +58,8 @@ def build(force=False, verbose=False):
         objs.append(obj)
         if (not force and os.path.exists(obj) and os.path.getmtime(obj) > max(hdr_t, os.path.getmtime(src))):
             continue
-        cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, src]
+        extra = os.environ.get("MSDA_NVCC_EXTRA", "").split()
+        cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, src]
         procs.append((src, subprocess.Popen(cmd, cwd=CSRC, env=env, stdout=subprocess.PIPE,
                                             stderr=subprocess.STDOUT, text=True)))
     failed = []
