@@ -39,6 +39,10 @@ from kinet_b200.workloads import algorithmic_bytes, make_inputs, resolve  # noqa
 WORKLOAD = "detr_6enc_6dec_bf16"
 ENC_TAG, DEC_TAG, LAYERS = "C2_enc", "C2_dec", 6
 METRIC, UNIT = "msda_fwd_bwd_GBps", "GB/s"
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from the committed
+# `ncu --set full` capture (bench.py never runs under a profiler, so this is a recorded measurement)
+ENC_BWD_DRAM_TRAFFIC = 206.4e6 + 94.3e6
+ENC_BWD_DRAM_TRAFFIC_SRC = "profiles/r1h_ncu_full_C2enc_bf16.txt"
 
 
 def measured_peak():
@@ -390,8 +394,9 @@ def main():
                         "api": "kinet_b200.MSDeformAttnFunction.apply + Tensor.backward, pinned host tensors; H2D, kernels and D2H on three streams"},
                 "gpu_launches": r["launches"],
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                             "kernel": "msda_backward_kernel<bf16,f32,8,4,8> (encoder form, N=2 Lq=S=22223)",
+                             "frac": achieved / peak, "traffic": ENC_BWD_DRAM_TRAFFIC, "traffic_source": ENC_BWD_DRAM_TRAFFIC_SRC,
+                             "peak_source": peak_src,
+                             "kernel": "msda_backward_kernel<bf16,f32,VEC=4,GS=8,NW=8> (encoder form, N=2 Lq=S=22223)",
                              "kernel_us_avg": kavg * 1e3, "kernel_us_min": kms[0] * 1e3,
                              "launches_timed": len(kms), "algorithmic_bytes_per_launch": r["enc_bwd_bytes"],
                              "step_frac_of_hbm": value / world / peak,

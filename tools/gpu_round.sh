@@ -13,7 +13,7 @@ python tools/quick_bench.py --dtype f32 --ref --iters 10 > $O/quick_f32.txt 2>&1
 python tools/quick_bench.py --dtype bf16 --iters 10 > $O/quick_bf16.txt 2>&1; cat $O/quick_bf16.txt
 python tools/quick_bench.py --dtype f32 --regime uniform --iters 10 C2_enc C2_dec > $O/quick_f32_uniform.txt 2>&1; cat $O/quick_f32_uniform.txt
 python bench.py --steps 2 --warmup 3 --e2e-steps 1 --cpu-steps 1 > $O/plain_bench.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches.csv \
+ncu --metrics gpu__time_duration.sum --clock-control none -k regex:msda_ -c 600 --csv --log-file $O/launches.csv \
     python bench.py --steps 2 --warmup 3 --e2e-steps 1 --cpu-steps 1 > $O/ncu_launches.log 2>&1
 python tools/quick_bench.py C2_enc --dtype bf16 --iters 2 > $O/plain_qb.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:'msda_(forward|backward)_kernel' -s 3 -c 4 \
