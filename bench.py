@@ -43,6 +43,10 @@ METRIC, UNIT = "msda_fwd_bwd_GBps", "GB/s"
 # `ncu --set full` capture (bench.py never runs under a profiler, so this is a recorded measurement)
 ENC_BWD_DRAM_TRAFFIC = 206.4e6 + 94.3e6
 ENC_BWD_DRAM_TRAFFIC_SRC = "profiles/r1h_ncu_full_C2enc_bf16.txt"
+# the same kernel against the unit that actually binds it: every sample adds 4 corner rows of D fp32
+# channels into grad_value (upper bound: zero-weight border corners are skipped)
+SCATTER_BYTES = 2 * 22223 * 8 * 16 * 4 * 32 * 4
+RED_CEILING_GBPS = 6411.7
 
 
 def measured_peak():
@@ -400,7 +404,15 @@ def main():
                              "kernel_us_avg": kavg * 1e3, "kernel_us_min": kms[0] * 1e3,
                              "launches_timed": len(kms), "algorithmic_bytes_per_launch": r["enc_bwd_bytes"],
                              "step_frac_of_hbm": value / world / peak,
-                             "note": "true limiter is the SM L1 data pipe / SM->L2 write path, see DESIGN.md"},
+                             "binding_limit": {
+                                 "what": "SM->L2 request port / L2 fp32 reduction rate: the grad_value scatter is "
+                                         "4 corner rows x 128 B of red.global.add.v4.f32 per sample",
+                                 "scatter_bytes_per_launch": SCATTER_BYTES,
+                                 "scatter_GBps": SCATTER_BYTES / (kavg * 1e-3) / 1e9,
+                                 "measured_ceiling_GBps": RED_CEILING_GBPS,
+                                 "frac_of_ceiling": SCATTER_BYTES / (kavg * 1e-3) / 1e9 / RED_CEILING_GBPS,
+                                 "ceiling_source": "tools/micro/scatter_ceiling.cu -> profiles/r1_scatter_gather_ceilings.txt"},
+                             "note": "HBM is not the binding unit of this kernel (dram throughput 4-7 %); see DESIGN.md 5.2"},
                 "cpu_baseline": {"value": cpu["value"], "unit": UNIT, "cores": cpu["cores"], "kind": "port",
                                  "sample": cpu["sample"], "ms_per_sample": cpu["ms"]},
                 "clocks": r["clocks"]}

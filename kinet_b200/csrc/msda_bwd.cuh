@@ -16,6 +16,9 @@
 #pragma once
 #include "msda_common.cuh"
 
+#ifndef MSDA_BWD_MINB
+#define MSDA_BWD_MINB 2
+#endif
 namespace msda {
 
 // Sum across the GS lanes of a group; every lane of the group gets the total.
@@ -205,7 +208,7 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
 }
 
 template <typename VT, typename AT, int VEC, int GS, int NWARPS>
-__global__ void __launch_bounds__(NWARPS * 32, 2)
+__global__ void __launch_bounds__(NWARPS * 32, MSDA_BWD_MINB)
 msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ shapes,
                      const int64_t* __restrict__ level_start, const AT* __restrict__ loc,
                      const AT* __restrict__ attn, const VT* __restrict__ grad_out,

@@ -290,3 +290,64 @@ def test_module_matches_reference_math():
             loc = ref[:, :, None, :, None, :2] + off / 4 * ref[:, :, None, :, None, 2:] * 0.5
         want = m.output_proj(torch_port_forward(value, shapes, loc, aw))
         assert _relerr(got.detach().cpu().numpy(), want.detach().cpu().numpy()) <= 2e-5
+
+
+def test_c_abi_calls_are_cuda_graph_capturable():
+    """The library never allocates, synchronises or touches the host inside a call
+    (include/msda_b200.h), so forward + backward can be captured into a CUDA graph and replayed --
+    what SURVEY.md 7.3 asks for the per-frame tracker graph.  The replay must reproduce the eager result."""
+    import ctypes
+    from kinet_b200 import _lib
+    dev = _dev()
+    lib = _lib.load()
+    N, M, D, Lq, levels, P = 2, 8, 32, 300, [(20, 27), (10, 14), (5, 7), (3, 4)], 4
+    for dtype in (torch.float32, torch.bfloat16):
+        value, shapes, loc, attn, go = _random_case(dev, N, M, D, Lq, levels, P, dtype=dtype, seed=5)
+        S = value.shape[1]
+        dims = _lib.MsdaDims(N, S, M, D, len(levels), Lq, P)
+        vcode, acode = _lib.dtype_code(dtype), _lib.dtype_code(loc.dtype)
+        out = torch.zeros(N, Lq, M * D, dtype=dtype, device=dev)
+        gv, gl, ga = torch.zeros_like(value), torch.zeros_like(loc), torch.zeros_like(attn)
+        wsb = int(lib.msda_b200_backward_workspace_bytes(vcode, ctypes.byref(dims)))
+        ws = torch.empty(max(wsb // 4, 4), dtype=torch.float32, device=dev)
+        p = lambda t: ctypes.c_void_p(t.data_ptr())
+
+        def run(stream):
+            st = ctypes.c_void_p(stream.cuda_stream)
+            rc = lib.msda_b200_forward(p(value), vcode, p(shapes), None, p(loc), p(attn), acode, p(out),
+                                       ctypes.byref(dims), st)
+            assert rc == 0, rc
+            rc = lib.msda_b200_backward(p(value), vcode, p(shapes), None, p(loc), p(attn), acode, p(go), p(gv),
+                                        p(gl), p(ga), p(ws), ctypes.c_size_t(wsb), ctypes.byref(dims), st)
+            assert rc == 0, rc
+
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            run(side)                       # eager reference (also warms up lazy module loading)
+        side.synchronize()
+        want = [t.clone() for t in (out, gv, gl, ga)]
+        for t in (out, gv, gl, ga):
+            t.zero_()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            run(torch.cuda.current_stream())
+        assert not out.any()                # capture records, it does not execute
+        graph.replay()
+        torch.cuda.synchronize()
+        tol = 2e-6 if dtype == torch.float32 else 1e-2      # grad_value: atomic order differs run to run
+        for got, ref in zip((out, gv, gl, ga), want):
+            assert _relerr(got.float().cpu().numpy(), ref.float().cpu().numpy()) <= tol
+
+
+def test_extension_module_shim_on_gpu():
+    """`import MultiScaleDeformableAttention as MSDA` (reference ms_deform_attn_func.py:11) used exactly like
+    the reference's autograd function uses it (:18-19, :26-29), 5/6 positional arguments."""
+    import MultiScaleDeformableAttention as MSDA
+    dev = _dev()
+    value, shapes, loc, attn, go = _random_case(dev, 2, 8, 32, 41, [(9, 13), (5, 7), (3, 4)], 4, seed=8)
+    out = MSDA.ms_deform_attn_forward(value, shapes, loc, attn, 64)
+    gv, gl, ga = MSDA.ms_deform_attn_backward(value, shapes, loc, attn, go, 64)
+    ref_out, ref_grads = _oracle64(value, shapes, loc, attn, go)
+    assert out.shape == (2, 41, 256)
+    assert _relerr(out.cpu().numpy(), ref_out) <= 1e-5
+    _check_grads((gv, gl, ga), ref_grads, shapes, loc, 1e-5)
