@@ -45,7 +45,7 @@
 extern "C" {
 #endif
 
-#define MSDA_B200_ABI_VERSION 1
+#define MSDA_B200_ABI_VERSION 2
 
 /* element types */
 #define MSDA_F32 0
@@ -101,6 +101,44 @@ int msda_b200_backward(const void *value, int value_dtype,
                        void *grad_value, void *grad_sampling_loc, void *grad_attn_weight,
                        void *workspace, size_t workspace_bytes,
                        const msda_dims *dims, void *stream);
+
+/* ---- Fused module prologue -------------------------------------------------
+ * The reference's MSDeformAttn.forward (ops/modules/ms_deform_attn.py:69-82) materialises softmax'ed
+ * attention weights and sampling locations with ~6 elementwise kernels before it calls the op.  The
+ * fused entry points read what the module's Linear layers produce instead and do that arithmetic in
+ * the kernel:
+ *   attention[n,q,m,:]  = softmax over the L*P logits of (n,q,m); 0 for queries with query_mask != 0
+ *   location[n,q,m,l,p] = ref[n,q,l,:] + offset[n,q,m,l,p,:] / offset_norm[l,:]            (ref_dim 2)
+ *                       = ref[n,q,l,:2] + offset / P * ref[n,q,l,2:] * 0.5                 (ref_dim 4)
+ * offset_norm is what the module divides by: the reference passes input_spatial_shapes, i.e. (H_l, W_l)
+ * for the (x, y) offsets (:77-79; upstream Deformable-DETR uses (W_l, H_l)) -- the caller decides.
+ * The backward returns the gradients w.r.t. the raw offsets and logits (through the location
+ * arithmetic and the softmax) and, when grad_sampling_loc != NULL, d out / d location in fp32
+ * ([N][Lq][M][L][P][2]) from which the caller reduces the reference-point gradient.
+ * Return MSDA_E_SHAPE = no fused kernel for this shape (D not in {16,32,36,64}, misaligned pointers, or
+ * L*P > 4 * D/4 in the backward): run the prologue outside and call the plain entry points. */
+typedef struct msda_fused_inputs {
+    const void *sampling_offsets;     /* [N][Lq][M][L][P][2]  aux_dtype, raw Linear output */
+    const void *attn_logits;          /* [N][Lq][M][L*P]      aux_dtype, before softmax */
+    const float *reference_points;    /* [N][Lq][L][ref_dim]  fp32, 16-byte aligned */
+    const float *offset_norm;         /* [L][2] fp32 divisors of (x, y) offsets; ref_dim == 2 only */
+    const unsigned char *query_mask;  /* [N][Lq] or NULL; nonzero = attention weights of the query zeroed */
+    int32_t ref_dim;                  /* 2 or 4 */
+} msda_fused_inputs;
+
+int msda_b200_forward_fused(const void *value, int value_dtype,
+                            const int64_t *spatial_shapes, const int64_t *level_start,
+                            const msda_fused_inputs *inputs, int aux_dtype,
+                            void *output, const msda_dims *dims, void *stream);
+
+int msda_b200_backward_fused(const void *value, int value_dtype,
+                             const int64_t *spatial_shapes, const int64_t *level_start,
+                             const msda_fused_inputs *inputs, int aux_dtype,
+                             const void *grad_output,
+                             void *grad_value, void *grad_offsets, void *grad_logits,
+                             float *grad_sampling_loc /* optional */,
+                             void *workspace, size_t workspace_bytes,
+                             const msda_dims *dims, void *stream);
 
 /* Number of kernels the last forward / backward call of this thread launched
  * (bench.py's gpu_launches evidence). */

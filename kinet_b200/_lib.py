@@ -20,7 +20,16 @@ class MsdaDims(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in ("N", "S", "M", "D", "L", "Lq", "P")]
 
 
+class MsdaFusedInputs(ctypes.Structure):
+    _fields_ = [("sampling_offsets", ctypes.c_void_p), ("attn_logits", ctypes.c_void_p),
+                ("reference_points", ctypes.c_void_p), ("offset_norm", ctypes.c_void_p),
+                ("query_mask", ctypes.c_void_p), ("ref_dim", ctypes.c_int32)]
+
+
+MSDA_E_SHAPE = -2
+
 EXPORTS = ("msda_b200_abi_version", "msda_b200_error_string", "msda_b200_forward",
+           "msda_b200_forward_fused", "msda_b200_backward_fused",
            "msda_b200_backward_workspace_bytes", "msda_b200_backward",
            "msda_b200_last_launch_count", "msda_b200_trace_next")
 
@@ -48,10 +57,15 @@ def load():
     lib.msda_b200_backward.restype = i
     lib.msda_b200_backward.argtypes = [vp, i, vp, vp, vp, vp, i, vp, vp, vp, vp, vp,
                                        ctypes.c_size_t, dp, vp]
+    fp = ctypes.POINTER(MsdaFusedInputs)
+    lib.msda_b200_forward_fused.restype = i
+    lib.msda_b200_forward_fused.argtypes = [vp, i, vp, vp, fp, i, vp, dp, vp]
+    lib.msda_b200_backward_fused.restype = i
+    lib.msda_b200_backward_fused.argtypes = [vp, i, vp, vp, fp, i, vp, vp, vp, vp, vp, vp, ctypes.c_size_t, dp, vp]
     lib.msda_b200_last_launch_count.restype = i
     lib.msda_b200_trace_next.restype = None
     lib.msda_b200_trace_next.argtypes = [vp, vp]
-    if lib.msda_b200_abi_version() != 1:
+    if lib.msda_b200_abi_version() != 2:
         raise RuntimeError("kinet_b200: libmsda_b200.so ABI version mismatch")
     _lib = lib
     return lib

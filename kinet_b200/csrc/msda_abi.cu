@@ -60,7 +60,7 @@ int msda_b200_forward(const void* value, int value_dtype, const int64_t* spatial
     if (!output) return MSDA_E_NULL;
     cudaStream_t st = (cudaStream_t)stream;
 #define MSDA_FWD(VT, AT) \
-    return forward_typed<VT, AT>(value, spatial_shapes, level_start, sampling_loc, attn_weight, output, dims, st)
+    return forward_typed<VT, AT>(value, spatial_shapes, level_start, sampling_loc, attn_weight, output, dims, st, nullptr)
     if (value_dtype == MSDA_F32 && aux_dtype == MSDA_F32) MSDA_FWD(float, float);
     if (value_dtype == MSDA_BF16 && aux_dtype == MSDA_F32) MSDA_FWD(__nv_bfloat16, float);
     if (value_dtype == MSDA_BF16 && aux_dtype == MSDA_BF16) MSDA_FWD(__nv_bfloat16, __nv_bfloat16);
@@ -93,7 +93,8 @@ int msda_b200_backward(const void* value, int value_dtype, const int64_t* spatia
     cudaStream_t st = (cudaStream_t)stream;
 #define MSDA_BWD(VT, AT) \
     return backward_typed<VT, AT>(value, spatial_shapes, level_start, sampling_loc, attn_weight, grad_output, \
-                                  grad_value, grad_sampling_loc, grad_attn_weight, workspace, workspace_bytes, dims, st)
+                                  grad_value, grad_sampling_loc, grad_attn_weight, workspace, workspace_bytes, dims, st, \
+                                  nullptr)
     if (value_dtype == MSDA_F32 && aux_dtype == MSDA_F32) MSDA_BWD(float, float);
     if (value_dtype == MSDA_BF16 && aux_dtype == MSDA_F32) MSDA_BWD(__nv_bfloat16, float);
     if (value_dtype == MSDA_BF16 && aux_dtype == MSDA_BF16) MSDA_BWD(__nv_bfloat16, __nv_bfloat16);
@@ -103,6 +104,76 @@ int msda_b200_backward(const void* value, int value_dtype, const int64_t* spatia
     if (value_dtype == MSDA_F64 && aux_dtype == MSDA_F64)
         return backward_f64(value, spatial_shapes, level_start, sampling_loc, attn_weight, grad_output,
                             grad_value, grad_sampling_loc, grad_attn_weight, dims, st);
+    return MSDA_E_DTYPE;
+}
+
+
+// ---- fused prologue ------------------------------------------------------------------
+
+static int check_fused(const msda_fused_inputs* in, const msda_dims* dims, FusedArgs* fa)
+{
+    if (!in) return MSDA_E_NULL;
+    if (dims->Lq > 0 && (!in->sampling_offsets || !in->attn_logits || !in->reference_points)) return MSDA_E_NULL;
+    if (in->ref_dim != 2 && in->ref_dim != 4) return MSDA_E_SHAPE;
+    if (in->ref_dim == 2 && !in->offset_norm) return MSDA_E_NULL;
+    if ((reinterpret_cast<uintptr_t>(in->reference_points) & 15u) || (reinterpret_cast<uintptr_t>(in->offset_norm) & 7u))
+        return MSDA_E_ALIGN;
+    fa->ref = in->reference_points;
+    fa->norm = in->offset_norm;
+    fa->qmask = in->query_mask;
+    fa->grad_loc = nullptr;
+    fa->ref_dim = in->ref_dim;
+    return 0;
+}
+
+int msda_b200_forward_fused(const void* value, int value_dtype, const int64_t* spatial_shapes,
+                            const int64_t* level_start, const msda_fused_inputs* in, int aux_dtype,
+                            void* output, const msda_dims* dims, void* stream)
+{
+    g_last_launches = 0;
+    if (!in) return MSDA_E_NULL;
+    if (int rc = check_common(value, spatial_shapes, in->sampling_offsets, in->attn_logits, dims)) return rc;
+    FusedArgs fa;
+    if (int rc = check_fused(in, dims, &fa)) return rc;
+    if (dims->Lq == 0) return 0;
+    if (!output) return MSDA_E_NULL;
+    cudaStream_t st = (cudaStream_t)stream;
+#define MSDA_FWD(VT, AT) \
+    return forward_typed<VT, AT>(value, spatial_shapes, level_start, in->sampling_offsets, in->attn_logits, output, dims, \
+                                 st, &fa)
+    if (value_dtype == MSDA_F32 && aux_dtype == MSDA_F32) MSDA_FWD(float, float);
+    if (value_dtype == MSDA_BF16 && aux_dtype == MSDA_F32) MSDA_FWD(__nv_bfloat16, float);
+    if (value_dtype == MSDA_BF16 && aux_dtype == MSDA_BF16) MSDA_FWD(__nv_bfloat16, __nv_bfloat16);
+    if (value_dtype == MSDA_F16 && aux_dtype == MSDA_F32) MSDA_FWD(__half, float);
+    if (value_dtype == MSDA_F16 && aux_dtype == MSDA_F16) MSDA_FWD(__half, __half);
+#undef MSDA_FWD
+    return MSDA_E_DTYPE;
+}
+
+int msda_b200_backward_fused(const void* value, int value_dtype, const int64_t* spatial_shapes,
+                             const int64_t* level_start, const msda_fused_inputs* in, int aux_dtype,
+                             const void* grad_output, void* grad_value, void* grad_offsets, void* grad_logits,
+                             float* grad_sampling_loc, void* workspace, size_t workspace_bytes,
+                             const msda_dims* dims, void* stream)
+{
+    g_last_launches = 0;
+    if (!in) return MSDA_E_NULL;
+    if (int rc = check_common(value, spatial_shapes, in->sampling_offsets, in->attn_logits, dims)) return rc;
+    FusedArgs fa;
+    if (int rc = check_fused(in, dims, &fa)) return rc;
+    fa.grad_loc = grad_sampling_loc;
+    if (!grad_value) return MSDA_E_NULL;
+    if (dims->Lq > 0 && (!grad_output || !grad_offsets || !grad_logits)) return MSDA_E_NULL;
+    cudaStream_t st = (cudaStream_t)stream;
+#define MSDA_BWD(VT, AT) \
+    return backward_typed<VT, AT>(value, spatial_shapes, level_start, in->sampling_offsets, in->attn_logits, grad_output, \
+                                  grad_value, grad_offsets, grad_logits, workspace, workspace_bytes, dims, st, &fa)
+    if (value_dtype == MSDA_F32 && aux_dtype == MSDA_F32) MSDA_BWD(float, float);
+    if (value_dtype == MSDA_BF16 && aux_dtype == MSDA_F32) MSDA_BWD(__nv_bfloat16, float);
+    if (value_dtype == MSDA_BF16 && aux_dtype == MSDA_BF16) MSDA_BWD(__nv_bfloat16, __nv_bfloat16);
+    if (value_dtype == MSDA_F16 && aux_dtype == MSDA_F32) MSDA_BWD(__half, float);
+    if (value_dtype == MSDA_F16 && aux_dtype == MSDA_F16) MSDA_BWD(__half, __half);
+#undef MSDA_BWD
     return MSDA_E_DTYPE;
 }
 

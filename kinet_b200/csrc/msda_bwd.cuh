@@ -68,14 +68,18 @@ __device__ __forceinline__ void reduce_scatter(float (&U)[N][4], int gl, float (
 }
 
 // WIDE: every level has W > 1 (uniform column step of the 2x2 footprint).
-template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE>
+// FUSED: loc / attn are raw sampling offsets / attention logits, grad_loc / grad_attn their gradients
+// (through the location arithmetic and the softmax); see SampleSrc<AT, true> in msda_common.cuh.
+template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE, bool FUSED>
 __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage_a, int* stage_dx, float4* stage_b,
                                                const VT* __restrict__ value,
                                                const AT* __restrict__ loc, const AT* __restrict__ attn,
                                                const VT* __restrict__ grad_out,
                                                float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
-                                               AT* __restrict__ grad_attn, const KernelDims& d)
+                                               AT* __restrict__ grad_attn, const KernelDims& d, const FusedArgs& fa)
 {
+    constexpr int MAXCH = kFusedMaxChunks;   // fused: chunks of a row whose d out / d attention stay in registers until
+                               // the row's softmax backward (launcher guarantees L*P <= MAXCH*GS)
     constexpr int GPW = 32 / GS;
     constexpr int D = VEC * GS;
     constexpr bool POW2 = (GS & (GS - 1)) == 0;
@@ -105,9 +109,12 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
         for (int i0 = warp * GPW; i0 < ti.count; i0 += NWARPS * GPW) {
             const int q = (lane_used && i0 + grp < ti.count) ? tile_query(ti, i0 + grp) : -1;
             const bool row_ok = q >= 0;
-            const size_t row = ((size_t)b * d.Lq + (row_ok ? q : 0)) * d.M + m;
-            const AT* lrow = loc + row * LP * 2;
-            const AT* arow = attn + row * LP;
+            const size_t rowq = (size_t)b * d.Lq + (row_ok ? q : 0);
+            const size_t row = rowq * d.M + m;
+            SampleSrc<AT, FUSED> src;
+            src.template begin<GS>(loc, attn, fa, d, row, rowq, row_ok, gl, grp_base);
+            float ga_keep[MAXCH] = {0.f, 0.f, 0.f, 0.f};   // fused: d out / d attention of this lane's samples
+            float dot = 0.f;                                // fused: sum_s prob_s * d out / d attention_s
 
             float g[VEC];
 #pragma unroll
@@ -117,13 +124,10 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
                 // owner phase: lane gl prepares sample s0 + gl of its row
                 const int s = s0 + gl;
                 const bool mine = row_ok && s < LP;
-                float2 xy = make_float2(0.f, 0.f);
-                float a = 0.f;
-                if (mine) {
-                    xy = load_loc<AT>(lrow + s * 2);
-                    a = load_attn<AT>(arow + s);
-                }
                 const int ls = min(s, LP - 1) / d.P;
+                float2 xy;
+                float a;
+                src.get(s, s0 / GS, ls, mine, d, xy.x, xy.y, a);
                 const int H = lt.H[ls], W = lt.W[ls];
                 const OwnerTap t = make_owner_tap(mine, xy.x, xy.y, a, H, W, lt.start[ls], rsv);
                 const float wa0 = t.ay.w0 * t.a, wa1 = t.ay.w1 * t.a;
@@ -199,21 +203,45 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
                     const float gy = t.ay.d0 * (t.ax.w0 * u[0] + t.ax.w1 * u[1]) +
                                      t.ay.d1 * (t.ax.w0 * u[2] + t.ax.w1 * u[3]);
                     // .cuh:373-374: pixel-space derivative times attn times W (x) / H (y)
-                    store_loc<AT>(grad_loc + (row * LP + s) * 2, gx * t.a * (float)W, gy * t.a * (float)H);
-                    grad_attn[row * LP + s] = from_f32<AT>(ga);
+                    const float glx = gx * t.a * (float)W, gly = gy * t.a * (float)H;
+                    if constexpr (!FUSED) {
+                        store_loc<AT>(grad_loc + (row * LP + s) * 2, glx, gly);
+                        grad_attn[row * LP + s] = from_f32<AT>(ga);
+                    } else {
+                        // location = ref + offset * (sx, sy)  ->  d/d offset; d/d location kept if asked for
+                        store_loc<AT>(grad_loc + (row * LP + s) * 2, glx * src.sx, gly * src.sy);
+                        if (fa.grad_loc) store_loc<float>(fa.grad_loc + (row * LP + s) * 2, glx, gly);
+                        const float gam = src.masked ? 0.f : ga;   // masked_fill(mask, 0): no gradient to the softmax
+                        const int c = s0 / GS;
+#pragma unroll
+                        for (int k = 0; k < MAXCH; ++k)
+                            if (c == k) ga_keep[k] = gam;
+                        dot = fmaf(src.prob(c), gam, dot);
+                    }
+                }
+            }
+            if constexpr (FUSED) {
+                // softmax backward of the row: d/d logit_s = prob_s * (g_s - sum_t prob_t * g_t)
+                const float tot = group_reduce<GS, SumOp>(dot, gl, grp_base);
+                if (row_ok) {
+#pragma unroll
+                    for (int k = 0; k < MAXCH; ++k) {
+                        const int s = k * GS + gl;
+                        if (s < LP) grad_attn[row * LP + s] = from_f32<AT>(src.prob(k) * (ga_keep[k] - tot));
+                    }
                 }
             }
         }
     }
 }
 
-template <typename VT, typename AT, int VEC, int GS, int NWARPS>
+template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool FUSED>
 __global__ void __launch_bounds__(NWARPS * 32, MSDA_BWD_MINB)
 msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ shapes,
                      const int64_t* __restrict__ level_start, const AT* __restrict__ loc,
                      const AT* __restrict__ attn, const VT* __restrict__ grad_out,
                      float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
-                     AT* __restrict__ grad_attn, const KernelDims d)
+                     AT* __restrict__ grad_attn, const KernelDims d, const FusedArgs fa)
 {
     __shared__ LevelTable lt;
     stage_levels(lt, shapes, level_start, d);
@@ -222,11 +250,11 @@ msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ s
     __shared__ float4 stage_b[NWARPS][32];
     const int warp = threadIdx.x >> 5;
     if (lt.min_w > 1)
-        backward_items<VT, AT, VEC, GS, NWARPS, true>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc, attn,
-                                                      grad_out, grad_value_acc, grad_loc, grad_attn, d);
+        backward_items<VT, AT, VEC, GS, NWARPS, true, FUSED>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc,
+                                                             attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa);
     else
-        backward_items<VT, AT, VEC, GS, NWARPS, false>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc, attn,
-                                                       grad_out, grad_value_acc, grad_loc, grad_attn, d);
+        backward_items<VT, AT, VEC, GS, NWARPS, false, FUSED>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc,
+                                                              attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa);
 }
 
 // fp32 workspace -> 16-bit grad_value (one rounding of the full sum).

@@ -339,6 +339,140 @@ __device__ __forceinline__ OwnerTap make_owner_tap(bool mine, float lx, float ly
     return t;
 }
 
+// ---- where a row's samples come from ----------------------------------------------------------
+// Plain entry points read materialised sampling locations and attention weights.  The fused entry
+// points (msda_b200_forward_fused / _backward_fused) read what the module's Linear layers produce --
+// raw sampling offsets and attention logits -- plus the reference points, and do the module's
+// prologue (reference ops/modules/ms_deform_attn.py:69-82) in the owner lanes:
+//   attention = softmax over the row's L*P logits, zeroed for masked queries (:71-74),
+//   location  = ref + offset / norm[level]                         (2-d reference points, :76-79)
+//             = ref_xy + offset / P * ref_wh * 0.5                 (4-d reference boxes,  :80-82)
+struct FusedArgs {
+    const float* ref;             // [N][Lq][L][ref_dim]
+    const float* norm;            // [L][2] divisors of the (x, y) offsets (ref_dim == 2 only)
+    const unsigned char* qmask;   // [N][Lq], nonzero = query masked; may be nullptr
+    float* grad_loc;              // backward only, optional: d out / d location, [N][Lq][M][L][P][2] fp32
+    int ref_dim;                  // 2 or 4
+};
+
+struct MaxOp { static __device__ __forceinline__ float f(float a, float b) { return fmaxf(a, b); } };
+struct SumOp { static __device__ __forceinline__ float f(float a, float b) { return a + b; } };
+
+// Reduction over the GS lanes of a row group; every lane of the group gets the result.
+template <int GS, typename Op>
+__device__ __forceinline__ float group_reduce(float v, int gl, int grp_base)
+{
+    if constexpr ((GS & (GS - 1)) == 0) {
+#pragma unroll
+        for (int o = GS / 2; o > 0; o >>= 1) v = Op::f(v, __shfl_xor_sync(0xffffffffu, v, o));
+        return v;
+    } else {
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) {
+            const float t = __shfl_down_sync(0xffffffffu, v, o);
+            if (gl < o && gl + o < GS) v = Op::f(v, t);
+        }
+        return __shfl_sync(0xffffffffu, v, grp_base);
+    }
+}
+
+template <typename AT, bool FUSED> struct SampleSrc;
+
+template <typename AT> struct SampleSrc<AT, false> {
+    const AT* lrow;
+    const AT* arow;
+    template <int GS>
+    __device__ __forceinline__ void begin(const AT* loc, const AT* attn, const FusedArgs&, const KernelDims& d, size_t row,
+                                          size_t, bool, int, int)
+    {
+        const int LP = d.L * d.P;
+        lrow = loc + row * LP * 2;
+        arow = attn + row * LP;
+    }
+    __device__ __forceinline__ void get(int s, int, int, bool mine, const KernelDims&, float& lx, float& ly, float& a) const
+    {
+        lx = 0.f; ly = 0.f; a = 0.f;
+        if (mine) {
+            const float2 xy = load_loc<AT>(lrow + s * 2);
+            lx = xy.x; ly = xy.y;
+            a = load_attn<AT>(arow + s);
+        }
+    }
+};
+
+constexpr int kFusedMaxChunks = 4;   // fused: a lane keeps the softmax numerators of its <= 4 samples of a row
+
+template <typename AT> struct SampleSrc<AT, true> {
+    const AT* orow;      // raw offsets of the row
+    const float* rrow;   // reference points of the query, [L][ref_dim]
+    const float* norm;
+    float e[kFusedMaxChunks];   // exp(logit - max) of this lane's samples gl, gl + GS, ... of the row
+    float inv_sum;       // 1 / sum of the row's numerators
+    float sx, sy;        // d location / d offset of the last get() (backward)
+    bool masked;
+    int ref_dim;
+
+    // One pass over the row's logits (launcher guarantees L*P <= kFusedMaxChunks * GS).
+    template <int GS>
+    __device__ __forceinline__ void begin(const AT* off, const AT* logit, const FusedArgs& fa, const KernelDims& d,
+                                          size_t row, size_t rowq, bool row_ok, int gl, int grp_base)
+    {
+        const int LP = d.L * d.P;
+        orow = off + row * LP * 2;
+        const AT* grow = logit + row * LP;
+        ref_dim = fa.ref_dim;
+        rrow = fa.ref + rowq * d.L * ref_dim;
+        norm = fa.norm;
+        masked = fa.qmask != nullptr && row_ok && fa.qmask[rowq] != 0;
+        float m_ = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < kFusedMaxChunks; ++c) {
+            const int s = c * GS + gl;
+            e[c] = (row_ok && s < LP) ? load_attn<AT>(grow + s) : -INFINITY;
+            m_ = fmaxf(m_, e[c]);
+        }
+        const float mx = group_reduce<GS, MaxOp>(m_, gl, grp_base);
+        float sum_ = 0.f;
+#pragma unroll
+        for (int c = 0; c < kFusedMaxChunks; ++c) {
+            e[c] = row_ok ? expf(e[c] - mx) : 0.f;      // exp(-inf) = 0 for the slots without a sample
+            sum_ += e[c];
+        }
+        const float sum = group_reduce<GS, SumOp>(sum_, gl, grp_base);
+        inv_sum = row_ok ? 1.f / sum : 0.f;
+    }
+    // softmax probability of this lane's sample of chunk c
+    __device__ __forceinline__ float prob(int c) const
+    {
+        float v = e[0];
+#pragma unroll
+        for (int k = 1; k < kFusedMaxChunks; ++k) v = (c == k) ? e[k] : v;
+        return v * inv_sum;
+    }
+    __device__ __forceinline__ void get(int s, int c, int ls, bool mine, const KernelDims& d, float& lx, float& ly,
+                                        float& a)
+    {
+        lx = 0.f; ly = 0.f; a = 0.f; sx = 0.f; sy = 0.f;
+        if (mine) {
+            const float2 o = load_loc<AT>(orow + s * 2);
+            if (ref_dim == 2) {
+                const float2 r = *reinterpret_cast<const float2*>(rrow + ls * 2);
+                const float2 n = *reinterpret_cast<const float2*>(norm + ls * 2);
+                lx = r.x + o.x / n.x;
+                ly = r.y + o.y / n.y;
+                sx = 1.f / n.x; sy = 1.f / n.y;
+            } else {
+                const float4 r = *reinterpret_cast<const float4*>(rrow + ls * 4);
+                const float p = (float)d.P;
+                lx = r.x + o.x / p * r.z * 0.5f;
+                ly = r.y + o.y / p * r.w * 0.5f;
+                sx = r.z * 0.5f / p; sy = r.w * 0.5f / p;
+            }
+            a = masked ? 0.f : prob(c);
+        }
+    }
+};
+
 // acc[0..VEC) += w * v[0..VEC) with packed fp32x2 FMAs (sm_100 FFMA2).
 template <int VEC>
 __device__ __forceinline__ void axpy_vec(float (&acc)[VEC], float w, const float (&v)[VEC])

@@ -34,11 +34,13 @@ __device__ __forceinline__ void gather_sample(float (&acc)[VEC], const VT* lane_
 }
 
 // WIDE: every level has W > 1, so the column step of the 2x2 footprint is the same for all samples.
-template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE>
+// FUSED: `loc` / `attn` are the module's raw sampling offsets / attention logits and the prologue
+// (softmax, location arithmetic) runs in the owner lanes (SampleSrc<AT, true>, msda_common.cuh).
+template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE, bool FUSED>
 __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_a, int* stage_dx, float4* stage_b,
                                               const VT* __restrict__ value,
                                               const AT* __restrict__ loc, const AT* __restrict__ attn,
-                                              VT* __restrict__ out, const KernelDims& d)
+                                              VT* __restrict__ out, const KernelDims& d, const FusedArgs& fa)
 {
     constexpr int GPW = 32 / GS;           // rows per warp
     constexpr int D = VEC * GS;
@@ -59,9 +61,10 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_
         for (int i0 = warp * GPW; i0 < ti.count; i0 += NWARPS * GPW) {
             const int q = (lane_used && i0 + grp < ti.count) ? tile_query(ti, i0 + grp) : -1;
             const bool row_ok = q >= 0;
-            const size_t row = ((size_t)b * d.Lq + (row_ok ? q : 0)) * d.M + m;
-            const AT* lrow = loc + row * LP * 2;
-            const AT* arow = attn + row * LP;
+            const size_t rowq = (size_t)b * d.Lq + (row_ok ? q : 0);
+            const size_t row = rowq * d.M + m;
+            SampleSrc<AT, FUSED> src;
+            src.template begin<GS>(loc, attn, fa, d, row, rowq, row_ok, gl, grp * GS);
 
             float acc[VEC];
 #pragma unroll
@@ -71,13 +74,10 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_
                 // owner phase: lane gl of the group prepares sample s0 + gl of its row
                 const int s = s0 + gl;
                 const bool mine = row_ok && s < LP;
-                float2 xy = make_float2(0.f, 0.f);
-                float a = 0.f;
-                if (mine) {
-                    xy = load_loc<AT>(lrow + s * 2);
-                    a = load_attn<AT>(arow + s);
-                }
                 const int ls = min(s, LP - 1) / d.P;
+                float2 xy;
+                float a;
+                src.get(s, s0 / GS, ls, mine, d, xy.x, xy.y, a);
                 const OwnerTap t = make_owner_tap(mine, xy.x, xy.y, a, lt.H[ls], lt.W[ls], lt.start[ls], rsv);
                 const float wa0 = t.ay.w0 * t.a, wa1 = t.ay.w1 * t.a;
                 // publish the finished tap in shared memory, laid out [sample j][group] so the
@@ -107,11 +107,11 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_
     }
 }
 
-template <typename VT, typename AT, int VEC, int GS, int NWARPS>
+template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool FUSED>
 __global__ void __launch_bounds__(NWARPS * 32, 3)
 msda_forward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ shapes,
                     const int64_t* __restrict__ level_start, const AT* __restrict__ loc,
-                    const AT* __restrict__ attn, VT* __restrict__ out, const KernelDims d)
+                    const AT* __restrict__ attn, VT* __restrict__ out, const KernelDims d, const FusedArgs fa)
 {
     __shared__ LevelTable lt;
     stage_levels(lt, shapes, level_start, d);
@@ -121,9 +121,11 @@ msda_forward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ sh
     __shared__ float4 stage_b[NWARPS][32];
     const int warp = threadIdx.x >> 5;
     if (lt.min_w > 1)
-        forward_items<VT, AT, VEC, GS, NWARPS, true>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc, attn, out, d);
+        forward_items<VT, AT, VEC, GS, NWARPS, true, FUSED>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc,
+                                                            attn, out, d, fa);
     else
-        forward_items<VT, AT, VEC, GS, NWARPS, false>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc, attn, out, d);
+        forward_items<VT, AT, VEC, GS, NWARPS, false, FUSED>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc,
+                                                             attn, out, d, fa);
 }
 
 // Generic fallback: any D, any supported type (incl. fp64).  One warp per

@@ -131,22 +131,35 @@ inline long long items_upper_bound(const KernelDims& k)
     return tiles * k.N * k.M;
 }
 
-template <typename VT, typename AT, int VEC, int GS>
-int launch_forward_vec(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
-                       const void* attn, void* out, const msda_dims* d, cudaStream_t st)
+// fa == nullptr: loc / attn are materialised sampling locations / attention weights;
+// otherwise they are raw offsets / logits and *fa carries the rest of the module prologue's inputs.
+template <typename VT, typename AT, int VEC, int GS, bool FUSED>
+int launch_forward_vec_impl(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
+                            const void* attn, void* out, const msda_dims* d, cudaStream_t st, const FusedArgs& fa)
 {
     constexpr int NW = 8;
     const KernelDims k = make_dims(d, NW * (32 / GS));
-    auto kern = msda_forward_kernel<VT, AT, VEC, GS, NW>;
+    auto kern = msda_forward_kernel<VT, AT, VEC, GS, NW, FUSED>;
     static const int occ = query_occupancy(kern, NW * 32);   // once per instantiation
     const int grid = persistent_grid(occ, items_upper_bound(k));
     {
         TraceScope trace(st);
         kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                                       (VT*)out, k);
+                                       (VT*)out, k, fa);
     }
     ++g_last_launches;
     return (int)cudaGetLastError();
+}
+
+template <typename VT, typename AT, int VEC, int GS>
+int launch_forward_vec(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
+                       const void* attn, void* out, const msda_dims* d, cudaStream_t st, const FusedArgs* fa)
+{
+    if (fa) {
+        if (d->L * d->P > kFusedMaxChunks * GS) return MSDA_E_SHAPE;   // a lane keeps <= 4 softmax numerators per row
+        return launch_forward_vec_impl<VT, AT, VEC, GS, true>(value, shapes, ls, loc, attn, out, d, st, *fa);
+    }
+    return launch_forward_vec_impl<VT, AT, VEC, GS, false>(value, shapes, ls, loc, attn, out, d, st, FusedArgs{});
 }
 
 template <typename VT, typename AT, typename ACC>
@@ -166,48 +179,64 @@ int launch_forward_generic(const void* value, const int64_t* shapes, const int64
     return (int)cudaGetLastError();
 }
 
+// MSDA_E_SHAPE from a fused call = "no fused kernel for this shape": the caller runs the prologue
+// itself and uses the plain entry point.
 template <typename VT, typename AT>
 int forward_typed(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
-                  const void* attn, void* out, const msda_dims* d, cudaStream_t st)
+                  const void* attn, void* out, const msda_dims* d, cudaStream_t st, const FusedArgs* fa)
 {
     const bool al = aligned16(value) && aligned16(out) && !env_int("MSDA_B200_FORCE_GENERIC", 0);
     if constexpr (sizeof(VT) == 4) {
         if (al) switch (d->D) {
-            case 16: return launch_forward_vec<VT, AT, 4, 4>(value, shapes, ls, loc, attn, out, d, st);
-            case 32: return launch_forward_vec<VT, AT, 4, 8>(value, shapes, ls, loc, attn, out, d, st);
-            case 36: return launch_forward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, out, d, st);
-            case 64: return launch_forward_vec<VT, AT, 4, 16>(value, shapes, ls, loc, attn, out, d, st);
+            case 16: return launch_forward_vec<VT, AT, 4, 4>(value, shapes, ls, loc, attn, out, d, st, fa);
+            case 32: return launch_forward_vec<VT, AT, 4, 8>(value, shapes, ls, loc, attn, out, d, st, fa);
+            case 36: return launch_forward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, out, d, st, fa);
+            case 64: return launch_forward_vec<VT, AT, 4, 16>(value, shapes, ls, loc, attn, out, d, st, fa);
             default: break;
         }
     } else {
         if (al) switch (d->D) {
-            case 16: return launch_forward_vec<VT, AT, 8, 2>(value, shapes, ls, loc, attn, out, d, st);
-            case 32: return launch_forward_vec<VT, AT, 8, 4>(value, shapes, ls, loc, attn, out, d, st);
-            case 36: return launch_forward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, out, d, st);
-            case 64: return launch_forward_vec<VT, AT, 8, 8>(value, shapes, ls, loc, attn, out, d, st);
+            case 16: return launch_forward_vec<VT, AT, 8, 2>(value, shapes, ls, loc, attn, out, d, st, fa);
+            case 32: return launch_forward_vec<VT, AT, 8, 4>(value, shapes, ls, loc, attn, out, d, st, fa);
+            case 36: return launch_forward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, out, d, st, fa);
+            case 64: return launch_forward_vec<VT, AT, 8, 8>(value, shapes, ls, loc, attn, out, d, st, fa);
             default: break;
         }
     }
+    if (fa) return MSDA_E_SHAPE;
     return launch_forward_generic<VT, AT, float>(value, shapes, ls, loc, attn, out, d, st);
 }
 
-template <typename VT, typename AT, int VEC, int GS>
-int launch_backward_vec(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
-                        const void* attn, const void* go, float* gv_acc, void* gl, void* ga,
-                        const msda_dims* d, cudaStream_t st)
+template <typename VT, typename AT, int VEC, int GS, bool FUSED>
+int launch_backward_vec_impl(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
+                             const void* attn, const void* go, float* gv_acc, void* gl, void* ga,
+                             const msda_dims* d, cudaStream_t st, const FusedArgs& fa)
 {
     constexpr int NW = 8;
     const KernelDims k = make_dims(d, NW * (32 / GS));
-    auto kern = msda_backward_kernel<VT, AT, VEC, GS, NW>;
+    auto kern = msda_backward_kernel<VT, AT, VEC, GS, NW, FUSED>;
     static const int occ = query_occupancy(kern, NW * 32);   // once per instantiation
     const int grid = persistent_grid(occ, items_upper_bound(k));
     {
         TraceScope trace(st);
         kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k);
+                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa);
     }
     ++g_last_launches;
     return (int)cudaGetLastError();
+}
+
+template <typename VT, typename AT, int VEC, int GS>
+int launch_backward_vec(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
+                        const void* attn, const void* go, float* gv_acc, void* gl, void* ga,
+                        const msda_dims* d, cudaStream_t st, const FusedArgs* fa)
+{
+    if (fa) {
+        if (d->L * d->P > kFusedMaxChunks * GS) return MSDA_E_SHAPE;   // a lane keeps <= 4 samples of a row in registers
+        return launch_backward_vec_impl<VT, AT, VEC, GS, true>(value, shapes, ls, loc, attn, go, gv_acc, gl, ga, d, st, *fa);
+    }
+    return launch_backward_vec_impl<VT, AT, VEC, GS, false>(value, shapes, ls, loc, attn, go, gv_acc, gl, ga, d, st,
+                                                            FusedArgs{});
 }
 
 template <typename VT, typename AT, typename ACC>
@@ -232,7 +261,7 @@ int launch_backward_generic(const void* value, const int64_t* shapes, const int6
 template <typename VT, typename AT>
 int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
                    const void* attn, const void* go, void* gv, void* gl, void* ga, void* ws,
-                   size_t ws_bytes, const msda_dims* d, cudaStream_t st)
+                   size_t ws_bytes, const msda_dims* d, cudaStream_t st, const FusedArgs* fa)
 {
     const size_t nval = (size_t)d->N * d->S * d->M * d->D;
     float* acc;
@@ -250,27 +279,20 @@ int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, 
         const bool al = aligned16(value) && aligned16(go) && aligned16(acc) &&
                         !env_int("MSDA_B200_FORCE_GENERIC", 0);
         bool done = false;
-        if constexpr (sizeof(VT) == 4) {
-            if (al) switch (d->D) {
-                case 16: rc = launch_backward_vec<VT, AT, 4, 4>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                case 32: rc = launch_backward_vec<VT, AT, 4, 8>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                case 36: rc = launch_backward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                case 64: rc = launch_backward_vec<VT, AT, 4, 16>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                default: break;
-            }
-        } else {
-            if (al) switch (d->D) {
-                // 4 channels per lane also for 16-bit values (8-byte loads): a lane's reduction is then
-                // 16 contiguous bytes of the fp32 accumulator row and one instruction covers whole
-                // 128-byte rows, i.e. the fewest SM->L2 request packets per byte
-                case 16: rc = launch_backward_vec<VT, AT, 4, 4>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                case 32: rc = launch_backward_vec<VT, AT, 4, 8>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                case 36: rc = launch_backward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                case 64: rc = launch_backward_vec<VT, AT, 4, 16>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st); done = true; break;
-                default: break;
-            }
+        // 4 channels per lane for every value type (16-bit rows are read with 8-byte loads): a lane's
+        // reduction is then 16 contiguous bytes of the fp32 accumulator row and one instruction covers
+        // whole 128-byte rows, i.e. the fewest SM->L2 request packets per byte
+        if (al) switch (d->D) {
+            case 16: rc = launch_backward_vec<VT, AT, 4, 4>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st, fa); done = true; break;
+            case 32: rc = launch_backward_vec<VT, AT, 4, 8>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st, fa); done = true; break;
+            case 36: rc = launch_backward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st, fa); done = true; break;
+            case 64: rc = launch_backward_vec<VT, AT, 4, 16>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st, fa); done = true; break;
+            default: break;
         }
-        if (!done) rc = launch_backward_generic<VT, AT, float>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st);
+        if (!done) {
+            if (fa) return MSDA_E_SHAPE;      // no fused generic kernel: the caller runs the prologue itself
+            rc = launch_backward_generic<VT, AT, float>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st);
+        }
         if (rc) return rc;
     }
     if constexpr (sizeof(VT) == 2) {
@@ -296,9 +318,10 @@ int backward_f64(const void* value, const int64_t* shapes, const int64_t* ls, co
 
 #define MSDA_DECLARE_TYPED(EXTERN, VT, AT)                                                                   \
     EXTERN template int forward_typed<VT, AT>(const void*, const int64_t*, const int64_t*, const void*,      \
-                                              const void*, void*, const msda_dims*, cudaStream_t);           \
+                                              const void*, void*, const msda_dims*, cudaStream_t,            \
+                                              const FusedArgs*);                                             \
     EXTERN template int backward_typed<VT, AT>(const void*, const int64_t*, const int64_t*, const void*,     \
                                                const void*, const void*, void*, void*, void*, void*, size_t, \
-                                               const msda_dims*, cudaStream_t);
+                                               const msda_dims*, cudaStream_t, const FusedArgs*);
 
 }  // namespace msda

@@ -187,3 +187,111 @@ def ms_deform_attn_core_pytorch(value, value_spatial_shapes, sampling_locations,
     taps = torch.cat(taps, dim=-1)
     wts = attention_weights.permute(0, 2, 1, 3, 4).reshape(N * M, 1, Lq, L * P)
     return (taps * wts).sum(-1).reshape(N, M * D, Lq).transpose(1, 2).contiguous()
+
+
+# ---------------------------------------------------------------------------------------------------
+# Fused module prologue: softmax over the logits, query mask and the sampling-
+# location arithmetic of MSDeformAttn.forward (reference ops/modules/ms_deform_attn.py:69-82) run inside
+# the kernels; the (N,Lq,M,L,P,2) location tensor and the softmax output are never materialised.
+# ---------------------------------------------------------------------------------------------------
+def fused_supported(value, n_levels, n_points):
+    """True when libmsda_b200 has a fused kernel for this call (else: run the prologue in PyTorch)."""
+    D = value.shape[-1]
+    return (value.is_cuda and value.dtype in (torch.float32, torch.bfloat16, torch.float16)
+            and D in (16, 32, 36, 64) and n_levels * n_points <= 4 * (D // (4 if value.dtype == torch.float32 or D == 36 else 8)))
+
+
+def _fused_inputs(value, offsets, logits, reference_points, offset_norm, query_mask):
+    if value.dtype == torch.float32:
+        aux = torch.float32
+    elif offsets.dtype == value.dtype and logits.dtype == value.dtype:
+        aux = value.dtype
+    else:
+        aux = torch.float32
+    off = offsets.to(aux).contiguous()
+    lg = logits.to(aux).contiguous()
+    ref = reference_points.to(torch.float32).contiguous()
+    norm = offset_norm.to(device=value.device, dtype=torch.float32).contiguous() if offset_norm is not None else None
+    mask = query_mask.to(torch.uint8).contiguous() if query_mask is not None else None
+    args = _lib.MsdaFusedInputs(off.data_ptr(), lg.data_ptr(), ref.data_ptr(),
+                                norm.data_ptr() if norm is not None else None,
+                                mask.data_ptr() if mask is not None else None, ref.shape[-1])
+    return aux, args, (off, lg, ref, norm, mask)      # keep the tensors alive for the duration of the call
+
+
+class MSDeformAttnFusedFunction(Function):
+    """apply(value, spatial_shapes, reference_points, sampling_offsets, attention_logits, query_attn_mask,
+             offset_norm, im2col_step) -> (N, Lq, M*D)
+
+    value (N,S,M,D); reference_points (N,Lq,L,2|4); sampling_offsets (N,Lq,M,L,P,2) and attention_logits
+    (N,Lq,M,L*P) straight from the module's Linear layers; query_attn_mask (N,Lq) bool or None;
+    offset_norm (L,2): what the (x, y) offsets are divided by for 2-d reference points (the reference
+    module divides by input_spatial_shapes, ms_deform_attn.py:77-79), ignored for 4-d boxes."""
+
+    @staticmethod
+    def forward(ctx, value, spatial_shapes, reference_points, sampling_offsets, attention_logits, query_attn_mask,
+                offset_norm, im2col_step):
+        N, S, M, D = value.shape
+        _, Lq, M2, L, P, two = sampling_offsets.shape
+        if M2 != M or two != 2 or tuple(attention_logits.shape) != (N, Lq, M, L * P):
+            raise RuntimeError("sampling_offsets must be (N,Lq,M,L,P,2) and attention_logits (N,Lq,M,L*P)")
+        if tuple(reference_points.shape[:3]) != (N, Lq, L) or reference_points.shape[-1] not in (2, 4):
+            raise RuntimeError("reference_points must be (N, Lq, L, 2) or (N, Lq, L, 4)")
+        _check_inputs(value, spatial_shapes, sampling_offsets, attention_logits.view(N, Lq, M, L, P), im2col_step)
+        lib = _lib.load()
+        shapes = spatial_shapes.to(torch.int64).contiguous()
+        aux, args, keep = _fused_inputs(value, sampling_offsets, attention_logits, reference_points, offset_norm,
+                                        query_attn_mask)
+        dims = _lib.MsdaDims(N, S, M, D, L, Lq, P)
+        out = torch.empty((N, Lq, M * D), dtype=value.dtype, device=value.device)
+        with torch.cuda.device(value.device):
+            rc = lib.msda_b200_forward_fused(_ptr(value), _lib.dtype_code(value.dtype), _ptr(shapes), None,
+                                             ctypes.byref(args), _lib.dtype_code(aux), _ptr(out), ctypes.byref(dims),
+                                             ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+        _lib.check(rc, "msda_b200_forward_fused")
+        ctx.save_for_backward(value, shapes, reference_points, sampling_offsets, attention_logits,
+                              query_attn_mask if query_attn_mask is not None else torch.empty(0),
+                              offset_norm if offset_norm is not None else torch.empty(0))
+        ctx.im2col_step = im2col_step
+        del keep
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, grad_output):
+        value, shapes, ref, offsets, logits, mask, norm = ctx.saved_tensors
+        mask = mask if mask.numel() else None
+        norm = norm if norm.numel() else None
+        N, S, M, D = value.shape
+        _, Lq, _, L, P, _ = offsets.shape
+        lib = _lib.load()
+        aux, args, keep = _fused_inputs(value, offsets, logits, ref, norm, mask)
+        off_c = keep[0]
+        dims = _lib.MsdaDims(N, S, M, D, L, Lq, P)
+        go = grad_output.to(value.dtype).contiguous()
+        grad_value = torch.empty_like(value)
+        grad_off = torch.empty((N, Lq, M, L, P, 2), dtype=aux, device=value.device)
+        grad_logit = torch.empty((N, Lq, M, L * P), dtype=aux, device=value.device)
+        need_ref = ctx.needs_input_grad[2]
+        grad_loc = torch.empty((N, Lq, M, L, P, 2), dtype=torch.float32, device=value.device) if need_ref else None
+        vcode = _lib.dtype_code(value.dtype)
+        ws_bytes = int(lib.msda_b200_backward_workspace_bytes(vcode, ctypes.byref(dims)))
+        ws = torch.empty(ws_bytes // 4, dtype=torch.float32, device=value.device) if ws_bytes else None
+        with torch.cuda.device(value.device):
+            rc = lib.msda_b200_backward_fused(_ptr(value), vcode, _ptr(shapes), None, ctypes.byref(args),
+                                              _lib.dtype_code(aux), _ptr(go), _ptr(grad_value), _ptr(grad_off),
+                                              _ptr(grad_logit), _ptr(grad_loc), _ptr(ws), ctypes.c_size_t(ws_bytes),
+                                              ctypes.byref(dims),
+                                              ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+        _lib.check(rc, "msda_b200_backward_fused")
+        grad_ref = None
+        if need_ref:
+            # location = ref_xy + ...: every (head, point) sample of a (query, level) shares the reference point
+            if ref.shape[-1] == 2:
+                grad_ref = grad_loc.sum(dim=(2, 4))
+            else:
+                g_xy = grad_loc.sum(dim=(2, 4))
+                g_wh = (grad_loc * off_c.float()).sum(dim=(2, 4)) * (0.5 / P)
+                grad_ref = torch.cat([g_xy, g_wh], -1)
+            grad_ref = grad_ref.to(ref.dtype)
+        return (grad_value, None, grad_ref, grad_off.to(offsets.dtype), grad_logit.to(logits.dtype), None, None, None)

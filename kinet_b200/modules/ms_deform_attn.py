@@ -15,13 +15,17 @@ import torch.nn.functional as F
 from torch import nn
 from torch.nn.init import constant_, xavier_uniform_
 
-from ..functions import MSDeformAttnFunction
+from ..functions import MSDeformAttnFunction, MSDeformAttnFusedFunction, fused_supported
 
 
 class MSDeformAttn(nn.Module):
     def __init__(self, d_model=256, n_levels=4, n_heads=8, n_points=4, im2col_step=64):
         super().__init__()
         assert d_model % n_heads == 0
+        # True: softmax, query mask and the sampling-location arithmetic below run inside the CUDA
+        # kernels (MSDeformAttnFusedFunction) whenever the library has a fused kernel for the shape;
+        # False: the reference's own sequence of PyTorch ops followed by MSDeformAttnFunction.
+        self.fused_prologue = True
 
         self.im2col_step = im2col_step
         self.d_model = d_model
@@ -77,6 +81,16 @@ class MSDeformAttn(nn.Module):
             N, Len_q, self.n_heads, self.n_levels, self.n_points, 2)
         attention_weights = self.attention_weights(query).view(
             N, Len_q, self.n_heads, self.n_levels * self.n_points)
+        if reference_points.shape[-1] not in (2, 4):
+            raise ValueError(
+                'Last dim of reference_points must be 2 or 4, but get {} instead.'.format(
+                    reference_points.shape[-1]))
+        if self.fused_prologue and fused_supported(value, self.n_levels, self.n_points):
+            # same arithmetic as the lines below (reference :69-82), done in the kernels' owner lanes
+            output = MSDeformAttnFusedFunction.apply(
+                value, input_spatial_shapes, reference_points, sampling_offsets, attention_weights,
+                query_attn_mask, input_spatial_shapes, self.im2col_step)
+            return self.output_proj(output)
         attention_weights = F.softmax(attention_weights, -1).view(
             N, Len_q, self.n_heads, self.n_levels, self.n_points)
 
