@@ -78,3 +78,43 @@ def test_full_size_properties(tag, dtype):
     # zero attention weights: zero output, zero grad_value, zero grad_loc
     z_out, (z_gv, z_gl, _) = _ours(value, shapes, loc, torch.zeros_like(attn), go)
     assert not z_out.any() and not z_gv.any() and not z_gl.any()
+
+
+def test_speed_vs_reference_cuda_kernels():
+    """Same-box GPU baseline: the reference's own kernels (compiled for sm_100a, its host pipeline with the
+    `columns` scratch + sum restated in oracle/msda_ref_cuda.py) against this library, fp32, CUDA events,
+    L2 flushed between iterations.  Prints the table kept under profiles/ and asserts the speed-up."""
+    from oracle import msda_ref_cuda as ref
+    if not ref.available():
+        pytest.skip("oracle/_ref/libmsda_ref_cuda.so not built (needs /root/reference at build time)")
+    from kinet_b200.functions import ms_deform_attn_backward, ms_deform_attn_forward
+    dev = torch.device("cuda:0")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def med(fn, iters=5):
+        for _ in range(2):
+            fn()
+        ts = []
+        for _ in range(iters):
+            flush.zero_()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda._sleep(400000)
+            a.record(); fn(); b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b) * 1e3)
+        return sorted(ts)[len(ts) // 2]
+
+    print()
+    for tag in TAGS:
+        s = resolve(tag)
+        value, shapes, loc, attn = make_inputs(tag, dev, torch.float32, torch.float32, "structured", seed=3)
+        go = torch.randn(s["N"], s["Lq"], s["M"] * s["D"], device=dev)
+        cols = torch.empty(s["L"] * s["P"], s["N"], s["Lq"], s["M"], s["D"], device=dev)
+        of = med(lambda: ms_deform_attn_forward(value, shapes, loc, attn, 64))
+        ob = med(lambda: ms_deform_attn_backward(value, shapes, loc, attn, go, 64))
+        rf = med(lambda: ref.ref_cuda_forward(value, shapes, loc, attn, cols), 3)
+        rb = med(lambda: ref.ref_cuda_backward(value, shapes, loc, attn, go), 3)
+        print("%-7s fp32  ours fwd %8.1f us bwd %8.1f us | reference kernels fwd %8.1f us bwd %8.1f us | x%.1f fwd x%.1f bwd"
+              % (tag, of, ob, rf, rb, rf / of, rb / ob), flush=True)
+        assert of < rf and ob < rb, tag

@@ -9,9 +9,10 @@ python -m pytest tests -m gpu -x -q > $O/pytest_gpu.log 2>&1; echo "pytest exit 
 tail -3 $O/pytest_gpu.log
 python bench.py --steps 10 --warmup 3 > $O/bench.json 2> $O/bench.err; echo "bench exit $?"; cat $O/bench.json
 python bench.py --impl reference --steps 3 --warmup 1 > $O/bench_ref.json 2> $O/bench_ref.err; cat $O/bench_ref.json
-python tools/quick_bench.py --dtype f32 --ref --iters 10 > $O/quick_f32.txt 2>&1; cat $O/quick_f32.txt
+python tools/quick_bench.py --dtype f32 --iters 10 > $O/quick_f32.txt 2>&1; cat $O/quick_f32.txt
 python tools/quick_bench.py --dtype bf16 --iters 10 > $O/quick_bf16.txt 2>&1; cat $O/quick_bf16.txt
 python tools/quick_bench.py --dtype f32 --regime uniform --iters 10 C2_enc C2_dec > $O/quick_f32_uniform.txt 2>&1; cat $O/quick_f32_uniform.txt
+python -m pytest tests/test_full_size_gpu.py tests/test_transformer_gpu.py -m gpu -q -s -k "timing or speed" > $O/ref_kernel_timing.txt 2>&1; tail -30 $O/ref_kernel_timing.txt
 python bench.py --steps 2 --warmup 3 --e2e-steps 1 --cpu-steps 1 > $O/plain_bench.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:msda_ -c 600 --csv --log-file $O/launches.csv \
     python bench.py --steps 2 --warmup 3 --e2e-steps 1 --cpu-steps 1 > $O/ncu_launches.log 2>&1

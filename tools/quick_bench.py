@@ -38,7 +38,6 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--no-bwd", action="store_true")
     ap.add_argument("--warm", action="store_true", help="do not flush L2 between iterations")
-    ap.add_argument("--ref", action="store_true", help="also time the reference's own CUDA kernels (oracle/_ref, fp32)")
     args = ap.parse_args()
     dt = {"f32": torch.float32, "bf16": torch.bfloat16, "f16": torch.float16}[args.dtype]
     aux = dt if args.aux == "same" else torch.float32
@@ -61,12 +60,6 @@ def main():
             med, best = time_op(lambda: ms_deform_attn_backward(value, shapes, loc, attn, go, 64), flush, args.iters)
             line += " | bwd %8.1f us (best %8.1f)  %7.1f GB/s  %.3f" % (
                 med, best, bb / med / 1e3, bb / med / 1e3 / peak)
-        if args.ref and dt == torch.float32:
-            from oracle import msda_ref_cuda as ref
-            cols = torch.empty(s["L"] * s["P"], s["N"], s["Lq"], s["M"], s["D"], device=dev)
-            rf, _ = time_op(lambda: ref.ref_cuda_forward(value, shapes, loc, attn, cols), flush, max(3, args.iters // 2))
-            rb, _ = time_op(lambda: ref.ref_cuda_backward(value, shapes, loc, attn, go), flush, max(3, args.iters // 2))
-            line += " | REF fwd %8.1f us bwd %8.1f us" % (rf, rb)
         print(line, flush=True)
 
 
