@@ -71,7 +71,8 @@ __device__ __forceinline__ void reduce_scatter(float (&U)[N][4], int gl, float (
 // FUSED: loc / attn are raw sampling offsets / attention logits, grad_loc / grad_attn their gradients
 // (through the location arithmetic and the softmax); see SampleSrc<AT, true> in msda_common.cuh.
 template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE, bool FUSED>
-__device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage_a, int* stage_dx, float4* stage_b,
+__device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage_a, int* stage_dx,
+                                               float4* stage_b,
                                                const VT* __restrict__ value,
                                                const AT* __restrict__ loc, const AT* __restrict__ attn,
                                                const VT* __restrict__ grad_out,
@@ -97,7 +98,11 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
     const int rsv = d.M * GS;
     const int items = lt.total_tiles * d.N * d.M;
 
-    for (int item = blockIdx.x; item < items; item += gridDim.x) {
+    constexpr int PASS = NWARPS * GPW;     // query rows per CTA pass
+    WorkSplit ws;
+    ws.init(items, d, PASS);
+
+    for (int item, p0, p1; ws.next(item, p0, p1);) {
         const int tile = item / (d.N * d.M);
         const int bm = item - tile * (d.N * d.M);
         const int b = bm / d.M, m = bm - b * d.M;
@@ -106,7 +111,8 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
         float* gv_base = grad_value_acc + bbase;
 
         const TileInfo ti = decode_tile(lt, d, tile);
-        for (int i0 = warp * GPW; i0 < ti.count; i0 += NWARPS * GPW) {
+        const int i_end = min(ti.count, p1 * PASS);
+        for (int i0 = p0 * PASS + warp * GPW; i0 < i_end; i0 += PASS) {
             const int q = (lane_used && i0 + grp < ti.count) ? tile_query(ti, i0 + grp) : -1;
             const bool row_ok = q >= 0;
             const size_t rowq = (size_t)b * d.Lq + (row_ok ? q : 0);

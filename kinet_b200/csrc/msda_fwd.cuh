@@ -14,6 +14,9 @@
 #pragma once
 #include "msda_common.cuh"
 
+#ifndef MSDA_FWD_MINB
+#define MSDA_FWD_MINB 3
+#endif
 namespace msda {
 
 // One gathered sample: four 16-byte corner loads issued back to back, then 4*VEC FMAs.
@@ -37,7 +40,8 @@ __device__ __forceinline__ void gather_sample(float (&acc)[VEC], const VT* lane_
 // FUSED: `loc` / `attn` are the module's raw sampling offsets / attention logits and the prologue
 // (softmax, location arithmetic) runs in the owner lanes (SampleSrc<AT, true>, msda_common.cuh).
 template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE, bool FUSED>
-__device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_a, int* stage_dx, float4* stage_b,
+__device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_a, int* stage_dx,
+                                              float4* stage_b,
                                               const VT* __restrict__ value,
                                               const AT* __restrict__ loc, const AT* __restrict__ attn,
                                               VT* __restrict__ out, const KernelDims& d, const FusedArgs& fa)
@@ -51,14 +55,19 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_
     const int rsv = d.M * GS;              // vectors between neighbouring pixels
     const int items = lt.total_tiles * d.N * d.M;
 
-    for (int item = blockIdx.x; item < items; item += gridDim.x) {
+    constexpr int PASS = NWARPS * GPW;     // query rows per CTA pass
+    WorkSplit ws;
+    ws.init(items, d, PASS);
+
+    for (int item, p0, p1; ws.next(item, p0, p1);) {
         const int tile = item / (d.N * d.M);
         const int bm = item - tile * (d.N * d.M);
         const int b = bm / d.M, m = bm - b * d.M;
         const VT* lane_base = value + ((size_t)b * d.S * d.M + m) * D + gl * VEC;
 
         const TileInfo ti = decode_tile(lt, d, tile);
-        for (int i0 = warp * GPW; i0 < ti.count; i0 += NWARPS * GPW) {
+        const int i_end = min(ti.count, p1 * PASS);
+        for (int i0 = p0 * PASS + warp * GPW; i0 < i_end; i0 += PASS) {
             const int q = (lane_used && i0 + grp < ti.count) ? tile_query(ti, i0 + grp) : -1;
             const bool row_ok = q >= 0;
             const size_t rowq = (size_t)b * d.Lq + (row_ok ? q : 0);
@@ -108,7 +117,7 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_
 }
 
 template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool FUSED>
-__global__ void __launch_bounds__(NWARPS * 32, 3)
+__global__ void __launch_bounds__(NWARPS * 32, MSDA_FWD_MINB)
 msda_forward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ shapes,
                     const int64_t* __restrict__ level_start, const AT* __restrict__ loc,
                     const AT* __restrict__ attn, VT* __restrict__ out, const KernelDims d, const FusedArgs fa)

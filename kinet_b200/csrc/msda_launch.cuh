@@ -60,6 +60,8 @@ inline int check_common(const void* value, const int64_t* shapes, const void* lo
     // 32-bit element offsets inside one batch item
     if ((long long)d->S * d->M * d->D >= (1ll << 31)) return MSDA_E_SHAPE;
     if ((long long)d->L * d->P >= (1 << 20)) return MSDA_E_SHAPE;
+    // 32-bit work-unit counters in the kernels (cta_work_range)
+    if ((long long)d->N * d->M * d->Lq >= (1ll << 30)) return MSDA_E_SHAPE;
     if (!value || !shapes) return MSDA_E_NULL;
     if (d->Lq > 0 && (!loc || !attn)) return MSDA_E_NULL;
     return 0;
@@ -75,6 +77,8 @@ inline KernelDims make_dims(const msda_dims* d, int rows_per_pass)
 {
     KernelDims k;
     k.N = d->N; k.S = d->S; k.M = d->M; k.D = d->D; k.L = d->L; k.Lq = d->Lq; k.P = d->P;
+    k.split = env_int("MSDA_B200_SPLIT", 2);
+    k.balanced = env_int("MSDA_B200_BALANCED", 1);
     const int sms = device_info().sms > 0 ? device_info().sms : 148;
     const int force_1d = env_int("MSDA_B200_TILE_1D", 0);
     if (d->Lq == d->S && !force_1d) {
@@ -138,7 +142,7 @@ int launch_forward_vec_impl(const void* value, const int64_t* shapes, const int6
                             const void* attn, void* out, const msda_dims* d, cudaStream_t st, const FusedArgs& fa)
 {
     constexpr int NW = 8;
-    const KernelDims k = make_dims(d, NW * (32 / GS));
+    KernelDims k = make_dims(d, NW * (32 / GS));
     auto kern = msda_forward_kernel<VT, AT, VEC, GS, NW, FUSED>;
     static const int occ = query_occupancy(kern, NW * 32);   // once per instantiation
     const int grid = persistent_grid(occ, items_upper_bound(k));
@@ -213,7 +217,7 @@ int launch_backward_vec_impl(const void* value, const int64_t* shapes, const int
                              const msda_dims* d, cudaStream_t st, const FusedArgs& fa)
 {
     constexpr int NW = 8;
-    const KernelDims k = make_dims(d, NW * (32 / GS));
+    KernelDims k = make_dims(d, NW * (32 / GS));
     auto kern = msda_backward_kernel<VT, AT, VEC, GS, NW, FUSED>;
     static const int occ = query_occupancy(kern, NW * 32);   // once per instantiation
     const int grid = persistent_grid(occ, items_upper_bound(k));
