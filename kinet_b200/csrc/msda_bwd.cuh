@@ -21,31 +21,13 @@
 #endif
 namespace msda {
 
-// Sum across the GS lanes of a group; every lane of the group gets the total.
-template <int GS>
-__device__ __forceinline__ float group_sum(float v, int gl, int grp_base)
-{
-    if constexpr ((GS & (GS - 1)) == 0) {
-#pragma unroll
-        for (int o = GS / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        return v;
-    } else {
-        // non power-of-two group (D = 36 -> GS = 9): fold down, then broadcast lane 0
-#pragma unroll
-        for (int o = 8; o > 0; o >>= 1) {
-            const float t = __shfl_down_sync(0xffffffffu, v, o);
-            if (gl < o && gl + o < GS) v += t;
-        }
-        return __shfl_sync(0xffffffffu, v, grp_base);
-    }
-}
-
-// Reduce-scatter over the GS lanes of a row group (GS a power of two): on entry every lane
-// holds, for each of the N samples, 4 partial dot products; on exit lane gl holds the group
-// totals of sample gl.  log2(GS) butterfly steps that halve the number of live values, i.e.
-// 4*(GS-1) shuffles per chunk instead of 4*GS*log2(GS) for per-sample all-reduces.
+// Reduce-scatter over the first N lanes of a row group (N a power of two; the group starts at lane
+// grp_base, which need not be a multiple of N): on entry every lane holds, for each of the N samples,
+// 4 partial dot products; on exit lane gl < N holds the totals over those N lanes of sample gl.
+// log2(N) butterfly steps that halve the number of live values, i.e. 4*(N-1) shuffles per chunk
+// instead of 4*N*log2(N) for per-sample all-reduces.
 template <int N>
-__device__ __forceinline__ void reduce_scatter(float (&U)[N][4], int gl, float (&out)[4])
+__device__ __forceinline__ void reduce_scatter(float (&U)[N][4], int gl, int grp_base, float (&out)[4])
 {
     if constexpr (N == 1) {
 #pragma unroll
@@ -60,10 +42,10 @@ __device__ __forceinline__ void reduce_scatter(float (&U)[N][4], int gl, float (
             for (int c = 0; c < 4; ++c) {
                 const float keep = upper ? U[i + HALF][c] : U[i][c];
                 const float send = upper ? U[i][c] : U[i + HALF][c];
-                K[i][c] = keep + __shfl_xor_sync(0xffffffffu, send, HALF);
+                K[i][c] = keep + __shfl_sync(0xffffffffu, send, (grp_base + (gl ^ HALF)) & 31);   // lanes gl >= group size of the butterfly read garbage, unused
             }
         }
-        reduce_scatter<HALF>(K, gl, out);
+        reduce_scatter<HALF>(K, gl, grp_base, out);
     }
 }
 
@@ -72,7 +54,7 @@ __device__ __forceinline__ void reduce_scatter(float (&U)[N][4], int gl, float (
 // (through the location arithmetic and the softmax); see SampleSrc<AT, true> in msda_common.cuh.
 template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE, bool FUSED>
 __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage_a, int* stage_dx,
-                                               float4* stage_b,
+                                               float4* stage_b, float4* fold,
                                                const VT* __restrict__ value,
                                                const AT* __restrict__ loc, const AT* __restrict__ attn,
                                                const VT* __restrict__ grad_out,
@@ -83,7 +65,7 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
                                // the row's softmax backward (launcher guarantees L*P <= MAXCH*GS)
     constexpr int GPW = 32 / GS;
     constexpr int D = VEC * GS;
-    constexpr bool POW2 = (GS & (GS - 1)) == 0;
+    constexpr int CH = chunk_of(GS);   // samples per chunk, prepared by the owner lanes gl < CH
     // VEC = 4 for every value type: a lane's reduction is 16 contiguous bytes of the fp32 accumulator
     // row, the GS lanes of a row cover it without gaps, and one warp instruction carries whole rows.
     // The SM->L2 request port sends one packet (header + 32-byte sectors) per 128-byte line touched,
@@ -118,7 +100,7 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
             const size_t rowq = (size_t)b * d.Lq + (row_ok ? q : 0);
             const size_t row = rowq * d.M + m;
             SampleSrc<AT, FUSED> src;
-            src.template begin<GS>(loc, attn, fa, d, row, rowq, row_ok, gl, grp_base);
+            src.template begin<GS, CH>(loc, attn, fa, d, row, rowq, row_ok, gl, grp_base);
             float ga_keep[MAXCH] = {0.f, 0.f, 0.f, 0.f};   // fused: d out / d attention of this lane's samples
             float dot = 0.f;                                // fused: sum_s prob_s * d out / d attention_s
 
@@ -126,20 +108,20 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
 #pragma unroll
             for (int k = 0; k < VEC; ++k) g[k] = 0.f;
             if (row_ok) VecIO<VT, VEC>::load_stream(grad_out + row * D + gl * VEC, g);
-            for (int s0 = 0; s0 < LP; s0 += GS) {
-                // owner phase: lane gl prepares sample s0 + gl of its row
+            for (int s0 = 0; s0 < LP; s0 += CH) {
+                // owner phase: lane gl < CH prepares sample s0 + gl of its row
                 const int s = s0 + gl;
-                const bool mine = row_ok && s < LP;
+                const bool mine = row_ok && gl < CH && s < LP;
                 const int ls = min(s, LP - 1) / d.P;
                 float2 xy;
                 float a;
-                src.get(s, s0 / GS, ls, mine, d, xy.x, xy.y, a);
+                src.get(s, s0 / CH, ls, mine, d, xy.x, xy.y, a);
                 const int H = lt.H[ls], W = lt.W[ls];
                 const OwnerTap t = make_owner_tap(mine, xy.x, xy.y, a, H, W, lt.start[ls], rsv);
                 const float wa0 = t.ay.w0 * t.a, wa1 = t.ay.w1 * t.a;
                 // publish the tap (offsets; corner weight * attn) in shared memory, [sample][group]
                 __syncwarp();
-                if (lane_used) {
+                if (lane_used && gl < CH) {
                     stage_a[gl * GPW + grp] = make_int2(t.off0, t.off0 + t.dy);
                     if constexpr (!WIDE) stage_dx[gl * GPW + grp] = t.dx;
                     stage_b[gl * GPW + grp] = make_float4(wa0 * t.ax.w0, wa0 * t.ax.w1, wa1 * t.ax.w0, wa1 * t.ax.w1);
@@ -148,9 +130,9 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
                 const int gsel = lane_used ? grp : 0;
 
                 // broadcast phase: every lane of the group handles its VEC channels of sample s0+j
-                float U[GS][4];
+                float U[CH][4];
 #pragma unroll
-                for (int j = 0; j < GS; ++j) {
+                for (int j = 0; j < CH; ++j) {
                     const int2 ra = stage_a[j * GPW + gsel];
                     const float4 rb = stage_b[j * GPW + gsel];
                     const int o0 = ra.x, o2 = ra.y, dx = WIDE ? rsv : stage_dx[j * GPW + gsel];
@@ -186,19 +168,20 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
                 }
                 // bring the group totals of sample s0+gl to its owner lane
                 float u[4];
-                if constexpr (POW2) {
-                    reduce_scatter<GS>(U, gl, u);
-                } else {
+                if constexpr (GS != CH) {
+                    // lanes gl >= CH (D = 36: lane 8) hand their partials to the owners through shared memory
+                    static_assert(GS == CH + 1, "one extra channel lane per group");
+                    __syncwarp();
+                    if (lane_used && gl == CH) {
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) u[c] = 0.f;
-#pragma unroll
-                    for (int j = 0; j < GS; ++j) {
-#pragma unroll
-                        for (int c = 0; c < 4; ++c) {
-                            const float tot = group_sum<GS>(U[j][c], gl, grp_base);
-                            if (gl == j) u[c] = tot;
-                        }
+                        for (int j = 0; j < CH; ++j) fold[grp * CH + j] = make_float4(U[j][0], U[j][1], U[j][2], U[j][3]);
                     }
+                    __syncwarp();
+                }
+                reduce_scatter<CH>(U, gl, grp_base, u);
+                if constexpr (GS != CH) {
+                    const float4 f = fold[(lane_used ? grp : 0) * CH + (gl & (CH - 1))];
+                    u[0] += f.x; u[1] += f.y; u[2] += f.z; u[3] += f.w;
                 }
                 if (mine) {
                     // owner lane: its own (unbroadcast) tap turns u into the three gradients
@@ -218,7 +201,7 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
                         store_loc<AT>(grad_loc + (row * LP + s) * 2, glx * src.sx, gly * src.sy);
                         if (fa.grad_loc) store_loc<float>(fa.grad_loc + (row * LP + s) * 2, glx, gly);
                         const float gam = src.masked ? 0.f : ga;   // masked_fill(mask, 0): no gradient to the softmax
-                        const int c = s0 / GS;
+                        const int c = s0 / CH;
 #pragma unroll
                         for (int k = 0; k < MAXCH; ++k)
                             if (c == k) ga_keep[k] = gam;
@@ -232,8 +215,8 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
                 if (row_ok) {
 #pragma unroll
                     for (int k = 0; k < MAXCH; ++k) {
-                        const int s = k * GS + gl;
-                        if (s < LP) grad_attn[row * LP + s] = from_f32<AT>(src.prob(k) * (ga_keep[k] - tot));
+                        const int s = k * CH + gl;
+                        if (gl < CH && s < LP) grad_attn[row * LP + s] = from_f32<AT>(src.prob(k) * (ga_keep[k] - tot));
                     }
                 }
             }
@@ -254,12 +237,14 @@ msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ s
     __shared__ int2 stage_a[NWARPS][32];
     __shared__ int stage_dx[NWARPS][32];
     __shared__ float4 stage_b[NWARPS][32];
+    constexpr int FOLD = GS == chunk_of(GS) ? 1 : (32 / GS) * chunk_of(GS);   // only groups with a non-owner lane fold
+    __shared__ float4 fold[NWARPS][FOLD];
     const int warp = threadIdx.x >> 5;
     if (lt.min_w > 1)
-        backward_items<VT, AT, VEC, GS, NWARPS, true, FUSED>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc,
+        backward_items<VT, AT, VEC, GS, NWARPS, true, FUSED>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], fold[warp], value, loc,
                                                              attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa);
     else
-        backward_items<VT, AT, VEC, GS, NWARPS, false, FUSED>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc,
+        backward_items<VT, AT, VEC, GS, NWARPS, false, FUSED>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], fold[warp], value, loc,
                                                               attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa);
 }
 

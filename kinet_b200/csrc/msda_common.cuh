@@ -431,12 +431,22 @@ __device__ __forceinline__ float group_reduce(float v, int gl, int grp_base)
     }
 }
 
+// Samples of a row are prepared CH at a time by the "owner" lanes gl < CH of its group, CH = the
+// largest power of two <= GS (GS = 9 for D = 36: lane 8 only carries channels).  A power-of-two chunk
+// divides the usual L*P (16, 32) without a ragged tail and keeps the backward's reduce-scatter a butterfly.
+__host__ __device__ constexpr int chunk_of(int gs)
+{
+    int c = 1;
+    while (c * 2 <= gs) c *= 2;
+    return c;
+}
+
 template <typename AT, bool FUSED> struct SampleSrc;
 
 template <typename AT> struct SampleSrc<AT, false> {
     const AT* lrow;
     const AT* arow;
-    template <int GS>
+    template <int GS, int CH>
     __device__ __forceinline__ void begin(const AT* loc, const AT* attn, const FusedArgs&, const KernelDims& d, size_t row,
                                           size_t, bool, int, int)
     {
@@ -461,14 +471,14 @@ template <typename AT> struct SampleSrc<AT, true> {
     const AT* orow;      // raw offsets of the row
     const float* rrow;   // reference points of the query, [L][ref_dim]
     const float* norm;
-    float e[kFusedMaxChunks];   // exp(logit - max) of this lane's samples gl, gl + GS, ... of the row
+    float e[kFusedMaxChunks];   // exp(logit - max) of this lane's samples gl, gl + CH, ... of the row (gl < CH)
     float inv_sum;       // 1 / sum of the row's numerators
     float sx, sy;        // d location / d offset of the last get() (backward)
     bool masked;
     int ref_dim;
 
-    // One pass over the row's logits (launcher guarantees L*P <= kFusedMaxChunks * GS).
-    template <int GS>
+    // One pass over the row's logits (launcher guarantees L*P <= kFusedMaxChunks * CH).
+    template <int GS, int CH>
     __device__ __forceinline__ void begin(const AT* off, const AT* logit, const FusedArgs& fa, const KernelDims& d,
                                           size_t row, size_t rowq, bool row_ok, int gl, int grp_base)
     {
@@ -482,8 +492,8 @@ template <typename AT> struct SampleSrc<AT, true> {
         float m_ = -INFINITY;
 #pragma unroll
         for (int c = 0; c < kFusedMaxChunks; ++c) {
-            const int s = c * GS + gl;
-            e[c] = (row_ok && s < LP) ? load_attn<AT>(grow + s) : -INFINITY;
+            const int s = c * CH + gl;
+            e[c] = (row_ok && gl < CH && s < LP) ? load_attn<AT>(grow + s) : -INFINITY;
             m_ = fmaxf(m_, e[c]);
         }
         const float mx = group_reduce<GS, MaxOp>(m_, gl, grp_base);

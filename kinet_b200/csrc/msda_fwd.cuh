@@ -47,6 +47,7 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_
                                               VT* __restrict__ out, const KernelDims& d, const FusedArgs& fa)
 {
     constexpr int GPW = 32 / GS;           // rows per warp
+    constexpr int CH = chunk_of(GS);       // samples prepared per chunk (owner lanes gl < CH)
     constexpr int D = VEC * GS;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int grp = lane / GS, gl = lane - grp * GS;
@@ -73,38 +74,38 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_
             const size_t rowq = (size_t)b * d.Lq + (row_ok ? q : 0);
             const size_t row = rowq * d.M + m;
             SampleSrc<AT, FUSED> src;
-            src.template begin<GS>(loc, attn, fa, d, row, rowq, row_ok, gl, grp * GS);
+            src.template begin<GS, CH>(loc, attn, fa, d, row, rowq, row_ok, gl, grp * GS);
 
             float acc[VEC];
 #pragma unroll
             for (int k = 0; k < VEC; ++k) acc[k] = 0.f;
 
-            for (int s0 = 0; s0 < LP; s0 += GS) {
-                // owner phase: lane gl of the group prepares sample s0 + gl of its row
+            for (int s0 = 0; s0 < LP; s0 += CH) {
+                // owner phase: lane gl < CH of the group prepares sample s0 + gl of its row
                 const int s = s0 + gl;
-                const bool mine = row_ok && s < LP;
+                const bool mine = row_ok && gl < CH && s < LP;
                 const int ls = min(s, LP - 1) / d.P;
                 float2 xy;
                 float a;
-                src.get(s, s0 / GS, ls, mine, d, xy.x, xy.y, a);
+                src.get(s, s0 / CH, ls, mine, d, xy.x, xy.y, a);
                 const OwnerTap t = make_owner_tap(mine, xy.x, xy.y, a, lt.H[ls], lt.W[ls], lt.start[ls], rsv);
                 const float wa0 = t.ay.w0 * t.a, wa1 = t.ay.w1 * t.a;
                 // publish the finished tap in shared memory, laid out [sample j][group] so the
                 // broadcast reads of one step (one 16-byte record per group) are conflict-free.
                 // (Shuffles would cost one LSU data-pipe wavefront per value; this is 3 per sample.)
                 __syncwarp();
-                if (lane_used) {
+                if (lane_used && gl < CH) {
                     stage_a[gl * GPW + grp] = make_int2(t.off0, t.off0 + t.dy);
                     if constexpr (!WIDE) stage_dx[gl * GPW + grp] = t.dx;
                     stage_b[gl * GPW + grp] = make_float4(wa0 * t.ax.w0, wa0 * t.ax.w1, wa1 * t.ax.w0, wa1 * t.ax.w1);
                 }
                 __syncwarp();
                 // broadcast phase: all lanes of the group consume sample s0 + j.  A ragged last
-                // chunk runs the full GS steps too: lanes without a sample publish weight 0 at
+                // chunk runs the full CH steps too: lanes without a sample publish weight 0 at
                 // offset 0 (valid memory), so no guards are needed inside the unrolled body.
                 const int gsel = lane_used ? grp : 0;
 #pragma unroll
-                for (int j = 0; j < GS; ++j) {
+                for (int j = 0; j < CH; ++j) {
                     const int2 ra = stage_a[j * GPW + gsel];
                     const float4 rb = stage_b[j * GPW + gsel];
                     gather_sample<VT, VEC>(acc, lane_base, ra.x, ra.y, WIDE ? rsv : stage_dx[j * GPW + gsel], rb.x, rb.y,

@@ -160,7 +160,7 @@ int launch_forward_vec(const void* value, const int64_t* shapes, const int64_t* 
                        const void* attn, void* out, const msda_dims* d, cudaStream_t st, const FusedArgs* fa)
 {
     if (fa) {
-        if (d->L * d->P > kFusedMaxChunks * GS) return MSDA_E_SHAPE;   // a lane keeps <= 4 softmax numerators per row
+        if (d->L * d->P > kFusedMaxChunks * chunk_of(GS)) return MSDA_E_SHAPE;   // a lane keeps <= 4 softmax numerators per row
         return launch_forward_vec_impl<VT, AT, VEC, GS, true>(value, shapes, ls, loc, attn, out, d, st, *fa);
     }
     return launch_forward_vec_impl<VT, AT, VEC, GS, false>(value, shapes, ls, loc, attn, out, d, st, FusedArgs{});
@@ -236,7 +236,7 @@ int launch_backward_vec(const void* value, const int64_t* shapes, const int64_t*
                         const msda_dims* d, cudaStream_t st, const FusedArgs* fa)
 {
     if (fa) {
-        if (d->L * d->P > kFusedMaxChunks * GS) return MSDA_E_SHAPE;   // a lane keeps <= 4 samples of a row in registers
+        if (d->L * d->P > kFusedMaxChunks * chunk_of(GS)) return MSDA_E_SHAPE;   // a lane keeps <= 4 samples of a row in registers
         return launch_backward_vec_impl<VT, AT, VEC, GS, true>(value, shapes, ls, loc, attn, go, gv_acc, gl, ga, d, st, *fa);
     }
     return launch_backward_vec_impl<VT, AT, VEC, GS, false>(value, shapes, ls, loc, attn, go, gv_acc, gl, ga, d, st,
