@@ -65,6 +65,7 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
                                // the row's softmax backward (launcher guarantees L*P <= MAXCH*GS)
     constexpr int GPW = 32 / GS;
     constexpr int D = VEC * GS;
+    constexpr int RS = record_stride(GS);  // records per sample in the shared-memory tap arrays
     constexpr int CH = chunk_of(GS);   // samples per chunk, prepared by the owner lanes gl < CH
     // VEC = 4 for every value type: a lane's reduction is 16 contiguous bytes of the fp32 accumulator
     // row, the GS lanes of a row cover it without gaps, and one warp instruction carries whole rows.
@@ -122,9 +123,9 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
                 // publish the tap (offsets; corner weight * attn) in shared memory, [sample][group]
                 __syncwarp();
                 if (lane_used && gl < CH) {
-                    stage_a[gl * GPW + grp] = make_int2(t.off0, t.off0 + t.dy);
-                    if constexpr (!WIDE) stage_dx[gl * GPW + grp] = t.dx;
-                    stage_b[gl * GPW + grp] = make_float4(wa0 * t.ax.w0, wa0 * t.ax.w1, wa1 * t.ax.w0, wa1 * t.ax.w1);
+                    stage_a[gl * RS + grp] = make_int2(t.off0, t.off0 + t.dy);
+                    if constexpr (!WIDE) stage_dx[gl * RS + grp] = t.dx;
+                    stage_b[gl * RS + grp] = make_float4(wa0 * t.ax.w0, wa0 * t.ax.w1, wa1 * t.ax.w0, wa1 * t.ax.w1);
                 }
                 __syncwarp();
                 const int gsel = lane_used ? grp : 0;
@@ -133,9 +134,9 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
                 float U[CH][4];
 #pragma unroll
                 for (int j = 0; j < CH; ++j) {
-                    const int2 ra = stage_a[j * GPW + gsel];
-                    const float4 rb = stage_b[j * GPW + gsel];
-                    const int o0 = ra.x, o2 = ra.y, dx = WIDE ? rsv : stage_dx[j * GPW + gsel];
+                    const int2 ra = stage_a[j * RS + gsel];
+                    const float4 rb = stage_b[j * RS + gsel];
+                    const int o0 = ra.x, o2 = ra.y, dx = WIDE ? rsv : stage_dx[j * RS + gsel];
                     const float bw[4] = {rb.x, rb.y, rb.z, rb.w};
                     const unsigned o[4] = {(unsigned)o0, (unsigned)(o0 + dx), (unsigned)o2, (unsigned)(o2 + dx)};
                     float v[4][VEC];
@@ -234,9 +235,9 @@ msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ s
 {
     __shared__ LevelTable lt;
     stage_levels(lt, shapes, level_start, d);
-    __shared__ int2 stage_a[NWARPS][32];
-    __shared__ int stage_dx[NWARPS][32];
-    __shared__ float4 stage_b[NWARPS][32];
+    __shared__ int2 stage_a[NWARPS][record_count(GS)];
+    __shared__ int stage_dx[NWARPS][record_count(GS)];
+    __shared__ float4 stage_b[NWARPS][record_count(GS)];
     constexpr int FOLD = GS == chunk_of(GS) ? 1 : (32 / GS) * chunk_of(GS);   // only groups with a non-owner lane fold
     __shared__ float4 fold[NWARPS][FOLD];
     const int warp = threadIdx.x >> 5;

@@ -441,6 +441,23 @@ __host__ __device__ constexpr int chunk_of(int gs)
     return c;
 }
 
+// Tap records live in shared memory as [sample j][group], `record_stride(GS)` records per sample.
+// The owner lanes of a warp write their records at once (lane (grp, gl) -> record (gl, grp)); with the
+// natural stride 32/GS the eight 16-byte records of a quarter warp fall into one or two 16-byte bank
+// groups (ncu: 21 data-pipe wavefronts per chunk for the two stores instead of 6).  A stride congruent
+// to max(1, 8/GS) modulo 8 spreads them over all eight bank groups and keeps the broadcast reads of a
+// step (one record per group, consecutive records) conflict-free.
+__host__ __device__ constexpr int record_stride(int gs)
+{
+    const int gpw = 32 / gs;
+    const int b = 8 / gs > 1 ? 8 / gs : 1;
+    if (b == 1) return gpw | 1;
+    int s = gpw;
+    while (s % 8 != b) ++s;
+    return s;
+}
+__host__ __device__ constexpr int record_count(int gs) { return chunk_of(gs) * record_stride(gs); }
+
 template <typename AT, bool FUSED> struct SampleSrc;
 
 template <typename AT> struct SampleSrc<AT, false> {

@@ -47,6 +47,7 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_
                                               VT* __restrict__ out, const KernelDims& d, const FusedArgs& fa)
 {
     constexpr int GPW = 32 / GS;           // rows per warp
+    constexpr int RS = record_stride(GS);  // records per sample in the shared-memory tap arrays
     constexpr int CH = chunk_of(GS);       // samples prepared per chunk (owner lanes gl < CH)
     constexpr int D = VEC * GS;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -95,9 +96,9 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_
                 // (Shuffles would cost one LSU data-pipe wavefront per value; this is 3 per sample.)
                 __syncwarp();
                 if (lane_used && gl < CH) {
-                    stage_a[gl * GPW + grp] = make_int2(t.off0, t.off0 + t.dy);
-                    if constexpr (!WIDE) stage_dx[gl * GPW + grp] = t.dx;
-                    stage_b[gl * GPW + grp] = make_float4(wa0 * t.ax.w0, wa0 * t.ax.w1, wa1 * t.ax.w0, wa1 * t.ax.w1);
+                    stage_a[gl * RS + grp] = make_int2(t.off0, t.off0 + t.dy);
+                    if constexpr (!WIDE) stage_dx[gl * RS + grp] = t.dx;
+                    stage_b[gl * RS + grp] = make_float4(wa0 * t.ax.w0, wa0 * t.ax.w1, wa1 * t.ax.w0, wa1 * t.ax.w1);
                 }
                 __syncwarp();
                 // broadcast phase: all lanes of the group consume sample s0 + j.  A ragged last
@@ -106,9 +107,9 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_
                 const int gsel = lane_used ? grp : 0;
 #pragma unroll
                 for (int j = 0; j < CH; ++j) {
-                    const int2 ra = stage_a[j * GPW + gsel];
-                    const float4 rb = stage_b[j * GPW + gsel];
-                    gather_sample<VT, VEC>(acc, lane_base, ra.x, ra.y, WIDE ? rsv : stage_dx[j * GPW + gsel], rb.x, rb.y,
+                    const int2 ra = stage_a[j * RS + gsel];
+                    const float4 rb = stage_b[j * RS + gsel];
+                    gather_sample<VT, VEC>(acc, lane_base, ra.x, ra.y, WIDE ? rsv : stage_dx[j * RS + gsel], rb.x, rb.y,
                                            rb.z, rb.w);
                 }
             }
@@ -126,9 +127,9 @@ msda_forward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ sh
     __shared__ LevelTable lt;
     stage_levels(lt, shapes, level_start, d);
     // With W > 1 everywhere and at least two pixels, base + column step is always valid memory.
-    __shared__ int2 stage_a[NWARPS][32];
-    __shared__ int stage_dx[NWARPS][32];
-    __shared__ float4 stage_b[NWARPS][32];
+    __shared__ int2 stage_a[NWARPS][record_count(GS)];
+    __shared__ int stage_dx[NWARPS][record_count(GS)];
+    __shared__ float4 stage_b[NWARPS][record_count(GS)];
     const int warp = threadIdx.x >> 5;
     if (lt.min_w > 1)
         forward_items<VT, AT, VEC, GS, NWARPS, true, FUSED>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc,
