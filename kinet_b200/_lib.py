@@ -3,6 +3,7 @@
 The library is the product; there is no fallback.  If it is missing, or a call
 fails, this module raises -- it never routes around the CUDA kernels.
 """
+import contextlib
 import ctypes
 import os
 
@@ -69,6 +70,22 @@ def load():
         raise RuntimeError("kinet_b200: libmsda_b200.so ABI version mismatch")
     _lib = lib
     return lib
+
+
+_NO_GUARD = contextlib.nullcontext()
+
+
+def raw_stream(device):
+    """cudaStream_t (as int) of torch's current stream on `device`: one C call, no Stream object."""
+    try:
+        return torch._C._cuda_getCurrentRawStream(device.index)
+    except AttributeError:          # older / newer torch without the private accessor
+        return torch.cuda.current_stream(device).cuda_stream
+
+
+def device_guard(device):
+    """Kernels launch on the CUDA runtime's current device: switch only when it is not `device`."""
+    return _NO_GUARD if device.index == torch.cuda.current_device() else torch.cuda.device(device)
 
 
 def dtype_code(dtype):

@@ -80,7 +80,8 @@ def _prep(value, spatial_shapes, level_start_index, sampling_loc, attn_weight):
 
 
 def _ptr(t):
-    return ctypes.c_void_p(t.data_ptr()) if t is not None and t.numel() > 0 else ctypes.c_void_p(0)
+    # plain ints: the argtypes declared in _lib.load() convert them (None -> NULL)
+    return t.data_ptr() if t is not None and t.numel() > 0 else None
 
 
 def ms_deform_attn_forward(value, spatial_shapes, sampling_loc, attn_weight, im2col_step,
@@ -91,11 +92,10 @@ def ms_deform_attn_forward(value, spatial_shapes, sampling_loc, attn_weight, im2
     aux, loc, attn, shapes, lsi = _prep(value, spatial_shapes, level_start_index, sampling_loc, attn_weight)
     dims = _dims(value, loc)
     out = torch.empty((dims.N, dims.Lq, dims.M * dims.D), dtype=value.dtype, device=value.device)
-    with torch.cuda.device(value.device):
-        stream = torch.cuda.current_stream().cuda_stream
+    with _lib.device_guard(value.device):
         rc = lib.msda_b200_forward(_ptr(value), _lib.dtype_code(value.dtype), _ptr(shapes), _ptr(lsi),
                                    _ptr(loc), _ptr(attn), _lib.dtype_code(aux), _ptr(out),
-                                   ctypes.byref(dims), ctypes.c_void_p(stream))
+                                   ctypes.byref(dims), _lib.raw_stream(value.device))
     _lib.check(rc, "ms_deform_attn_forward")
     return out
 
@@ -117,12 +117,11 @@ def ms_deform_attn_backward(value, spatial_shapes, sampling_loc, attn_weight, gr
     vcode = _lib.dtype_code(value.dtype)
     ws_bytes = int(lib.msda_b200_backward_workspace_bytes(vcode, ctypes.byref(dims)))
     ws = torch.empty(ws_bytes // 4, dtype=torch.float32, device=value.device) if ws_bytes else None
-    with torch.cuda.device(value.device):
-        stream = torch.cuda.current_stream().cuda_stream
+    with _lib.device_guard(value.device):
         rc = lib.msda_b200_backward(_ptr(value), vcode, _ptr(shapes), _ptr(lsi), _ptr(loc), _ptr(attn),
                                     _lib.dtype_code(aux), _ptr(go), _ptr(grad_value), _ptr(grad_loc),
-                                    _ptr(grad_attn), _ptr(ws), ctypes.c_size_t(ws_bytes),
-                                    ctypes.byref(dims), ctypes.c_void_p(stream))
+                                    _ptr(grad_attn), _ptr(ws), ws_bytes,
+                                    ctypes.byref(dims), _lib.raw_stream(value.device))
     _lib.check(rc, "ms_deform_attn_backward")
     if grad_loc.dtype != sampling_loc.dtype:
         grad_loc = grad_loc.to(sampling_loc.dtype)
@@ -244,10 +243,10 @@ class MSDeformAttnFusedFunction(Function):
                                         query_attn_mask)
         dims = _lib.MsdaDims(N, S, M, D, L, Lq, P)
         out = torch.empty((N, Lq, M * D), dtype=value.dtype, device=value.device)
-        with torch.cuda.device(value.device):
+        with _lib.device_guard(value.device):
             rc = lib.msda_b200_forward_fused(_ptr(value), _lib.dtype_code(value.dtype), _ptr(shapes), None,
                                              ctypes.byref(args), _lib.dtype_code(aux), _ptr(out), ctypes.byref(dims),
-                                             ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+                                             _lib.raw_stream(value.device))
         _lib.check(rc, "msda_b200_forward_fused")
         ctx.save_for_backward(value, shapes, reference_points, sampling_offsets, attention_logits,
                               query_attn_mask if query_attn_mask is not None else torch.empty(0),
@@ -277,12 +276,11 @@ class MSDeformAttnFusedFunction(Function):
         vcode = _lib.dtype_code(value.dtype)
         ws_bytes = int(lib.msda_b200_backward_workspace_bytes(vcode, ctypes.byref(dims)))
         ws = torch.empty(ws_bytes // 4, dtype=torch.float32, device=value.device) if ws_bytes else None
-        with torch.cuda.device(value.device):
+        with _lib.device_guard(value.device):
             rc = lib.msda_b200_backward_fused(_ptr(value), vcode, _ptr(shapes), None, ctypes.byref(args),
                                               _lib.dtype_code(aux), _ptr(go), _ptr(grad_value), _ptr(grad_off),
-                                              _ptr(grad_logit), _ptr(grad_loc), _ptr(ws), ctypes.c_size_t(ws_bytes),
-                                              ctypes.byref(dims),
-                                              ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+                                              _ptr(grad_logit), _ptr(grad_loc), _ptr(ws), ws_bytes,
+                                              ctypes.byref(dims), _lib.raw_stream(value.device))
         _lib.check(rc, "msda_b200_backward_fused")
         grad_ref = None
         if need_ref:
