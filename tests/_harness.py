@@ -123,10 +123,19 @@ class Stack(nn.Module):
             if isinstance(m, SwitchableMSDeformAttn):
                 m.core = core
 
+    def _geometry(self, N, device):
+        # built once per (batch, device): constant inputs must not be re-created (and copied from the
+        # host) inside a CUDA-graph capture, and the modules validate a shapes tensor once per object
+        key = (N, str(device))
+        if getattr(self, "_geo_key", None) != key:
+            self._geo = (torch.as_tensor(self.levels, dtype=torch.long, device=device),
+                         encoder_reference_points(self.levels, N, device).contiguous())
+            self._geo_key = key
+        return self._geo
+
     def forward(self, src, pos):
         N, S, d = src.shape
-        shapes = torch.as_tensor(self.levels, dtype=torch.long, device=src.device)
-        ref = encoder_reference_points(self.levels, N, src.device).contiguous()
+        shapes, ref = self._geometry(N, src.device)
         mem = src
         for layer in self.enc:
             mem = layer(mem, pos, ref, shapes)
