@@ -87,3 +87,11 @@ def test_extension_module_name_shim():
         MSDA.ms_deform_attn_forward(v, shapes, loc, attn, 64)
     with pytest.raises(TypeError):
         MSDA.ms_deform_attn_forward(v, shapes, loc)
+
+
+def test_graft_entry_build_returns():
+    """build() must return to its caller (an earlier version ended in sys.exit via runpy)."""
+    import __graft_entry__ as g
+    g.build()
+    from kinet_b200 import _lib
+    assert _lib.load() is not None
