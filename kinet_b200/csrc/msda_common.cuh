@@ -27,21 +27,15 @@ constexpr int kMaxLevels = MSDA_MAX_LEVELS;
 struct LevelTable {
     int H[kMaxLevels];
     int W[kMaxLevels];
-    int start[kMaxLevels];       // first pixel of the level in the flattened pyramid
-    int tiles_x[kMaxLevels];     // 2-D tiling (encoder form): tiles per row
-    int tiles_y[kMaxLevels];     // 2-D tiling: tile rows of the level
-    int tile_begin[kMaxLevels];  // 2-D tiling: first tile id of the level
-    int total_tiles;
+    int start[kMaxLevels];       // first pixel of the level in the flattened pyramid (value rows)
+    int qstart[kMaxLevels + 1];  // encoder form: first query of the level (prefix sums of H*W)
     int min_w;                   // smallest level width (W == 1 levels need a per-sample column step)
 };
 
 struct KernelDims {
     int N, S, M, D, L, Lq, P;
-    int tile_q;   // queries per tile (1-D tiling) == tile_h * tile_w (2-D tiling)
-    int tile_h;   // 2-D tiling: tile height; 0 selects 1-D tiling over the query index
-    int tile_w;
-    int split;    // WorkSplit mode: 0 round-robin whole items, 1 contiguous unit ranges, 2 (default) round-robin + cut last round
-    int balanced; // 2-D tiling: balanced tile edges (default) instead of full tiles + ragged border
+    int tile_q;   // query rows per work item
+    int band_h;   // encoder form (Lq == S): rows of a band of the band-ordered query walk; 0: plain query order
 };
 
 // Fills the level table (all threads call; ends with __syncthreads()).
@@ -50,116 +44,45 @@ __device__ __forceinline__ void stage_levels(LevelTable& t, const int64_t* __res
                                              const KernelDims& d)
 {
     if (threadIdx.x == 0) {
-        int run = 0, trun = 0, min_w = 1 << 30;
+        int run = 0, min_w = 1 << 30;
         for (int l = 0; l < d.L; ++l) {
             const int H = (int)shapes[2 * l], W = (int)shapes[2 * l + 1];
             t.H[l] = H;
             t.W[l] = W;
             t.start[l] = level_start ? (int)level_start[l] : run;
+            t.qstart[l] = run;
             run += H * W;
             min_w = min(min_w, W);
-            if (d.tile_h > 0) {
-                const int tx = (W + d.tile_w - 1) / d.tile_w;
-                const int ty = (H + d.tile_h - 1) / d.tile_h;
-                t.tiles_x[l] = tx;
-                t.tiles_y[l] = ty;
-                t.tile_begin[l] = trun;
-                trun += tx * ty;
-            }
         }
+        t.qstart[d.L] = run;
         t.min_w = min_w;
-        t.total_tiles = d.tile_h > 0 ? trun : (d.Lq + d.tile_q - 1) / d.tile_q;
     }
     __syncthreads();
 }
 
-// A decoded query tile: `count` valid queries, enumerated densely (no empty slots for ragged
-// border tiles): query(i) = origin + (i / vw) * pitch + (i % vw).
-struct TileInfo {
-    int origin;   // query index of the tile's first query
-    int vw;       // valid width of the tile (1-D tiling: count)
-    int pitch;    // query-index step between tile rows (level width; 1-D tiling: 0)
-    int count;    // number of valid queries
-};
-
-__device__ __forceinline__ TileInfo decode_tile(const LevelTable& t, const KernelDims& d, int tile)
+// Work items.  An item is (chunk of tile_q consecutive positions of the query walk, batch, head); item
+// ids run head-fastest, so the CTAs in flight at any time cover all heads of the same few chunks, whose
+// loc / attn / grad rows are contiguous in DRAM.  ONE ITEM PER CTA, and several times more CTAs than
+// resident slots: the hardware's CTA scheduler hands out items as SMs free up.  The SMs do not run at
+// the same speed (profiles/r1k_per_sm_finish_times.txt: with equal static shares the same dozen SMs
+// finish 15-20 % late in every run), so equal shares make the kernel as slow as its slowest SM.
+//
+// Encoder form: the walk visits the pixels of a level band by band (band_h rows), column by column
+// inside a band, so tile_q consecutive positions are a band_h x (tile_q / band_h) patch of one level --
+// the gather footprint of an item is compact and stays in L1 -- while the number of items depends only
+// on Lq (the host never needs the level shapes, which live in device memory).
+__device__ __forceinline__ int walk_query(const LevelTable& t, const KernelDims& d, int pos)
 {
-    TileInfo ti;
-    if (d.tile_h == 0) {
-        ti.origin = tile * d.tile_q;
-        ti.count = min(d.tile_q, d.Lq - ti.origin);
-        ti.vw = max(ti.count, 1);
-        ti.pitch = 0;
-        return ti;
-    }
+    if (d.band_h == 0) return pos;
     int l = 0;
-    while (l + 1 < d.L && tile >= t.tile_begin[l + 1]) ++l;
-    const int rel = tile - t.tile_begin[l];
-    const int ty = rel / t.tiles_x[l], tx = rel - ty * t.tiles_x[l];
-    // balanced edges: the level is cut into tiles_x * tiles_y near-equal tiles (each at most
-    // tile_w x tile_h) instead of full tiles plus a thin ragged border, so work items weigh the same
-    int x0, x1, y0, y1;
-    if (d.balanced) {
-        x0 = tx * t.W[l] / t.tiles_x[l]; x1 = (tx + 1) * t.W[l] / t.tiles_x[l];
-        y0 = ty * t.H[l] / t.tiles_y[l]; y1 = (ty + 1) * t.H[l] / t.tiles_y[l];
-    } else {
-        x0 = tx * d.tile_w; x1 = min(x0 + d.tile_w, t.W[l]);
-        y0 = ty * d.tile_h; y1 = min(y0 + d.tile_h, t.H[l]);
-    }
-    ti.vw = x1 - x0;
-    const int vh = y1 - y0;
-    ti.pitch = t.W[l];
-    ti.origin = t.start[l] + y0 * t.W[l] + x0;
-    ti.count = ti.vw * vh;
-    return ti;
-}
-
-// Static split of one launch over the CTAs of the persistent grid.  The unit is one pass of a CTA over
-// a tile (`pass_rows` query rows); every work item (tile, batch, head) counts as ppt =
-// ceil(tile_q / pass_rows) units.  Whole items are dealt round-robin (item i -> CTA i mod grid: the CTAs
-// running at the same time then cover all heads of the same few tiles, whose loc / attn / grad rows are
-// contiguous in DRAM) for as many full rounds as there are; the items of the last, partial round are
-// cut at pass granularity into grid equal shares.  Without the cut a CTA gets floor or ceil of
-// items/grid whole items (C3-enc, N=1: 2.65 -> 2 or 3; ncu showed the SMs idle 34 % of the kernel).
-struct WorkSplit {
-    int r, rr_end, stride;   // round-robin part
-    int base, u, u_end;      // pass-granular part: units [u, u_end) of the items from `base` on
-    int ppt;
-
-    __device__ __forceinline__ void init(int items, const KernelDims& d, int pass_rows)
-    {
-        ppt = (d.tile_q + pass_rows - 1) / pass_rows;
-        const int G = (int)gridDim.x, b = (int)blockIdx.x;
-        rr_end = d.split == 0 ? items : (d.split == 1 ? 0 : items / G * G);
-        r = b;
-        stride = G;
-        base = rr_end;
-        const long long units = (long long)(items - base) * ppt;
-        u = (int)(units * b / G);
-        u_end = (int)(units * (b + 1) / G);
-    }
-    // -> false when the CTA is out of work; otherwise passes [p0, p1) of `item`
-    __device__ __forceinline__ bool next(int& item, int& p0, int& p1)
-    {
-        if (r < rr_end) {
-            item = r; p0 = 0; p1 = ppt;
-            r += stride;
-            return true;
-        }
-        if (u >= u_end) return false;
-        const int it = u / ppt;
-        p0 = u - it * ppt;
-        p1 = min(ppt, p0 + (u_end - u));
-        u += p1 - p0;
-        item = base + it;
-        return true;
-    }
-};
-
-__device__ __forceinline__ int tile_query(const TileInfo& ti, int i)
-{
-    const int iy = i / ti.vw;
-    return ti.origin + iy * ti.pitch + (i - iy * ti.vw);
+    while (l + 1 < d.L && pos >= t.qstart[l + 1]) ++l;
+    const int W = t.W[l], H = t.H[l];
+    const int r = pos - t.qstart[l];
+    const int band = r / (d.band_h * W);
+    const int rr = r - band * d.band_h * W;
+    const int hb = min(d.band_h, H - band * d.band_h);   // the last band of a level may be lower
+    const int ix = rr / hb, iy = rr - ix * hb;
+    return t.qstart[l] + (band * d.band_h + iy) * W + ix;
 }
 
 // ---- element conversion -------------------------------------------------------------

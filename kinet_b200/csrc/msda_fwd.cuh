@@ -55,22 +55,20 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_
     const bool lane_used = grp < GPW;
     const int LP = d.L * d.P;
     const int rsv = d.M * GS;              // vectors between neighbouring pixels
-    const int items = lt.total_tiles * d.N * d.M;
-
+    const int chunks = (d.Lq + d.tile_q - 1) / d.tile_q;
+    const int items = chunks * d.N * d.M;
     constexpr int PASS = NWARPS * GPW;     // query rows per CTA pass
-    WorkSplit ws;
-    ws.init(items, d, PASS);
 
-    for (int item, p0, p1; ws.next(item, p0, p1);) {
-        const int tile = item / (d.N * d.M);
-        const int bm = item - tile * (d.N * d.M);
+    for (int item = blockIdx.x; item < items; item += gridDim.x) {   // one item per CTA (grid == items)
+        const int chunk = item / (d.N * d.M);
+        const int bm = item - chunk * (d.N * d.M);
         const int b = bm / d.M, m = bm - b * d.M;
         const VT* lane_base = value + ((size_t)b * d.S * d.M + m) * D + gl * VEC;
 
-        const TileInfo ti = decode_tile(lt, d, tile);
-        const int i_end = min(ti.count, p1 * PASS);
-        for (int i0 = p0 * PASS + warp * GPW; i0 < i_end; i0 += PASS) {
-            const int q = (lane_used && i0 + grp < ti.count) ? tile_query(ti, i0 + grp) : -1;
+        const int pos0 = chunk * d.tile_q;
+        const int count = min(d.tile_q, d.Lq - pos0);
+        for (int i0 = warp * GPW; i0 < count; i0 += PASS) {
+            const int q = (lane_used && i0 + grp < count) ? walk_query(lt, d, pos0 + i0 + grp) : -1;
             const bool row_ok = q >= 0;
             const size_t rowq = (size_t)b * d.Lq + (row_ok ? q : 0);
             const size_t row = rowq * d.M + m;

@@ -69,38 +69,35 @@ inline int check_common(const void* value, const int64_t* shapes, const void* lo
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
-// Tiling choice.  Encoder form (Lq == S: queries are the pyramid's pixels, whose
-// samples cluster around the query's own position): 2-D tiles per level so the
-// gather footprint of one CTA is a compact patch.  Otherwise 1-D tiles over the
-// query index, sized so the grid still covers every SM.
-inline KernelDims make_dims(const msda_dims* d, int rows_per_pass)
+// Work items (see walk_query in msda_common.cuh).  Encoder form (Lq == S: the queries are the pyramid's
+// pixels and their samples cluster around the query's own position): band-ordered walk, so an item is a
+// compact band_h x (tile_q / band_h) patch.  Otherwise plain query order.  The item length trades the
+// scheduling tail (one item per CTA, handed out by the hardware as SMs free up: shorter items, shorter
+// tail) against the per-CTA prologue; it shrinks further when there are too few items to cover every SM.
+constexpr int kForwardTileQ = 128;
+constexpr int kBackwardTileQ = 128;
+
+inline KernelDims make_dims(const msda_dims* d, int rows_per_pass, int default_tile_q)
 {
     KernelDims k;
     k.N = d->N; k.S = d->S; k.M = d->M; k.D = d->D; k.L = d->L; k.Lq = d->Lq; k.P = d->P;
-    k.split = env_int("MSDA_B200_SPLIT", 2);
-    k.balanced = env_int("MSDA_B200_BALANCED", 1);
     const int sms = device_info().sms > 0 ? device_info().sms : 148;
-    const int force_1d = env_int("MSDA_B200_TILE_1D", 0);
-    if (d->Lq == d->S && !force_1d) {
-        k.tile_h = env_int("MSDA_B200_TILE_H", 8);
-        k.tile_w = env_int("MSDA_B200_TILE_W", 32);
-        k.tile_q = k.tile_h * k.tile_w;
-    } else {
-        k.tile_h = 0; k.tile_w = 0;
-        int tq = env_int("MSDA_B200_TILE_Q", 0);
-        if (tq <= 0) {
-            tq = 256;
-            // shrink until there are at least ~4 items per SM (or one pass per item)
-            while (tq > rows_per_pass &&
-                   (long long)d->N * d->M * ((d->Lq + tq - 1) / tq) < 4ll * sms)
-                tq >>= 1;
-            if (tq < rows_per_pass) tq = rows_per_pass;
-        }
-        k.tile_q = tq;
+    k.band_h = (d->Lq == d->S && !env_int("MSDA_B200_TILE_1D", 0)) ? env_int("MSDA_B200_TILE_H", 8) : 0;
+    if (k.band_h < 0) k.band_h = 0;
+    int tq = env_int("MSDA_B200_TILE_Q", 0);
+    if (tq <= 0) {
+        tq = default_tile_q;
+        // shrink until there are at least ~4 items per SM (or one pass per item)
+        while (tq > rows_per_pass && (long long)d->N * d->M * ((d->Lq + tq - 1) / tq) < 4ll * sms) tq >>= 1;
+        // whole passes: a ragged last pass leaves warps of the CTA without rows (D = 36: 24 rows per pass)
+        tq = tq / rows_per_pass * rows_per_pass;
     }
+    if (tq < rows_per_pass) tq = rows_per_pass;
+    k.tile_q = tq;
     return k;
 }
 
+// Generic kernels: a persistent grid of warps striding over the rows.
 template <typename Kern>
 int query_occupancy(Kern kern, int threads)
 {
@@ -109,30 +106,20 @@ int query_occupancy(Kern kern, int threads)
     return occ < 1 ? 1 : occ;
 }
 
-// Persistent grid: one wave of resident CTAs (or fewer when there is less work).
 inline int persistent_grid(int occ, long long items_upper)
 {
-    const int cap = env_int("MSDA_B200_CTAS_PER_SM", 0);
-    if (cap > 0 && cap < occ) occ = cap;
     const int sms = device_info().sms > 0 ? device_info().sms : 148;
     long long g = (long long)sms * occ;
     if (items_upper < g) g = items_upper;
     return (int)(g < 1 ? 1 : g);
 }
 
-// Upper bound of the number of work items without knowing the level shapes on the
-// host (they live in device memory): 2-D tiling adds at most one ragged tile row
-// and column per level, bounded by S/tile + (S/tile_w + S/tile_h + 1) per level;
-// the kernel loops `item < items` with the exact count, so a loose bound only
-// means a few idle CTAs.
-inline long long items_upper_bound(const KernelDims& k)
+// One CTA per item; gridDim.x is capped only by what the hardware accepts (the kernels stride).
+inline int item_grid(const KernelDims& k)
 {
-    long long tiles;
-    if (k.tile_h > 0)
-        tiles = (long long)k.S / k.tile_q + (long long)k.L * ((long long)k.S / k.tile_w + (long long)k.S / k.tile_h + 1);
-    else
-        tiles = (k.Lq + k.tile_q - 1) / k.tile_q;
-    return tiles * k.N * k.M;
+    const long long items = (long long)((k.Lq + k.tile_q - 1) / k.tile_q) * k.N * k.M;
+    const long long cap = 1ll << 30;
+    return (int)(items < 1 ? 1 : (items > cap ? cap : items));
 }
 
 // fa == nullptr: loc / attn are materialised sampling locations / attention weights;
@@ -142,10 +129,9 @@ int launch_forward_vec_impl(const void* value, const int64_t* shapes, const int6
                             const void* attn, void* out, const msda_dims* d, cudaStream_t st, const FusedArgs& fa)
 {
     constexpr int NW = 8;
-    KernelDims k = make_dims(d, NW * (32 / GS));
+    const KernelDims k = make_dims(d, NW * (32 / GS), kForwardTileQ);
     auto kern = msda_forward_kernel<VT, AT, VEC, GS, NW, FUSED>;
-    static const int occ = query_occupancy(kern, NW * 32);   // once per instantiation
-    const int grid = persistent_grid(occ, items_upper_bound(k));
+    const int grid = item_grid(k);
     {
         TraceScope trace(st);
         kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
@@ -171,8 +157,8 @@ int launch_forward_generic(const void* value, const int64_t* shapes, const int64
                            const void* loc, const void* attn, void* out, const msda_dims* d,
                            cudaStream_t st)
 {
-    KernelDims k = make_dims(d, 8);
-    k.tile_h = 0; k.tile_w = 0; k.tile_q = 8;
+    KernelDims k = make_dims(d, 8, 8);
+    k.band_h = 0; k.tile_q = 8;
     const long long rows = (long long)d->N * d->Lq * d->M;
     auto kern = msda_forward_generic_kernel<VT, AT, ACC>;
     static const int occ = query_occupancy(kern, 256);
@@ -217,10 +203,9 @@ int launch_backward_vec_impl(const void* value, const int64_t* shapes, const int
                              const msda_dims* d, cudaStream_t st, const FusedArgs& fa)
 {
     constexpr int NW = 8;
-    KernelDims k = make_dims(d, NW * (32 / GS));
+    const KernelDims k = make_dims(d, NW * (32 / GS), kBackwardTileQ);
     auto kern = msda_backward_kernel<VT, AT, VEC, GS, NW, FUSED>;
-    static const int occ = query_occupancy(kern, NW * 32);   // once per instantiation
-    const int grid = persistent_grid(occ, items_upper_bound(k));
+    const int grid = item_grid(k);
     {
         TraceScope trace(st);
         kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
@@ -248,8 +233,8 @@ int launch_backward_generic(const void* value, const int64_t* shapes, const int6
                             const void* loc, const void* attn, const void* go, ACC* gv_acc,
                             void* gl, void* ga, const msda_dims* d, cudaStream_t st)
 {
-    KernelDims k = make_dims(d, 8);
-    k.tile_h = 0; k.tile_w = 0; k.tile_q = 8;
+    KernelDims k = make_dims(d, 8, 8);
+    k.band_h = 0; k.tile_q = 8;
     const long long rows = (long long)d->N * d->Lq * d->M;
     auto kern = msda_backward_generic_kernel<VT, AT, ACC>;
     static const int occ = query_occupancy(kern, 256);
