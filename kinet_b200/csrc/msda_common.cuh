@@ -5,8 +5,8 @@
 // shift x = loc_x*W - 0.5 (:227-228), open sample window -1 < x < W (:229),
 // zero contribution from corners outside [0,W-1]x[0,H-1] (:24-67).
 // Nothing here is derived from that file's code; it is a new design:
-//   * a CTA owns one (batch, head) pair and a tile of queries, so the gather
-//     footprint of a tile (one head's 64/128-byte rows) stays L1-resident;
+//   * a CTA owns one (batch, head) pair and a compact patch of queries, so the gather
+//     footprint of the patch (one head's 64/128-byte rows) stays L1-resident;
 //   * a group of GS lanes owns one (query, head) row, each lane VEC channels
 //     (16-byte loads: fp32x4 / bf16x8), several rows per warp;
 //   * spatial shapes / level starts are staged in shared memory by the CTA

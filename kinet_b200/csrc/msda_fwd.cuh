@@ -5,7 +5,7 @@
 // kernel that gathers, interpolates, weights and reduces in registers and writes
 // every output element exactly once.
 //
-// Mapping.  A CTA loops (persistently) over work items (query tile, batch, head).
+// Mapping.  A CTA handles one work item (chunk of the query walk, batch, head; see walk_query).
 // Inside an item a group of GS lanes owns one (query, head) row; each lane owns
 // VEC consecutive channels and issues one 16-byte load per bilinear corner, so a
 // warp-wide load instruction touches 32/GS distinct rows.  Sample metadata
