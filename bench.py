@@ -41,8 +41,8 @@ ENC_TAG, DEC_TAG, LAYERS = "C2_enc", "C2_dec", 6
 METRIC, UNIT = "msda_fwd_bwd_GBps", "GB/s"
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from the committed
 # `ncu --set full` capture (bench.py never runs under a profiler, so this is a recorded measurement)
-ENC_BWD_DRAM_TRAFFIC = 210.9e6 + 97.2e6
-ENC_BWD_DRAM_TRAFFIC_SRC = "profiles/r1j_ncu_full_C2enc_bf16.txt"
+ENC_BWD_DRAM_TRAFFIC = 218.9e6 + 104.9e6
+ENC_BWD_DRAM_TRAFFIC_SRC = "profiles/r1l_ncu_full_C2enc_bf16.txt"
 # the same kernel against the unit that actually binds it: every sample adds 4 corner rows of D fp32
 # channels into grad_value (upper bound: zero-weight border corners are skipped)
 SCATTER_BYTES = 2 * 22223 * 8 * 16 * 4 * 32 * 4
