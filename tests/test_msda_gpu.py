@@ -161,11 +161,38 @@ def test_fp64_generic_matches_oracle():
 
 
 def test_encoder_form_2d_tiling_matches_oracle():
-    """Lq == S switches the kernels to 2-D query tiles; result must not depend on the tiling."""
+    """Lq == S switches the kernels to the band-ordered query walk; the result must not depend on it."""
     dev = _dev()
     levels = [(37, 45), (19, 23), (10, 12), (5, 6)]
     S = sum(h * w for h, w in levels)
     value, shapes, loc, attn, go = _random_case(dev, 2, 8, 32, S, levels, 4, spread=1.1)
+    out, grads = _run_cuda(value, shapes, loc, attn, go)
+    ref_out, ref_grads = _oracle64(value, shapes, loc, attn, go)
+    assert _relerr(out.cpu().numpy(), ref_out) <= 1e-5
+    _check_grads(grads, ref_grads, shapes, loc, 1e-5)
+
+
+WALK_CASES = [
+    # (levels, D, {launcher switches}): the encoder form walks each level band by band; every query must be
+    # visited exactly once whatever the band height, the item length and the level shapes
+    ([(37, 45), (19, 23), (10, 12), (5, 6)], 32, {}),
+    ([(9, 1), (1, 7), (3, 3), (1, 1)], 32, {}),                                  # W == 1, H == 1, 1x1 levels
+    ([(13, 21), (7, 11)], 36, {}),                                               # 24-row passes (D = 36)
+    ([(13, 21), (7, 11)], 32, {"MSDA_B200_TILE_H": "3", "MSDA_B200_TILE_Q": "40"}),
+    ([(13, 21), (7, 11)], 32, {"MSDA_B200_TILE_H": "16", "MSDA_B200_TILE_Q": "1000"}),
+    ([(13, 21), (7, 11)], 64, {"MSDA_B200_TILE_H": "1"}),
+    ([(13, 21), (7, 11)], 16, {"MSDA_B200_TILE_1D": "1"}),
+]
+
+
+@pytest.mark.parametrize("case", WALK_CASES)
+def test_encoder_walk_covers_every_query(case, monkeypatch):
+    levels, D, env = case
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    dev = _dev()
+    S = sum(h * w for h, w in levels)
+    value, shapes, loc, attn, go = _random_case(dev, 2, 8, D, S, levels, 4, spread=1.1, seed=5)
     out, grads = _run_cuda(value, shapes, loc, attn, go)
     ref_out, ref_grads = _oracle64(value, shapes, loc, attn, go)
     assert _relerr(out.cpu().numpy(), ref_out) <= 1e-5
