@@ -14,8 +14,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libmsda_b200.so")
-SOURCES = ["msda_abi.cu", "msda_inst_f32.cu", "msda_inst_bf16.cu", "msda_inst_f16.cu", "msda_enc.cu"]
-HEADERS = ["msda_common.cuh", "msda_fwd.cuh", "msda_bwd.cuh", "msda_launch.cuh", "msda_enc.cuh",
+SOURCES = ["msda_abi.cu", "msda_inst_f32.cu", "msda_inst_bf16.cu", "msda_inst_f16.cu"]
+HEADERS = ["msda_common.cuh", "msda_fwd.cuh", "msda_bwd.cuh", "msda_launch.cuh",
            os.path.join("..", "..", "include", "msda_b200.h")]
 
 NVCC_FLAGS = [
