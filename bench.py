@@ -338,6 +338,22 @@ def reduce_max(values, device, world):
     return [float(x) for x in t.tolist()]
 
 
+def bind_to_gpu_numa_node(index):
+    """Pin this process to the CPU cores next to its GPU before any pinned host buffer is allocated, so
+    the e2e leg's host buffers sit on the GPU's NUMA node (with N ranks on one box, buffers on the wrong
+    socket turn every copy into inter-socket traffic).  Returns what was done, for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        p = torch.cuda.get_device_properties(index)     # NVML order != CUDA order under CUDA_VISIBLE_DEVICES
+        bus_id = "%08x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bus_id.encode())
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        return "cpus near gpu %d (%d cores)" % (index, len(os.sched_getaffinity(0)))
+    except Exception as e:      # no NVML / not permitted: keep the default placement
+        return "default (%s)" % type(e).__name__
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -376,6 +392,8 @@ def main():
                          "(use --impl reference for the CPU baseline)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # N = 1 keeps every core: the cpu_baseline leg of that run uses all host threads
+    config["host_affinity"] = bind_to_gpu_numa_node(local) if world > 1 else "all cores (single rank)"
     if world > 1:
         torch.distributed.init_process_group("nccl", device_id=dev)
     r = run_ours(args, rank, world, dev)
