@@ -82,7 +82,8 @@ __device__ __forceinline__ int walk_query(const LevelTable& t, const KernelDims&
     const int rr = r - band * d.band_h * W;
     const int hb = min(d.band_h, H - band * d.band_h);   // the last band of a level may be lower
     const int ix = rr / hb, iy = rr - ix * hb;
-    return t.qstart[l] + (band * d.band_h + iy) * W + ix;
+    const int q = t.qstart[l] + (band * d.band_h + iy) * W + ix;
+    return q < d.Lq ? q : -1;   // only if the shapes do not add up to S (caller error): drop, never write out of range
 }
 
 // ---- element conversion -------------------------------------------------------------

@@ -1,5 +1,5 @@
-// msda_launch.cuh -- host-side launchers: kernel selection from (dtype, D), tiling choice and
-// persistent grid sizing.  Included by msda_abi.cu (entry points) and by the msda_inst_*.cu files,
+// msda_launch.cuh -- host-side launchers: kernel selection from (dtype, D), work-item length and
+// grid sizing.  Included by msda_abi.cu (entry points) and by the msda_inst_*.cu files,
 // which hold the explicit instantiations so the dtype families compile in parallel.
 #pragma once
 #include <cstdlib>
