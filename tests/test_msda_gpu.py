@@ -495,3 +495,36 @@ def test_module_fused_and_unfused_agree_under_autocast():
             else:
                 assert _relerr(a.cpu().numpy(), b.cpu().numpy()) <= 1e-4, name
     m.fused_prologue = True
+
+
+def test_concurrent_threads_and_streams():
+    """Boundary row "streams / threading" (SURVEY.md 8(b)): the library keeps no mutable state shared between
+    callers, ctypes releases the GIL around the calls, and every launch goes to the caller's stream -- two
+    Python threads driving two streams at once get the same results as running alone."""
+    import threading
+    dev = _dev()
+    cases = [_random_case(dev, 2, 8, 32, 700, [(20, 30), (10, 10)], 4, seed=s) for s in (1, 2)]
+    want = [_run_cuda(*c) for c in cases]
+    got, errs = [None, None], []
+
+    def worker(i):
+        try:
+            s = torch.cuda.Stream()
+            with torch.cuda.stream(s):
+                for _ in range(20):
+                    res = _run_cuda(*cases[i])
+            s.synchronize()
+            got[i] = res
+        except Exception as e:          # surfaced below: an exception in a thread does not fail the test by itself
+            errs.append(e)
+
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(2)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errs, errs
+    for (out, grads), (wout, wgrads) in zip(got, want):
+        assert torch.equal(out, wout)
+        assert torch.equal(grads[1], wgrads[1]) and torch.equal(grads[2], wgrads[2])
+        assert _relerr(grads[0].cpu().numpy(), wgrads[0].cpu().numpy()) <= 1e-5     # atomics: order varies
