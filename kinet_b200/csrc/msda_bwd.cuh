@@ -98,7 +98,7 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
             const bool row_ok = q >= 0;
             const size_t rowq = (size_t)b * d.Lq + (row_ok ? q : 0);
             const size_t row = rowq * d.M + m;
-            SampleSrc<AT, FUSED> src;
+            SampleSrc<AT, FUSED, 4> src;
             src.template begin<GS, CH>(loc, attn, fa, d, row, rowq, row_ok, gl, grp_base);
             float ga_keep[MAXCH] = {0.f, 0.f, 0.f, 0.f};   // fused: d out / d attention of this lane's samples
             float dot = 0.f;                                // fused: sum_s prob_s * d out / d attention_s

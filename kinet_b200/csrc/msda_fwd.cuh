@@ -75,7 +75,7 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_
             const bool row_ok = q >= 0;
             const size_t rowq = (size_t)b * d.Lq + (row_ok ? q : 0);
             const size_t row = rowq * d.M + m;
-            SampleSrc<AT, FUSED> src;
+            SampleSrc<AT, FUSED, 0> src;
             src.template begin<GS, CH>(loc, attn, fa, d, row, rowq, row_ok, gl, grp * GS);
 
             float acc[VEC];
