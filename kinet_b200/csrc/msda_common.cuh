@@ -443,6 +443,7 @@ template <typename AT, int PRE> struct SampleSrc<AT, true, PRE> {
     float e[kFusedMaxChunks];   // exp(logit - max) of this lane's samples gl, gl + CH, ... of the row (gl < CH)
     float inv_sum;       // 1 / sum of the row's numerators
     float sx, sy;        // d location / d offset of the last get() (backward)
+    float2 po[PRE > 0 ? PRE : 1];   // raw offsets of the first PRE chunks, loaded when the row starts (see above)
     bool masked;
     int ref_dim;
 
@@ -464,6 +465,11 @@ template <typename AT, int PRE> struct SampleSrc<AT, true, PRE> {
             const int s = c * CH + gl;
             e[c] = (row_ok && gl < CH && s < LP) ? load_attn<AT>(grow + s) : -INFINITY;
             m_ = fmaxf(m_, e[c]);
+        }
+#pragma unroll
+        for (int c = 0; c < PRE; ++c) {
+            const int s = c * CH + gl;
+            po[c] = (row_ok && gl < CH && s < LP) ? load_loc<AT>(orow + s * 2) : make_float2(0.f, 0.f);
         }
         const float mx = group_reduce<GS, MaxOp>(m_, gl, grp_base);
         float sum_ = 0.f;
@@ -488,7 +494,17 @@ template <typename AT, int PRE> struct SampleSrc<AT, true, PRE> {
     {
         lx = 0.f; ly = 0.f; a = 0.f; sx = 0.f; sy = 0.f;
         if (mine) {
-            const float2 o = load_loc<AT>(orow + s * 2);
+            float2 o;
+            if (PRE > 0 && c < PRE) {
+                o = po[0];
+#pragma unroll
+                for (int k = 1; k < PRE; ++k) {
+                    o.x = (c == k) ? po[k].x : o.x;
+                    o.y = (c == k) ? po[k].y : o.y;
+                }
+            } else {
+                o = load_loc<AT>(orow + s * 2);
+            }
             if (ref_dim == 2) {
                 const float2 r = *reinterpret_cast<const float2*>(rrow + ls * 2);
                 const float2 n = *reinterpret_cast<const float2*>(norm + ls * 2);
