@@ -508,15 +508,17 @@ template <typename AT, int PRE> struct SampleSrc<AT, true, PRE> {
             if (ref_dim == 2) {
                 const float2 r = *reinterpret_cast<const float2*>(rrow + ls * 2);
                 const float2 n = *reinterpret_cast<const float2*>(norm + ls * 2);
-                lx = r.x + o.x / n.x;
-                ly = r.y + o.y / n.y;
-                sx = 1.f / n.x; sy = 1.f / n.y;
+                // one reciprocal (MUFU.RCP, <= 1 ulp) instead of two IEEE divisions per sample: the divisor is
+                // a level size, the offset term moves by < 1e-6 px against the reference's offset / size
+                sx = __frcp_rn(n.x); sy = __frcp_rn(n.y);
+                lx = fmaf(o.x, sx, r.x);
+                ly = fmaf(o.y, sy, r.y);
             } else {
                 const float4 r = *reinterpret_cast<const float4*>(rrow + ls * 4);
-                const float p = (float)d.P;
-                lx = r.x + o.x / p * r.z * 0.5f;
-                ly = r.y + o.y / p * r.w * 0.5f;
-                sx = r.z * 0.5f / p; sy = r.w * 0.5f / p;
+                const float hp = 0.5f * __frcp_rn((float)d.P);
+                sx = r.z * hp; sy = r.w * hp;
+                lx = fmaf(o.x, sx, r.x);
+                ly = fmaf(o.y, sy, r.y);
             }
             a = masked ? 0.f : prob(c);
         }
