@@ -1,0 +1,94 @@
+#!/usr/bin/env python
+"""Tracking-configuration throughput of the transformer part (BASELINE.json configs[2], SURVEY.md C3 shapes):
+per frame one 6-layer MSDeformAttn encoder over the MOT17 pyramid (S = 20 906, d = 288 -> D = 36) and one
+6-layer decoder with 500 object + 60 track queries, bf16 autocast, forward only, recorded into ONE CUDA graph
+per GPU and replayed frame after frame.  Sequences are independent, so N GPUs run N replicas with no
+communication (engine.py:290-296 assigns sequences round-robin); frames/s is the sum over GPUs.
+The backbone, heads and the tracker's Python are the reference's and are not part of this number.
+
+    python tools/frames_bench.py [--frames 200]
+    python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 tools/frames_bench.py
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from _harness import Stack  # noqa: E402  (encoder/decoder stack around kinet_b200.MSDeformAttn)
+from kinet_b200.workloads import PYRAMIDS  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--frames", type=int, default=200)
+    ap.add_argument("--eager", action="store_true", help="no CUDA graph (launch-bound reference point)")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        torch.distributed.init_process_group("nccl", device_id=dev)
+    levels = PYRAMIDS["mot17_750x1333"]
+    S = sum(h * w for h, w in levels)
+    torch.manual_seed(rank)
+    model = Stack(levels, n_queries=560, d=288).to(dev).eval()
+    src = torch.randn(1, S, 288, device=dev)
+    pos = torch.randn(1, S, 288, device=dev) * 0.1
+    frames = [torch.randn(1, S, 288, device=dev) for _ in range(4)]   # stand-ins for the backbone's output
+
+    def frame():
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+            return model(src, pos)
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(3):
+            frame()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    if args.eager:
+        step = frame
+    else:
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            frame()
+        step = graph.replay
+
+    def run(n):
+        for i in range(n):
+            src.copy_(frames[i & 3], non_blocking=True)     # a new frame lands in the static input buffer
+            step()
+
+    run(10)
+    torch.cuda.synchronize()
+    if world > 1:
+        torch.distributed.barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    run(args.frames)
+    b.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([a.elapsed_time(b)], device=dev)
+    if world > 1:
+        torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)
+    if rank == 0:
+        ms = float(ms)
+        print(json.dumps({"metric": "tracking_transformer_frames_per_s", "value": world * args.frames / ms * 1e3,
+                          "n_gpus": world, "ms_per_frame_per_gpu": ms / args.frames, "frames_per_gpu": args.frames,
+                          "mode": "eager" if args.eager else "cuda_graph",
+                          "config": "MOT17 750x1333 pyramid, S=20906, d=288 (D=36), 6 enc + 6 dec layers, "
+                                    "560 queries, bf16 autocast, forward; replicas, no communication"}))
+    if world > 1:
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
