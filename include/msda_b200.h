@@ -116,7 +116,8 @@ int msda_b200_backward(const void *value, int value_dtype,
  * arithmetic and the softmax) and, when grad_sampling_loc != NULL, d out / d location in fp32
  * ([N][Lq][M][L][P][2]) from which the caller reduces the reference-point gradient.
  * Return MSDA_E_SHAPE = no fused kernel for this shape (D not in {16,32,36,64}, misaligned pointers, or
- * L*P > 4 * D/4 in the backward): run the prologue outside and call the plain entry points. */
+ * L*P > 4 * 2^floor(log2(D/4)) -- D/8 for the 16-bit forward): run the prologue outside and call the plain
+ * entry points. */
 typedef struct msda_fused_inputs {
     const void *sampling_offsets;     /* [N][Lq][M][L][P][2]  aux_dtype, raw Linear output */
     const void *attn_logits;          /* [N][Lq][M][L*P]      aux_dtype, before softmax */

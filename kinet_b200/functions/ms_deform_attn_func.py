@@ -196,8 +196,13 @@ def ms_deform_attn_core_pytorch(value, value_spatial_shapes, sampling_locations,
 def fused_supported(value, n_levels, n_points):
     """True when libmsda_b200 has a fused kernel for this call (else: run the prologue in PyTorch)."""
     D = value.shape[-1]
-    return (value.is_cuda and value.dtype in (torch.float32, torch.bfloat16, torch.float16)
-            and D in (16, 32, 36, 64) and n_levels * n_points <= 4 * (D // (4 if value.dtype == torch.float32 or D == 36 else 8)))
+    if not (value.is_cuda and value.dtype in (torch.float32, torch.bfloat16, torch.float16) and D in (16, 32, 36, 64)):
+        return False
+    # a lane keeps the softmax numerators of <= 4 samples of a row (kFusedMaxChunks, msda_common.cuh); samples
+    # are dealt to the first 2^k <= D/VEC lanes of the row's group, VEC = 8 only in the 16-bit forward
+    lanes = D // (4 if value.dtype == torch.float32 or D == 36 else 8)
+    owners = 1 << (lanes.bit_length() - 1)
+    return n_levels * n_points <= 4 * owners
 
 
 def _fused_inputs(value, offsets, logits, reference_points, offset_norm, query_mask):

@@ -9,6 +9,8 @@ Tolerances (north_star: 1e-5 relative in fp32; bf16 tolerance stated here):
         rounded inputs: max|err| <= 1.2e-2 * max|ref| (output rounding 2^-9 plus, for
         grad_sampling_loc, cancellation in corner differences).
 """
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -528,3 +530,25 @@ def test_concurrent_threads_and_streams():
         assert torch.equal(out, wout)
         assert torch.equal(grads[1], wgrads[1]) and torch.equal(grads[2], wgrads[2])
         assert _relerr(grads[0].cpu().numpy(), wgrads[0].cpu().numpy()) <= 1e-5     # atomics: order varies
+
+
+def test_c_abi_from_a_cpp_host_program(tmp_path):
+    """The drop-in boundary is a C ABI: tests/abi_c/abi_smoke.cpp includes include/msda_b200.h, links
+    libmsda_b200.so and the CUDA runtime -- no torch, no Python in the process -- runs forward + backward in
+    fp32 and bf16 on an encoder-form problem and checks them against the C oracle linked into the test."""
+    import shutil
+    import subprocess
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        pytest.skip("nvcc not available on this box")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    libdir = os.path.join(root, "kinet_b200")
+    exe, obj = str(tmp_path / "abi_smoke"), str(tmp_path / "msda_oracle.o")
+    env = {k: v for k, v in os.environ.items() if k not in ("CC", "CXX")}
+    subprocess.check_call(["gcc", "-O2", "-c", os.path.join(root, "oracle", "msda_oracle.c"), "-o", obj], env=env)
+    subprocess.check_call([nvcc, "-O2", "-std=c++17", "-Wno-deprecated-gpu-targets", "-I", os.path.join(root, "include"),
+                           "-o", exe, os.path.join(root, "tests", "abi_c", "abi_smoke.cpp"), obj,
+                           "-L", libdir, "-lmsda_b200", "-Xlinker", "-rpath", "-Xlinker", libdir, "-lm"], env=env)
+    res = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    print(res.stdout)
+    assert res.returncode == 0, res.stdout + res.stderr
