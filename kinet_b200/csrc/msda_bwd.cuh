@@ -117,6 +117,11 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
                 src.get(s, s0 / CH, ls, mine, d, xy.x, xy.y, a);
                 const int H = lt.H[ls], W = lt.W[ls];
                 const OwnerTap t = make_owner_tap(mine, xy.x, xy.y, a, H, W, lt.start[ls], rsv);
+#ifdef MSDA_BOUNDS_CHECK
+                // debug builds (compute-sanitizer replacement): the whole 2x2 footprint lies inside the batch item
+                if (mine) assert(t.off0 >= 0 && (long long)t.off0 + t.dy + (WIDE ? rsv : t.dx) <= (long long)(d.S - 1) * rsv);
+                if (row_ok) assert(q < d.Lq && b < d.N);
+#endif
                 const float wa0 = t.ay.w0 * t.a, wa1 = t.ay.w1 * t.a;
                 // publish the tap (offsets; corner weight * attn) in shared memory, [sample][group]
                 __syncwarp();

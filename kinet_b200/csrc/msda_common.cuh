@@ -12,6 +12,7 @@
 //   * spatial shapes / level starts are staged in shared memory by the CTA
 //     prologue (level starts are computed there when the caller passes none).
 #pragma once
+#include <cassert>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
