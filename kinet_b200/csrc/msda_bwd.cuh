@@ -42,7 +42,8 @@ __device__ __forceinline__ void reduce_scatter(float (&U)[N][4], int gl, int grp
             for (int c = 0; c < 4; ++c) {
                 const float keep = upper ? U[i + HALF][c] : U[i][c];
                 const float send = upper ? U[i][c] : U[i + HALF][c];
-                K[i][c] = keep + __shfl_sync(0xffffffffu, send, (grp_base + (gl ^ HALF)) & 31);   // lanes gl >= group size of the butterfly read garbage, unused
+                // lanes outside the butterfly (gl >= its size; unused lanes of the warp) read garbage, never used
+                K[i][c] = keep + __shfl_sync(0xffffffffu, send, (grp_base + (gl ^ HALF)) & 31);
             }
         }
         reduce_scatter<HALF>(K, gl, grp_base, out);
@@ -61,8 +62,9 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
                                                float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
                                                AT* __restrict__ grad_attn, const KernelDims& d, const FusedArgs& fa)
 {
-    constexpr int MAXCH = kFusedMaxChunks;   // fused: chunks of a row whose d out / d attention stay in registers until
-                               // the row's softmax backward (launcher guarantees L*P <= MAXCH*GS)
+    // fused: chunks of a row whose d out / d attention stay in registers until the row's softmax backward
+    // (the launcher guarantees L*P <= MAXCH * CH)
+    constexpr int MAXCH = kFusedMaxChunks;
     constexpr int GPW = 32 / GS;
     constexpr int D = VEC * GS;
     constexpr int RS = record_stride(GS);  // records per sample in the shared-memory tap arrays
