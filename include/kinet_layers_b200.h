@@ -1,0 +1,84 @@
+/*
+ * kinet_layers_b200.h -- C ABI of the glue kernels of the deformable-transformer layers that CALL
+ * the MSDeformAttn op.  Same library as msda_b200.h
+ * (libmsda_b200.so), same conventions: device pointers, plain sizes, work is enqueued on `stream`
+ * (cudaStream_t as void*), nothing is allocated, nothing synchronises, nothing throws; return 0,
+ * a negative MSDA_E_* or a positive cudaError_t.
+ *
+ * What they replace in the reference (LuisCossioUOH/Kinet, src/trackformer/models/
+ * deformable_transformer.py), per residual branch of a layer:
+ *
+ *   src = src + dropout(src2); src = norm(src)        :294-296, :282-284 (encoder), :375-376, :382-383,
+ *                                                     :363-365 (decoder)
+ *   with_pos_embed(src, pos)                          :277-278, :293, :369, :379   (input of the next op)
+ *   + the dtype casts autocast inserts in front of the next Linear layers
+ *
+ * i.e. an fp32 add, a LayerNorm, another fp32 add and up to three cast kernels (and their autograd
+ * twins, of which LayerNorm's gamma/beta reduction and the Linear bias reductions are the slowest
+ * kernels of a training step) become ONE pass forward and ONE pass backward over the rows.
+ *
+ * Element types use the MSDA_F32 / MSDA_BF16 codes of msda_b200.h.
+ */
+#ifndef KINET_LAYERS_B200_H
+#define KINET_LAYERS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KINET_LN_MAX_C 1024 /* channels per row: multiple of 4, <= 1024 */
+
+/* y = LayerNorm(x + r) * gamma + beta ; y_lp = cast(y) ; ypos_lp = cast(y + pos).
+ * Rows are [rows][C] contiguous.  Statistics and the affine transform are computed in fp32 on
+ * the fp32 sum x + r (two-pass variance over registers), as torch.nn.functional.layer_norm does. */
+typedef struct kinet_ln_fwd_args {
+    const void* x;      int32_t x_dtype;   /* residual stream in                          */
+    const void* r;      int32_t r_dtype;   /* branch output added to x; NULL = none        */
+    const void* pos;    int32_t pos_dtype; /* positional embedding; NULL = no ypos_lp      */
+    int64_t pos_rows;                      /* row i uses pos[i % pos_rows] (broadcast over the batch) */
+    const float* gamma; const float* beta; /* [C] fp32                                    */
+    void* y;            int32_t y_dtype;   /* LayerNorm output (residual stream out)      */
+    void* y_lp;                            /* optional copy of y in lp_dtype               */
+    void* ypos_lp;      int32_t lp_dtype;  /* optional y + pos in lp_dtype                 */
+    float* mean_rstd;                      /* optional [rows][2] saved for the backward    */
+    int64_t rows;       int32_t C;
+    float eps;
+} kinet_ln_fwd_args;
+
+int kinet_b200_add_layernorm_forward(const kinet_ln_fwd_args* args, void* stream);
+
+/* Backward of the above.  The incoming gradient of a row is dy + dy_lp + dypos_lp (each optional).
+ * dx (x_dtype) and dr (r_dtype, optional) receive the same values d(x + r); dgamma_dbeta [2][C]
+ * fp32 is fully overwritten.  `partial` is a caller-provided fp32 scratch of
+ * kinet_b200_colsum_partial_floats(2 * C) elements (per-CTA column sums, reduced in a fixed order:
+ * the result does not depend on scheduling). */
+typedef struct kinet_ln_bwd_args {
+    const void* dy;       int32_t dy_dtype;
+    const void* dy_lp;    const void* dypos_lp; int32_t lp_dtype;
+    const void* x;        int32_t x_dtype;
+    const void* r;        int32_t r_dtype;
+    const float* gamma;
+    const float* mean_rstd;
+    void* dx;
+    void* dr;
+    float* dgamma_dbeta;
+    float* partial;
+    int64_t rows;         int32_t C;
+} kinet_ln_bwd_args;
+
+int kinet_b200_add_layernorm_backward(const kinet_ln_bwd_args* args, void* stream);
+
+/* Column sums out[c] = sum_i a[i][c] of a [rows][C] matrix (the bias gradient of a Linear layer,
+ * which PyTorch computes with a generic reduce kernel): fp32 accumulation, fixed summation order.
+ * C: multiple of 4, <= 1024.  out is out_dtype [C]; partial as above with n = C. */
+size_t kinet_b200_colsum_partial_floats(int32_t n_columns);
+int kinet_b200_colsum(const void* a, int32_t a_dtype, int64_t rows, int32_t C,
+                      void* out, int32_t out_dtype, float* partial, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

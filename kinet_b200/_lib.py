@@ -33,6 +33,37 @@ EXPORTS = ("msda_b200_abi_version", "msda_b200_error_string", "msda_b200_forward
            "msda_b200_forward_fused", "msda_b200_backward_fused",
            "msda_b200_backward_workspace_bytes", "msda_b200_backward",
            "msda_b200_last_launch_count", "msda_b200_trace_next")
+# include/kinet_layers_b200.h (glue kernels of the layers that call the op)
+LAYER_EXPORTS = ("kinet_b200_add_layernorm_forward", "kinet_b200_add_layernorm_backward",
+                 "kinet_b200_colsum_partial_floats", "kinet_b200_colsum")
+
+
+class KinetLnFwdArgs(ctypes.Structure):
+    _fields_ = [("x", ctypes.c_void_p), ("x_dtype", ctypes.c_int32),
+                ("r", ctypes.c_void_p), ("r_dtype", ctypes.c_int32),
+                ("pos", ctypes.c_void_p), ("pos_dtype", ctypes.c_int32),
+                ("pos_rows", ctypes.c_int64),
+                ("gamma", ctypes.c_void_p), ("beta", ctypes.c_void_p),
+                ("y", ctypes.c_void_p), ("y_dtype", ctypes.c_int32),
+                ("y_lp", ctypes.c_void_p),
+                ("ypos_lp", ctypes.c_void_p), ("lp_dtype", ctypes.c_int32),
+                ("mean_rstd", ctypes.c_void_p),
+                ("rows", ctypes.c_int64), ("C", ctypes.c_int32),
+                ("eps", ctypes.c_float)]
+
+
+class KinetLnBwdArgs(ctypes.Structure):
+    _fields_ = [("dy", ctypes.c_void_p), ("dy_dtype", ctypes.c_int32),
+                ("dy_lp", ctypes.c_void_p), ("dypos_lp", ctypes.c_void_p), ("lp_dtype", ctypes.c_int32),
+                ("x", ctypes.c_void_p), ("x_dtype", ctypes.c_int32),
+                ("r", ctypes.c_void_p), ("r_dtype", ctypes.c_int32),
+                ("gamma", ctypes.c_void_p),
+                ("mean_rstd", ctypes.c_void_p),
+                ("dx", ctypes.c_void_p),
+                ("dr", ctypes.c_void_p),
+                ("dgamma_dbeta", ctypes.c_void_p),
+                ("partial", ctypes.c_void_p),
+                ("rows", ctypes.c_int64), ("C", ctypes.c_int32)]
 
 _lib = None
 
@@ -66,6 +97,14 @@ def load():
     lib.msda_b200_last_launch_count.restype = i
     lib.msda_b200_trace_next.restype = None
     lib.msda_b200_trace_next.argtypes = [vp, vp]
+    lib.kinet_b200_add_layernorm_forward.restype = i
+    lib.kinet_b200_add_layernorm_forward.argtypes = [ctypes.POINTER(KinetLnFwdArgs), vp]
+    lib.kinet_b200_add_layernorm_backward.restype = i
+    lib.kinet_b200_add_layernorm_backward.argtypes = [ctypes.POINTER(KinetLnBwdArgs), vp]
+    lib.kinet_b200_colsum_partial_floats.restype = ctypes.c_size_t
+    lib.kinet_b200_colsum_partial_floats.argtypes = [ctypes.c_int32]
+    lib.kinet_b200_colsum.restype = i
+    lib.kinet_b200_colsum.argtypes = [vp, ctypes.c_int32, ctypes.c_int64, ctypes.c_int32, vp, ctypes.c_int32, vp, vp]
     if lib.msda_b200_abi_version() != 2:
         raise RuntimeError("kinet_b200: libmsda_b200.so ABI version mismatch")
     _lib = lib

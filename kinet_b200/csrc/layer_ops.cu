@@ -1,0 +1,388 @@
+// layer_ops.cu -- glue kernels of the deformable-transformer layers around MSDeformAttn
+// (include/kinet_layers_b200.h): fused residual-add + LayerNorm (+ positional add, + low-precision
+// companions for the next GEMMs), its backward, and deterministic column sums for bias gradients.
+//
+// These are row-streaming, HBM/L2-bound kernels: one warp owns a row (C <= 1024 channels sit in
+// registers, 16 bytes per lane and access), rows are read once and written once, the statistics
+// are warp-shuffle reductions.  Column reductions (dgamma, dbeta, bias gradients) are kept in
+// registers across all the rows a warp / thread visits, folded once per CTA through shared memory
+// into a [CTA][column] scratch and summed by a second tiny kernel in a fixed order.
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/kinet_layers_b200.h"
+#include "../../include/msda_b200.h"
+
+namespace kinet {
+
+constexpr int kWarps = 8;           // warps (= rows in flight) per CTA
+constexpr int kMaxCtas = 148 * 4;   // partial-sum scratch is [kMaxCtas][columns]
+
+// 4 consecutive elements at element index i (a multiple of 4) of an fp32 or bf16 array
+__device__ __forceinline__ float4 load4(const void* p, int dtype, size_t i)
+{
+    if (dtype == MSDA_F32) return __ldcs(reinterpret_cast<const float4*>(static_cast<const float*>(p) + i));
+    const uint2 u = __ldcs(reinterpret_cast<const uint2*>(static_cast<const __nv_bfloat16*>(p) + i));
+    float4 f;
+    f.x = __uint_as_float(u.x << 16); f.y = __uint_as_float(u.x & 0xffff0000u);
+    f.z = __uint_as_float(u.y << 16); f.w = __uint_as_float(u.y & 0xffff0000u);
+    return f;
+}
+
+__device__ __forceinline__ void store4(void* p, int dtype, size_t i, float4 f)
+{
+    if (dtype == MSDA_F32) {
+        *reinterpret_cast<float4*>(static_cast<float*>(p) + i) = f;
+    } else {
+        const __nv_bfloat162 a = __floats2bfloat162_rn(f.x, f.y), b = __floats2bfloat162_rn(f.z, f.w);
+        uint2 u;
+        u.x = *reinterpret_cast<const unsigned*>(&a);
+        u.y = *reinterpret_cast<const unsigned*>(&b);
+        *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(p) + i) = u;
+    }
+}
+
+__device__ __forceinline__ float warp_sum(float v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// KMAX: 16-byte vectors per lane; a row has C / 4 vectors, lane l owns vectors l, l + 32, ...
+template <int KMAX>
+__global__ void __launch_bounds__(kWarps * 32)
+add_layernorm_fwd_kernel(const kinet_ln_fwd_args a)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nvec = a.C >> 2;
+    const float inv_c = 1.f / (float)a.C;
+    float4 gam[KMAX], bet[KMAX];
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) {
+        const int v = lane + 32 * k;
+        if (v < nvec) {
+            gam[k] = reinterpret_cast<const float4*>(a.gamma)[v];
+            bet[k] = reinterpret_cast<const float4*>(a.beta)[v];
+        }
+    }
+    for (int64_t row = (int64_t)blockIdx.x * kWarps + warp; row < a.rows; row += (int64_t)gridDim.x * kWarps) {
+        const size_t base = (size_t)row * a.C;
+        float4 z[KMAX];
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k) {
+            const int v = lane + 32 * k;
+            z[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (v < nvec) {
+                z[k] = load4(a.x, a.x_dtype, base + 4 * v);
+                if (a.r) {
+                    const float4 r = load4(a.r, a.r_dtype, base + 4 * v);
+                    z[k].x += r.x; z[k].y += r.y; z[k].z += r.z; z[k].w += r.w;
+                }
+                s += (z[k].x + z[k].y) + (z[k].z + z[k].w);
+            }
+        }
+        const float mean = warp_sum(s) * inv_c;
+        float q = 0.f;
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k) {
+            if (lane + 32 * k < nvec) {
+                const float dx = z[k].x - mean, dy = z[k].y - mean, dz = z[k].z - mean, dw = z[k].w - mean;
+                q += (dx * dx + dy * dy) + (dz * dz + dw * dw);
+            }
+        }
+        const float rstd = rsqrtf(warp_sum(q) * inv_c + a.eps);
+        if (a.mean_rstd && lane == 0) reinterpret_cast<float2*>(a.mean_rstd)[row] = make_float2(mean, rstd);
+        const size_t pbase = a.pos ? (size_t)(row % a.pos_rows) * a.C : 0;
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k) {
+            const int v = lane + 32 * k;
+            if (v < nvec) {
+                float4 y;
+                y.x = (z[k].x - mean) * rstd * gam[k].x + bet[k].x;
+                y.y = (z[k].y - mean) * rstd * gam[k].y + bet[k].y;
+                y.z = (z[k].z - mean) * rstd * gam[k].z + bet[k].z;
+                y.w = (z[k].w - mean) * rstd * gam[k].w + bet[k].w;
+                store4(a.y, a.y_dtype, base + 4 * v, y);
+                if (a.y_lp) store4(a.y_lp, a.lp_dtype, base + 4 * v, y);
+                if (a.ypos_lp) {
+                    const float4 p = load4(a.pos, a.pos_dtype, pbase + 4 * v);
+                    store4(a.ypos_lp, a.lp_dtype, base + 4 * v, make_float4(y.x + p.x, y.y + p.y, y.z + p.z, y.w + p.w));
+                }
+            }
+        }
+    }
+}
+
+// Fold per-warp column accumulators of a CTA into partial[blockIdx][col0 .. col0 + C).
+template <int KMAX>
+__device__ __forceinline__ void fold_columns(float4 (&acc)[KMAX], float* smem, float* partial_row, int C, int lane, int warp)
+{
+    const int nvec = C >> 2;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) {
+        const int v = lane + 32 * k;
+        if (v < nvec) reinterpret_cast<float4*>(smem + (size_t)warp * C)[v] = acc[k];
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) t += smem[(size_t)w * C + c];
+        partial_row[c] = t;
+    }
+}
+
+template <int KMAX>
+__global__ void __launch_bounds__(kWarps * 32)
+add_layernorm_bwd_kernel(const kinet_ln_bwd_args a)
+{
+    extern __shared__ float smem[];   // [kWarps][C]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nvec = a.C >> 2;
+    const float inv_c = 1.f / (float)a.C;
+    float4 gam[KMAX], dg[KMAX], db[KMAX];
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) {
+        const int v = lane + 32 * k;
+        dg[k] = db[k] = gam[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (v < nvec) gam[k] = reinterpret_cast<const float4*>(a.gamma)[v];
+    }
+    for (int64_t row = (int64_t)blockIdx.x * kWarps + warp; row < a.rows; row += (int64_t)gridDim.x * kWarps) {
+        const size_t base = (size_t)row * a.C;
+        const float2 ms = reinterpret_cast<const float2*>(a.mean_rstd)[row];
+        float4 xh[KMAX], wd[KMAX];
+        float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k) {
+            const int v = lane + 32 * k;
+            xh[k] = wd[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (v < nvec) {
+                float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (a.dy) g = load4(a.dy, a.dy_dtype, base + 4 * v);
+                if (a.dy_lp) {
+                    const float4 t = load4(a.dy_lp, a.lp_dtype, base + 4 * v);
+                    g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+                }
+                if (a.dypos_lp) {
+                    const float4 t = load4(a.dypos_lp, a.lp_dtype, base + 4 * v);
+                    g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+                }
+                float4 z = load4(a.x, a.x_dtype, base + 4 * v);
+                if (a.r) {
+                    const float4 r = load4(a.r, a.r_dtype, base + 4 * v);
+                    z.x += r.x; z.y += r.y; z.z += r.z; z.w += r.w;
+                }
+                xh[k] = make_float4((z.x - ms.x) * ms.y, (z.y - ms.x) * ms.y, (z.z - ms.x) * ms.y, (z.w - ms.x) * ms.y);
+                dg[k].x += g.x * xh[k].x; dg[k].y += g.y * xh[k].y; dg[k].z += g.z * xh[k].z; dg[k].w += g.w * xh[k].w;
+                db[k].x += g.x; db[k].y += g.y; db[k].z += g.z; db[k].w += g.w;
+                wd[k] = make_float4(g.x * gam[k].x, g.y * gam[k].y, g.z * gam[k].z, g.w * gam[k].w);
+                c1 += (wd[k].x + wd[k].y) + (wd[k].z + wd[k].w);
+                c2 += (wd[k].x * xh[k].x + wd[k].y * xh[k].y) + (wd[k].z * xh[k].z + wd[k].w * xh[k].w);
+            }
+        }
+        c1 = warp_sum(c1) * inv_c;
+        c2 = warp_sum(c2) * inv_c;
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k) {
+            const int v = lane + 32 * k;
+            if (v < nvec) {
+                float4 d;
+                d.x = ms.y * (wd[k].x - c1 - xh[k].x * c2);
+                d.y = ms.y * (wd[k].y - c1 - xh[k].y * c2);
+                d.z = ms.y * (wd[k].z - c1 - xh[k].z * c2);
+                d.w = ms.y * (wd[k].w - c1 - xh[k].w * c2);
+                store4(a.dx, a.x_dtype, base + 4 * v, d);
+                if (a.dr) store4(a.dr, a.r_dtype, base + 4 * v, d);
+            }
+        }
+    }
+    float* prow = a.partial + (size_t)blockIdx.x * 2 * a.C;
+    fold_columns<KMAX>(dg, smem, prow, a.C, lane, warp);
+    fold_columns<KMAX>(db, smem, prow + a.C, a.C, lane, warp);
+}
+
+// out[c] = sum over the G rows of partial[G][n], fixed order.  A CTA of 32 x 32 threads owns 32 columns:
+// thread (tx, ty) adds rows ty, ty + 32, ... of column tx (independent loads, a few latency rounds instead
+// of G dependent ones), the 32 row lanes are folded through shared memory.
+__global__ void __launch_bounds__(1024)
+colsum_finalize_kernel(const float* __restrict__ partial, int G, int n, void* out, int out_dtype)
+{
+    __shared__ float tile[32][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + tx;
+    float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f;
+    if (c < n) {
+        int g = ty;
+        for (; g + 96 < G; g += 128) {
+            t0 += partial[(size_t)g * n + c];
+            t1 += partial[(size_t)(g + 32) * n + c];
+            t2 += partial[(size_t)(g + 64) * n + c];
+            t3 += partial[(size_t)(g + 96) * n + c];
+        }
+        for (; g < G; g += 32) t0 += partial[(size_t)g * n + c];
+    }
+    tile[ty][tx] = (t0 + t1) + (t2 + t3);
+    __syncthreads();
+    if (ty == 0 && c < n) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < 32; ++w) t += tile[w][tx];
+        if (out_dtype == MSDA_F32) static_cast<float*>(out)[c] = t;
+        else static_cast<__nv_bfloat16*>(out)[c] = __float2bfloat16_rn(t);
+    }
+}
+
+// Column sums of a [rows][C] matrix.  Thread layout: tx = column vector (4 columns), ty = row lane;
+// a CTA walks rows ty, ty + RL, ... of its slab with 4 independent loads in flight per thread.
+__global__ void __launch_bounds__(256)
+colsum_kernel(const void* __restrict__ a, int dtype, int64_t rows, int C, int RL, float* __restrict__ partial)
+{
+    extern __shared__ float smem[];   // [RL][C]
+    const int nvec = C >> 2;
+    const int tx = threadIdx.x % nvec, ty = threadIdx.x / nvec;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ty < RL) {
+        const int64_t stride = (int64_t)gridDim.x * RL;
+        int64_t row = (int64_t)blockIdx.x * RL + ty;
+        for (; row + 3 * stride < rows; row += 4 * stride) {
+            const float4 v0 = load4(a, dtype, (size_t)row * C + 4 * tx);
+            const float4 v1 = load4(a, dtype, (size_t)(row + stride) * C + 4 * tx);
+            const float4 v2 = load4(a, dtype, (size_t)(row + 2 * stride) * C + 4 * tx);
+            const float4 v3 = load4(a, dtype, (size_t)(row + 3 * stride) * C + 4 * tx);
+            acc.x += (v0.x + v1.x) + (v2.x + v3.x);
+            acc.y += (v0.y + v1.y) + (v2.y + v3.y);
+            acc.z += (v0.z + v1.z) + (v2.z + v3.z);
+            acc.w += (v0.w + v1.w) + (v2.w + v3.w);
+        }
+        for (; row < rows; row += stride) {
+            const float4 v0 = load4(a, dtype, (size_t)row * C + 4 * tx);
+            acc.x += v0.x; acc.y += v0.y; acc.z += v0.z; acc.w += v0.w;
+        }
+        reinterpret_cast<float4*>(smem + (size_t)ty * C)[tx] = acc;
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float t = 0.f;
+        for (int w = 0; w < RL; ++w) t += smem[(size_t)w * C + c];
+        partial[(size_t)blockIdx.x * C + c] = t;
+    }
+}
+
+inline bool ok_dtype(int d) { return d == MSDA_F32 || d == MSDA_BF16; }
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+inline bool aligned_for(const void* p, int dtype) { return (reinterpret_cast<uintptr_t>(p) & (dtype == MSDA_F32 ? 15 : 7)) == 0; }
+
+inline int row_grid(int64_t rows)
+{
+    const int64_t need = (rows + kWarps - 1) / kWarps;
+    return (int)(need < kMaxCtas ? (need > 0 ? need : 1) : kMaxCtas);
+}
+
+template <int KMAX>
+int launch_fwd(const kinet_ln_fwd_args& a, cudaStream_t st)
+{
+    add_layernorm_fwd_kernel<KMAX><<<row_grid(a.rows), kWarps * 32, 0, st>>>(a);
+    return (int)cudaGetLastError();
+}
+
+template <int KMAX>
+int launch_bwd(const kinet_ln_bwd_args& a, int grid, cudaStream_t st)
+{
+    const size_t smem = (size_t)kWarps * a.C * sizeof(float);
+    add_layernorm_bwd_kernel<KMAX><<<grid, kWarps * 32, smem, st>>>(a);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace kinet
+
+using namespace kinet;
+
+extern "C" {
+
+int kinet_b200_add_layernorm_forward(const kinet_ln_fwd_args* args, void* stream)
+{
+    if (!args) return MSDA_E_NULL;
+    const kinet_ln_fwd_args& a = *args;
+    if (!a.x || !a.y || !a.gamma || !a.beta) return MSDA_E_NULL;
+    if (a.rows < 0 || a.C <= 0 || (a.C & 3) || a.C > KINET_LN_MAX_C) return MSDA_E_SHAPE;
+    if (!ok_dtype(a.x_dtype) || !ok_dtype(a.y_dtype) || (a.r && !ok_dtype(a.r_dtype))) return MSDA_E_DTYPE;
+    if ((a.y_lp || a.ypos_lp) && !ok_dtype(a.lp_dtype)) return MSDA_E_DTYPE;
+    if (a.ypos_lp && (!a.pos || !ok_dtype(a.pos_dtype) || a.pos_rows <= 0)) return MSDA_E_NULL;
+    if (!aligned_for(a.x, a.x_dtype) || !aligned_for(a.y, a.y_dtype) || !aligned16(a.gamma) || !aligned16(a.beta) ||
+        (a.r && !aligned_for(a.r, a.r_dtype)) || (a.y_lp && !aligned_for(a.y_lp, a.lp_dtype)) ||
+        (a.ypos_lp && (!aligned_for(a.ypos_lp, a.lp_dtype) || !aligned_for(a.pos, a.pos_dtype))) ||
+        (a.mean_rstd && (reinterpret_cast<uintptr_t>(a.mean_rstd) & 7)))
+        return MSDA_E_ALIGN;
+    if (a.rows == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int k = (a.C + 127) / 128;
+    if (k <= 2) return launch_fwd<2>(a, st);
+    if (k <= 3) return launch_fwd<3>(a, st);
+    if (k <= 4) return launch_fwd<4>(a, st);
+    return launch_fwd<8>(a, st);
+}
+
+size_t kinet_b200_colsum_partial_floats(int32_t n_columns)
+{
+    return n_columns > 0 ? (size_t)kMaxCtas * (size_t)n_columns : 0;
+}
+
+int kinet_b200_add_layernorm_backward(const kinet_ln_bwd_args* args, void* stream)
+{
+    if (!args) return MSDA_E_NULL;
+    const kinet_ln_bwd_args& a = *args;
+    if (!a.x || !a.dx || !a.gamma || !a.mean_rstd || !a.dgamma_dbeta || !a.partial) return MSDA_E_NULL;
+    if (!a.dy && !a.dy_lp && !a.dypos_lp) return MSDA_E_NULL;
+    if (a.r == nullptr && a.dr != nullptr) return MSDA_E_NULL;
+    if (a.rows < 0 || a.C <= 0 || (a.C & 3) || a.C > KINET_LN_MAX_C) return MSDA_E_SHAPE;
+    if (!ok_dtype(a.x_dtype) || (a.r && !ok_dtype(a.r_dtype)) || (a.dy && !ok_dtype(a.dy_dtype)) ||
+        ((a.dy_lp || a.dypos_lp) && !ok_dtype(a.lp_dtype)))
+        return MSDA_E_DTYPE;
+    if (!aligned_for(a.x, a.x_dtype) || !aligned_for(a.dx, a.x_dtype) || !aligned16(a.gamma) ||
+        (a.r && !aligned_for(a.r, a.r_dtype)) || (a.dr && !aligned_for(a.dr, a.r_dtype)) ||
+        (a.dy && !aligned_for(a.dy, a.dy_dtype)) || (a.dy_lp && !aligned_for(a.dy_lp, a.lp_dtype)) ||
+        (a.dypos_lp && !aligned_for(a.dypos_lp, a.lp_dtype)) || !aligned16(a.partial))
+        return MSDA_E_ALIGN;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int grid = a.rows > 0 ? row_grid(a.rows) : 0;
+    if (grid > 0) {
+        const int k = (a.C + 127) / 128;
+        int rc;
+        if (k <= 2) rc = launch_bwd<2>(a, grid, st);
+        else if (k <= 3) rc = launch_bwd<3>(a, grid, st);
+        else if (k <= 4) rc = launch_bwd<4>(a, grid, st);
+        else rc = launch_bwd<8>(a, grid, st);
+        if (rc) return rc;
+    }
+    const int n = 2 * a.C;
+    colsum_finalize_kernel<<<(n + 31) / 32, 1024, 0, st>>>(a.partial, grid, n, a.dgamma_dbeta, MSDA_F32);
+    return (int)cudaGetLastError();
+}
+
+int kinet_b200_colsum(const void* a, int32_t a_dtype, int64_t rows, int32_t C, void* out, int32_t out_dtype,
+                      float* partial, void* stream)
+{
+    if (!out || !partial || (rows > 0 && !a)) return MSDA_E_NULL;
+    if (rows < 0 || C <= 0 || (C & 3) || C > KINET_LN_MAX_C) return MSDA_E_SHAPE;
+    if (!ok_dtype(a_dtype) || !ok_dtype(out_dtype)) return MSDA_E_DTYPE;
+    if ((rows > 0 && !aligned_for(a, a_dtype)) || !aligned16(partial)) return MSDA_E_ALIGN;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int nvec = C >> 2;
+    const int RL = 256 / nvec;     // row lanes per CTA (nvec <= 256)
+    int grid = 0;
+    if (rows > 0) {
+        // at least 8 rows per row lane, at most kMaxCtas CTAs
+        const int64_t want = (rows + (int64_t)RL * 8 - 1) / ((int64_t)RL * 8);
+        grid = (int)(want < kMaxCtas ? (want > 0 ? want : 1) : kMaxCtas);
+        colsum_kernel<<<grid, 256, (size_t)RL * C * sizeof(float), st>>>(a, a_dtype, rows, C, RL, partial);
+        if (int rc = (int)cudaGetLastError()) return rc;
+    }
+    colsum_finalize_kernel<<<(C + 31) / 32, 1024, 0, st>>>(partial, grid, C, out, out_dtype);
+    return (int)cudaGetLastError();
+}
+
+}  // extern "C"

@@ -1,0 +1,209 @@
+"""Autograd wrappers over the layer glue kernels (include/kinet_layers_b200.h, csrc/layer_ops.cu).
+
+``add_layer_norm`` fuses what the reference's encoder / decoder layers do between two GEMMs
+(src/trackformer/models/deformable_transformer.py:294-296, 282-284, 363-365, 375-376, 382-383):
+``x = norm(x + dropout(branch))`` followed by ``with_pos_embed(x, pos)`` for the next attention's
+query (:277-278, 293, 369, 379), plus the dtype casts autocast would put in front of the next Linear
+layers.  ``linear`` is ``F.linear`` whose bias gradient is a fixed-order fp32 column sum instead of
+PyTorch's generic reduce kernel.  CUDA only -- CPU tensors raise, like the op itself.
+"""
+import ctypes
+
+import torch
+import torch.nn.functional as F
+from torch.autograd import Function
+from torch.autograd.function import once_differentiable
+
+from .. import _lib
+
+_LN_DTYPES = (torch.float32, torch.bfloat16)
+MAX_C = 1024
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _code(t, default=0):
+    return default if t is None else _lib.dtype_code(t.dtype)
+
+
+def _rows(t, C):
+    if t.shape[-1] != C or not t.is_contiguous():
+        raise RuntimeError("kinet_b200: expected a contiguous tensor with %d channels last" % C)
+    return t.numel() // C
+
+
+def ln_supported(x, C):
+    """The fused kernel covers fp32 / bf16 CUDA tensors with C % 4 == 0, C <= 1024."""
+    return x.is_cuda and x.dtype in _LN_DTYPES and C % 4 == 0 and 0 < C <= MAX_C
+
+
+def _canon_pos(pos, x):
+    """pos as a contiguous [pos_rows, C] block that row i of x reads at i % pos_rows.
+    Accepts pos shaped like x, or broadcast over the leading (batch) dimension."""
+    if pos.shape[-1] != x.shape[-1]:
+        raise RuntimeError("kinet_b200: pos must have the channel count of x")
+    if pos.dim() == x.dim() and pos.shape != x.shape and pos.shape[0] == 1:
+        pos = pos[0]
+    if pos.dim() == x.dim() and pos.shape == x.shape and x.dim() >= 2 and pos.stride(0) == 0:
+        pos = pos[0]                                  # an .expand()ed batch dimension
+    if pos.dim() == x.dim():
+        if pos.shape != x.shape:
+            raise RuntimeError("kinet_b200: pos %s does not match x %s" % (tuple(pos.shape), tuple(x.shape)))
+    elif tuple(pos.shape) != tuple(x.shape[x.dim() - pos.dim():]):
+        raise RuntimeError("kinet_b200: pos %s does not broadcast over x %s" % (tuple(pos.shape), tuple(x.shape)))
+    return pos.contiguous()
+
+
+class AddLayerNormFunction(Function):
+    """(y, y_lp, ypos_lp) = AddLayerNormFunction.apply(x, r, pos, gamma, beta, eps, lp_dtype, want_lp)
+
+    y = LayerNorm(x + r) in x.dtype; y_lp = y.to(lp_dtype) if want_lp else None;
+    ypos_lp = (y + pos).to(lp_dtype) if pos is not None else None.  r may be None."""
+
+    @staticmethod
+    def forward(ctx, x, r, pos, gamma, beta, eps, lp_dtype, want_lp):
+        if not x.is_cuda:
+            raise RuntimeError("Not implemented on the CPU")
+        C = x.shape[-1]
+        x = x.contiguous()
+        rows = _rows(x, C)
+        if r is not None:
+            r = r.contiguous()
+            if r.shape != x.shape:
+                raise RuntimeError("kinet_b200: branch output %s does not match x %s" % (tuple(r.shape), tuple(x.shape)))
+        gamma32, beta32 = gamma.detach().float().contiguous(), beta.detach().float().contiguous()
+        posc = _canon_pos(pos.detach(), x) if pos is not None else None
+        need_stats = any(ctx.needs_input_grad[:5])
+        y = torch.empty_like(x)
+        y_lp = torch.empty(x.shape, dtype=lp_dtype, device=x.device) if want_lp else None
+        ypos = torch.empty(x.shape, dtype=lp_dtype, device=x.device) if posc is not None else None
+        stats = torch.empty(rows, 2, dtype=torch.float32, device=x.device) if need_stats else None
+        a = _lib.KinetLnFwdArgs(
+            _ptr(x), _code(x), _ptr(r), _code(r), _ptr(posc), _code(posc),
+            (posc.numel() // C) if posc is not None else 1,
+            _ptr(gamma32), _ptr(beta32), _ptr(y), _code(y), _ptr(y_lp), _ptr(ypos),
+            _lib.dtype_code(lp_dtype), _ptr(stats), rows, C, float(eps))
+        lib = _lib.load()
+        with _lib.device_guard(x.device):
+            rc = lib.kinet_b200_add_layernorm_forward(ctypes.byref(a), _lib.raw_stream(x.device))
+        _lib.check(rc, "kinet_b200_add_layernorm_forward")
+        ctx.set_materialize_grads(False)
+        if need_stats:
+            ctx.save_for_backward(x, r, gamma32, stats)
+            ctx.pos_meta = None if pos is None else (pos.shape, pos.dtype, posc.shape)
+            ctx.param_dtypes = (gamma.dtype, beta.dtype)
+        return y, y_lp, ypos
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy, dy_lp, dypos):
+        x, r, gamma32, stats = ctx.saved_tensors
+        if dy is None and dy_lp is None and dypos is None:
+            return (None,) * 8
+        C = x.shape[-1]
+        rows = x.numel() // C
+        lp = [t for t in (dy_lp, dypos) if t is not None]
+        if len(lp) == 2 and lp[0].dtype != lp[1].dtype:
+            raise RuntimeError("kinet_b200: companion gradients must share a dtype")
+        dy = dy.contiguous() if dy is not None else None
+        dy_lp = dy_lp.contiguous() if dy_lp is not None else None
+        dypos = dypos.contiguous() if dypos is not None else None
+        dx = torch.empty_like(x)
+        dr = torch.empty_like(r) if (r is not None and ctx.needs_input_grad[1]) else None
+        dgb = torch.empty(2, C, dtype=torch.float32, device=x.device)
+        lib = _lib.load()
+        partial = torch.empty(lib.kinet_b200_colsum_partial_floats(2 * C), dtype=torch.float32, device=x.device)
+        a = _lib.KinetLnBwdArgs(
+            _ptr(dy), _code(dy), _ptr(dy_lp), _ptr(dypos), _code(lp[0]) if lp else 0,
+            _ptr(x), _code(x), _ptr(r), _code(r), _ptr(gamma32), _ptr(stats),
+            _ptr(dx), _ptr(dr), _ptr(dgb), _ptr(partial), rows, C)
+        with _lib.device_guard(x.device):
+            rc = lib.kinet_b200_add_layernorm_backward(ctypes.byref(a), _lib.raw_stream(x.device))
+        _lib.check(rc, "kinet_b200_add_layernorm_backward")
+        dpos = None
+        if ctx.needs_input_grad[2] and dypos is not None:
+            shape, dtype, cshape = ctx.pos_meta
+            if tuple(shape) == tuple(x.shape):      # incl. an expanded batch dimension: autograd sums it
+                dpos = dypos.to(dtype)
+            else:
+                dpos = dypos.reshape((-1,) + tuple(cshape)).sum(0).to(dtype).reshape(shape)
+        gd, bd = ctx.param_dtypes
+        return (dx if ctx.needs_input_grad[0] else None, dr, dpos,
+                dgb[0].to(gd) if ctx.needs_input_grad[3] else None,
+                dgb[1].to(bd) if ctx.needs_input_grad[4] else None, None, None, None)
+
+
+def add_layer_norm(x, r, norm, pos=None, lp_dtype=None, want_lp=False):
+    """norm(x + r) with the layer's nn.LayerNorm parameters -> (y, y_lp, ypos_lp); see AddLayerNormFunction."""
+    if tuple(norm.normalized_shape) != (x.shape[-1],) or norm.weight is None or norm.bias is None:
+        raise RuntimeError("kinet_b200: add_layer_norm needs an affine LayerNorm over the last dimension")
+    return AddLayerNormFunction.apply(x, r, pos, norm.weight, norm.bias, norm.eps,
+                                      lp_dtype if lp_dtype is not None else x.dtype, want_lp)
+
+
+def column_sum(a2d, out_dtype=None):
+    """Fixed-order fp32 column sums of a contiguous (rows, C) CUDA matrix."""
+    if not a2d.is_cuda:
+        raise RuntimeError("Not implemented on the CPU")
+    rows, C = a2d.shape
+    out_dtype = out_dtype or a2d.dtype
+    lib = _lib.load()
+    out = torch.empty(C, dtype=out_dtype, device=a2d.device)
+    partial = torch.empty(lib.kinet_b200_colsum_partial_floats(C), dtype=torch.float32, device=a2d.device)
+    with _lib.device_guard(a2d.device):
+        rc = lib.kinet_b200_colsum(_ptr(a2d), _lib.dtype_code(a2d.dtype), rows, C, _ptr(out),
+                                   _lib.dtype_code(out_dtype), _ptr(partial), _lib.raw_stream(a2d.device))
+    _lib.check(rc, "kinet_b200_colsum")
+    return out
+
+
+def colsum_supported(a2d):
+    return (a2d.is_cuda and a2d.dtype in _LN_DTYPES and a2d.dim() == 2 and a2d.is_contiguous()
+            and a2d.shape[1] % 4 == 0 and 0 < a2d.shape[1] <= MAX_C)
+
+
+class LinearFunction(Function):
+    """y = x @ weight.T + bias (cuBLAS, as nn.Linear); under CUDA autocast the operands are cast to the
+    autocast dtype like F.linear would.  Backward: two cuBLAS GEMMs and the fused column sum for the bias."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        lp = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else None
+        w, b, x_dtype = weight, bias, x.dtype
+        if lp is not None:
+            x, w, b = x.to(lp), weight.to(lp), bias.to(lp)
+        elif x.dtype != weight.dtype:
+            x = x.to(weight.dtype)
+        with torch.autocast("cuda", enabled=False):
+            y = F.linear(x, w, b)
+        ctx.save_for_backward(x, w)
+        ctx.param_dtypes = (weight.dtype, bias.dtype)
+        ctx.x_dtype = x_dtype
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        x2 = x.reshape(-1, x.shape[-1])
+        wd, bd = ctx.param_dtypes
+        dx = (dy2 @ w).view(x.shape).to(ctx.x_dtype) if ctx.needs_input_grad[0] else None
+        dw = (dy2.t() @ x2).to(wd) if ctx.needs_input_grad[1] else None
+        db = None
+        if ctx.needs_input_grad[2]:
+            db = column_sum(dy2, bd) if colsum_supported(dy2) else dy2.sum(0).to(bd)
+        return dx, dw, db
+
+
+def linear(x, layer):
+    """``layer(x)`` for an nn.Linear: the plain (autocast-cached) F.linear when no parameter gradient is
+    needed, LinearFunction otherwise."""
+    if (x.is_cuda and layer.bias is not None and torch.is_grad_enabled()
+            and (layer.weight.requires_grad or layer.bias.requires_grad)):
+        return LinearFunction.apply(x, layer.weight, layer.bias)
+    return F.linear(x, layer.weight, layer.bias)

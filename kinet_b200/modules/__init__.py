@@ -1,1 +1,7 @@
 from .ms_deform_attn import MSDeformAttn  # noqa: F401
+from .deformable_transformer import (  # noqa: F401
+    DeformableTransformerDecoder,
+    DeformableTransformerDecoderLayer,
+    DeformableTransformerEncoder,
+    DeformableTransformerEncoderLayer,
+)

@@ -3,7 +3,8 @@ src/trackformer/models/ops/modules/ms_deform_attn.py:15-89 (same constructor, pa
 names/shapes/initialisation, forward signature incl. ``query_attn_mask``), so TrackFormer /
 KineTTracker checkpoints load unchanged and deformable_transformer.py can import it as is.
 
-The four Linear layers stay cuBLAS GEMMs; the sampling + weighted reduction runs in the
+The four Linear layers stay cuBLAS GEMMs (their bias gradients are fixed-order column sums,
+functions/layer_ops.py); the sampling + weighted reduction runs in the
 sm_100a kernels through MSDeformAttnFunction.  Reference quirk kept on purpose: 2-d reference
 points are normalised by ``input_spatial_shapes`` in (H, W) order (:77-79), i.e. the x offset is
 divided by H and the y offset by W -- upstream Deformable-DETR flips to (W, H); the reference
@@ -18,6 +19,7 @@ from torch import nn
 from torch.nn.init import constant_, xavier_uniform_
 
 from ..functions import MSDeformAttnFunction, MSDeformAttnFusedFunction, fused_supported
+from ..functions.layer_ops import linear as _linear
 
 
 _shapes_validated = None   # (weakref to the last validated spatial_shapes tensor, its version, Len_in)
@@ -94,14 +96,14 @@ class MSDeformAttn(nn.Module):
         N, Len_in, _ = input_flatten.shape
         _check_spatial_shapes(input_spatial_shapes, Len_in)
 
-        value = self.value_proj(input_flatten)
+        value = _linear(input_flatten, self.value_proj)
         if input_padding_mask is not None:
             value = value.masked_fill(input_padding_mask[..., None], float(0))
         value = value.view(N, Len_in, self.n_heads, self.d_model // self.n_heads)
 
-        sampling_offsets = self.sampling_offsets(query).view(
+        sampling_offsets = _linear(query, self.sampling_offsets).view(
             N, Len_q, self.n_heads, self.n_levels, self.n_points, 2)
-        attention_weights = self.attention_weights(query).view(
+        attention_weights = _linear(query, self.attention_weights).view(
             N, Len_q, self.n_heads, self.n_levels * self.n_points)
         if reference_points.shape[-1] not in (2, 4):
             raise ValueError(
@@ -112,7 +114,7 @@ class MSDeformAttn(nn.Module):
             output = MSDeformAttnFusedFunction.apply(
                 value, input_spatial_shapes, reference_points, sampling_offsets, attention_weights,
                 query_attn_mask, input_spatial_shapes, self.im2col_step)
-            return self.output_proj(output)
+            return _linear(output, self.output_proj)
         attention_weights = F.softmax(attention_weights, -1).view(
             N, Len_q, self.n_heads, self.n_levels, self.n_points)
 
@@ -132,5 +134,4 @@ class MSDeformAttn(nn.Module):
                     reference_points.shape[-1]))
         output = MSDeformAttnFunction.apply(
             value, input_spatial_shapes, sampling_locations, attention_weights, self.im2col_step)
-        output = self.output_proj(output)
-        return output
+        return _linear(output, self.output_proj)

@@ -145,3 +145,46 @@ class Stack(nn.Module):
         for layer in self.dec:
             tgt = layer(tgt, qpos, dref, mem, shapes)
         return tgt, mem
+
+
+class FusedStack(nn.Module):
+    """The same 6+6-layer stack built from kinet_b200.modules' encoder / decoder classes (fused residual +
+    LayerNorm + positional-add kernels between the GEMMs).  Parameter-compatible with Stack (load_from_stack)."""
+
+    def __init__(self, levels, n_enc=6, n_dec=6, n_queries=300, d=256):
+        super().__init__()
+        from kinet_b200.modules import (DeformableTransformerDecoder, DeformableTransformerDecoderLayer,
+                                        DeformableTransformerEncoder, DeformableTransformerEncoderLayer)
+        self.levels = levels
+        L = len(levels)
+        self.encoder = DeformableTransformerEncoder(DeformableTransformerEncoderLayer(d, 1024, 0.0, "relu", L, 8, 4), n_enc)
+        self.decoder = DeformableTransformerDecoder(DeformableTransformerDecoderLayer(d, 1024, 0.0, "relu", L, 8, 4), n_dec)
+        self.query_embed = nn.Embedding(n_queries, 2 * d)
+        self.ref_proj = nn.Linear(d, 2)
+        self.load_from_stack(Stack(levels, n_enc, n_dec, n_queries, d))
+
+    def load_from_stack(self, stack):
+        sd = {}
+        for k, v in stack.state_dict().items():
+            k = k.replace("enc.", "encoder.layers.", 1) if k.startswith("enc.") else k
+            k = k.replace("dec.", "decoder.layers.", 1) if k.startswith("dec.") else k
+            sd[k] = v
+        self.load_state_dict(sd, strict=True)
+
+    def _geometry(self, N, device):
+        key = (N, str(device))
+        if getattr(self, "_geo_key", None) != key:
+            self._geo = (torch.as_tensor(self.levels, dtype=torch.long, device=device),
+                         torch.ones(N, len(self.levels), 2, device=device))
+            self._geo_key = key
+        return self._geo
+
+    def forward(self, src, pos):
+        N, S, d = src.shape
+        shapes, valid = self._geometry(N, src.device)
+        mem = self.encoder(src, shapes, valid, pos, None, return_stream=True)
+        qpos, tgt = self.query_embed.weight.split(d, dim=1)
+        qpos, tgt = qpos[None].expand(N, -1, -1), tgt[None].expand(N, -1, -1)
+        dref = self.ref_proj(qpos).sigmoid()
+        out, _ = self.decoder(tgt, dref, mem, shapes, valid, qpos)
+        return out, mem.x

@@ -1,0 +1,232 @@
+"""GPU parity of the layer glue kernels (include/kinet_layers_b200.h) and of the encoder / decoder classes
+(kinet_b200/modules/deformable_transformer.py) against (a) fp64 PyTorch formulas of the same arithmetic and
+(b) golden vectors produced by the REFERENCE's own classes (tests/golden/make_golden_layers.py)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _dev():
+    return torch.device("cuda", 0)
+
+
+def _rel(a, b):
+    a, b = a.double(), b.double()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+@pytest.mark.parametrize("C", [4, 36, 128, 256, 288, 512, 1024])
+@pytest.mark.parametrize("stream,lp", [(torch.float32, torch.float32), (torch.float32, torch.bfloat16),
+                                       (torch.bfloat16, torch.bfloat16)])
+@pytest.mark.parametrize("pos_mode", ["none", "full", "batch_broadcast"])
+def test_add_layer_norm_forward_backward(C, stream, lp, pos_mode):
+    from kinet_b200.functions.layer_ops import AddLayerNormFunction
+    dev = _dev()
+    g = torch.Generator(device=dev).manual_seed(C)
+    N, Lq = 3, 13
+    x = torch.randn(N, Lq, C, device=dev, generator=g).to(stream).requires_grad_(True)
+    r = (0.5 * torch.randn(N, Lq, C, device=dev, generator=g)).to(lp).requires_grad_(True)
+    gamma = (1 + 0.2 * torch.randn(C, device=dev, generator=g)).requires_grad_(True)
+    beta = (0.2 * torch.randn(C, device=dev, generator=g)).requires_grad_(True)
+    pos = None
+    if pos_mode == "full":
+        pos = (0.3 * torch.randn(N, Lq, C, device=dev, generator=g)).requires_grad_(True)
+    elif pos_mode == "batch_broadcast":
+        pos = (0.3 * torch.randn(Lq, C, device=dev, generator=g)).requires_grad_(True)
+    pos_in = pos if pos_mode != "batch_broadcast" else pos[None].expand(N, -1, -1)
+    want_lp = lp != stream
+    y, y_lp, ypos = AddLayerNormFunction.apply(x, r, pos_in, gamma, beta, 1e-5, lp, want_lp)
+    assert y.dtype == stream and (y_lp is None) == (not want_lp) and (ypos is None) == (pos is None)
+
+    # fp64 restatement on the same (rounded) inputs
+    xd, rd = x.detach().double().requires_grad_(True), r.detach().double().requires_grad_(True)
+    gd, bd = gamma.detach().double().requires_grad_(True), beta.detach().double().requires_grad_(True)
+    pd = pos.detach().double().requires_grad_(True) if pos is not None else None
+    yd = F.layer_norm(xd + rd, (C,), gd, bd, 1e-5)
+    tol_s = 1e-5 if stream == torch.float32 else 1.2e-2
+    tol_l = 1e-5 if lp == torch.float32 else 1.2e-2
+    assert _rel(y, yd) < tol_s
+    ws = [torch.randn(N, Lq, C, device=dev, generator=g) for _ in range(3)]
+    loss = (y.float() * ws[0]).sum()
+    lossd = (yd * ws[0].double()).sum()
+    if want_lp:
+        assert _rel(y_lp, yd) < tol_l
+        loss = loss + (y_lp.float() * ws[1]).sum()
+        lossd = lossd + (yd * ws[1].to(lp).double()).sum()     # the gradient reaches the kernel rounded to lp
+    if pos is not None:
+        assert _rel(ypos, yd + pd) < tol_l
+        loss = loss + (ypos.float() * ws[2]).sum()
+        lossd = lossd + ((yd + pd) * ws[2].to(lp).double()).sum()
+    loss.backward()
+    lossd.backward()
+    gt = 2e-5 if (stream == torch.float32 and lp == torch.float32) else 1.5e-2
+    assert _rel(x.grad, xd.grad) < (2e-5 if stream == torch.float32 and lp == torch.float32 else 1.5e-2)
+    assert _rel(r.grad, rd.grad) < gt
+    assert _rel(gamma.grad, gd.grad) < gt and _rel(beta.grad, bd.grad) < gt
+    if pos is not None:
+        assert pos.grad.shape == pos.shape and _rel(pos.grad, pd.grad) < gt
+
+
+def test_add_layer_norm_no_branch_many_rows_and_determinism():
+    from kinet_b200.functions.layer_ops import AddLayerNormFunction
+    dev = _dev()
+    g = torch.Generator(device=dev).manual_seed(1)
+    x = torch.randn(2, 22223, 256, device=dev, generator=g).requires_grad_(True)
+    gamma = torch.randn(256, device=dev, generator=g).requires_grad_(True)
+    beta = torch.randn(256, device=dev, generator=g).requires_grad_(True)
+    w = torch.randn(2, 22223, 256, device=dev, generator=g)
+    grads = []
+    for _ in range(2):
+        y, _, _ = AddLayerNormFunction.apply(x, None, None, gamma, beta, 1e-5, torch.float32, False)
+        grads.append(torch.autograd.grad((y * w).sum(), (x, gamma, beta)))
+    ref = F.layer_norm(x.double(), (256,), gamma.double(), beta.double(), 1e-5)
+    assert _rel(y, ref) < 1e-5
+    rg = torch.autograd.grad((ref * w.double()).sum(), (x, gamma, beta))
+    for a, b in zip(grads[0], rg):
+        assert _rel(a, b) < 2e-5
+    for a, b in zip(grads[0], grads[1]):          # fixed summation order: bit-identical from run to run
+        assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("rows,C", [(1, 4), (77, 128), (44446, 256), (44446, 1024), (20906, 288), (5, 1000)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_column_sum(rows, C, dtype):
+    from kinet_b200.functions.layer_ops import column_sum
+    dev = _dev()
+    a = torch.randn(rows, C, device=dev, generator=torch.Generator(device=dev).manual_seed(rows)).to(dtype)
+    out = column_sum(a, torch.float32)
+    ref = a.double().sum(0)
+    assert float((out.double() - ref).abs().max()) <= 1e-5 * float(a.double().abs().sum(0).max())
+    assert torch.equal(out, column_sum(a, torch.float32))
+    assert column_sum(a).dtype == dtype
+
+
+@pytest.mark.parametrize("amp", [False, True])
+def test_linear_function_matches_nn_linear(amp):
+    from kinet_b200.functions.layer_ops import linear
+    dev = _dev()
+    torch.manual_seed(0)
+    lin = torch.nn.Linear(256, 384).to(dev)
+    x = torch.randn(2, 777, 256, device=dev, requires_grad=True)
+    w = torch.randn(2, 777, 384, device=dev)
+    with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
+        y = linear(x, lin)
+        y0 = lin(x)
+    assert y.dtype == y0.dtype and torch.equal(y, y0)
+    g = torch.autograd.grad((y.float() * w).sum(), (x, lin.weight, lin.bias))
+    g0 = torch.autograd.grad((y0.float() * w).sum(), (x, lin.weight, lin.bias))
+    tol = 2e-2 if amp else 1e-5
+    for a, b in zip(g, g0):
+        assert a.dtype == b.dtype and _rel(a, b) < tol
+    # the bias gradient is an fp32 sum of the (rounded) upstream gradient: compare with fp64
+    up = w.to(y.dtype).double().sum((0, 1))
+    assert _rel(g[2], up) < 1e-5
+
+
+def _load_golden():
+    z = np.load(os.path.join(HERE, "golden", "layers_f32.npz"))
+    return {k: z[k] for k in z.files}
+
+
+def _build_from_golden(z, dev):
+    from kinet_b200.modules import (DeformableTransformerDecoder, DeformableTransformerDecoderLayer,
+                                    DeformableTransformerEncoder, DeformableTransformerEncoderLayer)
+    d, ffn, L, M, P = 128, 64, 2, 8, 2
+    enc = DeformableTransformerEncoder(DeformableTransformerEncoderLayer(d, ffn, 0.0, "relu", L, M, P), 2)
+    dec = DeformableTransformerDecoder(DeformableTransformerDecoderLayer(d, ffn, 0.0, "relu", L, M, P), 2)
+    for prefix, m in (("enc.", enc), ("dec.", dec)):
+        sd = {k[len("p:" + prefix):]: torch.from_numpy(v) for k, v in z.items() if k.startswith("p:" + prefix)}
+        missing, unexpected = m.load_state_dict(sd, strict=True)
+        assert not missing and not unexpected
+    return enc.to(dev).eval(), dec.to(dev).eval()
+
+
+def _golden_inputs(z, dev):
+    t = lambda k: torch.from_numpy(z[k]).to(dev)
+    return dict(shapes=t("levels").long(), src=t("src").requires_grad_(True), pos=t("pos").requires_grad_(True),
+                valid=t("valid"), mask=t("mask"), tgt=t("tgt").requires_grad_(True),
+                qpos=t("qpos").requires_grad_(True), ref=t("ref"), qmask=t("qmask"), w_mem=t("w_mem"), w_out=t("w_out"))
+
+
+def test_encoder_decoder_match_reference_golden_fp32():
+    """The reference's own classes (CPU, fp32, oracle op) produced the golden file; ours run on the GPU."""
+    z = _load_golden()
+    dev = _dev()
+    enc, dec = _build_from_golden(z, dev)
+    i = _golden_inputs(z, dev)
+    memory = enc(i["src"], i["shapes"], i["valid"], i["pos"], i["mask"])
+    out, ref_out = dec(i["tgt"], i["ref"], memory, i["shapes"], i["valid"], i["qpos"], i["mask"], i["qmask"])
+    assert _rel(memory, torch.from_numpy(z["memory"]).to(dev)) < 2e-5
+    assert _rel(out, torch.from_numpy(z["out"]).to(dev)) < 2e-5
+    assert torch.equal(ref_out.cpu(), torch.from_numpy(z["ref_out"]))
+    loss = (memory * i["w_mem"]).sum() + (out * i["w_out"]).sum()
+    params = dict(("enc." + k, v) for k, v in enc.named_parameters())
+    params.update(("dec." + k, v) for k, v in dec.named_parameters())
+    names = [k for k in params if ("g:" + k) in z]
+    assert len(names) >= 60
+    grads = torch.autograd.grad(loss, [i["src"], i["pos"], i["tgt"], i["qpos"]] + [params[k] for k in names])
+    for k, g in zip(["g_src", "g_pos", "g_tgt", "g_qpos"] + ["g:" + k for k in names], grads):
+        assert _rel(g, torch.from_numpy(z[k]).to(dev)) < 1e-4, k
+
+
+def test_single_layer_forward_signatures_match_stream_path():
+    """layer.forward(...) with the reference's signature equals the stacked (stream) execution."""
+    z = _load_golden()
+    dev = _dev()
+    enc, dec = _build_from_golden(z, dev)
+    i = _golden_inputs(z, dev)
+    with torch.no_grad():
+        refp = enc.get_reference_points(i["shapes"], i["valid"], dev)
+        x = i["src"]
+        for layer in enc.layers:
+            x = layer(x, i["pos"], refp, i["shapes"], i["mask"])
+        memory = enc(i["src"], i["shapes"], i["valid"], i["pos"], i["mask"])
+        assert _rel(x, memory) < 1e-6
+        st = enc(i["src"], i["shapes"], i["valid"], i["pos"], i["mask"], return_stream=True)
+        out_a, _ = dec(i["tgt"], i["ref"], st, i["shapes"], i["valid"], i["qpos"], i["mask"], i["qmask"])
+        t = i["tgt"]
+        rin = i["ref"][:, :, None] * i["valid"][:, None]
+        for layer in dec.layers:
+            t = layer(t, i["qpos"], rin, memory, i["shapes"], i["mask"], i["qmask"])
+        assert _rel(t, out_a) < 1e-6
+        f = enc.layers[0].forward_ffn(i["src"])
+        l0 = enc.layers[0]
+        f0 = l0.norm2(i["src"] + l0.linear2(torch.relu(l0.linear1(i["src"]))))
+        assert _rel(f, f0) < 1e-5
+
+
+def test_autocast_matches_unfused_composition():
+    """Under bf16 autocast the fused layers follow what the reference's modules would compute under autocast
+    (fp32 residual stream, bf16 GEMM operands): compare with that composition written in plain PyTorch."""
+    z = _load_golden()
+    dev = _dev()
+    enc, _ = _build_from_golden(z, dev)
+    i = _golden_inputs(z, dev)
+    layer = enc.layers[0]
+    refp = enc.get_reference_points(i["shapes"], i["valid"], dev)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        y = layer(i["src"], i["pos"], refp, i["shapes"], i["mask"])
+        src = i["src"]
+        src2 = layer.self_attn(src + i["pos"], refp, src, i["shapes"], i["mask"])
+        s = layer.norm1(src + src2)
+        y0 = layer.norm2(s + layer.linear2(torch.relu(layer.linear1(s))))
+    assert y.dtype == torch.float32 and y0.dtype == torch.float32
+    assert _rel(y, y0) < 2e-2
+    g = torch.autograd.grad(y.square().sum(), [i["src"], layer.norm2.weight, layer.linear1.bias], retain_graph=True)
+    g0 = torch.autograd.grad(y0.square().sum(), [i["src"], layer.norm2.weight, layer.linear1.bias])
+    for a, b in zip(g, g0):
+        assert _rel(a, b) < 5e-2
+
+
+def test_cpu_tensors_raise():
+    from kinet_b200.functions.layer_ops import AddLayerNormFunction, column_sum
+    with pytest.raises(RuntimeError, match="Not implemented on the CPU"):
+        AddLayerNormFunction.apply(torch.zeros(2, 8), None, None, torch.ones(8), torch.zeros(8), 1e-5, torch.float32, False)
+    with pytest.raises(RuntimeError, match="Not implemented on the CPU"):
+        column_sum(torch.zeros(2, 8))
