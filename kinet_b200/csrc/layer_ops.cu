@@ -52,7 +52,7 @@ __device__ __forceinline__ float warp_sum(float v)
 
 // KMAX: 16-byte vectors per lane; a row has C / 4 vectors, lane l owns vectors l, l + 32, ...
 template <int KMAX>
-__global__ void __launch_bounds__(kWarps * 32)
+__global__ void __launch_bounds__(kWarps * 32, KMAX <= 3 ? 4 : 2)
 add_layernorm_fwd_kernel(const kinet_ln_fwd_args a)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -137,7 +137,7 @@ __device__ __forceinline__ void fold_columns(float4 (&acc)[KMAX], float* smem, f
 }
 
 template <int KMAX>
-__global__ void __launch_bounds__(kWarps * 32)
+__global__ void __launch_bounds__(kWarps * 32, KMAX <= 2 ? 3 : (KMAX <= 4 ? 2 : 1))
 add_layernorm_bwd_kernel(const kinet_ln_bwd_args a)
 {
     extern __shared__ float smem[];   // [kWarps][C]
@@ -276,24 +276,43 @@ inline bool ok_dtype(int d) { return d == MSDA_F32 || d == MSDA_BF16; }
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 inline bool aligned_for(const void* p, int dtype) { return (reinterpret_cast<uintptr_t>(p) & (dtype == MSDA_F32 ? 15 : 7)) == 0; }
 
-inline int row_grid(int64_t rows)
+// One wave: as many CTAs as are resident at once (a grid of a few more CTAs than that runs a second, nearly
+// empty wave and doubles the kernel's time), never more than the scratch has rows for.
+template <typename K>
+int resident_ctas(K kernel, int threads, size_t smem)
+{
+    int dev = 0, sms = 148, per_sm = 1;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess || per_sm < 1) {
+        (void)cudaGetLastError();
+        per_sm = 1;
+    }
+    const int n = sms * per_sm;
+    return n < kMaxCtas ? n : kMaxCtas;
+}
+
+inline int row_grid(int64_t rows, int resident)
 {
     const int64_t need = (rows + kWarps - 1) / kWarps;
-    return (int)(need < kMaxCtas ? (need > 0 ? need : 1) : kMaxCtas);
+    return (int)(need < resident ? (need > 0 ? need : 1) : resident);
 }
 
 template <int KMAX>
 int launch_fwd(const kinet_ln_fwd_args& a, cudaStream_t st)
 {
-    add_layernorm_fwd_kernel<KMAX><<<row_grid(a.rows), kWarps * 32, 0, st>>>(a);
+    static thread_local int resident = 0;     // per kernel instantiation and host thread; one device per process
+    if (!resident) resident = resident_ctas(add_layernorm_fwd_kernel<KMAX>, kWarps * 32, 0);
+    add_layernorm_fwd_kernel<KMAX><<<row_grid(a.rows, resident), kWarps * 32, 0, st>>>(a);
     return (int)cudaGetLastError();
 }
 
 template <int KMAX>
-int launch_bwd(const kinet_ln_bwd_args& a, int grid, cudaStream_t st)
+int launch_bwd(const kinet_ln_bwd_args& a, int* grid, cudaStream_t st)
 {
     const size_t smem = (size_t)kWarps * a.C * sizeof(float);
-    add_layernorm_bwd_kernel<KMAX><<<grid, kWarps * 32, smem, st>>>(a);
+    *grid = row_grid(a.rows, resident_ctas(add_layernorm_bwd_kernel<KMAX>, kWarps * 32, smem));
+    add_layernorm_bwd_kernel<KMAX><<<*grid, kWarps * 32, smem, st>>>(a);
     return (int)cudaGetLastError();
 }
 
@@ -348,14 +367,14 @@ int kinet_b200_add_layernorm_backward(const kinet_ln_bwd_args* args, void* strea
         (a.dypos_lp && !aligned_for(a.dypos_lp, a.lp_dtype)) || !aligned16(a.partial))
         return MSDA_E_ALIGN;
     cudaStream_t st = (cudaStream_t)stream;
-    const int grid = a.rows > 0 ? row_grid(a.rows) : 0;
-    if (grid > 0) {
+    int grid = 0;
+    if (a.rows > 0) {
         const int k = (a.C + 127) / 128;
         int rc;
-        if (k <= 2) rc = launch_bwd<2>(a, grid, st);
-        else if (k <= 3) rc = launch_bwd<3>(a, grid, st);
-        else if (k <= 4) rc = launch_bwd<4>(a, grid, st);
-        else rc = launch_bwd<8>(a, grid, st);
+        if (k <= 2) rc = launch_bwd<2>(a, &grid, st);
+        else if (k <= 3) rc = launch_bwd<3>(a, &grid, st);
+        else if (k <= 4) rc = launch_bwd<4>(a, &grid, st);
+        else rc = launch_bwd<8>(a, &grid, st);
         if (rc) return rc;
     }
     const int n = 2 * a.C;

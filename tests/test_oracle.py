@@ -81,3 +81,30 @@ def test_oracle_empty_queries():
     assert oracle_forward(value, shapes, loc, attn).shape == (1, 0, 4)
     gv, gl, ga = oracle_backward(value, shapes, loc, attn, np.zeros((1, 0, 4), np.float32))
     assert not gv.any() and gl.size == 0 and ga.size == 0
+
+
+def test_layers_oracle_matches_reference_golden():
+    """oracle/layers_oracle.py (CPU restatement of the reference's encoder / decoder layers) against the golden
+    file produced by the reference's own classes (tests/golden/make_golden_layers.py): outputs and gradients."""
+    import os
+    import torch
+    from oracle import layers_oracle as lo
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "layers_f32.npz"))
+    t = lambda k: torch.from_numpy(z[k])
+    p = {k[2:]: t(k).requires_grad_(True) for k in z.files if k.startswith("p:")}
+    levels = [tuple(int(v) for v in hw) for hw in z["levels"]]
+    shapes = t("levels").long()
+    cfg = (8, 2, 2)                                    # heads, levels, points of the golden model
+    src, pos = t("src").requires_grad_(True), t("pos").requires_grad_(True)
+    tgt, qpos = t("tgt").requires_grad_(True), t("qpos").requires_grad_(True)
+    memory = lo.encoder(p, "enc.", 2, src, levels, shapes, t("valid"), pos, t("mask"), cfg)
+    out, ref_out = lo.decoder(p, "dec.", 2, tgt, t("ref"), memory, shapes, t("valid"), qpos, t("mask"), t("qmask"), cfg)
+    _close(memory.detach().numpy(), z["memory"], 1e-4, 1e-5)
+    _close(out.detach().numpy(), z["out"], 1e-4, 1e-5)
+    assert np.array_equal(ref_out.numpy(), z["ref_out"])
+    loss = (memory * t("w_mem")).sum() + (out * t("w_out")).sum()
+    names = [k[2:] for k in z.files if k.startswith("g:")]
+    grads = torch.autograd.grad(loss, [src, pos, tgt, qpos] + [p[k] for k in names])
+    for k, g in zip(["g_src", "g_pos", "g_tgt", "g_qpos"] + ["g:" + k for k in names], grads):
+        scale = float(np.abs(z[k]).max())
+        assert float(np.abs(g.numpy() - z[k]).max()) <= 2e-4 * max(scale, 1e-6), k
