@@ -1,0 +1,117 @@
+"""Per-frame CUDA graphs for tracking inference with a VARIABLE number of queries.
+
+In the reference's tracker every frame runs the deformable transformer once with ``num_queries`` object queries
+plus one track query per live track (src/trackformer/models/tracker.py:286-309, 536-542;
+deformable_transformer.py:133-257), so the decoder's query count changes from frame to frame while the pyramid
+does not.  ``FrameGraphs`` records
+
+  * ONE graph of the encoder (fixed shapes), and
+  * one graph of the decoder per BUCKET of query counts: the queries are padded up to the next multiple of
+    ``bucket`` and the padding rows are switched off with the decoder's own ``query_attn_mask``
+    (key_padding_mask of the self-attention, zeroed sampling weights in MSDeformAttn,
+    deformable_transformer.py:371, 379-381) -- the mechanism the reference already uses for padded track
+    queries in a batch, so real queries see exactly the keys they would see unpadded,
+
+and replays them: no per-kernel launch cost, no device->host sync, nothing allocated after the first frame of a
+bucket.  Inputs are copied into the graphs' static buffers; outputs are views of static buffers (valid until
+the next call).  Weights are read from where they were at recording time: call ``reset()`` after changing
+them.  Inference only (``torch.no_grad``); ``encoder`` / ``decoder`` are kinet_b200.modules'
+DeformableTransformerEncoder / DeformableTransformerDecoder.
+"""
+import torch
+
+
+class FrameGraphs:
+    def __init__(self, encoder, decoder, spatial_shapes, bucket=32, autocast_dtype=torch.bfloat16, warmup=2):
+        if bucket <= 0:
+            raise ValueError("bucket must be positive")
+        self.encoder, self.decoder = encoder, decoder
+        self.shapes = spatial_shapes
+        self.bucket = int(bucket)
+        self.autocast_dtype = autocast_dtype
+        self.warmup = int(warmup)
+        self.reset()
+
+    def reset(self):
+        """Forget every recorded graph (after a weight update, or to release their memory)."""
+        self._enc = None          # (graph, src_buf, pos_buf, valid_buf, mask_buf, memory stream)
+        self._dec = {}            # padded query count -> (graph, static inputs, out, ref_out)
+        self.replays = 0
+
+    @property
+    def recorded_buckets(self):
+        return sorted(self._dec)
+
+    def _amp(self):
+        return torch.autocast("cuda", dtype=self.autocast_dtype, enabled=self.autocast_dtype is not None)
+
+    def _record(self, fn):
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(self.warmup):     # fills the per-tensor caches (shape check, level grids, weight copies)
+                fn()
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            out = fn()
+        return graph, out
+
+    def _encode(self, src, pos, valid_ratios, padding_mask):
+        if self._enc is None or self._enc[1].shape != src.shape:
+            bufs = (torch.empty_like(src), torch.empty_like(pos), torch.empty_like(valid_ratios),
+                    None if padding_mask is None else torch.empty_like(padding_mask))
+            for b, t in zip(bufs, (src, pos, valid_ratios, padding_mask)):
+                if b is not None:
+                    b.copy_(t)
+
+            def fn():
+                with torch.no_grad(), self._amp():
+                    return self.encoder(bufs[0], self.shapes, bufs[2], bufs[1], bufs[3], return_stream=True)
+            graph, mem = self._record(fn)
+            self._enc = (graph,) + bufs + (mem,)
+            self._dec = {}
+        graph, src_b, pos_b, valid_b, mask_b, mem = self._enc
+        src_b.copy_(src, non_blocking=True)
+        pos_b.copy_(pos, non_blocking=True)
+        valid_b.copy_(valid_ratios, non_blocking=True)
+        if mask_b is not None:
+            mask_b.copy_(padding_mask, non_blocking=True)
+        graph.replay()
+        return mem, valid_b, mask_b
+
+    def __call__(self, src, pos, valid_ratios, tgt, reference_points, query_pos, padding_mask=None,
+                 query_attn_mask=None):
+        """src, pos (N, S, C); valid_ratios (N, L, 2); tgt, query_pos (N, Lq, C); reference_points (N, Lq, 2|4);
+        padding_mask (N, S) bool or None (the choice is fixed at the first call); query_attn_mask (N, Lq) bool
+        or None.  Returns (hs, reference_points_out, memory) like decoder(...) + encoder(...): hs is
+        (N, Lq, C), or (layers, N, Lq, C) when the decoder returns intermediates."""
+        N, Lq, C = tgt.shape
+        mem, valid_b, mask_b = self._encode(src, pos, valid_ratios, padding_mask)
+        B = max(self.bucket, -(-Lq // self.bucket) * self.bucket)
+        if B not in self._dec:
+            dev = tgt.device
+            tgt_b = torch.zeros(N, B, C, dtype=tgt.dtype, device=dev)
+            qpos_b = torch.zeros(N, B, C, dtype=query_pos.dtype, device=dev)
+            ref_b = torch.full((N, B, reference_points.shape[-1]), 0.5, dtype=reference_points.dtype, device=dev)
+            qmask_b = torch.ones(N, B, dtype=torch.bool, device=dev)
+            qmask_b[:, :Lq] = False if query_attn_mask is None else query_attn_mask
+            tgt_b[:, :Lq], qpos_b[:, :Lq], ref_b[:, :Lq] = tgt, query_pos, reference_points
+
+            def fn():
+                with torch.no_grad(), self._amp():
+                    return self.decoder(tgt_b, ref_b, mem, self.shapes, valid_b, qpos_b, mask_b, qmask_b)
+            graph, (hs, ref_out) = self._record(fn)
+            self._dec[B] = (graph, tgt_b, qpos_b, ref_b, qmask_b, hs, ref_out)
+        graph, tgt_b, qpos_b, ref_b, qmask_b, hs, ref_out = self._dec[B]
+        tgt_b[:, :Lq].copy_(tgt, non_blocking=True)
+        qpos_b[:, :Lq].copy_(query_pos, non_blocking=True)
+        ref_b[:, :Lq].copy_(reference_points, non_blocking=True)
+        qmask_b.fill_(True)
+        if query_attn_mask is None:
+            qmask_b[:, :Lq] = False
+        else:
+            qmask_b[:, :Lq].copy_(query_attn_mask, non_blocking=True)
+        graph.replay()
+        self.replays += 1
+        return hs[..., :Lq, :], ref_out[..., :Lq, :], mem.x

@@ -200,10 +200,28 @@ class LinearFunction(Function):
         return dx, dw, db
 
 
+def _lp_params(layer, dtype):
+    """Low-precision copies of an nn.Linear's parameters for inference under autocast, made once and kept on
+    the layer until a parameter changes (in-place updates bump ``_version``; re-assignment changes the
+    identity).  Unlike autocast's own cache they outlive the autocast region, so a per-frame CUDA graph
+    recorded after one eager warm-up holds no weight casts.  A graph keeps reading the copies it was recorded
+    with: re-record it after changing the weights."""
+    w, b = layer.weight, layer.bias
+    key = (dtype, id(w), w._version, id(b), b._version if b is not None else 0)
+    hit = layer.__dict__.get("_kinet_lp")
+    if hit is None or hit[0] != key:
+        hit = (key, w.detach().to(dtype), b.detach().to(dtype) if b is not None else None)
+        layer.__dict__["_kinet_lp"] = hit
+    return hit[1], hit[2]
+
+
 def linear(x, layer):
-    """``layer(x)`` for an nn.Linear: the plain (autocast-cached) F.linear when no parameter gradient is
-    needed, LinearFunction otherwise."""
-    if (x.is_cuda and layer.bias is not None and torch.is_grad_enabled()
-            and (layer.weight.requires_grad or layer.bias.requires_grad)):
+    """``layer(x)`` for an nn.Linear.  With parameter gradients: LinearFunction (fused bias-gradient sum).
+    Without (inference): F.linear, under CUDA autocast on low-precision parameter copies cached on the layer."""
+    if x.is_cuda and torch.is_grad_enabled() and layer.bias is not None \
+            and (layer.weight.requires_grad or layer.bias.requires_grad):
         return LinearFunction.apply(x, layer.weight, layer.bias)
+    if x.is_cuda and not torch.is_grad_enabled() and torch.is_autocast_enabled("cuda"):
+        w, b = _lp_params(layer, torch.get_autocast_dtype("cuda"))
+        return F.linear(x if x.dtype == w.dtype else x.to(w.dtype), w, b)
     return F.linear(x, layer.weight, layer.bias)

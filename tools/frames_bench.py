@@ -27,6 +27,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--frames", type=int, default=200)
     ap.add_argument("--eager", action="store_true", help="no CUDA graph (launch-bound reference point)")
+    ap.add_argument("--varying-queries", action="store_true",
+                    help="500 object queries + a number of track queries that changes every frame (20..60), through "
+                         "kinet_b200.frame_graph.FrameGraphs (one decoder graph per bucket of 32 queries)")
     ap.add_argument("--layers", choices=("fused", "torch"), default="fused",
                     help="fused: kinet_b200.modules encoder/decoder classes; torch: the same layers as plain PyTorch ops")
     args = ap.parse_args()
@@ -56,14 +59,27 @@ def main():
         with torch.no_grad():
             return model(src, pos)
 
+    if args.varying_queries:
+        from kinet_b200.frame_graph import FrameGraphs
+        assert args.layers == "fused"
+        shapes = torch.as_tensor(levels, dtype=torch.long, device=dev)
+        valid = torch.ones(1, len(levels), 2, device=dev)
+        fg = FrameGraphs(model.encoder, model.decoder, shapes, bucket=32)
+        counts = [500 + 20 + (7 * i) % 41 for i in range(16)]                  # 520 .. 560 queries
+        qs = [(torch.randn(1, n, 288, device=dev), torch.rand(1, n, 2, device=dev) * 0.8 + 0.1,
+               torch.randn(1, n, 288, device=dev) * 0.1) for n in counts]
+        amp.__exit__(None, None, None)           # FrameGraphs manages autocast itself
+
     side = torch.cuda.Stream()
     side.wait_stream(torch.cuda.current_stream())
     with torch.cuda.stream(side):
-        for _ in range(3):
+        for _ in range(0 if args.varying_queries else 3):
             frame()
     torch.cuda.current_stream().wait_stream(side)
     torch.cuda.synchronize()
-    if args.eager:
+    if args.varying_queries:
+        step = None
+    elif args.eager:
         step = frame
     else:
         graph = torch.cuda.CUDAGraph()
@@ -73,6 +89,10 @@ def main():
 
     def run(n):
         for i in range(n):
+            if args.varying_queries:
+                tgt, ref, qpos = qs[i & 15]
+                fg(frames[i & 3], pos, valid, tgt, ref, qpos)
+                continue
             src.copy_(frames[i & 3], non_blocking=True)     # a new frame lands in the static input buffer
             step()
 
@@ -92,10 +112,11 @@ def main():
         ms = float(ms)
         print(json.dumps({"metric": "tracking_transformer_frames_per_s", "value": world * args.frames / ms * 1e3,
                           "n_gpus": world, "ms_per_frame_per_gpu": ms / args.frames, "frames_per_gpu": args.frames,
-                          "mode": "eager" if args.eager else "cuda_graph", "layers": args.layers,
+                          "mode": "frame_graphs_varying_queries" if args.varying_queries else ("eager" if args.eager else "cuda_graph"), "layers": args.layers,
                           "config": "MOT17 750x1333 pyramid, S=20906, d=288 (D=36), 6 enc + 6 dec layers, "
                                     "560 queries, bf16 autocast, forward; replicas, no communication"}))
-    amp.__exit__(None, None, None)
+    if not args.varying_queries:
+        amp.__exit__(None, None, None)
     if world > 1:
         torch.distributed.destroy_process_group()
 
