@@ -78,6 +78,12 @@ size_t kinet_b200_colsum_partial_floats(int32_t n_columns);
 int kinet_b200_colsum(const void* a, int32_t a_dtype, int64_t rows, int32_t C,
                       void* out, int32_t out_dtype, float* partial, void* stream);
 
+/* ReLU backward fused with the column sum: dh = dy * (h > 0) is written (dtype of dy / h) and summed
+ * over the rows in the same pass -- the bias gradient of the Linear layer feeding a ReLU
+ * (deformable_transformer.py:283, :362: linear2(dropout(activation(linear1(x))))).  h is the ReLU's OUTPUT. */
+int kinet_b200_relu_backward_colsum(const void* dy, const void* h, int32_t dtype, int64_t rows, int32_t C,
+                                    void* dh, void* out, int32_t out_dtype, float* partial, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

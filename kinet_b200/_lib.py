@@ -35,7 +35,7 @@ EXPORTS = ("msda_b200_abi_version", "msda_b200_error_string", "msda_b200_forward
            "msda_b200_last_launch_count", "msda_b200_trace_next")
 # include/kinet_layers_b200.h (glue kernels of the layers that call the op)
 LAYER_EXPORTS = ("kinet_b200_add_layernorm_forward", "kinet_b200_add_layernorm_backward",
-                 "kinet_b200_colsum_partial_floats", "kinet_b200_colsum")
+                 "kinet_b200_colsum_partial_floats", "kinet_b200_colsum", "kinet_b200_relu_backward_colsum")
 
 
 class KinetLnFwdArgs(ctypes.Structure):
@@ -105,6 +105,9 @@ def load():
     lib.kinet_b200_colsum_partial_floats.argtypes = [ctypes.c_int32]
     lib.kinet_b200_colsum.restype = i
     lib.kinet_b200_colsum.argtypes = [vp, ctypes.c_int32, ctypes.c_int64, ctypes.c_int32, vp, ctypes.c_int32, vp, vp]
+    lib.kinet_b200_relu_backward_colsum.restype = i
+    lib.kinet_b200_relu_backward_colsum.argtypes = [vp, vp, ctypes.c_int32, ctypes.c_int64, ctypes.c_int32, vp, vp,
+                                                    ctypes.c_int32, vp, vp]
     if lib.msda_b200_abi_version() != 2:
         raise RuntimeError("kinet_b200: libmsda_b200.so ABI version mismatch")
     _lib = lib

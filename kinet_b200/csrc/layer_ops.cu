@@ -234,28 +234,40 @@ colsum_finalize_kernel(const float* __restrict__ partial, int G, int n, void* ou
 
 // Column sums of a [rows][C] matrix.  Thread layout: tx = column vector (4 columns), ty = row lane;
 // a CTA walks rows ty, ty + RL, ... of its slab with 4 independent loads in flight per thread.
+// RELU: the matrix summed is dh = dy * (h > 0) (ReLU backward), which is also written out -- the bias
+// gradient of the Linear layer in front of a ReLU costs no pass of its own.
+template <bool RELU>
 __global__ void __launch_bounds__(256)
-colsum_kernel(const void* __restrict__ a, int dtype, int64_t rows, int C, int RL, float* __restrict__ partial)
+colsum_kernel(const void* __restrict__ a, const void* __restrict__ h, void* __restrict__ dh, int dtype,
+              int64_t rows, int C, int RL, float* __restrict__ partial)
 {
     extern __shared__ float smem[];   // [RL][C]
     const int nvec = C >> 2;
     const int tx = threadIdx.x % nvec, ty = threadIdx.x / nvec;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto fetch = [&](int64_t row) {
+        const size_t i = (size_t)row * C + 4 * tx;
+        float4 v = load4(a, dtype, i);
+        if constexpr (RELU) {
+            const float4 o = load4(h, dtype, i);
+            v.x = o.x > 0.f ? v.x : 0.f; v.y = o.y > 0.f ? v.y : 0.f;
+            v.z = o.z > 0.f ? v.z : 0.f; v.w = o.w > 0.f ? v.w : 0.f;
+            store4(dh, dtype, i, v);
+        }
+        return v;
+    };
     if (ty < RL) {
         const int64_t stride = (int64_t)gridDim.x * RL;
         int64_t row = (int64_t)blockIdx.x * RL + ty;
         for (; row + 3 * stride < rows; row += 4 * stride) {
-            const float4 v0 = load4(a, dtype, (size_t)row * C + 4 * tx);
-            const float4 v1 = load4(a, dtype, (size_t)(row + stride) * C + 4 * tx);
-            const float4 v2 = load4(a, dtype, (size_t)(row + 2 * stride) * C + 4 * tx);
-            const float4 v3 = load4(a, dtype, (size_t)(row + 3 * stride) * C + 4 * tx);
+            const float4 v0 = fetch(row), v1 = fetch(row + stride), v2 = fetch(row + 2 * stride), v3 = fetch(row + 3 * stride);
             acc.x += (v0.x + v1.x) + (v2.x + v3.x);
             acc.y += (v0.y + v1.y) + (v2.y + v3.y);
             acc.z += (v0.z + v1.z) + (v2.z + v3.z);
             acc.w += (v0.w + v1.w) + (v2.w + v3.w);
         }
         for (; row < rows; row += stride) {
-            const float4 v0 = load4(a, dtype, (size_t)row * C + 4 * tx);
+            const float4 v0 = fetch(row);
             acc.x += v0.x; acc.y += v0.y; acc.z += v0.z; acc.w += v0.w;
         }
         reinterpret_cast<float4*>(smem + (size_t)ty * C)[tx] = acc;
@@ -378,13 +390,17 @@ int kinet_b200_add_layernorm_backward(const kinet_ln_bwd_args* args, void* strea
     return (int)cudaGetLastError();
 }
 
-int kinet_b200_colsum(const void* a, int32_t a_dtype, int64_t rows, int32_t C, void* out, int32_t out_dtype,
-                      float* partial, void* stream)
+static int colsum_common(const void* a, const void* h, void* dh, int32_t a_dtype, int64_t rows, int32_t C, void* out,
+                         int32_t out_dtype, float* partial, void* stream)
 {
+    const bool relu = h != nullptr;
     if (!out || !partial || (rows > 0 && !a)) return MSDA_E_NULL;
+    if (relu && !dh) return MSDA_E_NULL;
     if (rows < 0 || C <= 0 || (C & 3) || C > KINET_LN_MAX_C) return MSDA_E_SHAPE;
     if (!ok_dtype(a_dtype) || !ok_dtype(out_dtype)) return MSDA_E_DTYPE;
-    if ((rows > 0 && !aligned_for(a, a_dtype)) || !aligned16(partial)) return MSDA_E_ALIGN;
+    if ((rows > 0 && !aligned_for(a, a_dtype)) || !aligned16(partial) ||
+        (relu && (!aligned_for(h, a_dtype) || !aligned_for(dh, a_dtype))))
+        return MSDA_E_ALIGN;
     cudaStream_t st = (cudaStream_t)stream;
     const int nvec = C >> 2;
     const int RL = 256 / nvec;     // row lanes per CTA (nvec <= 256)
@@ -393,11 +409,26 @@ int kinet_b200_colsum(const void* a, int32_t a_dtype, int64_t rows, int32_t C, v
         // at least 8 rows per row lane, at most kMaxCtas CTAs
         const int64_t want = (rows + (int64_t)RL * 8 - 1) / ((int64_t)RL * 8);
         grid = (int)(want < kMaxCtas ? (want > 0 ? want : 1) : kMaxCtas);
-        colsum_kernel<<<grid, 256, (size_t)RL * C * sizeof(float), st>>>(a, a_dtype, rows, C, RL, partial);
+        const size_t smem = (size_t)RL * C * sizeof(float);
+        if (relu) colsum_kernel<true><<<grid, 256, smem, st>>>(a, h, dh, a_dtype, rows, C, RL, partial);
+        else colsum_kernel<false><<<grid, 256, smem, st>>>(a, nullptr, nullptr, a_dtype, rows, C, RL, partial);
         if (int rc = (int)cudaGetLastError()) return rc;
     }
     colsum_finalize_kernel<<<(C + 31) / 32, 1024, 0, st>>>(partial, grid, C, out, out_dtype);
     return (int)cudaGetLastError();
+}
+
+int kinet_b200_colsum(const void* a, int32_t a_dtype, int64_t rows, int32_t C, void* out, int32_t out_dtype,
+                      float* partial, void* stream)
+{
+    return colsum_common(a, nullptr, nullptr, a_dtype, rows, C, out, out_dtype, partial, stream);
+}
+
+int kinet_b200_relu_backward_colsum(const void* dy, const void* h, int32_t dtype, int64_t rows, int32_t C, void* dh,
+                                    void* out, int32_t out_dtype, float* partial, void* stream)
+{
+    if (!h) return MSDA_E_NULL;
+    return colsum_common(dy, h, dh, dtype, rows, C, out, out_dtype, partial, stream);
 }
 
 }  // extern "C"

@@ -164,40 +164,72 @@ def colsum_supported(a2d):
             and a2d.shape[1] % 4 == 0 and 0 < a2d.shape[1] <= MAX_C)
 
 
+def relu_backward_column_sum(dy2d, h2d, out_dtype):
+    """dh = dy * (h > 0) and its column sums in one pass (h = the ReLU's output) -> (dh, sums)."""
+    rows, C = dy2d.shape
+    lib = _lib.load()
+    dh = torch.empty_like(dy2d)
+    out = torch.empty(C, dtype=out_dtype, device=dy2d.device)
+    partial = torch.empty(lib.kinet_b200_colsum_partial_floats(C), dtype=torch.float32, device=dy2d.device)
+    with _lib.device_guard(dy2d.device):
+        rc = lib.kinet_b200_relu_backward_colsum(_ptr(dy2d), _ptr(h2d), _lib.dtype_code(dy2d.dtype), rows, C, _ptr(dh),
+                                                 _ptr(out), _lib.dtype_code(out_dtype), _ptr(partial),
+                                                 _lib.raw_stream(dy2d.device))
+    _lib.check(rc, "kinet_b200_relu_backward_colsum")
+    return dh, out
+
+
 class LinearFunction(Function):
-    """y = x @ weight.T + bias (cuBLAS, as nn.Linear); under CUDA autocast the operands are cast to the
-    autocast dtype like F.linear would.  Backward: two cuBLAS GEMMs and the fused column sum for the bias."""
+    """y = act(x @ weight.T + bias), act = identity or ReLU (cuBLAS GEMMs, the ReLU in the GEMM's epilogue).
+    Under CUDA autocast the operands are cast to the autocast dtype like F.linear would; ``w_lp`` / ``b_lp``
+    are optional ready-made low-precision copies (training.FlatParams keeps them current with one cast kernel
+    per step).  Backward: two cuBLAS GEMMs (the weight gradient leaves the GEMM in the parameter's dtype) and
+    ONE fused pass for the bias gradient (+ the ReLU's backward)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias):
+    def forward(ctx, x, weight, bias, relu, w_lp, b_lp):
         lp = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else None
         w, b, x_dtype = weight, bias, x.dtype
         if lp is not None:
-            x, w, b = x.to(lp), weight.to(lp), bias.to(lp)
+            x = x.to(lp)
+            w, b = (w_lp, b_lp) if (w_lp is not None and w_lp.dtype == lp) else (weight.to(lp), bias.to(lp))
         elif x.dtype != weight.dtype:
             x = x.to(weight.dtype)
+        x2 = x.reshape(-1, x.shape[-1])
         with torch.autocast("cuda", enabled=False):
-            y = F.linear(x, w, b)
-        ctx.save_for_backward(x, w)
-        ctx.param_dtypes = (weight.dtype, bias.dtype)
-        ctx.x_dtype = x_dtype
-        return y
+            if relu:
+                y2 = torch._addmm_activation(b, x2, w.t(), use_gelu=False)
+            else:
+                y2 = torch.addmm(b, x2, w.t())
+        ctx.save_for_backward(x2, w, y2 if relu else None)
+        ctx.meta = (weight.dtype, bias.dtype, x_dtype, x.shape, bool(relu))
+        return y2.view(x.shape[:-1] + (w.shape[0],))
 
     @staticmethod
     @once_differentiable
     def backward(ctx, dy):
-        x, w = ctx.saved_tensors
+        x2, w, y2 = ctx.saved_tensors
+        wd, bd, x_dtype, x_shape, relu = ctx.meta
         dy2 = dy.reshape(-1, dy.shape[-1])
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
-        x2 = x.reshape(-1, x.shape[-1])
-        wd, bd = ctx.param_dtypes
-        dx = (dy2 @ w).view(x.shape).to(ctx.x_dtype) if ctx.needs_input_grad[0] else None
-        dw = (dy2.t() @ x2).to(wd) if ctx.needs_input_grad[1] else None
+        fused = colsum_supported(dy2)
         db = None
-        if ctx.needs_input_grad[2]:
-            db = column_sum(dy2, bd) if colsum_supported(dy2) else dy2.sum(0).to(bd)
-        return dx, dw, db
+        if relu:
+            if fused:
+                dy2, db = relu_backward_column_sum(dy2, y2, bd)
+            else:
+                dy2 = dy2 * (y2 > 0).to(dy2.dtype)
+        if db is None and ctx.needs_input_grad[2]:
+            db = column_sum(dy2, bd) if fused else dy2.sum(0).to(bd)
+        dx = (dy2 @ w).view(x_shape).to(x_dtype) if ctx.needs_input_grad[0] else None
+        dw = None
+        if ctx.needs_input_grad[1]:
+            if wd == torch.float32 and dy2.dtype in (torch.bfloat16, torch.float16):
+                dw = torch.mm(dy2.t(), x2, out_dtype=torch.float32)    # fp32 straight out of the GEMM: no cast pass
+            else:
+                dw = (dy2.t() @ x2).to(wd)
+        return dx, dw, db if ctx.needs_input_grad[2] else None, None, None, None
 
 
 def _lp_params(layer, dtype):
@@ -215,13 +247,29 @@ def _lp_params(layer, dtype):
     return hit[1], hit[2]
 
 
-def linear(x, layer):
-    """``layer(x)`` for an nn.Linear.  With parameter gradients: LinearFunction (fused bias-gradient sum).
-    Without (inference): F.linear, under CUDA autocast on low-precision parameter copies cached on the layer."""
-    if x.is_cuda and torch.is_grad_enabled() and layer.bias is not None \
-            and (layer.weight.requires_grad or layer.bias.requires_grad):
-        return LinearFunction.apply(x, layer.weight, layer.bias)
-    if x.is_cuda and not torch.is_grad_enabled() and torch.is_autocast_enabled("cuda"):
-        w, b = _lp_params(layer, torch.get_autocast_dtype("cuda"))
-        return F.linear(x if x.dtype == w.dtype else x.to(w.dtype), w, b)
-    return F.linear(x, layer.weight, layer.bias)
+def linear_params(x, weight, bias, relu=False, mirror=None):
+    """act(x @ weight.T + bias) on explicit parameter tensors (e.g. slices of an in_proj_weight).
+    mirror: optional (weight, bias) low-precision copies kept current by the caller."""
+    if x.is_cuda and torch.is_grad_enabled() and bias is not None and (weight.requires_grad or bias.requires_grad):
+        w_lp, b_lp = mirror if mirror is not None else (None, None)
+        return LinearFunction.apply(x, weight, bias, relu, w_lp, b_lp)
+    if mirror is not None and x.is_cuda and torch.is_autocast_enabled("cuda") \
+            and mirror[0].dtype == torch.get_autocast_dtype("cuda"):
+        weight, bias = mirror
+        x = x if x.dtype == weight.dtype else x.to(weight.dtype)
+    if relu and x.is_cuda and bias is not None and x.dtype == weight.dtype and not torch.is_grad_enabled():
+        y2 = torch._addmm_activation(bias, x.reshape(-1, x.shape[-1]), weight.t(), use_gelu=False)
+        return y2.view(x.shape[:-1] + (weight.shape[0],))
+    y = F.linear(x, weight, bias)
+    return F.relu(y) if relu else y
+
+
+def linear(x, layer, relu=False):
+    """``act(layer(x))`` for an nn.Linear, act = identity or ReLU.  With parameter gradients: LinearFunction.
+    Without (inference): one GEMM (ReLU in its epilogue), under CUDA autocast on low-precision parameter copies
+    cached on the layer (or kept current by training.FlatParams)."""
+    mirror = layer.__dict__.get("_kinet_mirror")
+    if mirror is None and x.is_cuda and not torch.is_grad_enabled() and torch.is_autocast_enabled("cuda") \
+            and layer.bias is not None:
+        mirror = _lp_params(layer, torch.get_autocast_dtype("cuda"))
+    return linear_params(x, layer.weight, layer.bias, relu, mirror)

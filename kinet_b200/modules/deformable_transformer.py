@@ -23,7 +23,7 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
-from ..functions.layer_ops import add_layer_norm, linear
+from ..functions.layer_ops import add_layer_norm, linear, linear_params
 from .ms_deform_attn import MSDeformAttn
 
 
@@ -80,6 +80,37 @@ def _level_grids(spatial_shapes, device):
     return out
 
 
+def _act_linear(x, layer, activation):
+    """activation(layer(x)); ReLU rides in the GEMM's epilogue (and, in the backward, in the bias-gradient pass)."""
+    if activation is F.relu:
+        return linear(x, layer, relu=True)
+    return activation(linear(x, layer))
+
+
+def _self_attention(mha, q_in, v_in, key_padding_mask):
+    """nn.MultiheadAttention(q, k = q, v)[0] on batch-first (N, Lq, C) inputs, computed from the module's own
+    parameters (in_proj_weight / in_proj_bias / out_proj: checkpoints unchanged): one GEMM for q and k, one for
+    v, F.scaled_dot_product_attention, out_proj.  Same arithmetic as the reference's call
+    (deformable_transformer.py:369-373, need_weights aside); the projections go through ``linear_params`` so their
+    bias gradients are fused column sums instead of 17 us generic reductions over 600 rows."""
+    N, Lq, C = q_in.shape
+    H = mha.num_heads
+    w, b = mha.in_proj_weight, mha.in_proj_bias
+    mirror = mha.__dict__.get("_kinet_mirror")
+    m_qk = m_v = None
+    if mirror is not None:
+        m_qk, m_v = (mirror[0][:2 * C], mirror[1][:2 * C]), (mirror[0][2 * C:], mirror[1][2 * C:])
+    qk = linear_params(q_in, w[:2 * C], b[:2 * C], False, m_qk)
+    v = linear_params(v_in, w[2 * C:], b[2 * C:], False, m_v)
+    q, k = qk.split(C, dim=-1)
+    q, k, v = (t.reshape(N, Lq, H, C // H).transpose(1, 2) for t in (q, k, v))
+    mask = None
+    if key_padding_mask is not None:
+        mask = ~key_padding_mask[:, None, None, :]                 # True = may attend
+    o = F.scaled_dot_product_attention(q, k, v, attn_mask=mask, dropout_p=mha.dropout if mha.training else 0.0)
+    return linear(o.transpose(1, 2).reshape(N, Lq, C), mha.out_proj)
+
+
 class _Stream:
     """Residual stream between fused steps: x (stream dtype), and the GEMM-side copies of x and x + pos."""
     __slots__ = ("x", "x_lp", "xpos_lp")
@@ -131,7 +162,7 @@ class DeformableTransformerEncoderLayer(nn.Module):
         return self._ffn(_Stream.start(src, None), None, False).x
 
     def _ffn(self, st, pos, want_pos):
-        h = self.dropout2(self.activation(linear(st.x_lp, self.linear1)))
+        h = self.dropout2(_act_linear(st.x_lp, self.linear1, self.activation))
         return _norm_step(st.x, self.dropout3(linear(h, self.linear2)), self.norm2, pos, want_pos)
 
     def _forward_stream(self, st, pos, reference_points, spatial_shapes, padding_mask, last):
@@ -200,15 +231,19 @@ class DeformableTransformerDecoderLayer(nn.Module):
         return self._ffn(_Stream.start(tgt, None), None, False).x
 
     def _ffn(self, st, pos, want_pos):
-        h = self.dropout3(self.activation(linear(st.x_lp, self.linear1)))
+        h = self.dropout3(_act_linear(st.x_lp, self.linear1, self.activation))
         return _norm_step(st.x, self.dropout4(linear(h, self.linear2)), self.norm3, pos, want_pos)
 
     def _forward_stream(self, st, query_pos, reference_points, src, src_spatial_shapes,
                         src_padding_mask, query_attn_mask, last):
         # self attention over the queries: q = k = tgt + query_pos, v = tgt   (reference :367-376)
-        q = st.xpos_lp.transpose(0, 1)
-        tgt2 = self.self_attn(q, q, st.x_lp.transpose(0, 1), key_padding_mask=query_attn_mask,
-                              need_weights=False)[0].transpose(0, 1)
+        mha = self.self_attn
+        if mha._qkv_same_embed_dim and mha.in_proj_bias is not None and mha.bias_k is None and not mha.add_zero_attn:
+            tgt2 = _self_attention(mha, st.xpos_lp, st.x_lp, query_attn_mask)
+        else:
+            q = st.xpos_lp.transpose(0, 1)
+            tgt2 = mha(q, q, st.x_lp.transpose(0, 1), key_padding_mask=query_attn_mask,
+                       need_weights=False)[0].transpose(0, 1)
         st = _norm_step(st.x, self.dropout2(tgt2), self.norm2, query_pos, query_pos is not None)
         # cross attention into the encoder memory (:378-383)
         tgt2 = self.cross_attn(st.xpos_lp, reference_points, src, src_spatial_shapes,

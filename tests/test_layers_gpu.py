@@ -118,7 +118,7 @@ def test_linear_function_matches_nn_linear(amp):
     with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
         y = linear(x, lin)
         y0 = lin(x)
-    assert y.dtype == y0.dtype and torch.equal(y, y0)
+    assert y.dtype == y0.dtype and _rel(y, y0) < (1e-2 if amp else 1e-5)
     g = torch.autograd.grad((y.float() * w).sum(), (x, lin.weight, lin.bias))
     g0 = torch.autograd.grad((y0.float() * w).sum(), (x, lin.weight, lin.bias))
     tol = 2e-2 if amp else 1e-5
@@ -127,6 +127,88 @@ def test_linear_function_matches_nn_linear(amp):
     # the bias gradient is an fp32 sum of the (rounded) upstream gradient: compare with fp64
     up = w.to(y.dtype).double().sum((0, 1))
     assert _rel(g[2], up) < 1e-5
+
+
+@pytest.mark.parametrize("amp", [False, True])
+def test_linear_relu_fused(amp):
+    """ReLU in the GEMM epilogue forward, ReLU backward fused with the bias-gradient column sum."""
+    from kinet_b200.functions.layer_ops import linear
+    dev = _dev()
+    torch.manual_seed(1)
+    lin = torch.nn.Linear(256, 1024).to(dev)
+    x = torch.randn(2, 555, 256, device=dev, requires_grad=True)
+    w = torch.randn(2, 555, 1024, device=dev)
+    with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
+        y = linear(x, lin, relu=True)
+        y0 = torch.relu(lin(x))
+        with torch.no_grad():
+            yi = linear(x, lin, relu=True)          # inference path: cached low-precision weights + epilogue ReLU
+    tol = 2e-2 if amp else 1e-5
+    assert y.dtype == y0.dtype == yi.dtype and _rel(y, y0) < tol and _rel(yi, y0) < tol
+    assert float(y.min()) == 0.0
+    g = torch.autograd.grad((y.float() * w).sum(), (x, lin.weight, lin.bias))
+    g0 = torch.autograd.grad((y0.float() * w).sum(), (x, lin.weight, lin.bias))
+    for a, b in zip(g, g0):
+        assert a.dtype == b.dtype and _rel(a, b) < (3e-2 if amp else 1e-5)
+
+
+@pytest.mark.parametrize("masked", [False, True])
+def test_self_attention_matches_nn_multihead_attention(masked):
+    from kinet_b200.modules.deformable_transformer import _self_attention
+    dev = _dev()
+    torch.manual_seed(2)
+    mha = torch.nn.MultiheadAttention(128, 8, dropout=0.0).to(dev)
+    with torch.no_grad():
+        mha.in_proj_bias.normal_(0, 0.1)
+        mha.out_proj.bias.normal_(0, 0.1)
+    q = torch.randn(2, 37, 128, device=dev, requires_grad=True)
+    v = torch.randn(2, 37, 128, device=dev, requires_grad=True)
+    mask = None
+    if masked:
+        mask = torch.zeros(2, 37, dtype=torch.bool, device=dev)
+        mask[0, -5:] = True
+    out = _self_attention(mha, q, v, mask)
+    ref = mha(q.transpose(0, 1), q.transpose(0, 1), v.transpose(0, 1), key_padding_mask=mask)[0].transpose(0, 1)
+    assert _rel(out, ref) < 1e-5
+    w = torch.randn_like(out)
+    ps = (q, v, mha.in_proj_weight, mha.in_proj_bias, mha.out_proj.weight, mha.out_proj.bias)
+    g = torch.autograd.grad((out * w).sum(), ps)
+    g0 = torch.autograd.grad((ref * w).sum(), ps)
+    for a, b in zip(g, g0):
+        assert _rel(a, b) < 2e-5
+
+
+def test_flat_params_training_step_matches_plain_parameters():
+    """FlatParams (flat master / gradient buffers + bf16 mirror) gives the gradients and the AdamW update of the
+    same model with ordinary parameters."""
+    from kinet_b200.training import FlatParams
+    z = _load_golden()
+    dev = _dev()
+    i = _golden_inputs(z, dev)
+
+    def one_step(flat):
+        enc, _ = _build_from_golden(z, dev)
+        enc.train()
+        if flat:
+            fp = FlatParams(enc)
+            opt = torch.optim.AdamW([fp.flat_parameter], lr=1e-3, weight_decay=1e-2)
+        else:
+            opt = torch.optim.AdamW(enc.parameters(), lr=1e-3, weight_decay=1e-2)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            mem = enc(i["src"].detach(), i["shapes"], i["valid"], i["pos"].detach(), i["mask"])
+        (mem.float() * i["w_mem"]).sum().backward()
+        grads = {k: p.grad.clone() for k, p in enc.named_parameters()}
+        opt.step()
+        if flat:
+            fp.refresh()
+            lin = enc.layers[0].linear1
+            assert torch.equal(lin._kinet_mirror[0], lin.weight.detach().bfloat16())
+        return grads, {k: p.detach().clone() for k, p in enc.named_parameters()}
+    ga, pa = one_step(True)
+    gb, pb = one_step(False)
+    for k in gb:
+        assert _rel(ga[k], gb[k]) < 3e-2, k
+        assert _rel(pa[k], pb[k]) < 1e-3, k
 
 
 def _load_golden():

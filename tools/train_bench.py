@@ -75,15 +75,13 @@ def main():
             opt.step()
             return loss
     else:
-        # B200 recipe: the step is two CUDA graphs (forward+backward into ONE flat fp32 gradient buffer; AdamW) with
-        # a single NCCL all-reduce of that buffer between them -- no per-kernel host cost, no bucket bookkeeping
-        params = list(model.parameters())
-        flat = torch.zeros(n_params, device=dev)
-        off = 0
-        for p in params:
-            p.grad = flat[off:off + p.numel()].view_as(p)
-            off += p.numel()
-        opt = torch.optim.AdamW(params, lr=1e-4, weight_decay=1e-4, fused=True, capturable=True)
+        # B200 recipe: the step is two CUDA graphs (forward+backward into ONE flat fp32 gradient buffer; AdamW on ONE
+        # flat parameter + one cast kernel refreshing the bf16 weight mirror) with a single NCCL all-reduce of the
+        # gradient buffer between them -- no per-kernel host cost, no bucket bookkeeping, no per-layer weight casts
+        from kinet_b200.training import FlatParams
+        fp = FlatParams(model)          # parameters / gradients as views of flat buffers + ONE bf16 mirror of all weights
+        flat = fp.grads
+        opt = torch.optim.AdamW([fp.flat_parameter], lr=1e-4, weight_decay=1e-4, fused=True, capturable=True)
         bufs = tuple(torch.empty_like(t) for t in batches[0])
         loss_buf = torch.zeros((), device=dev)
 
@@ -101,6 +99,7 @@ def main():
                 if world > 1:
                     torch.distributed.all_reduce(flat, op=torch.distributed.ReduceOp.AVG)
                 opt.step()
+                fp.refresh()
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         g_fb, g_opt = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
@@ -108,6 +107,7 @@ def main():
             body()
         with torch.cuda.graph(g_opt):
             opt.step()
+            fp.refresh()
 
         def step(i):
             for t, b in zip(bufs, batches[i & 3]):
