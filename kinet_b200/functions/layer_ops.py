@@ -232,19 +232,29 @@ class LinearFunction(Function):
         return dx, dw, db if ctx.needs_input_grad[2] else None, None, None, None
 
 
-def _lp_params(layer, dtype):
-    """Low-precision copies of an nn.Linear's parameters for inference under autocast, made once and kept on
-    the layer until a parameter changes (in-place updates bump ``_version``; re-assignment changes the
-    identity).  Unlike autocast's own cache they outlive the autocast region, so a per-frame CUDA graph
-    recorded after one eager warm-up holds no weight casts.  A graph keeps reading the copies it was recorded
-    with: re-record it after changing the weights."""
-    w, b = layer.weight, layer.bias
-    key = (dtype, id(w), w._version, id(b), b._version if b is not None else 0)
-    hit = layer.__dict__.get("_kinet_lp")
+def lp_params(owner, weight, bias, dtype):
+    """Low-precision copies of a module's (weight, bias) for inference under autocast, made once and kept on
+    ``owner`` until a parameter changes (in-place updates bump ``_version``; re-assignment changes the
+    identity).  Unlike autocast's own cache they outlive the autocast region (and cover parameters that are
+    used through slices, which autocast never caches), so a per-frame CUDA graph recorded after one eager
+    warm-up holds no weight casts.  A graph keeps reading the copies it was recorded with: re-record it after
+    changing the weights."""
+    key = (dtype, id(weight), weight._version, id(bias), bias._version if bias is not None else 0)
+    hit = owner.__dict__.get("_kinet_lp")
     if hit is None or hit[0] != key:
-        hit = (key, w.detach().to(dtype), b.detach().to(dtype) if b is not None else None)
-        layer.__dict__["_kinet_lp"] = hit
+        hit = (key, weight.detach().to(dtype), bias.detach().to(dtype) if bias is not None else None)
+        owner.__dict__["_kinet_lp"] = hit
     return hit[1], hit[2]
+
+
+def inference_mirror(owner, weight, bias, x):
+    """(weight, bias) copies to use for ``x`` right now: FlatParams' mirror when the module has one, the cached
+    inference copies under no-grad autocast, else None (use the parameters themselves)."""
+    mirror = owner.__dict__.get("_kinet_mirror")
+    if mirror is None and x.is_cuda and not torch.is_grad_enabled() and torch.is_autocast_enabled("cuda") \
+            and bias is not None:
+        mirror = lp_params(owner, weight, bias, torch.get_autocast_dtype("cuda"))
+    return mirror
 
 
 def linear_params(x, weight, bias, relu=False, mirror=None):
@@ -268,8 +278,4 @@ def linear(x, layer, relu=False):
     """``act(layer(x))`` for an nn.Linear, act = identity or ReLU.  With parameter gradients: LinearFunction.
     Without (inference): one GEMM (ReLU in its epilogue), under CUDA autocast on low-precision parameter copies
     cached on the layer (or kept current by training.FlatParams)."""
-    mirror = layer.__dict__.get("_kinet_mirror")
-    if mirror is None and x.is_cuda and not torch.is_grad_enabled() and torch.is_autocast_enabled("cuda") \
-            and layer.bias is not None:
-        mirror = _lp_params(layer, torch.get_autocast_dtype("cuda"))
-    return linear_params(x, layer.weight, layer.bias, relu, mirror)
+    return linear_params(x, layer.weight, layer.bias, relu, inference_mirror(layer, layer.weight, layer.bias, x))

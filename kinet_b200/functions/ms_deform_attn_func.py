@@ -14,6 +14,7 @@ drop-in shim for ``import MultiScaleDeformableAttention as MSDA``) re-exports.
 There is no CPU path: CPU tensors raise, like the reference (ms_deform_attn.h:27,48).
 """
 import ctypes
+import weakref
 
 import torch
 import torch.nn.functional as F
@@ -205,6 +206,23 @@ def fused_supported(value, n_levels, n_points):
     return n_levels * n_points <= 4 * owners
 
 
+_norm_f32 = None      # (weakref to the last offset_norm tensor, its version, device, its fp32 copy)
+
+
+def _offset_norm_f32(offset_norm, device):
+    """fp32 copy of the (L, 2) offset divisors.  Every layer of a frame passes the same spatial_shapes tensor,
+    so the int64 -> fp32 conversion (a 2 us kernel, twice per layer) is remembered per tensor object."""
+    global _norm_f32
+    if offset_norm.dtype == torch.float32 and offset_norm.device == device and offset_norm.is_contiguous():
+        return offset_norm
+    seen = _norm_f32
+    if seen is not None and seen[0]() is offset_norm and seen[1] == offset_norm._version and seen[2] == device:
+        return seen[3]
+    out = offset_norm.to(device=device, dtype=torch.float32).contiguous()
+    _norm_f32 = (weakref.ref(offset_norm), offset_norm._version, device, out)
+    return out
+
+
 def _fused_inputs(value, offsets, logits, reference_points, offset_norm, query_mask):
     if value.dtype == torch.float32:
         aux = torch.float32
@@ -215,7 +233,7 @@ def _fused_inputs(value, offsets, logits, reference_points, offset_norm, query_m
     off = offsets.to(aux).contiguous()
     lg = logits.to(aux).contiguous()
     ref = reference_points.to(torch.float32).contiguous()
-    norm = offset_norm.to(device=value.device, dtype=torch.float32).contiguous() if offset_norm is not None else None
+    norm = _offset_norm_f32(offset_norm, value.device) if offset_norm is not None else None
     mask = query_mask.to(torch.uint8).contiguous() if query_mask is not None else None
     args = _lib.MsdaFusedInputs(off.data_ptr(), lg.data_ptr(), ref.data_ptr(),
                                 norm.data_ptr() if norm is not None else None,

@@ -23,7 +23,7 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
-from ..functions.layer_ops import add_layer_norm, linear, linear_params
+from ..functions.layer_ops import add_layer_norm, inference_mirror, linear, linear_params
 from .ms_deform_attn import MSDeformAttn
 
 
@@ -96,7 +96,7 @@ def _self_attention(mha, q_in, v_in, key_padding_mask):
     N, Lq, C = q_in.shape
     H = mha.num_heads
     w, b = mha.in_proj_weight, mha.in_proj_bias
-    mirror = mha.__dict__.get("_kinet_mirror")
+    mirror = inference_mirror(mha, w, b, q_in)
     m_qk = m_v = None
     if mirror is not None:
         m_qk, m_v = (mirror[0][:2 * C], mirror[1][:2 * C]), (mirror[0][2 * C:], mirror[1][2 * C:])
