@@ -73,7 +73,8 @@ int kinet_b200_add_layernorm_backward(const kinet_ln_bwd_args* args, void* strea
 
 /* Column sums out[c] = sum_i a[i][c] of a [rows][C] matrix (the bias gradient of a Linear layer,
  * which PyTorch computes with a generic reduce kernel): fp32 accumulation, fixed summation order.
- * C: multiple of 4, <= 1024.  out is out_dtype [C]; partial as above with n = C. */
+ * C: multiple of 4, <= 1024.  out is out_dtype [C]; partial as above with n = C (not touched when rows <= 2048:
+ * few rows are summed by one launch without scratch). */
 size_t kinet_b200_colsum_partial_floats(int32_t n_columns);
 int kinet_b200_colsum(const void* a, int32_t a_dtype, int64_t rows, int32_t C,
                       void* out, int32_t out_dtype, float* partial, void* stream);

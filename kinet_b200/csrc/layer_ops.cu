@@ -280,6 +280,56 @@ colsum_kernel(const void* __restrict__ a, const void* __restrict__ h, void* __re
     }
 }
 
+// Few rows (the decoder's 300-800 queries x batch): one launch, no scratch.  A CTA of 32 x 32 threads owns 32
+// columns; thread (tx, ty) adds rows ty, ty + 32, ... of column tx, the row lanes fold through shared memory.
+__device__ __forceinline__ float load1(const void* p, int dtype, size_t i)
+{
+    return dtype == MSDA_F32 ? static_cast<const float*>(p)[i]
+                             : __bfloat162float(static_cast<const __nv_bfloat16*>(p)[i]);
+}
+
+template <bool RELU>
+__global__ void __launch_bounds__(1024)
+colsum_small_kernel(const void* __restrict__ a, const void* __restrict__ h, void* __restrict__ dh, int dtype,
+                    int rows, int C, void* out, int out_dtype)
+{
+    __shared__ float tile[32][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + tx;
+    float t0 = 0.f, t1 = 0.f;
+    if (c < C) {
+        for (int r = ty; r < rows; r += 64) {
+            const int r1 = r + 32;
+            float v0 = load1(a, dtype, (size_t)r * C + c);
+            float v1 = r1 < rows ? load1(a, dtype, (size_t)r1 * C + c) : 0.f;
+            if constexpr (RELU) {
+                v0 = load1(h, dtype, (size_t)r * C + c) > 0.f ? v0 : 0.f;
+                if (r1 < rows) v1 = load1(h, dtype, (size_t)r1 * C + c) > 0.f ? v1 : 0.f;
+                if (dtype == MSDA_F32) {
+                    static_cast<float*>(dh)[(size_t)r * C + c] = v0;
+                    if (r1 < rows) static_cast<float*>(dh)[(size_t)r1 * C + c] = v1;
+                } else {
+                    static_cast<__nv_bfloat16*>(dh)[(size_t)r * C + c] = __float2bfloat16_rn(v0);
+                    if (r1 < rows) static_cast<__nv_bfloat16*>(dh)[(size_t)r1 * C + c] = __float2bfloat16_rn(v1);
+                }
+            }
+            t0 += v0;
+            t1 += v1;
+        }
+    }
+    tile[ty][tx] = t0 + t1;
+    __syncthreads();
+    if (ty == 0 && c < C) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < 32; ++w) t += tile[w][tx];
+        if (out_dtype == MSDA_F32) static_cast<float*>(out)[c] = t;
+        else static_cast<__nv_bfloat16*>(out)[c] = __float2bfloat16_rn(t);
+    }
+}
+
+constexpr int kSmallRows = 2048;
+
 inline bool ok_dtype(int d) { return d == MSDA_F32 || d == MSDA_BF16; }
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 inline bool aligned_for(const void* p, int dtype) { return (reinterpret_cast<uintptr_t>(p) & (dtype == MSDA_F32 ? 15 : 7)) == 0; }
@@ -402,6 +452,12 @@ static int colsum_common(const void* a, const void* h, void* dh, int32_t a_dtype
         (relu && (!aligned_for(h, a_dtype) || !aligned_for(dh, a_dtype))))
         return MSDA_E_ALIGN;
     cudaStream_t st = (cudaStream_t)stream;
+    if (rows <= kSmallRows) {
+        const int g = (C + 31) / 32;
+        if (relu) colsum_small_kernel<true><<<g, 1024, 0, st>>>(a, h, dh, a_dtype, (int)rows, C, out, out_dtype);
+        else colsum_small_kernel<false><<<g, 1024, 0, st>>>(a, nullptr, nullptr, a_dtype, (int)rows, C, out, out_dtype);
+        return (int)cudaGetLastError();
+    }
     const int nvec = C >> 2;
     const int RL = 256 / nvec;     // row lanes per CTA (nvec <= 256)
     int grid = 0;

@@ -61,6 +61,78 @@ def test_argument_validation_without_gpu(lib):
     assert lib.msda_b200_forward(one, 7, one, null, one, one, 0, one, ctypes.byref(d), null) == -1
 
 
+def test_layer_abi_argument_validation_without_gpu(lib):
+    """include/kinet_layers_b200.h entry points check their arguments before touching CUDA."""
+    from kinet_b200._lib import KinetLnBwdArgs, KinetLnFwdArgs, MSDA_BF16, MSDA_F32
+    p16, p8, p2 = 4096, 4104, 4098          # fake device addresses: 16-, 8- and 2-byte aligned
+    assert lib.kinet_b200_add_layernorm_forward(None, None) == -3
+
+    def fwd(**kw):
+        base = dict(x=p16, x_dtype=MSDA_F32, r=p8, r_dtype=MSDA_BF16, pos=None, pos_dtype=0, pos_rows=1,
+                    gamma=p16, beta=p16, y=p16, y_dtype=MSDA_F32, y_lp=None, ypos_lp=None, lp_dtype=MSDA_BF16,
+                    mean_rstd=None, rows=0, C=256, eps=1e-5)
+        base.update(kw)
+        return lib.kinet_b200_add_layernorm_forward(ctypes.byref(KinetLnFwdArgs(**base)), None)
+    assert fwd() == 0                                   # rows == 0: nothing to do, no launch
+    assert fwd(x=None) == -3 and fwd(gamma=None) == -3
+    assert fwd(C=6) == -2 and fwd(C=1028) == -2 and fwd(C=0) == -2 and fwd(rows=-1) == -2
+    assert fwd(x_dtype=2) == -1 and fwd(r_dtype=3) == -1 and fwd(y_lp=p8, lp_dtype=3) == -1
+    assert fwd(x=p8) == -4 and fwd(r=p2) == -4 and fwd(y_lp=p2) == -4
+    assert fwd(ypos_lp=p8) == -3                        # y + pos asked for without pos
+    assert fwd(ypos_lp=p8, pos=p16, pos_rows=0) == -3
+
+    def bwd(**kw):
+        base = dict(dy=p16, dy_dtype=MSDA_F32, dy_lp=None, dypos_lp=None, lp_dtype=MSDA_BF16, x=p16, x_dtype=MSDA_F32,
+                    r=p8, r_dtype=MSDA_BF16, gamma=p16, mean_rstd=p16, dx=p16, dr=p8, dgamma_dbeta=p16, partial=p16,
+                    rows=4, C=256)
+        base.update(kw)
+        return lib.kinet_b200_add_layernorm_backward(ctypes.byref(KinetLnBwdArgs(**base)), None)
+    assert bwd(dy=None) == -3 and bwd(partial=None) == -3 and bwd(r=None) == -3      # dr without r
+    assert bwd(C=2) == -2 and bwd(dy_dtype=2) == -1 and bwd(dx=p8) == -4
+    assert lib.kinet_b200_colsum_partial_floats(256) >= 148 * 256 and lib.kinet_b200_colsum_partial_floats(0) == 0
+    assert lib.kinet_b200_colsum(p16, MSDA_BF16, 10, 256, None, MSDA_F32, p16, None) == -3
+    assert lib.kinet_b200_colsum(p16, MSDA_BF16, 10, 258, p16, MSDA_F32, p16, None) == -2
+    assert lib.kinet_b200_colsum(p16, 2, 10, 256, p16, MSDA_F32, p16, None) == -1
+    assert lib.kinet_b200_colsum(p2, MSDA_BF16, 10, 256, p16, MSDA_F32, p16, None) == -4
+    assert lib.kinet_b200_relu_backward_colsum(p16, None, MSDA_BF16, 10, 256, p16, p16, MSDA_F32, p16, None) == -3
+
+
+def test_layer_modules_mirror_the_reference_signatures():
+    """Constructor / forward signatures and parameter names of the reference's layer classes
+    (src/trackformer/models/deformable_transformer.py:260-433), checked without a GPU."""
+    import inspect
+    from kinet_b200.modules import (DeformableTransformerDecoder, DeformableTransformerDecoderLayer,
+                                    DeformableTransformerEncoder, DeformableTransformerEncoderLayer)
+    args = lambda f: list(inspect.signature(f).parameters)
+    assert args(DeformableTransformerEncoderLayer.__init__)[1:] == ["d_model", "d_ffn", "dropout", "activation",
+                                                                    "n_levels", "n_heads", "n_points"]
+    assert args(DeformableTransformerEncoderLayer.forward)[1:] == ["src", "pos", "reference_points", "spatial_shapes",
+                                                                   "padding_mask"]
+    assert args(DeformableTransformerEncoder.forward)[1:6] == ["src", "spatial_shapes", "valid_ratios", "pos",
+                                                               "padding_mask"]
+    assert args(DeformableTransformerDecoderLayer.forward)[1:] == ["tgt", "query_pos", "reference_points", "src",
+                                                                   "src_spatial_shapes", "src_padding_mask",
+                                                                   "query_attn_mask"]
+    assert args(DeformableTransformerDecoder.forward)[1:] == ["tgt", "reference_points", "src", "src_spatial_shapes",
+                                                              "src_valid_ratios", "query_pos", "src_padding_mask",
+                                                              "query_attn_mask"]
+    enc = DeformableTransformerEncoder(DeformableTransformerEncoderLayer(64, 32, 0.1, "relu", 2, 8, 2), 2)
+    dec = DeformableTransformerDecoder(DeformableTransformerDecoderLayer(64, 32, 0.1, "relu", 2, 8, 2), 2, True)
+    names = set(k for k, _ in enc.named_parameters())
+    assert {"layers.1.self_attn.sampling_offsets.weight", "layers.0.norm2.bias", "layers.0.linear1.weight"} <= names
+    names = set(k for k, _ in dec.named_parameters())
+    assert {"layers.0.cross_attn.value_proj.bias", "layers.1.self_attn.in_proj_weight",
+            "layers.0.self_attn.out_proj.bias", "layers.0.norm3.weight"} <= names
+    assert dec.bbox_embed is None and dec.class_embed is None and dec.return_intermediate
+    # reference points of the encoder: pixel centres / (valid ratio * size), for every level (CPU tensors are fine here)
+    shapes = torch.tensor([[2, 3], [1, 2]])
+    ref = DeformableTransformerEncoder.get_reference_points(shapes, torch.ones(1, 2, 2), torch.device("cpu"))
+    assert ref.shape == (1, 8, 2, 2)
+    assert torch.allclose(ref[0, :3, 0, 0], torch.tensor([0.5, 1.5, 2.5]) / 3) and torch.allclose(ref[0, 6:, 1, 0], torch.tensor([0.25, 0.75]))
+    with pytest.raises(RuntimeError, match="Not implemented on the CPU"):
+        enc(torch.zeros(1, 8, 64), shapes, torch.ones(1, 2, 2), torch.zeros(1, 8, 64))
+
+
 def test_cpu_tensors_raise_like_the_reference():
     from kinet_b200.functions import MSDeformAttnFunction
     value = torch.zeros(1, 4, 1, 4)

@@ -94,7 +94,8 @@ def test_add_layer_norm_no_branch_many_rows_and_determinism():
         assert torch.equal(a, b)
 
 
-@pytest.mark.parametrize("rows,C", [(1, 4), (77, 128), (44446, 256), (44446, 1024), (20906, 288), (5, 1000)])
+@pytest.mark.parametrize("rows,C", [(1, 4), (77, 128), (600, 256), (2048, 288), (2049, 256), (44446, 256), (44446, 1024),
+                                     (20906, 288), (5, 1000)])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_column_sum(rows, C, dtype):
     from kinet_b200.functions.layer_ops import column_sum
@@ -105,6 +106,20 @@ def test_column_sum(rows, C, dtype):
     assert float((out.double() - ref).abs().max()) <= 1e-5 * float(a.double().abs().sum(0).max())
     assert torch.equal(out, column_sum(a, torch.float32))
     assert column_sum(a).dtype == dtype
+
+
+@pytest.mark.parametrize("rows", [3, 600, 2048, 2049, 9000])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_relu_backward_column_sum(rows, dtype):
+    from kinet_b200.functions.layer_ops import relu_backward_column_sum
+    dev = _dev()
+    g = torch.Generator(device=dev).manual_seed(rows)
+    dy = torch.randn(rows, 1024, device=dev, generator=g).to(dtype)
+    h = torch.relu(torch.randn(rows, 1024, device=dev, generator=g)).to(dtype)
+    dh, db = relu_backward_column_sum(dy, h, torch.float32)
+    ref = dy * (h > 0).to(dtype)
+    assert torch.equal(dh, ref)
+    assert float((db.double() - ref.double().sum(0)).abs().max()) <= 1e-5 * float(ref.double().abs().sum(0).max())
 
 
 @pytest.mark.parametrize("amp", [False, True])
@@ -312,3 +327,25 @@ def test_cpu_tensors_raise():
         AddLayerNormFunction.apply(torch.zeros(2, 8), None, None, torch.ones(8), torch.zeros(8), 1e-5, torch.float32, False)
     with pytest.raises(RuntimeError, match="Not implemented on the CPU"):
         column_sum(torch.zeros(2, 8))
+
+
+def test_layer_abi_from_a_cpp_host_program(tmp_path):
+    """include/kinet_layers_b200.h is a C ABI: tests/abi_c/layers_smoke.cpp links libmsda_b200.so and the CUDA
+    runtime only (no torch, no Python in the process), runs add+LayerNorm forward / backward and a column sum and
+    checks them against its own double-precision restatement."""
+    import shutil
+    import subprocess
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        pytest.skip("nvcc not available on this box")
+    root = os.path.dirname(HERE)
+    libdir = os.path.join(root, "kinet_b200")
+    exe = str(tmp_path / "layers_smoke")
+    env = {k: v for k, v in os.environ.items() if k not in ("CC", "CXX")}
+    subprocess.check_call([nvcc, "-O2", "-std=c++17", "-Wno-deprecated-gpu-targets", "-I", os.path.join(root, "include"),
+                           "-o", exe, os.path.join(root, "tests", "abi_c", "layers_smoke.cpp"),
+                           "-L", libdir, "-lmsda_b200", "-Xlinker", "-rpath", "-Xlinker", libdir], env=env)
+    res = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    print(res.stdout)
+    assert res.returncode == 0, res.stdout + res.stderr
+    assert "PASS" in res.stdout

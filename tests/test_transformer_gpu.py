@@ -70,6 +70,30 @@ def test_stack_matches_reference_cuda_kernels_fp32():
         assert err <= 5e-4, (name, err)
 
 
+def test_fused_layer_classes_match_plain_stack_fp32():
+    """kinet_b200.modules' encoder / decoder classes (fused add+LayerNorm+pos kernels, own self-attention, ReLU in
+    the GEMM epilogue) against the same stack written in plain PyTorch ops, same parameters, fp32: forward
+    outputs, and gradients on identical forward values up to fp32 reordering."""
+    from _harness import FusedStack
+    dev = torch.device("cuda:0")
+    levels = [(25, 34), (13, 17), (7, 9), (4, 5)]
+    torch.manual_seed(0)
+    plain = Stack(levels, n_enc=2, n_dec=2, n_queries=50).to(dev)
+    fused = FusedStack(levels, n_enc=2, n_dec=2, n_queries=50).to(dev)
+    fused.load_from_stack(plain)
+    src, pos = _inputs(dev, levels)
+    want = _step(plain, src, pos, False)
+    got = _step(fused, src, pos, False)
+    for a, b in zip(got[:2], want[:2]):
+        assert float((a - b).norm() / b.norm()) <= 2e-5
+    # gradients: loose bound only (a 3e-7 forward perturbation moves them by ~1 %, see the test above)
+    assert float((got[2] - want[2]).norm() / want[2].norm()) <= 5e-2
+    names = dict(plain.named_parameters())
+    for k, p in fused.named_parameters():
+        k0 = k.replace("encoder.layers.", "enc.").replace("decoder.layers.", "dec.")
+        assert p.grad is not None and p.grad.shape == names[k0].grad.shape, k
+
+
 def test_full_size_stack_timing():
     dev = torch.device("cuda:0")
     levels = PYRAMIDS["detr_800x1333"]
