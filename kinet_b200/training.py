@@ -58,3 +58,68 @@ class FlatParams:
 
     def zero_grad(self):
         self.grads.zero_()
+
+
+class GraphedTrainStep:
+    """One data-parallel training step as two CUDA graphs with a single all-reduce between them:
+
+        graph 1: zero the flat gradient buffer, forward, loss, backward (every gradient lands in FlatParams.grads)
+        NCCL   : all_reduce(grads, AVG) when torch.distributed is initialised with more than one rank
+        graph 2: optimizer step on the flat parameter, refresh of the low-precision weight mirror
+
+    ``loss_fn(*inputs)`` runs the model (under whatever autocast it wants) and returns a scalar loss; ``inputs`` are
+    example tensors whose shapes every later batch must share (they become the graph's static input buffers).
+    Construction runs ``warmup`` REAL training steps on the example batch (eagerly, on a side stream) before
+    recording.  ``make_optimizer(params)`` builds a capturable optimizer, e.g.
+    ``lambda p: torch.optim.AdamW(p, lr=1e-4, fused=True, capturable=True)``.
+    Nothing in kinet_b200's kernels allocates, synchronises or reads device memory on the host, so the whole step
+    replays without per-kernel host cost (a 6+6-layer stack launches ~1 100 kernels per step)."""
+
+    def __init__(self, module, loss_fn, make_optimizer, example_inputs, lp_dtype=torch.bfloat16, warmup=3):
+        import torch.distributed as dist
+        self.flat = FlatParams(module, lp_dtype)
+        self.optimizer = make_optimizer([self.flat.flat_parameter])
+        self.inputs = tuple(torch.empty_like(t) for t in example_inputs)
+        for b, t in zip(self.inputs, example_inputs):
+            b.copy_(t)
+        self.loss = torch.zeros((), dtype=torch.float32, device=self.flat.master.device)
+        self._world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        self._loss_fn = loss_fn
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):     # eager runs: fill the per-tensor caches, let the optimizer build its state
+                self._forward_backward()
+                self._exchange()
+                self._update()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self._g_fb, self._g_opt = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._g_fb):
+            self._forward_backward()
+        with torch.cuda.graph(self._g_opt):
+            self._update()
+
+    def _forward_backward(self):
+        self.flat.zero_grad()
+        loss = self._loss_fn(*self.inputs)
+        loss.backward()
+        self.loss.copy_(loss.detach())
+
+    def _exchange(self):
+        if self._world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(self.flat.grads, op=dist.ReduceOp.AVG)
+
+    def _update(self):
+        self.optimizer.step()
+        self.flat.refresh()
+
+    def __call__(self, *inputs):
+        """Run one step on a new batch; returns the (device-resident, overwritten next step) loss tensor."""
+        for b, t in zip(self.inputs, inputs):
+            b.copy_(t, non_blocking=True)
+        self._g_fb.replay()
+        self._exchange()
+        self._g_opt.replay()
+        return self.loss

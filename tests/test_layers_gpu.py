@@ -226,6 +226,43 @@ def test_flat_params_training_step_matches_plain_parameters():
         assert _rel(pa[k], pb[k]) < 1e-3, k
 
 
+def test_graphed_train_step_follows_eager_training():
+    """training.GraphedTrainStep (two CUDA graphs around the gradient exchange) moves the parameters like the
+    same steps run eagerly with ordinary parameters."""
+    from kinet_b200.training import GraphedTrainStep
+    z = _load_golden()
+    dev = _dev()
+    i = _golden_inputs(z, dev)
+    batches = [(torch.from_numpy(z["src"]).to(dev) * (1 + 0.1 * k), torch.from_numpy(z["pos"]).to(dev)) for k in range(3)]
+
+    def make():
+        enc, _ = _build_from_golden(z, dev)
+        enc.train()
+
+        def loss_fn(src, pos):
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                return (enc(src, i["shapes"], i["valid"], pos, i["mask"]).float() * i["w_mem"]).sum() * 1e-3
+        return enc, loss_fn
+    enc_a, loss_a = make()
+    opt = torch.optim.AdamW(enc_a.parameters(), lr=1e-3, weight_decay=1e-2)
+    losses_a = []
+    for k in range(3 + 3):                      # GraphedTrainStep warms up with 3 real steps on its example batch
+        src, pos = batches[0] if k < 3 else batches[k - 3]
+        opt.zero_grad()
+        loss = loss_a(src, pos)
+        loss.backward()
+        opt.step()
+        losses_a.append(float(loss))
+    enc_b, loss_b = make()
+    step = GraphedTrainStep(enc_b, loss_b, lambda p: torch.optim.AdamW(p, lr=1e-3, weight_decay=1e-2, capturable=True),
+                            batches[0])
+    losses_b = [float(step(*batches[k])) for k in range(3)]
+    for a, b in zip(losses_a[3:], losses_b):
+        assert abs(a - b) <= 2e-2 * max(abs(a), 1e-3), (losses_a, losses_b)
+    for (k, pa), (_, pb) in zip(enc_a.named_parameters(), enc_b.named_parameters()):
+        assert _rel(pb.detach(), pa.detach()) < 2e-2, k
+
+
 def _load_golden():
     z = np.load(os.path.join(HERE, "golden", "layers_f32.npz"))
     return {k: z[k] for k in z.files}

@@ -78,45 +78,18 @@ def main():
         # B200 recipe: the step is two CUDA graphs (forward+backward into ONE flat fp32 gradient buffer; AdamW on ONE
         # flat parameter + one cast kernel refreshing the bf16 weight mirror) with a single NCCL all-reduce of the
         # gradient buffer between them -- no per-kernel host cost, no bucket bookkeeping, no per-layer weight casts
-        from kinet_b200.training import FlatParams
-        fp = FlatParams(model)          # parameters / gradients as views of flat buffers + ONE bf16 mirror of all weights
-        flat = fp.grads
-        opt = torch.optim.AdamW([fp.flat_parameter], lr=1e-4, weight_decay=1e-4, fused=True, capturable=True)
-        bufs = tuple(torch.empty_like(t) for t in batches[0])
-        loss_buf = torch.zeros((), device=dev)
+        from kinet_b200.training import GraphedTrainStep
 
-        def body():
-            flat.zero_()
-            loss_buf.copy_(fwd_bwd(model, *bufs).detach())
-
-        for t, b in zip(bufs, batches[0]):
-            t.copy_(b)
-        side = torch.cuda.Stream()
-        side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):
-            for _ in range(3):
-                body()
-                if world > 1:
-                    torch.distributed.all_reduce(flat, op=torch.distributed.ReduceOp.AVG)
-                opt.step()
-                fp.refresh()
-        torch.cuda.current_stream().wait_stream(side)
-        torch.cuda.synchronize()
-        g_fb, g_opt = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g_fb):
-            body()
-        with torch.cuda.graph(g_opt):
-            opt.step()
-            fp.refresh()
+        def loss_fn(src, pos, target):
+            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=not args.fp32):
+                out, _ = model(src, pos)
+            return (out.float() - target).square().mean()
+        graphed = GraphedTrainStep(model, loss_fn,
+                                   lambda p: torch.optim.AdamW(p, lr=1e-4, weight_decay=1e-4, fused=True, capturable=True),
+                                   batches[0])
 
         def step(i):
-            for t, b in zip(bufs, batches[i & 3]):
-                t.copy_(b, non_blocking=True)           # the next batch lands in the graph's input buffers
-            g_fb.replay()
-            if world > 1:
-                torch.distributed.all_reduce(flat, op=torch.distributed.ReduceOp.AVG)
-            g_opt.replay()
-            return loss_buf
+            return graphed(*batches[i & 3])
 
     for i in range(args.warmup):
         step(i)
