@@ -17,7 +17,7 @@
  * twins, of which LayerNorm's gamma/beta reduction and the Linear bias reductions are the slowest
  * kernels of a training step) become ONE pass forward and ONE pass backward over the rows.
  *
- * Element types use the MSDA_F32 / MSDA_BF16 codes of msda_b200.h.
+ * Element types use the MSDA_F32 / MSDA_BF16 / MSDA_F16 codes of msda_b200.h (no fp64).
  */
 #ifndef KINET_LAYERS_B200_H
 #define KINET_LAYERS_B200_H

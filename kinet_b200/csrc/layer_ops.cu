@@ -8,6 +8,7 @@
 // registers across all the rows a warp / thread visits, folded once per CTA through shared memory
 // into a [CTA][column] scratch and summed by a second tiny kernel in a fixed order.
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -23,8 +24,13 @@ constexpr int kMaxCtas = 148 * 4;   // partial-sum scratch is [kMaxCtas][columns
 __device__ __forceinline__ float4 load4(const void* p, int dtype, size_t i)
 {
     if (dtype == MSDA_F32) return __ldcs(reinterpret_cast<const float4*>(static_cast<const float*>(p) + i));
-    const uint2 u = __ldcs(reinterpret_cast<const uint2*>(static_cast<const __nv_bfloat16*>(p) + i));
+    const uint2 u = __ldcs(reinterpret_cast<const uint2*>(static_cast<const unsigned short*>(p) + i));
     float4 f;
+    if (dtype == MSDA_F16) {
+        const float2 lo = __half22float2(*reinterpret_cast<const __half2*>(&u.x));
+        const float2 hi = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
+        return make_float4(lo.x, lo.y, hi.x, hi.y);
+    }
     f.x = __uint_as_float(u.x << 16); f.y = __uint_as_float(u.x & 0xffff0000u);
     f.z = __uint_as_float(u.y << 16); f.w = __uint_as_float(u.y & 0xffff0000u);
     return f;
@@ -34,6 +40,12 @@ __device__ __forceinline__ void store4(void* p, int dtype, size_t i, float4 f)
 {
     if (dtype == MSDA_F32) {
         *reinterpret_cast<float4*>(static_cast<float*>(p) + i) = f;
+    } else if (dtype == MSDA_F16) {
+        const __half2 a = __floats2half2_rn(f.x, f.y), b = __floats2half2_rn(f.z, f.w);
+        uint2 u;
+        u.x = *reinterpret_cast<const unsigned*>(&a);
+        u.y = *reinterpret_cast<const unsigned*>(&b);
+        *reinterpret_cast<uint2*>(static_cast<__half*>(p) + i) = u;
     } else {
         const __nv_bfloat162 a = __floats2bfloat162_rn(f.x, f.y), b = __floats2bfloat162_rn(f.z, f.w);
         uint2 u;
@@ -41,6 +53,20 @@ __device__ __forceinline__ void store4(void* p, int dtype, size_t i, float4 f)
         u.y = *reinterpret_cast<const unsigned*>(&b);
         *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(p) + i) = u;
     }
+}
+
+__device__ __forceinline__ float load1(const void* p, int dtype, size_t i)
+{
+    if (dtype == MSDA_F32) return static_cast<const float*>(p)[i];
+    if (dtype == MSDA_F16) return __half2float(static_cast<const __half*>(p)[i]);
+    return __bfloat162float(static_cast<const __nv_bfloat16*>(p)[i]);
+}
+
+__device__ __forceinline__ void store1(void* p, int dtype, size_t i, float v)
+{
+    if (dtype == MSDA_F32) static_cast<float*>(p)[i] = v;
+    else if (dtype == MSDA_F16) static_cast<__half*>(p)[i] = __float2half_rn(v);
+    else static_cast<__nv_bfloat16*>(p)[i] = __float2bfloat16_rn(v);
 }
 
 __device__ __forceinline__ float warp_sum(float v)
@@ -227,8 +253,7 @@ colsum_finalize_kernel(const float* __restrict__ partial, int G, int n, void* ou
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < 32; ++w) t += tile[w][tx];
-        if (out_dtype == MSDA_F32) static_cast<float*>(out)[c] = t;
-        else static_cast<__nv_bfloat16*>(out)[c] = __float2bfloat16_rn(t);
+        store1(out, out_dtype, c, t);
     }
 }
 
@@ -282,12 +307,6 @@ colsum_kernel(const void* __restrict__ a, const void* __restrict__ h, void* __re
 
 // Few rows (the decoder's 300-800 queries x batch): one launch, no scratch.  A CTA of 32 x 32 threads owns 32
 // columns; thread (tx, ty) adds rows ty, ty + 32, ... of column tx, the row lanes fold through shared memory.
-__device__ __forceinline__ float load1(const void* p, int dtype, size_t i)
-{
-    return dtype == MSDA_F32 ? static_cast<const float*>(p)[i]
-                             : __bfloat162float(static_cast<const __nv_bfloat16*>(p)[i]);
-}
-
 template <bool RELU>
 __global__ void __launch_bounds__(1024)
 colsum_small_kernel(const void* __restrict__ a, const void* __restrict__ h, void* __restrict__ dh, int dtype,
@@ -305,13 +324,8 @@ colsum_small_kernel(const void* __restrict__ a, const void* __restrict__ h, void
             if constexpr (RELU) {
                 v0 = load1(h, dtype, (size_t)r * C + c) > 0.f ? v0 : 0.f;
                 if (r1 < rows) v1 = load1(h, dtype, (size_t)r1 * C + c) > 0.f ? v1 : 0.f;
-                if (dtype == MSDA_F32) {
-                    static_cast<float*>(dh)[(size_t)r * C + c] = v0;
-                    if (r1 < rows) static_cast<float*>(dh)[(size_t)r1 * C + c] = v1;
-                } else {
-                    static_cast<__nv_bfloat16*>(dh)[(size_t)r * C + c] = __float2bfloat16_rn(v0);
-                    if (r1 < rows) static_cast<__nv_bfloat16*>(dh)[(size_t)r1 * C + c] = __float2bfloat16_rn(v1);
-                }
+                store1(dh, dtype, (size_t)r * C + c, v0);
+                if (r1 < rows) store1(dh, dtype, (size_t)r1 * C + c, v1);
             }
             t0 += v0;
             t1 += v1;
@@ -323,14 +337,13 @@ colsum_small_kernel(const void* __restrict__ a, const void* __restrict__ h, void
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < 32; ++w) t += tile[w][tx];
-        if (out_dtype == MSDA_F32) static_cast<float*>(out)[c] = t;
-        else static_cast<__nv_bfloat16*>(out)[c] = __float2bfloat16_rn(t);
+        store1(out, out_dtype, c, t);
     }
 }
 
 constexpr int kSmallRows = 2048;
 
-inline bool ok_dtype(int d) { return d == MSDA_F32 || d == MSDA_BF16; }
+inline bool ok_dtype(int d) { return d == MSDA_F32 || d == MSDA_BF16 || d == MSDA_F16; }
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 inline bool aligned_for(const void* p, int dtype) { return (reinterpret_cast<uintptr_t>(p) & (dtype == MSDA_F32 ? 15 : 7)) == 0; }
 

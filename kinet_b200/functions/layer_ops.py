@@ -16,7 +16,7 @@ from torch.autograd.function import once_differentiable
 
 from .. import _lib
 
-_LN_DTYPES = (torch.float32, torch.bfloat16)
+_LN_DTYPES = (torch.float32, torch.bfloat16, torch.float16)
 MAX_C = 1024
 
 

@@ -76,7 +76,7 @@ def test_layer_abi_argument_validation_without_gpu(lib):
     assert fwd() == 0                                   # rows == 0: nothing to do, no launch
     assert fwd(x=None) == -3 and fwd(gamma=None) == -3
     assert fwd(C=6) == -2 and fwd(C=1028) == -2 and fwd(C=0) == -2 and fwd(rows=-1) == -2
-    assert fwd(x_dtype=2) == -1 and fwd(r_dtype=3) == -1 and fwd(y_lp=p8, lp_dtype=3) == -1
+    assert fwd(x_dtype=2) == -1 and fwd(r_dtype=7) == -1 and fwd(y_lp=p8, lp_dtype=2) == -1 and fwd(r_dtype=3) == 0
     assert fwd(x=p8) == -4 and fwd(r=p2) == -4 and fwd(y_lp=p2) == -4
     assert fwd(ypos_lp=p8) == -3                        # y + pos asked for without pos
     assert fwd(ypos_lp=p8, pos=p16, pos_rows=0) == -3

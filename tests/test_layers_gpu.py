@@ -23,7 +23,7 @@ def _rel(a, b):
 
 @pytest.mark.parametrize("C", [4, 36, 128, 256, 288, 512, 1024])
 @pytest.mark.parametrize("stream,lp", [(torch.float32, torch.float32), (torch.float32, torch.bfloat16),
-                                       (torch.bfloat16, torch.bfloat16)])
+                                       (torch.bfloat16, torch.bfloat16), (torch.float32, torch.float16)])
 @pytest.mark.parametrize("pos_mode", ["none", "full", "batch_broadcast"])
 def test_add_layer_norm_forward_backward(C, stream, lp, pos_mode):
     from kinet_b200.functions.layer_ops import AddLayerNormFunction
@@ -96,7 +96,7 @@ def test_add_layer_norm_no_branch_many_rows_and_determinism():
 
 @pytest.mark.parametrize("rows,C", [(1, 4), (77, 128), (600, 256), (2048, 288), (2049, 256), (44446, 256), (44446, 1024),
                                      (20906, 288), (5, 1000)])
-@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
 def test_column_sum(rows, C, dtype):
     from kinet_b200.functions.layer_ops import column_sum
     dev = _dev()
