@@ -193,6 +193,40 @@ def test_self_attention_matches_nn_multihead_attention(masked):
         assert _rel(a, b) < 2e-5
 
 
+@pytest.mark.parametrize("heads,C", [(8, 288), (8, 256)])
+def test_self_attention_mask_rides_in_a_spare_head_channel_bf16(heads, C):
+    """16-bit masked self-attention (key-padding mask folded into a spare head channel so that SDPA stays on the
+    flash kernel; head_dim 36 and 32) against nn.MultiheadAttention under the same autocast, incl. gradients."""
+    from kinet_b200.modules.deformable_transformer import _self_attention
+    dev = _dev()
+    torch.manual_seed(3)
+    mha = torch.nn.MultiheadAttention(C, heads, dropout=0.0).to(dev)
+    with torch.no_grad():
+        mha.in_proj_bias.normal_(0, 0.1)
+    q = torch.randn(2, 70, C, device=dev, requires_grad=True)
+    v = torch.randn(2, 70, C, device=dev, requires_grad=True)
+    mask = torch.zeros(2, 70, dtype=torch.bool, device=dev)
+    mask[0, -9:] = True
+    mask[1, 3] = True
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        out = _self_attention(mha, q.bfloat16(), v.bfloat16(), mask)
+        ref = mha(q.transpose(0, 1), q.transpose(0, 1), v.transpose(0, 1), key_padding_mask=mask)[0].transpose(0, 1)
+    assert out.dtype == torch.bfloat16 and bool(torch.isfinite(out).all())
+    assert _rel(out, ref) < 3e-2
+    # masked keys get exactly zero weight: changing their content does not change the output
+    v2 = v.detach().clone()
+    v2[0, -9:] += 100.0
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        a = _self_attention(mha, q.detach().bfloat16(), v.detach().bfloat16(), mask)
+        b = _self_attention(mha, q.detach().bfloat16(), v2.bfloat16(), mask)
+    assert torch.equal(a, b)
+    w = torch.randn_like(out, dtype=torch.float32)
+    g = torch.autograd.grad((out.float() * w).sum(), (q, v, mha.in_proj_weight))
+    g0 = torch.autograd.grad((ref.float() * w).sum(), (q, v, mha.in_proj_weight))
+    for x, y in zip(g, g0):
+        assert _rel(x, y) < 5e-2
+
+
 def test_flat_params_training_step_matches_plain_parameters():
     """FlatParams (flat master / gradient buffers + bf16 mirror) gives the gradients and the AdamW update of the
     same model with ordinary parameters."""

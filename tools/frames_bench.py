@@ -27,6 +27,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--frames", type=int, default=200)
     ap.add_argument("--eager", action="store_true", help="no CUDA graph (launch-bound reference point)")
+    ap.add_argument("--stream", choices=("f32", "bf16"), default="f32",
+                    help="dtype of the residual stream between layers: f32 = what the reference's modules do under "
+                         "autocast (default); bf16 = feed bf16 activations, every layer then reads and writes half the bytes")
     ap.add_argument("--varying-queries", action="store_true",
                     help="500 object queries + a number of track queries that changes every frame (20..60), through "
                          "kinet_b200.frame_graph.FrameGraphs (one decoder graph per bucket of 32 queries)")
@@ -48,6 +51,10 @@ def main():
     src = torch.randn(1, S, 288, device=dev)
     pos = torch.randn(1, S, 288, device=dev) * 0.1
     frames = [torch.randn(1, S, 288, device=dev) for _ in range(4)]   # stand-ins for the backbone's output
+    if args.stream == "bf16":
+        assert args.layers == "fused"
+        src, pos, frames = src.bfloat16(), pos.bfloat16(), [f.bfloat16() for f in frames]
+        model.query_embed.to(torch.bfloat16)        # tgt / query_pos start the decoder's stream
 
     # ONE autocast region around warm-up, capture and replay: autocast's cache of bf16 weight copies lives as
     # long as the outermost region, so the per-frame graph holds no weight casts (a tracker loop would wrap
@@ -112,7 +119,7 @@ def main():
         ms = float(ms)
         print(json.dumps({"metric": "tracking_transformer_frames_per_s", "value": world * args.frames / ms * 1e3,
                           "n_gpus": world, "ms_per_frame_per_gpu": ms / args.frames, "frames_per_gpu": args.frames,
-                          "mode": "frame_graphs_varying_queries" if args.varying_queries else ("eager" if args.eager else "cuda_graph"), "layers": args.layers,
+                          "mode": "frame_graphs_varying_queries" if args.varying_queries else ("eager" if args.eager else "cuda_graph"), "layers": args.layers, "residual_stream": args.stream,
                           "config": "MOT17 750x1333 pyramid, S=20906, d=288 (D=36), 6 enc + 6 dec layers, "
                                     "560 queries, bf16 autocast, forward; replicas, no communication"}))
     if not args.varying_queries:
