@@ -159,20 +159,18 @@ __device__ __forceinline__ void fold_columns(float4 (&acc)[KMAX], float* smem, f
 }
 
 template <int KMAX>
-__global__ void __launch_bounds__(kWarps * 32, KMAX <= 2 ? 3 : (KMAX <= 4 ? 2 : 1))
+__global__ void __launch_bounds__(kWarps * 32, KMAX <= 2 ? 4 : (KMAX <= 3 ? 3 : (KMAX <= 4 ? 2 : 1)))
 add_layernorm_bwd_kernel(const kinet_ln_bwd_args a)
 {
     extern __shared__ float smem[];   // [kWarps][C]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nvec = a.C >> 2;
     const float inv_c = 1.f / (float)a.C;
-    float4 gam[KMAX], dg[KMAX], db[KMAX];
+    // gamma is re-read per row (L1 hits), like in the forward: registers buy rows in flight
+    const float4* __restrict__ gamma4 = reinterpret_cast<const float4*>(a.gamma);
+    float4 dg[KMAX], db[KMAX];
 #pragma unroll
-    for (int k = 0; k < KMAX; ++k) {
-        const int v = lane + 32 * k;
-        dg[k] = db[k] = gam[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (v < nvec) gam[k] = reinterpret_cast<const float4*>(a.gamma)[v];
-    }
+    for (int k = 0; k < KMAX; ++k) dg[k] = db[k] = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int64_t row = (int64_t)blockIdx.x * kWarps + warp; row < a.rows; row += (int64_t)gridDim.x * kWarps) {
         const size_t base = (size_t)row * a.C;
         const float2 ms = reinterpret_cast<const float2*>(a.mean_rstd)[row];
@@ -201,7 +199,8 @@ add_layernorm_bwd_kernel(const kinet_ln_bwd_args a)
                 xh[k] = make_float4((z.x - ms.x) * ms.y, (z.y - ms.x) * ms.y, (z.z - ms.x) * ms.y, (z.w - ms.x) * ms.y);
                 dg[k].x += g.x * xh[k].x; dg[k].y += g.y * xh[k].y; dg[k].z += g.z * xh[k].z; dg[k].w += g.w * xh[k].w;
                 db[k].x += g.x; db[k].y += g.y; db[k].z += g.z; db[k].w += g.w;
-                wd[k] = make_float4(g.x * gam[k].x, g.y * gam[k].y, g.z * gam[k].z, g.w * gam[k].w);
+                const float4 gam = __ldg(gamma4 + v);
+                wd[k] = make_float4(g.x * gam.x, g.y * gam.y, g.z * gam.z, g.w * gam.w);
                 c1 += (wd[k].x + wd[k].y) + (wd[k].z + wd[k].w);
                 c2 += (wd[k].x * xh[k].x + wd[k].y * xh[k].y) + (wd[k].z * xh[k].z + wd[k].w * xh[k].w);
             }
