@@ -42,6 +42,8 @@ class FlatParams:
                 p.data = self.master[off:off + n].view_as(p)
                 p.grad = self.grads[off:off + n].view_as(p)
                 views[id(p)] = self.lp[off:off + n].view_as(p)
+        self.params = params
+        self.grad_views = [p.grad for p in params]
         self.flat_parameter = nn.Parameter(self.master)       # what the optimizer steps (same storage as the views)
         self.flat_parameter.grad = self.grads
         for m in module.modules():
@@ -59,11 +61,30 @@ class FlatParams:
     def zero_grad(self):
         self.grads.zero_()
 
+    def detach_grads(self):
+        """Before a backward: let autograd hand every parameter its gradient tensor as is (``p.grad = None``)
+        instead of adding it into the pre-set flat views -- one small add kernel per parameter and step
+        (258 of them, 0.5 ms, in a 6+6-layer stack).  ``gather_grads`` moves them into the flat buffer."""
+        for p in self.params:
+            p.grad = None
+
+    def gather_grads(self):
+        """After the backward started with ``detach_grads``: copy all gradients into the flat buffer with one
+        multi-tensor kernel (parameters that received none get zeros) and point ``p.grad`` at the views again."""
+        have = [(v, p.grad) for v, p in zip(self.grad_views, self.params) if p.grad is not None]
+        for v, p in zip(self.grad_views, self.params):
+            if p.grad is None:
+                v.zero_()
+        if have:
+            torch._foreach_copy_([v for v, _ in have], [g for _, g in have])
+        for v, p in zip(self.grad_views, self.params):
+            p.grad = v
+
 
 class GraphedTrainStep:
     """One data-parallel training step as two CUDA graphs with a single all-reduce between them:
 
-        graph 1: zero the flat gradient buffer, forward, loss, backward (every gradient lands in FlatParams.grads)
+        graph 1: forward, loss, backward, ONE multi-tensor copy of all gradients into FlatParams.grads
         NCCL   : all_reduce(grads, AVG) when torch.distributed is initialised with more than one rank
         graph 2: optimizer step on the flat parameter, refresh of the low-precision weight mirror
 
@@ -101,9 +122,10 @@ class GraphedTrainStep:
             self._update()
 
     def _forward_backward(self):
-        self.flat.zero_grad()
+        self.flat.detach_grads()
         loss = self._loss_fn(*self.inputs)
         loss.backward()
+        self.flat.gather_grads()
         self.loss.copy_(loss.detach())
 
     def _exchange(self):
