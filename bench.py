@@ -358,6 +358,95 @@ def bind_to_gpu_numa_node(index):
         return "default (%s)" % type(e).__name__
 
 
+# ---------------------------------------------------------------------------------------------
+# Callers: the other half of BASELINE.json's metric ("KineT frames/sec at 1/2/4/8 B200") and configs[3]
+# ---------------------------------------------------------------------------------------------
+def measure_callers(rank, world, dev, frames=100, train_steps=10):
+    """Tracking frames/s (configs[2]: MOT17 pyramid, d=288, 6+6 layers, 560 queries, bf16 autocast, one CUDA graph
+    per GPU, independent sequences per GPU) and data-parallel training samples/s (configs[3]: 800x1333 pyramid,
+    d=256, batch 2 per GPU, fwd+bwd+AdamW as two CUDA graphs around ONE NCCL all-reduce of the gradients) of the
+    6-layer encoder + 6-layer decoder built from kinet_b200.modules' layer classes -- the same measurements as
+    tools/frames_bench.py and tools/train_bench.py, device-timed, max over ranks.  The backbone, the heads, the
+    matcher and the tracker's Python are the reference's and are not part of these numbers."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from _harness import FusedStack
+    from kinet_b200.training import GraphedTrainStep
+    from kinet_b200.workloads import PYRAMIDS
+    out = {}
+    # ---- tracking frames ----
+    levels = PYRAMIDS["mot17_750x1333"]
+    S = sum(h * w for h, w in levels)
+    torch.manual_seed(1000 + rank)
+    model = FusedStack(levels, n_queries=560, d=288).to(dev).eval()
+    src = torch.randn(1, S, 288, device=dev)
+    pos = torch.randn(1, S, 288, device=dev) * 0.1
+    feeds = [torch.randn(1, S, 288, device=dev) for _ in range(4)]
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        def frame():
+            with torch.no_grad():
+                return model(src, pos)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                frame()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            frame()
+
+        def run(n):
+            for i in range(n):
+                src.copy_(feeds[i & 3], non_blocking=True)       # a new frame lands in the graph's input buffer
+                graph.replay()
+        run(10)
+        torch.cuda.synchronize()
+        if world > 1:
+            torch.distributed.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); run(frames); b.record()
+        torch.cuda.synchronize()
+    ms = reduce_max([a.elapsed_time(b)], dev, world)[0]
+    out["tracking_frames_per_s"] = {"value": world * frames / ms * 1e3, "ms_per_frame_per_gpu": ms / frames,
+                                    "config": "MOT17 750x1333 pyramid, S=20906, d=288 (D=36), 6 enc + 6 dec layers, "
+                                              "560 queries, bf16 autocast, forward, CUDA graph; replicas"}
+    del graph, model
+    # ---- data-parallel training ----
+    levels = PYRAMIDS["detr_800x1333"]
+    S = sum(h * w for h, w in levels)
+    torch.manual_seed(0)                                          # same initial weights on every rank
+    model = FusedStack(levels, n_queries=300, d=256).to(dev).train()
+    g = torch.Generator(device=dev).manual_seed(100 + rank)       # a different batch on every rank
+    batches = [(torch.randn(2, S, 256, device=dev, generator=g), torch.randn(2, S, 256, device=dev, generator=g) * 0.1,
+                torch.randn(2, 300, 256, device=dev, generator=g)) for _ in range(2)]
+
+    def loss_fn(x, p, target):
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            hs, _ = model(x, p)
+        return (hs.float() - target).square().mean()
+    step = GraphedTrainStep(model, loss_fn,
+                            lambda ps: torch.optim.AdamW(ps, lr=1e-4, weight_decay=1e-4, fused=True, capturable=True),
+                            batches[0])
+    for i in range(3):
+        step(*batches[i & 1])
+    torch.cuda.synchronize()
+    if world > 1:
+        torch.distributed.barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(train_steps):
+        step(*batches[i & 1])
+    b.record()
+    torch.cuda.synchronize()
+    ms = reduce_max([a.elapsed_time(b)], dev, world)[0]
+    out["training_samples_per_s"] = {"value": world * 2 * train_steps / ms * 1e3, "ms_per_step": ms / train_steps,
+                                     "config": "800x1333 pyramid, S=22223, d=256, 6 enc + 6 dec layers, 300 queries, "
+                                               "batch 2 per GPU, bf16 autocast, fwd+bwd+AdamW, two CUDA graphs + one "
+                                               "NCCL gradient all-reduce per step"}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -366,6 +455,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--e2e-steps", type=int, default=6)
     ap.add_argument("--cpu-steps", type=int, default=5)
+    ap.add_argument("--no-callers", action="store_true",
+                    help="skip the frames/s and training samples/s leg (tracking / training stacks around the op)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
@@ -403,6 +494,12 @@ def main():
     r = run_ours(args, rank, world, dev)
     ms, e2e_ms = r["ms"], r["e2e_ms"]
     ms, e2e_ms = reduce_max([ms, e2e_ms], dev, world)
+    callers = None
+    if not args.no_callers:
+        try:
+            callers = measure_callers(rank, world, dev)
+        except Exception as e:          # reported, never fatal for the contract line
+            callers = {"error": "%s: %s" % (type(e).__name__, str(e)[:200])}
     if rank == 0:
         peak, peak_src = measured_peak()
         ms_step = ms / args.steps
@@ -441,6 +538,8 @@ def main():
                 "cpu_baseline": {"value": cpu["value"], "unit": UNIT, "cores": cpu["cores"], "kind": "port",
                                  "sample": cpu["sample"], "ms_per_sample": cpu["ms"]},
                 "clocks": r["clocks"]}
+        if callers is not None:
+            line["callers"] = callers
         print(json.dumps(line), flush=True)
     if world > 1:
         torch.distributed.destroy_process_group()
