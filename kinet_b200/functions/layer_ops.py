@@ -34,11 +34,6 @@ def _rows(t, C):
     return t.numel() // C
 
 
-def ln_supported(x, C):
-    """The fused kernel covers fp32 / bf16 CUDA tensors with C % 4 == 0, C <= 1024."""
-    return x.is_cuda and x.dtype in _LN_DTYPES and C % 4 == 0 and 0 < C <= MAX_C
-
-
 def _canon_pos(pos, x):
     """pos as a contiguous [pos_rows, C] block that row i of x reads at i % pos_rows.
     Accepts pos shaped like x, or broadcast over the leading (batch) dimension."""

@@ -13,7 +13,7 @@ launches separate add / LayerNorm / add / cast kernels (and, in training, LayerN
 reduction and the generic bias-gradient reductions).  The residual stream keeps its dtype (fp32 under
 autocast, exactly as the reference's modules would behave under autocast); the GEMMs stay cuBLAS.
 
-Inputs the fused kernels do not cover (CPU tensors, fp16/fp64 streams, C % 4 != 0 or C > 1024) raise from
+Inputs the fused kernels do not cover (CPU tensors, fp64 streams, C % 4 != 0 or C > 1024) raise from
 the kernels' wrappers -- there is no PyTorch fallback behind these classes.
 """
 import copy
