@@ -17,6 +17,7 @@ Inputs the fused kernels do not cover (CPU tensors, fp64 streams, C % 4 != 0 or 
 the kernels' wrappers -- there is no PyTorch fallback behind these classes.
 """
 import copy
+import math
 import weakref
 
 import torch
@@ -318,3 +319,171 @@ class DeformableTransformerDecoder(nn.Module):
         if self.return_intermediate:
             return torch.stack(intermediate), torch.stack(intermediate_reference_points)
         return output, reference_points
+
+
+_shape_tensors = {}     # (tuple of (H, W), device) -> int64 tensor, so every forward hands the SAME tensor object down
+
+
+def _shapes_tensor(shapes, device):
+    """The (L, 2) int64 level-shape tensor for a pyramid.  The reference builds a fresh tensor on every forward
+    (:155), which defeats the per-tensor caches above and in MSDeformAttn (shape check, level grids, offset
+    divisors) and costs a host->device copy per frame; pyramids repeat, so the tensor is kept per shape list."""
+    key = (tuple(shapes), str(device))
+    t = _shape_tensors.get(key)
+    if t is None:
+        if len(_shape_tensors) > 64:
+            _shape_tensors.clear()
+        t = torch.as_tensor(shapes, dtype=torch.long, device=device)
+        _shape_tensors[key] = t
+    return t
+
+
+class DeformableTransformer(nn.Module):
+    """The reference's DeformableTransformer (:19-257): flattens the feature pyramid, runs the encoder (once, or
+    once per frame with ``multi_frame_attention_separate_encoder``), builds the decoder's queries (learned object
+    queries, optionally preceded by the previous frame's track queries from ``targets``; or two-stage proposals)
+    and runs the decoder.  Same constructor arguments, parameter names (``level_embed``, ``reference_points``,
+    ``enc_output*``, ``pos_trans*``) and return tuple."""
+
+    def __init__(self, d_model=256, nhead=8, num_encoder_layers=6, num_decoder_layers=6, dim_feedforward=1024,
+                 dropout=0.1, activation="relu", return_intermediate_dec=False, num_feature_levels=4,
+                 dec_n_points=4, enc_n_points=4, two_stage=False, two_stage_num_proposals=300,
+                 multi_frame_attention_separate_encoder=False):
+        super().__init__()
+        self.d_model = d_model
+        self.nhead = nhead
+        self.two_stage = two_stage
+        self.two_stage_num_proposals = two_stage_num_proposals
+        self.num_feature_levels = num_feature_levels
+        self.multi_frame_attention_separate_encoder = multi_frame_attention_separate_encoder
+
+        enc_levels = num_feature_levels // 2 if multi_frame_attention_separate_encoder else num_feature_levels
+        self.encoder = DeformableTransformerEncoder(
+            DeformableTransformerEncoderLayer(d_model, dim_feedforward, dropout, activation, enc_levels, nhead,
+                                              enc_n_points), num_encoder_layers)
+        self.decoder = DeformableTransformerDecoder(
+            DeformableTransformerDecoderLayer(d_model, dim_feedforward, dropout, activation, num_feature_levels, nhead,
+                                              dec_n_points), num_decoder_layers, return_intermediate_dec)
+        self.level_embed = nn.Parameter(torch.Tensor(num_feature_levels, d_model))
+        if two_stage:
+            self.enc_output = nn.Linear(d_model, d_model)
+            self.enc_output_norm = nn.LayerNorm(d_model)
+            self.pos_trans = nn.Linear(d_model * 2, d_model * 2)
+            self.pos_trans_norm = nn.LayerNorm(d_model * 2)
+        else:
+            self.reference_points = nn.Linear(d_model, 2)
+        self._reset_parameters()
+
+    def _reset_parameters(self):
+        for p in self.parameters():
+            if p.dim() > 1:
+                nn.init.xavier_uniform_(p)
+        for m in self.modules():
+            if isinstance(m, MSDeformAttn):
+                m._reset_parameters()
+        if not self.two_stage:
+            nn.init.xavier_uniform_(self.reference_points.weight.data, gain=1.0)
+            nn.init.constant_(self.reference_points.bias.data, 0.)
+        nn.init.normal_(self.level_embed)
+
+    @staticmethod
+    def get_valid_ratio(mask):
+        """Fraction of each image that is not padding, (w, h) order, from a (N, H, W) mask (True = padding)."""
+        _, H, W = mask.shape
+        valid_h = (~mask[:, :, 0]).sum(1).float() / H
+        valid_w = (~mask[:, 0, :]).sum(1).float() / W
+        return torch.stack([valid_w, valid_h], -1)
+
+    def get_proposal_pos_embed(self, proposals):
+        """Sine embedding of two-stage proposals (N, L, 4) -> (N, L, 512) (reference :70-83)."""
+        num_pos_feats, temperature = 128, 10000
+        dim_t = torch.arange(num_pos_feats, dtype=torch.float32, device=proposals.device)
+        dim_t = temperature ** (2 * (dim_t // 2) / num_pos_feats)
+        pos = (proposals.sigmoid() * (2 * math.pi))[:, :, :, None] / dim_t
+        return torch.stack((pos[:, :, :, 0::2].sin(), pos[:, :, :, 1::2].cos()), dim=4).flatten(2)
+
+    def gen_encoder_output_proposals(self, memory, memory_padding_mask, spatial_shapes):
+        """Two-stage: one box proposal per encoder token (pixel centre, level-dependent size) in logit space, invalid
+        ones pushed to +inf, and the projected memory they are scored from (reference :85-117).  ``spatial_shapes``
+        is the Python list of (H, W)."""
+        N_ = memory.shape[0]
+        proposals, cur = [], 0
+        for lvl, (H_, W_) in enumerate(spatial_shapes):
+            m = memory_padding_mask[:, cur:cur + H_ * W_].view(N_, H_, W_, 1)
+            valid_h = (~m[:, :, 0, 0]).sum(1)
+            valid_w = (~m[:, 0, :, 0]).sum(1)
+            gy, gx = torch.meshgrid(torch.linspace(0, H_ - 1, H_, dtype=torch.float32, device=memory.device),
+                                    torch.linspace(0, W_ - 1, W_, dtype=torch.float32, device=memory.device), indexing="ij")
+            grid = torch.stack([gx, gy], -1)
+            scale = torch.stack([valid_w, valid_h], 1).view(N_, 1, 1, 2)
+            grid = (grid[None].expand(N_, -1, -1, -1) + 0.5) / scale
+            wh = torch.ones_like(grid) * 0.05 * (2.0 ** lvl)
+            proposals.append(torch.cat((grid, wh), -1).view(N_, -1, 4))
+            cur += H_ * W_
+        out = torch.cat(proposals, 1)
+        valid = ((out > 0.01) & (out < 0.99)).all(-1, keepdim=True)
+        out = torch.log(out / (1 - out))
+        out = out.masked_fill(memory_padding_mask.unsqueeze(-1), float("inf")).masked_fill(~valid, float("inf"))
+        mem = memory.masked_fill(memory_padding_mask.unsqueeze(-1), 0.0).masked_fill(~valid, 0.0)
+        return self.enc_output_norm(self.enc_output(mem)), out
+
+    def forward(self, srcs, masks, pos_embeds, query_embed=None, targets=None):
+        """srcs / pos_embeds: per level (N, C, H, W); masks: per level (N, H, W) bool, True = padding;
+        query_embed (Lq, 2C) = [query_pos | tgt] (required unless two_stage); targets: optional list of dicts with
+        'track_query_hs_embeds' (T, C) and 'track_query_boxes' (T, 4) -- the previous frame's tracks, which become
+        the first T decoder queries.  -> (hs, memory, init_reference, inter_references, enc_class, enc_coord)."""
+        assert self.two_stage or query_embed is not None
+        shapes, src_l, mask_l, pos_l = [], [], [], []
+        for lvl, (src, mask, pos) in enumerate(zip(srcs, masks, pos_embeds)):
+            shapes.append((int(src.shape[2]), int(src.shape[3])))
+            src_l.append(src.flatten(2).transpose(1, 2))
+            mask_l.append(mask.flatten(1))
+            pos_l.append(pos.flatten(2).transpose(1, 2) + self.level_embed[lvl].view(1, 1, -1))
+        src_flatten, mask_flatten, pos_flatten = torch.cat(src_l, 1), torch.cat(mask_l, 1), torch.cat(pos_l, 1)
+        device = src_flatten.device
+        spatial_shapes = _shapes_tensor(shapes, device)
+        valid_ratios = torch.stack([self.get_valid_ratio(m) for m in masks], 1)
+
+        if self.multi_frame_attention_separate_encoder:
+            # levels [0, L/2) are the current frame's, [L/2, L) the previous frame's; one encoder, run per frame
+            half, hl = src_flatten.shape[1] // 2, self.num_feature_levels // 2
+            prev_memory = self.encoder(src_flatten[:, :half], _shapes_tensor(shapes[:hl], device), valid_ratios[:, :hl],
+                                       pos_flatten[:, :half], mask_flatten[:, :half])
+            memory = self.encoder(src_flatten[:, half:], _shapes_tensor(shapes[hl:], device), valid_ratios[:, hl:],
+                                  pos_flatten[:, half:], mask_flatten[:, half:])
+            memory = torch.cat([memory, prev_memory], 1)
+            memory_for_decoder = memory
+        else:
+            stream = self.encoder(src_flatten, spatial_shapes, valid_ratios, pos_flatten, mask_flatten,
+                                  return_stream=True)
+            memory, memory_for_decoder = stream.x, stream        # the decoder reuses the low-precision copy
+
+        bs, _, c = memory.shape
+        query_attn_mask = None
+        enc_outputs_class = enc_outputs_coord_unact = None
+        if self.two_stage:
+            output_memory, output_proposals = self.gen_encoder_output_proposals(memory, mask_flatten, shapes)
+            enc_outputs_class = self.decoder.class_embed[self.decoder.num_layers](output_memory)
+            enc_outputs_coord_unact = self.decoder.bbox_embed[self.decoder.num_layers](output_memory) + output_proposals
+            top = torch.topk(enc_outputs_class[..., 0], self.two_stage_num_proposals, dim=1)[1]
+            top_coords = torch.gather(enc_outputs_coord_unact, 1, top.unsqueeze(-1).repeat(1, 1, 4)).detach()
+            reference_points = top_coords.sigmoid()
+            query_embed, tgt = torch.split(self.pos_trans_norm(self.pos_trans(self.get_proposal_pos_embed(top_coords))),
+                                           c, dim=2)
+        else:
+            query_embed, tgt = torch.split(query_embed, c, dim=1)
+            query_embed = query_embed.unsqueeze(0).expand(bs, -1, -1)
+            tgt = tgt.unsqueeze(0).expand(bs, -1, -1)
+            reference_points = self.reference_points(query_embed).sigmoid()
+            if targets is not None and "track_query_hs_embeds" in targets[0]:
+                # track queries: content = the track's last decoder output, no positional part, reference = box centre
+                prev_hs = torch.stack([t["track_query_hs_embeds"] for t in targets])
+                prev_boxes = torch.stack([t["track_query_boxes"] for t in targets])
+                query_embed = torch.cat([torch.zeros_like(prev_hs), query_embed], dim=1)
+                tgt = torch.cat([prev_hs, tgt], dim=1)
+                reference_points = torch.cat([prev_boxes[..., :2], reference_points], dim=1)
+        init_reference_out = reference_points
+
+        hs, inter_references = self.decoder(tgt, reference_points, memory_for_decoder, spatial_shapes, valid_ratios,
+                                            query_embed, mask_flatten, query_attn_mask)
+        return hs, memory, init_reference_out, inter_references, enc_outputs_class, enc_outputs_coord_unact

@@ -420,3 +420,51 @@ def test_layer_abi_from_a_cpp_host_program(tmp_path):
     print(res.stdout)
     assert res.returncode == 0, res.stdout + res.stderr
     assert "PASS" in res.stdout
+
+
+def _transformer_golden(case, dev):
+    z = np.load(os.path.join(HERE, "golden", "transformer_f32.npz"))
+    t = lambda k: torch.from_numpy(z[case + "." + k]).to(dev)
+    n = sum(1 for k in z.files if k.startswith(case + ".src"))
+    srcs = [t("src%d" % i).requires_grad_(case == "a") for i in range(n)]
+    masks, poss = [t("mask%d" % i) for i in range(n)], [t("pos%d" % i) for i in range(n)]
+    sd = {k[len(case) + 3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith(case + ".p:")}
+    return z, t, srcs, masks, poss, sd
+
+
+def test_deformable_transformer_matches_reference_golden_track_queries():
+    """kinet_b200.modules.DeformableTransformer on the GPU against the REAL reference DeformableTransformer
+    (CPU, oracle op; tests/golden/make_golden_transformer.py): 2 levels, 7 object + 3 track queries from `targets`,
+    intermediate outputs, input gradients."""
+    from kinet_b200.modules import DeformableTransformer
+    dev = _dev()
+    z, t, srcs, masks, poss, sd = _transformer_golden("a", dev)
+    model = DeformableTransformer(128, 8, 2, 2, 64, 0.0, "relu", True, 2, 2, 2)
+    model.load_state_dict(sd, strict=True)
+    model = model.to(dev).eval()
+    query_embed = t("query_embed").requires_grad_(True)
+    targets = [dict(track_query_hs_embeds=t("track_hs")[i], track_query_boxes=t("track_boxes")[i]) for i in range(2)]
+    hs, memory, init_ref, inter_ref, ec, eb = model(srcs, masks, poss, query_embed, targets)
+    assert ec is None and eb is None and hs.shape == (2, 2, 10, 128)
+    assert _rel(hs, t("hs")) < 2e-5 and _rel(memory, t("memory")) < 2e-5
+    assert _rel(init_ref, t("init_ref")) < 1e-6 and _rel(inter_ref, t("inter_ref")) < 1e-6
+    grads = torch.autograd.grad((hs * t("w_hs")).sum() + (memory * t("w_mem")).sum(), srcs + [query_embed])
+    for g, k in zip(grads, ["g_src0", "g_src1", "g_query_embed"]):
+        assert _rel(g, t(k)) < 1e-4, k
+    # the level-shape tensor is reused from call to call (per-tensor caches hit; CUDA-graph capturable)
+    from kinet_b200.modules.deformable_transformer import _shapes_tensor
+    assert _shapes_tensor([(6, 8), (3, 4)], srcs[0].device) is _shapes_tensor([(6, 8), (3, 4)], srcs[0].device)
+
+
+def test_deformable_transformer_matches_reference_golden_separate_frame_encoders():
+    """4 levels (2 per frame), multi_frame_attention_separate_encoder=True: the encoder runs once per frame."""
+    from kinet_b200.modules import DeformableTransformer
+    dev = _dev()
+    z, t, srcs, masks, poss, sd = _transformer_golden("b", dev)
+    model = DeformableTransformer(64, 8, 1, 1, 32, 0.0, "relu", True, 4, 2, 2, multi_frame_attention_separate_encoder=True)
+    model.load_state_dict(sd, strict=True)
+    model = model.to(dev).eval()
+    with torch.no_grad():
+        hs, memory, init_ref, inter_ref, _, _ = model(srcs, masks, poss, t("query_embed"), None)
+    assert _rel(hs, t("hs")) < 2e-5 and _rel(memory, t("memory")) < 2e-5
+    assert _rel(init_ref, t("init_ref")) < 1e-6

@@ -108,3 +108,78 @@ def test_layers_oracle_matches_reference_golden():
     for k, g in zip(["g_src", "g_pos", "g_tgt", "g_qpos"] + ["g:" + k for k in names], grads):
         scale = float(np.abs(z[k]).max())
         assert float(np.abs(g.numpy() - z[k]).max()) <= 2e-4 * max(scale, 1e-6), k
+
+
+def _transformer_case(z, case, device="cpu"):
+    import torch
+    t = lambda k: torch.from_numpy(z[case + "." + k]).to(device)
+    n = sum(1 for k in z.files if k.startswith(case + ".src"))
+    srcs = [t("src%d" % i).requires_grad_(case == "a") for i in range(n)]
+    masks, poss = [t("mask%d" % i) for i in range(n)], [t("pos%d" % i) for i in range(n)]
+    sd = {k[len(case) + 3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith(case + ".p:")}
+    return srcs, masks, poss, t("query_embed"), sd
+
+
+def test_transformer_glue_matches_reference_golden_on_cpu():
+    """kinet_b200.modules.DeformableTransformer's own logic (pyramid flattening, level embedding, valid ratios,
+    per-frame encoder runs, track queries from `targets`, reference points, return tuple) against golden vectors
+    from the REAL reference class (tests/golden/make_golden_transformer.py).  The encoder / decoder stacks, which
+    need the CUDA kernels, are stood in for by oracle/layers_oracle.py here; tests/test_layers_gpu.py runs the
+    real ones against the same file on the GPU."""
+    import os
+    import types
+    import torch
+    from kinet_b200.modules import DeformableTransformer
+    from oracle import layers_oracle as lo
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "transformer_f32.npz"))
+
+    def stand_ins(model, cfg_enc, cfg_dec):
+        params = dict(model.named_parameters())
+
+        class Enc(torch.nn.Module):
+            def forward(self, src, shapes, valid, pos=None, mask=None, return_stream=False):
+                levels = [tuple(hw) for hw in shapes.tolist()]
+                mem = lo.encoder(params, "encoder.", model_layers[0], src, levels, shapes, valid, pos, mask, cfg_enc)
+                return types.SimpleNamespace(x=mem, x_lp=mem) if return_stream else mem
+
+        class Dec(torch.nn.Module):
+            num_layers = 0
+
+            def forward(self, tgt, ref, src, shapes, valid, query_pos=None, mask=None, qmask=None):
+                memory = src.x if hasattr(src, "x") else src
+                outs = []
+                for i in range(model_layers[1]):
+                    tgt = lo.decoder_layer(params, "decoder.layers.%d." % i, tgt, query_pos,
+                                           ref[:, :, None] * valid[:, None], memory, shapes, mask, qmask, cfg_dec)
+                    outs.append(tgt)
+                return torch.stack(outs), torch.stack([ref] * len(outs))
+        return Enc(), Dec()
+
+    # case a: track queries, 2 levels
+    srcs, masks, poss, query_embed, sd = _transformer_case(z, "a")
+    model = DeformableTransformer(128, 8, 2, 2, 64, 0.0, "relu", True, 2, 2, 2)
+    model.load_state_dict(sd, strict=True)
+    model_layers = (2, 2)
+    enc, dec = stand_ins(model, (8, 2, 2), (8, 2, 2))
+    model.__dict__["_modules"]["encoder"], model.__dict__["_modules"]["decoder"] = enc, dec
+    targets = [dict(track_query_hs_embeds=torch.from_numpy(z["a.track_hs"][i]), track_query_boxes=torch.from_numpy(z["a.track_boxes"][i]))
+               for i in range(2)]
+    hs, memory, init_ref, inter_ref, ec, eb = model(srcs, masks, poss, query_embed, targets)
+    assert ec is None and eb is None
+    _close(hs.detach().numpy(), z["a.hs"], 1e-4, 1e-5)
+    _close(memory.detach().numpy(), z["a.memory"], 1e-4, 1e-5)
+    assert np.allclose(init_ref.detach().numpy(), z["a.init_ref"], atol=1e-6)
+    assert np.allclose(inter_ref.detach().numpy(), z["a.inter_ref"], atol=1e-6)
+
+    # case b: 4 levels, separate encoder runs per frame
+    srcs, masks, poss, query_embed, sd = _transformer_case(z, "b")
+    model = DeformableTransformer(64, 8, 1, 1, 32, 0.0, "relu", True, 4, 2, 2, multi_frame_attention_separate_encoder=True)
+    model.load_state_dict(sd, strict=True)
+    model_layers = (1, 1)
+    enc, dec = stand_ins(model, (8, 2, 2), (8, 4, 2))
+    model.__dict__["_modules"]["encoder"], model.__dict__["_modules"]["decoder"] = enc, dec
+    with torch.no_grad():
+        hs, memory, init_ref, inter_ref, _, _ = model(srcs, masks, poss, query_embed, None)
+    _close(hs.numpy(), z["b.hs"], 1e-4, 1e-5)
+    _close(memory.numpy(), z["b.memory"], 1e-4, 1e-5)
+    assert np.allclose(init_ref.numpy(), z["b.init_ref"], atol=1e-6)
