@@ -188,3 +188,28 @@ class FusedStack(nn.Module):
         dref = self.ref_proj(qpos).sigmoid()
         out, _ = self.decoder(tgt, dref, mem, shapes, valid, qpos)
         return out, mem.x
+
+
+def randomise_by_name(model):
+    """Parameters as a pure function of their names -- the rule of tests/golden/make_golden_transformer.py
+    (case c: the two-stage model is too large to store in the golden file)."""
+    import zlib
+    with torch.no_grad():
+        for name, p in model.named_parameters():
+            gn = torch.Generator().manual_seed(zlib.crc32(name.encode()))
+            if "norm" in name and name.endswith("weight"):
+                p.copy_(1 + 0.1 * torch.randn(p.shape, generator=gn))
+            elif p.dim() == 1:
+                p.copy_(0.1 * torch.randn(p.shape, generator=gn))
+            else:
+                p.copy_(torch.randn(p.shape, generator=gn) * (0.5 / p.shape[-1] ** 0.5))
+
+
+def two_stage_model():
+    """The model of golden case c: two-stage DeformableTransformer with Linear stand-ins for the detection heads."""
+    from kinet_b200.modules import DeformableTransformer
+    model = DeformableTransformer(256, 8, 1, 2, 32, 0.0, "relu", True, 2, 2, 2, two_stage=True, two_stage_num_proposals=6)
+    model.decoder.class_embed = nn.ModuleList(nn.Linear(256, 3) for _ in range(3))
+    model.decoder.bbox_embed = nn.ModuleList(nn.Linear(256, 4) for _ in range(3))
+    randomise_by_name(model)
+    return model.eval()

@@ -13,6 +13,8 @@ src/trackformer/models/deformable_transformer.py:19-257 (fp32, CPU, dropout 0, r
      ``targets`` ('track_query_hs_embeds' / 'track_query_boxes', :203-229); outputs and input gradients
   b: d_model 64, 1 + 1 layers, 4 feature levels with multi_frame_attention_separate_encoder=True (the encoder
      runs once per frame on 2 levels each, the decoder sees all 4, :160-175); outputs only
+  c: d_model 256 (parameters are a function of their names, not stored), 1 + 2 layers, two_stage=True with 6 proposals (:181-196) and iterative box refinement in the
+     decoder (bbox_embed set, :413-424; 4-d reference points); outputs only
 """
 import os
 
@@ -35,6 +37,21 @@ def randomise(model, g):
                 p.copy_(0.1 * torch.randn(p.shape, generator=g))
             else:
                 p.copy_(torch.randn(p.shape, generator=g) * (0.5 / p.shape[-1] ** 0.5))
+
+
+def randomise_by_name(model):
+    """Parameters as a pure function of their NAME (seed = crc32 of the name): a test can rebuild them without the
+    golden file having to carry a d_model = 256 model (two-stage hard-codes 4 x 128 sine features, :71)."""
+    import zlib
+    with torch.no_grad():
+        for name, p in model.named_parameters():
+            gn = torch.Generator().manual_seed(zlib.crc32(name.encode()))
+            if "norm" in name and name.endswith("weight"):
+                p.copy_(1 + 0.1 * torch.randn(p.shape, generator=gn))
+            elif p.dim() == 1:
+                p.copy_(0.1 * torch.randn(p.shape, generator=gn))
+            else:
+                p.copy_(torch.randn(p.shape, generator=gn) * (0.5 / p.shape[-1] ** 0.5))
 
 
 def inputs(g, d, sizes, N):
@@ -98,6 +115,26 @@ def main():
         blob["b.src%d" % i], blob["b.mask%d" % i], blob["b.pos%d" % i] = s.detach().numpy(), m.numpy(), p.numpy()
     blob.update({"b.query_embed": query_embed.numpy(), "b.hs": hs.numpy(), "b.memory": memory.numpy(),
                  "b.init_ref": init_ref.numpy(), "b.inter_ref": inter_ref.numpy()})
+
+    # ---- case c: two-stage (proposals from the encoder output) + iterative box refinement in the decoder ----
+    d, N = 256, 2
+    sizes = [(6, 8), (3, 4)]
+    model = dt.DeformableTransformer(d_model=d, nhead=8, num_encoder_layers=1, num_decoder_layers=2, dim_feedforward=32,
+                                     dropout=0.0, activation="relu", return_intermediate_dec=True,
+                                     num_feature_levels=2, dec_n_points=2, enc_n_points=2,
+                                     two_stage=True, two_stage_num_proposals=6)
+    # the detection head normally installs these (deformable_detr.py); plain Linear layers stand in for them
+    model.decoder.class_embed = torch.nn.ModuleList(torch.nn.Linear(d, 3) for _ in range(3))
+    model.decoder.bbox_embed = torch.nn.ModuleList(torch.nn.Linear(d, 4) for _ in range(3))
+    randomise_by_name(model)
+    model.eval()
+    srcs, masks, poss = inputs(g, d, sizes, N)
+    with torch.no_grad():
+        hs, memory, init_ref, inter_ref, enc_cls, enc_box = model(srcs, masks, poss, None, None)
+    for i, (s_, m, p) in enumerate(zip(srcs, masks, poss)):
+        blob["c.src%d" % i], blob["c.mask%d" % i], blob["c.pos%d" % i] = s_.detach().numpy(), m.numpy(), p.numpy()
+    blob.update({"c.hs": hs.numpy(), "c.memory": memory.numpy(), "c.init_ref": init_ref.numpy(),
+                 "c.inter_ref": inter_ref.numpy(), "c.enc_cls": enc_cls.numpy(), "c.enc_box": enc_box.numpy()})
 
     path = os.path.join(HERE, "transformer_f32.npz")
     np.savez_compressed(path, **blob)

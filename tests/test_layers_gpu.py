@@ -468,3 +468,23 @@ def test_deformable_transformer_matches_reference_golden_separate_frame_encoders
         hs, memory, init_ref, inter_ref, _, _ = model(srcs, masks, poss, t("query_embed"), None)
     assert _rel(hs, t("hs")) < 2e-5 and _rel(memory, t("memory")) < 2e-5
     assert _rel(init_ref, t("init_ref")) < 1e-6
+
+
+def test_deformable_transformer_two_stage_matches_reference_golden():
+    """Two-stage proposals + iterative box refinement (4-d reference points through the fused MSDeformAttn
+    prologue) on the GPU against the reference class's golden case c."""
+    import sys
+    sys.path.insert(0, HERE)
+    from _harness import two_stage_model
+    dev = _dev()
+    z = np.load(os.path.join(HERE, "golden", "transformer_f32.npz"))
+    srcs, masks, poss = ([torch.from_numpy(z["c.%s%d" % (k, i)]).to(dev) for i in range(2)] for k in ("src", "mask", "pos"))
+    model = two_stage_model().to(dev)
+    with torch.no_grad():
+        hs, memory, init_ref, inter_ref, enc_cls, enc_box = model(srcs, masks, poss, None, None)
+    t = lambda k: torch.from_numpy(z["c." + k]).to(dev)
+    assert _rel(memory, t("memory")) < 2e-5 and _rel(enc_cls, t("enc_cls")) < 2e-5
+    assert torch.equal(torch.isinf(enc_box), torch.isinf(t("enc_box")))
+    # the same proposals were selected (top-k on the class logit) and refined to the same boxes
+    assert _rel(init_ref, t("init_ref")) < 1e-5
+    assert _rel(hs, t("hs")) < 5e-5 and _rel(inter_ref, t("inter_ref")) < 1e-5

@@ -183,3 +183,58 @@ def test_transformer_glue_matches_reference_golden_on_cpu():
     _close(hs.numpy(), z["b.hs"], 1e-4, 1e-5)
     _close(memory.numpy(), z["b.memory"], 1e-4, 1e-5)
     assert np.allclose(init_ref.numpy(), z["b.init_ref"], atol=1e-6)
+
+
+def test_two_stage_transformer_glue_matches_reference_golden_on_cpu():
+    """Two-stage proposals (gen_encoder_output_proposals, top-k, proposal position embedding) and the decoder's
+    iterative box refinement of kinet_b200.modules against the reference class's golden case c; encoder / decoder
+    layers stood in for by the oracle (the GPU twin is in tests/test_layers_gpu.py)."""
+    import os
+    import sys
+    import types
+    import torch
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from _harness import two_stage_model
+    from kinet_b200.modules.deformable_transformer import inverse_sigmoid
+    from oracle import layers_oracle as lo
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "transformer_f32.npz"))
+    srcs, masks, poss = ([torch.from_numpy(z["c.%s%d" % (k, i)]) for i in range(2)] for k in ("src", "mask", "pos"))
+    model = two_stage_model()
+    params = dict(model.named_parameters())
+    heads = model.decoder.bbox_embed
+
+    class Enc(torch.nn.Module):
+        def forward(self, src, shapes, valid, pos=None, mask=None, return_stream=False):
+            mem = lo.encoder(params, "encoder.", 1, src, [tuple(hw) for hw in shapes.tolist()], shapes, valid, pos, mask,
+                             (8, 2, 2))
+            return types.SimpleNamespace(x=mem, x_lp=mem) if return_stream else mem
+
+    class Dec(torch.nn.Module):
+        num_layers = 2
+
+        def __init__(self, real):
+            super().__init__()
+            self.class_embed, self.bbox_embed = real.class_embed, real.bbox_embed
+
+        def forward(self, tgt, ref, src, shapes, valid, query_pos=None, mask=None, qmask=None):
+            memory = src.x if hasattr(src, "x") else src
+            outs, refs = [], []
+            for i in range(2):
+                rin = ref[:, :, None] * torch.cat([valid, valid], -1)[:, None]
+                tgt = lo.decoder_layer(params, "decoder.layers.%d." % i, tgt, query_pos, rin, memory, shapes, mask, qmask,
+                                       (8, 2, 2))
+                ref = (heads[i](tgt) + inverse_sigmoid(ref)).sigmoid().detach()
+                outs.append(tgt)
+                refs.append(ref)
+            return torch.stack(outs), torch.stack(refs)
+    model.__dict__["_modules"]["encoder"], model.__dict__["_modules"]["decoder"] = Enc(), Dec(model.decoder)
+    with torch.no_grad():
+        hs, memory, init_ref, inter_ref, enc_cls, enc_box = model(srcs, masks, poss, None, None)
+    _close(memory.numpy(), z["c.memory"], 1e-4, 1e-5)
+    _close(enc_cls.numpy(), z["c.enc_cls"], 1e-4, 1e-5)
+    assert np.array_equal(np.isinf(enc_box.numpy()), np.isinf(z["c.enc_box"]))
+    fin = np.isfinite(z["c.enc_box"])
+    assert np.allclose(enc_box.numpy()[fin], z["c.enc_box"][fin], rtol=1e-4, atol=1e-4)
+    assert np.allclose(init_ref.numpy(), z["c.init_ref"], atol=1e-5)
+    _close(hs.numpy(), z["c.hs"], 1e-4, 1e-5)
+    assert np.allclose(inter_ref.numpy(), z["c.inter_ref"], atol=1e-5)
