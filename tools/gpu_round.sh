@@ -19,4 +19,8 @@ ncu --metrics gpu__time_duration.sum --clock-control none -k regex:msda_ -c 600 
 python tools/quick_bench.py C2_enc --dtype bf16 --iters 2 > $O/plain_qb.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:'msda_(forward|backward)_kernel' -s 3 -c 4 \
     -o $O/prof_enc_bf16 python tools/quick_bench.py C2_enc --dtype bf16 --iters 2 > $O/ncu_full.log 2>&1
+python tools/layer_bench.py > $O/layer_bench.txt 2>&1; cat $O/layer_bench.txt
+python tools/frames_bench.py > $O/frames_1gpu.json 2>/dev/null; python tools/frames_bench.py --varying-queries >> $O/frames_1gpu.json 2>/dev/null; cat $O/frames_1gpu.json
+python tools/train_bench.py > $O/train_1gpu.json 2>/dev/null; cat $O/train_1gpu.json
+python tools/frame_profile.py --top 20 > $O/frame_breakdown.txt 2>&1; python tools/frame_profile.py --train --top 30 > $O/train_breakdown.txt 2>&1
 ls -la $O
