@@ -1,0 +1,33 @@
+"""A few values remembered per tensor OBJECT (identity + in-place version counter).
+
+The reference reads device-resident metadata on the host in every layer of every frame (the Len_in assertion,
+ms_deform_attn.py:62; H and W of every level, deformable_transformer.py:311-314): one device->host sync each,
+and illegal while a CUDA graph is being captured.  The same few ``spatial_shapes`` tensors come back call after
+call (one per pyramid; two alternating ones in the multi-frame configuration: the encoder's levels and the
+decoder's twice as many), so the derived values are kept for the last few tensor objects seen.  A tensor that
+was modified in place (version counter) or garbage-collected and replaced (weak reference) misses.
+"""
+import weakref
+from collections import OrderedDict
+
+
+class PerTensorCache:
+    def __init__(self, maxsize=8):
+        self.maxsize = maxsize
+        self._entries = OrderedDict()       # id(tensor) -> (weakref, version, extra key, value)
+
+    def get(self, tensor, extra=None):
+        e = self._entries.get(id(tensor))
+        if e is not None and e[0]() is tensor and e[1] == tensor._version and e[2] == extra:
+            return e[3]
+        return None
+
+    def put(self, tensor, value, extra=None):
+        self._entries[id(tensor)] = (weakref.ref(tensor), tensor._version, extra, value)
+        self._entries.move_to_end(id(tensor))
+        while len(self._entries) > self.maxsize:
+            self._entries.popitem(last=False)
+        return value
+
+    def __len__(self):
+        return len(self._entries)

@@ -14,7 +14,6 @@ drop-in shim for ``import MultiScaleDeformableAttention as MSDA``) re-exports.
 There is no CPU path: CPU tensors raise, like the reference (ms_deform_attn.h:27,48).
 """
 import ctypes
-import weakref
 
 import torch
 import torch.nn.functional as F
@@ -22,6 +21,7 @@ from torch.autograd import Function
 from torch.autograd.function import once_differentiable
 
 from .. import _lib
+from .._cache import PerTensorCache
 
 
 def _dims(value, loc):
@@ -206,21 +206,18 @@ def fused_supported(value, n_levels, n_points):
     return n_levels * n_points <= 4 * owners
 
 
-_norm_f32 = None      # (weakref to the last offset_norm tensor, its version, device, its fp32 copy)
+_norm_f32 = PerTensorCache()      # offset_norm tensor object -> its fp32 copy, keyed additionally by device
 
 
 def _offset_norm_f32(offset_norm, device):
     """fp32 copy of the (L, 2) offset divisors.  Every layer of a frame passes the same spatial_shapes tensor,
     so the int64 -> fp32 conversion (a 2 us kernel, twice per layer) is remembered per tensor object."""
-    global _norm_f32
     if offset_norm.dtype == torch.float32 and offset_norm.device == device and offset_norm.is_contiguous():
         return offset_norm
-    seen = _norm_f32
-    if seen is not None and seen[0]() is offset_norm and seen[1] == offset_norm._version and seen[2] == device:
-        return seen[3]
-    out = offset_norm.to(device=device, dtype=torch.float32).contiguous()
-    _norm_f32 = (weakref.ref(offset_norm), offset_norm._version, device, out)
-    return out
+    hit = _norm_f32.get(offset_norm, str(device))
+    if hit is not None:
+        return hit
+    return _norm_f32.put(offset_norm, offset_norm.to(device=device, dtype=torch.float32).contiguous(), str(device))
 
 
 def _fused_inputs(value, offsets, logits, reference_points, offset_norm, query_mask):

@@ -18,12 +18,12 @@ the kernels' wrappers -- there is no PyTorch fallback behind these classes.
 """
 import copy
 import math
-import weakref
 
 import torch
 import torch.nn.functional as F
 from torch import nn
 
+from .._cache import PerTensorCache
 from ..functions.layer_ops import add_layer_norm, inference_mirror, linear, linear_params
 from .ms_deform_attn import MSDeformAttn
 
@@ -56,19 +56,19 @@ def _lp_dtype(x):
     return x.dtype
 
 
-_grids = None   # (weakref to the shapes tensor, its version, device, per-level pixel-centre grids)
+_grids = PerTensorCache()   # spatial_shapes tensor object -> per-level pixel-centre grids, keyed additionally by device
 
 
 def _level_grids(spatial_shapes, device):
     """Flattened pixel-centre coordinates (y, x) of every level.  Reading H and W out of a CUDA
     ``spatial_shapes`` tensor is a device->host sync (the reference pays it on every forward, :311-314, and it
-    is illegal while a CUDA graph is being captured), so the grids are remembered for the tensor object
+    is illegal while a CUDA graph is being captured), so the grids are remembered for the tensor objects
     (identity + version counter) they were built from; an eager warm-up run with the same tensor fills them."""
-    global _grids
     is_t = torch.is_tensor(spatial_shapes)
-    if (is_t and _grids is not None and _grids[0]() is spatial_shapes and _grids[1] == spatial_shapes._version
-            and _grids[2] == device):
-        return _grids[3]
+    if is_t:
+        hit = _grids.get(spatial_shapes, str(device))
+        if hit is not None:
+            return hit
     out = []
     for H_, W_ in (spatial_shapes.tolist() if is_t else spatial_shapes):
         H_, W_ = int(H_), int(W_)
@@ -77,7 +77,7 @@ def _level_grids(spatial_shapes, device):
         gy, gx = torch.meshgrid(ys, xs, indexing="ij")
         out.append((gy.reshape(-1), gx.reshape(-1), H_, W_))
     if is_t:
-        _grids = (weakref.ref(spatial_shapes), spatial_shapes._version, device, out)
+        _grids.put(spatial_shapes, out, str(device))
     return out
 
 

@@ -11,35 +11,33 @@ divided by H and the y offset by W -- upstream Deformable-DETR flips to (W, H); 
 does not, and parity is defined against the reference.
 """
 
-import weakref
-
 import torch
 import torch.nn.functional as F
 from torch import nn
 from torch.nn.init import constant_, xavier_uniform_
 
+from .._cache import PerTensorCache
 from ..functions import MSDeformAttnFunction, MSDeformAttnFusedFunction, fused_supported
 from ..functions.layer_ops import linear as _linear
 
 
-_shapes_validated = None   # (weakref to the last validated spatial_shapes tensor, its version, Len_in)
+_shapes_validated = PerTensorCache()   # spatial_shapes tensor object -> True, keyed additionally by Len_in
 
 
 def _check_spatial_shapes(shapes, len_in):
     """The reference's ``assert (shapes[:, 0] * shapes[:, 1]).sum() == Len_in`` (ms_deform_attn.py:62).
     On CUDA tensors the comparison is a device->host sync per call, 12 per frame in a 6+6-layer
     transformer although every layer receives the same tensor.  The result is remembered for the tensor
-    object it was computed on (identity + version counter, shared by all module instances), so a frame
-    pays for it once; while a CUDA graph is being captured a sync is illegal and the check is skipped
+    objects it was computed on (identity + version counter, shared by all module instances; a few of them, so
+    the multi-frame configuration's alternation between the encoder's and the decoder's level list hits too), so
+    a frame pays for it once; while a CUDA graph is being captured a sync is illegal and the check is skipped
     (capture needs an eager warm-up run with the same tensors anyway, which validates them)."""
-    global _shapes_validated
-    seen = _shapes_validated
-    if seen is not None and seen[0]() is shapes and seen[1] == shapes._version and seen[2] == len_in:
+    if _shapes_validated.get(shapes, len_in):
         return
     if shapes.is_cuda and torch.cuda.is_current_stream_capturing():
         return
     assert (shapes[:, 0] * shapes[:, 1]).sum() == len_in
-    _shapes_validated = (weakref.ref(shapes), shapes._version, len_in)
+    _shapes_validated.put(shapes, True, len_in)
 
 
 class MSDeformAttn(nn.Module):

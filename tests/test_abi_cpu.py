@@ -173,3 +173,41 @@ def test_graft_entry_build_returns():
     g.build()
     from kinet_b200 import _lib
     assert _lib.load() is not None
+
+
+def test_per_tensor_caches_survive_alternating_level_lists(monkeypatch):
+    """The multi-frame configuration alternates between two spatial_shapes tensors (encoder: L levels, decoder: 2L);
+    the per-tensor caches must hit for both, re-evaluate after an in-place change, and never serve a new tensor
+    that happens to reuse an id."""
+    from kinet_b200._cache import PerTensorCache
+    from kinet_b200.modules import ms_deform_attn as mod
+    from kinet_b200.modules.deformable_transformer import _level_grids, _shapes_tensor
+    enc, dec = torch.tensor([[2, 3], [1, 2]]), torch.tensor([[2, 3], [1, 2], [2, 3], [1, 2]])
+    mod._shapes_validated = PerTensorCache()
+    evaluations = []
+    real_sum = torch.Tensor.sum
+    monkeypatch.setattr(torch.Tensor, "sum", lambda self, *a, **k: (evaluations.append(1), real_sum(self, *a, **k))[1])
+    for _ in range(4):
+        mod._check_spatial_shapes(enc, 8)
+        mod._check_spatial_shapes(dec, 16)
+    assert len(evaluations) == 2                       # once per tensor object, not once per call
+    with pytest.raises(AssertionError):
+        mod._check_spatial_shapes(enc, 9)              # another Len_in is another question
+    enc[0, 0] = 5                                      # in-place change: version counter moves, cache misses
+    with pytest.raises(AssertionError):
+        mod._check_spatial_shapes(enc, 8)
+    monkeypatch.undo()
+    g1 = _level_grids(dec, torch.device("cpu"))
+    assert _level_grids(dec, torch.device("cpu")) is g1 and len(g1) == 4 and g1[0][0].numel() == 6
+    assert _shapes_tensor([(2, 3), (1, 2)], "cpu") is _shapes_tensor([(2, 3), (1, 2)], "cpu")
+    c = PerTensorCache(maxsize=2)
+    ts = [torch.zeros(1) for _ in range(3)]
+    for i, t in enumerate(ts):
+        c.put(t, i)
+    assert len(c) == 2 and c.get(ts[0]) is None and c.get(ts[2]) == 2
+    t = torch.zeros(1)
+    c.put(t, "old")
+    key = id(t)
+    del t
+    t2 = torch.ones(1)                                 # may or may not reuse the id; a dead weakref must never hit
+    assert c.get(t2) is None or id(t2) != key
