@@ -15,7 +15,8 @@ __device__ __forceinline__ uint32_t hash32(uint32_t x) {
 }
 
 // rows_per_instr groups of GS lanes; each group handles one 16*GS-byte row per step.
-// mode 0: red.v4.f32   1: st.v4.f32   2: ld.v4 (gather)    rows are `row_bytes` apart
+// mode 0: red.v4.f32   1: st.v4.f32   2: ld.v4 (gather)   3: red.v4.bf16x2 (16 B = 8 bf16 per lane: the same row
+// of channels in HALF the sectors -- the 16-bit accumulator option of DESIGN.md section 10)    rows are `row_bytes` apart
 template <int GS, int MODE>
 __global__ void __launch_bounds__(256) k_rows(float* buf, uint32_t nrows, int row_floats, int steps, uint32_t seed,
                                               int local_span, float* sink)
@@ -32,6 +33,9 @@ __global__ void __launch_bounds__(256) k_rows(float* buf, uint32_t nrows, int ro
         float* p = buf + (size_t)r * row_floats + gl * 4;
         if (MODE == 0) {
             asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(p), "f"(1.f), "f"(2.f), "f"(3.f), "f"(4.f) : "memory");
+        } else if (MODE == 3) {
+            const unsigned one2 = 0x3f803f80u;      // bf16x2 {1.0, 1.0}
+            asm volatile("red.relaxed.gpu.global.add.noftz.v4.bf16x2 [%0], {%1,%2,%3,%4};" :: "l"(p), "r"(one2), "r"(one2), "r"(one2), "r"(one2) : "memory");
         } else if (MODE == 1) {
             *reinterpret_cast<float4*>(p) = make_float4(1.f, 2.f, 3.f, 4.f);
         } else {
@@ -116,6 +120,9 @@ int main()
         printf("%-22s ld.v4       64B rows (8 rows/instr): %8.3f ms  %7.1f GB/s  %6.2f Grow/s\n", rg.name, ms, warps * steps * 8 * 64 / ms / 1e6, warps * steps * 8 / ms / 1e6);
         ms = time_ms([&] { k_rows<4, 0><<<grid, threads>>>(buf, nrows64, 16, steps, 1u, rg.span, sink); });
         printf("%-22s red.v4.f32  64B rows (8 rows/instr): %8.3f ms  %7.1f GB/s  %6.2f Grow/s\n", rg.name, ms, warps * steps * 8 * 64 / ms / 1e6, warps * steps * 8 / ms / 1e6);
+        // 32 bf16 channels = one 64-byte row per 4 lanes: what a 16-bit grad_value accumulator would send
+        ms = time_ms([&] { k_rows<4, 3><<<grid, threads>>>(buf, nrows64, 16, steps, 1u, rg.span, sink); });
+        printf("%-22s red.v4.bf16x2 64B rows (8 rows/instr): %6.3f ms  %7.1f GB/s  %6.2f Grow/s\n", rg.name, ms, warps * steps * 8 * 64 / ms / 1e6, warps * steps * 8 / ms / 1e6);
     }
     {
         const uint32_t nrows128 = (uint32_t)(bytes / 128);
