@@ -53,14 +53,19 @@ __device__ __forceinline__ void reduce_scatter(float (&U)[N][4], int gl, int grp
 // WIDE: every level has W > 1 (uniform column step of the 2x2 footprint).
 // FUSED: loc / attn are raw sampling offsets / attention logits, grad_loc / grad_attn their gradients
 // (through the location arithmetic and the softmax); see SampleSrc<AT, true> in msda_common.cuh.
-template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE, bool FUSED>
-__device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage_a, int* stage_dx,
-                                               float4* stage_b, float4* fold,
-                                               const VT* __restrict__ value,
-                                               const AT* __restrict__ loc, const AT* __restrict__ attn,
-                                               const VT* __restrict__ grad_out,
-                                               float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
-                                               AT* __restrict__ grad_attn, const KernelDims& d, const FusedArgs& fa)
+//
+// backward_rows: the `count` query rows qmap(0) .. qmap(count-1) (-1 = no row) of one (batch, head) pair, NWARPS
+// warps.  Called once per work item by msda_backward_kernel, and by the dense-window kernel (msda_dense.cuh) for
+// the items whose sampling footprint does not fit its windows.
+template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE, bool FUSED, typename QMap>
+__device__ __forceinline__ void backward_rows(const LevelTable& lt, int2* stage_a, int* stage_dx,
+                                              float4* stage_b, float4* fold,
+                                              const VT* __restrict__ value,
+                                              const AT* __restrict__ loc, const AT* __restrict__ attn,
+                                              const VT* __restrict__ grad_out,
+                                              float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
+                                              AT* __restrict__ grad_attn, const KernelDims& d, const FusedArgs& fa,
+                                              int b, int m, int count, const QMap& qmap)
 {
     // fused: chunks of a row whose d out / d attention stay in registers until the row's softmax backward
     // (the launcher guarantees L*P <= MAXCH * CH)
@@ -81,22 +86,14 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
     const int grp_base = grp * GS;
     const int LP = d.L * d.P;
     const int rsv = d.M * GS;
-    const int chunks = (d.Lq + d.tile_q - 1) / d.tile_q;
-    const int items = chunks * d.N * d.M;
     constexpr int PASS = NWARPS * GPW;     // query rows per CTA pass
-
-    for (int item = blockIdx.x; item < items; item += gridDim.x) {   // one item per CTA (grid == items)
-        const int chunk = item / (d.N * d.M);
-        const int bm = item - chunk * (d.N * d.M);
-        const int b = bm / d.M, m = bm - b * d.M;
+    {
         const size_t bbase = ((size_t)b * d.S * d.M + m) * D + gl * VEC;
         const VT* lane_base = value + bbase;
         float* gv_base = grad_value_acc + bbase;
 
-        const int pos0 = chunk * d.tile_q;
-        const int count = min(d.tile_q, d.Lq - pos0);
         for (int i0 = warp * GPW; i0 < count; i0 += PASS) {
-            const int q = (lane_used && i0 + grp < count) ? walk_query(lt, d, pos0 + i0 + grp) : -1;
+            const int q = (lane_used && i0 + grp < count) ? qmap(i0 + grp) : -1;
             const bool row_ok = q >= 0;
             const size_t rowq = (size_t)b * d.Lq + (row_ok ? q : 0);
             const size_t row = rowq * d.M + m;
@@ -227,6 +224,31 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage
                 }
             }
         }
+    }
+}
+
+// One work item per CTA (grid == items; the loop only guards against a capped grid): item = (chunk of tile_q
+// positions of the query walk, batch, head), see walk_query.
+template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE, bool FUSED>
+__device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage_a, int* stage_dx,
+                                               float4* stage_b, float4* fold,
+                                               const VT* __restrict__ value,
+                                               const AT* __restrict__ loc, const AT* __restrict__ attn,
+                                               const VT* __restrict__ grad_out,
+                                               float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
+                                               AT* __restrict__ grad_attn, const KernelDims& d, const FusedArgs& fa)
+{
+    const int chunks = (d.Lq + d.tile_q - 1) / d.tile_q;
+    const int items = chunks * d.N * d.M;
+    for (int item = blockIdx.x; item < items; item += gridDim.x) {
+        const int chunk = item / (d.N * d.M);
+        const int bm = item - chunk * (d.N * d.M);
+        const int b = bm / d.M, m = bm - b * d.M;
+        const int pos0 = chunk * d.tile_q;
+        const int count = min(d.tile_q, d.Lq - pos0);
+        backward_rows<VT, AT, VEC, GS, NWARPS, WIDE, FUSED>(
+            lt, stage_a, stage_dx, stage_b, fold, value, loc, attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa,
+            b, m, count, [&](int i) { return walk_query(lt, d, pos0 + i); });
     }
 }
 

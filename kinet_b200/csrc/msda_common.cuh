@@ -209,6 +209,15 @@ template <> __device__ __forceinline__ float2 load_loc<__half>(const __half* p) 
     float2 r; unpack_f16x2(w, r.x, r.y); return r;
 }
 template <typename A> __device__ __forceinline__ float load_attn(const A* p) { return to_f32<A>(__ldg(p)); }
+// The same through L1 (the dense-window kernel reads a row's samples twice: window search, then level by level).
+template <typename A> __device__ __forceinline__ float2 load_loc_cached(const A* p);
+template <> __device__ __forceinline__ float2 load_loc_cached<float>(const float* p) { return __ldg(reinterpret_cast<const float2*>(p)); }
+template <> __device__ __forceinline__ float2 load_loc_cached<__nv_bfloat16>(const __nv_bfloat16* p) {
+    float2 r; unpack_bf16x2(__ldg(reinterpret_cast<const uint32_t*>(p)), r.x, r.y); return r;
+}
+template <> __device__ __forceinline__ float2 load_loc_cached<__half>(const __half* p) {
+    float2 r; unpack_f16x2(__ldg(reinterpret_cast<const uint32_t*>(p)), r.x, r.y); return r;
+}
 
 template <typename A> __device__ __forceinline__ void store_loc(A* p, float x, float y);
 template <> __device__ __forceinline__ void store_loc<float>(float* p, float x, float y) {

@@ -1,0 +1,582 @@
+// msda_dense.cuh -- encoder-form MSDeformAttn backward on the sm_100a tensor cores (tcgen05 + TMEM).
+//
+// Replaces, for the encoder form (the queries are the pyramid's pixels, Lq == S) and 16-bit values, the
+// reference's col2im kernels (ms_deform_im2col_cuda.cuh:239-378: one global atomicAdd per channel and
+// corner) and this library's own one-reduction-per-corner-row kernel (msda_bwd.cuh).  Nothing here follows
+// the reference's code; the semantics (pixel-centre shift, open window, zero padding, one-sided
+// derivatives at the kinks: .cuh:24-163, 227-229, 373-374) are those of make_axis (msda_common.cuh).
+//
+// Why.  In the encoder a tile of neighbouring queries samples a compact window of every level (reference
+// point = the query's own position, offsets of a few pixels).  Per (batch, head) the four levels of the
+// 800 x 1333 pyramid receive 21 / 85 / 339 / 1302 corner rows per pixel row: sending each of them to L2 as
+// its own 128-byte reduction is what bounds msda_bwd.cuh (2.56 GB of reductions into a 91 MB accumulator).
+// Here the per-corner work is O(1) scalar work and the fan-out over the D channels is done by two dense
+// tile products per 128-pixel window chunk:
+//
+//   item      = (tile of <= 128 queries of one level, batch, head); one thread owns one query row
+//   window_l  = bounding box of the item's 2x2 footprints in level l (found per item, data driven)
+//   chunk     = 128 consecutive pixels of a window (row-major inside the window)
+//   U  [q][pix] = G[q][:] . V[pix][:]     (128 x 128 x D,  tcgen05.mma, bf16/f16 x same -> fp32 in TMEM)
+//       -> <grad_out, corner> for every (query, window pixel); the owner thread picks its <= 16 corners
+//          of the level and forms grad_attn / grad_loc with its own fp32 bilinear weights
+//   GV [pix][:] = sum_q W[pix][q] G[q][:] (128 x D x 128)  with W[pix][q] = bilinear x attention weight,
+//       densified in shared memory by the owner threads (column q of W belongs to thread q: no atomics)
+//       -> the item's whole contribution to the chunk's grad_value rows, flushed with ONE
+//          red.global.add.v4.f32 row per touched pixel instead of one per (query, sample, corner).
+//
+// Numerics: G and V are exact in the operand type; W is rounded to the operand type (bf16: 2^-9 relative per
+// weight, below the final rounding of the 16-bit grad_value), all accumulation is fp32.  grad_attn and
+// grad_loc use fp32 weights on exact fp32 dot products.
+//
+// Items whose windows would need more than kMaxItemChunks chunks (tiles of the coarsest levels, whose samples
+// span most of the fine levels; arbitrary sampling locations) run the per-row code of msda_bwd.cuh instead
+// (backward_rows), inside the same kernel: the result never depends on locality, only the speed does.
+#pragma once
+#include "msda_bwd.cuh"
+
+namespace msda {
+namespace dense {
+
+constexpr int kThreads = 128;        // = query rows per item = TMEM lanes
+constexpr int kPix = 128;            // window pixels per chunk (MMA M of the scatter product, N of the dot product)
+constexpr int kMaxItemChunks = 32;   // beyond this the per-row path is cheaper
+constexpr int kMaxP = 4;             // samples per level a thread keeps in registers
+constexpr int kTmemCols = 256;       // U: 128 columns, GV: D columns (<= 64)
+
+// ---- tcgen05 / mbarrier wrappers (PTX ISA 8.6+, sm_100a) ---------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// K-major, SWIZZLE_NONE matrix descriptor: core matrix = 8 rows x 16 bytes (rows 16 bytes apart);
+// lbo = byte distance between the two 16-byte K chunks of one MMA, sbo = between 8-row groups.
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo)
+{
+    return (uint64_t)((saddr >> 4) & 0x3fff) | ((uint64_t)((lbo >> 4) & 0x3fff) << 16) |
+           ((uint64_t)((sbo >> 4) & 0x3fff) << 32) | ((uint64_t)1 << 46);
+}
+// instruction descriptor: fp32 accumulate, A and B K-major, fmt 0 = f16, 1 = bf16
+__host__ __device__ constexpr uint32_t umma_idesc(int M, int N, int fmt)
+{
+    return (1u << 4) | ((uint32_t)fmt << 7) | ((uint32_t)fmt << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, bool accumulate)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 :: "r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"((uint32_t)accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t mbar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(mbar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity)
+{
+    asm volatile("{\n\t.reg .pred P1;\n\tWAIT_%=:\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+                 "@P1 bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}"
+                 :: "r"(mbar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tmem_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void proxy_fence() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// 32 consecutive fp32 columns of this thread's TMEM lane (warp w reads lanes 32w .. 32w+31)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32])
+{
+    uint32_t r[32];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32"
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15,"
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+                   "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+                   "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                 : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+}
+
+// ---- operand type helpers --------------------------------------------------------------------------------------
+template <typename T> struct Op16;
+template <> struct Op16<__nv_bfloat16> {
+    static constexpr int fmt = 1;
+    static __device__ __forceinline__ float up(uint16_t h) { return __uint_as_float((uint32_t)h << 16); }
+    static __device__ __forceinline__ uint16_t down(float f) { return __bfloat16_as_ushort(__float2bfloat16_rn(f)); }
+};
+template <> struct Op16<__half> {
+    static constexpr int fmt = 0;
+    static __device__ __forceinline__ float up(uint16_t h) { return __half2float(__ushort_as_half(h)); }
+    static __device__ __forceinline__ uint16_t down(float f) { return __half_as_ushort(__float2half_rn(f)); }
+};
+
+// ---- shared-memory plan --------------------------------------------------------------------------------------
+// All MMA operands are K-major SWIZZLE_NONE; strides are padded by 16 bytes where the owner threads' 2-byte /
+// 4-byte accesses would otherwise fall into the same banks.
+template <int D> struct Plan {
+    static_assert(D % 16 == 0 && D >= 16 && D <= 64, "channels per head: whole K = 16 steps, <= 64 accumulator columns");
+    static constexpr int KCH = D / 8;                       // 16-byte chunks of a channel row
+    // G [128 q][D] and V [128 pix][D]: rows of D channels
+    static constexpr uint32_t G_LBO = 128, G_SBO = KCH * 128, G_BYTES = 16 * G_SBO;
+    // W [128 pix][128 q]
+    static constexpr uint32_t W_LBO = 144, W_SBO = 16 * 144 + 16, W_BYTES = 16 * W_SBO;
+    // Gt [D ch][128 q]
+    static constexpr uint32_t T_LBO = 144, T_SBO = 16 * 144, T_BYTES = (D / 8) * T_SBO;
+    static constexpr int STAGE_STRIDE = 68;                 // floats per thread-private staging row (64 + 4: conflict-free 16-byte stores)
+    static constexpr uint32_t STAGE_BYTES = kThreads * STAGE_STRIDE * 4;
+    static constexpr uint32_t OFF_G = 0, OFF_V = OFF_G + G_BYTES, OFF_W = OFF_V + G_BYTES, OFF_T = OFF_W + W_BYTES,
+                              OFF_STAGE = OFF_T + T_BYTES, TOTAL = OFF_STAGE + STAGE_BYTES;
+};
+
+// ---- tiles ---------------------------------------------------------------------------------------------------
+// The query grid of every level is cut into nty x ntx balanced tiles of at most th x tw <= 128 queries; th is
+// chosen per level to minimise the tile count (ties: the squarer tile, whose windows are smaller).  Tiles are
+// numbered coarsest level first: their windows in the fine levels are the largest, and the heaviest items
+// should be handed out first.
+struct TileTable {
+    int nty[kMaxLevels], ntx[kMaxLevels];
+    int first[kMaxLevels];      // schedule index of the level's first tile
+    int total;
+};
+
+__device__ __forceinline__ void build_tiles(TileTable& tt, int* scratch /* [kMaxLevels] */, const LevelTable& lt, int L)
+{
+    const int t = threadIdx.x;
+    if (t < kMaxLevels) scratch[t] = 0x7fffffff;
+    __syncthreads();
+    const int l = t >> 4, cand = t & 15;
+    int th = 1, tw = 1;
+    if (l < L) {
+        const int H = lt.H[l], W = lt.W[l];
+        th = min(3 + cand, H);
+        tw = min(kThreads / th, W);
+        const int count = ((H + th - 1) / th) * ((W + tw - 1) / tw);
+        const int score = min(count, (1 << 20) - 1) * 128 + min(abs(th - tw), 127);
+        atomicMin(&scratch[l], score * 16 + cand);
+    }
+    __syncthreads();
+    if (t == 0) {
+        int run = 0;
+        for (int k = L - 1; k >= 0; --k) {
+            const int H = lt.H[k], W = lt.W[k];
+            const int c = scratch[k] & 15;
+            const int h = min(3 + c, H), w = min(kThreads / h, W);
+            tt.nty[k] = (H + h - 1) / h;
+            tt.ntx[k] = (W + w - 1) / w;
+            tt.first[k] = run;
+            run += tt.nty[k] * tt.ntx[k];
+        }
+        tt.total = run;
+    }
+    __syncthreads();
+}
+
+struct DenseArgs {
+    int* claim;                    // zero-initialised work counter (in the caller's workspace)
+};
+
+template <typename VT, typename AT, int D, bool FUSED>
+__global__ void __launch_bounds__(kThreads, 2)
+msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restrict__ shapes,
+                           const int64_t* __restrict__ level_start, const AT* __restrict__ loc,
+                           const AT* __restrict__ attn, const VT* __restrict__ grad_out,
+                           float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
+                           AT* __restrict__ grad_attn, const KernelDims d, const FusedArgs fa, const DenseArgs da)
+{
+    static_assert(!FUSED, "the fused prologue of the dense kernel is a separate instantiation (not built yet)");
+    static_assert(D % 32 == 0, "accumulator rows are read 32 columns at a time");
+    using P = Plan<D>;
+    using O = Op16<VT>;
+    constexpr int GS = D / 4;                  // lanes per row of the per-row fallback (VEC = 4)
+    constexpr int NW = kThreads / 32;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ LevelTable lt;
+    __shared__ TileTable tt;
+    __shared__ int s_scratch[kMaxLevels];
+    __shared__ int s_box[NW][kMaxLevels][4];
+    __shared__ int s_win[kMaxLevels][5];       // ymin, xmin, wh, ww, chunks
+    __shared__ int s_item[2];
+    __shared__ uint32_t s_tmem;
+    __shared__ __align__(8) uint64_t s_mbar[2];   // dot products ready / scatter product ready
+    // tap records of the per-row fallback
+    __shared__ int2 fb_a[NW][record_count(GS)];
+    __shared__ int fb_dx[NW][record_count(GS)];
+    __shared__ float4 fb_b[NW][record_count(GS)];
+    __shared__ float4 fb_fold[NW][1];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    stage_levels(lt, shapes, level_start, d);
+    build_tiles(tt, s_scratch, lt, d.L);
+
+    uint8_t* sG = smem + P::OFF_G;
+    uint8_t* sV = smem + P::OFF_V;
+    uint8_t* sW = smem + P::OFF_W;
+    uint8_t* sT = smem + P::OFF_T;
+    float* stage = reinterpret_cast<float*>(smem + P::OFF_STAGE) + tid * P::STAGE_STRIDE;   // this thread's row
+
+    // one-time setup: zero W (the owner threads restore the zeros after every chunk), TMEM, barrier
+    for (uint32_t i = tid * 16; i < P::W_BYTES; i += kThreads * 16) *reinterpret_cast<uint4*>(sW + i) = make_uint4(0, 0, 0, 0);
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(&s_tmem)), "r"((uint32_t)kTmemCols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(&s_mbar[0])), "r"(1u));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(&s_mbar[1])), "r"(1u));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        s_item[0] = atomicAdd(da.claim, 1);
+    }
+    tmem_fence_before();
+    __syncthreads();
+    tmem_fence_after();
+    const uint32_t tmem_u = s_tmem, tmem_gv = s_tmem + kPix;
+    const uint32_t lane_sel = (uint32_t)(warp * 32) << 16;
+    const uint32_t mbar = smem_u32(&s_mbar[0]), mbar2 = smem_u32(&s_mbar[1]);
+    uint32_t phase = 0;
+    const int LP = d.L * d.P;
+    const int items = tt.total * d.N * d.M;
+    constexpr uint32_t idesc_u = umma_idesc(128, kPix, O::fmt);
+    constexpr uint32_t idesc_gv = umma_idesc(128, D, O::fmt);
+
+    int slot = 0;
+    for (int item = s_item[0]; item < items; item = s_item[slot]) {
+        // claim the next item now; it is read after the barrier that ends this one
+        if (tid == 0) s_item[slot ^ 1] = atomicAdd(da.claim, 1);
+        slot ^= 1;
+
+        // ---- item -> (tile, batch, head) -> this thread's query -------------------------------------------------
+        const int tile = item / (d.N * d.M);
+        const int bm = item - tile * (d.N * d.M);
+        const int b = bm / d.M, m = bm - b * d.M;
+        int lq = 0;
+        for (int k = 0; k < d.L; ++k)
+            if (tile >= tt.first[k] && tile < tt.first[k] + tt.nty[k] * tt.ntx[k]) lq = k;
+        const int tl = tile - tt.first[lq];
+        const int ty = tl / tt.ntx[lq], tx = tl - ty * tt.ntx[lq];
+        const int qH = lt.H[lq], qW = lt.W[lq];
+        const int y0 = (ty * qH) / tt.nty[lq], y1 = ((ty + 1) * qH) / tt.nty[lq];
+        const int x0 = (tx * qW) / tt.ntx[lq], x1 = ((tx + 1) * qW) / tt.ntx[lq];
+        const int cw = x1 - x0, chh = y1 - y0;
+        const int iy = tid / cw, ix = tid - iy * cw;
+        int q = (iy < chh) ? lt.qstart[lq] + (y0 + iy) * qW + x0 + ix : -1;
+        if (q >= d.Lq) q = -1;
+        const bool row_ok = q >= 0;
+        const size_t rowq = (size_t)b * d.Lq + (row_ok ? q : 0);
+        const size_t row = rowq * d.M + m;
+        const AT* lrow = loc + row * LP * 2;
+        const AT* arow = attn + row * LP;
+
+        // ---- windows: bounding box of the footprint origins, per level ----------------------------------------------
+        for (int l = 0; l < d.L; ++l) {
+            const int H = lt.H[l], W = lt.W[l];
+            int ymin = 1 << 30, ymax = -1, xmin = 1 << 30, xmax = -1;
+            if (row_ok) {
+                for (int p = 0; p < d.P; ++p) {
+                    const float2 xy = load_loc_cached<AT>(lrow + (l * d.P + p) * 2);
+                    const float x = fmaf(xy.x, (float)W, -0.5f), y = fmaf(xy.y, (float)H, -0.5f);
+                    if ((y > -1.f) && (x > -1.f) && (y < (float)H) && (x < (float)W)) {
+                        const int yb = min(max((int)floorf(y), 0), max(H - 2, 0));
+                        const int xb = min(max((int)floorf(x), 0), max(W - 2, 0));
+                        ymin = min(ymin, yb); ymax = max(ymax, yb);
+                        xmin = min(xmin, xb); xmax = max(xmax, xb);
+                    }
+                }
+            }
+            ymin = __reduce_min_sync(0xffffffffu, ymin); ymax = __reduce_max_sync(0xffffffffu, ymax);
+            xmin = __reduce_min_sync(0xffffffffu, xmin); xmax = __reduce_max_sync(0xffffffffu, xmax);
+            if (lane == 0) { s_box[warp][l][0] = ymin; s_box[warp][l][1] = ymax; s_box[warp][l][2] = xmin; s_box[warp][l][3] = xmax; }
+        }
+        __syncthreads();
+        if (tid < d.L) {
+            const int l = tid;
+            int ymin = 1 << 30, ymax = -1, xmin = 1 << 30, xmax = -1;
+            for (int w = 0; w < NW; ++w) {
+                ymin = min(ymin, s_box[w][l][0]); ymax = max(ymax, s_box[w][l][1]);
+                xmin = min(xmin, s_box[w][l][2]); xmax = max(xmax, s_box[w][l][3]);
+            }
+            int wh = 0, ww = 0;
+            if (ymax >= 0) {
+                wh = min(ymax - ymin + 2, lt.H[l]);
+                ww = min(xmax - xmin + 2, lt.W[l]);
+            } else { ymin = 0; xmin = 0; }
+            s_win[l][0] = ymin; s_win[l][1] = xmin; s_win[l][2] = wh; s_win[l][3] = ww;
+            s_win[l][4] = (wh * ww + kPix - 1) / kPix;
+        }
+        __syncthreads();
+        int total_chunks = 0;
+        for (int l = 0; l < d.L; ++l) total_chunks += s_win[l][4];
+
+        if (total_chunks > kMaxItemChunks) {
+            // ---- per-row path (msda_bwd.cuh) for this item ---------------------------------------------------------
+            auto qmap = [&](int i) {
+                const int jy = i / cw, jx = i - jy * cw;
+                const int qq = (jy < chh) ? lt.qstart[lq] + (y0 + jy) * qW + x0 + jx : -1;
+                return qq < d.Lq ? qq : -1;
+            };
+            if (lt.min_w > 1)
+                backward_rows<VT, AT, 4, GS, NW, true, FUSED>(lt, fb_a[warp], fb_dx[warp], fb_b[warp], fb_fold[warp], value, loc, attn,
+                                                              grad_out, grad_value_acc, grad_loc, grad_attn, d, fa, b, m, kThreads, qmap);
+            else
+                backward_rows<VT, AT, 4, GS, NW, false, FUSED>(lt, fb_a[warp], fb_dx[warp], fb_b[warp], fb_fold[warp], value, loc, attn,
+                                                               grad_out, grad_value_acc, grad_loc, grad_attn, d, fa, b, m, kThreads, qmap);
+            __syncthreads();
+            continue;
+        }
+
+        // ---- G: this row of grad_out -> operand A of the dot product, and transposed -> operand B of the scatter product
+        {
+            uint4 g4[P::KCH];
+#pragma unroll
+            for (int c = 0; c < P::KCH; ++c) g4[c] = make_uint4(0, 0, 0, 0);
+            if (row_ok) {
+                const uint4* gp = reinterpret_cast<const uint4*>(grad_out + row * D);
+#pragma unroll
+                for (int c = 0; c < P::KCH; ++c) g4[c] = __ldg(gp + c);
+            }
+            uint8_t* ga = sG + (tid & 7) * 16 + (tid >> 3) * P::G_SBO;
+#pragma unroll
+            for (int c = 0; c < P::KCH; ++c) *reinterpret_cast<uint4*>(ga + c * P::G_LBO) = g4[c];
+            uint8_t* gt = sT + (tid >> 3) * P::T_LBO + (tid & 7) * 2;
+#pragma unroll
+            for (int c = 0; c < P::KCH; ++c) {
+                const uint32_t w4[4] = {g4[c].x, g4[c].y, g4[c].z, g4[c].w};
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const int ch = c * 8 + e;
+                    const uint16_t h = (uint16_t)(w4[e >> 1] >> ((e & 1) * 16));
+                    *reinterpret_cast<uint16_t*>(gt + (ch & 7) * 16 + (ch >> 3) * P::T_SBO) = h;
+                }
+            }
+        }
+
+        const VT* vbase = value + ((size_t)b * d.S * d.M + m) * D;
+        float* gvbase = grad_value_acc + ((size_t)b * d.S * d.M + m) * D;
+        const size_t pix_stride = (size_t)d.M * D;
+
+        for (int l = 0; l < d.L; ++l) {
+            const int nch = s_win[l][4];
+            if (nch == 0) {
+                // nothing of this item samples inside level l: zero gradients for its samples
+                if (row_ok) {
+                    for (int p = 0; p < d.P; ++p) {
+                        const int s = l * d.P + p;
+                        store_loc<AT>(grad_loc + (row * LP + s) * 2, 0.f, 0.f);
+                        grad_attn[row * LP + s] = from_f32<AT>(0.f);
+                    }
+                }
+                continue;
+            }
+            const int H = lt.H[l], W = lt.W[l];
+            const int ymin = s_win[l][0], xmin = s_win[l][1], wh = s_win[l][2], ww = s_win[l][3];
+            const int npix = wh * ww;
+            const int rstep = H > 1 ? ww : 0, cstep = W > 1 ? 1 : 0;
+
+            // ---- this row's 4 * P corner targets of the level, everything the chunk loop needs precomputed ----
+            // key  = window-linear pixel index >> 6 (which 64-column half of which chunk), kNone: no target
+            // wa   = byte address of the target's W element inside a chunk (column `tid`)
+            // sa   = byte address of its dot product inside this thread's staging row
+            // tw   = bilinear x attention weight (scatter product)
+            // cga / cgx / cgy = coefficients of <grad_out, corner> in grad_attn / grad_loc.x / grad_loc.y
+            //        (.cuh:373-374: pixel-space derivative times attention weight times W (x) / H (y))
+            constexpr int NT = 4 * kMaxP;
+            constexpr int kNone = -(1 << 20);
+            int key[NT];
+            uint32_t wa[NT], sa[NT];
+            float tw[NT], cga[NT], cgx[NT], cgy[NT];
+            float acc_a[kMaxP], acc_x[kMaxP], acc_y[kMaxP];
+            const uint32_t w_col = smem_u32(sW) + (tid >> 3) * P::W_LBO + (tid & 7) * 2;
+            const uint32_t st_row = smem_u32(stage);
+#pragma unroll
+            for (int p = 0; p < kMaxP; ++p) {
+                acc_a[p] = acc_x[p] = acc_y[p] = 0.f;
+                bool ok = false;
+                int r00 = 0;
+                float a = 0.f;
+                Axis ay, ax;
+                ay.b = ax.b = 0; ay.w0 = ay.w1 = ay.d0 = ay.d1 = ax.w0 = ax.w1 = ax.d0 = ax.d1 = 0.f;
+                if (row_ok && p < d.P) {
+                    const int s = l * d.P + p;
+                    const float2 xy = load_loc_cached<AT>(lrow + s * 2);
+                    a = load_attn<AT>(arow + s);
+                    const float x = fmaf(xy.x, (float)W, -0.5f), y = fmaf(xy.y, (float)H, -0.5f);
+                    ok = (y > -1.f) && (x > -1.f) && (y < (float)H) && (x < (float)W);
+                    ay = make_axis(y, H, ok);
+                    ax = make_axis(x, W, ok);
+                    r00 = (ay.b - ymin) * ww + (ax.b - xmin);
+                }
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int t = p * 4 + c;
+                    const float wy = (c >> 1) ? ay.w1 : ay.w0, wx = (c & 1) ? ax.w1 : ax.w0;
+                    const float dy = (c >> 1) ? ay.d1 : ay.d0, dx = (c & 1) ? ax.d1 : ax.d0;
+                    // a footprint row / column that does not exist (H == 1 / W == 1) carries no weight and no derivative
+                    const bool live = ok && !((c >> 1) && rstep == 0) && !((c & 1) && cstep == 0);
+                    const int r = r00 + (c >> 1) * rstep + (c & 1) * cstep;
+                    key[t] = live ? (r >> 6) : kNone;
+                    const int idx = r & (kPix - 1);
+                    wa[t] = w_col + (idx & 7) * 16 + (idx >> 3) * P::W_SBO;
+                    sa[t] = st_row + (r & 63) * 4;
+                    tw[t] = wy * wx * a;
+                    cga[t] = wy * wx;
+                    cgx[t] = wy * dx * a * (float)W;
+                    cgy[t] = dy * wx * a * (float)H;
+                }
+            }
+
+            // window coordinates of this thread's pixel of the current chunk, advanced incrementally
+            int pwy = tid / ww, pwx = tid - pwy * ww;
+            const int step_y = kPix / ww, step_x = kPix - step_y * ww;
+
+            for (int k = 0; k < nch; ++k) {
+                const int r0 = k * kPix;
+                // (a) this thread's window pixel: its value row -> registers
+                const bool pix_ok = r0 + tid < npix;
+                const size_t pix = (size_t)lt.start[l] + (size_t)(ymin + pwy) * W + (xmin + pwx);
+                pwy += step_y; pwx += step_x;
+                if (pwx >= ww) { pwx -= ww; ++pwy; }
+                uint4 v4[P::KCH];
+#pragma unroll
+                for (int c = 0; c < P::KCH; ++c) v4[c] = make_uint4(0, 0, 0, 0);
+                if (pix_ok) {
+                    const uint4* vp = reinterpret_cast<const uint4*>(vbase + pix * pix_stride);
+#pragma unroll
+                    for (int c = 0; c < P::KCH; ++c) v4[c] = __ldg(vp + c);
+                }
+                // (b) densify: column `tid` of W gets this row's corner weights that fall into the chunk.  The four
+                // corners of one sample are distinct pixels: four independent read-modify-writes; corners of
+                // different samples may coincide, so the samples go one after the other.
+#pragma unroll
+                for (int p = 0; p < kMaxP; ++p) {
+                    uint16_t h[4];
+                    bool hit[4];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        const int t = p * 4 + c;
+                        hit[c] = (key[t] >> 1) == k && tw[t] != 0.f;
+                        h[c] = 0;
+                        if (hit[c]) asm volatile("ld.shared.u16 %0, [%1];" : "=h"(h[c]) : "r"(wa[t]) : "memory");
+                    }
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        const int t = p * 4 + c;
+                        if (hit[c]) {
+                            const uint16_t nh = O::down(O::up(h[c]) + tw[t]);
+                            asm volatile("st.shared.u16 [%0], %1;" :: "r"(wa[t]), "h"(nh) : "memory");
+                        }
+                    }
+                }
+                // (c) value rows -> operand B of the dot product
+                {
+                    uint8_t* va = sV + (tid & 7) * 16 + (tid >> 3) * P::G_SBO;
+#pragma unroll
+                    for (int c = 0; c < P::KCH; ++c) *reinterpret_cast<uint4*>(va + c * P::G_LBO) = v4[c];
+                }
+                // (d) operands visible to the tensor core; TMEM reads of the previous chunk are complete
+                proxy_fence();
+                tmem_fence_before();
+                __syncthreads();
+                // (e) one thread issues both products; the dot products are committed first so that the picks
+                // below overlap the scatter product
+                if (tid == 0) {
+                    tmem_fence_after();
+                    const uint64_t dg = umma_desc(smem_u32(sG), P::G_LBO, P::G_SBO);
+                    const uint64_t dv = umma_desc(smem_u32(sV), P::G_LBO, P::G_SBO);
+#pragma unroll
+                    for (int j = 0; j < D / 16; ++j)
+                        umma(tmem_u, dg + (uint64_t)(j * 2 * P::G_LBO / 16), dv + (uint64_t)(j * 2 * P::G_LBO / 16), idesc_u, j > 0);
+                    umma_commit(mbar);
+                    const uint64_t dw = umma_desc(smem_u32(sW), P::W_LBO, P::W_SBO);
+                    const uint64_t dt = umma_desc(smem_u32(sT), P::T_LBO, P::T_SBO);
+#pragma unroll
+                    for (int j = 0; j < kThreads / 16; ++j)
+                        umma(tmem_gv, dw + (uint64_t)(j * 2 * P::W_LBO / 16), dt + (uint64_t)(j * 2 * P::T_LBO / 16), idesc_gv, j > 0);
+                    umma_commit(mbar2);
+                }
+                // (f) dot products ready
+                mbar_wait(mbar, phase);
+                tmem_fence_after();
+                // (g) this row's 128 columns -> private staging row (64 at a time) -> pick the corners of this chunk
+#pragma unroll 1
+                for (int half = 0; half < 2; ++half) {
+                    if (half * 64 >= npix - r0) break;       // columns beyond the window
+                    {
+                        float u[32];
+                        tmem_ld32(tmem_u + lane_sel + half * 64, u);
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(stage + j) = make_float4(u[j], u[j + 1], u[j + 2], u[j + 3]);
+                        tmem_ld32(tmem_u + lane_sel + half * 64 + 32, u);
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(stage + 32 + j) = make_float4(u[j], u[j + 1], u[j + 2], u[j + 3]);
+                    }
+                    const int want = 2 * k + half;
+#pragma unroll
+                    for (int t = 0; t < NT; ++t) {
+                        float u = 0.f;
+                        if (key[t] == want) asm volatile("ld.shared.f32 %0, [%1];" : "=f"(u) : "r"(sa[t]) : "memory");
+                        acc_a[t >> 2] = fmaf(cga[t], u, acc_a[t >> 2]);
+                        acc_x[t >> 2] = fmaf(cgx[t], u, acc_x[t >> 2]);
+                        acc_y[t >> 2] = fmaf(cgy[t], u, acc_y[t >> 2]);
+                    }
+                }
+                // (h) the item's contribution to the chunk's grad_value rows: TMEM lane = window pixel r0 + tid
+                mbar_wait(mbar2, phase);
+                phase ^= 1;
+                tmem_fence_after();
+                {
+                    float gv[D];
+#pragma unroll
+                    for (int c0 = 0; c0 < D; c0 += 32) tmem_ld32(tmem_gv + lane_sel + c0, *reinterpret_cast<float(*)[32]>(&gv[c0]));
+                    uint32_t any = 0;
+#pragma unroll
+                    for (int j = 0; j < D; ++j) any |= __float_as_uint(gv[j]);
+                    const bool nz = (any << 1) != 0 && pix_ok;          // -0.0 counts as zero
+                    __syncwarp();
+#pragma unroll
+                    for (int j = 0; j < D; j += 4) *reinterpret_cast<float4*>(stage + j) = make_float4(gv[j], gv[j + 1], gv[j + 2], gv[j + 3]);
+                    const unsigned live = __ballot_sync(0xffffffffu, nz);
+                    __syncwarp();
+                    // a warp instruction carries 32 / (D / 4) whole rows (16 bytes per lane)
+                    constexpr int LPR = D / 4, RPI = 32 / LPR;
+                    const float* wstage = reinterpret_cast<const float*>(smem + P::OFF_STAGE) + (warp * 32 + lane / LPR) * P::STAGE_STRIDE + (lane % LPR) * 4;
+                    float* my_dst = gvbase + (lane % LPR) * 4;
+                    const unsigned my_pix = (unsigned)pix;
+#pragma unroll
+                    for (int i = 0; i < 32; i += RPI) {
+                        const int rr = i + lane / LPR;
+                        const unsigned spix = __shfl_sync(0xffffffffu, my_pix, rr);
+                        if ((live >> rr) & 1u) {
+                            const float4 x = *reinterpret_cast<const float4*>(wstage + i * P::STAGE_STRIDE);
+                            red_add_f32x4(my_dst + (size_t)spix * pix_stride, x.x, x.y, x.z, x.w);
+                        }
+                    }
+                    __syncwarp();
+                }
+                // (i) restore the zeros of W
+#pragma unroll
+                for (int t = 0; t < NT; ++t)
+                    if ((key[t] >> 1) == k) asm volatile("st.shared.u16 [%0], %1;" :: "r"(wa[t]), "h"((uint16_t)0) : "memory");
+            }
+
+            // ---- the level's samples are complete: gradients of the sampling locations and attention weights ----
+            if (row_ok) {
+#pragma unroll
+                for (int p = 0; p < kMaxP; ++p) {
+                    if (p < d.P) {
+                        const int s = l * d.P + p;
+                        store_loc<AT>(grad_loc + (row * LP + s) * 2, acc_x[p], acc_y[p]);
+                        grad_attn[row * LP + s] = from_f32<AT>(acc_a[p]);
+                    }
+                }
+            }
+        }
+        // G / Gt / the window table are rewritten by the next item
+        tmem_fence_before();
+        __syncthreads();
+    }
+
+    tmem_fence_before();
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(s_tmem), "r"((uint32_t)kTmemCols));
+}
+
+}  // namespace dense
+}  // namespace msda

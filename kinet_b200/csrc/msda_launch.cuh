@@ -6,6 +6,7 @@
 #include <cstring>
 
 #include "msda_bwd.cuh"
+#include "msda_dense.cuh"
 #include "msda_fwd.cuh"
 
 namespace msda {
@@ -245,6 +246,39 @@ int launch_backward_generic(const void* value, const int64_t* shapes, const int6
     return (int)cudaGetLastError();
 }
 
+// Encoder-form backward on the tensor cores (msda_dense.cuh).  The work counter lives behind the fp32
+// accumulator in the caller's workspace and is zeroed by the same memset.
+inline size_t dense_counter_offset(size_t nval) { return (nval * sizeof(float) + 255) & ~(size_t)255; }
+constexpr size_t kDenseCounterBytes = 256;
+
+template <typename VT, typename AT, int D>
+int launch_backward_dense(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
+                          const void* attn, const void* go, float* gv_acc, void* gl, void* ga, int* claim,
+                          const msda_dims* d, cudaStream_t st)
+{
+    KernelDims k = make_dims(d, 16, kBackwardTileQ);
+    auto kern = dense::msda_backward_dense_kernel<VT, AT, D, false>;
+    constexpr int smem = (int)dense::Plan<D>::TOTAL;
+    static thread_local int configured_dev = -1;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (configured_dev != dev) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return (int)e;
+        configured_dev = dev;
+    }
+    const int sms = device_info().sms > 0 ? device_info().sms : 148;
+    dense::DenseArgs da;
+    da.claim = claim;
+    {
+        TraceScope trace(st);
+        kern<<<2 * sms, dense::kThreads, smem, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
+                                                     (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, FusedArgs{}, da);
+    }
+    ++g_last_launches;
+    return (int)cudaGetLastError();
+}
+
 // VT = float: gradients accumulate straight into grad_value (zero-filled first).
 // 16-bit VT: accumulate in the fp32 workspace, then round once.
 template <typename VT, typename AT>
@@ -261,17 +295,33 @@ int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, 
         if (!aligned16(ws)) return MSDA_E_ALIGN;
         acc = (float*)ws;
     }
-    cudaError_t e = cudaMemsetAsync(acc, 0, nval * sizeof(float), st);
+    // dense-window tensor-core path: encoder form, 16-bit values, D = 32 / 64, and a workspace with room for
+    // the work counter (msda_b200_backward_workspace_bytes)
+    bool dense_ok = false;
+    if constexpr (sizeof(VT) == 2) {
+        dense_ok = !fa && d->Lq == d->S && d->Lq > 0 && d->P <= dense::kMaxP && (d->D == 32 || d->D == 64) &&
+                   ws_bytes >= dense_counter_offset(nval) + kDenseCounterBytes && aligned16(value) && aligned16(go) &&
+                   env_int("MSDA_B200_DENSE", 1) && !env_int("MSDA_B200_FORCE_GENERIC", 0) && !env_int("MSDA_B200_TILE_1D", 0);
+    }
+    cudaError_t e = cudaMemsetAsync(acc, 0, dense_ok ? dense_counter_offset(nval) + kDenseCounterBytes : nval * sizeof(float), st);
     if (e != cudaSuccess) return (int)e;
     int rc = 0;
     if (d->Lq > 0) {
         const bool al = aligned16(value) && aligned16(go) && aligned16(acc) &&
                         !env_int("MSDA_B200_FORCE_GENERIC", 0);
         bool done = false;
+        if constexpr (sizeof(VT) == 2) {
+            if (dense_ok) {
+                int* claim = reinterpret_cast<int*>(reinterpret_cast<char*>(ws) + dense_counter_offset(nval));
+                if (d->D == 32) rc = launch_backward_dense<VT, AT, 32>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, d, st);
+                else rc = launch_backward_dense<VT, AT, 64>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, d, st);
+                done = true;
+            }
+        }
         // 4 channels per lane for every value type (16-bit rows are read with 8-byte loads): a lane's
         // reduction is then 16 contiguous bytes of the fp32 accumulator row and one instruction covers
         // whole 128-byte rows, i.e. the fewest SM->L2 request packets per byte
-        if (al) switch (d->D) {
+        if (al && !done) switch (d->D) {
             case 16: rc = launch_backward_vec<VT, AT, 4, 4>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st, fa); done = true; break;
             case 32: rc = launch_backward_vec<VT, AT, 4, 8>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st, fa); done = true; break;
             case 36: rc = launch_backward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st, fa); done = true; break;
