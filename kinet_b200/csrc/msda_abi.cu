@@ -75,9 +75,9 @@ int msda_b200_forward(const void* value, int value_dtype, const int64_t* spatial
 size_t msda_b200_backward_workspace_bytes(int value_dtype, const msda_dims* d)
 {
     if (!d) return 0;
-    // fp32 accumulator + the dense-window kernel's work counter
+    // fp32 accumulator + the dense-window kernel's work counter and deferred-item flags
     if (value_dtype == MSDA_BF16 || value_dtype == MSDA_F16)
-        return dense_counter_offset((size_t)d->N * d->S * d->M * d->D) + kDenseCounterBytes;
+        return dense_counter_offset((size_t)d->N * d->S * d->M * d->D) + dense_extra_bytes(d);
     return 0;
 }
 

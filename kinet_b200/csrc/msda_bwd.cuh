@@ -55,8 +55,8 @@ __device__ __forceinline__ void reduce_scatter(float (&U)[N][4], int gl, int grp
 // (through the location arithmetic and the softmax); see SampleSrc<AT, true> in msda_common.cuh.
 //
 // backward_rows: the `count` query rows qmap(0) .. qmap(count-1) (-1 = no row) of one (batch, head) pair, NWARPS
-// warps.  Called once per work item by msda_backward_kernel, and by the dense-window kernel (msda_dense.cuh) for
-// the items whose sampling footprint does not fit its windows.
+// warps.  Called once per work item by msda_backward_kernel (walk items; in split mode also the tiles the
+// dense-window kernel of msda_dense.cuh handed back).
 template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE, bool FUSED, typename QMap>
 __device__ __forceinline__ void backward_rows(const LevelTable& lt, int2* stage_a, int* stage_dx,
                                               float4* stage_b, float4* fold,
@@ -229,26 +229,57 @@ __device__ __forceinline__ void backward_rows(const LevelTable& lt, int2* stage_
 
 // One work item per CTA (grid == items; the loop only guards against a capped grid): item = (chunk of tile_q
 // positions of the query walk, batch, head), see walk_query.
+//
+// Split mode (deferred != nullptr; the dense-window kernel of msda_dense.cuh ran before on the same stream): the
+// queries of the finest level belong to the dense kernel, which flags the (tile, batch, head) items it did not do
+// (windows too large for its chunks).  This kernel then processes (1) the walk items without the finest level's
+// queries and (2) the flagged tiles, shared by tile_ctas extra CTAs at the end of the grid.
 template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE, bool FUSED>
-__device__ __forceinline__ void backward_items(const LevelTable& lt, int2* stage_a, int* stage_dx,
+__device__ __forceinline__ void backward_items(const LevelTable& lt, const FineTiles& ft, int2* stage_a, int* stage_dx,
                                                float4* stage_b, float4* fold,
                                                const VT* __restrict__ value,
                                                const AT* __restrict__ loc, const AT* __restrict__ attn,
                                                const VT* __restrict__ grad_out,
                                                float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
-                                               AT* __restrict__ grad_attn, const KernelDims& d, const FusedArgs& fa)
+                                               AT* __restrict__ grad_attn, const KernelDims& d, const FusedArgs& fa,
+                                               const uint8_t* __restrict__ deferred, int tile_ctas)
 {
     const int chunks = (d.Lq + d.tile_q - 1) / d.tile_q;
-    const int items = chunks * d.N * d.M;
+    const int walk_items = chunks * d.N * d.M;
+    const bool split = deferred != nullptr && ft.level >= 0;
+    if (deferred != nullptr && (int)blockIdx.x >= walk_items) {
+        // the last tile_ctas CTAs of the grid share the tile items (normally none is flagged: a few byte loads each)
+        if (!split) return;
+        const int tile_items = ft.total * d.N * d.M;
+        for (int it = blockIdx.x - walk_items; it < tile_items; it += tile_ctas) {
+            if (deferred[it] == 0) continue;
+            const int tile = it / (d.N * d.M);
+            const int bm = it - tile * (d.N * d.M);
+            const int b = bm / d.M, m = bm - b * d.M;
+            const TileRect r = fine_tile_rect(ft, lt, tile);
+            backward_rows<VT, AT, VEC, GS, NWARPS, WIDE, FUSED>(
+                lt, stage_a, stage_dx, stage_b, fold, value, loc, attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa,
+                b, m, kTileQueries, [&](int i) { return fine_tile_query(ft, lt, r, i, d.Lq); });
+        }
+        return;
+    }
+    const int items = walk_items;
     for (int item = blockIdx.x; item < items; item += gridDim.x) {
-        const int chunk = item / (d.N * d.M);
-        const int bm = item - chunk * (d.N * d.M);
-        const int b = bm / d.M, m = bm - b * d.M;
-        const int pos0 = chunk * d.tile_q;
-        const int count = min(d.tile_q, d.Lq - pos0);
-        backward_rows<VT, AT, VEC, GS, NWARPS, WIDE, FUSED>(
-            lt, stage_a, stage_dx, stage_b, fold, value, loc, attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa,
-            b, m, count, [&](int i) { return walk_query(lt, d, pos0 + i); });
+        {
+            const int chunk = item / (d.N * d.M);
+            const int bm = item - chunk * (d.N * d.M);
+            const int b = bm / d.M, m = bm - b * d.M;
+            const int pos0 = chunk * d.tile_q;
+            const int count = min(d.tile_q, d.Lq - pos0);
+            // walk positions and queries of a level share one index range
+            if (split && pos0 >= ft.q_begin && pos0 + count <= ft.q_end) continue;
+            backward_rows<VT, AT, VEC, GS, NWARPS, WIDE, FUSED>(
+                lt, stage_a, stage_dx, stage_b, fold, value, loc, attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa,
+                b, m, count, [&](int i) {
+                    const int q = walk_query(lt, d, pos0 + i);
+                    return (split && q >= ft.q_begin && q < ft.q_end) ? -1 : q;
+                });
+        }
     }
 }
 
@@ -258,10 +289,14 @@ msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ s
                      const int64_t* __restrict__ level_start, const AT* __restrict__ loc,
                      const AT* __restrict__ attn, const VT* __restrict__ grad_out,
                      float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
-                     AT* __restrict__ grad_attn, const KernelDims d, const FusedArgs fa)
+                     AT* __restrict__ grad_attn, const KernelDims d, const FusedArgs fa,
+                     const uint8_t* __restrict__ deferred, int tiles_bound, int tile_ctas)
 {
     __shared__ LevelTable lt;
+    __shared__ FineTiles ft;
+    __shared__ int ft_scratch;
     stage_levels(lt, shapes, level_start, d);
+    if (deferred != nullptr) build_fine_tiles(ft, &ft_scratch, lt, d.L, tiles_bound);
     __shared__ int2 stage_a[NWARPS][record_count(GS)];
     __shared__ int stage_dx[NWARPS][record_count(GS)];
     __shared__ float4 stage_b[NWARPS][record_count(GS)];
@@ -269,11 +304,11 @@ msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ s
     __shared__ float4 fold[NWARPS][FOLD];
     const int warp = threadIdx.x >> 5;
     if (lt.min_w > 1)
-        backward_items<VT, AT, VEC, GS, NWARPS, true, FUSED>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], fold[warp], value, loc,
-                                                             attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa);
+        backward_items<VT, AT, VEC, GS, NWARPS, true, FUSED>(lt, ft, stage_a[warp], stage_dx[warp], stage_b[warp], fold[warp], value, loc,
+                                                             attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa, deferred, tile_ctas);
     else
-        backward_items<VT, AT, VEC, GS, NWARPS, false, FUSED>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], fold[warp], value, loc,
-                                                              attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa);
+        backward_items<VT, AT, VEC, GS, NWARPS, false, FUSED>(lt, ft, stage_a[warp], stage_dx[warp], stage_b[warp], fold[warp], value, loc,
+                                                              attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa, deferred, tile_ctas);
 }
 
 // fp32 workspace -> 16-bit grad_value (one rounding of the full sum).

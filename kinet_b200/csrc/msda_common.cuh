@@ -87,6 +87,71 @@ __device__ __forceinline__ int walk_query(const LevelTable& t, const KernelDims&
     return q < d.Lq ? q : -1;   // only if the shapes do not add up to S (caller error): drop, never write out of range
 }
 
+// ---- tiles of the finest level (encoder form; shared by the dense-window kernel and the per-row kernel) -------
+// The dense-window backward (msda_dense.cuh) takes the queries of the FINEST level (the one with the most pixels:
+// its tiles look into windows of their own size in their own level and smaller ones in every coarser level) and
+// cuts that level's query grid into nty x ntx balanced tiles of at most kTileQueries queries; the tile height is
+// chosen to minimise tiles x window area (halo of kTileHalo pixels around the tile: offsets of a few pixels).
+// The per-row kernel processes every other query, and the tiles the dense kernel hands back (deferred flags).
+constexpr int kTileQueries = 128;
+constexpr int kTileHalo = 12;
+struct FineTiles {
+    int level;          // -1: no split (tile table does not fit the flag array, or not the encoder form)
+    int nty, ntx, total;
+    int q_begin, q_end; // the level's queries
+};
+
+// All threads call (blockDim.x >= 16); ends with __syncthreads().  scratch: one int of shared memory.
+__device__ __forceinline__ void build_fine_tiles(FineTiles& ft, int* scratch, const LevelTable& t, int L, int tiles_bound)
+{
+    int f = 0;
+    for (int l = 1; l < L; ++l)
+        if (t.H[l] * t.W[l] > t.H[f] * t.W[f]) f = l;
+    const int H = t.H[f], W = t.W[f];
+    if (threadIdx.x == 0) *scratch = 0x7fffffff;
+    __syncthreads();
+    if (threadIdx.x < 16) {
+        const int cand = threadIdx.x;
+        const int th = min(3 + cand, H), tw = min(kTileQueries / th, W);
+        const long long count = (long long)((H + th - 1) / th) * ((W + tw - 1) / tw);
+        const long long cost = count * (th + kTileHalo) * (tw + kTileHalo);
+        const int score = (int)min(cost >> 4, (long long)((1 << 27) - 1));
+        atomicMin(scratch, score * 16 + cand);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int c = *scratch & 15;
+        const int th = min(3 + c, H), tw = min(kTileQueries / th, W);
+        ft.nty = (H + th - 1) / th;
+        ft.ntx = (W + tw - 1) / tw;
+        ft.total = ft.nty * ft.ntx;
+        ft.level = ft.total <= tiles_bound ? f : -1;
+        ft.q_begin = t.qstart[f];
+        ft.q_end = t.qstart[f + 1];
+    }
+    __syncthreads();
+}
+
+// Query of position i (row-major inside the tile) of tile `tile`; -1 beyond the tile.
+struct TileRect { int y0, x0, h, w; };
+__device__ __forceinline__ TileRect fine_tile_rect(const FineTiles& ft, const LevelTable& t, int tile)
+{
+    const int ty = tile / ft.ntx, tx = tile - ty * ft.ntx;
+    const int H = t.H[ft.level], W = t.W[ft.level];
+    TileRect r;
+    r.y0 = (ty * H) / ft.nty;
+    r.x0 = (tx * W) / ft.ntx;
+    r.h = ((ty + 1) * H) / ft.nty - r.y0;
+    r.w = ((tx + 1) * W) / ft.ntx - r.x0;
+    return r;
+}
+__device__ __forceinline__ int fine_tile_query(const FineTiles& ft, const LevelTable& t, const TileRect& r, int i, int Lq)
+{
+    const int iy = i / r.w, ix = i - iy * r.w;
+    const int q = (iy < r.h) ? ft.q_begin + (r.y0 + iy) * t.W[ft.level] + r.x0 + ix : -1;
+    return q < Lq ? q : -1;
+}
+
 // ---- element conversion -------------------------------------------------------------
 template <typename T> __device__ __forceinline__ float to_f32(T v);
 template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }

@@ -28,9 +28,12 @@
 // weight, below the final rounding of the 16-bit grad_value), all accumulation is fp32.  grad_attn and
 // grad_loc use fp32 weights on exact fp32 dot products.
 //
-// Items whose windows would need more than kMaxItemChunks chunks (tiles of the coarsest levels, whose samples
-// span most of the fine levels; arbitrary sampling locations) run the per-row code of msda_bwd.cuh instead
-// (backward_rows), inside the same kernel: the result never depends on locality, only the speed does.
+// Division of labour with msda_bwd.cuh (launched right after this kernel, same stream, split mode): this kernel
+// takes the tiles of the FINEST level's queries -- their windows are compact in every level -- and flags the
+// (tile, batch, head) items whose windows would still need more than kMaxItemChunks chunks (arbitrary sampling
+// locations); the per-row kernel processes the flagged tiles and all queries of the coarser levels (a tile of a
+// coarse level looks into windows 2x, 4x, ... its own size in the finer levels with ~1 corner per pixel: nothing to
+// aggregate).  The result never depends on locality, only the speed does.
 #pragma once
 #include "msda_bwd.cuh"
 
@@ -116,62 +119,97 @@ template <int D> struct Plan {
     static_assert(D % 16 == 0 && D >= 16 && D <= 64, "channels per head: whole K = 16 steps, <= 64 accumulator columns");
     static constexpr int KCH = D / 8;                       // 16-byte chunks of a channel row
     // G [128 q][D] and V [128 pix][D]: rows of D channels
-    static constexpr uint32_t G_LBO = 128, G_SBO = KCH * 128, G_BYTES = 16 * G_SBO;
+    // (chunk stride 160 / 144 bytes: the D / 8 lanes that store one row's chunks hit different banks)
+    static constexpr uint32_t G_LBO = KCH == 4 ? 160 : 144, G_SBO = KCH * G_LBO, G_BYTES = 16 * G_SBO;
     // W [128 pix][128 q]
     static constexpr uint32_t W_LBO = 144, W_SBO = 16 * 144 + 16, W_BYTES = 16 * W_SBO;
     // Gt [D ch][128 q]
-    static constexpr uint32_t T_LBO = 144, T_SBO = 16 * 144, T_BYTES = (D / 8) * T_SBO;
+    static constexpr uint32_t T_LBO = 144, T_SBO = 16 * 144 + 16, T_BYTES = (D / 8) * T_SBO;
     static constexpr int STAGE_STRIDE = 68;                 // floats per thread-private staging row (64 + 4: conflict-free 16-byte stores)
     static constexpr uint32_t STAGE_BYTES = kThreads * STAGE_STRIDE * 4;
     static constexpr uint32_t OFF_G = 0, OFF_V = OFF_G + G_BYTES, OFF_W = OFF_V + G_BYTES, OFF_T = OFF_W + W_BYTES,
                               OFF_STAGE = OFF_T + T_BYTES, TOTAL = OFF_STAGE + STAGE_BYTES;
 };
 
-// ---- tiles ---------------------------------------------------------------------------------------------------
-// The query grid of every level is cut into nty x ntx balanced tiles of at most th x tw <= 128 queries; th is
-// chosen per level to minimise the tile count (ties: the squarer tile, whose windows are smaller).  Tiles are
-// numbered coarsest level first: their windows in the fine levels are the largest, and the heaviest items
-// should be handed out first.
-struct TileTable {
-    int nty[kMaxLevels], ntx[kMaxLevels];
-    int first[kMaxLevels];      // schedule index of the level's first tile
-    int total;
-};
-
-__device__ __forceinline__ void build_tiles(TileTable& tt, int* scratch /* [kMaxLevels] */, const LevelTable& lt, int L)
-{
-    const int t = threadIdx.x;
-    if (t < kMaxLevels) scratch[t] = 0x7fffffff;
-    __syncthreads();
-    const int l = t >> 4, cand = t & 15;
-    int th = 1, tw = 1;
-    if (l < L) {
-        const int H = lt.H[l], W = lt.W[l];
-        th = min(3 + cand, H);
-        tw = min(kThreads / th, W);
-        const int count = ((H + th - 1) / th) * ((W + tw - 1) / tw);
-        const int score = min(count, (1 << 20) - 1) * 128 + min(abs(th - tw), 127);
-        atomicMin(&scratch[l], score * 16 + cand);
-    }
-    __syncthreads();
-    if (t == 0) {
-        int run = 0;
-        for (int k = L - 1; k >= 0; --k) {
-            const int H = lt.H[k], W = lt.W[k];
-            const int c = scratch[k] & 15;
-            const int h = min(3 + c, H), w = min(kThreads / h, W);
-            tt.nty[k] = (H + h - 1) / h;
-            tt.ntx[k] = (W + w - 1) / w;
-            tt.first[k] = run;
-            run += tt.nty[k] * tt.ntx[k];
+// The P samples of level l of one (query, head) row: sampling locations + attention weights in, their gradients out.
+// A row's samples of one level are contiguous (P * 2 and P elements): with P == 4 they move as 16-byte vectors --
+// neighbouring lanes own rows that are M * L * P elements apart, so every access of a lane is its own L1 wavefront
+// and the instruction count is what matters.
+template <typename AT> struct LevelIO;
+template <> struct LevelIO<float> {
+    static __device__ __forceinline__ void load(const float* lrow, const float* arow, int l, int P, bool have,
+                                                float2 (&xy)[kMaxP], float (&a)[kMaxP])
+    {
+#pragma unroll
+        for (int p = 0; p < kMaxP; ++p) { xy[p] = make_float2(-8.f, -8.f); a[p] = 0.f; }
+        if (!have) return;
+        if (P == 4) {
+            const float4 u = __ldg(reinterpret_cast<const float4*>(lrow + l * 8));
+            const float4 v = __ldg(reinterpret_cast<const float4*>(lrow + l * 8 + 4));
+            const float4 w = __ldg(reinterpret_cast<const float4*>(arow + l * 4));
+            xy[0] = make_float2(u.x, u.y); xy[1] = make_float2(u.z, u.w);
+            xy[2] = make_float2(v.x, v.y); xy[3] = make_float2(v.z, v.w);
+            a[0] = w.x; a[1] = w.y; a[2] = w.z; a[3] = w.w;
+        } else {
+#pragma unroll
+            for (int p = 0; p < kMaxP; ++p)
+                if (p < P) { xy[p] = load_loc_cached<float>(lrow + (l * P + p) * 2); a[p] = load_attn<float>(arow + l * P + p); }
         }
-        tt.total = run;
     }
-    __syncthreads();
-}
+    static __device__ __forceinline__ void store(float* glrow, float* garow, int l, int P, const float (&gx)[kMaxP],
+                                                 const float (&gy)[kMaxP], const float (&ga)[kMaxP])
+    {
+        if (P == 4) {
+            *reinterpret_cast<float4*>(glrow + l * 8) = make_float4(gx[0], gy[0], gx[1], gy[1]);
+            *reinterpret_cast<float4*>(glrow + l * 8 + 4) = make_float4(gx[2], gy[2], gx[3], gy[3]);
+            *reinterpret_cast<float4*>(garow + l * 4) = make_float4(ga[0], ga[1], ga[2], ga[3]);
+        } else {
+#pragma unroll
+            for (int p = 0; p < kMaxP; ++p)
+                if (p < P) { store_loc<float>(glrow + (l * P + p) * 2, gx[p], gy[p]); garow[l * P + p] = ga[p]; }
+        }
+    }
+};
+template <typename H> struct LevelIO16 {
+    static __device__ __forceinline__ void load(const H* lrow, const H* arow, int l, int P, bool have,
+                                                float2 (&xy)[kMaxP], float (&a)[kMaxP])
+    {
+#pragma unroll
+        for (int p = 0; p < kMaxP; ++p) { xy[p] = make_float2(-8.f, -8.f); a[p] = 0.f; }
+        if (!have) return;
+        if (P == 4) {
+            const uint4 u = __ldg(reinterpret_cast<const uint4*>(lrow + l * 8));
+            const uint2 w = __ldg(reinterpret_cast<const uint2*>(arow + l * 4));
+            Half2Codec<H>::unpack(u.x, xy[0].x, xy[0].y); Half2Codec<H>::unpack(u.y, xy[1].x, xy[1].y);
+            Half2Codec<H>::unpack(u.z, xy[2].x, xy[2].y); Half2Codec<H>::unpack(u.w, xy[3].x, xy[3].y);
+            Half2Codec<H>::unpack(w.x, a[0], a[1]); Half2Codec<H>::unpack(w.y, a[2], a[3]);
+        } else {
+#pragma unroll
+            for (int p = 0; p < kMaxP; ++p)
+                if (p < P) { xy[p] = load_loc_cached<H>(lrow + (l * P + p) * 2); a[p] = load_attn<H>(arow + l * P + p); }
+        }
+    }
+    static __device__ __forceinline__ void store(H* glrow, H* garow, int l, int P, const float (&gx)[kMaxP],
+                                                 const float (&gy)[kMaxP], const float (&ga)[kMaxP])
+    {
+        if (P == 4) {
+            *reinterpret_cast<uint4*>(glrow + l * 8) = make_uint4(Half2Codec<H>::pack(gx[0], gy[0]), Half2Codec<H>::pack(gx[1], gy[1]),
+                                                                  Half2Codec<H>::pack(gx[2], gy[2]), Half2Codec<H>::pack(gx[3], gy[3]));
+            *reinterpret_cast<uint2*>(garow + l * 4) = make_uint2(Half2Codec<H>::pack(ga[0], ga[1]), Half2Codec<H>::pack(ga[2], ga[3]));
+        } else {
+#pragma unroll
+            for (int p = 0; p < kMaxP; ++p)
+                if (p < P) { store_loc<H>(glrow + (l * P + p) * 2, gx[p], gy[p]); garow[l * P + p] = from_f32<H>(ga[p]); }
+        }
+    }
+};
+template <> struct LevelIO<__nv_bfloat16> : LevelIO16<__nv_bfloat16> {};
+template <> struct LevelIO<__half> : LevelIO16<__half> {};
 
 struct DenseArgs {
     int* claim;                    // zero-initialised work counter (in the caller's workspace)
+    uint8_t* deferred;             // zero-initialised, [tiles_bound * N * M]: 1 = item left to the per-row kernel
+    int tiles_bound;
 };
 
 template <typename VT, typename AT, int D, bool FUSED>
@@ -186,26 +224,20 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
     static_assert(D % 32 == 0, "accumulator rows are read 32 columns at a time");
     using P = Plan<D>;
     using O = Op16<VT>;
-    constexpr int GS = D / 4;                  // lanes per row of the per-row fallback (VEC = 4)
     constexpr int NW = kThreads / 32;
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ LevelTable lt;
-    __shared__ TileTable tt;
-    __shared__ int s_scratch[kMaxLevels];
+    __shared__ FineTiles ft;
+    __shared__ int s_scratch;
     __shared__ int s_box[NW][kMaxLevels][4];
     __shared__ int s_win[kMaxLevels][5];       // ymin, xmin, wh, ww, chunks
     __shared__ int s_item[2];
     __shared__ uint32_t s_tmem;
     __shared__ __align__(8) uint64_t s_mbar[2];   // dot products ready / scatter product ready
-    // tap records of the per-row fallback
-    __shared__ int2 fb_a[NW][record_count(GS)];
-    __shared__ int fb_dx[NW][record_count(GS)];
-    __shared__ float4 fb_b[NW][record_count(GS)];
-    __shared__ float4 fb_fold[NW][1];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     stage_levels(lt, shapes, level_start, d);
-    build_tiles(tt, s_scratch, lt, d.L);
+    build_fine_tiles(ft, &s_scratch, lt, d.L, da.tiles_bound);
 
     uint8_t* sG = smem + P::OFF_G;
     uint8_t* sV = smem + P::OFF_V;
@@ -233,7 +265,7 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
     const uint32_t mbar = smem_u32(&s_mbar[0]), mbar2 = smem_u32(&s_mbar[1]);
     uint32_t phase = 0;
     const int LP = d.L * d.P;
-    const int items = tt.total * d.N * d.M;
+    const int items = ft.level >= 0 ? ft.total * d.N * d.M : 0;
     constexpr uint32_t idesc_u = umma_idesc(128, kPix, O::fmt);
     constexpr uint32_t idesc_gv = umma_idesc(128, D, O::fmt);
 
@@ -247,38 +279,37 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
         const int tile = item / (d.N * d.M);
         const int bm = item - tile * (d.N * d.M);
         const int b = bm / d.M, m = bm - b * d.M;
-        int lq = 0;
-        for (int k = 0; k < d.L; ++k)
-            if (tile >= tt.first[k] && tile < tt.first[k] + tt.nty[k] * tt.ntx[k]) lq = k;
-        const int tl = tile - tt.first[lq];
-        const int ty = tl / tt.ntx[lq], tx = tl - ty * tt.ntx[lq];
-        const int qH = lt.H[lq], qW = lt.W[lq];
-        const int y0 = (ty * qH) / tt.nty[lq], y1 = ((ty + 1) * qH) / tt.nty[lq];
-        const int x0 = (tx * qW) / tt.ntx[lq], x1 = ((tx + 1) * qW) / tt.ntx[lq];
-        const int cw = x1 - x0, chh = y1 - y0;
-        const int iy = tid / cw, ix = tid - iy * cw;
-        int q = (iy < chh) ? lt.qstart[lq] + (y0 + iy) * qW + x0 + ix : -1;
-        if (q >= d.Lq) q = -1;
+        const TileRect rect = fine_tile_rect(ft, lt, tile);
+        const int q = fine_tile_query(ft, lt, rect, tid, d.Lq);
         const bool row_ok = q >= 0;
         const size_t rowq = (size_t)b * d.Lq + (row_ok ? q : 0);
         const size_t row = rowq * d.M + m;
         const AT* lrow = loc + row * LP * 2;
         const AT* arow = attn + row * LP;
 
-        // ---- windows: bounding box of the footprint origins, per level ----------------------------------------------
+        // samples of the level being processed next (requested one level ahead)
+        float2 nxt_xy[kMaxP];
+        float nxt_a[kMaxP];
+        // ---- windows: bounding box of the live corner pixels, per level ---------------------------------------------
+        // (a corner is live when its pixel exists: the reference's guarded corner loads, .cuh:36-60, and the open
+        // sample window -1 < x < W, :229)
         for (int l = 0; l < d.L; ++l) {
             const int H = lt.H[l], W = lt.W[l];
             int ymin = 1 << 30, ymax = -1, xmin = 1 << 30, xmax = -1;
-            if (row_ok) {
-                for (int p = 0; p < d.P; ++p) {
-                    const float2 xy = load_loc_cached<AT>(lrow + (l * d.P + p) * 2);
-                    const float x = fmaf(xy.x, (float)W, -0.5f), y = fmaf(xy.y, (float)H, -0.5f);
-                    if ((y > -1.f) && (x > -1.f) && (y < (float)H) && (x < (float)W)) {
-                        const int yb = min(max((int)floorf(y), 0), max(H - 2, 0));
-                        const int xb = min(max((int)floorf(x), 0), max(W - 2, 0));
-                        ymin = min(ymin, yb); ymax = max(ymax, yb);
-                        xmin = min(xmin, xb); xmax = max(xmax, xb);
-                    }
+            float2 xy[kMaxP];
+            float aw[kMaxP];
+            LevelIO<AT>::load(lrow, arow, l, d.P, row_ok, xy, aw);
+            if (l == 0) {       // the chunk phase starts with level 0: keep its samples
+#pragma unroll
+                for (int p = 0; p < kMaxP; ++p) { nxt_xy[p] = xy[p]; nxt_a[p] = aw[p]; }
+            }
+#pragma unroll
+            for (int p = 0; p < kMaxP; ++p) {
+                const float x = fmaf(xy[p].x, (float)W, -0.5f), y = fmaf(xy[p].y, (float)H, -0.5f);
+                if ((y > -1.f) && (x > -1.f) && (y < (float)H) && (x < (float)W)) {
+                    const int iy = (int)floorf(y), ix = (int)floorf(x);
+                    ymin = min(ymin, max(iy, 0)); ymax = max(ymax, min(iy + 1, H - 1));
+                    xmin = min(xmin, max(ix, 0)); xmax = max(xmax, min(ix + 1, W - 1));
                 }
             }
             ymin = __reduce_min_sync(0xffffffffu, ymin); ymax = __reduce_max_sync(0xffffffffu, ymax);
@@ -295,8 +326,8 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
             }
             int wh = 0, ww = 0;
             if (ymax >= 0) {
-                wh = min(ymax - ymin + 2, lt.H[l]);
-                ww = min(xmax - xmin + 2, lt.W[l]);
+                wh = ymax - ymin + 1;
+                ww = xmax - xmin + 1;
             } else { ymin = 0; xmin = 0; }
             s_win[l][0] = ymin; s_win[l][1] = xmin; s_win[l][2] = wh; s_win[l][3] = ww;
             s_win[l][4] = (wh * ww + kPix - 1) / kPix;
@@ -304,47 +335,30 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
         __syncthreads();
         int total_chunks = 0;
         for (int l = 0; l < d.L; ++l) total_chunks += s_win[l][4];
-
         if (total_chunks > kMaxItemChunks) {
-            // ---- per-row path (msda_bwd.cuh) for this item ---------------------------------------------------------
-            auto qmap = [&](int i) {
-                const int jy = i / cw, jx = i - jy * cw;
-                const int qq = (jy < chh) ? lt.qstart[lq] + (y0 + jy) * qW + x0 + jx : -1;
-                return qq < d.Lq ? qq : -1;
-            };
-            if (lt.min_w > 1)
-                backward_rows<VT, AT, 4, GS, NW, true, FUSED>(lt, fb_a[warp], fb_dx[warp], fb_b[warp], fb_fold[warp], value, loc, attn,
-                                                              grad_out, grad_value_acc, grad_loc, grad_attn, d, fa, b, m, kThreads, qmap);
-            else
-                backward_rows<VT, AT, 4, GS, NW, false, FUSED>(lt, fb_a[warp], fb_dx[warp], fb_b[warp], fb_fold[warp], value, loc, attn,
-                                                               grad_out, grad_value_acc, grad_loc, grad_attn, d, fa, b, m, kThreads, qmap);
+            // windows too large for dense chunks: the per-row kernel does this item
+            if (tid == 0) da.deferred[item] = 1;
             __syncthreads();
             continue;
         }
 
-        // ---- G: this row of grad_out -> operand A of the dot product, and transposed -> operand B of the scatter product
+        // ---- G: the item's rows of grad_out -> operand A of the dot product, and transposed -> operand B of the scatter
+        // product.  D / 8 lanes per row (16 bytes each): a warp instruction reads 32 / (D / 8) whole rows.
+        constexpr int LPRV = P::KCH, RPIV = 32 / LPRV;
         {
-            uint4 g4[P::KCH];
 #pragma unroll
-            for (int c = 0; c < P::KCH; ++c) g4[c] = make_uint4(0, 0, 0, 0);
-            if (row_ok) {
-                const uint4* gp = reinterpret_cast<const uint4*>(grad_out + row * D);
+            for (int i = 0; i < LPRV; ++i) {
+                const int rr = i * RPIV + lane / LPRV, c = lane % LPRV;
+                const int qq = __shfl_sync(0xffffffffu, q, rr);
+                uint4 g4 = make_uint4(0, 0, 0, 0);
+                if (qq >= 0) g4 = __ldg(reinterpret_cast<const uint4*>(grad_out + (((size_t)b * d.Lq + qq) * d.M + m) * D) + c);
+                const int trow = warp * 32 + rr;
+                *reinterpret_cast<uint4*>(sG + (trow & 7) * 16 + (trow >> 3) * P::G_SBO + c * P::G_LBO) = g4;
+                uint8_t* gt = sT + (trow >> 3) * P::T_LBO + (trow & 7) * 2 + c * P::T_SBO;
+                const uint32_t w4[4] = {g4.x, g4.y, g4.z, g4.w};
 #pragma unroll
-                for (int c = 0; c < P::KCH; ++c) g4[c] = __ldg(gp + c);
-            }
-            uint8_t* ga = sG + (tid & 7) * 16 + (tid >> 3) * P::G_SBO;
-#pragma unroll
-            for (int c = 0; c < P::KCH; ++c) *reinterpret_cast<uint4*>(ga + c * P::G_LBO) = g4[c];
-            uint8_t* gt = sT + (tid >> 3) * P::T_LBO + (tid & 7) * 2;
-#pragma unroll
-            for (int c = 0; c < P::KCH; ++c) {
-                const uint32_t w4[4] = {g4[c].x, g4[c].y, g4[c].z, g4[c].w};
-#pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const int ch = c * 8 + e;
-                    const uint16_t h = (uint16_t)(w4[e >> 1] >> ((e & 1) * 16));
-                    *reinterpret_cast<uint16_t*>(gt + (ch & 7) * 16 + (ch >> 3) * P::T_SBO) = h;
-                }
+                for (int e = 0; e < 8; ++e)
+                    *reinterpret_cast<uint16_t*>(gt + e * 16) = (uint16_t)(w4[e >> 1] >> ((e & 1) * 16));
             }
         }
 
@@ -357,89 +371,94 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
             if (nch == 0) {
                 // nothing of this item samples inside level l: zero gradients for its samples
                 if (row_ok) {
-                    for (int p = 0; p < d.P; ++p) {
-                        const int s = l * d.P + p;
-                        store_loc<AT>(grad_loc + (row * LP + s) * 2, 0.f, 0.f);
-                        grad_attn[row * LP + s] = from_f32<AT>(0.f);
-                    }
+                    const float z[kMaxP] = {0.f, 0.f, 0.f, 0.f};
+                    LevelIO<AT>::store(grad_loc + row * LP * 2, grad_attn + row * LP, l, d.P, z, z, z);
+                }
+                if (l + 1 < d.L) {
+                    LevelIO<AT>::load(lrow, arow, l + 1, d.P, row_ok, nxt_xy, nxt_a);
                 }
                 continue;
             }
             const int H = lt.H[l], W = lt.W[l];
             const int ymin = s_win[l][0], xmin = s_win[l][1], wh = s_win[l][2], ww = s_win[l][3];
             const int npix = wh * ww;
-            const int rstep = H > 1 ? ww : 0, cstep = W > 1 ? 1 : 0;
-
             // ---- this row's 4 * P corner targets of the level, everything the chunk loop needs precomputed ----
-            // key  = window-linear pixel index >> 6 (which 64-column half of which chunk), kNone: no target
+            // tr   = window-linear pixel index of the corner (kNone: the corner's pixel does not exist / no sample)
             // wa   = byte address of the target's W element inside a chunk (column `tid`)
-            // sa   = byte address of its dot product inside this thread's staging row
             // tw   = bilinear x attention weight (scatter product)
-            // cga / cgx / cgy = coefficients of <grad_out, corner> in grad_attn / grad_loc.x / grad_loc.y
-            //        (.cuh:373-374: pixel-space derivative times attention weight times W (x) / H (y))
+            // cga / cgx / cgy = coefficients of <grad_out, corner> in grad_attn / d sample / d x / d sample / d y
             constexpr int NT = 4 * kMaxP;
             constexpr int kNone = -(1 << 20);
-            int key[NT];
-            uint32_t wa[NT], sa[NT];
+            int tr[NT];
+            uint32_t wa[NT];
             float tw[NT], cga[NT], cgx[NT], cgy[NT];
-            float acc_a[kMaxP], acc_x[kMaxP], acc_y[kMaxP];
+            float acc_a[kMaxP], acc_x[kMaxP], acc_y[kMaxP], att[kMaxP];
             const uint32_t w_col = smem_u32(sW) + (tid >> 3) * P::W_LBO + (tid & 7) * 2;
             const uint32_t st_row = smem_u32(stage);
 #pragma unroll
             for (int p = 0; p < kMaxP; ++p) {
                 acc_a[p] = acc_x[p] = acc_y[p] = 0.f;
-                bool ok = false;
-                int r00 = 0;
-                float a = 0.f;
-                Axis ay, ax;
-                ay.b = ax.b = 0; ay.w0 = ay.w1 = ay.d0 = ay.d1 = ax.w0 = ax.w1 = ax.d0 = ax.d1 = 0.f;
-                if (row_ok && p < d.P) {
-                    const int s = l * d.P + p;
-                    const float2 xy = load_loc_cached<AT>(lrow + s * 2);
-                    a = load_attn<AT>(arow + s);
-                    const float x = fmaf(xy.x, (float)W, -0.5f), y = fmaf(xy.y, (float)H, -0.5f);
-                    ok = (y > -1.f) && (x > -1.f) && (y < (float)H) && (x < (float)W);
-                    ay = make_axis(y, H, ok);
-                    ax = make_axis(x, W, ok);
-                    r00 = (ay.b - ymin) * ww + (ax.b - xmin);
-                }
+                // the level's samples were requested while the previous level was being processed
+                const float2 xy = nxt_xy[p];
+                const float a = nxt_a[p];
+                att[p] = a;
+                const float x = fmaf(xy.x, (float)W, -0.5f), y = fmaf(xy.y, (float)H, -0.5f);
+                const bool inside = (y > -1.f) && (x > -1.f) && (y < (float)H) && (x < (float)W);
+                const float fy = floorf(y), fx = floorf(x);
+                const int iy = (int)fy, ix = (int)fx;
+                const float ly = y - fy, lx = x - fx;
+                const bool vy[2] = {inside && iy >= 0, inside && iy + 1 <= H - 1};
+                const bool vx[2] = {inside && ix >= 0, inside && ix + 1 <= W - 1};
+                const float wy[2] = {1.f - ly, ly}, wx[2] = {1.f - lx, lx};
+                const int r00 = (iy - ymin) * ww + (ix - xmin);
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
-                    const int t = p * 4 + c;
-                    const float wy = (c >> 1) ? ay.w1 : ay.w0, wx = (c & 1) ? ax.w1 : ax.w0;
-                    const float dy = (c >> 1) ? ay.d1 : ay.d0, dx = (c & 1) ? ax.d1 : ax.d0;
-                    // a footprint row / column that does not exist (H == 1 / W == 1) carries no weight and no derivative
-                    const bool live = ok && !((c >> 1) && rstep == 0) && !((c & 1) && cstep == 0);
-                    const int r = r00 + (c >> 1) * rstep + (c & 1) * cstep;
-                    key[t] = live ? (r >> 6) : kNone;
+                    const int t = p * 4 + c, cy = c >> 1, cx = c & 1;
+                    const bool live = vy[cy] && vx[cx];
+                    const int r = r00 + cy * ww + cx;
+                    tr[t] = live ? r : kNone;
                     const int idx = r & (kPix - 1);
                     wa[t] = w_col + (idx & 7) * 16 + (idx >> 3) * P::W_SBO;
-                    sa[t] = st_row + (r & 63) * 4;
-                    tw[t] = wy * wx * a;
-                    cga[t] = wy * wx;
-                    cgx[t] = wy * dx * a * (float)W;
-                    cgy[t] = dy * wx * a * (float)H;
+                    cga[t] = live ? wy[cy] * wx[cx] : 0.f;
+                    tw[t] = cga[t] * a;
+                    // one-sided derivatives of the bilinear weights (.cuh:141-160): -1 / +1 for the lower / upper pixel
+                    cgx[t] = live ? (cx ? wy[cy] : -wy[cy]) : 0.f;
+                    cgy[t] = live ? (cy ? wx[cx] : -wx[cx]) : 0.f;
                 }
+            }
+            // request the next level's samples now
+            if (l + 1 < d.L) {
+                LevelIO<AT>::load(lrow, arow, l + 1, d.P, row_ok, nxt_xy, nxt_a);
             }
 
             // window coordinates of this thread's pixel of the current chunk, advanced incrementally
             int pwy = tid / ww, pwx = tid - pwy * ww;
             const int step_y = kPix / ww, step_x = kPix - step_y * ww;
+            int vwy[LPRV], vwx[LPRV];       // ... and of the pixels whose value rows this thread fetches
+#pragma unroll
+            for (int i = 0; i < LPRV; ++i) {
+                const int r = warp * 32 + i * RPIV + lane / LPRV;
+                vwy[i] = r / ww;
+                vwx[i] = r - vwy[i] * ww;
+            }
 
             for (int k = 0; k < nch; ++k) {
                 const int r0 = k * kPix;
-                // (a) this thread's window pixel: its value row -> registers
+                // (a) the chunk's value rows -> registers, D / 8 lanes per pixel row (16 bytes each)
                 const bool pix_ok = r0 + tid < npix;
                 const size_t pix = (size_t)lt.start[l] + (size_t)(ymin + pwy) * W + (xmin + pwx);
                 pwy += step_y; pwx += step_x;
                 if (pwx >= ww) { pwx -= ww; ++pwy; }
-                uint4 v4[P::KCH];
+                uint4 v4[LPRV];
 #pragma unroll
-                for (int c = 0; c < P::KCH; ++c) v4[c] = make_uint4(0, 0, 0, 0);
-                if (pix_ok) {
-                    const uint4* vp = reinterpret_cast<const uint4*>(vbase + pix * pix_stride);
-#pragma unroll
-                    for (int c = 0; c < P::KCH; ++c) v4[c] = __ldg(vp + c);
+                for (int i = 0; i < LPRV; ++i) {
+                    v4[i] = make_uint4(0, 0, 0, 0);
+                    if (r0 + warp * 32 + i * RPIV + lane / LPRV < npix) {
+                        const size_t vp = (size_t)lt.start[l] + (size_t)(ymin + vwy[i]) * W + (xmin + vwx[i]);
+                        v4[i] = __ldg(reinterpret_cast<const uint4*>(vbase + vp * pix_stride) + lane % LPRV);
+                    }
+                    vwy[i] += step_y; vwx[i] += step_x;
+                    if (vwx[i] >= ww) { vwx[i] -= ww; ++vwy[i]; }
                 }
                 // (b) densify: column `tid` of W gets this row's corner weights that fall into the chunk.  The four
                 // corners of one sample are distinct pixels: four independent read-modify-writes; corners of
@@ -451,7 +470,7 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
                         const int t = p * 4 + c;
-                        hit[c] = (key[t] >> 1) == k && tw[t] != 0.f;
+                        hit[c] = (tr[t] >> 7) == k;
                         h[c] = 0;
                         if (hit[c]) asm volatile("ld.shared.u16 %0, [%1];" : "=h"(h[c]) : "r"(wa[t]) : "memory");
                     }
@@ -465,10 +484,10 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                     }
                 }
                 // (c) value rows -> operand B of the dot product
-                {
-                    uint8_t* va = sV + (tid & 7) * 16 + (tid >> 3) * P::G_SBO;
 #pragma unroll
-                    for (int c = 0; c < P::KCH; ++c) *reinterpret_cast<uint4*>(va + c * P::G_LBO) = v4[c];
+                for (int i = 0; i < LPRV; ++i) {
+                    const int trow = warp * 32 + i * RPIV + lane / LPRV;
+                    *reinterpret_cast<uint4*>(sV + (trow & 7) * 16 + (trow >> 3) * P::G_SBO + (lane % LPRV) * P::G_LBO) = v4[i];
                 }
                 // (d) operands visible to the tensor core; TMEM reads of the previous chunk are complete
                 proxy_fence();
@@ -511,7 +530,7 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
 #pragma unroll
                     for (int t = 0; t < NT; ++t) {
                         float u = 0.f;
-                        if (key[t] == want) asm volatile("ld.shared.f32 %0, [%1];" : "=f"(u) : "r"(sa[t]) : "memory");
+                        if ((tr[t] >> 6) == want) asm volatile("ld.shared.f32 %0, [%1];" : "=f"(u) : "r"(st_row + (tr[t] & 63) * 4) : "memory");
                         acc_a[t >> 2] = fmaf(cga[t], u, acc_a[t >> 2]);
                         acc_x[t >> 2] = fmaf(cgx[t], u, acc_x[t >> 2]);
                         acc_y[t >> 2] = fmaf(cgy[t], u, acc_y[t >> 2]);
@@ -553,19 +572,19 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                 // (i) restore the zeros of W
 #pragma unroll
                 for (int t = 0; t < NT; ++t)
-                    if ((key[t] >> 1) == k) asm volatile("st.shared.u16 [%0], %1;" :: "r"(wa[t]), "h"((uint16_t)0) : "memory");
+                    if ((tr[t] >> 7) == k) asm volatile("st.shared.u16 [%0], %1;" :: "r"(wa[t]), "h"((uint16_t)0) : "memory");
             }
 
             // ---- the level's samples are complete: gradients of the sampling locations and attention weights ----
             if (row_ok) {
+                float gx[kMaxP], gy[kMaxP];
 #pragma unroll
                 for (int p = 0; p < kMaxP; ++p) {
-                    if (p < d.P) {
-                        const int s = l * d.P + p;
-                        store_loc<AT>(grad_loc + (row * LP + s) * 2, acc_x[p], acc_y[p]);
-                        grad_attn[row * LP + s] = from_f32<AT>(acc_a[p]);
-                    }
+                    // .cuh:373-374: pixel-space derivative times attention weight times W (x) / H (y)
+                    gx[p] = acc_x[p] * att[p] * (float)W;
+                    gy[p] = acc_y[p] * att[p] * (float)H;
                 }
+                LevelIO<AT>::store(grad_loc + row * LP * 2, grad_attn + row * LP, l, d.P, gx, gy, acc_a);
             }
         }
         // G / Gt / the window table are rewritten by the next item

@@ -198,19 +198,27 @@ int forward_typed(const void* value, const int64_t* shapes, const int64_t* ls, c
     return launch_forward_generic<VT, AT, float>(value, shapes, ls, loc, attn, out, d, st);
 }
 
+// deferred != nullptr: split mode, after the dense-window kernel (see backward_items); the grid then also covers
+// the tile items.  traced: this launch is the one msda_b200_trace_next brackets.
 template <typename VT, typename AT, int VEC, int GS, bool FUSED>
 int launch_backward_vec_impl(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
                              const void* attn, const void* go, float* gv_acc, void* gl, void* ga,
-                             const msda_dims* d, cudaStream_t st, const FusedArgs& fa)
+                             const msda_dims* d, cudaStream_t st, const FusedArgs& fa,
+                             const uint8_t* deferred = nullptr, int tiles_bound = 0, bool traced = true)
 {
     constexpr int NW = 8;
     const KernelDims k = make_dims(d, NW * (32 / GS), kBackwardTileQ);
     auto kern = msda_backward_kernel<VT, AT, VEC, GS, NW, FUSED>;
-    const int grid = item_grid(k);
-    {
+    const int sms = device_info().sms > 0 ? device_info().sms : 148;
+    const int tile_ctas = deferred ? 2 * sms : 0;
+    const int grid = item_grid(k) + tile_ctas;
+    if (traced) {
         TraceScope trace(st);
         kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa);
+                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, deferred, tiles_bound, tile_ctas);
+    } else {
+        kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
+                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, deferred, tiles_bound, tile_ctas);
     }
     ++g_last_launches;
     return (int)cudaGetLastError();
@@ -246,15 +254,21 @@ int launch_backward_generic(const void* value, const int64_t* shapes, const int6
     return (int)cudaGetLastError();
 }
 
-// Encoder-form backward on the tensor cores (msda_dense.cuh).  The work counter lives behind the fp32
-// accumulator in the caller's workspace and is zeroed by the same memset.
+// Encoder-form backward on the tensor cores (msda_dense.cuh) + the per-row kernel in split mode for the rest.
+// Behind the fp32 accumulator the caller's workspace holds the dense kernel's work counter and the deferred-item
+// flags (one byte per (tile, batch, head)); one memset zeroes all three.
 inline size_t dense_counter_offset(size_t nval) { return (nval * sizeof(float) + 255) & ~(size_t)255; }
 constexpr size_t kDenseCounterBytes = 256;
+inline int dense_tiles_bound(const msda_dims* d) { return d->Lq / 32 + 64; }
+inline size_t dense_extra_bytes(const msda_dims* d)
+{
+    return kDenseCounterBytes + (((size_t)dense_tiles_bound(d) * d->N * d->M + 255) & ~(size_t)255);
+}
 
 template <typename VT, typename AT, int D>
 int launch_backward_dense(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
                           const void* attn, const void* go, float* gv_acc, void* gl, void* ga, int* claim,
-                          const msda_dims* d, cudaStream_t st)
+                          uint8_t* deferred, const msda_dims* d, cudaStream_t st)
 {
     KernelDims k = make_dims(d, 16, kBackwardTileQ);
     auto kern = dense::msda_backward_dense_kernel<VT, AT, D, false>;
@@ -270,13 +284,16 @@ int launch_backward_dense(const void* value, const int64_t* shapes, const int64_
     const int sms = device_info().sms > 0 ? device_info().sms : 148;
     dense::DenseArgs da;
     da.claim = claim;
-    {
-        TraceScope trace(st);
-        kern<<<2 * sms, dense::kThreads, smem, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                                                     (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, FusedArgs{}, da);
-    }
+    da.deferred = deferred;
+    da.tiles_bound = dense_tiles_bound(d);
+    TraceScope trace(st);       // the pair of launches is "the backward kernel" of msda_b200_trace_next
+    kern<<<2 * sms, dense::kThreads, smem, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
+                                                 (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, FusedArgs{}, da);
     ++g_last_launches;
-    return (int)cudaGetLastError();
+    if (cudaError_t e = cudaGetLastError()) return (int)e;
+    // the queries of the coarser levels, and whatever the dense kernel handed back
+    return launch_backward_vec_impl<VT, AT, 4, D / 4, false>(value, shapes, ls, loc, attn, go, gv_acc, gl, ga, d, st, FusedArgs{},
+                                                             deferred, da.tiles_bound, false);
 }
 
 // VT = float: gradients accumulate straight into grad_value (zero-filled first).
@@ -300,10 +317,11 @@ int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, 
     bool dense_ok = false;
     if constexpr (sizeof(VT) == 2) {
         dense_ok = !fa && d->Lq == d->S && d->Lq > 0 && d->P <= dense::kMaxP && (d->D == 32 || d->D == 64) &&
-                   ws_bytes >= dense_counter_offset(nval) + kDenseCounterBytes && aligned16(value) && aligned16(go) &&
+                   ws_bytes >= dense_counter_offset(nval) + dense_extra_bytes(d) && aligned16(value) && aligned16(go) &&
+                   aligned16(loc) && aligned16(attn) && aligned16(gl) && aligned16(ga) &&
                    env_int("MSDA_B200_DENSE", 1) && !env_int("MSDA_B200_FORCE_GENERIC", 0) && !env_int("MSDA_B200_TILE_1D", 0);
     }
-    cudaError_t e = cudaMemsetAsync(acc, 0, dense_ok ? dense_counter_offset(nval) + kDenseCounterBytes : nval * sizeof(float), st);
+    cudaError_t e = cudaMemsetAsync(acc, 0, dense_ok ? dense_counter_offset(nval) + dense_extra_bytes(d) : nval * sizeof(float), st);
     if (e != cudaSuccess) return (int)e;
     int rc = 0;
     if (d->Lq > 0) {
@@ -313,8 +331,9 @@ int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, 
         if constexpr (sizeof(VT) == 2) {
             if (dense_ok) {
                 int* claim = reinterpret_cast<int*>(reinterpret_cast<char*>(ws) + dense_counter_offset(nval));
-                if (d->D == 32) rc = launch_backward_dense<VT, AT, 32>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, d, st);
-                else rc = launch_backward_dense<VT, AT, 64>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, d, st);
+                uint8_t* deferred = reinterpret_cast<uint8_t*>(claim) + kDenseCounterBytes;
+                if (d->D == 32) rc = launch_backward_dense<VT, AT, 32>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, deferred, d, st);
+                else rc = launch_backward_dense<VT, AT, 64>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, deferred, d, st);
                 done = true;
             }
         }

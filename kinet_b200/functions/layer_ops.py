@@ -229,17 +229,27 @@ class LinearFunction(Function):
 
 def lp_params(owner, weight, bias, dtype):
     """Low-precision copies of a module's (weight, bias) for inference under autocast, made once and kept on
-    ``owner`` until a parameter changes (in-place updates bump ``_version``; re-assignment changes the
-    identity).  Unlike autocast's own cache they outlive the autocast region (and cover parameters that are
+    ``owner`` until a parameter changes: in-place updates through the parameter bump ``_version``, re-assignment
+    changes the identity, ``p.data = ...`` / ``module.to()`` / ``module.half()`` change ``data_ptr``.  In-place edits
+    THROUGH ``.data`` (``p.data.copy_()``, ``constant_(p.data, ...)``; EMA weight swaps) change none of the three:
+    call ``invalidate_lp_cache(module)`` after those.  Unlike autocast's own cache they outlive the autocast region (and cover parameters that are
     used through slices, which autocast never caches), so a per-frame CUDA graph recorded after one eager
     warm-up holds no weight casts.  A graph keeps reading the copies it was recorded with: re-record it after
     changing the weights."""
-    key = (dtype, id(weight), weight._version, id(bias), bias._version if bias is not None else 0)
+    key = (dtype, id(weight), weight._version, weight.data_ptr(),
+           id(bias), bias._version if bias is not None else 0, bias.data_ptr() if bias is not None else 0)
     hit = owner.__dict__.get("_kinet_lp")
     if hit is None or hit[0] != key:
         hit = (key, weight.detach().to(dtype), bias.detach().to(dtype) if bias is not None else None)
         owner.__dict__["_kinet_lp"] = hit
     return hit[1], hit[2]
+
+
+def invalidate_lp_cache(module):
+    """Drop the cached low-precision parameter copies of ``module`` and all its submodules (after parameter edits
+    that ``lp_params`` cannot see, e.g. ``p.data.copy_(...)``)."""
+    for m in module.modules():
+        m.__dict__.pop("_kinet_lp", None)
 
 
 def inference_mirror(owner, weight, bias, x):

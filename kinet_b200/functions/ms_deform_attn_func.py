@@ -14,6 +14,7 @@ drop-in shim for ``import MultiScaleDeformableAttention as MSDA``) re-exports.
 There is no CPU path: CPU tensors raise, like the reference (ms_deform_attn.h:27,48).
 """
 import ctypes
+import os
 
 import torch
 import torch.nn.functional as F
@@ -199,6 +200,10 @@ def fused_supported(value, n_levels, n_points):
     D = value.shape[-1]
     if not (value.is_cuda and value.dtype in (torch.float32, torch.bfloat16, torch.float16) and D in (16, 32, 36, 64)):
         return False
+    # the vector kernels need 16-byte aligned rows (an offset view of a larger buffer may not be); the library
+    # answers MSDA_E_SHAPE for those, and for MSDA_B200_FORCE_GENERIC, instead of running a fused kernel
+    if value.data_ptr() % 16 or not value.is_contiguous() or os.environ.get("MSDA_B200_FORCE_GENERIC", "0") not in ("", "0"):
+        return False
     # a lane keeps the softmax numerators of <= 4 samples of a row (kFusedMaxChunks, msda_common.cuh); samples
     # are dealt to the first 2^k <= D/VEC lanes of the row's group, VEC = 8 only in the 16-bit forward
     lanes = D // (4 if value.dtype == torch.float32 or D == 36 else 8)
@@ -220,6 +225,11 @@ def _offset_norm_f32(offset_norm, device):
     return _norm_f32.put(offset_norm, offset_norm.to(device=device, dtype=torch.float32).contiguous(), str(device))
 
 
+def _aligned16(t):
+    """The kernels read these with 16-byte vector loads; an offset view can start anywhere."""
+    return t if t.data_ptr() % 16 == 0 else t.clone()
+
+
 def _fused_inputs(value, offsets, logits, reference_points, offset_norm, query_mask):
     if value.dtype == torch.float32:
         aux = torch.float32
@@ -229,7 +239,7 @@ def _fused_inputs(value, offsets, logits, reference_points, offset_norm, query_m
         aux = torch.float32
     off = offsets.to(aux).contiguous()
     lg = logits.to(aux).contiguous()
-    ref = reference_points.to(torch.float32).contiguous()
+    ref = _aligned16(reference_points.to(torch.float32).contiguous())
     norm = _offset_norm_f32(offset_norm, value.device) if offset_norm is not None else None
     mask = query_mask.to(torch.uint8).contiguous() if query_mask is not None else None
     args = _lib.MsdaFusedInputs(off.data_ptr(), lg.data_ptr(), ref.data_ptr(),
@@ -287,7 +297,7 @@ class MSDeformAttnFusedFunction(Function):
         aux, args, keep = _fused_inputs(value, offsets, logits, ref, norm, mask)
         off_c = keep[0]
         dims = _lib.MsdaDims(N, S, M, D, L, Lq, P)
-        go = grad_output.to(value.dtype).contiguous()
+        go = _aligned16(grad_output.to(value.dtype).contiguous())
         grad_value = torch.empty_like(value)
         grad_off = torch.empty((N, Lq, M, L, P, 2), dtype=aux, device=value.device)
         grad_logit = torch.empty((N, Lq, M, L * P), dtype=aux, device=value.device)

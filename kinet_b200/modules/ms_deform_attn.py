@@ -18,7 +18,7 @@ from torch.nn.init import constant_, xavier_uniform_
 
 from .._cache import PerTensorCache
 from ..functions import MSDeformAttnFunction, MSDeformAttnFusedFunction, fused_supported
-from ..functions.layer_ops import linear as _linear
+from ..functions.layer_ops import invalidate_lp_cache, linear as _linear
 
 
 _shapes_validated = PerTensorCache()   # spatial_shapes tensor object -> True, keyed additionally by Len_in
@@ -38,6 +38,23 @@ def _check_spatial_shapes(shapes, len_in):
         return
     assert (shapes[:, 0] * shapes[:, 1]).sum() == len_in
     _shapes_validated.put(shapes, True, len_in)
+
+
+_mask_empty = PerTensorCache()        # padding-mask tensor object -> True when it masks nothing
+
+
+def _no_padding(mask):
+    """True when the (N, S) padding mask is all False -- tracking inference and any batch of equally sized images.
+    The reference zero-fills ``value`` through the mask in every layer regardless (ms_deform_attn.py:65-66): a
+    read and a write of the whole value tensor, 12 times per frame, for nothing.  The answer is one device->host
+    read per mask tensor OBJECT (every layer of a forward receives the same one); during CUDA-graph capture no
+    read is possible and an unknown mask is applied."""
+    hit = _mask_empty.get(mask)
+    if hit is not None:
+        return hit
+    if mask.is_cuda and torch.cuda.is_current_stream_capturing():
+        return False
+    return _mask_empty.put(mask, not bool(mask.any()))
 
 
 class MSDeformAttn(nn.Module):
@@ -81,6 +98,7 @@ class MSDeformAttn(nn.Module):
         constant_(self.value_proj.bias.data, 0.)
         xavier_uniform_(self.output_proj.weight.data)
         constant_(self.output_proj.bias.data, 0.)
+        invalidate_lp_cache(self)       # the .data edits above are invisible to the low-precision copies' cache key
 
     def forward(self, query, reference_points, input_flatten, input_spatial_shapes,
                 input_padding_mask=None, query_attn_mask=None):
@@ -95,7 +113,7 @@ class MSDeformAttn(nn.Module):
         _check_spatial_shapes(input_spatial_shapes, Len_in)
 
         value = _linear(input_flatten, self.value_proj)
-        if input_padding_mask is not None:
+        if input_padding_mask is not None and not _no_padding(input_padding_mask):
             value = value.masked_fill(input_padding_mask[..., None], float(0))
         value = value.view(N, Len_in, self.n_heads, self.d_model // self.n_heads)
 

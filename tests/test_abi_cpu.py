@@ -47,7 +47,11 @@ def test_workspace_size(lib):
     from kinet_b200._lib import MsdaDims, MSDA_BF16, MSDA_F32
     d = MsdaDims(2, 100, 8, 32, 4, 7, 4)
     assert lib.msda_b200_backward_workspace_bytes(MSDA_F32, ctypes.byref(d)) == 0
-    assert lib.msda_b200_backward_workspace_bytes(MSDA_BF16, ctypes.byref(d)) == 2 * 100 * 8 * 32 * 4
+    # fp32 accumulator (rounded up to 256 bytes) + the dense-window kernel's work counter (256 bytes) and its
+    # deferred-item flags: one byte per (tile, batch, head), at most Lq / 32 + 64 tiles
+    acc = 2 * 100 * 8 * 32 * 4
+    flags = (7 // 32 + 64) * 2 * 8
+    assert lib.msda_b200_backward_workspace_bytes(MSDA_BF16, ctypes.byref(d)) == (acc + 255) // 256 * 256 + 256 + (flags + 255) // 256 * 256
 
 
 def test_argument_validation_without_gpu(lib):
@@ -211,3 +215,74 @@ def test_per_tensor_caches_survive_alternating_level_lists(monkeypatch):
     del t
     t2 = torch.ones(1)                                 # may or may not reuse the id; a dead weakref must never hit
     assert c.get(t2) is None or id(t2) != key
+
+
+def test_per_tensor_cache_accepts_inference_tensors():
+    """Tensors created under torch.inference_mode() have no version counter (reading it raises); the reference
+    module works there, so must ours (the shapes tensor is built inside forward, like the reference's)."""
+    from kinet_b200._cache import PerTensorCache
+    from kinet_b200.modules import ms_deform_attn as mod
+    from kinet_b200.modules.deformable_transformer import _level_grids
+    with torch.inference_mode():
+        shapes = torch.tensor([[2, 3], [1, 2]])
+        mod._check_spatial_shapes(shapes, 8)
+        mod._check_spatial_shapes(shapes, 8)
+        with pytest.raises(AssertionError):
+            mod._check_spatial_shapes(shapes, 9)
+        g = _level_grids(shapes, torch.device("cpu"))
+        assert _level_grids(shapes, torch.device("cpu")) is g
+        mask = torch.zeros(1, 8, dtype=torch.bool)
+        assert mod._no_padding(mask) and mod._no_padding(mask)
+    c = PerTensorCache()
+    with torch.inference_mode():
+        t = torch.zeros(3)
+    c.put(t, "v")
+    assert c.get(t) == "v"
+    m = torch.zeros(2, 4, dtype=torch.bool)
+    assert mod._no_padding(m)
+    m[0, 1] = True                                     # in-place change: asked again
+    assert not mod._no_padding(m)
+
+
+def test_flat_params_groups_clip_and_state_dict_refresh():
+    """The reference's optimizer groups (src/train.py:103-117) and gradient clipping (engine.py:147-148) on the
+    flat layout, against the same model trained the plain way; load_state_dict refreshes the bf16 mirror."""
+    from torch import nn
+    from kinet_b200.training import FlatParams, reference_param_groups
+
+    class Net(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.value_proj = nn.Linear(6, 6)
+            self.sampling_offsets = nn.Linear(6, 4)
+            self.reference_points = nn.Linear(6, 2)
+
+        def forward(self, x):
+            return self.value_proj(x).sum() + (self.sampling_offsets(x) ** 2).sum() + self.reference_points(x).sum()
+
+    torch.manual_seed(0)
+    a, b = Net(), Net()
+    b.load_state_dict(a.state_dict())
+    x = torch.randn(5, 6)
+    ga = reference_param_groups(a, lr=1e-2, lr_linear_proj_mult=0.1)
+    assert [len(g["params"]) for g in ga] == [2, 4] and ga[1]["lr"] == pytest.approx(1e-3)
+    opt_a = torch.optim.AdamW(ga, lr=1e-2, weight_decay=1e-4)
+    fp = FlatParams(b, groups=reference_param_groups(b, lr=1e-2, lr_linear_proj_mult=0.1))
+    opt_b = torch.optim.AdamW(fp.optimizer_groups(), lr=1e-2, weight_decay=1e-4)
+    for _ in range(3):
+        opt_a.zero_grad()
+        a(x).backward()
+        torch.nn.utils.clip_grad_norm_(a.parameters(), 0.1)
+        opt_a.step()
+        fp.zero_grad()
+        b(x).backward()
+        fp.clip_grad_norm_(0.1)
+        opt_b.step()
+        fp.refresh()
+    for (n, pa), (_, pb) in zip(a.named_parameters(), b.named_parameters()):
+        assert torch.allclose(pa, pb, rtol=1e-5, atol=1e-7), n
+    assert torch.allclose(fp.lp.float(), fp.master, rtol=1e-2, atol=1e-3)
+    b.load_state_dict({k: torch.ones_like(v) for k, v in b.state_dict().items()})
+    assert fp.lp.float().sum() == fp.master.sum() == fp.numel        # mirror follows a checkpoint load
+    with pytest.raises(ValueError):
+        FlatParams(Net(), groups=[{"params": list(Net().parameters())}])   # groups of another module

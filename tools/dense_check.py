@@ -65,9 +65,12 @@ def main():
         for dt in (torch.bfloat16, torch.float16):
             for regime in ("structured", "uniform"):
                 case(name, s, dt, regime, False)
-    for tag in ("C2_enc", "C5_enc"):
-        for regime in ("structured", "uniform"):
-            case(tag, resolve(tag), torch.bfloat16, regime, timeit)
+    for mc in [int(x) for x in os.environ.get("SWEEP_MAXCH", "5").split(",")]:
+        os.environ["MSDA_B200_DENSE_MAXCH"] = str(mc)
+        print("max level chunks", mc)
+        for tag in ("C2_enc", "C5_enc"):
+            for regime in ("structured", "uniform"):
+                case(tag, resolve(tag), torch.bfloat16, regime, timeit)
 
 
 if __name__ == "__main__":
