@@ -156,6 +156,39 @@ template <> struct LevelIO<float> {
                 if (p < P) { xy[p] = load_loc_cached<float>(lrow + (l * P + p) * 2); a[p] = load_attn<float>(arow + l * P + p); }
         }
     }
+    // plain (coherent) loads: the softmax backward re-reads what this thread stored
+    static __device__ __forceinline__ void load_attn_only(const float* arow, int l, int P, bool have, float (&a)[kMaxP])
+    {
+#pragma unroll
+        for (int p = 0; p < kMaxP; ++p) a[p] = 0.f;
+        if (!have) return;
+        if (P == 4) {
+            const float4 w = *reinterpret_cast<const float4*>(arow + l * 4);
+            a[0] = w.x; a[1] = w.y; a[2] = w.z; a[3] = w.w;
+        } else {
+#pragma unroll
+            for (int p = 0; p < kMaxP; ++p) if (p < P) a[p] = arow[l * P + p];
+        }
+    }
+    static __device__ __forceinline__ void store_attn_only(float* garow, int l, int P, const float (&ga)[kMaxP])
+    {
+        if (P == 4) *reinterpret_cast<float4*>(garow + l * 4) = make_float4(ga[0], ga[1], ga[2], ga[3]);
+        else {
+#pragma unroll
+            for (int p = 0; p < kMaxP; ++p) if (p < P) garow[l * P + p] = ga[p];
+        }
+    }
+    static __device__ __forceinline__ void store_loc_only(float* glrow, int l, int P, const float (&gx)[kMaxP],
+                                                          const float (&gy)[kMaxP])
+    {
+        if (P == 4) {
+            *reinterpret_cast<float4*>(glrow + l * 8) = make_float4(gx[0], gy[0], gx[1], gy[1]);
+            *reinterpret_cast<float4*>(glrow + l * 8 + 4) = make_float4(gx[2], gy[2], gx[3], gy[3]);
+        } else {
+#pragma unroll
+            for (int p = 0; p < kMaxP; ++p) if (p < P) store_loc<float>(glrow + (l * P + p) * 2, gx[p], gy[p]);
+        }
+    }
     static __device__ __forceinline__ void store(float* glrow, float* garow, int l, int P, const float (&gx)[kMaxP],
                                                  const float (&gy)[kMaxP], const float (&ga)[kMaxP])
     {
@@ -189,6 +222,27 @@ template <typename H> struct LevelIO16 {
                 if (p < P) { xy[p] = load_loc_cached<H>(lrow + (l * P + p) * 2); a[p] = load_attn<H>(arow + l * P + p); }
         }
     }
+    static __device__ __forceinline__ void load_attn_only(const H* arow, int l, int P, bool have, float (&a)[kMaxP])
+    {
+#pragma unroll
+        for (int p = 0; p < kMaxP; ++p) a[p] = 0.f;
+        if (!have) return;
+        if (P == 4) {
+            const uint2 w = *reinterpret_cast<const uint2*>(arow + l * 4);
+            Half2Codec<H>::unpack(w.x, a[0], a[1]); Half2Codec<H>::unpack(w.y, a[2], a[3]);
+        } else {
+#pragma unroll
+            for (int p = 0; p < kMaxP; ++p) if (p < P) a[p] = to_f32<H>(arow[l * P + p]);
+        }
+    }
+    static __device__ __forceinline__ void store_attn_only(H* garow, int l, int P, const float (&ga)[kMaxP])
+    {
+        if (P == 4) *reinterpret_cast<uint2*>(garow + l * 4) = make_uint2(Half2Codec<H>::pack(ga[0], ga[1]), Half2Codec<H>::pack(ga[2], ga[3]));
+        else {
+#pragma unroll
+            for (int p = 0; p < kMaxP; ++p) if (p < P) garow[l * P + p] = from_f32<H>(ga[p]);
+        }
+    }
     static __device__ __forceinline__ void store(H* glrow, H* garow, int l, int P, const float (&gx)[kMaxP],
                                                  const float (&gy)[kMaxP], const float (&ga)[kMaxP])
     {
@@ -220,7 +274,6 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                            float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
                            AT* __restrict__ grad_attn, const KernelDims d, const FusedArgs fa, const DenseArgs da)
 {
-    static_assert(!FUSED, "the fused prologue of the dense kernel is a separate instantiation (not built yet)");
     static_assert(D % 32 == 0, "accumulator rows are read 32 columns at a time");
     using P = Plan<D>;
     using O = Op16<VT>;
@@ -284,8 +337,57 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
         const bool row_ok = q >= 0;
         const size_t rowq = (size_t)b * d.Lq + (row_ok ? q : 0);
         const size_t row = rowq * d.M + m;
-        const AT* lrow = loc + row * LP * 2;
-        const AT* arow = attn + row * LP;
+        const AT* lrow = loc + row * LP * 2;       // sampling locations (FUSED: raw sampling offsets)
+        const AT* arow = attn + row * LP;          // attention weights  (FUSED: attention logits)
+        // FUSED: the module prologue (reference ops/modules/ms_deform_attn.py:69-82) in the owner thread:
+        //   attention = softmax over the row's L*P logits, zero for masked queries; location = ref + offset * scale
+        float sm_max = 0.f, sm_inv = 0.f;
+        bool masked = false;
+        const float* rrow = nullptr;
+        if constexpr (FUSED) {
+            rrow = fa.ref + rowq * d.L * fa.ref_dim;
+            masked = fa.qmask != nullptr && row_ok && fa.qmask[rowq] != 0;
+            float mx = -INFINITY;
+            for (int l = 0; l < d.L; ++l) {
+                float lg[kMaxP];
+                LevelIO<AT>::load_attn_only(arow, l, d.P, row_ok, lg);
+#pragma unroll
+                for (int p = 0; p < kMaxP; ++p) if (p < d.P) mx = fmaxf(mx, lg[p]);
+            }
+            float sum = 0.f;
+            for (int l = 0; l < d.L; ++l) {
+                float lg[kMaxP];
+                LevelIO<AT>::load_attn_only(arow, l, d.P, row_ok, lg);
+#pragma unroll
+                for (int p = 0; p < kMaxP; ++p) if (p < d.P) sum += expf(lg[p] - mx);
+            }
+            sm_max = row_ok ? mx : 0.f;
+            sm_inv = row_ok ? 1.f / sum : 0.f;
+        }
+        // raw (offset, logit) of a level's samples -> (location, attention weight); sx / sy = d location / d offset
+        auto prologue = [&](int l, float2 (&xy)[kMaxP], float (&a)[kMaxP], float& sx, float& sy) {
+            sx = sy = 1.f;
+            if constexpr (FUSED) {
+                float rx, ry;
+                if (fa.ref_dim == 2) {
+                    const float2 r = *reinterpret_cast<const float2*>(rrow + l * 2);
+                    const float2 n = *reinterpret_cast<const float2*>(fa.norm + l * 2);
+                    sx = __frcp_rn(n.x); sy = __frcp_rn(n.y);
+                    rx = r.x; ry = r.y;
+                } else {
+                    const float4 r = *reinterpret_cast<const float4*>(rrow + l * 4);
+                    const float hp = 0.5f * __frcp_rn((float)d.P);
+                    sx = r.z * hp; sy = r.w * hp;
+                    rx = r.x; ry = r.y;
+                }
+#pragma unroll
+                for (int p = 0; p < kMaxP; ++p) {
+                    const bool have = row_ok && p < d.P;
+                    xy[p] = have ? make_float2(fmaf(xy[p].x, sx, rx), fmaf(xy[p].y, sy, ry)) : make_float2(-8.f, -8.f);
+                    a[p] = (have && !masked) ? expf(a[p] - sm_max) * sm_inv : 0.f;
+                }
+            }
+        };
 
         // samples of the level being processed next (requested one level ahead)
         float2 nxt_xy[kMaxP];
@@ -299,9 +401,13 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
             float2 xy[kMaxP];
             float aw[kMaxP];
             LevelIO<AT>::load(lrow, arow, l, d.P, row_ok, xy, aw);
-            if (l == 0) {       // the chunk phase starts with level 0: keep its samples
+            if (l == 0) {       // the chunk phase starts with level 0: keep its (raw) samples
 #pragma unroll
                 for (int p = 0; p < kMaxP; ++p) { nxt_xy[p] = xy[p]; nxt_a[p] = aw[p]; }
+            }
+            {
+                float sx, sy;
+                prologue(l, xy, aw, sx, sy);
             }
 #pragma unroll
             for (int p = 0; p < kMaxP; ++p) {
@@ -366,6 +472,7 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
         float* gvbase = grad_value_acc + ((size_t)b * d.S * d.M + m) * D;
         const size_t pix_stride = (size_t)d.M * D;
 
+        float sm_dot = 0.f;
         for (int l = 0; l < d.L; ++l) {
             const int nch = s_win[l][4];
             if (nch == 0) {
@@ -373,6 +480,9 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                 if (row_ok) {
                     const float z[kMaxP] = {0.f, 0.f, 0.f, 0.f};
                     LevelIO<AT>::store(grad_loc + row * LP * 2, grad_attn + row * LP, l, d.P, z, z, z);
+                    if constexpr (FUSED) {
+                        if (fa.grad_loc) LevelIO<float>::store_loc_only(fa.grad_loc + row * LP * 2, l, d.P, z, z);
+                    }
                 }
                 if (l + 1 < d.L) {
                     LevelIO<AT>::load(lrow, arow, l + 1, d.P, row_ok, nxt_xy, nxt_a);
@@ -395,10 +505,12 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
             float acc_a[kMaxP], acc_x[kMaxP], acc_y[kMaxP], att[kMaxP];
             const uint32_t w_col = smem_u32(sW) + (tid >> 3) * P::W_LBO + (tid & 7) * 2;
             const uint32_t st_row = smem_u32(stage);
+            // the level's samples were requested while the previous level was being processed
+            float lev_sx, lev_sy;
+            prologue(l, nxt_xy, nxt_a, lev_sx, lev_sy);
 #pragma unroll
             for (int p = 0; p < kMaxP; ++p) {
                 acc_a[p] = acc_x[p] = acc_y[p] = 0.f;
-                // the level's samples were requested while the previous level was being processed
                 const float2 xy = nxt_xy[p];
                 const float a = nxt_a[p];
                 att[p] = a;
@@ -584,7 +696,31 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                     gx[p] = acc_x[p] * att[p] * (float)W;
                     gy[p] = acc_y[p] * att[p] * (float)H;
                 }
+                if constexpr (FUSED) {
+                    // d / d location kept if asked for (the caller reduces it to d / d reference point)
+                    if (fa.grad_loc) LevelIO<float>::store_loc_only(fa.grad_loc + row * LP * 2, l, d.P, gx, gy);
+#pragma unroll
+                    for (int p = 0; p < kMaxP; ++p) {
+                        gx[p] *= lev_sx; gy[p] *= lev_sy;                     // location = ref + offset * scale
+                        if (masked) acc_a[p] = 0.f;                          // masked_fill(mask, 0): no gradient to the softmax
+                        sm_dot = fmaf(att[p], acc_a[p], sm_dot);             // sum_s prob_s * d out / d attention_s
+                    }
+                }
+                // FUSED: grad_attn holds d out / d attention until the row's softmax backward below
                 LevelIO<AT>::store(grad_loc + row * LP * 2, grad_attn + row * LP, l, d.P, gx, gy, acc_a);
+            }
+        }
+        if constexpr (FUSED) {
+            // softmax backward of the row: d / d logit_s = prob_s * (g_s - sum_t prob_t g_t); g_s were parked in grad_attn
+            if (row_ok) {
+                for (int l = 0; l < d.L; ++l) {
+                    float lg[kMaxP], g[kMaxP];
+                    LevelIO<AT>::load_attn_only(arow, l, d.P, true, lg);
+                    LevelIO<AT>::load_attn_only(grad_attn + row * LP, l, d.P, true, g);
+#pragma unroll
+                    for (int p = 0; p < kMaxP; ++p) g[p] = expf(lg[p] - sm_max) * sm_inv * (g[p] - sm_dot);
+                    LevelIO<AT>::store_attn_only(grad_attn + row * LP, l, d.P, g);
+                }
             }
         }
         // G / Gt / the window table are rewritten by the next item

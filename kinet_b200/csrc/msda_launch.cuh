@@ -265,13 +265,13 @@ inline size_t dense_extra_bytes(const msda_dims* d)
     return kDenseCounterBytes + (((size_t)dense_tiles_bound(d) * d->N * d->M + 255) & ~(size_t)255);
 }
 
-template <typename VT, typename AT, int D>
+template <typename VT, typename AT, int D, bool FUSED>
 int launch_backward_dense(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
                           const void* attn, const void* go, float* gv_acc, void* gl, void* ga, int* claim,
-                          uint8_t* deferred, const msda_dims* d, cudaStream_t st)
+                          uint8_t* deferred, const msda_dims* d, cudaStream_t st, const FusedArgs& fa)
 {
     KernelDims k = make_dims(d, 16, kBackwardTileQ);
-    auto kern = dense::msda_backward_dense_kernel<VT, AT, D, false>;
+    auto kern = dense::msda_backward_dense_kernel<VT, AT, D, FUSED>;
     constexpr int smem = (int)dense::Plan<D>::TOTAL;
     static thread_local int configured_dev = -1;
     int dev = 0;
@@ -288,11 +288,11 @@ int launch_backward_dense(const void* value, const int64_t* shapes, const int64_
     da.tiles_bound = dense_tiles_bound(d);
     TraceScope trace(st);       // the pair of launches is "the backward kernel" of msda_b200_trace_next
     kern<<<2 * sms, dense::kThreads, smem, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                                                 (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, FusedArgs{}, da);
+                                                 (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, da);
     ++g_last_launches;
     if (cudaError_t e = cudaGetLastError()) return (int)e;
     // the queries of the coarser levels, and whatever the dense kernel handed back
-    return launch_backward_vec_impl<VT, AT, 4, D / 4, false>(value, shapes, ls, loc, attn, go, gv_acc, gl, ga, d, st, FusedArgs{},
+    return launch_backward_vec_impl<VT, AT, 4, D / 4, FUSED>(value, shapes, ls, loc, attn, go, gv_acc, gl, ga, d, st, fa,
                                                              deferred, da.tiles_bound, false);
 }
 
@@ -316,7 +316,8 @@ int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, 
     // the work counter (msda_b200_backward_workspace_bytes)
     bool dense_ok = false;
     if constexpr (sizeof(VT) == 2) {
-        dense_ok = !fa && d->Lq == d->S && d->Lq > 0 && d->P <= dense::kMaxP && (d->D == 32 || d->D == 64) &&
+        dense_ok = d->Lq == d->S && d->Lq > 0 && d->P <= dense::kMaxP && (d->D == 32 || d->D == 64) &&
+                   (!fa || d->L * d->P <= kFusedMaxChunks * chunk_of(d->D / 4)) &&     // the per-row kernel's fused limit
                    ws_bytes >= dense_counter_offset(nval) + dense_extra_bytes(d) && aligned16(value) && aligned16(go) &&
                    aligned16(loc) && aligned16(attn) && aligned16(gl) && aligned16(ga) &&
                    env_int("MSDA_B200_DENSE", 1) && !env_int("MSDA_B200_FORCE_GENERIC", 0) && !env_int("MSDA_B200_TILE_1D", 0);
@@ -332,8 +333,13 @@ int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, 
             if (dense_ok) {
                 int* claim = reinterpret_cast<int*>(reinterpret_cast<char*>(ws) + dense_counter_offset(nval));
                 uint8_t* deferred = reinterpret_cast<uint8_t*>(claim) + kDenseCounterBytes;
-                if (d->D == 32) rc = launch_backward_dense<VT, AT, 32>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, deferred, d, st);
-                else rc = launch_backward_dense<VT, AT, 64>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, deferred, d, st);
+                if (fa) {
+                    if (d->D == 32) rc = launch_backward_dense<VT, AT, 32, true>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, deferred, d, st, *fa);
+                    else rc = launch_backward_dense<VT, AT, 64, true>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, deferred, d, st, *fa);
+                } else {
+                    if (d->D == 32) rc = launch_backward_dense<VT, AT, 32, false>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, deferred, d, st, FusedArgs{});
+                    else rc = launch_backward_dense<VT, AT, 64, false>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, deferred, d, st, FusedArgs{});
+                }
                 done = true;
             }
         }

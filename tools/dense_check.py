@@ -47,6 +47,39 @@ def case(name, s, dt, regime, timeit):
     print(msg, flush=True)
 
 
+def fused_case(name, s, dt, ref_dim, masked):
+    """Module-prologue entry point (raw offsets / logits / reference points): dense vs per-row kernels."""
+    from kinet_b200.functions import MSDeformAttnFusedFunction
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device=dev).manual_seed(1)
+    N, S, M, D, L, P, Lq = s["N"], s["S"], s["M"], s["D"], s["L"], s["P"], s["Lq"]
+    value = torch.randn(N, S, M, D, generator=g, device=dev).to(dt)
+    shapes = torch.as_tensor(s["levels"], dtype=torch.int64, device=dev)
+    from kinet_b200.workloads import encoder_reference_points
+    ref = encoder_reference_points(s["levels"], N, dev).contiguous()
+    if ref_dim == 4:
+        wh = torch.rand(N, Lq, L, 2, generator=g, device=dev) * 0.1 + 0.02
+        ref = torch.cat([ref, wh], -1).contiguous()
+    off = (torch.randn(N, Lq, M, L, P, 2, generator=g, device=dev) * 2.0)
+    logit = torch.randn(N, Lq, M, L * P, generator=g, device=dev)
+    mask = (torch.rand(N, Lq, generator=g, device=dev) < 0.1) if masked else None
+    go = torch.randn(N, Lq, M * D, generator=g, device=dev).to(dt)
+    outs = []
+    for dense in (True, False):
+        os.environ["MSDA_B200_DENSE"] = "1" if dense else "0"
+        v = value.clone().requires_grad_(True)
+        r = ref.clone().requires_grad_(True)
+        o = off.clone().requires_grad_(True)
+        lg = logit.clone().requires_grad_(True)
+        out = MSDeformAttnFusedFunction.apply(v, shapes, r, o, lg, mask, shapes, 64)
+        out.backward(go)
+        torch.cuda.synchronize()
+        outs.append((v.grad, o.grad, lg.grad, r.grad))
+    a, b = outs
+    print("%-18s %-8s ref%d mask=%d  gv %.3e  goff %.3e  glogit %.3e  gref %.3e" % (
+        name, str(dt).split(".")[1], ref_dim, int(masked), rel(a[0], b[0]), rel(a[1], b[1]), rel(a[2], b[2]), rel(a[3], b[3])), flush=True)
+
+
 def main():
     timeit = "--time" in sys.argv
     small = dict(levels=[(20, 31), (10, 16), (5, 8), (3, 4)], N=2, M=2, D=32, P=4, encoder=True)
@@ -65,6 +98,11 @@ def main():
         for dt in (torch.bfloat16, torch.float16):
             for regime in ("structured", "uniform"):
                 case(name, s, dt, regime, False)
+    for name, s in (("small", small), ("odd", odd), ("d64", d64)):
+        for dt in (torch.bfloat16, torch.float16):
+            for ref_dim, masked in ((2, False), (2, True), (4, True)):
+                fused_case(name, s, dt, ref_dim, masked)
+    fused_case("C2_enc", resolve("C2_enc"), torch.bfloat16, 2, False)
     for mc in [int(x) for x in os.environ.get("SWEEP_MAXCH", "5").split(",")]:
         os.environ["MSDA_B200_DENSE_MAXCH"] = str(mc)
         print("max level chunks", mc)
