@@ -44,6 +44,8 @@ const char* msda_b200_error_string(int code)
 
 int msda_b200_last_launch_count(void) { return g_last_launches; }
 
+
+
 void msda_b200_trace_next(void* start_event, void* stop_event)
 {
     g_trace_start = (cudaEvent_t)start_event;

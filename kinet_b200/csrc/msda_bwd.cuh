@@ -232,8 +232,10 @@ __device__ __forceinline__ void backward_rows(const LevelTable& lt, int2* stage_
 //
 // Split mode (deferred != nullptr; the dense-window kernel of msda_dense.cuh ran before on the same stream): the
 // queries of the finest level belong to the dense kernel, which flags the (tile, batch, head) items it did not do
-// (windows too large for its chunks).  This kernel then processes (1) the walk items without the finest level's
-// queries and (2) the flagged tiles, shared by tile_ctas extra CTAs at the end of the grid.
+// (windows too large for its chunks).  This kernel is then a persistent grid that claims, from a zero-initialised
+// counter, (1) chunks of tile_q walk positions of the OTHER levels' queries and (2) the flagged tiles.  (The host
+// does not know where the finest level's queries start -- the shapes live in device memory -- so it cannot size a
+// one-item-per-CTA grid for them.)
 template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE, bool FUSED>
 __device__ __forceinline__ void backward_items(const LevelTable& lt, const FineTiles& ft, int2* stage_a, int* stage_dx,
                                                float4* stage_b, float4* fold,
@@ -242,16 +244,49 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, const FineT
                                                const VT* __restrict__ grad_out,
                                                float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
                                                AT* __restrict__ grad_attn, const KernelDims& d, const FusedArgs& fa,
-                                               const uint8_t* __restrict__ deferred, int tile_ctas)
+                                               const uint8_t* __restrict__ deferred, int* __restrict__ split_claim, int* s_claim)
 {
-    const int chunks = (d.Lq + d.tile_q - 1) / d.tile_q;
-    const int walk_items = chunks * d.N * d.M;
-    const bool split = deferred != nullptr && ft.level >= 0;
-    if (deferred != nullptr && (int)blockIdx.x >= walk_items) {
-        // the last tile_ctas CTAs of the grid share the tile items (normally none is flagged: a few byte loads each)
-        if (!split) return;
-        const int tile_items = ft.total * d.N * d.M;
-        for (int it = blockIdx.x - walk_items; it < tile_items; it += tile_ctas) {
+    if (deferred == nullptr) {
+        const int chunks = (d.Lq + d.tile_q - 1) / d.tile_q;
+        const int items = chunks * d.N * d.M;
+        for (int item = blockIdx.x; item < items; item += gridDim.x) {
+            const int chunk = item / (d.N * d.M);
+            const int bm = item - chunk * (d.N * d.M);
+            const int b = bm / d.M, m = bm - b * d.M;
+            const int pos0 = chunk * d.tile_q;
+            const int count = min(d.tile_q, d.Lq - pos0);
+            backward_rows<VT, AT, VEC, GS, NWARPS, WIDE, FUSED>(
+                lt, stage_a, stage_dx, stage_b, fold, value, loc, attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa,
+                b, m, count, [&](int i) { return walk_query(lt, d, pos0 + i); });
+        }
+        return;
+    }
+    const bool split = ft.level >= 0;
+    // walk positions and queries of a level share one index range: the positions outside [q_begin, q_end)
+    const int skip_begin = split ? ft.q_begin : d.Lq, skip_len = split ? ft.q_end - ft.q_begin : 0;
+    const int coarse = d.Lq - skip_len;
+    const int walk_items = ((coarse + d.tile_q - 1) / d.tile_q) * d.N * d.M;
+    const int tile_items = split ? ft.total * d.N * d.M : 0;
+    for (;;) {
+        if (threadIdx.x == 0) *s_claim = atomicAdd(split_claim, 1);
+        __syncthreads();
+        const int item = *s_claim;
+        __syncthreads();
+        if (item >= walk_items + tile_items) break;
+        if (item < walk_items) {
+            const int chunk = item / (d.N * d.M);
+            const int bm = item - chunk * (d.N * d.M);
+            const int b = bm / d.M, m = bm - b * d.M;
+            const int c0 = chunk * d.tile_q;
+            const int count = min(d.tile_q, coarse - c0);
+            backward_rows<VT, AT, VEC, GS, NWARPS, WIDE, FUSED>(
+                lt, stage_a, stage_dx, stage_b, fold, value, loc, attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa,
+                b, m, count, [&](int i) {
+                    const int c = c0 + i;
+                    return walk_query(lt, d, c < skip_begin ? c : c + skip_len);
+                });
+        } else {
+            const int it = item - walk_items;
             if (deferred[it] == 0) continue;
             const int tile = it / (d.N * d.M);
             const int bm = it - tile * (d.N * d.M);
@@ -260,25 +295,6 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, const FineT
             backward_rows<VT, AT, VEC, GS, NWARPS, WIDE, FUSED>(
                 lt, stage_a, stage_dx, stage_b, fold, value, loc, attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa,
                 b, m, kTileQueries, [&](int i) { return fine_tile_query(ft, lt, r, i, d.Lq); });
-        }
-        return;
-    }
-    const int items = walk_items;
-    for (int item = blockIdx.x; item < items; item += gridDim.x) {
-        {
-            const int chunk = item / (d.N * d.M);
-            const int bm = item - chunk * (d.N * d.M);
-            const int b = bm / d.M, m = bm - b * d.M;
-            const int pos0 = chunk * d.tile_q;
-            const int count = min(d.tile_q, d.Lq - pos0);
-            // walk positions and queries of a level share one index range
-            if (split && pos0 >= ft.q_begin && pos0 + count <= ft.q_end) continue;
-            backward_rows<VT, AT, VEC, GS, NWARPS, WIDE, FUSED>(
-                lt, stage_a, stage_dx, stage_b, fold, value, loc, attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa,
-                b, m, count, [&](int i) {
-                    const int q = walk_query(lt, d, pos0 + i);
-                    return (split && q >= ft.q_begin && q < ft.q_end) ? -1 : q;
-                });
         }
     }
 }
@@ -290,11 +306,11 @@ msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ s
                      const AT* __restrict__ attn, const VT* __restrict__ grad_out,
                      float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
                      AT* __restrict__ grad_attn, const KernelDims d, const FusedArgs fa,
-                     const uint8_t* __restrict__ deferred, int tiles_bound, int tile_ctas)
+                     const uint8_t* __restrict__ deferred, int tiles_bound, int* __restrict__ split_claim)
 {
     __shared__ LevelTable lt;
     __shared__ FineTiles ft;
-    __shared__ int ft_scratch;
+    __shared__ int ft_scratch, s_claim;
     stage_levels(lt, shapes, level_start, d);
     if (deferred != nullptr) build_fine_tiles(ft, &ft_scratch, lt, d.L, tiles_bound);
     __shared__ int2 stage_a[NWARPS][record_count(GS)];
@@ -305,10 +321,10 @@ msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ s
     const int warp = threadIdx.x >> 5;
     if (lt.min_w > 1)
         backward_items<VT, AT, VEC, GS, NWARPS, true, FUSED>(lt, ft, stage_a[warp], stage_dx[warp], stage_b[warp], fold[warp], value, loc,
-                                                             attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa, deferred, tile_ctas);
+                                                             attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa, deferred, split_claim, &s_claim);
     else
         backward_items<VT, AT, VEC, GS, NWARPS, false, FUSED>(lt, ft, stage_a[warp], stage_dx[warp], stage_b[warp], fold[warp], value, loc,
-                                                              attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa, deferred, tile_ctas);
+                                                              attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa, deferred, split_claim, &s_claim);
 }
 
 // fp32 workspace -> 16-bit grad_value (one rounding of the full sum).

@@ -40,6 +40,19 @@
 namespace msda {
 namespace dense {
 
+// Development aid (-DMSDA_DENSE_TIMING): thread 0 of every CTA accumulates the cycles between phase marks and adds
+// them to dense_phase_cycles[] at kernel end (read back with msda_b200_debug_dense_phase_cycles).
+#ifdef MSDA_DENSE_TIMING
+__device__ unsigned long long dense_phase_cycles[16];
+#define DT_DECL long long dt_last = clock64(); unsigned long long dt_acc[16] = {0};
+#define DT_MARK(i) { if (threadIdx.x == 0) { const long long t_ = clock64(); dt_acc[i] += (unsigned long long)(t_ - dt_last); dt_last = t_; } }
+#define DT_FLUSH { if (threadIdx.x == 0) for (int i_ = 0; i_ < 16; ++i_) atomicAdd(&dense_phase_cycles[i_], dt_acc[i_]); }
+#else
+#define DT_DECL
+#define DT_MARK(i)
+#define DT_FLUSH
+#endif
+
 constexpr int kThreads = 128;        // = query rows per item = TMEM lanes
 constexpr int kPix = 128;            // window pixels per chunk (MMA M of the scatter product, N of the dot product)
 constexpr int kMaxItemChunks = 32;   // beyond this the per-row path is cheaper
@@ -127,7 +140,8 @@ template <int D> struct Plan {
     static constexpr uint32_t T_LBO = 144, T_SBO = 16 * 144 + 16, T_BYTES = (D / 8) * T_SBO;
     static constexpr int STAGE_STRIDE = 68;                 // floats per thread-private staging row (64 + 4: conflict-free 16-byte stores)
     static constexpr uint32_t STAGE_BYTES = kThreads * STAGE_STRIDE * 4;
-    static constexpr uint32_t OFF_G = 0, OFF_V = OFF_G + G_BYTES, OFF_W = OFF_V + G_BYTES, OFF_T = OFF_W + W_BYTES,
+    // (two V buffers: the next chunk's value rows are fetched with cp.async while the current chunk is processed)
+    static constexpr uint32_t OFF_G = 0, OFF_V = OFF_G + G_BYTES, OFF_W = OFF_V + 2 * G_BYTES, OFF_T = OFF_W + W_BYTES,
                               OFF_STAGE = OFF_T + T_BYTES, TOTAL = OFF_STAGE + STAGE_BYTES;
 };
 
@@ -323,7 +337,9 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
     constexpr uint32_t idesc_gv = umma_idesc(128, D, O::fmt);
 
     int slot = 0;
+    DT_DECL
     for (int item = s_item[0]; item < items; item = s_item[slot]) {
+        DT_MARK(0)
         // claim the next item now; it is read after the barrier that ends this one
         if (tid == 0) s_item[slot ^ 1] = atomicAdd(da.claim, 1);
         slot ^= 1;
@@ -392,35 +408,44 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
         // samples of the level being processed next (requested one level ahead)
         float2 nxt_xy[kMaxP];
         float nxt_a[kMaxP];
+        DT_MARK(1)
         // ---- windows: bounding box of the live corner pixels, per level ---------------------------------------------
         // (a corner is live when its pixel exists: the reference's guarded corner loads, .cuh:36-60, and the open
         // sample window -1 < x < W, :229)
-        for (int l = 0; l < d.L; ++l) {
-            const int H = lt.H[l], W = lt.W[l];
-            int ymin = 1 << 30, ymax = -1, xmin = 1 << 30, xmax = -1;
-            float2 xy[kMaxP];
-            float aw[kMaxP];
-            LevelIO<AT>::load(lrow, arow, l, d.P, row_ok, xy, aw);
-            if (l == 0) {       // the chunk phase starts with level 0: keep its (raw) samples
+        // the loads of four levels are issued before the first use (one memory round trip per group, not per level)
+        for (int l0 = 0; l0 < d.L; l0 += 4) {
+            float2 bxy[4][kMaxP];
+            float baw[4][kMaxP];
 #pragma unroll
-                for (int p = 0; p < kMaxP; ++p) { nxt_xy[p] = xy[p]; nxt_a[p] = aw[p]; }
-            }
-            {
-                float sx, sy;
-                prologue(l, xy, aw, sx, sy);
+            for (int j = 0; j < 4; ++j) LevelIO<AT>::load(lrow, arow, min(l0 + j, d.L - 1), d.P, row_ok && l0 + j < d.L, bxy[j], baw[j]);
+            if (l0 == 0) {      // the chunk phase starts with level 0: keep its (raw) samples
+#pragma unroll
+                for (int p = 0; p < kMaxP; ++p) { nxt_xy[p] = bxy[0][p]; nxt_a[p] = baw[0][p]; }
             }
 #pragma unroll
-            for (int p = 0; p < kMaxP; ++p) {
-                const float x = fmaf(xy[p].x, (float)W, -0.5f), y = fmaf(xy[p].y, (float)H, -0.5f);
-                if ((y > -1.f) && (x > -1.f) && (y < (float)H) && (x < (float)W)) {
-                    const int iy = (int)floorf(y), ix = (int)floorf(x);
-                    ymin = min(ymin, max(iy, 0)); ymax = max(ymax, min(iy + 1, H - 1));
-                    xmin = min(xmin, max(ix, 0)); xmax = max(xmax, min(ix + 1, W - 1));
+            for (int j = 0; j < 4; ++j) {
+                const int l = l0 + j;
+                if (l < d.L) {
+                    const int H = lt.H[l], W = lt.W[l];
+                    int ymin = 1 << 30, ymax = -1, xmin = 1 << 30, xmax = -1;
+                    {
+                        float sx, sy;
+                        prologue(l, bxy[j], baw[j], sx, sy);
+                    }
+#pragma unroll
+                    for (int p = 0; p < kMaxP; ++p) {
+                        const float x = fmaf(bxy[j][p].x, (float)W, -0.5f), y = fmaf(bxy[j][p].y, (float)H, -0.5f);
+                        if ((y > -1.f) && (x > -1.f) && (y < (float)H) && (x < (float)W)) {
+                            const int iy = (int)floorf(y), ix = (int)floorf(x);
+                            ymin = min(ymin, max(iy, 0)); ymax = max(ymax, min(iy + 1, H - 1));
+                            xmin = min(xmin, max(ix, 0)); xmax = max(xmax, min(ix + 1, W - 1));
+                        }
+                    }
+                    ymin = __reduce_min_sync(0xffffffffu, ymin); ymax = __reduce_max_sync(0xffffffffu, ymax);
+                    xmin = __reduce_min_sync(0xffffffffu, xmin); xmax = __reduce_max_sync(0xffffffffu, xmax);
+                    if (lane == 0) { s_box[warp][l][0] = ymin; s_box[warp][l][1] = ymax; s_box[warp][l][2] = xmin; s_box[warp][l][3] = xmax; }
                 }
             }
-            ymin = __reduce_min_sync(0xffffffffu, ymin); ymax = __reduce_max_sync(0xffffffffu, ymax);
-            xmin = __reduce_min_sync(0xffffffffu, xmin); xmax = __reduce_max_sync(0xffffffffu, xmax);
-            if (lane == 0) { s_box[warp][l][0] = ymin; s_box[warp][l][1] = ymax; s_box[warp][l][2] = xmin; s_box[warp][l][3] = xmax; }
         }
         __syncthreads();
         if (tid < d.L) {
@@ -448,6 +473,27 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
             continue;
         }
 
+        // The next item's rows (sampling locations, attention weights, grad_out) are requested into L2 now: its window
+        // search and its operand staging would otherwise start with a trip to DRAM (the claim made at the top of this
+        // item became visible with the barriers above).
+        {
+            const int nitem = s_item[slot];
+            if (nitem < items) {
+                const int ntile = nitem / (d.N * d.M);
+                const int nbm = nitem - ntile * (d.N * d.M);
+                const int nb = nbm / d.M, nm = nbm - nb * d.M;
+                const TileRect nrect = fine_tile_rect(ft, lt, ntile);
+                const int nq = fine_tile_query(ft, lt, nrect, tid, d.Lq);
+                if (nq >= 0) {
+                    const size_t nrow = ((size_t)nb * d.Lq + nq) * d.M + nm;
+                    asm volatile("prefetch.global.L2 [%0];" :: "l"(loc + nrow * LP * 2));
+                    if (LP * 2 * sizeof(AT) > 128) asm volatile("prefetch.global.L2 [%0];" :: "l"(reinterpret_cast<const char*>(loc + nrow * LP * 2) + 128));
+                    asm volatile("prefetch.global.L2 [%0];" :: "l"(attn + nrow * LP));
+                    asm volatile("prefetch.global.L2 [%0];" :: "l"(grad_out + nrow * D));
+                }
+            }
+        }
+        DT_MARK(2)
         // ---- G: the item's rows of grad_out -> operand A of the dot product, and transposed -> operand B of the scatter
         // product.  D / 8 lanes per row (16 bytes each): a warp instruction reads 32 / (D / 8) whole rows.
         constexpr int LPRV = P::KCH, RPIV = 32 / LPRV;
@@ -496,12 +542,14 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
             // tr   = window-linear pixel index of the corner (kNone: the corner's pixel does not exist / no sample)
             // wa   = byte address of the target's W element inside a chunk (column `tid`)
             // tw   = bilinear x attention weight (scatter product)
-            // cga / cgx / cgy = coefficients of <grad_out, corner> in grad_attn / d sample / d x / d sample / d y
+            // cga  = bilinear weight: coefficient of <grad_out, corner> in grad_attn (those of d / dx, d / dy are the
+            //        sample's row / column weights with a sign)
             constexpr int NT = 4 * kMaxP;
             constexpr int kNone = -(1 << 20);
             int tr[NT];
             uint32_t wa[NT];
-            float tw[NT], cga[NT], cgx[NT], cgy[NT];
+            float tw[NT], cga[NT];
+            float swy[kMaxP][2], swx[kMaxP][2];     // per-sample row / column weights (their derivatives are -1 / +1)
             float acc_a[kMaxP], acc_x[kMaxP], acc_y[kMaxP], att[kMaxP];
             const uint32_t w_col = smem_u32(sW) + (tid >> 3) * P::W_LBO + (tid & 7) * 2;
             const uint32_t st_row = smem_u32(stage);
@@ -531,47 +579,58 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                     tr[t] = live ? r : kNone;
                     const int idx = r & (kPix - 1);
                     wa[t] = w_col + (idx & 7) * 16 + (idx >> 3) * P::W_SBO;
-                    cga[t] = live ? wy[cy] * wx[cx] : 0.f;
+                    // (dead corners never match a chunk: their weights need no zeroing)
+                    cga[t] = wy[cy] * wx[cx];
                     tw[t] = cga[t] * a;
-                    // one-sided derivatives of the bilinear weights (.cuh:141-160): -1 / +1 for the lower / upper pixel
-                    cgx[t] = live ? (cx ? wy[cy] : -wy[cy]) : 0.f;
-                    cgy[t] = live ? (cy ? wx[cx] : -wx[cx]) : 0.f;
                 }
+                swy[p][0] = wy[0]; swy[p][1] = wy[1]; swx[p][0] = wx[0]; swx[p][1] = wx[1];
             }
             // request the next level's samples now
             if (l + 1 < d.L) {
                 LevelIO<AT>::load(lrow, arow, l + 1, d.P, row_ok, nxt_xy, nxt_a);
             }
-
             // window coordinates of this thread's pixel of the current chunk, advanced incrementally
-            int pwy = tid / ww, pwx = tid - pwy * ww;
-            const int step_y = kPix / ww, step_x = kPix - step_y * ww;
+            // (r / ww for r < 2^16 through the reciprocal: exact with the half-pixel offset)
+            const float inv_ww = 1.f / (float)ww;
+            int pwy = (int)(((float)tid + 0.5f) * inv_ww), pwx = tid - pwy * ww;
+            const int step_y = (int)(((float)kPix + 0.5f) * inv_ww), step_x = kPix - step_y * ww;
             int vwy[LPRV], vwx[LPRV];       // ... and of the pixels whose value rows this thread fetches
 #pragma unroll
             for (int i = 0; i < LPRV; ++i) {
                 const int r = warp * 32 + i * RPIV + lane / LPRV;
-                vwy[i] = r / ww;
+                vwy[i] = (int)(((float)r + 0.5f) * inv_ww);
                 vwx[i] = r - vwy[i] * ww;
             }
 
+            // value rows of chunk kk -> V buffer kk & 1 (operand B of the dot product): D / 8 lanes per pixel row, 16 bytes
+            // each, global -> shared without passing through registers; rows beyond the window are zero-filled
+            auto fetch_values = [&](int kk) {
+                uint8_t* vb = sV + (kk & 1) * P::G_BYTES;
+#pragma unroll
+                for (int i = 0; i < LPRV; ++i) {
+                    const int trow = warp * 32 + i * RPIV + lane / LPRV;
+                    const bool ok = kk * kPix + trow < npix;
+                    const size_t vp = ok ? (size_t)lt.start[l] + (size_t)(ymin + vwy[i]) * W + (xmin + vwx[i]) : 0;
+                    const uint32_t dst = smem_u32(vb + (trow & 7) * 16 + (trow >> 3) * P::G_SBO + (lane % LPRV) * P::G_LBO);
+                    const void* src = reinterpret_cast<const uint4*>(vbase + vp * pix_stride) + lane % LPRV;
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(ok ? 16 : 0) : "memory");
+                    vwy[i] += step_y; vwx[i] += step_x;
+                    if (vwx[i] >= ww) { vwx[i] -= ww; ++vwy[i]; }
+                }
+                asm volatile("cp.async.commit_group;" ::: "memory");
+            };
+            fetch_values(0);
+
             for (int k = 0; k < nch; ++k) {
                 const int r0 = k * kPix;
-                // (a) the chunk's value rows -> registers, D / 8 lanes per pixel row (16 bytes each)
+                DT_MARK(3)
+                // (a) this thread's window pixel (the epilogue's TMEM lane); the NEXT chunk's value rows start moving
                 const bool pix_ok = r0 + tid < npix;
                 const size_t pix = (size_t)lt.start[l] + (size_t)(ymin + pwy) * W + (xmin + pwx);
                 pwy += step_y; pwx += step_x;
                 if (pwx >= ww) { pwx -= ww; ++pwy; }
-                uint4 v4[LPRV];
-#pragma unroll
-                for (int i = 0; i < LPRV; ++i) {
-                    v4[i] = make_uint4(0, 0, 0, 0);
-                    if (r0 + warp * 32 + i * RPIV + lane / LPRV < npix) {
-                        const size_t vp = (size_t)lt.start[l] + (size_t)(ymin + vwy[i]) * W + (xmin + vwx[i]);
-                        v4[i] = __ldg(reinterpret_cast<const uint4*>(vbase + vp * pix_stride) + lane % LPRV);
-                    }
-                    vwy[i] += step_y; vwx[i] += step_x;
-                    if (vwx[i] >= ww) { vwx[i] -= ww; ++vwy[i]; }
-                }
+                if (k + 1 < nch) fetch_values(k + 1);
+                DT_MARK(4)
                 // (b) densify: column `tid` of W gets this row's corner weights that fall into the chunk.  The four
                 // corners of one sample are distinct pixels: four independent read-modify-writes; corners of
                 // different samples may coincide, so the samples go one after the other.
@@ -595,22 +654,22 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                         }
                     }
                 }
-                // (c) value rows -> operand B of the dot product
-#pragma unroll
-                for (int i = 0; i < LPRV; ++i) {
-                    const int trow = warp * 32 + i * RPIV + lane / LPRV;
-                    *reinterpret_cast<uint4*>(sV + (trow & 7) * 16 + (trow >> 3) * P::G_SBO + (lane % LPRV) * P::G_LBO) = v4[i];
-                }
+                DT_MARK(5)
+                // (c) this chunk's value rows (operand B of the dot product) have landed
+                if (k + 1 < nch) asm volatile("cp.async.wait_group 1;" ::: "memory");
+                else asm volatile("cp.async.wait_group 0;" ::: "memory");
+                DT_MARK(6)
                 // (d) operands visible to the tensor core; TMEM reads of the previous chunk are complete
                 proxy_fence();
                 tmem_fence_before();
                 __syncthreads();
+                DT_MARK(7)
                 // (e) one thread issues both products; the dot products are committed first so that the picks
                 // below overlap the scatter product
                 if (tid == 0) {
                     tmem_fence_after();
                     const uint64_t dg = umma_desc(smem_u32(sG), P::G_LBO, P::G_SBO);
-                    const uint64_t dv = umma_desc(smem_u32(sV), P::G_LBO, P::G_SBO);
+                    const uint64_t dv = umma_desc(smem_u32(sV) + (k & 1) * P::G_BYTES, P::G_LBO, P::G_SBO);
 #pragma unroll
                     for (int j = 0; j < D / 16; ++j)
                         umma(tmem_u, dg + (uint64_t)(j * 2 * P::G_LBO / 16), dv + (uint64_t)(j * 2 * P::G_LBO / 16), idesc_u, j > 0);
@@ -622,9 +681,11 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                         umma(tmem_gv, dw + (uint64_t)(j * 2 * P::W_LBO / 16), dt + (uint64_t)(j * 2 * P::T_LBO / 16), idesc_gv, j > 0);
                     umma_commit(mbar2);
                 }
+                DT_MARK(8)
                 // (f) dot products ready
                 mbar_wait(mbar, phase);
                 tmem_fence_after();
+                DT_MARK(9)
                 // (g) this row's 128 columns -> private staging row (64 at a time) -> pick the corners of this chunk
 #pragma unroll 1
                 for (int half = 0; half < 2; ++half) {
@@ -643,16 +704,20 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                     for (int t = 0; t < NT; ++t) {
                         float u = 0.f;
                         if ((tr[t] >> 6) == want) asm volatile("ld.shared.f32 %0, [%1];" : "=f"(u) : "r"(st_row + (tr[t] & 63) * 4) : "memory");
+                        // one-sided derivatives of the bilinear weights (.cuh:141-160): -1 / +1 for the lower / upper pixel
+                        const int cy = (t >> 1) & 1, cx = t & 1;
                         acc_a[t >> 2] = fmaf(cga[t], u, acc_a[t >> 2]);
-                        acc_x[t >> 2] = fmaf(cgx[t], u, acc_x[t >> 2]);
-                        acc_y[t >> 2] = fmaf(cgy[t], u, acc_y[t >> 2]);
+                        acc_x[t >> 2] = fmaf(cx ? swy[t >> 2][cy] : -swy[t >> 2][cy], u, acc_x[t >> 2]);
+                        acc_y[t >> 2] = fmaf(cy ? swx[t >> 2][cx] : -swx[t >> 2][cx], u, acc_y[t >> 2]);
                     }
                 }
+                DT_MARK(10)
                 // (h) the item's contribution to the chunk's grad_value rows: TMEM lane = window pixel r0 + tid
                 mbar_wait(mbar2, phase);
                 phase ^= 1;
                 tmem_fence_after();
-                {
+                DT_MARK(11)
+                if (r0 + warp * 32 < npix) {         // (warp-uniform) this warp's 32 pixel rows exist
                     float gv[D];
 #pragma unroll
                     for (int c0 = 0; c0 < D; c0 += 32) tmem_ld32(tmem_gv + lane_sel + c0, *reinterpret_cast<float(*)[32]>(&gv[c0]));
@@ -681,12 +746,14 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                     }
                     __syncwarp();
                 }
+                DT_MARK(12)
                 // (i) restore the zeros of W
 #pragma unroll
                 for (int t = 0; t < NT; ++t)
                     if ((tr[t] >> 7) == k) asm volatile("st.shared.u16 [%0], %1;" :: "r"(wa[t]), "h"((uint16_t)0) : "memory");
             }
 
+            DT_MARK(13)
             // ---- the level's samples are complete: gradients of the sampling locations and attention weights ----
             if (row_ok) {
                 float gx[kMaxP], gy[kMaxP];
@@ -728,6 +795,8 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
         __syncthreads();
     }
 
+    DT_MARK(14)
+    DT_FLUSH
     tmem_fence_before();
     __syncthreads();
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(s_tmem), "r"((uint32_t)kTmemCols));

@@ -204,21 +204,23 @@ template <typename VT, typename AT, int VEC, int GS, bool FUSED>
 int launch_backward_vec_impl(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
                              const void* attn, const void* go, float* gv_acc, void* gl, void* ga,
                              const msda_dims* d, cudaStream_t st, const FusedArgs& fa,
-                             const uint8_t* deferred = nullptr, int tiles_bound = 0, bool traced = true)
+                             const uint8_t* deferred = nullptr, int tiles_bound = 0, bool traced = true,
+                             int* split_claim = nullptr)
 {
     constexpr int NW = 8;
-    const KernelDims k = make_dims(d, NW * (32 / GS), kBackwardTileQ);
+    KernelDims k = make_dims(d, NW * (32 / GS), kBackwardTileQ);
     auto kern = msda_backward_kernel<VT, AT, VEC, GS, NW, FUSED>;
     const int sms = device_info().sms > 0 ? device_info().sms : 148;
-    const int tile_ctas = deferred ? 2 * sms : 0;
-    const int grid = item_grid(k) + tile_ctas;
+    // split mode: a persistent grid claims (64-row chunks of the coarse levels' queries, then the flagged tiles)
+    if (deferred) k.tile_q = 64 / (NW * (32 / GS)) * (NW * (32 / GS)) > 0 ? 64 / (NW * (32 / GS)) * (NW * (32 / GS)) : NW * (32 / GS);
+    const int grid = deferred ? MSDA_BWD_MINB * sms : item_grid(k);
     if (traced) {
         TraceScope trace(st);
         kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, deferred, tiles_bound, tile_ctas);
+                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, deferred, tiles_bound, split_claim);
     } else {
         kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, deferred, tiles_bound, tile_ctas);
+                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, deferred, tiles_bound, split_claim);
     }
     ++g_last_launches;
     return (int)cudaGetLastError();
@@ -286,14 +288,14 @@ int launch_backward_dense(const void* value, const int64_t* shapes, const int64_
     da.claim = claim;
     da.deferred = deferred;
     da.tiles_bound = dense_tiles_bound(d);
-    TraceScope trace(st);       // the pair of launches is "the backward kernel" of msda_b200_trace_next
+    TraceScope trace(st);       // the group of launches is "the backward kernel" of msda_b200_trace_next
     kern<<<2 * sms, dense::kThreads, smem, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
                                                  (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, da);
     ++g_last_launches;
     if (cudaError_t e = cudaGetLastError()) return (int)e;
     // the queries of the coarser levels, and whatever the dense kernel handed back
     return launch_backward_vec_impl<VT, AT, 4, D / 4, FUSED>(value, shapes, ls, loc, attn, go, gv_acc, gl, ga, d, st, fa,
-                                                             deferred, da.tiles_bound, false);
+                                                             deferred, da.tiles_bound, false, claim + 1);
 }
 
 // VT = float: gradients accumulate straight into grad_value (zero-filled first).
