@@ -161,11 +161,19 @@ __device__ __forceinline__ void backward_rows(const LevelTable& lt, int2* stage_
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
                         if (bw[c] != 0.f) {
-                            float* dst = gv_base + (size_t)o[c] * VEC;
+                            if (sizeof(VT) == 2 && d.acc16) {
+                                // sparse query sets (~1 contribution per pixel row): straight into the 16-bit output
+                                VT* dst = reinterpret_cast<VT*>(grad_value_acc) + bbase + (size_t)o[c] * VEC;
 #pragma unroll
-                            for (int k = 0; k < VEC; k += 4)
-                                red_add_f32x4(dst + k, bw[c] * g[k], bw[c] * g[k + 1], bw[c] * g[k + 2],
-                                              bw[c] * g[k + 3]);
+                                for (int k = 0; k < VEC; k += 4)
+                                    red_add_16x4<VT>(dst + k, bw[c] * g[k], bw[c] * g[k + 1], bw[c] * g[k + 2], bw[c] * g[k + 3]);
+                            } else {
+                                float* dst = gv_base + (size_t)o[c] * VEC;
+#pragma unroll
+                                for (int k = 0; k < VEC; k += 4)
+                                    red_add_f32x4(dst + k, bw[c] * g[k], bw[c] * g[k + 1], bw[c] * g[k + 2],
+                                                  bw[c] * g[k + 3]);
+                            }
                         }
                     }
                 }

@@ -37,6 +37,7 @@ struct KernelDims {
     int N, S, M, D, L, Lq, P;
     int tile_q;   // query rows per work item
     int band_h;   // encoder form (Lq == S): rows of a band of the band-ordered query walk; 0: plain query order
+    int acc16;    // backward, 16-bit values: grad_value_acc IS the 16-bit grad_value; packed 16-bit reductions (sparse query sets)
 };
 
 // Fills the level table (all threads call; ends with __syncthreads()).
@@ -255,6 +256,18 @@ __device__ __forceinline__ void red_add_f32x4(float* p, float a, float b, float 
     asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1,%2,%3,%4};"
                  :: "l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
+
+// Packed 16-bit reductions (sm_90+): 8 bytes = 4 channels per instruction, straight into a bf16 / f16 tensor.
+template <typename T> __device__ __forceinline__ void red_add_16x4(T* p, float a, float b, float c, float d);
+template <> __device__ __forceinline__ void red_add_16x4<__nv_bfloat16>(__nv_bfloat16* p, float a, float b, float c, float d) {
+    asm volatile("red.relaxed.gpu.global.add.noftz.v2.bf16x2 [%0], {%1,%2};"
+                 :: "l"(p), "r"(pack_bf16x2(a, b)), "r"(pack_bf16x2(c, d)) : "memory");
+}
+template <> __device__ __forceinline__ void red_add_16x4<__half>(__half* p, float a, float b, float c, float d) {
+    asm volatile("red.relaxed.gpu.global.add.noftz.v2.f16x2 [%0], {%1,%2};"
+                 :: "l"(p), "r"(pack_f16x2(a, b)), "r"(pack_f16x2(c, d)) : "memory");
+}
+template <> __device__ __forceinline__ void red_add_16x4<float>(float*, float, float, float, float) {}
 
 // Streaming scalar loads of the per-sample metadata (read exactly once).
 template <typename A> __device__ __forceinline__ float2 load_loc(const A* p);

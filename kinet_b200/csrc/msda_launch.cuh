@@ -82,6 +82,7 @@ inline KernelDims make_dims(const msda_dims* d, int rows_per_pass, int default_t
 {
     KernelDims k;
     k.N = d->N; k.S = d->S; k.M = d->M; k.D = d->D; k.L = d->L; k.Lq = d->Lq; k.P = d->P;
+    k.acc16 = 0;
     const int sms = device_info().sms > 0 ? device_info().sms : 148;
     k.band_h = (d->Lq == d->S && !env_int("MSDA_B200_TILE_1D", 0)) ? env_int("MSDA_B200_TILE_H", 8) : 0;
     if (k.band_h < 0) k.band_h = 0;
@@ -205,10 +206,11 @@ int launch_backward_vec_impl(const void* value, const int64_t* shapes, const int
                              const void* attn, const void* go, float* gv_acc, void* gl, void* ga,
                              const msda_dims* d, cudaStream_t st, const FusedArgs& fa,
                              const uint8_t* deferred = nullptr, int tiles_bound = 0, bool traced = true,
-                             int* split_claim = nullptr)
+                             int* split_claim = nullptr, bool acc16 = false)
 {
     constexpr int NW = 8;
     KernelDims k = make_dims(d, NW * (32 / GS), kBackwardTileQ);
+    k.acc16 = acc16 ? 1 : 0;
     auto kern = msda_backward_kernel<VT, AT, VEC, GS, NW, FUSED>;
     const int sms = device_info().sms > 0 ? device_info().sms : 148;
     // split mode: a persistent grid claims (64-row chunks of the coarse levels' queries, then the flagged tiles)
@@ -229,14 +231,15 @@ int launch_backward_vec_impl(const void* value, const int64_t* shapes, const int
 template <typename VT, typename AT, int VEC, int GS>
 int launch_backward_vec(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
                         const void* attn, const void* go, float* gv_acc, void* gl, void* ga,
-                        const msda_dims* d, cudaStream_t st, const FusedArgs* fa)
+                        const msda_dims* d, cudaStream_t st, const FusedArgs* fa, bool acc16 = false)
 {
     if (fa) {
         if (d->L * d->P > kFusedMaxChunks * chunk_of(GS)) return MSDA_E_SHAPE;   // a lane keeps <= 4 samples of a row in registers
-        return launch_backward_vec_impl<VT, AT, VEC, GS, true>(value, shapes, ls, loc, attn, go, gv_acc, gl, ga, d, st, *fa);
+        return launch_backward_vec_impl<VT, AT, VEC, GS, true>(value, shapes, ls, loc, attn, go, gv_acc, gl, ga, d, st, *fa,
+                                                               nullptr, 0, true, nullptr, acc16);
     }
     return launch_backward_vec_impl<VT, AT, VEC, GS, false>(value, shapes, ls, loc, attn, go, gv_acc, gl, ga, d, st,
-                                                            FusedArgs{});
+                                                            FusedArgs{}, nullptr, 0, true, nullptr, acc16);
 }
 
 template <typename VT, typename AT, typename ACC>
@@ -254,6 +257,16 @@ int launch_backward_generic(const void* value, const int64_t* shapes, const int6
                                (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k);
     ++g_last_launches;
     return (int)cudaGetLastError();
+}
+
+// 16-bit values and a sparse query set (the decoder form: a few hundred queries over a 20k-pixel pyramid): with at
+// most ~1 corner per pixel row on average (4 * Lq * L * P <= S) accumulating in the 16-bit output itself loses nothing
+// against the stated 16-bit tolerance, and the call needs no fp32 workspace, zero-fills half the bytes and has no
+// rounding pass.  Denser query sets keep fp32 accumulation with one final rounding.
+inline bool sparse_16bit_regime(const msda_dims* d)
+{
+    return 4ll * d->Lq * d->L * d->P <= (long long)d->S && (d->D == 16 || d->D == 32 || d->D == 36 || d->D == 64) &&
+           env_int("MSDA_B200_ACC16", 1) && !env_int("MSDA_B200_FORCE_GENERIC", 0);
 }
 
 // Encoder-form backward on the tensor cores (msda_dense.cuh) + the per-row kernel in split mode for the rest.
@@ -307,24 +320,32 @@ int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, 
 {
     const size_t nval = (size_t)d->N * d->S * d->M * d->D;
     float* acc;
+    bool acc16 = false;
     if constexpr (sizeof(VT) == 4) {
         acc = (float*)gv;
     } else {
-        if (!ws || ws_bytes < nval * sizeof(float)) return MSDA_E_WORKSPACE;
-        if (!aligned16(ws)) return MSDA_E_ALIGN;
-        acc = (float*)ws;
+        acc16 = sparse_16bit_regime(d) && aligned16(value) && aligned16(go) && aligned16(gv) &&
+                (!fa || d->L * d->P <= kFusedMaxChunks * chunk_of(d->D / 4));
+        if (acc16) {
+            acc = (float*)gv;       // the kernels reinterpret it (KernelDims::acc16)
+        } else {
+            if (!ws || ws_bytes < nval * sizeof(float)) return MSDA_E_WORKSPACE;
+            if (!aligned16(ws)) return MSDA_E_ALIGN;
+            acc = (float*)ws;
+        }
     }
     // dense-window tensor-core path: encoder form, 16-bit values, D = 32 / 64, and a workspace with room for
     // the work counter (msda_b200_backward_workspace_bytes)
     bool dense_ok = false;
     if constexpr (sizeof(VT) == 2) {
-        dense_ok = d->Lq == d->S && d->Lq > 0 && d->P <= dense::kMaxP && (d->D == 32 || d->D == 64) &&
+        dense_ok = !acc16 && d->Lq == d->S && d->Lq > 0 && d->P <= dense::kMaxP && (d->D == 32 || d->D == 64) &&
                    (!fa || d->L * d->P <= kFusedMaxChunks * chunk_of(d->D / 4)) &&     // the per-row kernel's fused limit
                    ws_bytes >= dense_counter_offset(nval) + dense_extra_bytes(d) && aligned16(value) && aligned16(go) &&
                    aligned16(loc) && aligned16(attn) && aligned16(gl) && aligned16(ga) &&
                    env_int("MSDA_B200_DENSE", 1) && !env_int("MSDA_B200_FORCE_GENERIC", 0) && !env_int("MSDA_B200_TILE_1D", 0);
     }
-    cudaError_t e = cudaMemsetAsync(acc, 0, dense_ok ? dense_counter_offset(nval) + dense_extra_bytes(d) : nval * sizeof(float), st);
+    cudaError_t e = cudaMemsetAsync(acc, 0, dense_ok ? dense_counter_offset(nval) + dense_extra_bytes(d)
+                                                     : nval * (acc16 ? sizeof(VT) : sizeof(float)), st);
     if (e != cudaSuccess) return (int)e;
     int rc = 0;
     if (d->Lq > 0) {
@@ -349,10 +370,10 @@ int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, 
         // reduction is then 16 contiguous bytes of the fp32 accumulator row and one instruction covers
         // whole 128-byte rows, i.e. the fewest SM->L2 request packets per byte
         if (al && !done) switch (d->D) {
-            case 16: rc = launch_backward_vec<VT, AT, 4, 4>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st, fa); done = true; break;
-            case 32: rc = launch_backward_vec<VT, AT, 4, 8>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st, fa); done = true; break;
-            case 36: rc = launch_backward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st, fa); done = true; break;
-            case 64: rc = launch_backward_vec<VT, AT, 4, 16>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st, fa); done = true; break;
+            case 16: rc = launch_backward_vec<VT, AT, 4, 4>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st, fa, acc16); done = true; break;
+            case 32: rc = launch_backward_vec<VT, AT, 4, 8>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st, fa, acc16); done = true; break;
+            case 36: rc = launch_backward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st, fa, acc16); done = true; break;
+            case 64: rc = launch_backward_vec<VT, AT, 4, 16>(value, shapes, ls, loc, attn, go, acc, gl, ga, d, st, fa, acc16); done = true; break;
             default: break;
         }
         if (!done) {
@@ -362,6 +383,7 @@ int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, 
         if (rc) return rc;
     }
     if constexpr (sizeof(VT) == 2) {
+        if (acc16) return rc;       // accumulated in place
         const int sms = device_info().sms > 0 ? device_info().sms : 148;
         if (nval % 8 == 0 && aligned16(gv)) {
             msda_round_grad_value_kernel<VT><<<sms * 8, 256, 0, st>>>(acc, (VT*)gv, nval / 8);

@@ -52,6 +52,9 @@ def test_workspace_size(lib):
     acc = 2 * 100 * 8 * 32 * 4
     flags = (7 // 32 + 64) * 2 * 8
     assert lib.msda_b200_backward_workspace_bytes(MSDA_BF16, ctypes.byref(d)) == (acc + 255) // 256 * 256 + 256 + (flags + 255) // 256 * 256
+    # sparse query sets (4 * Lq * L * P <= S: the decoder form) accumulate in the 16-bit output: no workspace
+    sparse = MsdaDims(2, 22223, 8, 32, 4, 300, 4)
+    assert lib.msda_b200_backward_workspace_bytes(MSDA_BF16, ctypes.byref(sparse)) == 0
 
 
 def test_argument_validation_without_gpu(lib):
