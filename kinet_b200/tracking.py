@@ -1,0 +1,255 @@
+"""Per-frame tracking loop around kinet_b200's deformable transformer -- the caller the headline metric
+("KineT frames/sec") is named after, SURVEY.md section 8(f) row 3 and BASELINE.json configs[2].
+
+Mirrors the reference's per-frame logic
+  * src/trackformer/models/tracker.py:269-309  -- the live tracks of frame t become frame t+1's track queries
+    (content = the track's last decoder output ``hs_embed``, reference point = its box centre),
+  * :334-420 -- a track survives while its score stays above ``track_obj_score_thresh`` (terminated after
+    ``steps_termination`` consecutive misses), NMS among tracks,
+  * :422-505 -- object queries above ``detection_obj_score_thresh`` start new tracks; NMS in which existing tracks
+    always win over new ones,
+  * :536-557 -- per-frame results, and src/track.py:127-161 -- the frame loop over a sequence,
+  * src/trackformer/models/deformable_detr.py:229-252, 286-326 -- class / box heads on the last decoder layer
+    (box = sigmoid(MLP(hs) + inverse_sigmoid(reference))), scores = sigmoid(logits).max(-1), boxes scaled to pixels,
+on top of ``kinet_b200.modules.DeformableTransformer`` -- eagerly, or through ``FrameGraphs`` (one CUDA graph for
+the encoder, one per bucket of query counts for the decoder): the number of queries changes EVERY frame.
+
+What is different from the reference, on purpose: track state lives in device tensors (boxes, embeddings) instead
+of one Python object per track holding device scalars, and a frame is read back ONCE (scores, labels, boxes of
+all queries in one packed copy) instead of once per track and field (tracker.py:293, 536-542); thresholding and
+NMS then run on the host on a few hundred boxes.  Not covered: re-identification of inactive tracks
+(``inactive_patience`` >= 0; the reference's cfgs/track.yaml sets -1, i.e. off), public detections, masks,
+attention maps -- they contain no MSDeformAttn work.  The backbone is out of scope: frames
+enter as the multi-scale feature maps the backbone + input projections would produce.
+"""
+import math
+
+import numpy as np
+import torch
+from torch import nn
+
+from .frame_graph import FrameGraphs
+from .modules.deformable_transformer import _shapes_tensor, inverse_sigmoid
+
+
+class MLP(nn.Module):
+    """The reference's box head (src/trackformer/models/detr.py MLP: Linear-ReLU stack)."""
+
+    def __init__(self, input_dim, hidden_dim, output_dim, num_layers):
+        super().__init__()
+        h = [hidden_dim] * (num_layers - 1)
+        self.layers = nn.ModuleList(nn.Linear(n, k) for n, k in zip([input_dim] + h, h + [output_dim]))
+
+    def forward(self, x):
+        for i, layer in enumerate(self.layers):
+            x = torch.relu(layer(x)) if i < len(self.layers) - 1 else layer(x)
+        return x
+
+
+class DetectionHeads(nn.Module):
+    """class_embed / bbox_embed of the last decoder layer (deformable_detr.py:88-110, 229-252; inference has no use
+    for the auxiliary heads)."""
+
+    def __init__(self, d_model, num_classes=1):
+        super().__init__()
+        self.class_embed = nn.Linear(d_model, num_classes)
+        self.bbox_embed = MLP(d_model, d_model, 4, 3)
+        prior = 0.01
+        nn.init.constant_(self.class_embed.bias, -math.log((1 - prior) / prior))
+        nn.init.constant_(self.bbox_embed.layers[-1].weight, 0.0)
+        nn.init.constant_(self.bbox_embed.layers[-1].bias, 0.0)
+
+    def forward(self, hs_last, reference):
+        """hs_last (N, Lq, C); reference (N, Lq, 2|4) in [0,1] -> logits (N, Lq, K), boxes (N, Lq, 4) cxcywh in [0,1]."""
+        logits = self.class_embed(hs_last.float())
+        tmp = self.bbox_embed(hs_last.float())
+        ref = inverse_sigmoid(reference.float())
+        if ref.shape[-1] == 4:
+            tmp = tmp + ref
+        else:
+            tmp = torch.cat([tmp[..., :2] + ref, tmp[..., 2:]], -1)
+        return logits, tmp.sigmoid()
+
+
+def _nms(boxes, scores, thresh):
+    """Indices kept by greedy IoU suppression (torchvision.ops.nms semantics: IoU > thresh suppresses), on the host."""
+    order = np.argsort(-scores, kind="stable")
+    area = np.clip(boxes[:, 2] - boxes[:, 0], 0, None) * np.clip(boxes[:, 3] - boxes[:, 1], 0, None)
+    keep = []
+    dead = np.zeros(len(boxes), dtype=bool)
+    for i in order:
+        if dead[i]:
+            continue
+        keep.append(i)
+        xx1 = np.maximum(boxes[i, 0], boxes[:, 0]); yy1 = np.maximum(boxes[i, 1], boxes[:, 1])
+        xx2 = np.minimum(boxes[i, 2], boxes[:, 2]); yy2 = np.minimum(boxes[i, 3], boxes[:, 3])
+        inter = np.clip(xx2 - xx1, 0, None) * np.clip(yy2 - yy1, 0, None)
+        iou = inter / np.maximum(area[i] + area - inter, 1e-12)
+        dead |= iou > thresh
+    return np.asarray(sorted(keep), dtype=np.int64)
+
+
+class SequenceTracker:
+    """Tracks one sequence frame by frame.
+
+        tracker = SequenceTracker(transformer, heads, query_embed, img_size=(1080, 1920))
+        for srcs, masks, pos_embeds in frames:           # per level (1, C, H, W) / (1, H, W) bool / (1, C, H, W)
+            result = tracker.step(srcs, masks, pos_embeds)   # {track_id: {"bbox": xyxy px, "score": float}}
+
+    transformer: kinet_b200.modules.DeformableTransformer (not two-stage); heads: DetectionHeads;
+    query_embed: (num_object_queries, 2C) learned object queries.  use_graphs: replay FrameGraphs (the query count
+    is padded to ``bucket``); otherwise the transformer runs eagerly.  autocast_dtype: None = fp32."""
+
+    def __init__(self, transformer, heads, query_embed, img_size, detection_obj_score_thresh=0.4,
+                 track_obj_score_thresh=0.4, detection_nms_thresh=0.9, track_nms_thresh=0.9, steps_termination=1,
+                 use_graphs=False, bucket=32, autocast_dtype=None):
+        assert not transformer.two_stage and not transformer.multi_frame_attention_separate_encoder
+        self.transformer, self.heads = transformer, heads
+        self.query_embed = query_embed
+        self.num_object_queries = query_embed.shape[0]
+        self.img_h, self.img_w = float(img_size[0]), float(img_size[1])
+        self.det_thresh, self.trk_thresh = detection_obj_score_thresh, track_obj_score_thresh
+        self.det_nms, self.trk_nms = detection_nms_thresh, track_nms_thresh
+        self.steps_termination = steps_termination
+        self.use_graphs, self.bucket, self.autocast_dtype = use_graphs, bucket, autocast_dtype
+        self._graphs = None
+        self.reset()
+
+    def reset(self):
+        """Start a new sequence (tracker.py:75-95); recorded graphs are kept (same weights, same pyramid)."""
+        self.track_ids = []                      # host: ids of the live tracks, in query order
+        self.track_misses = []                   # host: consecutive frames below track_obj_score_thresh
+        self.track_boxes = None                  # device (T, 4) xyxy pixels
+        self.track_scores = None                 # host numpy (T,)
+        self._host_boxes = None                  # host numpy (T, 4), the same boxes
+        self.track_hs = None                     # device (T, C)
+        self.next_id = 0
+        self.frame_index = 0
+        self.results = {}
+
+    # ---- the transformer call ---------------------------------------------------------------------------------------
+    def _flatten(self, srcs, masks, pos_embeds):
+        tr = self.transformer
+        shapes, src_l, pos_l = [], [], []
+        for lvl, (src, pos) in enumerate(zip(srcs, pos_embeds)):
+            shapes.append((int(src.shape[2]), int(src.shape[3])))
+            src_l.append(src.flatten(2).transpose(1, 2))
+            pos_l.append(pos.flatten(2).transpose(1, 2) + tr.level_embed[lvl].view(1, 1, -1))
+        return torch.cat(src_l, 1), torch.cat(pos_l, 1), shapes
+
+    def _run_transformer(self, srcs, masks, pos_embeds, targets):
+        tr = self.transformer
+        if not self.use_graphs:
+            with torch.autocast("cuda", dtype=self.autocast_dtype, enabled=self.autocast_dtype is not None):
+                hs, _, init_ref, inter_ref, _, _ = tr(srcs, masks, pos_embeds, self.query_embed, targets)
+            if hs.dim() == 4:                    # return_intermediate_dec: last layer, reference of the layer before
+                ref = inter_ref[-2] if inter_ref.shape[0] > 1 else init_ref
+                return hs[-1], ref
+            return hs, init_ref
+        # graphs: the pyramid is fixed, the number of queries is not.  No padding in tracking frames (N = 1).
+        src, pos, shapes = self._flatten(srcs, masks, pos_embeds)
+        dev = src.device
+        if self._graphs is None:
+            self._graphs = FrameGraphs(tr.encoder, tr.decoder, _shapes_tensor(shapes, dev), bucket=self.bucket,
+                                       autocast_dtype=self.autocast_dtype)
+            self._valid = torch.ones(1, len(shapes), 2, device=dev)
+        c = src.shape[-1]
+        qpos, tgt = torch.split(self.query_embed, c, dim=1)
+        qpos, tgt = qpos[None], tgt[None]
+        ref = tr.reference_points(qpos).sigmoid()
+        if targets is not None:
+            prev_hs = targets[0]["track_query_hs_embeds"][None]
+            qpos = torch.cat([torch.zeros_like(prev_hs), qpos], 1)
+            tgt = torch.cat([prev_hs, tgt], 1)
+            ref = torch.cat([targets[0]["track_query_boxes"][None, :, :2], ref], 1)
+        hs, ref_out, _ = self._graphs(src, pos, self._valid, tgt, ref, qpos)
+        if hs.dim() == 4:
+            return hs[-1], (ref_out[-2] if ref_out.shape[0] > 1 else ref)
+        return hs, ref
+
+    # ---- one frame --------------------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def step(self, srcs, masks, pos_embeds):
+        dev = srcs[0].device
+        T = len(self.track_ids)
+        targets = None
+        if T:
+            b = self.track_boxes                                   # xyxy px -> cxcywh normalised (tracker.py:299-304)
+            cxcywh = torch.stack([(b[:, 0] + b[:, 2]) / 2, (b[:, 1] + b[:, 3]) / 2, b[:, 2] - b[:, 0], b[:, 3] - b[:, 1]], -1)
+            cxcywh = cxcywh / torch.tensor([self.img_w, self.img_h, self.img_w, self.img_h], device=dev)
+            targets = [{"track_query_boxes": cxcywh, "track_query_hs_embeds": self.track_hs}]
+        hs, ref = self._run_transformer(srcs, masks, pos_embeds, targets)
+        logits, boxes = self.heads(hs, ref)
+        prob = logits.sigmoid()
+        scores, labels = prob.max(-1)
+        x, y, w, h = boxes.unbind(-1)
+        xyxy = torch.stack([x - 0.5 * w, y - 0.5 * h, x + 0.5 * w, y + 0.5 * h], -1)
+        xyxy = xyxy * torch.tensor([self.img_w, self.img_h, self.img_w, self.img_h], device=dev)
+        lim = torch.tensor([self.img_w, self.img_h, self.img_w, self.img_h], device=dev)
+        xyxy = torch.minimum(xyxy.clamp(min=0), lim)               # clip_boxes_to_image
+        # ONE device -> host read per frame
+        packed = torch.cat([scores[0, :, None], labels[0, :, None].to(scores.dtype), xyxy[0]], -1).cpu().numpy()
+        sc, lb, bx = packed[:, 0], packed[:, 1].astype(np.int64), packed[:, 2:6].astype(np.float64)
+
+        # tracks (tracker.py:334-420): entry = [id, misses, query index this frame or -1 (stale), old row, box, score]
+        live = []
+        for j in range(T):
+            if sc[j] > self.trk_thresh and lb[j] == 0:
+                live.append([self.track_ids[j], 0, j, j, bx[j], sc[j]])
+            elif self.track_misses[j] + 1 < self.steps_termination:      # missed, not yet terminated: keeps its state
+                live.append([self.track_ids[j], self.track_misses[j] + 1, -1, j, self._host_boxes[j], self.track_scores[j]])
+        if self.trk_nms and live:
+            k = _nms(np.stack([e[4] for e in live]), np.asarray([e[5] for e in live]), self.trk_nms)
+            live = [live[j] for j in k]
+        # new detections (tracker.py:422-505)
+        new = [[-1, 0, int(i), -1, bx[i], sc[i]] for i in range(T, T + self.num_object_queries)
+               if sc[i] > self.det_thresh and lb[i] == 0]
+        # NMS in which existing tracks always win over new ones (:485-505)
+        if self.det_nms and (live or new):
+            boxes_all = np.stack([e[4] for e in live + new])
+            scores_all = np.asarray([np.inf] * len(live) + [e[5] for e in new])
+            k = set(_nms(boxes_all, scores_all, self.det_nms).tolist())
+            new = [e for j, e in enumerate(new) if j + len(live) in k]
+            live = [e for j, e in enumerate(live) if j in k]
+        for e in new:
+            e[0] = self.next_id
+            self.next_id += 1
+        entries = live + new
+        # next frame's track state, gathered on the device
+        if entries:
+            q_rows = torch.as_tensor([max(e[2], 0) for e in entries], device=dev)
+            new_boxes, new_hs = xyxy[0, q_rows], hs[0, q_rows].float()
+            stale = [j for j, e in enumerate(entries) if e[2] < 0]
+            if stale:                                               # a missed frame keeps the previous box / embedding
+                dst = torch.as_tensor(stale, device=dev)
+                src_rows = torch.as_tensor([entries[j][3] for j in stale], device=dev)
+                new_boxes[dst] = self.track_boxes[src_rows]
+                new_hs[dst] = self.track_hs[src_rows]
+            self.track_boxes, self.track_hs = new_boxes, new_hs
+        else:
+            self.track_boxes = self.track_hs = None
+        self.track_ids = [e[0] for e in entries]
+        self.track_misses = [e[1] for e in entries]
+        self._host_boxes = np.asarray([e[4] for e in entries], dtype=np.float64).reshape(-1, 4)
+        self.track_scores = np.asarray([e[5] for e in entries], dtype=np.float64)
+        frame = {e[0]: {"bbox": np.array(e[4], dtype=np.float64), "score": float(e[5])} for e in entries}
+        for t, r in frame.items():
+            self.results.setdefault(t, {})[self.frame_index] = r
+        self.frame_index += 1
+        return frame
+
+
+def synthetic_sequence(levels, d_model, n_frames, device, seed=0, drift=0.05, dtype=torch.float32):
+    """Frames of a synthetic sequence as the transformer sees them: per-level feature maps (1, C, H, W), all-False
+    padding masks and positional maps.  Consecutive frames are correlated (a fixed scene plus a slowly varying
+    part), so detections persist for a while and then change -- the number of track queries varies from frame to
+    frame like it does on video.  Yields (srcs, masks, pos_embeds)."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    scene = [torch.randn(1, d_model, h, w, generator=g) for h, w in levels]
+    pos = [torch.randn(1, d_model, h, w, generator=g) * 0.1 for h, w in levels]
+    masks = [torch.zeros(1, h, w, dtype=torch.bool, device=device) for h, w in levels]
+    pos = [p.to(device=device, dtype=dtype) for p in pos]
+    cur = [s.clone() for s in scene]
+    for _ in range(n_frames):
+        cur = [(1 - drift) * c + drift * torch.randn(c.shape, generator=g) + drift * s for c, s in zip(cur, scene)]
+        yield [c.to(device=device, dtype=dtype) for c in cur], masks, pos
