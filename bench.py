@@ -14,11 +14,14 @@ metric: msda_fwd_bwd_GBps = algorithmic bytes of the step (SURVEY.md section 8(d
   value    inputs resident in HBM, calls made straight through the C ABI (libmsda_b200.so)
   e2e      same step through the public Python API (MSDeformAttnFunction) with HOST pinned inputs:
            H2D of every input, forward, backward, D2H of output and gradients inside the timed region
-  roofline dominant kernel = the encoder-form backward kernel, timed alone with CUDA events recorded
-           by the library around that launch (msda_b200_trace_next)
+  roofline dominant kernel = the encoder-form backward (the dense-window tcgen05 kernel + the per-row kernel
+           for the coarser levels: two launches the library brackets as one with CUDA events,
+           msda_b200_trace_next); DRAM traffic etc. come from profiles/roofline_inputs.json, written from
+           an ncu capture together with a hash of kinet_b200/csrc -- a capture of other kernels is flagged stale
+  sweep    BASELINE.json configs[4] (MOT20 crowd, full-res pyramid, 300 + 500 queries): per-call times
   cpu_baseline / --impl reference: the reference's CPU-runnable path (per-level grid_sample + autograd,
-           restated in oracle/msda_oracle.py because /root/reference is absent on the GPU box) on a
-           bounded sample, all host threads.
+           restated in oracle/msda_oracle.py because /root/reference is absent on the GPU box) on the SAME
+           step (6 encoder-form + 6 decoder-form calls, full Lq, fp32), all host threads.
 """
 import argparse
 import ctypes
@@ -39,18 +42,31 @@ from kinet_b200.workloads import algorithmic_bytes, make_inputs, resolve  # noqa
 WORKLOAD = "detr_6enc_6dec_bf16"
 ENC_TAG, DEC_TAG, LAYERS = "C2_enc", "C2_dec", 6
 METRIC, UNIT = "msda_fwd_bwd_GBps", "GB/s"
-# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from the committed
-# `ncu --set full` capture (bench.py never runs under a profiler, so this is a recorded measurement)
-ENC_BWD_DRAM_TRAFFIC = 210.0e6 + 104.5e6
-ENC_BWD_DRAM_TRAFFIC_SRC = "profiles/r1n_ncu_full_C2enc_bf16.txt"
-# the same kernel against the unit that actually binds it: every sample adds 4 corner rows of D fp32
-# channels into grad_value (upper bound: zero-weight border corners are skipped)
-SCATTER_BYTES = 2 * 22223 * 8 * 16 * 4 * 32 * 4
-# what the kernel really sends: corners with zero weight (outside the level / exact integer coordinates) are
-# skipped.  l1tex__t_sectors_pipe_lsu_mem_global_op_red.sum of one launch on this workload (recorded, same
-# ncu capture as the DRAM traffic above) x 32 bytes
-SCATTER_BYTES_ISSUED = 80064552 * 32
-RED_CEILING_GBPS = 6411.7
+ROOFLINE_INPUTS = os.path.join(ROOT, "profiles", "roofline_inputs.json")
+
+
+def csrc_hash():
+    """sha256 over the CUDA sources, the key profiles/roofline_inputs.json was recorded under."""
+    import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "kinet_b200", "csrc")
+    for name in sorted(os.listdir(d)):
+        if name.endswith((".cu", ".cuh")):
+            with open(os.path.join(d, name), "rb") as f:
+                h.update(name.encode() + b"\0" + f.read())
+    return h.hexdigest()[:16]
+
+
+def roofline_inputs():
+    """DRAM traffic / reduction sectors of the dominant kernel from the committed ncu capture (bench.py never runs
+    under a profiler).  stale = the capture was taken on other kernel sources than the ones being measured."""
+    try:
+        with open(ROOFLINE_INPUTS) as f:
+            r = json.load(f)
+    except Exception:
+        return {"traffic": None, "stale": None, "source": None}
+    r["stale"] = r.get("csrc_hash") != csrc_hash()
+    return r
 
 
 def measured_peak():
@@ -281,8 +297,10 @@ def run_ours(args, rank, world, dev):
     e1.record()
     barrier()
     e2e_ms = e0.elapsed_time(e1) / e2e_steps
+    ceiling_ms = copy_ceiling(host, sink, dev, world)
     return dict(ms=ms, kern_ms=kern_ms, launches=launches, clocks=clocks, total_bytes=total_bytes,
-                enc_bwd_bytes=enc_bwd_bytes, e2e_ms=e2e_ms, h2d=h2d, d2h=d2h, e2e_steps=e2e_steps)
+                enc_bwd_bytes=enc_bwd_bytes, e2e_ms=e2e_ms, h2d=h2d, d2h=d2h, e2e_steps=e2e_steps,
+                ceiling_ms=ceiling_ms)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -310,27 +328,35 @@ def cpu_step(cases):
 
 
 def cpu_cases():
-    # bounded sample of the same workload: ONE decoder-layer call (exact config-1 shape, Lq=300) and
-    # ONE encoder-layer call cut to its first 8192 queries, fp32 (the reference has no bf16)
-    cases = [cpu_sample_inputs(DEC_TAG), cpu_sample_inputs(ENC_TAG, lq_cap=8192)]
+    # the SAME step as the GPU arm: 6 encoder-form + 6 decoder-form calls, full Lq, forward + backward, fp32 (the
+    # reference has no bf16); the layers share one set of inputs (the CPU has no cache that could hold them)
+    enc, dec = cpu_sample_inputs(ENC_TAG), cpu_sample_inputs(DEC_TAG)
+    cases = [enc] * LAYERS + [dec] * LAYERS
     nbytes = 0
     for s, *_ in cases:
         f, b = algorithmic_bytes(s, 4, 4)
         nbytes += f + b
-    return cases, nbytes, "1 decoder call (N=2,Lq=300) + 1 encoder call cut to Lq=8192, fwd+bwd, fp32, 800x1333 pyramid"
+    return cases, nbytes, ("the full step: %d encoder-form calls (N=2, Lq=S=22223) + %d decoder-form calls (Lq=300), "
+                           "fwd+bwd, fp32, 800x1333 pyramid" % (LAYERS, LAYERS))
 
 
-def run_cpu(steps, warmup):
+def run_cpu(steps, warmup, budget_s=240.0):
+    """`steps` identical steps after `warmup` (at most one: a CPU has no clocks to ramp); on a host too slow for that
+    within `budget_s` the number of timed steps is cut (never the step itself) and reported as steps_run."""
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     cases, nbytes, sample = cpu_cases()
-    for _ in range(warmup):
+    t = time.perf_counter()
+    for _ in range(min(warmup, 1)):
         cpu_step(cases)
+    est = time.perf_counter() - t
+    if est > 0:
+        steps = max(1, min(steps, int(budget_s / est)))
     t = time.perf_counter()
     for _ in range(steps):
         cpu_step(cases)
     dt = (time.perf_counter() - t) / steps
-    return dict(value=nbytes / dt / 1e9, ms=dt * 1e3, cores=torch.get_num_threads(), sample=sample)
+    return dict(value=nbytes / dt / 1e9, ms=dt * 1e3, cores=torch.get_num_threads(), sample=sample, steps_run=steps)
 
 
 def reduce_max(values, device, world):
@@ -361,73 +387,104 @@ def bind_to_gpu_numa_node(index):
 # ---------------------------------------------------------------------------------------------
 # Callers: the other half of BASELINE.json's metric ("KineT frames/sec at 1/2/4/8 B200") and configs[3]
 # ---------------------------------------------------------------------------------------------
-def measure_callers(rank, world, dev, frames=100, train_steps=10):
-    """Tracking frames/s (configs[2]: MOT17 pyramid, d=288, 6+6 layers, 560 queries, bf16 autocast, one CUDA graph
-    per GPU, independent sequences per GPU) and data-parallel training samples/s (configs[3]: 800x1333 pyramid,
-    d=256, batch 2 per GPU, fwd+bwd+AdamW as two CUDA graphs around ONE NCCL all-reduce of the gradients) of the
-    6-layer encoder + 6-layer decoder built from kinet_b200.modules' layer classes -- the same measurements as
-    tools/frames_bench.py and tools/train_bench.py, device-timed, max over ranks.  The backbone, the heads, the
-    matcher and the tracker's Python are the reference's and are not part of these numbers."""
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    from _harness import FusedStack
-    from kinet_b200.training import GraphedTrainStep
+def measure_callers(rank, world, dev, frames=120, train_steps=10):
+    """The callers of the op, through the product API, device-timed, max over ranks:
+
+    tracking frames/s (BASELINE.json configs[2]) -- kinet_b200.tracking.SequenceTracker: the reference's per-frame
+      loop (tracker.py:269-557) over kinet_b200.modules.DeformableTransformer + FrameGraphs on a synthetic MOT17
+      sequence (750x1333 pyramid, d=288, 6+6 layers, 500 object queries + the previous frame's surviving tracks as
+      track queries, so the query count changes every frame), bf16 autocast, one read-back per frame; one
+      independent sequence per GPU (replicas);
+    training samples/s (configs[3]) -- kinet_b200.training.GraphedTrainStep over the same transformer class
+      (800x1333 pyramid, d=256, batch 2 per GPU, dropout 0.1, the reference's optimizer groups and gradient clipping,
+      src/train.py:103-117, engine.py:147): fwd+bwd and AdamW as two CUDA graphs around ONE NCCL all-reduce.
+
+    The backbone, the matcher / losses and the datasets are the reference's and are not part of these numbers."""
+    from torch import nn
+    from kinet_b200.modules import DeformableTransformer
+    from kinet_b200.tracking import DetectionHeads, SequenceTracker
+    from kinet_b200.training import GraphedTrainStep, reference_param_groups
     from kinet_b200.workloads import PYRAMIDS
     out = {}
-    # ---- tracking frames ----
-    levels = PYRAMIDS["mot17_750x1333"]
-    S = sum(h * w for h, w in levels)
+    # ---- tracking ----
+    levels, d, nq = PYRAMIDS["mot17_750x1333"], 288, 500
     torch.manual_seed(1000 + rank)
-    model = FusedStack(levels, n_queries=560, d=288).to(dev).eval()
-    src = torch.randn(1, S, 288, device=dev)
-    pos = torch.randn(1, S, 288, device=dev) * 0.1
-    feeds = [torch.randn(1, S, 288, device=dev) for _ in range(4)]
-    with torch.autocast("cuda", dtype=torch.bfloat16):
-        def frame():
-            with torch.no_grad():
-                return model(src, pos)
-        side = torch.cuda.Stream()
-        side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):
-            for _ in range(3):
-                frame()
-        torch.cuda.current_stream().wait_stream(side)
-        torch.cuda.synchronize()
-        graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph):
-            frame()
-
-        def run(n):
-            for i in range(n):
-                src.copy_(feeds[i & 3], non_blocking=True)       # a new frame lands in the graph's input buffer
-                graph.replay()
-        run(10)
-        torch.cuda.synchronize()
-        if world > 1:
-            torch.distributed.barrier()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(); run(frames); b.record()
-        torch.cuda.synchronize()
+    tr = DeformableTransformer(d, 8, 6, 6, 1024, 0.1, "relu", True, len(levels), 4, 4).to(dev).eval()
+    heads = DetectionHeads(d, 1).to(dev).eval()
+    with torch.no_grad():                       # random weights: let detections come and go around the threshold
+        heads.class_embed.bias.zero_()
+        nn.init.normal_(heads.class_embed.weight, std=0.5)
+        nn.init.normal_(heads.bbox_embed.layers[-1].weight, std=0.02)
+    qe = torch.randn(nq, 2 * d, device=dev)
+    g = torch.Generator(device=dev).manual_seed(7 + rank)
+    scene = [torch.randn(1, d, h, w, device=dev, generator=g) for h, w in levels]
+    pos = [torch.randn(1, d, h, w, device=dev, generator=g) * 0.1 for h, w in levels]
+    masks = [torch.zeros(1, h, w, dtype=torch.bool, device=dev) for h, w in levels]
+    feeds = [[s_ + 0.3 * torch.randn(s_.shape, device=dev, generator=g) for s_ in scene] for _ in range(8)]
+    tracker = SequenceTracker(tr, heads, qe, img_size=(1080, 1920), use_graphs=True, bucket=32,
+                              autocast_dtype=torch.bfloat16)
+    # calibrate the score threshold on the first frame so that ~8 % of the object queries fire (T ~ 20-60 like MOT17)
+    tracker.det_thresh = tracker.trk_thresh = 2.0
+    tracker.step(feeds[0], masks, pos)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        hs, _, init_ref, inter_ref, _, _ = tr(feeds[0], masks, pos, qe, None)
+        sc = heads(hs[-1], inter_ref[-2])[0].sigmoid().max(-1)[0].flatten()
+    thr = float(torch.quantile(sc.float(), 0.92))
+    tracker.det_thresh = tracker.trk_thresh = thr
+    tracker.reset()
+    counts = []
+    for i in range(24):                         # warm-up: records the decoder graphs of the buckets that occur
+        tracker.step(feeds[i & 7], masks, pos)
+    torch.cuda.synchronize()
+    if world > 1:
+        torch.distributed.barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(frames):
+        counts.append(len(tracker.track_ids) + nq)
+        tracker.step(feeds[i & 7], masks, pos)
+    b.record()
+    torch.cuda.synchronize()
     ms = reduce_max([a.elapsed_time(b)], dev, world)[0]
-    out["tracking_frames_per_s"] = {"value": world * frames / ms * 1e3, "ms_per_frame_per_gpu": ms / frames,
-                                    "config": "MOT17 750x1333 pyramid, S=20906, d=288 (D=36), 6 enc + 6 dec layers, "
-                                              "560 queries, bf16 autocast, forward, CUDA graph; replicas"}
-    del graph, model
+    out["tracking_frames_per_s"] = {
+        "value": world * frames / ms * 1e3, "ms_per_frame_per_gpu": ms / frames,
+        "queries_min_max": [min(counts), max(counts)], "tracks_started": tracker.next_id,
+        "decoder_graph_buckets": tracker._graphs.recorded_buckets,
+        "config": "kinet_b200.tracking.SequenceTracker: MOT17 750x1333 pyramid, S=20906, d=288 (D=36), 6 enc + 6 dec "
+                  "layers, 500 object + T track queries (T changes every frame), bf16 autocast, FrameGraphs, one "
+                  "read-back per frame; one sequence per GPU"}
+    del tracker, tr
     # ---- data-parallel training ----
-    levels = PYRAMIDS["detr_800x1333"]
-    S = sum(h * w for h, w in levels)
-    torch.manual_seed(0)                                          # same initial weights on every rank
-    model = FusedStack(levels, n_queries=300, d=256).to(dev).train()
-    g = torch.Generator(device=dev).manual_seed(100 + rank)       # a different batch on every rank
-    batches = [(torch.randn(2, S, 256, device=dev, generator=g), torch.randn(2, S, 256, device=dev, generator=g) * 0.1,
-                torch.randn(2, 300, 256, device=dev, generator=g)) for _ in range(2)]
+    levels, d = PYRAMIDS["detr_800x1333"], 256
 
-    def loss_fn(x, p, target):
+    class Net(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.transformer = DeformableTransformer(d, 8, 6, 6, 1024, 0.1, "relu", False, len(levels), 4, 4)
+            self.query_embed = nn.Embedding(300, 2 * d)
+
+        def forward(self, srcs, pos):
+            masks_ = [torch.zeros(s_.shape[0], s_.shape[2], s_.shape[3], dtype=torch.bool, device=s_.device) for s_ in srcs]
+            return self.transformer(srcs, masks_, pos, self.query_embed.weight, None)[0]
+
+    torch.manual_seed(0)                                          # same initial weights on every rank
+    model = Net().to(dev).train()
+    g = torch.Generator(device=dev).manual_seed(100 + rank)       # a different batch on every rank
+    L = len(levels)
+
+    def batch():
+        srcs = [torch.randn(2, d, h, w, device=dev, generator=g) for h, w in levels]
+        pos_ = [torch.randn(2, d, h, w, device=dev, generator=g) * 0.1 for h, w in levels]
+        return tuple(srcs + pos_ + [torch.randn(2, 300, d, device=dev, generator=g)])
+    batches = [batch() for _ in range(2)]
+
+    def loss_fn(*t):
         with torch.autocast("cuda", dtype=torch.bfloat16):
-            hs, _ = model(x, p)
-        return (hs.float() - target).square().mean()
+            hs = model(list(t[:L]), list(t[L:2 * L]))
+        return (hs.float() - t[-1]).square().mean()
     step = GraphedTrainStep(model, loss_fn,
-                            lambda ps: torch.optim.AdamW(ps, lr=1e-4, weight_decay=1e-4, fused=True, capturable=True),
-                            batches[0])
+                            lambda ps: torch.optim.AdamW(ps, lr=2e-4, weight_decay=1e-4, fused=True, capturable=True),
+                            batches[0], param_groups=reference_param_groups(model), clip_max_norm=0.1)
     for i in range(3):
         step(*batches[i & 1])
     torch.cuda.synchronize()
@@ -440,11 +497,81 @@ def measure_callers(rank, world, dev, frames=100, train_steps=10):
     b.record()
     torch.cuda.synchronize()
     ms = reduce_max([a.elapsed_time(b)], dev, world)[0]
-    out["training_samples_per_s"] = {"value": world * 2 * train_steps / ms * 1e3, "ms_per_step": ms / train_steps,
-                                     "config": "800x1333 pyramid, S=22223, d=256, 6 enc + 6 dec layers, 300 queries, "
-                                               "batch 2 per GPU, bf16 autocast, fwd+bwd+AdamW, two CUDA graphs + one "
-                                               "NCCL gradient all-reduce per step"}
+    out["training_samples_per_s"] = {
+        "value": world * 2 * train_steps / ms * 1e3, "ms_per_step": ms / train_steps,
+        "config": "kinet_b200.modules.DeformableTransformer + GraphedTrainStep: 800x1333 pyramid, S=22223, d=256, "
+                  "6 enc + 6 dec layers, 300 queries, batch 2 per GPU, dropout 0.1, bf16 autocast, fwd+bwd + gradient "
+                  "clipping 0.1 + AdamW with the reference's 3 learning-rate groups; two CUDA graphs + one NCCL "
+                  "gradient all-reduce per step; synthetic MSE loss (matcher / set criterion are the reference's)"}
     return out
+
+
+def measure_sweep(dev, iters=5):
+    """BASELINE.json configs[4] (MOT20 crowd stress): full-res 1080x1920 pyramid, encoder form and the decoder form
+    at 300 object + 500 track queries, forward and backward, bf16 and fp32 values; CUDA events, L2 flushed between
+    iterations (a 256 MB buffer is overwritten)."""
+    from kinet_b200.functions import ms_deform_attn_backward, ms_deform_attn_forward
+    peak, _ = measured_peak()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    out = {}
+    for tag in ("C5_enc", "C5_dec"):
+        for name, dt in (("bf16", torch.bfloat16), ("f32", torch.float32)):
+            s = resolve(tag)
+            value, shapes, loc, attn = make_inputs(tag, dev, dt, torch.float32, "structured", 3)
+            go = torch.randn(s["N"], s["Lq"], s["M"] * s["D"], device=dev).to(dt)
+            bf, bb = algorithmic_bytes(s, value.element_size(), 4)
+            res = {}
+            for what, fn, nbytes in (("fwd", lambda: ms_deform_attn_forward(value, shapes, loc, attn, 64), bf),
+                                     ("bwd", lambda: ms_deform_attn_backward(value, shapes, loc, attn, go, 64), bb)):
+                for _ in range(2):
+                    fn()
+                ts = []
+                for _ in range(iters):
+                    flush.zero_()
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    torch.cuda._sleep(200000)
+                    a.record(); fn(); b.record()
+                    torch.cuda.synchronize()
+                    ts.append(a.elapsed_time(b) * 1e3)
+                ts.sort()
+                us = ts[len(ts) // 2]
+                res[what] = {"us": us, "GBps": nbytes / us / 1e3, "frac_of_hbm": nbytes / us / 1e3 / peak}
+            out["%s_%s" % (tag, name)] = res
+    out["config"] = ("MOT20 full-res pyramid (135,240)(68,120)(34,60)(17,30), S=43110, N=1, M=8, D=32, L=4, P=4; "
+                     "C5_enc: Lq=S; C5_dec: Lq=800 (300 object + 500 track queries); backward incl. zero-fill / rounding")
+    return out
+
+
+def copy_ceiling(host, sink, dev, world, steps=3):
+    """What the box gives for the e2e leg's transfers alone: the same pinned host tensors copied H2D and the same
+    result sizes copied D2H, concurrently on two streams, one cudaMemcpyAsync per tensor, no kernels."""
+    land = [tuple(torch.empty_like(t, device=dev) for t in tup) for tup in host]
+    res = [tuple(torch.empty_like(t, device=dev) for t in tup) for tup in sink]
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+
+    def once():
+        with torch.cuda.stream(s_in):
+            for hs_, ds_ in zip(host, land):
+                for h_, d_ in zip(hs_, ds_):
+                    d_.copy_(h_, non_blocking=True)
+        with torch.cuda.stream(s_out):
+            for hs_, ds_ in zip(sink, res):
+                for h_, d_ in zip(hs_, ds_):
+                    h_.copy_(d_, non_blocking=True)
+    once()
+    torch.cuda.synchronize()
+    if world > 1:
+        torch.distributed.barrier()
+    cur = torch.cuda.current_stream()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    s_in.wait_event(a); s_out.wait_event(a)
+    for _ in range(steps):
+        once()
+    cur.wait_stream(s_in); cur.wait_stream(s_out)
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / steps
 
 
 def main():
@@ -454,7 +581,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--e2e-steps", type=int, default=6)
-    ap.add_argument("--cpu-steps", type=int, default=5)
+    ap.add_argument("--cpu-steps", type=int, default=3)
+    ap.add_argument("--no-sweep", action="store_true", help="skip the configs[4] (MOT20 crowd) per-call sweep")
     ap.add_argument("--no-callers", action="store_true",
                     help="skip the frames/s and training samples/s leg (tracking / training stacks around the op)")
     args = ap.parse_args()
@@ -475,6 +603,7 @@ def main():
         line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms"], "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+                "steps_run": r["steps_run"],
                 "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
                                  "sample": r["sample"]},
                 "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -493,7 +622,13 @@ def main():
         torch.distributed.init_process_group("nccl", device_id=dev)
     r = run_ours(args, rank, world, dev)
     ms, e2e_ms = r["ms"], r["e2e_ms"]
-    ms, e2e_ms = reduce_max([ms, e2e_ms], dev, world)
+    ms, e2e_ms, ceiling_ms = reduce_max([ms, e2e_ms, r["ceiling_ms"]], dev, world)
+    sweep = None
+    if rank == 0 and world == 1 and not args.no_sweep:
+        try:
+            sweep = measure_sweep(dev)
+        except Exception as e:
+            sweep = {"error": "%s: %s" % (type(e).__name__, str(e)[:200])}
     callers = None
     if not args.no_callers:
         try:
@@ -509,37 +644,45 @@ def main():
         kavg = sum(kms) / len(kms)
         achieved = r["enc_bwd_bytes"] / (kavg * 1e-3) / 1e9
         cpu = run_cpu(args.cpu_steps, 1)
+        ri = roofline_inputs()
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": config,
                 "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
                         "ms_per_step": e2e_ms, "steps": r["e2e_steps"],
+                        "copy_ceiling_ms_per_step": ceiling_ms, "frac_of_copy_ceiling": ceiling_ms / e2e_ms,
+                        "copy_ceiling": "the same pinned tensors copied H2D and the same result sizes copied D2H "
+                                        "concurrently on two streams, one cudaMemcpyAsync per tensor, no kernels, "
+                                        "all ranks at once (max over ranks)",
                         "api": "kinet_b200.MSDeformAttnFunction.apply + Tensor.backward, pinned host tensors; H2D, kernels and D2H on three streams"},
                 "gpu_launches": r["launches"],
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": achieved / peak, "traffic": ENC_BWD_DRAM_TRAFFIC, "traffic_source": ENC_BWD_DRAM_TRAFFIC_SRC,
-                             "peak_source": peak_src,
-                             "kernel": "msda_backward_kernel<bf16,f32,VEC=4,GS=8,NW=8> (encoder form, N=2 Lq=S=22223)",
+                             "frac": achieved / peak, "traffic": ri.get("traffic"), "traffic_source": ri.get("source"),
+                             "traffic_stale": ri.get("stale"), "peak_source": peak_src,
+                             "kernel": "encoder-form backward (N=2, Lq=S=22223, bf16 value / f32 loc+attn): "
+                                       "dense::msda_backward_dense_kernel<bf16,f32,D=32> (finest level's query tiles, "
+                                       "tcgen05 + TMEM) + msda_backward_kernel<bf16,f32,VEC=4,GS=8,NW=8> in split mode "
+                                       "(the coarser levels' queries); the two launches are timed as one",
                              "kernel_us_avg": kavg * 1e3, "kernel_us_min": kms[0] * 1e3,
                              "launches_timed": len(kms), "algorithmic_bytes_per_launch": r["enc_bwd_bytes"],
                              "step_frac_of_hbm": value / world / peak,
                              "binding_limit": {
-                                 "what": "SM->L2 request port / L2 fp32 reduction rate: the grad_value scatter is "
-                                         "4 corner rows x 128 B of red.global.add.v4.f32 per sample",
-                                 "scatter_bytes_per_launch": SCATTER_BYTES,
-                                 "scatter_bytes_issued_per_launch": SCATTER_BYTES_ISSUED,
-                                 "scatter_GBps": SCATTER_BYTES_ISSUED / (kavg * 1e-3) / 1e9,
-                                 "measured_ceiling_GBps": RED_CEILING_GBPS,
-                                 "frac_of_ceiling": SCATTER_BYTES_ISSUED / (kavg * 1e-3) / 1e9 / RED_CEILING_GBPS,
-                                 "issued_note": "12 % of the corner rows have weight 0 and are not sent (ncu sector "
-                                                "count of the same launch); the fraction is on the bytes sent",
-                                 "ceiling_source": "tools/micro/scatter_ceiling.cu -> profiles/r1_scatter_gather_ceilings.txt"},
-                             "note": "HBM is not the binding unit of this kernel (dram throughput 4-7 %); see DESIGN.md 5.2"},
+                                 "what": "not HBM (dram throughput < 10 %): the dense kernel is bound by the SM's L1 / "
+                                         "shared-memory data pipe and instruction issue (per-corner scalar work of one "
+                                         "thread per query row), the per-row kernel by the L2 fp32 reduction rate",
+                                 "red_sectors_per_launch": ri.get("red_sectors"),
+                                 "red_sectors_per_launch_round1": 80064552,
+                                 "dense_kernel_us_ncu": ri.get("dense_us"), "per_row_kernel_us_ncu": ri.get("rows_us"),
+                                 "l1_data_pipe_pct_dense": ri.get("l1_data_pipe_pct"),
+                                 "source": ri.get("source")},
+                             "note": "see DESIGN.md 5.2 / 5.5"},
                 "cpu_baseline": {"value": cpu["value"], "unit": UNIT, "cores": cpu["cores"], "kind": "port",
                                  "sample": cpu["sample"], "ms_per_sample": cpu["ms"]},
                 "clocks": r["clocks"]}
         if callers is not None:
             line["callers"] = callers
+        if sweep is not None:
+            line["sweep"] = sweep
         print(json.dumps(line), flush=True)
     if world > 1:
         torch.distributed.destroy_process_group()
