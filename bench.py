@@ -464,8 +464,9 @@ def measure_callers(rank, world, dev, frames=120, train_steps=10):
             self.query_embed = nn.Embedding(300, 2 * d)
 
         def forward(self, srcs, pos):
-            masks_ = [torch.zeros(s_.shape[0], s_.shape[2], s_.shape[3], dtype=torch.bool, device=s_.device) for s_ in srcs]
-            return self.transformer(srcs, masks_, pos, self.query_embed.weight, None)[0]
+            if getattr(self, "_masks", None) is None:      # equally sized images: no padding, the same mask tensors every step
+                self._masks = [torch.zeros(s_.shape[0], s_.shape[2], s_.shape[3], dtype=torch.bool, device=s_.device) for s_ in srcs]
+            return self.transformer(srcs, self._masks, pos, self.query_embed.weight, None)[0]
 
     torch.manual_seed(0)                                          # same initial weights on every rank
     model = Net().to(dev).train()

@@ -19,6 +19,8 @@ the kernels' wrappers -- there is no PyTorch fallback behind these classes.
 import copy
 import math
 
+import weakref
+
 import torch
 import torch.nn.functional as F
 from torch import nn
@@ -321,6 +323,31 @@ class DeformableTransformerDecoder(nn.Module):
         return output, reference_points
 
 
+_mask_lists = {}        # (id, version) of every per-level mask tensor -> True when none of them masks anything
+
+
+def _remember_no_padding(masks, mask_flatten):
+    """The flattened padding mask is a new tensor on every forward, so MSDeformAttn's per-tensor "masks nothing"
+    answer (one device->host read) would be asked again every frame -- and cannot be asked at all while a CUDA graph
+    is captured.  Callers that pass the SAME per-level mask tensors every time (a tracker on a fixed-size stream, a
+    graphed training step with static input buffers) get the answer from the first eager forward."""
+    from .ms_deform_attn import _mask_empty, _no_padding
+    if any(m.is_inference() for m in masks):
+        return
+    key = tuple((id(m), m._version) for m in masks)
+    hit = _mask_lists.get(key)
+    if hit is None:
+        if mask_flatten.is_cuda and torch.cuda.is_current_stream_capturing():
+            return
+        if len(_mask_lists) > 16:
+            _mask_lists.clear()
+        hit = _mask_lists[key] = (_no_padding(mask_flatten), [weakref.ref(m) for m in masks])
+    elif any(r() is not m for r, m in zip(hit[1], masks)):       # ids were reused by other tensors
+        _mask_lists.pop(key, None)
+        return
+    _mask_empty.put(mask_flatten, hit[0])
+
+
 _shape_tensors = {}     # (tuple of (H, W), device) -> int64 tensor, so every forward hands the SAME tensor object down
 
 
@@ -440,6 +467,7 @@ class DeformableTransformer(nn.Module):
             mask_l.append(mask.flatten(1))
             pos_l.append(pos.flatten(2).transpose(1, 2) + self.level_embed[lvl].view(1, 1, -1))
         src_flatten, mask_flatten, pos_flatten = torch.cat(src_l, 1), torch.cat(mask_l, 1), torch.cat(pos_l, 1)
+        _remember_no_padding(masks, mask_flatten)
         device = src_flatten.device
         spatial_shapes = _shapes_tensor(shapes, device)
         valid_ratios = torch.stack([self.get_valid_ratio(m) for m in masks], 1)

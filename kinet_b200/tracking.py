@@ -72,20 +72,27 @@ class DetectionHeads(nn.Module):
 
 
 def _nms(boxes, scores, thresh):
-    """Indices kept by greedy IoU suppression (torchvision.ops.nms semantics: IoU > thresh suppresses), on the host."""
+    """Indices kept by greedy IoU suppression (torchvision.ops.nms semantics: IoU > thresh suppresses), on the host.
+    One vectorised IoU matrix; the common case (nothing overlaps that much) returns without a Python loop."""
+    n = len(boxes)
+    if n <= 1:
+        return np.arange(n, dtype=np.int64)
+    x1, y1, x2, y2 = boxes[:, 0], boxes[:, 1], boxes[:, 2], boxes[:, 3]
+    area = np.clip(x2 - x1, 0, None) * np.clip(y2 - y1, 0, None)
+    iw = np.clip(np.minimum(x2[:, None], x2[None]) - np.maximum(x1[:, None], x1[None]), 0, None)
+    ih = np.clip(np.minimum(y2[:, None], y2[None]) - np.maximum(y1[:, None], y1[None]), 0, None)
+    inter = iw * ih
+    over = inter / np.maximum(area[:, None] + area[None] - inter, 1e-12) > thresh
+    np.fill_diagonal(over, False)
+    if not over.any():
+        return np.arange(n, dtype=np.int64)
     order = np.argsort(-scores, kind="stable")
-    area = np.clip(boxes[:, 2] - boxes[:, 0], 0, None) * np.clip(boxes[:, 3] - boxes[:, 1], 0, None)
+    dead = np.zeros(n, dtype=bool)
     keep = []
-    dead = np.zeros(len(boxes), dtype=bool)
     for i in order:
-        if dead[i]:
-            continue
-        keep.append(i)
-        xx1 = np.maximum(boxes[i, 0], boxes[:, 0]); yy1 = np.maximum(boxes[i, 1], boxes[:, 1])
-        xx2 = np.minimum(boxes[i, 2], boxes[:, 2]); yy2 = np.minimum(boxes[i, 3], boxes[:, 3])
-        inter = np.clip(xx2 - xx1, 0, None) * np.clip(yy2 - yy1, 0, None)
-        iou = inter / np.maximum(area[i] + area - inter, 1e-12)
-        dead |= iou > thresh
+        if not dead[i]:
+            keep.append(i)
+            dead |= over[i]
     return np.asarray(sorted(keep), dtype=np.int64)
 
 
@@ -171,22 +178,21 @@ class SequenceTracker:
     @torch.no_grad()
     def step(self, srcs, masks, pos_embeds):
         dev = srcs[0].device
+        if getattr(self, "_scale", None) is None or self._scale.device != dev:
+            self._scale = torch.tensor([self.img_w, self.img_h, self.img_w, self.img_h], device=dev)
         T = len(self.track_ids)
         targets = None
         if T:
             b = self.track_boxes                                   # xyxy px -> cxcywh normalised (tracker.py:299-304)
             cxcywh = torch.stack([(b[:, 0] + b[:, 2]) / 2, (b[:, 1] + b[:, 3]) / 2, b[:, 2] - b[:, 0], b[:, 3] - b[:, 1]], -1)
-            cxcywh = cxcywh / torch.tensor([self.img_w, self.img_h, self.img_w, self.img_h], device=dev)
-            targets = [{"track_query_boxes": cxcywh, "track_query_hs_embeds": self.track_hs}]
+            targets = [{"track_query_boxes": cxcywh / self._scale, "track_query_hs_embeds": self.track_hs}]
         hs, ref = self._run_transformer(srcs, masks, pos_embeds, targets)
         logits, boxes = self.heads(hs, ref)
         prob = logits.sigmoid()
         scores, labels = prob.max(-1)
         x, y, w, h = boxes.unbind(-1)
         xyxy = torch.stack([x - 0.5 * w, y - 0.5 * h, x + 0.5 * w, y + 0.5 * h], -1)
-        xyxy = xyxy * torch.tensor([self.img_w, self.img_h, self.img_w, self.img_h], device=dev)
-        lim = torch.tensor([self.img_w, self.img_h, self.img_w, self.img_h], device=dev)
-        xyxy = torch.minimum(xyxy.clamp(min=0), lim)               # clip_boxes_to_image
+        xyxy = torch.minimum((xyxy * self._scale).clamp(min=0), self._scale)     # scale to pixels, clip_boxes_to_image
         # ONE device -> host read per frame
         packed = torch.cat([scores[0, :, None], labels[0, :, None].to(scores.dtype), xyxy[0]], -1).cpu().numpy()
         sc, lb, bx = packed[:, 0], packed[:, 1].astype(np.int64), packed[:, 2:6].astype(np.float64)
