@@ -1,0 +1,63 @@
+#!/usr/bin/env python
+"""Kernel breakdown of the data-parallel training step bench.py measures (product API: DeformableTransformer at
+dropout 0.1, bf16 autocast, 800x1333 pyramid, batch 2), one eager step under the torch profiler.
+    python tools/train_profile.py [--top 40]"""
+import argparse
+import collections
+import os
+import sys
+
+import torch
+from torch import nn
+from torch.profiler import ProfilerActivity, profile
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from kinet_b200.modules import DeformableTransformer  # noqa: E402
+from kinet_b200.training import FlatParams, reference_param_groups  # noqa: E402
+from kinet_b200.workloads import PYRAMIDS  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--top", type=int, default=40)
+ap.add_argument("--dropout", type=float, default=0.1)
+args = ap.parse_args()
+dev = torch.device("cuda", 0)
+levels, d = PYRAMIDS["detr_800x1333"], 256
+torch.manual_seed(0)
+tr = DeformableTransformer(d, 8, 6, 6, 1024, args.dropout, "relu", False, len(levels), 4, 4).to(dev).train()
+qe = nn.Embedding(300, 2 * d).to(dev)
+net = nn.ModuleList([tr, qe])
+fp = FlatParams(net, groups=reference_param_groups(net))
+opt = torch.optim.AdamW(fp.optimizer_groups(), lr=2e-4, weight_decay=1e-4, fused=True)
+srcs = [torch.randn(2, d, h, w, device=dev) for h, w in levels]
+pos = [torch.randn(2, d, h, w, device=dev) * 0.1 for h, w in levels]
+masks = [torch.zeros(2, h, w, dtype=torch.bool, device=dev) for h, w in levels]
+target = torch.randn(2, 300, d, device=dev)
+
+
+def step():
+    fp.detach_grads()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        hs = tr(srcs, masks, pos, qe.weight, None)[0]
+    (hs.float() - target).square().mean().backward()
+    fp.gather_grads()
+    fp.clip_grad_norm_(0.1)
+    opt.step()
+    fp.refresh()
+
+
+for _ in range(3):
+    step()
+torch.cuda.synchronize()
+with profile(activities=[ProfilerActivity.CUDA]) as prof:
+    step()
+    torch.cuda.synchronize()
+agg = collections.defaultdict(lambda: [0.0, 0])
+for e in prof.events():
+    if e.device_type == torch.autograd.DeviceType.CUDA:
+        agg[e.name][0] += e.device_time
+        agg[e.name][1] += 1
+total = sum(v[0] for v in agg.values())
+print("training step (dropout %.2f): %.0f us of kernels, %d launches" % (args.dropout, total, sum(v[1] for v in agg.values())))
+for name, (us, n) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:args.top]:
+    print("%9.1f us %5.1f %%  x%-4d %s" % (us, 100 * us / total, n, name[:120]))
