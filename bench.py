@@ -440,9 +440,8 @@ def measure_callers(rank, world, dev, frames=120, train_steps=10):
         torch.distributed.barrier()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
-    for i in range(frames):
+    for _ in tracker.run((feeds[i & 7], masks, pos) for i in range(frames)):
         counts.append(len(tracker.track_ids) + nq)
-        tracker.step(feeds[i & 7], masks, pos)
     b.record()
     torch.cuda.synchronize()
     ms = reduce_max([a.elapsed_time(b)], dev, world)[0]
@@ -452,7 +451,8 @@ def measure_callers(rank, world, dev, frames=120, train_steps=10):
         "decoder_graph_buckets": tracker._graphs.recorded_buckets,
         "config": "kinet_b200.tracking.SequenceTracker: MOT17 750x1333 pyramid, S=20906, d=288 (D=36), 6 enc + 6 dec "
                   "layers, 500 object + T track queries (T changes every frame), bf16 autocast, FrameGraphs, one "
-                  "read-back per frame; one sequence per GPU"}
+                  "read-back per frame, the next frame's encoder enqueued before the host waits for it "
+                  "(SequenceTracker.run); one sequence per GPU"}
     del tracker, tr
     # ---- data-parallel training ----
     levels, d = PYRAMIDS["detr_800x1333"], 256

@@ -80,14 +80,28 @@ class FrameGraphs:
         graph.replay()
         return mem, valid_b, mask_b
 
+    def encode(self, src, pos, valid_ratios, padding_mask=None):
+        """Replay the encoder graph on a new frame.  The decoder graphs read its output buffer, so the call may be
+        issued as soon as the previous frame's decode() has been ENQUEUED (same stream): a tracker can start frame
+        t+1's encoder while the host is still reading frame t's results back."""
+        self._enc_out = self._encode(src, pos, valid_ratios, padding_mask)
+
+    def decode(self, tgt, reference_points, query_pos, query_attn_mask=None):
+        """Replay the decoder graph of the bucket that fits the query count, on the memory of the last encode()."""
+        return self._decode(self._enc_out, tgt, reference_points, query_pos, query_attn_mask)
+
     def __call__(self, src, pos, valid_ratios, tgt, reference_points, query_pos, padding_mask=None,
                  query_attn_mask=None):
         """src, pos (N, S, C); valid_ratios (N, L, 2); tgt, query_pos (N, Lq, C); reference_points (N, Lq, 2|4);
         padding_mask (N, S) bool or None (the choice is fixed at the first call); query_attn_mask (N, Lq) bool
         or None.  Returns (hs, reference_points_out, memory) like decoder(...) + encoder(...): hs is
         (N, Lq, C), or (layers, N, Lq, C) when the decoder returns intermediates."""
+        return self._decode(self._encode(src, pos, valid_ratios, padding_mask), tgt, reference_points, query_pos,
+                            query_attn_mask)
+
+    def _decode(self, enc_out, tgt, reference_points, query_pos, query_attn_mask):
         N, Lq, C = tgt.shape
-        mem, valid_b, mask_b = self._encode(src, pos, valid_ratios, padding_mask)
+        mem, valid_b, mask_b = enc_out
         B = max(self.bucket, -(-Lq // self.bucket) * self.bucket)
         if B not in self._dec:
             dev = tgt.device

@@ -154,13 +154,22 @@ class SequenceTracker:
                 return hs[-1], ref
             return hs, init_ref
         # graphs: the pyramid is fixed, the number of queries is not.  No padding in tracking frames (N = 1).
+        self._encode_graph(srcs, masks, pos_embeds)
+        return self._decode_graph(targets)
+
+    def _encode_graph(self, srcs, masks, pos_embeds):
+        tr = self.transformer
         src, pos, shapes = self._flatten(srcs, masks, pos_embeds)
         dev = src.device
         if self._graphs is None:
             self._graphs = FrameGraphs(tr.encoder, tr.decoder, _shapes_tensor(shapes, dev), bucket=self.bucket,
                                        autocast_dtype=self.autocast_dtype)
             self._valid = torch.ones(1, len(shapes), 2, device=dev)
-        c = src.shape[-1]
+        self._graphs.encode(src, pos, self._valid)
+
+    def _decode_graph(self, targets):
+        tr = self.transformer
+        c = self.query_embed.shape[1] // 2
         qpos, tgt = torch.split(self.query_embed, c, dim=1)
         qpos, tgt = qpos[None], tgt[None]
         ref = tr.reference_points(qpos).sigmoid()
@@ -169,32 +178,84 @@ class SequenceTracker:
             qpos = torch.cat([torch.zeros_like(prev_hs), qpos], 1)
             tgt = torch.cat([prev_hs, tgt], 1)
             ref = torch.cat([targets[0]["track_query_boxes"][None, :, :2], ref], 1)
-        hs, ref_out, _ = self._graphs(src, pos, self._valid, tgt, ref, qpos)
+        hs, ref_out, _ = self._graphs.decode(tgt, ref, qpos)
         if hs.dim() == 4:
             return hs[-1], (ref_out[-2] if ref_out.shape[0] > 1 else ref)
         return hs, ref
 
     # ---- one frame --------------------------------------------------------------------------------------------------
-    @torch.no_grad()
-    def step(self, srcs, masks, pos_embeds):
-        dev = srcs[0].device
+    def _targets(self, dev):
         if getattr(self, "_scale", None) is None or self._scale.device != dev:
             self._scale = torch.tensor([self.img_w, self.img_h, self.img_w, self.img_h], device=dev)
-        T = len(self.track_ids)
-        targets = None
-        if T:
-            b = self.track_boxes                                   # xyxy px -> cxcywh normalised (tracker.py:299-304)
-            cxcywh = torch.stack([(b[:, 0] + b[:, 2]) / 2, (b[:, 1] + b[:, 3]) / 2, b[:, 2] - b[:, 0], b[:, 3] - b[:, 1]], -1)
-            targets = [{"track_query_boxes": cxcywh / self._scale, "track_query_hs_embeds": self.track_hs}]
-        hs, ref = self._run_transformer(srcs, masks, pos_embeds, targets)
+        if not self.track_ids:
+            return None
+        b = self.track_boxes                                       # xyxy px -> cxcywh normalised (tracker.py:299-304)
+        cxcywh = torch.stack([(b[:, 0] + b[:, 2]) / 2, (b[:, 1] + b[:, 3]) / 2, b[:, 2] - b[:, 0], b[:, 3] - b[:, 1]], -1)
+        return [{"track_query_boxes": cxcywh / self._scale, "track_query_hs_embeds": self.track_hs}]
+
+    @torch.no_grad()
+    def step(self, srcs, masks, pos_embeds):
+        """One frame, start to finish (the device idles while the host reads the results and updates the tracks;
+        ``run`` overlaps that with the next frame's encoder)."""
+        dev = srcs[0].device
+        hs, ref = self._run_transformer(srcs, masks, pos_embeds, self._targets(dev))
+        hs, xyxy, packed = self._heads_and_pack(hs, ref)
+        return self._update_tracks(hs, xyxy, packed.cpu().numpy())          # ONE device -> host read per frame
+
+    @torch.no_grad()
+    def run(self, frames):
+        """Generator over a sequence, ``for result in tracker.run(frames)``: like calling step() on every frame, but
+        with the CUDA-graph path frame t+1's encoder (which does not depend on the tracks) is enqueued BEFORE the host
+        waits for frame t's results, so the read-back, the thresholding / NMS and the launches of the next decoder
+        hide behind ~60 % of a frame's device work.  Results are identical to step()'s."""
+        if not self.use_graphs:
+            for srcs, masks, pos_embeds in frames:
+                yield self.step(srcs, masks, pos_embeds)
+            return
+        it = iter(frames)
+        try:
+            cur = next(it)
+        except StopIteration:
+            return
+        dev = cur[0][0].device
+        side = torch.cuda.Stream(device=dev)
+        main = torch.cuda.current_stream(dev)
+        host_buf = None
+        self._encode_graph(*cur)
+        while cur is not None:
+            hs, ref = self._decode_graph(self._targets(dev))
+            hs, xyxy, packed = self._heads_and_pack(hs, ref)
+            if host_buf is None or host_buf.shape[0] < packed.shape[0]:
+                host_buf = torch.empty(packed.shape[0] + 256, 6, dtype=packed.dtype).pin_memory()
+            ready = torch.cuda.Event()
+            ready.record(main)
+            side.wait_event(ready)
+            with torch.cuda.stream(side):
+                host_buf[:packed.shape[0]].copy_(packed, non_blocking=True)
+                copied = torch.cuda.Event()
+                copied.record(side)
+            packed.record_stream(side)
+            nxt = next(it, None)
+            if nxt is not None:
+                self._encode_graph(*nxt)          # the device keeps working while the host reads frame t back
+            copied.synchronize()
+            yield self._update_tracks(hs, xyxy, host_buf[:packed.shape[0]].numpy().copy())
+            cur = nxt
+
+    def _heads_and_pack(self, hs, ref):
         logits, boxes = self.heads(hs, ref)
         prob = logits.sigmoid()
         scores, labels = prob.max(-1)
         x, y, w, h = boxes.unbind(-1)
         xyxy = torch.stack([x - 0.5 * w, y - 0.5 * h, x + 0.5 * w, y + 0.5 * h], -1)
         xyxy = torch.minimum((xyxy * self._scale).clamp(min=0), self._scale)     # scale to pixels, clip_boxes_to_image
-        # ONE device -> host read per frame
-        packed = torch.cat([scores[0, :, None], labels[0, :, None].to(scores.dtype), xyxy[0]], -1).cpu().numpy()
+        packed = torch.cat([scores[0, :, None], labels[0, :, None].to(scores.dtype), xyxy[0]], -1)
+        return hs, xyxy, packed
+
+    def _update_tracks(self, hs, xyxy, packed):
+        """Host side of a frame: packed = (Lq, 6) numpy [score, label, x1, y1, x2, y2] of all queries."""
+        dev = hs.device
+        T = len(self.track_ids)
         sc, lb, bx = packed[:, 0], packed[:, 1].astype(np.int64), packed[:, 2:6].astype(np.float64)
 
         # tracks (tracker.py:334-420): entry = [id, misses, query index this frame or -1 (stale), old row, box, score]

@@ -110,6 +110,11 @@ def test_tracking_loop_cuda_graphs_match_eager():
     graphed.reset()
     fc, _ = _run(graphed, 20)
     _compare(fa, fc, 1e-3)
+    # the pipelined generator (next frame's encoder enqueued before the read-back) gives the same results
+    from kinet_b200.tracking import synthetic_sequence
+    graphed.reset()
+    fp = list(graphed.run(synthetic_sequence(LEVELS, D, 20, dev, seed=0, drift=0.25)))
+    _compare(fa, fp, 1e-3)
     lowp = SequenceTracker(tr, heads, qe, use_graphs=True, bucket=8, autocast_dtype=torch.bfloat16, **kw)
     fd, _ = _run(lowp, 20)
     same = sum(sorted(a) == sorted(b) for a, b in zip(fa, fd))
