@@ -61,7 +61,7 @@ inline int check_common(const void* value, const int64_t* shapes, const void* lo
     // 32-bit element offsets inside one batch item
     if ((long long)d->S * d->M * d->D >= (1ll << 31)) return MSDA_E_SHAPE;
     if ((long long)d->L * d->P >= (1 << 20)) return MSDA_E_SHAPE;
-    // 32-bit work-unit counters in the kernels (cta_work_range)
+    // 32-bit item / row indices in the kernels (forward_items, backward_items: item = chunk * N * M + b * M + m)
     if ((long long)d->N * d->M * d->Lq >= (1ll << 30)) return MSDA_E_SHAPE;
     if (!value || !shapes) return MSDA_E_NULL;
     if (d->Lq > 0 && (!loc || !attn)) return MSDA_E_NULL;
