@@ -51,7 +51,9 @@ def _check_grads(grads, ref_grads, shapes, loc, tol):
     m = _smooth_mask(shapes, loc)
     masked = 1.0 - float(m.mean()) if m.size else 0.0
     # the kink mask must stay a rounding-noise filter: a regression cannot hide behind it
-    assert masked < 0.005 or m.size < 4000, ("kink-masked fraction of grad_sampling_loc", masked)
+    # (16-bit locations have 8 / 11 significant bits: loc * W - 0.5 is an integer far more often than for fp32 ones)
+    limit = 0.05 if loc.dtype in (torch.bfloat16, torch.float16) else 0.005
+    assert masked < limit or m.size < 4000, ("kink-masked fraction of grad_sampling_loc", masked)
     names = ("grad_value", "grad_sampling_loc", "grad_attn_weight")
     for i, (got, ref) in enumerate(zip(grads, ref_grads)):
         got = got.float().cpu().numpy() if got.dtype in (torch.bfloat16, torch.float16) else got.cpu().numpy()
