@@ -59,6 +59,7 @@ extern "C" {
 #define MSDA_E_NULL (-3)    /* required pointer is NULL */
 #define MSDA_E_ALIGN (-4)   /* pointer not 16-byte aligned */
 #define MSDA_E_WORKSPACE (-5) /* workspace too small */
+#define MSDA_E_SCRATCH_LIMIT (-6) /* msda_b200_backward_static_scratch: the call needs more than MSDA_B200_STATIC_SCRATCH_BYTES */
 
 #define MSDA_MAX_LEVELS 16
 
@@ -101,6 +102,36 @@ int msda_b200_backward(const void *value, int value_dtype,
                        void *grad_value, void *grad_sampling_loc, void *grad_attn_weight,
                        void *workspace, size_t workspace_bytes,
                        const msda_dims *dims, void *stream);
+
+/* ---- Backward without a workspace and without any allocation ---------------------------------------
+ * No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, results and return codes as msda_b200_backward minus `workspace` / `workspace_bytes`:
+ * the scratch the 16-bit backward needs (fp32 grad_value accumulator + the dense-window kernel's counter
+ * and flags, i.e. msda_b200_backward_workspace_bytes) lives in ONE file-scope `static __device__` array of
+ * MSDA_B200_STATIC_SCRATCH_BYTES inside the library image; every GPU that loads the library holds it
+ * until the process exits.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library
+ * routine); the array's device address is resolved once per device (cudaGetSymbolAddress, with that
+ * device current) on the first call.
+ *   - a call that needs more scratch than the array holds returns MSDA_E_SCRATCH_LIMIT and launches
+ *     nothing (32 MiB: N*S*M*D <= ~8.3 M value elements, e.g. the tracking configuration N=1, S=20906,
+ *     M=8, D=36; the 800x1333 training batch N=2, D=32 needs 91 MB -> use msda_b200_backward);
+ *   - every call on a device shares the array and finds the previous call's contents in it; the part a
+ *     call uses is zero-filled on `stream` before its kernels, so calls that are ordered on the GPU
+ *     (same stream, or streams ordered by events) are independent of each other;
+ *   - calls that OVERLAP on the GPU (different streams, no ordering between them; concurrent graph
+ *     launches; several host threads with their own streams) race on the array and produce garbage:
+ *     serialise them or use msda_b200_backward with one workspace per stream;
+ *   - f32 values need no scratch (the call equals msda_b200_backward with a NULL workspace); f64 is not
+ *     offered here (MSDA_E_DTYPE). */
+#define MSDA_B200_STATIC_SCRATCH_BYTES (32u * 1024u * 1024u)
+
+int msda_b200_backward_static_scratch(const void *value, int value_dtype,
+                                      const int64_t *spatial_shapes, const int64_t *level_start,
+                                      const void *sampling_loc, const void *attn_weight, int aux_dtype,
+                                      const void *grad_output,
+                                      void *grad_value, void *grad_sampling_loc, void *grad_attn_weight,
+                                      const msda_dims *dims, void *stream);
 
 /* ---- Fused module prologue -------------------------------------------------
  * The reference's MSDeformAttn.forward (ops/modules/ms_deform_attn.py:69-82) materialises softmax'ed

@@ -28,10 +28,12 @@ class MsdaFusedInputs(ctypes.Structure):
 
 
 MSDA_E_SHAPE = -2
+MSDA_E_SCRATCH_LIMIT = -6
+STATIC_SCRATCH_BYTES = 32 * 1024 * 1024       # MSDA_B200_STATIC_SCRATCH_BYTES
 
 EXPORTS = ("msda_b200_abi_version", "msda_b200_error_string", "msda_b200_forward",
            "msda_b200_forward_fused", "msda_b200_backward_fused",
-           "msda_b200_backward_workspace_bytes", "msda_b200_backward",
+           "msda_b200_backward_workspace_bytes", "msda_b200_backward", "msda_b200_backward_static_scratch",
            "msda_b200_last_launch_count", "msda_b200_trace_next")
 # include/kinet_layers_b200.h (glue kernels of the layers that call the op)
 LAYER_EXPORTS = ("kinet_b200_add_layernorm_forward", "kinet_b200_add_layernorm_backward",
@@ -89,6 +91,8 @@ def load():
     lib.msda_b200_backward.restype = i
     lib.msda_b200_backward.argtypes = [vp, i, vp, vp, vp, vp, i, vp, vp, vp, vp, vp,
                                        ctypes.c_size_t, dp, vp]
+    lib.msda_b200_backward_static_scratch.restype = i
+    lib.msda_b200_backward_static_scratch.argtypes = [vp, i, vp, vp, vp, vp, i, vp, vp, vp, vp, dp, vp]
     fp = ctypes.POINTER(MsdaFusedInputs)
     lib.msda_b200_forward_fused.restype = i
     lib.msda_b200_forward_fused.argtypes = [vp, i, vp, vp, fp, i, vp, dp, vp]

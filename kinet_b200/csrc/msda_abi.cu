@@ -36,6 +36,9 @@ const char* msda_b200_error_string(int code)
         case MSDA_E_NULL: return "msda_b200: required pointer is NULL";
         case MSDA_E_ALIGN: return "msda_b200: pointer is not 16-byte aligned";
         case MSDA_E_WORKSPACE: return "msda_b200: workspace missing or too small";
+        case MSDA_E_SCRATCH_LIMIT:
+            return "msda_b200: the call needs more scratch than the static array of msda_b200_backward_static_scratch "
+                   "holds (MSDA_B200_STATIC_SCRATCH_BYTES); use msda_b200_backward with a workspace";
         default: break;
     }
     if (code > 0) return cudaGetErrorString((cudaError_t)code);
