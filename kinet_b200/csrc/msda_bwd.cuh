@@ -275,6 +275,7 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, const FineT
     const int coarse = d.Lq - skip_len;
     const int walk_items = ((coarse + d.tile_q - 1) / d.tile_q) * d.N * d.M;
     const int tile_items = split ? ft.total * d.N * d.M : 0;
+    bool waited = false;
     for (;;) {
         if (threadIdx.x == 0) *s_claim = atomicAdd(split_claim, 1);
         __syncthreads();
@@ -295,6 +296,9 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, const FineT
                 });
         } else {
             const int it = item - walk_items;
+            // the flags are the dense-window kernel's: wait for it (no-op unless this grid was launched as its
+            // programmatic dependent, and after the first time)
+            if (!waited) { asm volatile("griddepcontrol.wait;" ::: "memory"); waited = true; }
             if (deferred[it] == 0) continue;
             const int tile = it / (d.N * d.M);
             const int bm = it - tile * (d.N * d.M);
@@ -305,6 +309,8 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, const FineT
                 b, m, kTileQueries, [&](int i) { return fine_tile_query(ft, lt, r, i, d.Lq); });
         }
     }
+    // this grid must not complete before the dense-window kernel has (the rounding pass is ordered behind this grid)
+    if (!waited) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool FUSED>

@@ -303,6 +303,9 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
     __shared__ __align__(8) uint64_t s_mbar[2];   // dot products ready / scatter product ready
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // The per-row kernel behind this one is its programmatic dependent (launch_backward_vec_impl): release it now, so its
+    // CTAs move in as soon as CTAs of this grid retire.  It waits for this grid before it reads the deferred-item flags.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     stage_levels(lt, shapes, level_start, d);
     build_fine_tiles(ft, &s_scratch, lt, d.L, da.tiles_bound);
 

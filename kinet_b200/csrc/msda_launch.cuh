@@ -220,6 +220,25 @@ int launch_backward_vec_impl(const void* value, const int64_t* shapes, const int
         TraceScope trace(st);
         kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
                                        (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, deferred, tiles_bound, split_claim);
+    } else if (deferred && env_int("MSDA_B200_PDL", 1)) {
+        // Programmatic dependent launch behind the dense-window kernel, which releases its dependents as soon as it
+        // starts: CTAs of this grid become resident as dense CTAs retire and do the coarse levels' queries (independent
+        // of the dense kernel: commutative reductions, rows of their own) while the last dense items finish; they wait
+        // for the dense kernel (griddepcontrol.wait) only before they read its deferred-item flags.
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(grid);
+        cfg.blockDim = dim3(NW * 32);
+        cfg.dynamicSmemBytes = 0;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
+                                           (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, deferred, tiles_bound, split_claim);
+        ++g_last_launches;
+        return (int)e;
     } else {
         kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
                                        (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, deferred, tiles_bound, split_claim);
