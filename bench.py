@@ -504,6 +504,18 @@ def measure_callers(rank, world, dev, frames=120, train_steps=10):
                   "6 enc + 6 dec layers, 300 queries, batch 2 per GPU, dropout 0.1, bf16 autocast, fwd+bwd + gradient "
                   "clipping 0.1 + AdamW with the reference's 3 learning-rate groups; two CUDA graphs + one NCCL "
                   "gradient all-reduce per step; synthetic MSE loss (matcher / set criterion are the reference's)"}
+    del step, model
+    # ---- the literal `kine` path: detection-token transformer, no MSDeformAttn in it ----
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "tools"))
+    import kine_bench
+    k = kine_bench.measure(dev, frames=200, seed=rank)
+    ms = reduce_max([k["fused_graphs_ms_per_frame"]], dev, world)[0]
+    out["kine_frames_per_s"] = {
+        "value": world * 1e3 / ms, "ms_per_frame_per_gpu": ms, "graphs_recorded": k["graphs_recorded"],
+        "same_parameters_through_stock_pytorch_modules_ms": {"eager": k["plain_eager_ms"], "one_cuda_graph": k["plain_graph_ms"]},
+        "config": "kinet_b200.modules.kinematic_transformer.DualKinematicTransformer + class / box heads through "
+                  "kinet_b200.frame_graph.KineFrameGraphs: " + k["config"] + ", " + k["dtype"] +
+                  "; token and track-query counts change every frame; one sequence per GPU"}
     return out
 
 

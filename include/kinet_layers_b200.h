@@ -85,6 +85,47 @@ int kinet_b200_colsum(const void* a, int32_t a_dtype, int64_t rows, int32_t C,
 int kinet_b200_relu_backward_colsum(const void* dy, const void* h, int32_t dtype, int64_t rows, int32_t C,
                                     void* dh, void* out, int32_t out_dtype, float* partial, void* stream);
 
+/* ---- attention core of nn.MultiheadAttention for short sequences: the `kine` path ----
+ *
+ * Replaces, inside the reference's KinematicTransformer / DualKinematicTransformer
+ * (src/trackformer/models/transformer.py:85-185), what nn.MultiheadAttention does between its input and output
+ * projections in TransformerEncoderLayer.forward_post (:331-333) and TransformerDecoderLayer.forward_post
+ * (:393-401): out[n][i][h][:] = sum_j softmax_j(scale * <q[n][i][h], k[n][j][h]> + (-inf if key j is masked)) v[n][j][h][:]
+ * for <= 150 object + T tracklet tokens, 8 heads of 36 channels (cfgs/train_kinet.yaml:17-18).  The projections stay
+ * cuBLAS GEMMs.  fp32 arithmetic for every storage type; D <= KINET_MHA_MAX_D; any Lq, Lk (keys are walked in tiles
+ * with an online softmax).  A query whose keys are ALL masked yields 0 (torch >= 2.5; torch 1.5 returned NaN).
+ *
+ * Element (n, i, h, c) of q lives at q + n * q_batch_stride + i * q_row_stride + h * D + c (elements): batch-first
+ * and sequence-first layouts, and slices of a packed q|k|v GEMM output, are all expressible.  Same for k, v, out. */
+#define KINET_MHA_MAX_D 64
+
+typedef struct kinet_mha_args {
+    const void* q; const void* k; const void* v;
+    int64_t q_batch_stride, q_row_stride, k_batch_stride, k_row_stride, v_batch_stride, v_row_stride;
+    const uint8_t* key_padding_mask;   /* [N][Lk], nonzero = key masked; NULL = none                              */
+    void* out;                         /* element (n, i, h, c) at out + n * out_batch_stride + i * out_row_stride + h * D + c */
+    int64_t out_batch_stride, out_row_stride;
+    float* lse;                        /* optional [N][H][Lq] fp32: log-sum-exp of the scaled logits (the backward reads it) */
+    int32_t dtype;                     /* MSDA_F32 / MSDA_BF16 / MSDA_F16: q, k, v, out (and the backward's tensors)  */
+    int32_t N, H, D, Lq, Lk;
+    float scale;                       /* 1 / sqrt(D) for nn.MultiheadAttention                                   */
+} kinet_mha_args;
+
+int kinet_b200_small_mha_forward(const kinet_mha_args* args, void* stream);
+
+/* Backward: fwd holds the forward's arguments (out and lse as the forward wrote them).  dq [N][Lq][H*D], dk and dv
+ * [N][Lk][H*D] are contiguous, element type fwd.dtype, fully overwritten; two kernels (dK / dV per key tile, dQ per
+ * query tile), probabilities recomputed from lse, one writer per element (no atomics: bit-reproducible).
+ * Rows whose keys were all masked get zero gradients. */
+typedef struct kinet_mha_bwd_args {
+    kinet_mha_args fwd;
+    const void* dout;                  /* gradient of out, addressed like out with its own strides                 */
+    int64_t dout_batch_stride, dout_row_stride;
+    void* dq; void* dk; void* dv;
+} kinet_mha_bwd_args;
+
+int kinet_b200_small_mha_backward(const kinet_mha_bwd_args* args, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

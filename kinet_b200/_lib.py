@@ -37,7 +37,9 @@ EXPORTS = ("msda_b200_abi_version", "msda_b200_error_string", "msda_b200_forward
            "msda_b200_last_launch_count", "msda_b200_trace_next")
 # include/kinet_layers_b200.h (glue kernels of the layers that call the op)
 LAYER_EXPORTS = ("kinet_b200_add_layernorm_forward", "kinet_b200_add_layernorm_backward",
-                 "kinet_b200_colsum_partial_floats", "kinet_b200_colsum", "kinet_b200_relu_backward_colsum")
+                 "kinet_b200_colsum_partial_floats", "kinet_b200_colsum", "kinet_b200_relu_backward_colsum",
+                 "kinet_b200_small_mha_forward", "kinet_b200_small_mha_backward")
+MHA_MAX_D = 64                                 # KINET_MHA_MAX_D
 
 
 class KinetLnFwdArgs(ctypes.Structure):
@@ -66,6 +68,30 @@ class KinetLnBwdArgs(ctypes.Structure):
                 ("dgamma_dbeta", ctypes.c_void_p),
                 ("partial", ctypes.c_void_p),
                 ("rows", ctypes.c_int64), ("C", ctypes.c_int32)]
+
+
+
+class KinetMhaArgs(ctypes.Structure):
+    _fields_ = [("q", ctypes.c_void_p), ("k", ctypes.c_void_p), ("v", ctypes.c_void_p),
+                ("q_batch_stride", ctypes.c_int64), ("q_row_stride", ctypes.c_int64),
+                ("k_batch_stride", ctypes.c_int64), ("k_row_stride", ctypes.c_int64),
+                ("v_batch_stride", ctypes.c_int64), ("v_row_stride", ctypes.c_int64),
+                ("key_padding_mask", ctypes.c_void_p),
+                ("out", ctypes.c_void_p),
+                ("out_batch_stride", ctypes.c_int64), ("out_row_stride", ctypes.c_int64),
+                ("lse", ctypes.c_void_p),
+                ("dtype", ctypes.c_int32),
+                ("N", ctypes.c_int32), ("H", ctypes.c_int32), ("D", ctypes.c_int32),
+                ("Lq", ctypes.c_int32), ("Lk", ctypes.c_int32),
+                ("scale", ctypes.c_float)]
+
+
+class KinetMhaBwdArgs(ctypes.Structure):
+    _fields_ = [("fwd", KinetMhaArgs),
+                ("dout", ctypes.c_void_p),
+                ("dout_batch_stride", ctypes.c_int64), ("dout_row_stride", ctypes.c_int64),
+                ("dq", ctypes.c_void_p), ("dk", ctypes.c_void_p), ("dv", ctypes.c_void_p)]
+
 
 _lib = None
 
@@ -112,6 +138,10 @@ def load():
     lib.kinet_b200_relu_backward_colsum.restype = i
     lib.kinet_b200_relu_backward_colsum.argtypes = [vp, vp, ctypes.c_int32, ctypes.c_int64, ctypes.c_int32, vp, vp,
                                                     ctypes.c_int32, vp, vp]
+    lib.kinet_b200_small_mha_forward.restype = i
+    lib.kinet_b200_small_mha_forward.argtypes = [ctypes.POINTER(KinetMhaArgs), vp]
+    lib.kinet_b200_small_mha_backward.restype = i
+    lib.kinet_b200_small_mha_backward.argtypes = [ctypes.POINTER(KinetMhaBwdArgs), vp]
     if lib.msda_b200_abi_version() != 2:
         raise RuntimeError("kinet_b200: libmsda_b200.so ABI version mismatch")
     _lib = lib

@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libmsda_b200.so")
-SOURCES = ["msda_abi.cu", "msda_inst_f32.cu", "msda_inst_bf16.cu", "msda_inst_f16.cu", "msda_static.cu", "layer_ops.cu"]
+SOURCES = ["msda_abi.cu", "msda_inst_f32.cu", "msda_inst_bf16.cu", "msda_inst_f16.cu", "msda_static.cu", "layer_ops.cu", "small_mha.cu"]
 HEADERS = ["msda_common.cuh", "msda_fwd.cuh", "msda_bwd.cuh", "msda_dense.cuh", "msda_launch.cuh",
            os.path.join("..", "..", "include", "msda_b200.h"),
            os.path.join("..", "..", "include", "kinet_layers_b200.h")]

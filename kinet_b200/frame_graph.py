@@ -129,3 +129,78 @@ class FrameGraphs:
         graph.replay()
         self.replays += 1
         return hs[..., :Lq, :], ref_out[..., :Lq, :], mem.x
+
+
+class KineFrameGraphs:
+    """Per-frame CUDA graphs for the `kine` detector (modules.kinematic_detector.KinematicDetectorTransformer around
+    modules.kinematic_transformer.DualKinematicTransformer; reference detr.py:288-417, transformer.py:145-185).
+
+    A frame brings T detection tokens and K track queries, both changing from frame to frame.  Tokens are padded up to
+    a multiple of ``token_bucket`` and switched off with the model's own key-padding ``mask`` (what the reference's
+    NestedTensor batching does); track queries are padded up to a multiple of ``track_bucket`` at the FRONT of the
+    query list with rows that nothing reads back -- padded queries still act as keys of the decoder's self-attention,
+    which has no padding mask on this path (transformer.py:393-395 passes tgt_key_padding_mask=None), so exact
+    per-frame parity with an unpadded run needs ``track_bucket=1``; the default buckets trade that for a handful of
+    graphs.  One graph per (padded T, padded K); inputs are copied into static buffers, outputs are views of static
+    buffers valid until the next call.  Inference only."""
+
+    def __init__(self, transformer, heads, token_bucket=32, track_bucket=1, autocast_dtype=torch.bfloat16, warmup=2):
+        self.transformer, self.heads = transformer, heads
+        self.token_bucket, self.track_bucket = int(token_bucket), int(track_bucket)
+        self.autocast_dtype, self.warmup = autocast_dtype, int(warmup)
+        self._graphs = {}
+        self.replays = 0
+
+    def reset(self):
+        self._graphs = {}
+
+    @property
+    def recorded_buckets(self):
+        return sorted(self._graphs)
+
+    def __call__(self, src_det, src_meta, pos_det, pos_meta, tgt_det=None, tgt_meta=None):
+        """src_* / pos_* (1, T, C) token embeddings; tgt_* (K, 1, C) projected track-query embeddings or None.
+        ``heads(hs_det, hs_meta)`` maps the transformer's (layers, 1, K + num_queries, C) outputs to what the caller
+        wants back.  Returns heads' output computed on the padded problem with the K padding rows removed by the
+        caller's ``heads`` (it receives ``pad_k`` as a keyword)."""
+        T, C = src_det.shape[1], src_det.shape[2]
+        K = 0 if tgt_det is None else tgt_det.shape[0]
+        Tp = -(-T // self.token_bucket) * self.token_bucket
+        Kp = -(-K // self.track_bucket) * self.track_bucket
+        key = (Tp, Kp)
+        dev = src_det.device
+        if key not in self._graphs:
+            bufs = dict(src_det=torch.zeros(1, Tp, C, device=dev), src_meta=torch.zeros(1, Tp, C, device=dev),
+                        pos_det=torch.zeros(1, Tp, C, device=dev), pos_meta=torch.zeros(1, Tp, C, device=dev),
+                        mask=torch.ones(1, Tp, dtype=torch.bool, device=dev),
+                        tgt_det=torch.zeros(Kp, 1, C, device=dev), tgt_meta=torch.zeros(Kp, 1, C, device=dev))
+
+            def fn():
+                with torch.no_grad(), torch.autocast("cuda", dtype=self.autocast_dtype,
+                                                     enabled=self.autocast_dtype is not None):
+                    return self.heads(self.transformer, bufs, Kp)
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(self.warmup):
+                    fn()
+            torch.cuda.current_stream().wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                out = fn()
+            self._graphs[key] = (graph, bufs, out)
+        graph, bufs, out = self._graphs[key]
+        for name, t in (("src_det", src_det), ("src_meta", src_meta), ("pos_det", pos_det), ("pos_meta", pos_meta)):
+            bufs[name][:, :T].copy_(t, non_blocking=True)
+        bufs["mask"][:, :T] = False
+        if Tp > T:
+            bufs["mask"][:, T:] = True
+        if K:
+            bufs["tgt_det"][Kp - K:].copy_(tgt_det, non_blocking=True)
+            bufs["tgt_meta"][Kp - K:].copy_(tgt_meta, non_blocking=True)
+        if Kp > K:
+            bufs["tgt_det"][:Kp - K].zero_()
+            bufs["tgt_meta"][:Kp - K].zero_()
+        graph.replay()
+        self.replays += 1
+        return out, Kp - K

@@ -1,0 +1,197 @@
+#!/usr/bin/env python
+"""Frames/s of the literal KineT (`kine`) transformer path at the reference's configuration (cfgs/train_kinet.yaml:
+hidden_dim 288, 8 heads, 1 encoder + 1 decoder layer, 150 object queries; dim_feedforward 2048, cfgs/train.yaml:51):
+
+  fused    kinet_b200.modules.kinematic_transformer.DualKinematicTransformer + the detector heads, recorded into
+           per-(tokens, track queries) CUDA graphs (kinet_b200.frame_graph.KineFrameGraphs)
+  plain    the same parameters through nn.MultiheadAttention / nn.LayerNorm / nn.Linear written as the reference's
+           forward_post does (src/trackformer/models/transformer.py:323-339, :385-407, :483-487), eager and as one
+           CUDA graph
+
+Synthetic detection tokens (T ~ 100-150 per frame, changing every frame) and K ~ 20-60 track queries; bf16 autocast
+(--fp32 for fp32).  Prints one JSON line.
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+import torch.nn.functional as F
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def build(dev, d=288, nq=150):
+    from kinet_b200.modules.kinematic_detector import MLP
+    from kinet_b200.modules.kinematic_transformer import DualKinematicTransformer
+    torch.manual_seed(0)
+    tr = DualKinematicTransformer(d_model=d, nhead=8, num_encoder_layers=1, num_decoder_layers=1, dim_feedforward=2048,
+                                  dropout=0.1, return_intermediate_dec=True).to(dev).eval()
+    mods = torch.nn.ModuleDict(dict(class_embed=torch.nn.Linear(d, 2), bbox_embed=MLP(d, d, 4, 3),
+                                    query_embed_det=torch.nn.Embedding(nq, d),
+                                    query_embed_metadata=torch.nn.Embedding(nq, d))).to(dev).eval()
+    return tr, mods
+
+
+def make_heads(mods):
+    from kinet_b200.functions.layer_ops import linear
+
+    def heads(transformer, bufs, Kp):
+        qd = F.pad(mods["query_embed_det"].weight[:, None], (0, 0, 0, 0, Kp, 0))
+        qm = F.pad(mods["query_embed_metadata"].weight[:, None], (0, 0, 0, 0, Kp, 0))
+        nq = mods["query_embed_det"].weight.shape[0]
+        td = F.pad(bufs["tgt_det"], (0, 0, 0, 0, 0, nq)) if Kp else None
+        tm = F.pad(bufs["tgt_meta"], (0, 0, 0, 0, 0, nq)) if Kp else None
+        hs_det, hs_meta, _, _ = transformer(bufs["src_det"], bufs["src_meta"], bufs["mask"], qd, qm, td, tm,
+                                            bufs["pos_det"], bufs["pos_meta"])
+        return linear(hs_meta[-1], mods["class_embed"]).float(), mods["bbox_embed"](hs_det[-1]).float().sigmoid(), hs_det[-1]
+    return heads
+
+
+def plain_forward(tr, mods, src_b, src_m, mask, qd, qm, td, tm, pos_b, pos_m):
+    """The reference's arithmetic on the same parameters with stock PyTorch modules (sequence-first inside)."""
+    def enc_layer(l, src, pos):
+        q = src + pos
+        src = l.norm1(src + l.self_attn(q, q, value=src, key_padding_mask=mask, need_weights=False)[0])
+        return l.norm2(src + l.linear2(F.relu(l.linear1(src))))
+
+    def dec_layer(l, tgt, mem, pos, qpos):
+        q = tgt + qpos
+        tgt = l.norm1(tgt + l.self_attn(q, q, value=tgt, need_weights=False)[0])
+        tgt = l.norm2(tgt + l.multihead_attn(tgt + qpos, mem + pos, value=mem, key_padding_mask=mask, need_weights=False)[0])
+        return l.norm3(tgt + l.linear2(F.relu(l.linear1(tgt))))
+
+    def one(t, src, pos, qe, tgt):
+        src, pos = src.permute(1, 0, 2), pos.permute(1, 0, 2)
+        tgt = torch.zeros_like(qe) if tgt is None else tgt
+        for l in t.encoder.layers:
+            src = enc_layer(l, src, pos)
+        inter = []
+        for l in t.decoder.layers:
+            tgt = dec_layer(l, tgt, src, pos, qe)
+            inter.append(tgt)
+        return t.decoder.norm(torch.stack(inter))
+
+    def branch(b, s1, s2):
+        return b.norm(F.relu(torch.cat([b.linear_input1(s1), b.linear_input2(s2)], -1)) + s1)
+    hd = one(tr.transformer_det, src_b, pos_b, qd, td)
+    hm = one(tr.transformer_metadata, src_m, pos_m, qm, tm)
+    hd = branch(tr.detection_branch, hd, hm)
+    hm = branch(tr.metadata_branch, hm, hd)
+    hd, hm = hd.transpose(1, 2), hm.transpose(1, 2)
+    x = hd[-1]
+    for i, layer in enumerate(mods["bbox_embed"].layers):
+        x = F.relu(layer(x)) if i < 2 else layer(x)
+    return mods["class_embed"](hm[-1]).float(), x.float().sigmoid(), hd[-1]
+
+
+def measure(dev, frames=200, fp32=False, nq=150, d=288, seed=0):
+    from kinet_b200.frame_graph import KineFrameGraphs
+    tr, mods = build(dev, d, nq)
+    amp = None if fp32 else torch.bfloat16
+    g = torch.Generator(device=dev).manual_seed(seed)
+    sizes = [(100 + (37 * i) % 51, 20 + (13 * i) % 41) for i in range(16)]        # (tokens, track queries) per frame
+    feeds = []
+    for T, K in sizes:
+        feeds.append(tuple(torch.randn(1, T, d, device=dev, generator=g) for _ in range(4)) +
+                     tuple(torch.randn(K, 1, d, device=dev, generator=g) for _ in range(2)))
+    fg = KineFrameGraphs(tr, make_heads(mods), token_bucket=32, track_bucket=16, autocast_dtype=amp)
+    for f in feeds:
+        fg(*f)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(frames):
+        out, pad = fg(*feeds[i & 15])
+    b.record()
+    torch.cuda.synchronize()
+    fused_ms = a.elapsed_time(b) / frames
+
+    # plain PyTorch modules on the same parameters: eager (what the reference runs) and one graph at a fixed size
+    T, K = 150, 48
+    src_b, src_m, pos_b, pos_m = (torch.randn(1, T, d, device=dev, generator=g) for _ in range(4))
+    mask = torch.zeros(1, T, dtype=torch.bool, device=dev)
+    qd = F.pad(mods["query_embed_det"].weight[:, None], (0, 0, 0, 0, K, 0)).detach()
+    qm = F.pad(mods["query_embed_metadata"].weight[:, None], (0, 0, 0, 0, K, 0)).detach()
+    td = F.pad(torch.randn(K, 1, d, device=dev, generator=g), (0, 0, 0, 0, 0, nq))
+    tm = F.pad(torch.randn(K, 1, d, device=dev, generator=g), (0, 0, 0, 0, 0, nq))
+
+    def plain():
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16, enabled=not fp32):
+            return plain_forward(tr, mods, src_b, src_m, mask, qd, qm, td, tm, pos_b, pos_m)
+
+    def fused_fixed():
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16, enabled=not fp32):
+            hd, hm, _, _ = tr(src_b, src_m, mask, qd, qm, td, tm, pos_b, pos_m)
+            return hd
+
+    def timed(fn, n):
+        for _ in range(5):
+            fn()
+        torch.cuda.synchronize()
+        a.record()
+        for _ in range(n):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / n
+
+    def graphed(fn):
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            fn(); fn()
+        torch.cuda.current_stream().wait_stream(s)
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            fn()
+        return gr.replay
+    with torch.no_grad():
+        want = plain()[2]
+        got = fused_fixed()[-1]
+    err = float((got.float() - want.float()).abs().max() / want.float().abs().max())
+    res = dict(fused_graphs_ms_per_frame=fused_ms, fused_frames_per_s=1e3 / fused_ms,
+               graphs_recorded=len(fg.recorded_buckets),
+               plain_eager_ms=timed(plain, 50), plain_graph_ms=timed(graphed(plain), 200),
+               fused_eager_ms=timed(fused_fixed, 50), fused_graph_fixed_ms=timed(graphed(fused_fixed), 200),
+               fused_vs_plain_max_rel=err, dtype="fp32" if fp32 else "bf16 autocast",
+               config="DualKinematicTransformer d=288, 8 heads (D=36), 1+1 layers, ffn 2048, %d object queries + K "
+                      "track queries (20-60), T detection tokens (100-150), batch 1" % nq)
+    return res
+
+
+def profile(dev, fp32):
+    """Kernel breakdown (torch profiler, eager) of one fused and one plain frame at T = 150, K = 48."""
+    from torch.profiler import ProfilerActivity, profile as prof
+    d, nq, T, K = 288, 150, 150, 48
+    tr, mods = build(dev, d, nq)
+    g = torch.Generator(device=dev).manual_seed(0)
+    src_b, src_m, pos_b, pos_m = (torch.randn(1, T, d, device=dev, generator=g) for _ in range(4))
+    mask = torch.zeros(1, T, dtype=torch.bool, device=dev)
+    qd = F.pad(mods["query_embed_det"].weight[:, None], (0, 0, 0, 0, K, 0)).detach()
+    td = F.pad(torch.randn(K, 1, d, device=dev, generator=g), (0, 0, 0, 0, 0, nq))
+    for name, fn in (("fused", lambda: tr(src_b, src_m, mask, qd, qd, td, td, pos_b, pos_m)),
+                     ("plain", lambda: plain_forward(tr, mods, src_b, src_m, mask, qd, qd, td, td, pos_b, pos_m))):
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16, enabled=not fp32):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize()
+            with prof(activities=[ProfilerActivity.CUDA]) as pr:
+                for _ in range(10):
+                    fn()
+                torch.cuda.synchronize()
+        print("==", name, "fp32" if fp32 else "bf16", "(10 frames)")
+        print(pr.key_averages().table(sort_by="cuda_time_total", row_limit=18, max_name_column_width=70))
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--frames", type=int, default=200)
+    ap.add_argument("--fp32", action="store_true")
+    ap.add_argument("--profile", action="store_true")
+    a = ap.parse_args()
+    if a.profile:
+        profile(torch.device("cuda:0"), a.fp32)
+        sys.exit(0)
+    print(json.dumps(measure(torch.device("cuda:0"), a.frames, a.fp32)))
