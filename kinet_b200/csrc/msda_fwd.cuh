@@ -42,7 +42,14 @@ __device__ __forceinline__ void gather_sample(float (&acc)[VEC], const VT* lane_
 // WIDE: every level has W > 1, so the column step of the 2x2 footprint is the same for all samples.
 // FUSED: `loc` / `attn` are the module's raw sampling offsets / attention logits and the prologue
 // (softmax, location arithmetic) runs in the owner lanes (SampleSrc<AT, true>, msda_common.cuh).
-template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE, bool FUSED>
+// DCH: channels per head.  DCH == VEC * GS: the GS lanes of a row tile its channels exactly.  DCH < VEC * GS
+// ("overhang"; 16-bit D = 36 with 5 lanes of 8 channels): a (pixel, head) row of 72 bytes starts on a 16-byte
+// boundary for even heads and 8 bytes past one for odd heads (M even), so the five 16-byte lanes cover
+// [row, row + 80) for even heads and [row - 8, row + 72) for odd heads -- always inside the pixel's M rows, always
+// aligned -- and the 4 channels a group reads beyond its row (the neighbouring head's) are accumulated into
+// registers that are never stored.  Six rows per warp instruction with 16-byte loads instead of three with 8-byte
+// loads (GS = 9, VEC = 4).
+template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE, bool FUSED, int DCH>
 __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_a, int* stage_dx,
                                               float4* stage_b,
                                               const VT* __restrict__ value,
@@ -52,12 +59,14 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_
     constexpr int GPW = 32 / GS;           // rows per warp
     constexpr int RS = record_stride(GS);  // records per sample in the shared-memory tap arrays
     constexpr int CH = chunk_of(GS);       // samples prepared per chunk (owner lanes gl < CH)
-    constexpr int D = VEC * GS;
+    constexpr int D = DCH;
+    constexpr bool OVERHANG = DCH != VEC * GS;
+    static_assert(!OVERHANG || (VEC == 8 && VEC * GS - DCH == 4 && sizeof(VT) == 2), "overhang: one half vector beyond the row");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int grp = lane / GS, gl = lane - grp * GS;
     const bool lane_used = grp < GPW;
     const int LP = d.L * d.P;
-    const int rsv = d.M * GS;              // vectors between neighbouring pixels
+    const int rsv = d.M * D / VEC;         // vectors between neighbouring pixels (overhang: M is even)
     const int chunks = (d.Lq + d.tile_q - 1) / d.tile_q;
     const int items = chunks * d.N * d.M;
     constexpr int PASS = NWARPS * GPW;     // query rows per CTA pass
@@ -66,7 +75,8 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_
         const int chunk = item / (d.N * d.M);
         const int bm = item - chunk * (d.N * d.M);
         const int b = bm / d.M, m = bm - b * d.M;
-        const VT* lane_base = value + ((size_t)b * d.S * d.M + m) * D + gl * VEC;
+        const int shift = (OVERHANG && (m & 1)) ? -(VEC / 2) : 0;   // odd heads: the aligned window starts 4 channels early
+        const VT* lane_base = value + ((size_t)b * d.S * d.M + m) * D + shift + gl * VEC;
 
         const int pos0 = chunk * d.tile_q;
         const int count = min(d.tile_q, d.Lq - pos0);
@@ -119,12 +129,22 @@ __device__ __forceinline__ void forward_items(const LevelTable& lt, int2* stage_
                                            rb.z, rb.w);
                 }
             }
-            if (row_ok) VecIO<VT, VEC>::store(out + row * D + gl * VEC, acc);
+            if (row_ok) {
+                VT* o = out + row * D + shift + gl * VEC;
+                if constexpr (!OVERHANG) {
+                    VecIO<VT, VEC>::store(o, acc);
+                } else {
+                    // the lane holding the neighbouring head's 4 channels stores its own half only
+                    if (shift == 0 && gl == GS - 1) VecIO<VT, VEC / 2>::store(o, *reinterpret_cast<float(*)[VEC / 2]>(&acc[0]));
+                    else if (shift != 0 && gl == 0) VecIO<VT, VEC / 2>::store(o + VEC / 2, *reinterpret_cast<float(*)[VEC / 2]>(&acc[VEC / 2]));
+                    else VecIO<VT, VEC>::store(o, acc);
+                }
+            }
         }
     }
 }
 
-template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool FUSED>
+template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool FUSED, int DCH = VEC * GS>
 __global__ void __launch_bounds__(NWARPS * 32, MSDA_FWD_MINB)
 msda_forward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ shapes,
                     const int64_t* __restrict__ level_start, const AT* __restrict__ loc,
@@ -138,10 +158,10 @@ msda_forward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ sh
     __shared__ float4 stage_b[NWARPS][record_count(GS)];
     const int warp = threadIdx.x >> 5;
     if (lt.min_w > 1)
-        forward_items<VT, AT, VEC, GS, NWARPS, true, FUSED>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc,
+        forward_items<VT, AT, VEC, GS, NWARPS, true, FUSED, DCH>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc,
                                                             attn, out, d, fa);
     else
-        forward_items<VT, AT, VEC, GS, NWARPS, false, FUSED>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc,
+        forward_items<VT, AT, VEC, GS, NWARPS, false, FUSED, DCH>(lt, stage_a[warp], stage_dx[warp], stage_b[warp], value, loc,
                                                              attn, out, d, fa);
 }
 

@@ -126,13 +126,13 @@ inline int item_grid(const KernelDims& k)
 
 // fa == nullptr: loc / attn are materialised sampling locations / attention weights;
 // otherwise they are raw offsets / logits and *fa carries the rest of the module prologue's inputs.
-template <typename VT, typename AT, int VEC, int GS, bool FUSED>
+template <typename VT, typename AT, int VEC, int GS, bool FUSED, int DCH = VEC * GS>
 int launch_forward_vec_impl(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
                             const void* attn, void* out, const msda_dims* d, cudaStream_t st, const FusedArgs& fa)
 {
     constexpr int NW = 8;
     const KernelDims k = make_dims(d, NW * (32 / GS), kForwardTileQ);
-    auto kern = msda_forward_kernel<VT, AT, VEC, GS, NW, FUSED>;
+    auto kern = msda_forward_kernel<VT, AT, VEC, GS, NW, FUSED, DCH>;
     const int grid = item_grid(k);
     {
         TraceScope trace(st);
@@ -143,15 +143,15 @@ int launch_forward_vec_impl(const void* value, const int64_t* shapes, const int6
     return (int)cudaGetLastError();
 }
 
-template <typename VT, typename AT, int VEC, int GS>
+template <typename VT, typename AT, int VEC, int GS, int DCH = VEC * GS>
 int launch_forward_vec(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
                        const void* attn, void* out, const msda_dims* d, cudaStream_t st, const FusedArgs* fa)
 {
     if (fa) {
         if (d->L * d->P > kFusedMaxChunks * chunk_of(GS)) return MSDA_E_SHAPE;   // a lane keeps <= 4 softmax numerators per row
-        return launch_forward_vec_impl<VT, AT, VEC, GS, true>(value, shapes, ls, loc, attn, out, d, st, *fa);
+        return launch_forward_vec_impl<VT, AT, VEC, GS, true, DCH>(value, shapes, ls, loc, attn, out, d, st, *fa);
     }
-    return launch_forward_vec_impl<VT, AT, VEC, GS, false>(value, shapes, ls, loc, attn, out, d, st, FusedArgs{});
+    return launch_forward_vec_impl<VT, AT, VEC, GS, false, DCH>(value, shapes, ls, loc, attn, out, d, st, FusedArgs{});
 }
 
 template <typename VT, typename AT, typename ACC>
@@ -190,7 +190,17 @@ int forward_typed(const void* value, const int64_t* shapes, const int64_t* ls, c
         if (al) switch (d->D) {
             case 16: return launch_forward_vec<VT, AT, 8, 2>(value, shapes, ls, loc, attn, out, d, st, fa);
             case 32: return launch_forward_vec<VT, AT, 8, 4>(value, shapes, ls, loc, attn, out, d, st, fa);
-            case 36: return launch_forward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, out, d, st, fa);
+            case 36:
+                // 5 lanes of 8 channels on 16-byte windows (msda_fwd.cuh, "overhang") when the heads come in pairs, fused,
+                // the row's samples fit four chunks of 4, and there are enough rows to fill the machine with 48-row passes
+                // (C3-enc 109 -> 97 us; the 560-query decoder form is latency-bound and loses with half as many CTAs:
+                // 20.6 -> 26.6 us); else 9 lanes of 4 channels
+                if ((d->M & 1) == 0 && (!fa || d->L * d->P <= kFusedMaxChunks * chunk_of(5)) &&
+                    ((long long)d->N * d->M * d->Lq >= 48ll * 8 * (device_info().sms > 0 ? device_info().sms : 148) ||
+                     env_int("MSDA_B200_D36_WIDE", 0)) &&
+                    !env_int("MSDA_B200_D36_NARROW", 0))
+                    return launch_forward_vec<VT, AT, 8, 5, 36>(value, shapes, ls, loc, attn, out, d, st, fa);
+                return launch_forward_vec<VT, AT, 4, 9>(value, shapes, ls, loc, attn, out, d, st, fa);
             case 64: return launch_forward_vec<VT, AT, 8, 8>(value, shapes, ls, loc, attn, out, d, st, fa);
             default: break;
         }

@@ -156,6 +156,40 @@ def test_16bit_matches_oracle(case, dtype, aux_same):
     _check_grads(grads, ref_grads, shapes, loc, tol)
 
 
+D36_WIDE_CASES = [
+    # (N, M, Lq or None = encoder form, levels, P): the 16-bit D = 36 forward with 5 lanes of 8 channels on 16-byte
+    # windows (msda_fwd.cuh "overhang"): even and odd heads read 4 channels of the neighbouring head's row, which
+    # must never reach the output; forced here for small shapes (the launcher picks it for >= 57 k rows)
+    (2, 8, None, [(13, 21), (7, 11), (4, 6), (2, 3)], 4),
+    (1, 2, 53, [(9, 1), (1, 7), (3, 3), (1, 1)], 4),                  # W == 1 / H == 1 levels, ragged passes
+    (3, 4, 7, [(5, 6), (3, 3)], 3),                                   # fewer samples than a chunk row
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("case", D36_WIDE_CASES)
+def test_d36_wide_forward_matches_oracle_and_narrow(case, dtype, monkeypatch):
+    from kinet_b200.functions import ms_deform_attn_forward
+    dev = _dev()
+    N, M, Lq, levels, P = case
+    S = sum(h * w for h, w in levels)
+    value, shapes, loc, attn, go = _random_case(dev, N, M, 36, Lq or S, levels, P, dtype=dtype, aux=torch.float32,
+                                                spread=1.1)
+    # neighbouring heads carry large values: a leak of their channels into a row's output would be visible
+    value = value.clone()
+    value[:, :, 1::2] *= 50.0
+    monkeypatch.setenv("MSDA_B200_D36_NARROW", "1")
+    narrow = ms_deform_attn_forward(value, shapes, loc, attn, 64)
+    monkeypatch.delenv("MSDA_B200_D36_NARROW")
+    monkeypatch.setenv("MSDA_B200_D36_WIDE", "1")
+    wide = ms_deform_attn_forward(value, shapes, loc, attn, 64)
+    ref_out, _ = _oracle64(value, shapes, loc, attn, go)
+    assert wide.dtype == dtype
+    assert _relerr(wide.float().cpu().numpy(), ref_out) <= 1.2e-2
+    # same fp32 arithmetic per channel, same rounding: the two lane mappings agree to the last bit
+    assert torch.equal(wide, narrow)
+
+
 def test_fp64_generic_matches_oracle():
     dev = _dev()
     value, shapes, loc, attn, go = _random_case(dev, 2, 2, 4, 5, [(12, 8), (6, 4), (3, 2)], 2,
@@ -411,13 +445,20 @@ FUSED_CASES = [
     (2, 4, 64, 19, [(6, 5), (3, 3)], 2, False, torch.float32),
     (2, 8, 32, 57, [(12, 17), (6, 9), (3, 5), (2, 3)], 2, True, torch.bfloat16),
     (2, 8, 32, 57, [(12, 17), (6, 9), (3, 5), (2, 3)], 4, True, torch.float16),
+    # 16-bit D = 36 with the 5-lane "overhang" forward forced (msda_fwd.cuh): softmax over 5-lane groups, 4 chunks of 4
+    (2, 8, 36, 57, [(12, 17), (6, 9), (3, 5), (2, 3)], 2, True, torch.bfloat16, {"MSDA_B200_D36_WIDE": "1"}),
+    (1, 4, 36, 31, [(12, 17), (6, 9), (3, 5), (2, 3)], 4, False, torch.float16, {"MSDA_B200_D36_WIDE": "1"}),
 ]
 
 
 @pytest.mark.parametrize("case", FUSED_CASES)
-def test_fused_prologue_matches_unfused(case):
+def test_fused_prologue_matches_unfused(case, monkeypatch):
     from kinet_b200.functions import MSDeformAttnFusedFunction, fused_supported
     dev = _dev()
+    if len(case) == 9:
+        for k_, v_ in case[8].items():
+            monkeypatch.setenv(k_, v_)
+        case = case[:8]
     N, M, D, Lq, levels, ref_dim, masked, dtype = case
     L, P = len(levels), 4
     S = sum(h * w for h, w in levels)
