@@ -80,7 +80,7 @@ int msda_b200_forward(const void* value, int value_dtype, const int64_t* spatial
 size_t msda_b200_backward_workspace_bytes(int value_dtype, const msda_dims* d)
 {
     if (!d) return 0;
-    // fp32 accumulator + the dense-window kernel's work counter and deferred-item flags; nothing for sparse query
+    // fp32 accumulator + the dense-window kernel's work counter and done-item flags; nothing for sparse query
     // sets, which accumulate in the 16-bit output itself
     if (value_dtype == MSDA_BF16 || value_dtype == MSDA_F16) {
         if (sparse_16bit_regime(d)) return 0;

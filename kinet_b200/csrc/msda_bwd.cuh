@@ -238,10 +238,10 @@ __device__ __forceinline__ void backward_rows(const LevelTable& lt, int2* stage_
 // One work item per CTA (grid == items; the loop only guards against a capped grid): item = (chunk of tile_q
 // positions of the query walk, batch, head), see walk_query.
 //
-// Split mode (deferred != nullptr; the dense-window kernel of msda_dense.cuh ran before on the same stream): the
-// queries of the finest level belong to the dense kernel, which flags the (tile, batch, head) items it did not do
-// (windows too large for its chunks).  This kernel is then a persistent grid that claims, from a zero-initialised
-// counter, (1) chunks of tile_q walk positions of the OTHER levels' queries and (2) the flagged tiles.  (The host
+// Split mode (dense_done != nullptr; the dense-window kernel of msda_dense.cuh ran before on the same stream): the
+// queries of the finest level belong to the dense kernel, which flags the (tile, batch, head) items it has done
+// (it leaves those whose windows are too large for its chunks).  This kernel is then a persistent grid that claims, from a
+// zero-initialised counter, (1) chunks of tile_q walk positions of the OTHER levels' queries and (2) the unflagged tiles.  (The host
 // does not know where the finest level's queries start -- the shapes live in device memory -- so it cannot size a
 // one-item-per-CTA grid for them.)
 template <typename VT, typename AT, int VEC, int GS, int NWARPS, bool WIDE, bool FUSED>
@@ -252,9 +252,9 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, const FineT
                                                const VT* __restrict__ grad_out,
                                                float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
                                                AT* __restrict__ grad_attn, const KernelDims& d, const FusedArgs& fa,
-                                               const uint8_t* __restrict__ deferred, int* __restrict__ split_claim, int* s_claim)
+                                               const uint8_t* dense_done, int* __restrict__ split_claim, int* s_claim)
 {
-    if (deferred == nullptr) {
+    if (dense_done == nullptr) {
         const int chunks = (d.Lq + d.tile_q - 1) / d.tile_q;
         const int items = chunks * d.N * d.M;
         for (int item = blockIdx.x; item < items; item += gridDim.x) {
@@ -276,12 +276,16 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, const FineT
     const int walk_items = ((coarse + d.tile_q - 1) / d.tile_q) * d.N * d.M;
     const int tile_items = split ? ft.total * d.N * d.M : 0;
     bool waited = false;
+    // The next claim is issued BEFORE the current item is processed and read after it: the counter's atomic queues
+    // behind this SM's outstanding reductions (1-2 us), which the item's own work hides.
+    if (threadIdx.x == 0) *s_claim = atomicAdd(split_claim, 1);
+    __syncthreads();
+    int item = *s_claim;
     for (;;) {
-        if (threadIdx.x == 0) *s_claim = atomicAdd(split_claim, 1);
-        __syncthreads();
-        const int item = *s_claim;
-        __syncthreads();
+        __syncthreads();                     // every thread has read *s_claim
         if (item >= walk_items + tile_items) break;
+        int next_claim = 0;
+        if (threadIdx.x == 0) next_claim = atomicAdd(split_claim, 1);
         if (item < walk_items) {
             const int chunk = item / (d.N * d.M);
             const int bm = item - chunk * (d.N * d.M);
@@ -299,15 +303,21 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, const FineT
             // the flags are the dense-window kernel's: wait for it (no-op unless this grid was launched as its
             // programmatic dependent, and after the first time)
             if (!waited) { asm volatile("griddepcontrol.wait;" ::: "memory"); waited = true; }
-            if (deferred[it] == 0) continue;
-            const int tile = it / (d.N * d.M);
-            const int bm = it - tile * (d.N * d.M);
-            const int b = bm / d.M, m = bm - b * d.M;
-            const TileRect r = fine_tile_rect(ft, lt, tile);
-            backward_rows<VT, AT, VEC, GS, NWARPS, WIDE, FUSED>(
-                lt, stage_a, stage_dx, stage_b, fold, value, loc, attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa,
-                b, m, kTileQueries, [&](int i) { return fine_tile_query(ft, lt, r, i, d.Lq); });
+            // (written by the dense-window grid while THIS grid is already resident: a coherent load -- the read-only
+            // data path, which `const __restrict__` invites, may serve a line cached before that grid finished)
+            if (*reinterpret_cast<const volatile uint8_t*>(dense_done + it) == 0) {
+                const int tile = it / (d.N * d.M);
+                const int bm = it - tile * (d.N * d.M);
+                const int b = bm / d.M, m = bm - b * d.M;
+                const TileRect r = fine_tile_rect(ft, lt, tile);
+                backward_rows<VT, AT, VEC, GS, NWARPS, WIDE, FUSED>(
+                    lt, stage_a, stage_dx, stage_b, fold, value, loc, attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa,
+                    b, m, kTileQueries, [&](int i) { return fine_tile_query(ft, lt, r, i, d.Lq); });
+            }
         }
+        if (threadIdx.x == 0) *s_claim = next_claim;
+        __syncthreads();
+        item = *s_claim;
     }
     // this grid must not complete before the dense-window kernel has (the rounding pass is ordered behind this grid)
     if (!waited) asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -320,13 +330,13 @@ msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ s
                      const AT* __restrict__ attn, const VT* __restrict__ grad_out,
                      float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
                      AT* __restrict__ grad_attn, const KernelDims d, const FusedArgs fa,
-                     const uint8_t* __restrict__ deferred, int tiles_bound, int* __restrict__ split_claim)
+                     const uint8_t* dense_done, int tiles_bound, int* __restrict__ split_claim)
 {
     __shared__ LevelTable lt;
     __shared__ FineTiles ft;
     __shared__ int ft_scratch, s_claim;
     stage_levels(lt, shapes, level_start, d);
-    if (deferred != nullptr) build_fine_tiles(ft, &ft_scratch, lt, d.L, tiles_bound);
+    if (dense_done != nullptr) build_fine_tiles(ft, &ft_scratch, lt, d.L, tiles_bound);
     __shared__ int2 stage_a[NWARPS][record_count(GS)];
     __shared__ int stage_dx[NWARPS][record_count(GS)];
     __shared__ float4 stage_b[NWARPS][record_count(GS)];
@@ -335,10 +345,10 @@ msda_backward_kernel(const VT* __restrict__ value, const int64_t* __restrict__ s
     const int warp = threadIdx.x >> 5;
     if (lt.min_w > 1)
         backward_items<VT, AT, VEC, GS, NWARPS, true, FUSED>(lt, ft, stage_a[warp], stage_dx[warp], stage_b[warp], fold[warp], value, loc,
-                                                             attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa, deferred, split_claim, &s_claim);
+                                                             attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa, dense_done, split_claim, &s_claim);
     else
         backward_items<VT, AT, VEC, GS, NWARPS, false, FUSED>(lt, ft, stage_a[warp], stage_dx[warp], stage_b[warp], fold[warp], value, loc,
-                                                              attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa, deferred, split_claim, &s_claim);
+                                                              attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa, dense_done, split_claim, &s_claim);
 }
 
 // fp32 workspace -> 16-bit grad_value (one rounding of the full sum).

@@ -93,7 +93,7 @@ __device__ __forceinline__ int walk_query(const LevelTable& t, const KernelDims&
 // its tiles look into windows of their own size in their own level and smaller ones in every coarser level) and
 // cuts that level's query grid into nty x ntx balanced tiles of at most kTileQueries queries; the tile height is
 // chosen to minimise tiles x window area (halo of kTileHalo pixels around the tile: offsets of a few pixels).
-// The per-row kernel processes every other query, and the tiles the dense kernel hands back (deferred flags).
+// The per-row kernel processes every other query, and the tiles the dense kernel leaves (done flags).
 constexpr int kTileQueries = 128;
 constexpr int kTileHalo = 12;
 struct FineTiles {

@@ -30,8 +30,8 @@
 //
 // Division of labour with msda_bwd.cuh (launched right after this kernel, same stream, split mode): this kernel
 // takes the tiles of the FINEST level's queries -- their windows are compact in every level -- and flags the
-// (tile, batch, head) items whose windows would still need more than kMaxItemChunks chunks (arbitrary sampling
-// locations); the per-row kernel processes the flagged tiles and all queries of the coarser levels (a tile of a
+// (tile, batch, head) items it has done; items whose windows would still need more than kMaxItemChunks chunks (arbitrary
+// sampling locations) are left unflagged; the per-row kernel processes the unflagged tiles and all queries of the coarser levels (a tile of a
 // coarse level looks into windows 2x, 4x, ... its own size in the finer levels with ~1 corner per pixel: nothing to
 // aggregate).  The result never depends on locality, only the speed does.
 #pragma once
@@ -276,7 +276,7 @@ template <> struct LevelIO<__half> : LevelIO16<__half> {};
 
 struct DenseArgs {
     int* claim;                    // zero-initialised work counter (in the caller's workspace)
-    uint8_t* deferred;             // zero-initialised, [tiles_bound * N * M]: 1 = item left to the per-row kernel
+    uint8_t* done;                 // zero-initialised, [tiles_bound * N * M]: 1 = item done here; the per-row kernel does the rest
     int tiles_bound;
 };
 
@@ -299,12 +299,13 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
     __shared__ int s_box[NW][kMaxLevels][4];
     __shared__ int s_win[kMaxLevels][5];       // ymin, xmin, wh, ww, chunks
     __shared__ int s_item[2];
+    __shared__ int s_bail[2];                  // decided when the item in the same slot was claimed: stop (see below)
     __shared__ uint32_t s_tmem;
     __shared__ __align__(8) uint64_t s_mbar[2];   // dot products ready / scatter product ready
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     // The per-row kernel behind this one is its programmatic dependent (launch_backward_vec_impl): release it now, so its
-    // CTAs move in as soon as CTAs of this grid retire.  It waits for this grid before it reads the deferred-item flags.
+    // CTAs move in as soon as CTAs of this grid retire.  It waits for this grid before it reads the done-item flags.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     stage_levels(lt, shapes, level_start, d);
     build_fine_tiles(ft, &s_scratch, lt, d.L, da.tiles_bound);
@@ -326,6 +327,7 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
         asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(&s_mbar[1])), "r"(1u));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         s_item[0] = atomicAdd(da.claim, 1);
+        s_bail[0] = 0;
     }
     tmem_fence_before();
     __syncthreads();
@@ -344,8 +346,19 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
     for (int item = s_item[0]; item < items; item = s_item[slot]) {
         DT_MARK(0)
         // claim the next item now; it is read after the barrier that ends this one
-        if (tid == 0) s_item[slot ^ 1] = atomicAdd(da.claim, 1);
+        if (tid == 0) {
+            s_item[slot ^ 1] = atomicAdd(da.claim, 1);
+            // Sampling locations without locality (windows beyond kMaxItemChunks chunks everywhere): once at least 64
+            // items were left to the per-row kernel and they outnumber the items done here 8 : 1, this CTA stops --
+            // items nobody marks done are the per-row kernel's -- and the grid is gone after about one window search
+            // per CTA, which frees its SMs (a dense CTA pair holds every register of its SM) for the per-row kernel.
+            // (da.claim[2] / [3]: items done / left, zeroed with the work counter.)
+            const int n_back = *reinterpret_cast<volatile int*>(da.claim + 3), n_done = *reinterpret_cast<volatile int*>(da.claim + 2);
+            s_bail[slot ^ 1] = n_back >= 64 && n_back >= 8 * n_done;
+        }
+        const bool bail = s_bail[slot] != 0;
         slot ^= 1;
+        if (bail) break;
 
         // ---- item -> (tile, batch, head) -> this thread's query -------------------------------------------------
         const int tile = item / (d.N * d.M);
@@ -471,7 +484,7 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
         for (int l = 0; l < d.L; ++l) total_chunks += s_win[l][4];
         if (total_chunks > kMaxItemChunks) {
             // windows too large for dense chunks: the per-row kernel does this item
-            if (tid == 0) da.deferred[item] = 1;
+            if (tid == 0) atomicAdd(da.claim + 3, 1);
             __syncthreads();
             continue;
         }
@@ -794,6 +807,7 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
             }
         }
         // G / Gt / the window table are rewritten by the next item
+        if (tid == 0) { da.done[item] = 1; atomicAdd(da.claim + 2, 1); }
         tmem_fence_before();
         __syncthreads();
     }

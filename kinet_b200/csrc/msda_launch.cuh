@@ -209,13 +209,13 @@ int forward_typed(const void* value, const int64_t* shapes, const int64_t* ls, c
     return launch_forward_generic<VT, AT, float>(value, shapes, ls, loc, attn, out, d, st);
 }
 
-// deferred != nullptr: split mode, after the dense-window kernel (see backward_items); the grid then also covers
+// dense_done != nullptr: split mode, after the dense-window kernel (see backward_items); the grid then also covers
 // the tile items.  traced: this launch is the one msda_b200_trace_next brackets.
 template <typename VT, typename AT, int VEC, int GS, bool FUSED>
 int launch_backward_vec_impl(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
                              const void* attn, const void* go, float* gv_acc, void* gl, void* ga,
                              const msda_dims* d, cudaStream_t st, const FusedArgs& fa,
-                             const uint8_t* deferred = nullptr, int tiles_bound = 0, bool traced = true,
+                             const uint8_t* dense_done = nullptr, int tiles_bound = 0, bool traced = true,
                              int* split_claim = nullptr, bool acc16 = false)
 {
     constexpr int NW = 8;
@@ -224,17 +224,17 @@ int launch_backward_vec_impl(const void* value, const int64_t* shapes, const int
     auto kern = msda_backward_kernel<VT, AT, VEC, GS, NW, FUSED>;
     const int sms = device_info().sms > 0 ? device_info().sms : 148;
     // split mode: a persistent grid claims (64-row chunks of the coarse levels' queries, then the flagged tiles)
-    if (deferred) k.tile_q = 64 / (NW * (32 / GS)) * (NW * (32 / GS)) > 0 ? 64 / (NW * (32 / GS)) * (NW * (32 / GS)) : NW * (32 / GS);
-    const int grid = deferred ? MSDA_BWD_MINB * sms : item_grid(k);
+    if (dense_done) k.tile_q = 64 / (NW * (32 / GS)) * (NW * (32 / GS)) > 0 ? 64 / (NW * (32 / GS)) * (NW * (32 / GS)) : NW * (32 / GS);
+    const int grid = dense_done ? MSDA_BWD_MINB * sms : item_grid(k);
     if (traced) {
         TraceScope trace(st);
         kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, deferred, tiles_bound, split_claim);
-    } else if (deferred && env_int("MSDA_B200_PDL", 1)) {
+                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, dense_done, tiles_bound, split_claim);
+    } else if (dense_done && env_int("MSDA_B200_PDL", 1)) {
         // Programmatic dependent launch behind the dense-window kernel, which releases its dependents as soon as it
         // starts: CTAs of this grid become resident as dense CTAs retire and do the coarse levels' queries (independent
         // of the dense kernel: commutative reductions, rows of their own) while the last dense items finish; they wait
-        // for the dense kernel (griddepcontrol.wait) only before they read its deferred-item flags.
+        // for the dense kernel (griddepcontrol.wait) only before they read its done-item flags.
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(grid);
         cfg.blockDim = dim3(NW * 32);
@@ -246,12 +246,12 @@ int launch_backward_vec_impl(const void* value, const int64_t* shapes, const int
         cfg.attrs = attr;
         cfg.numAttrs = 1;
         cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                                           (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, deferred, tiles_bound, split_claim);
+                                           (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, dense_done, tiles_bound, split_claim);
         ++g_last_launches;
         return (int)e;
     } else {
         kern<<<grid, NW * 32, 0, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
-                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, deferred, tiles_bound, split_claim);
+                                       (const VT*)go, gv_acc, (AT*)gl, (AT*)ga, k, fa, dense_done, tiles_bound, split_claim);
     }
     ++g_last_launches;
     return (int)cudaGetLastError();
@@ -299,7 +299,7 @@ inline bool sparse_16bit_regime(const msda_dims* d)
 }
 
 // Encoder-form backward on the tensor cores (msda_dense.cuh) + the per-row kernel in split mode for the rest.
-// Behind the fp32 accumulator the caller's workspace holds the dense kernel's work counter and the deferred-item
+// Behind the fp32 accumulator the caller's workspace holds the dense kernel's work counter and the dense_done-item
 // flags (one byte per (tile, batch, head)); one memset zeroes all three.
 inline size_t dense_counter_offset(size_t nval) { return (nval * sizeof(float) + 255) & ~(size_t)255; }
 constexpr size_t kDenseCounterBytes = 256;
@@ -312,7 +312,7 @@ inline size_t dense_extra_bytes(const msda_dims* d)
 template <typename VT, typename AT, int D, bool FUSED>
 int launch_backward_dense(const void* value, const int64_t* shapes, const int64_t* ls, const void* loc,
                           const void* attn, const void* go, float* gv_acc, void* gl, void* ga, int* claim,
-                          uint8_t* deferred, const msda_dims* d, cudaStream_t st, const FusedArgs& fa)
+                          uint8_t* dense_done, const msda_dims* d, cudaStream_t st, const FusedArgs& fa)
 {
     KernelDims k = make_dims(d, 16, kBackwardTileQ);
     auto kern = dense::msda_backward_dense_kernel<VT, AT, D, FUSED>;
@@ -328,7 +328,7 @@ int launch_backward_dense(const void* value, const int64_t* shapes, const int64_
     const int sms = device_info().sms > 0 ? device_info().sms : 148;
     dense::DenseArgs da;
     da.claim = claim;
-    da.deferred = deferred;
+    da.done = dense_done;
     da.tiles_bound = dense_tiles_bound(d);
     TraceScope trace(st);       // the group of launches is "the backward kernel" of msda_b200_trace_next
     kern<<<2 * sms, dense::kThreads, smem, st>>>((const VT*)value, shapes, ls, (const AT*)loc, (const AT*)attn,
@@ -337,7 +337,7 @@ int launch_backward_dense(const void* value, const int64_t* shapes, const int64_
     if (cudaError_t e = cudaGetLastError()) return (int)e;
     // the queries of the coarser levels, and whatever the dense kernel handed back
     return launch_backward_vec_impl<VT, AT, 4, D / 4, FUSED>(value, shapes, ls, loc, attn, go, gv_acc, gl, ga, d, st, fa,
-                                                             deferred, da.tiles_bound, false, claim + 1);
+                                                             dense_done, da.tiles_bound, false, claim + 1);
 }
 
 // VT = float: gradients accumulate straight into grad_value (zero-filled first).
@@ -384,13 +384,13 @@ int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, 
         if constexpr (sizeof(VT) == 2) {
             if (dense_ok) {
                 int* claim = reinterpret_cast<int*>(reinterpret_cast<char*>(ws) + dense_counter_offset(nval));
-                uint8_t* deferred = reinterpret_cast<uint8_t*>(claim) + kDenseCounterBytes;
+                uint8_t* dense_done = reinterpret_cast<uint8_t*>(claim) + kDenseCounterBytes;
                 if (fa) {
-                    if (d->D == 32) rc = launch_backward_dense<VT, AT, 32, true>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, deferred, d, st, *fa);
-                    else rc = launch_backward_dense<VT, AT, 64, true>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, deferred, d, st, *fa);
+                    if (d->D == 32) rc = launch_backward_dense<VT, AT, 32, true>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, dense_done, d, st, *fa);
+                    else rc = launch_backward_dense<VT, AT, 64, true>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, dense_done, d, st, *fa);
                 } else {
-                    if (d->D == 32) rc = launch_backward_dense<VT, AT, 32, false>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, deferred, d, st, FusedArgs{});
-                    else rc = launch_backward_dense<VT, AT, 64, false>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, deferred, d, st, FusedArgs{});
+                    if (d->D == 32) rc = launch_backward_dense<VT, AT, 32, false>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, dense_done, d, st, FusedArgs{});
+                    else rc = launch_backward_dense<VT, AT, 64, false>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, dense_done, d, st, FusedArgs{});
                 }
                 done = true;
             }

@@ -1,5 +1,5 @@
 // msda_static.cu -- msda_b200_backward_static_scratch: the 16-bit backward with its scratch memory (fp32 grad_value
-// accumulator, the dense-window kernel's work counter and deferred-item flags) in a device array that is part of
+// accumulator, the dense-window kernel's work counter and done-item flags) in a device array that is part of
 // the library image instead of a caller-provided workspace.  No counterpart in the reference; see
 // include/msda_b200.h.  For callers that cannot allocate (or cannot size a workspace ahead of time): the call
 // itself allocates nothing, and there is nothing for the caller to allocate either.
