@@ -136,13 +136,12 @@ template <int D> struct Plan {
     static constexpr uint32_t G_LBO = KCH == 4 ? 160 : 144, G_SBO = KCH * G_LBO, G_BYTES = 16 * G_SBO;
     // W [128 pix][128 q]
     static constexpr uint32_t W_LBO = 144, W_SBO = 16 * 144 + 16, W_BYTES = 16 * W_SBO;
-    // Gt [D ch][128 q]
-    static constexpr uint32_t T_LBO = 144, T_SBO = 16 * 144 + 16, T_BYTES = (D / 8) * T_SBO;
+    // (the scatter product's B operand is G itself, read MN-major: no transposed copy)
     static constexpr int STAGE_STRIDE = 68;                 // floats per thread-private staging row (64 + 4: conflict-free 16-byte stores)
     static constexpr uint32_t STAGE_BYTES = kThreads * STAGE_STRIDE * 4;
     // (two V buffers: the next chunk's value rows are fetched with cp.async while the current chunk is processed)
-    static constexpr uint32_t OFF_G = 0, OFF_V = OFF_G + G_BYTES, OFF_W = OFF_V + 2 * G_BYTES, OFF_T = OFF_W + W_BYTES,
-                              OFF_STAGE = OFF_T + T_BYTES, TOTAL = OFF_STAGE + STAGE_BYTES;
+    static constexpr uint32_t OFF_G = 0, OFF_V = OFF_G + G_BYTES, OFF_W = OFF_V + 2 * G_BYTES,
+                              OFF_STAGE = OFF_W + W_BYTES, TOTAL = OFF_STAGE + STAGE_BYTES;
 };
 
 // The P samples of level l of one (query, head) row: sampling locations + attention weights in, their gradients out.
@@ -313,7 +312,6 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
     uint8_t* sG = smem + P::OFF_G;
     uint8_t* sV = smem + P::OFF_V;
     uint8_t* sW = smem + P::OFF_W;
-    uint8_t* sT = smem + P::OFF_T;
     float* stage = reinterpret_cast<float*>(smem + P::OFF_STAGE) + tid * P::STAGE_STRIDE;   // this thread's row
 
     // one-time setup: zero W (the owner threads restore the zeros after every chunk), TMEM, barrier
@@ -339,7 +337,10 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
     const int LP = d.L * d.P;
     const int items = ft.level >= 0 ? ft.total * d.N * d.M : 0;
     constexpr uint32_t idesc_u = umma_idesc(128, kPix, O::fmt);
-    constexpr uint32_t idesc_gv = umma_idesc(128, D, O::fmt);
+    // B = G as staged for the dot product, [K = 128 query rows][N = D channels]: MN-major (instruction descriptor bit 16);
+    // for an MN-major SWIZZLE_NONE operand the descriptor's LBO is the stride between 8-row groups along K and its SBO
+    // the stride between 16-byte chunks along N (tools/micro/umma_probe.cu tests 8 / 9, profiles/r2_umma_probe.txt)
+    constexpr uint32_t idesc_gv = umma_idesc(128, D, O::fmt) | (1u << 16);
 
     int slot = 0;
     DT_DECL
@@ -510,8 +511,8 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
             }
         }
         DT_MARK(2)
-        // ---- G: the item's rows of grad_out -> operand A of the dot product, and transposed -> operand B of the scatter
-        // product.  D / 8 lanes per row (16 bytes each): a warp instruction reads 32 / (D / 8) whole rows.
+        // ---- G: the item's rows of grad_out -> operand A of the dot product (K-major) and, the same bytes read MN-major,
+        // operand B of the scatter product.  D / 8 lanes per row (16 bytes each): a warp instruction reads 32 / (D / 8) whole rows.
         constexpr int LPRV = P::KCH, RPIV = 32 / LPRV;
         {
 #pragma unroll
@@ -522,11 +523,6 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                 if (qq >= 0) g4 = __ldg(reinterpret_cast<const uint4*>(grad_out + (((size_t)b * d.Lq + qq) * d.M + m) * D) + c);
                 const int trow = warp * 32 + rr;
                 *reinterpret_cast<uint4*>(sG + (trow & 7) * 16 + (trow >> 3) * P::G_SBO + c * P::G_LBO) = g4;
-                uint8_t* gt = sT + (trow >> 3) * P::T_LBO + (trow & 7) * 2 + c * P::T_SBO;
-                const uint32_t w4[4] = {g4.x, g4.y, g4.z, g4.w};
-#pragma unroll
-                for (int e = 0; e < 8; ++e)
-                    *reinterpret_cast<uint16_t*>(gt + e * 16) = (uint16_t)(w4[e >> 1] >> ((e & 1) * 16));
             }
         }
 
@@ -691,10 +687,10 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                         umma(tmem_u, dg + (uint64_t)(j * 2 * P::G_LBO / 16), dv + (uint64_t)(j * 2 * P::G_LBO / 16), idesc_u, j > 0);
                     umma_commit(mbar);
                     const uint64_t dw = umma_desc(smem_u32(sW), P::W_LBO, P::W_SBO);
-                    const uint64_t dt = umma_desc(smem_u32(sT), P::T_LBO, P::T_SBO);
+                    const uint64_t dt = umma_desc(smem_u32(sG), P::G_SBO, P::G_LBO);
 #pragma unroll
                     for (int j = 0; j < kThreads / 16; ++j)
-                        umma(tmem_gv, dw + (uint64_t)(j * 2 * P::W_LBO / 16), dt + (uint64_t)(j * 2 * P::T_LBO / 16), idesc_gv, j > 0);
+                        umma(tmem_gv, dw + (uint64_t)(j * 2 * P::W_LBO / 16), dt + (uint64_t)(j * 2 * P::G_SBO / 16), idesc_gv, j > 0);
                     umma_commit(mbar2);
                 }
                 DT_MARK(8)
@@ -806,7 +802,7 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                 }
             }
         }
-        // G / Gt / the window table are rewritten by the next item
+        // G / the window table are rewritten by the next item
         if (tid == 0) { da.done[item] = 1; atomicAdd(da.claim + 2, 1); }
         tmem_fence_before();
         __syncthreads();

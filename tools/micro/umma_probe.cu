@@ -202,6 +202,14 @@ int main(int argc, char** argv)
     }
     if (test == 3) swap = true;
     if (test == 6) repeat = 64;
+    // test 8 / 9: as test 2 (M=128 N=32 K=128, the scatter product), but B is MN-major: the image of G as the dot
+    // product stages it ([K = 128 query rows][N = 32 channels], core matrix = 8 rows x 16 bytes, chunk stride 160, row
+    // group stride 640) with idesc bit 16 (b_major) set -- would make the transposed copy Gt unnecessary.
+    // 8: LBO = chunk stride (N direction), SBO = row-group stride (K direction); 9: the two swapped.
+    bool b_mn = false;
+    if (test == 8 || test == 9) {
+        N = 32; K = 128; a_lbo = 144; a_sbo = 16 * 144 + 16; b_lbo = 160; b_sbo = 640; b_mn = true;
+    }
     if (test == 7) {   // free form: 7 M N K a_fmt b_fmt repeat [a_lbo a_sbo b_lbo b_sbo]
         M = atoi(argv[2]); N = atoi(argv[3]); K = atoi(argv[4]); a_fmt = atoi(argv[5]); b_fmt = atoi(argv[6]); repeat = atoi(argv[7]);
         a_lbo = b_lbo = 128; a_sbo = b_sbo = (K / 8) * 128;
@@ -216,7 +224,8 @@ int main(int argc, char** argv)
     for (int r = 0; r < M; ++r) for (int k = 0; k < K; ++k)
         put16(ia, kmajor_off(r, k, a_lbo, a_sbo), a_fmt ? bf16_bits(A[(size_t)r * K + k]) : f16_bits(A[(size_t)r * K + k]));
     for (int r = 0; r < N; ++r) for (int k = 0; k < K; ++k)
-        put16(ib, kmajor_off(r, k, b_lbo, b_sbo), b_fmt ? bf16_bits(B[(size_t)r * K + k]) : f16_bits(B[(size_t)r * K + k]));
+        put16(ib, b_mn ? kmajor_off(k, r, b_lbo, b_sbo) : kmajor_off(r, k, b_lbo, b_sbo),
+              b_fmt ? bf16_bits(B[(size_t)r * K + k]) : f16_bits(B[(size_t)r * K + k]));
     ia.resize((ia.size() + 15) & ~15ull, 0);
     ib.resize((ib.size() + 15) & ~15ull, 0);
 
@@ -227,6 +236,11 @@ int main(int argc, char** argv)
     p.a_kstep = 2 * a_lbo; p.b_kstep = 2 * b_lbo;
     p.ksteps = K / 16;
     p.idesc = make_idesc(M, N, a_fmt, b_fmt);
+    if (b_mn) {
+        p.idesc |= 1u << 16;             // B is MN-major
+        p.b_kstep = 2 * b_sbo;           // 16 K rows = two row groups
+        if (test == 9) { p.b_lbo = b_sbo; p.b_sbo = b_lbo; }
+    }
     p.n = (uint32_t)N; p.m = (uint32_t)M; p.repeat = (uint32_t)repeat;
 
     uint8_t *da, *db; float* dd; long long* dc; int* ds;
