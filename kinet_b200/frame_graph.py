@@ -22,10 +22,14 @@ import torch
 
 
 class FrameGraphs:
-    def __init__(self, encoder, decoder, spatial_shapes, bucket=32, autocast_dtype=torch.bfloat16, warmup=2):
+    def __init__(self, encoder, decoder, spatial_shapes, bucket=32, autocast_dtype=torch.bfloat16, warmup=2, post=None):
+        """post: optional ``post(hs, reference_points_out)`` recorded into every decoder graph behind the decoder (e.g.
+        the detection heads); it sees the PADDED query rows; its result (static buffers, valid until the next call) is
+        left in ``self.post_out`` by decode()."""
         if bucket <= 0:
             raise ValueError("bucket must be positive")
         self.encoder, self.decoder = encoder, decoder
+        self.post, self.post_out = post, None
         self.shapes = spatial_shapes
         self.bucket = int(bucket)
         self.autocast_dtype = autocast_dtype
@@ -114,10 +118,12 @@ class FrameGraphs:
 
             def fn():
                 with torch.no_grad(), self._amp():
-                    return self.decoder(tgt_b, ref_b, mem, self.shapes, valid_b, qpos_b, mask_b, qmask_b)
-            graph, (hs, ref_out) = self._record(fn)
-            self._dec[B] = (graph, tgt_b, qpos_b, ref_b, qmask_b, hs, ref_out)
-        graph, tgt_b, qpos_b, ref_b, qmask_b, hs, ref_out = self._dec[B]
+                    hs_, ref_ = self.decoder(tgt_b, ref_b, mem, self.shapes, valid_b, qpos_b, mask_b, qmask_b)
+                with torch.no_grad():
+                    return hs_, ref_, (self.post(hs_, ref_) if self.post is not None else None)
+            graph, (hs, ref_out, extra) = self._record(fn)
+            self._dec[B] = (graph, tgt_b, qpos_b, ref_b, qmask_b, hs, ref_out, extra)
+        graph, tgt_b, qpos_b, ref_b, qmask_b, hs, ref_out, extra = self._dec[B]
         tgt_b[:, :Lq].copy_(tgt, non_blocking=True)
         qpos_b[:, :Lq].copy_(query_pos, non_blocking=True)
         ref_b[:, :Lq].copy_(reference_points, non_blocking=True)
@@ -128,6 +134,7 @@ class FrameGraphs:
             qmask_b[:, :Lq].copy_(query_attn_mask, non_blocking=True)
         graph.replay()
         self.replays += 1
+        self.post_out = extra
         return hs[..., :Lq, :], ref_out[..., :Lq, :], mem.x
 
 

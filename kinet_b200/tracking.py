@@ -137,12 +137,16 @@ class SequenceTracker:
     # ---- the transformer call ---------------------------------------------------------------------------------------
     def _flatten(self, srcs, masks, pos_embeds):
         tr = self.transformer
-        shapes, src_l, pos_l = [], [], []
-        for lvl, (src, pos) in enumerate(zip(srcs, pos_embeds)):
-            shapes.append((int(src.shape[2]), int(src.shape[3])))
-            src_l.append(src.flatten(2).transpose(1, 2))
-            pos_l.append(pos.flatten(2).transpose(1, 2) + tr.level_embed[lvl].view(1, 1, -1))
-        return torch.cat(src_l, 1), torch.cat(pos_l, 1), shapes
+        shapes = [(int(src.shape[2]), int(src.shape[3])) for src in srcs]
+        src = torch.cat([s_.flatten(2).transpose(1, 2) for s_ in srcs], 1)
+        # the positional maps (+ level embedding) are the same tensors frame after frame: flattened once
+        key = tuple((id(p), p._version, p.data_ptr()) for p in pos_embeds) + (tr.level_embed._version,)
+        hit = getattr(self, "_pos_flat", None)
+        if hit is None or hit[0] != key:
+            pos = torch.cat([p.flatten(2).transpose(1, 2) + tr.level_embed[lvl].view(1, 1, -1)
+                             for lvl, p in enumerate(pos_embeds)], 1)
+            hit = self._pos_flat = (key, pos, list(pos_embeds))      # (the list keeps the ids alive)
+        return src, hit[1], shapes
 
     def _run_transformer(self, srcs, masks, pos_embeds, targets):
         tr = self.transformer
@@ -163,7 +167,7 @@ class SequenceTracker:
         dev = src.device
         if self._graphs is None:
             self._graphs = FrameGraphs(tr.encoder, tr.decoder, _shapes_tensor(shapes, dev), bucket=self.bucket,
-                                       autocast_dtype=self.autocast_dtype)
+                                       autocast_dtype=self.autocast_dtype, post=self._graph_post)
             self._valid = torch.ones(1, len(shapes), 2, device=dev)
         self._graphs.encode(src, pos, self._valid)
 
@@ -179,9 +183,21 @@ class SequenceTracker:
             tgt = torch.cat([prev_hs, tgt], 1)
             ref = torch.cat([targets[0]["track_query_boxes"][None, :, :2], ref], 1)
         hs, ref_out, _ = self._graphs.decode(tgt, ref, qpos)
+        post = self._graphs.post_out
+        if post is not None:             # heads + packing were recorded behind the decoder: slice the padded rows off
+            Lq = hs.shape[-2]
+            self._pre = (post[1][:, :Lq], post[2][:Lq])
+            return post[0][:, :Lq], None
         if hs.dim() == 4:
             return hs[-1], (ref_out[-2] if ref_out.shape[0] > 1 else ref)
         return hs, ref
+
+    def _graph_post(self, hs, ref_out):
+        """Recorded into the decoder graphs (FrameGraphs post): class / box heads and the packed read-back rows of the
+        last decoder layer -- ~20 small kernels that would otherwise be launched one by one from Python every frame."""
+        if hs.dim() != 4 or ref_out.shape[0] < 2:
+            return None                  # the reference of the last layer is the caller's: heads run eagerly
+        return self._heads_and_pack(hs[-1], ref_out[-2])
 
     # ---- one frame --------------------------------------------------------------------------------------------------
     def _targets(self, dev):
@@ -243,6 +259,10 @@ class SequenceTracker:
             cur = nxt
 
     def _heads_and_pack(self, hs, ref):
+        pre = getattr(self, "_pre", None)
+        if ref is None and pre is not None:      # done inside the decoder graph (_graph_post)
+            self._pre = None
+            return hs, pre[0], pre[1]
         logits, boxes = self.heads(hs, ref)
         prob = logits.sigmoid()
         scores, labels = prob.max(-1)
@@ -251,6 +271,30 @@ class SequenceTracker:
         xyxy = torch.minimum((xyxy * self._scale).clamp(min=0), self._scale)     # scale to pixels, clip_boxes_to_image
         packed = torch.cat([scores[0, :, None], labels[0, :, None].to(scores.dtype), xyxy[0]], -1)
         return hs, xyxy, packed
+
+    def _to_device_indices(self, dev, *lists):
+        """Index lists -> device int64 tensors through PINNED staging memory and one non-blocking copy.  A copy from
+        pageable memory (torch.as_tensor(list, device=...)) first synchronises the stream it is issued on -- here the
+        stream that already holds the next frame's encoder, i.e. the host would sit out the very work run() queued to
+        hide its own latency.  Two staging buffers alternate: a frame's copy has executed (it is ordered before that
+        frame's decoder, whose results the host has read) long before its buffer comes round again."""
+        n = sum(len(l) for l in lists)
+        st = getattr(self, "_idx_stage", None)
+        if st is None or st[0].shape[0] < n or st[2].device != dev:
+            cap = max(1024, 2 * n)
+            st = [torch.empty(cap, dtype=torch.int64).pin_memory(), torch.empty(cap, dtype=torch.int64).pin_memory(),
+                  torch.empty(cap, dtype=torch.int64, device=dev), 0]
+            self._idx_stage = st
+        st[3] ^= 1
+        host = st[st[3]]
+        flat = host.numpy()
+        out, o = [], 0
+        for l in lists:
+            flat[o:o + len(l)] = l
+            out.append((o, o + len(l)))
+            o += len(l)
+        st[2][:n].copy_(host[:n], non_blocking=True)
+        return [st[2][a:b] for a, b in out]      # (consumed by this frame's gathers, stream-ordered before the next copy)
 
     def _update_tracks(self, hs, xyxy, packed):
         """Host side of a frame: packed = (Lq, 6) numpy [score, label, x1, y1, x2, y2] of all queries."""
@@ -269,8 +313,9 @@ class SequenceTracker:
             k = _nms(np.stack([e[4] for e in live]), np.asarray([e[5] for e in live]), self.trk_nms)
             live = [live[j] for j in k]
         # new detections (tracker.py:422-505)
-        new = [[-1, 0, int(i), -1, bx[i], sc[i]] for i in range(T, T + self.num_object_queries)
-               if sc[i] > self.det_thresh and lb[i] == 0]
+        obj = slice(T, T + self.num_object_queries)
+        new = [[-1, 0, int(i), -1, bx[i], sc[i]]
+               for i in T + np.flatnonzero((sc[obj] > self.det_thresh) & (lb[obj] == 0))]
         # NMS in which existing tracks always win over new ones (:485-505)
         if self.det_nms and (live or new):
             boxes_all = np.stack([e[4] for e in live + new])
@@ -284,12 +329,11 @@ class SequenceTracker:
         entries = live + new
         # next frame's track state, gathered on the device
         if entries:
-            q_rows = torch.as_tensor([max(e[2], 0) for e in entries], device=dev)
-            new_boxes, new_hs = xyxy[0, q_rows], hs[0, q_rows].float()
             stale = [j for j, e in enumerate(entries) if e[2] < 0]
+            q_rows, dst, src_rows = self._to_device_indices(
+                dev, [max(e[2], 0) for e in entries], stale, [entries[j][3] for j in stale])
+            new_boxes, new_hs = xyxy[0, q_rows], hs[0, q_rows].float()
             if stale:                                               # a missed frame keeps the previous box / embedding
-                dst = torch.as_tensor(stale, device=dev)
-                src_rows = torch.as_tensor([entries[j][3] for j in stale], device=dev)
                 new_boxes[dst] = self.track_boxes[src_rows]
                 new_hs[dst] = self.track_hs[src_rows]
             self.track_boxes, self.track_hs = new_boxes, new_hs
