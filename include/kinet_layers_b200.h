@@ -46,6 +46,14 @@ typedef struct kinet_ln_fwd_args {
     float* mean_rstd;                      /* optional [rows][2] saved for the backward    */
     int64_t rows;       int32_t C;
     float eps;
+    /* ABI 3: dropout of the branch inside the kernel, y = LayerNorm(x + dropout(r)) -- the reference's
+     * src = src + self.dropoutN(src2); src = self.normN(src) (deformable_transformer.py:294-296 ...) without a
+     * dropout kernel and its mask tensor.  drop_p = 0: none.  An element is kept with probability 1 - p' (p' = p
+     * rounded to 1 / 65536) and scaled by 1 / (1 - p'); which elements are kept is a hash of (element index,
+     * drop_seed, drop_site, *drop_step): the backward, given the same four values, regenerates the mask.
+     * drop_step may be NULL (= 0); as a DEVICE pointer it lets a replayed CUDA graph draw a new mask every step. */
+    float drop_p;       uint32_t drop_site;
+    uint64_t drop_seed; const int64_t* drop_step;
 } kinet_ln_fwd_args;
 
 int kinet_b200_add_layernorm_forward(const kinet_ln_fwd_args* args, void* stream);
@@ -67,6 +75,13 @@ typedef struct kinet_ln_bwd_args {
     float* dgamma_dbeta;
     float* partial;
     int64_t rows;         int32_t C;
+    /* ABI 3: the forward's dropout arguments (dr = mask * d(x + r) / (1 - p')), and want_dbias: dgamma_dbeta is
+     * [3][C] and its third row receives the column sums of dr -- the bias gradient of the Linear layer that produced
+     * the branch (output_proj, linear2), which then needs no reduction pass of its own; `partial` must hold
+     * kinet_b200_colsum_partial_floats(3 * C) elements in that case. */
+    int32_t want_dbias;
+    float drop_p;         uint32_t drop_site;
+    uint64_t drop_seed;   const int64_t* drop_step;
 } kinet_ln_bwd_args;
 
 int kinet_b200_add_layernorm_backward(const kinet_ln_bwd_args* args, void* stream);

@@ -45,7 +45,7 @@
 extern "C" {
 #endif
 
-#define MSDA_B200_ABI_VERSION 2
+#define MSDA_B200_ABI_VERSION 3
 
 /* element types */
 #define MSDA_F32 0

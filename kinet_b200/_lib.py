@@ -53,7 +53,9 @@ class KinetLnFwdArgs(ctypes.Structure):
                 ("ypos_lp", ctypes.c_void_p), ("lp_dtype", ctypes.c_int32),
                 ("mean_rstd", ctypes.c_void_p),
                 ("rows", ctypes.c_int64), ("C", ctypes.c_int32),
-                ("eps", ctypes.c_float)]
+                ("eps", ctypes.c_float),
+                ("drop_p", ctypes.c_float), ("drop_site", ctypes.c_uint32),
+                ("drop_seed", ctypes.c_uint64), ("drop_step", ctypes.c_void_p)]
 
 
 class KinetLnBwdArgs(ctypes.Structure):
@@ -67,7 +69,10 @@ class KinetLnBwdArgs(ctypes.Structure):
                 ("dr", ctypes.c_void_p),
                 ("dgamma_dbeta", ctypes.c_void_p),
                 ("partial", ctypes.c_void_p),
-                ("rows", ctypes.c_int64), ("C", ctypes.c_int32)]
+                ("rows", ctypes.c_int64), ("C", ctypes.c_int32),
+                ("want_dbias", ctypes.c_int32),
+                ("drop_p", ctypes.c_float), ("drop_site", ctypes.c_uint32),
+                ("drop_seed", ctypes.c_uint64), ("drop_step", ctypes.c_void_p)]
 
 
 
@@ -142,7 +147,7 @@ def load():
     lib.kinet_b200_small_mha_forward.argtypes = [ctypes.POINTER(KinetMhaArgs), vp]
     lib.kinet_b200_small_mha_backward.restype = i
     lib.kinet_b200_small_mha_backward.argtypes = [ctypes.POINTER(KinetMhaBwdArgs), vp]
-    if lib.msda_b200_abi_version() != 2:
+    if lib.msda_b200_abi_version() != 3:
         raise RuntimeError("kinet_b200: libmsda_b200.so ABI version mismatch")
     _lib = lib
     return lib

@@ -76,11 +76,48 @@ __device__ __forceinline__ float warp_sum(float v)
     return v;
 }
 
+// ---- dropout of the branch inside the add + LayerNorm kernels ----------------------------------------------
+// Counter-based: the keep / drop decision of an element is a hash of its index and a per-call key, so the backward
+// regenerates the mask instead of reading one.  One 32-bit hash (two multiply-xorshift rounds: full avalanche) serves
+// two elements, 16 bits each, compared with p * 65536.
+struct Drop {
+    uint32_t thr;      // drop when the element's 16 bits are below thr; 0 = no dropout
+    uint32_t key;
+    float scale;       // 1 / (1 - thr / 65536)
+};
+__device__ __forceinline__ uint32_t mix32(uint32_t x)
+{
+    x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+    return x;
+}
+__device__ __forceinline__ Drop make_drop(float p, uint32_t site, uint64_t seed, const int64_t* step)
+{
+    Drop d;
+    d.thr = p > 0.f ? (uint32_t)fminf(p * 65536.f + 0.5f, 65535.f) : 0u;
+    d.scale = 65536.f / (float)(65536u - d.thr);
+    const uint64_t st = step ? (uint64_t)*step : 0ull;
+    d.key = mix32((uint32_t)seed ^ mix32((uint32_t)(seed >> 32) ^ mix32(site * 0x9e3779b1U ^ mix32((uint32_t)st ^ (uint32_t)(st >> 32) * 0x85ebca6bU))));
+    return d;
+}
+// keep bits (bit i = element i of the vector survives) of vector `vec` (= row * vectors per row + v, modulo 2^31)
+__device__ __forceinline__ uint32_t drop_keep4(const Drop& d, uint32_t vec)
+{
+    const uint32_t h0 = mix32(vec * 2u + d.key), h1 = mix32(vec * 2u + 1u + d.key);
+    return ((h0 & 0xffffu) >= d.thr ? 1u : 0u) | ((h0 >> 16) >= d.thr ? 2u : 0u) |
+           ((h1 & 0xffffu) >= d.thr ? 4u : 0u) | ((h1 >> 16) >= d.thr ? 8u : 0u);
+}
+__device__ __forceinline__ float4 drop_scale4(float4 r, uint32_t keep, float scale)
+{
+    return make_float4((keep & 1u) ? r.x * scale : 0.f, (keep & 2u) ? r.y * scale : 0.f,
+                       (keep & 4u) ? r.z * scale : 0.f, (keep & 8u) ? r.w * scale : 0.f);
+}
+
 // KMAX: 16-byte vectors per lane; a row has C / 4 vectors, lane l owns vectors l, l + 32, ...
 template <int KMAX>
 __global__ void __launch_bounds__(kWarps * 32, KMAX <= 3 ? 6 : (KMAX <= 4 ? 4 : 2))
 add_layernorm_fwd_kernel(const kinet_ln_fwd_args a)
 {
+    const Drop drop = make_drop(a.r ? a.drop_p : 0.f, a.drop_site, a.drop_seed, a.drop_step);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nvec = a.C >> 2;
     const float inv_c = 1.f / (float)a.C;
@@ -99,7 +136,8 @@ add_layernorm_fwd_kernel(const kinet_ln_fwd_args a)
             if (v < nvec) {
                 z[k] = load4(a.x, a.x_dtype, base + 4 * v);
                 if (a.r) {
-                    const float4 r = load4(a.r, a.r_dtype, base + 4 * v);
+                    float4 r = load4(a.r, a.r_dtype, base + 4 * v);
+                    if (drop.thr) r = drop_scale4(r, drop_keep4(drop, (uint32_t)row * (uint32_t)nvec + (uint32_t)v), drop.scale);
                     z[k].x += r.x; z[k].y += r.y; z[k].z += r.z; z[k].w += r.w;
                 }
                 s += (z[k].x + z[k].y) + (z[k].z + z[k].w);
@@ -158,11 +196,17 @@ __device__ __forceinline__ void fold_columns(float4 (&acc)[KMAX], float* smem, f
     }
 }
 
-template <int KMAX>
-__global__ void __launch_bounds__(kWarps * 32, KMAX <= 2 ? 4 : (KMAX <= 3 ? 3 : (KMAX <= 4 ? 2 : 1)))
+// EXT: dropout of the branch and / or the column sums of dr (want_dbias); its own instantiation so that the plain
+// kernel keeps its register budget (4 / 3 CTAs per SM).
+template <int KMAX, bool EXT>
+__global__ void __launch_bounds__(kWarps * 32, EXT ? (KMAX <= 2 ? 3 : (KMAX <= 4 ? 2 : 1)) : (KMAX <= 2 ? 4 : (KMAX <= 3 ? 3 : (KMAX <= 4 ? 2 : 1))))
 add_layernorm_bwd_kernel(const kinet_ln_bwd_args a)
 {
     extern __shared__ float smem[];   // [kWarps][C]
+    const Drop drop = make_drop((EXT && a.r) ? a.drop_p : 0.f, a.drop_site, a.drop_seed, a.drop_step);
+    float4 dbr[EXT ? KMAX : 1];
+#pragma unroll
+    for (int k = 0; k < (EXT ? KMAX : 1); ++k) dbr[k] = make_float4(0.f, 0.f, 0.f, 0.f);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nvec = a.C >> 2;
     const float inv_c = 1.f / (float)a.C;
@@ -175,6 +219,7 @@ add_layernorm_bwd_kernel(const kinet_ln_bwd_args a)
         const size_t base = (size_t)row * a.C;
         const float2 ms = reinterpret_cast<const float2*>(a.mean_rstd)[row];
         float4 xh[KMAX], wd[KMAX];
+        uint32_t keep[EXT ? KMAX : 1];
         float c1 = 0.f, c2 = 0.f;
 #pragma unroll
         for (int k = 0; k < KMAX; ++k) {
@@ -193,7 +238,14 @@ add_layernorm_bwd_kernel(const kinet_ln_bwd_args a)
                 }
                 float4 z = load4(a.x, a.x_dtype, base + 4 * v);
                 if (a.r) {
-                    const float4 r = load4(a.r, a.r_dtype, base + 4 * v);
+                    float4 r = load4(a.r, a.r_dtype, base + 4 * v);
+                    if constexpr (EXT) {
+                        keep[k] = 15u;
+                        if (drop.thr) {
+                            keep[k] = drop_keep4(drop, (uint32_t)row * (uint32_t)nvec + (uint32_t)v);
+                            r = drop_scale4(r, keep[k], drop.scale);
+                        }
+                    }
                     z.x += r.x; z.y += r.y; z.z += r.z; z.w += r.w;
                 }
                 xh[k] = make_float4((z.x - ms.x) * ms.y, (z.y - ms.x) * ms.y, (z.z - ms.x) * ms.y, (z.w - ms.x) * ms.y);
@@ -217,13 +269,25 @@ add_layernorm_bwd_kernel(const kinet_ln_bwd_args a)
                 d.z = ms.y * (wd[k].z - c1 - xh[k].z * c2);
                 d.w = ms.y * (wd[k].w - c1 - xh[k].w * c2);
                 store4(a.dx, a.x_dtype, base + 4 * v, d);
-                if (a.dr) store4(a.dr, a.r_dtype, base + 4 * v, d);
+                if constexpr (EXT) {
+                    if (a.r) {
+                        const float4 e = drop.thr ? drop_scale4(d, keep[k], drop.scale) : d;     // d (x + dropout(r)) / d r
+                        if (a.dr) store4(a.dr, a.r_dtype, base + 4 * v, e);
+                        dbr[k].x += e.x; dbr[k].y += e.y; dbr[k].z += e.z; dbr[k].w += e.w;
+                    }
+                } else {
+                    if (a.dr) store4(a.dr, a.r_dtype, base + 4 * v, d);
+                }
             }
         }
     }
-    float* prow = a.partial + (size_t)blockIdx.x * 2 * a.C;
+    const int ncol = (EXT && a.want_dbias) ? 3 : 2;
+    float* prow = a.partial + (size_t)blockIdx.x * ncol * a.C;
     fold_columns<KMAX>(dg, smem, prow, a.C, lane, warp);
     fold_columns<KMAX>(db, smem, prow + a.C, a.C, lane, warp);
+    if constexpr (EXT) {
+        if (a.want_dbias) fold_columns<KMAX>(dbr, smem, prow + 2 * a.C, a.C, lane, warp);
+    }
 }
 
 // out[c] = sum over the G rows of partial[G][n], fixed order.  A CTA of 32 x 32 threads owns 32 columns:
@@ -376,14 +440,21 @@ int launch_fwd(const kinet_ln_fwd_args& a, cudaStream_t st)
     return (int)cudaGetLastError();
 }
 
+template <int KMAX, bool EXT>
+int launch_bwd_impl(const kinet_ln_bwd_args& a, int* grid, cudaStream_t st)
+{
+    const size_t smem = (size_t)kWarps * a.C * sizeof(float);
+    const int resident = resident_ctas(add_layernorm_bwd_kernel<KMAX, EXT>, kWarps * 32, smem);
+    *grid = row_grid(a.rows, resident < kMaxCtas ? resident : kMaxCtas);   // the scratch has kMaxCtas rows
+    add_layernorm_bwd_kernel<KMAX, EXT><<<*grid, kWarps * 32, smem, st>>>(a);
+    return (int)cudaGetLastError();
+}
+
 template <int KMAX>
 int launch_bwd(const kinet_ln_bwd_args& a, int* grid, cudaStream_t st)
 {
-    const size_t smem = (size_t)kWarps * a.C * sizeof(float);
-    const int resident = resident_ctas(add_layernorm_bwd_kernel<KMAX>, kWarps * 32, smem);
-    *grid = row_grid(a.rows, resident < kMaxCtas ? resident : kMaxCtas);   // the scratch has kMaxCtas rows
-    add_layernorm_bwd_kernel<KMAX><<<*grid, kWarps * 32, smem, st>>>(a);
-    return (int)cudaGetLastError();
+    const bool ext = a.want_dbias || (a.r && a.drop_p > 0.f);
+    return ext ? launch_bwd_impl<KMAX, true>(a, grid, st) : launch_bwd_impl<KMAX, false>(a, grid, st);
 }
 
 }  // namespace kinet
@@ -398,6 +469,7 @@ int kinet_b200_add_layernorm_forward(const kinet_ln_fwd_args* args, void* stream
     const kinet_ln_fwd_args& a = *args;
     if (!a.x || !a.y || !a.gamma || !a.beta) return MSDA_E_NULL;
     if (a.rows < 0 || a.C <= 0 || (a.C & 3) || a.C > KINET_LN_MAX_C) return MSDA_E_SHAPE;
+    if (!(a.drop_p >= 0.f && a.drop_p < 1.f)) return MSDA_E_SHAPE;
     if (!ok_dtype(a.x_dtype) || !ok_dtype(a.y_dtype) || (a.r && !ok_dtype(a.r_dtype))) return MSDA_E_DTYPE;
     if ((a.y_lp || a.ypos_lp) && !ok_dtype(a.lp_dtype)) return MSDA_E_DTYPE;
     if (a.ypos_lp && (!a.pos || !ok_dtype(a.pos_dtype) || a.pos_rows <= 0)) return MSDA_E_NULL;
@@ -426,8 +498,9 @@ int kinet_b200_add_layernorm_backward(const kinet_ln_bwd_args* args, void* strea
     const kinet_ln_bwd_args& a = *args;
     if (!a.x || !a.dx || !a.gamma || !a.mean_rstd || !a.dgamma_dbeta || !a.partial) return MSDA_E_NULL;
     if (!a.dy && !a.dy_lp && !a.dypos_lp) return MSDA_E_NULL;
-    if (a.r == nullptr && a.dr != nullptr) return MSDA_E_NULL;
+    if (a.r == nullptr && (a.dr != nullptr || a.want_dbias)) return MSDA_E_NULL;
     if (a.rows < 0 || a.C <= 0 || (a.C & 3) || a.C > KINET_LN_MAX_C) return MSDA_E_SHAPE;
+    if (!(a.drop_p >= 0.f && a.drop_p < 1.f)) return MSDA_E_SHAPE;
     if (!ok_dtype(a.x_dtype) || (a.r && !ok_dtype(a.r_dtype)) || (a.dy && !ok_dtype(a.dy_dtype)) ||
         ((a.dy_lp || a.dypos_lp) && !ok_dtype(a.lp_dtype)))
         return MSDA_E_DTYPE;
@@ -447,7 +520,7 @@ int kinet_b200_add_layernorm_backward(const kinet_ln_bwd_args* args, void* strea
         else rc = launch_bwd<8>(a, &grid, st);
         if (rc) return rc;
     }
-    const int n = 2 * a.C;
+    const int n = (a.want_dbias ? 3 : 2) * a.C;
     colsum_finalize_kernel<<<(n + 31) / 32, 1024, 0, st>>>(a.partial, grid, n, a.dgamma_dbeta, MSDA_F32);
     return (int)cudaGetLastError();
 }

@@ -51,14 +51,56 @@ def _canon_pos(pos, x):
     return pos.contiguous()
 
 
-class AddLayerNormFunction(Function):
-    """(y, y_lp, ypos_lp) = AddLayerNormFunction.apply(x, r, pos, gamma, beta, eps, lp_dtype, want_lp)
+# ---- dropout inside the add + LayerNorm kernels ---------------------------------------------------------------------
+# The kernels decide which elements of the branch survive from a hash of (element index, seed, site, step) and the
+# backward regenerates the mask (include/kinet_layers_b200.h).  seed: per process (from torch.initial_seed(), i.e.
+# torch.manual_seed controls it); site: a running number per forward call, so eager calls never share a mask; step: a
+# DEVICE counter that a CUDA-graph training step advances inside the graph (advance_dropout_step), so every replay
+# draws new masks although the sites are baked into the graph.
+_drop_state = {"seed": None, "site": 0, "steps": {}}
 
-    y = LayerNorm(x + r) in x.dtype; y_lp = y.to(lp_dtype) if want_lp else None;
-    ypos_lp = (y + pos).to(lp_dtype) if pos is not None else None.  r may be None."""
+
+def set_dropout_seed(seed):
+    _drop_state["seed"] = int(seed) & 0xFFFFFFFFFFFFFFFF
+
+
+def _dropout_seed():
+    if _drop_state["seed"] is None:
+        set_dropout_seed(torch.initial_seed() * 0x9E3779B97F4A7C15 + 0x1234567)
+    return _drop_state["seed"]
+
+
+def dropout_step_tensor(device):
+    """The int64 device counter the kernels read (one per device)."""
+    key = str(device)
+    t = _drop_state["steps"].get(key)
+    if t is None:
+        t = _drop_state["steps"][key] = torch.zeros(1, dtype=torch.int64, device=device)
+    return t
+
+
+def advance_dropout_step(device):
+    """New masks from here on (an in-place add on the device: capturable, replays advance it too)."""
+    dropout_step_tensor(device).add_(1)
+
+
+def _next_site():
+    _drop_state["site"] = (_drop_state["site"] + 1) & 0xFFFFFFFF
+    return _drop_state["site"]
+
+
+class AddLayerNormFunction(Function):
+    """(y, y_lp, ypos_lp) = AddLayerNormFunction.apply(x, r, pos, gamma, beta, eps, lp_dtype, want_lp,
+                                                       drop_p=0.0, branch_bias=None)
+
+    y = LayerNorm(x + dropout(r, drop_p)) in x.dtype; y_lp = y.to(lp_dtype) if want_lp else None;
+    ypos_lp = (y + pos).to(lp_dtype) if pos is not None else None.  r may be None.
+    branch_bias: the bias parameter of the Linear layer that produced r (already added by that layer: it is NOT
+    added here); its gradient -- the column sums of d r -- comes out of this function's backward, so that layer can
+    skip its own bias-gradient pass (linear(..., skip_bias_grad=True))."""
 
     @staticmethod
-    def forward(ctx, x, r, pos, gamma, beta, eps, lp_dtype, want_lp):
+    def forward(ctx, x, r, pos, gamma, beta, eps, lp_dtype, want_lp, drop_p=0.0, branch_bias=None):
         if not x.is_cuda:
             raise RuntimeError("Not implemented on the CPU")
         C = x.shape[-1]
@@ -74,12 +116,18 @@ class AddLayerNormFunction(Function):
         y = torch.empty_like(x)
         y_lp = torch.empty(x.shape, dtype=lp_dtype, device=x.device) if want_lp else None
         ypos = torch.empty(x.shape, dtype=lp_dtype, device=x.device) if posc is not None else None
+        need_stats = need_stats or (branch_bias is not None and ctx.needs_input_grad[9])
         stats = torch.empty(rows, 2, dtype=torch.float32, device=x.device) if need_stats else None
+        drop_p = float(drop_p) if r is not None else 0.0
+        drop = (0.0, 0, 0, None)
+        if drop_p > 0.0:
+            drop = (drop_p, _next_site(), _dropout_seed(), dropout_step_tensor(x.device))
         a = _lib.KinetLnFwdArgs(
             _ptr(x), _code(x), _ptr(r), _code(r), _ptr(posc), _code(posc),
             (posc.numel() // C) if posc is not None else 1,
             _ptr(gamma32), _ptr(beta32), _ptr(y), _code(y), _ptr(y_lp), _ptr(ypos),
-            _lib.dtype_code(lp_dtype), _ptr(stats), rows, C, float(eps))
+            _lib.dtype_code(lp_dtype), _ptr(stats), rows, C, float(eps),
+            drop[0], drop[1], drop[2], _ptr(drop[3]))
         lib = _lib.load()
         with _lib.device_guard(x.device):
             rc = lib.kinet_b200_add_layernorm_forward(ctypes.byref(a), _lib.raw_stream(x.device))
@@ -89,6 +137,8 @@ class AddLayerNormFunction(Function):
             ctx.save_for_backward(x, r, gamma32, stats)
             ctx.pos_meta = None if pos is None else (pos.shape, pos.dtype, posc.shape)
             ctx.param_dtypes = (gamma.dtype, beta.dtype)
+            ctx.drop = drop
+            ctx.bias_dtype = None if branch_bias is None or r is None else branch_bias.dtype
         return y, y_lp, ypos
 
     @staticmethod
@@ -96,7 +146,7 @@ class AddLayerNormFunction(Function):
     def backward(ctx, dy, dy_lp, dypos):
         x, r, gamma32, stats = ctx.saved_tensors
         if dy is None and dy_lp is None and dypos is None:
-            return (None,) * 8
+            return (None,) * 10
         C = x.shape[-1]
         rows = x.numel() // C
         lp = [t for t in (dy_lp, dypos) if t is not None]
@@ -107,13 +157,17 @@ class AddLayerNormFunction(Function):
         dypos = dypos.contiguous() if dypos is not None else None
         dx = torch.empty_like(x)
         dr = torch.empty_like(r) if (r is not None and ctx.needs_input_grad[1]) else None
-        dgb = torch.empty(2, C, dtype=torch.float32, device=x.device)
+        want_dbias = ctx.bias_dtype is not None and ctx.needs_input_grad[9]
+        ncol = 3 if want_dbias else 2
+        dgb = torch.empty(ncol, C, dtype=torch.float32, device=x.device)
         lib = _lib.load()
-        partial = torch.empty(lib.kinet_b200_colsum_partial_floats(2 * C), dtype=torch.float32, device=x.device)
+        partial = torch.empty(lib.kinet_b200_colsum_partial_floats(ncol * C), dtype=torch.float32, device=x.device)
+        drop = ctx.drop
         a = _lib.KinetLnBwdArgs(
             _ptr(dy), _code(dy), _ptr(dy_lp), _ptr(dypos), _code(lp[0]) if lp else 0,
             _ptr(x), _code(x), _ptr(r), _code(r), _ptr(gamma32), _ptr(stats),
-            _ptr(dx), _ptr(dr), _ptr(dgb), _ptr(partial), rows, C)
+            _ptr(dx), _ptr(dr), _ptr(dgb), _ptr(partial), rows, C,
+            1 if want_dbias else 0, drop[0], drop[1], drop[2], _ptr(drop[3]))
         with _lib.device_guard(x.device):
             rc = lib.kinet_b200_add_layernorm_backward(ctypes.byref(a), _lib.raw_stream(x.device))
         _lib.check(rc, "kinet_b200_add_layernorm_backward")
@@ -127,15 +181,17 @@ class AddLayerNormFunction(Function):
         gd, bd = ctx.param_dtypes
         return (dx if ctx.needs_input_grad[0] else None, dr, dpos,
                 dgb[0].to(gd) if ctx.needs_input_grad[3] else None,
-                dgb[1].to(bd) if ctx.needs_input_grad[4] else None, None, None, None)
+                dgb[1].to(bd) if ctx.needs_input_grad[4] else None, None, None, None, None,
+                dgb[2].to(ctx.bias_dtype) if want_dbias else None)
 
 
-def add_layer_norm(x, r, norm, pos=None, lp_dtype=None, want_lp=False):
-    """norm(x + r) with the layer's nn.LayerNorm parameters -> (y, y_lp, ypos_lp); see AddLayerNormFunction."""
+def add_layer_norm(x, r, norm, pos=None, lp_dtype=None, want_lp=False, drop_p=0.0, branch_bias=None):
+    """norm(x + dropout(r, drop_p)) with the layer's nn.LayerNorm parameters -> (y, y_lp, ypos_lp); see
+    AddLayerNormFunction."""
     if tuple(norm.normalized_shape) != (x.shape[-1],) or norm.weight is None or norm.bias is None:
         raise RuntimeError("kinet_b200: add_layer_norm needs an affine LayerNorm over the last dimension")
     return AddLayerNormFunction.apply(x, r, pos, norm.weight, norm.bias, norm.eps,
-                                      lp_dtype if lp_dtype is not None else x.dtype, want_lp)
+                                      lp_dtype if lp_dtype is not None else x.dtype, want_lp, drop_p, branch_bias)
 
 
 def column_sum(a2d, out_dtype=None):
@@ -182,7 +238,8 @@ class LinearFunction(Function):
     ONE fused pass for the bias gradient (+ the ReLU's backward)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, relu, w_lp, b_lp):
+    def forward(ctx, x, weight, bias, relu, w_lp, b_lp, skip_bias_grad=False):
+        ctx.skip_bias_grad = bool(skip_bias_grad)      # the bias gradient comes out of the next add + LayerNorm's backward
         lp = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else None
         w, b, x_dtype = weight, bias, x.dtype
         if lp is not None:
@@ -215,7 +272,9 @@ class LinearFunction(Function):
                 dy2, db = relu_backward_column_sum(dy2, y2, bd)
             else:
                 dy2 = dy2 * (y2 > 0).to(dy2.dtype)
-        if db is None and ctx.needs_input_grad[2]:
+        if ctx.skip_bias_grad:
+            db = None
+        elif db is None and ctx.needs_input_grad[2]:
             db = column_sum(dy2, bd) if fused else dy2.sum(0).to(bd)
         dx = (dy2 @ w).view(x_shape).to(x_dtype) if ctx.needs_input_grad[0] else None
         dw = None
@@ -224,7 +283,7 @@ class LinearFunction(Function):
                 dw = torch.mm(dy2.t(), x2, out_dtype=torch.float32)    # fp32 straight out of the GEMM: no cast pass
             else:
                 dw = (dy2.t() @ x2).to(wd)
-        return dx, dw, db if ctx.needs_input_grad[2] else None, None, None, None
+        return dx, dw, db if ctx.needs_input_grad[2] else None, None, None, None, None
 
 
 def lp_params(owner, weight, bias, dtype):
@@ -262,12 +321,13 @@ def inference_mirror(owner, weight, bias, x):
     return mirror
 
 
-def linear_params(x, weight, bias, relu=False, mirror=None):
+def linear_params(x, weight, bias, relu=False, mirror=None, skip_bias_grad=False):
     """act(x @ weight.T + bias) on explicit parameter tensors (e.g. slices of an in_proj_weight).
-    mirror: optional (weight, bias) low-precision copies kept current by the caller."""
+    mirror: optional (weight, bias) low-precision copies kept current by the caller.  skip_bias_grad: the caller
+    obtains the bias gradient elsewhere (add_layer_norm(..., branch_bias=bias))."""
     if x.is_cuda and torch.is_grad_enabled() and bias is not None and (weight.requires_grad or bias.requires_grad):
         w_lp, b_lp = mirror if mirror is not None else (None, None)
-        return LinearFunction.apply(x, weight, bias, relu, w_lp, b_lp)
+        return LinearFunction.apply(x, weight, bias, relu, w_lp, b_lp, skip_bias_grad and not relu)
     if mirror is not None and x.is_cuda and torch.is_autocast_enabled("cuda") \
             and mirror[0].dtype == torch.get_autocast_dtype("cuda"):
         weight, bias = mirror
@@ -279,8 +339,9 @@ def linear_params(x, weight, bias, relu=False, mirror=None):
     return F.relu(y) if relu else y
 
 
-def linear(x, layer, relu=False):
+def linear(x, layer, relu=False, skip_bias_grad=False):
     """``act(layer(x))`` for an nn.Linear, act = identity or ReLU.  With parameter gradients: LinearFunction.
     Without (inference): one GEMM (ReLU in its epilogue), under CUDA autocast on low-precision parameter copies
     cached on the layer (or kept current by training.FlatParams)."""
-    return linear_params(x, layer.weight, layer.bias, relu, inference_mirror(layer, layer.weight, layer.bias, x))
+    return linear_params(x, layer.weight, layer.bias, relu, inference_mirror(layer, layer.weight, layer.bias, x),
+                         skip_bias_grad)

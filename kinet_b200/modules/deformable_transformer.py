@@ -90,7 +90,21 @@ def _act_linear(x, layer, activation):
     return activation(linear(x, layer))
 
 
-def _self_attention(mha, q_in, v_in, key_padding_mask):
+class _skip_output_bias_grad:
+    """While active, ``attn`` (an MSDeformAttn) leaves the bias gradient of its output_proj to the add + LayerNorm
+    step that consumes its output (``_norm_step(..., branch_bias=attn.output_proj.bias)``)."""
+
+    def __init__(self, attn):
+        self.attn = attn
+
+    def __enter__(self):
+        self.attn._kinet_skip_output_bias_grad = True
+
+    def __exit__(self, *exc):
+        self.attn._kinet_skip_output_bias_grad = False
+
+
+def _self_attention(mha, q_in, v_in, key_padding_mask, skip_out_bias_grad=False):
     """nn.MultiheadAttention(q, k = q, v)[0] on batch-first (N, Lq, C) inputs, computed from the module's own
     parameters (in_proj_weight / in_proj_bias / out_proj: checkpoints unchanged): one GEMM for q and k, one for
     v, F.scaled_dot_product_attention, out_proj.  Same arithmetic as the reference's call
@@ -124,7 +138,7 @@ def _self_attention(mha, q_in, v_in, key_padding_mask):
         o = F.scaled_dot_product_attention(qe, ke, ve, dropout_p=drop, scale=d ** -0.5)[..., :d]
     else:
         o = F.scaled_dot_product_attention(q, k, v, attn_mask=~key_padding_mask[:, None, None, :], dropout_p=drop)
-    return linear(o.transpose(1, 2).reshape(N, Lq, C), mha.out_proj)
+    return linear(o.transpose(1, 2).reshape(N, Lq, C), mha.out_proj, skip_bias_grad=skip_out_bias_grad)
 
 
 class _Stream:
@@ -144,11 +158,18 @@ class _Stream:
         return _Stream(x, x_lp, xpos if lp == xpos.dtype else xpos.to(lp))
 
 
-def _norm_step(x, branch, norm, pos, want_pos):
-    """x <- norm(x + branch); returns the next _Stream (copies only where the stream dtype differs)."""
+def _norm_step(x, branch, norm, pos, want_pos, drop=None, branch_bias=None):
+    """x <- norm(x + drop(branch)); returns the next _Stream (copies only where the stream dtype differs).
+    drop: the layer's nn.Dropout for this branch -- applied INSIDE the fused kernel (no dropout kernel, no mask
+    tensor; the backward regenerates the mask).  branch_bias: bias of the Linear layer that produced ``branch`` when
+    that layer was told to skip its bias gradient (it then comes out of this step's backward)."""
     lp = _lp_dtype(x)
     same = lp == x.dtype
-    y, y_lp, ypos = add_layer_norm(x, branch, norm, pos=pos if want_pos else None, lp_dtype=lp, want_lp=not same)
+    p = drop.p if (drop is not None and drop.training) else 0.0
+    if branch_bias is not None and not (torch.is_grad_enabled() and branch_bias.requires_grad):
+        branch_bias = None
+    y, y_lp, ypos = add_layer_norm(x, branch, norm, pos=pos if want_pos else None, lp_dtype=lp, want_lp=not same,
+                                   drop_p=p, branch_bias=branch_bias)
     if same:
         y_lp = y
     return _Stream(y, y_lp, ypos if ypos is not None else y_lp)
@@ -179,12 +200,16 @@ class DeformableTransformerEncoderLayer(nn.Module):
 
     def _ffn(self, st, pos, want_pos):
         h = self.dropout2(_act_linear(st.x_lp, self.linear1, self.activation))
-        return _norm_step(st.x, self.dropout3(linear(h, self.linear2)), self.norm2, pos, want_pos)
+        # dropout3 and linear2's bias gradient ride in the fused add + LayerNorm step
+        return _norm_step(st.x, linear(h, self.linear2, skip_bias_grad=True), self.norm2, pos, want_pos,
+                          drop=self.dropout3, branch_bias=self.linear2.bias)
 
     def _forward_stream(self, st, pos, reference_points, spatial_shapes, padding_mask, last):
         # self attention: query = src + pos, value source = src   (reference :293-296)
-        src2 = self.self_attn(st.xpos_lp, reference_points, st.x_lp, spatial_shapes, padding_mask)
-        st = _norm_step(st.x, self.dropout1(src2), self.norm1, None, False)
+        with _skip_output_bias_grad(self.self_attn):
+            src2 = self.self_attn(st.xpos_lp, reference_points, st.x_lp, spatial_shapes, padding_mask)
+        st = _norm_step(st.x, src2, self.norm1, None, False, drop=self.dropout1,
+                        branch_bias=self.self_attn.output_proj.bias)
         # ffn (:282-287); the closing norm also prepares src + pos for the next layer's query
         return self._ffn(st, pos, pos is not None and not last)
 
@@ -248,23 +273,29 @@ class DeformableTransformerDecoderLayer(nn.Module):
 
     def _ffn(self, st, pos, want_pos):
         h = self.dropout3(_act_linear(st.x_lp, self.linear1, self.activation))
-        return _norm_step(st.x, self.dropout4(linear(h, self.linear2)), self.norm3, pos, want_pos)
+        return _norm_step(st.x, linear(h, self.linear2, skip_bias_grad=True), self.norm3, pos, want_pos,
+                          drop=self.dropout4, branch_bias=self.linear2.bias)
 
     def _forward_stream(self, st, query_pos, reference_points, src, src_spatial_shapes,
                         src_padding_mask, query_attn_mask, last):
         # self attention over the queries: q = k = tgt + query_pos, v = tgt   (reference :367-376)
         mha = self.self_attn
+        out_bias = None
         if mha._qkv_same_embed_dim and mha.in_proj_bias is not None and mha.bias_k is None and not mha.add_zero_attn:
-            tgt2 = _self_attention(mha, st.xpos_lp, st.x_lp, query_attn_mask)
+            tgt2 = _self_attention(mha, st.xpos_lp, st.x_lp, query_attn_mask, skip_out_bias_grad=True)
+            out_bias = mha.out_proj.bias
         else:
             q = st.xpos_lp.transpose(0, 1)
             tgt2 = mha(q, q, st.x_lp.transpose(0, 1), key_padding_mask=query_attn_mask,
                        need_weights=False)[0].transpose(0, 1)
-        st = _norm_step(st.x, self.dropout2(tgt2), self.norm2, query_pos, query_pos is not None)
+        st = _norm_step(st.x, tgt2, self.norm2, query_pos, query_pos is not None, drop=self.dropout2,
+                        branch_bias=out_bias)
         # cross attention into the encoder memory (:378-383)
-        tgt2 = self.cross_attn(st.xpos_lp, reference_points, src, src_spatial_shapes,
-                               src_padding_mask, query_attn_mask)
-        st = _norm_step(st.x, self.dropout1(tgt2), self.norm1, None, False)
+        with _skip_output_bias_grad(self.cross_attn):
+            tgt2 = self.cross_attn(st.xpos_lp, reference_points, src, src_spatial_shapes,
+                                   src_padding_mask, query_attn_mask)
+        st = _norm_step(st.x, tgt2, self.norm1, None, False, drop=self.dropout1,
+                        branch_bias=self.cross_attn.output_proj.bias)
         # ffn (:361-365); the closing norm prepares tgt + query_pos for the next layer
         return self._ffn(st, query_pos, query_pos is not None and not last)
 

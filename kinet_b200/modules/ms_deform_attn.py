@@ -130,7 +130,7 @@ class MSDeformAttn(nn.Module):
             output = MSDeformAttnFusedFunction.apply(
                 value, input_spatial_shapes, reference_points, sampling_offsets, attention_weights,
                 query_attn_mask, input_spatial_shapes, self.im2col_step)
-            return _linear(output, self.output_proj)
+            return _linear(output, self.output_proj, skip_bias_grad=getattr(self, "_kinet_skip_output_bias_grad", False))
         attention_weights = F.softmax(attention_weights, -1).view(
             N, Len_q, self.n_heads, self.n_levels, self.n_points)
 
@@ -150,4 +150,4 @@ class MSDeformAttn(nn.Module):
                     reference_points.shape[-1]))
         output = MSDeformAttnFunction.apply(
             value, input_spatial_shapes, sampling_locations, attention_weights, self.im2col_step)
-        return _linear(output, self.output_proj)
+        return _linear(output, self.output_proj, skip_bias_grad=getattr(self, "_kinet_skip_output_bias_grad", False))

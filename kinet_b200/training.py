@@ -13,6 +13,8 @@ CUDA graph there are no hooks to run, so the buffers are laid out once, up front
 views up from ``layer._kinet_mirror``.
 """
 import torch
+
+from .functions.layer_ops import advance_dropout_step
 from torch import nn
 
 _ALIGN = 64     # elements: every parameter starts 128 / 256 bytes aligned in the bf16 / fp32 buffers
@@ -191,6 +193,9 @@ class GraphedTrainStep:
 
     def _forward_backward(self):
         self.flat.detach_grads()
+        # the fused add + LayerNorm kernels draw their dropout masks from (seed, call site, THIS counter): advancing it
+        # inside the graph gives every replay new masks although the call sites are baked in
+        advance_dropout_step(self.flat.master.device)
         loss = self._loss_fn(*self.inputs)
         loss.backward()
         self.flat.gather_grads()

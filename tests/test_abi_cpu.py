@@ -37,7 +37,7 @@ def test_header_symbols_are_exported(lib):
 
 
 def test_abi_version_and_error_strings(lib):
-    assert lib.msda_b200_abi_version() == 2
+    assert lib.msda_b200_abi_version() == 3
     assert lib.msda_b200_error_string(0) == b"success"
     for code in (-1, -2, -3, -4, -5):
         assert lib.msda_b200_error_string(code).startswith(b"msda_b200:")

@@ -488,3 +488,122 @@ def test_deformable_transformer_two_stage_matches_reference_golden():
     # the same proposals were selected (top-k on the class logit) and refined to the same boxes
     assert _rel(init_ref, t("init_ref")) < 1e-5
     assert _rel(hs, t("hs")) < 5e-5 and _rel(inter_ref, t("inter_ref")) < 1e-5
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("C,stream,lp", [(256, torch.float32, torch.bfloat16), (288, torch.float32, torch.float32),
+                                         (1024, torch.bfloat16, torch.bfloat16)])
+def test_add_layer_norm_fused_dropout_and_branch_bias(C, stream, lp):
+    """y = LayerNorm(x + dropout(r)) with the mask generated inside the kernels: the mask the backward regenerates
+    (read off d r) is the one the forward used, its density is p, the arithmetic matches PyTorch's with that mask, the
+    column sums of d r come out as the branch bias gradient, new sites / steps draw new masks."""
+    from kinet_b200.functions import layer_ops as lo
+    dev = _dev()
+    g = torch.Generator().manual_seed(C)
+    rows, p = 3000, 0.1
+    x = torch.randn(rows, C, generator=g).to(dev, stream).requires_grad_(True)
+    r = torch.randn(rows, C, generator=g).to(dev, lp).requires_grad_(True)
+    gamma = (1 + 0.1 * torch.randn(C, generator=g)).to(dev).requires_grad_(True)
+    beta = (0.1 * torch.randn(C, generator=g)).to(dev).requires_grad_(True)
+    bias = torch.zeros(C, device=dev, requires_grad=True)
+    w = torch.randn(rows, C, generator=g).to(dev)
+    lo.set_dropout_seed(1234)
+    y, _, _ = lo.AddLayerNormFunction.apply(x, r, None, gamma, beta, 1e-5, lp, False, p, bias)
+    dx, dr, dg, db, dbias = torch.autograd.grad((y.float() * w).sum(), [x, r, gamma, beta, bias])
+    # the mask, as the backward saw it: d r = mask / (1 - p') * d x
+    mask = dr.float() != 0
+    dropped = 1.0 - mask.float().mean().item()
+    assert abs(dropped - p) < 4 * (p * (1 - p) / (rows * C)) ** 0.5 + 2e-5, dropped
+    scale = 65536.0 / (65536 - round(p * 65536))
+    xd, rd, gd, bd = (t.detach().double().requires_grad_(True) for t in (x, r, gamma, beta))
+    z = xd + rd * mask.double() * scale
+    yd = torch.nn.functional.layer_norm(z, (C,), gd, bd, 1e-5)
+    rdx, rdr, rdg, rdb = torch.autograd.grad((yd * w.double()).sum(), [xd, rd, gd, bd])
+    tol = 2e-5 if stream == torch.float32 else 1.2e-2
+    assert _rel(y, yd.detach()) < tol                 # the forward used the same mask
+    assert _rel(dx, rdx) < tol and _rel(dg, rdg) < max(tol, 1e-4) and _rel(db, rdb) < max(tol, 1e-4)
+    assert _rel(dr, rdr) < (2e-5 if lp == torch.float32 else 1.2e-2)
+    assert _rel(dbias, rdr.sum(0)) < (1e-4 if lp == torch.float32 else 1.2e-2)
+    # a second call is a new site: another mask; the same site and step reproduce (checked through the C ABI's determinism:
+    # forward twice with the site counter rewound)
+    site = lo._drop_state["site"]
+    y2, _, _ = lo.AddLayerNormFunction.apply(x, r, None, gamma, beta, 1e-5, lp, False, p, None)
+    assert not torch.equal(y2, y)
+    lo._drop_state["site"] = site - 1
+    y3, _, _ = lo.AddLayerNormFunction.apply(x, r, None, gamma, beta, 1e-5, lp, False, p, None)
+    assert torch.equal(y3, y)
+    lo._drop_state["site"] = site - 1
+    lo.advance_dropout_step(dev)
+    y4, _, _ = lo.AddLayerNormFunction.apply(x, r, None, gamma, beta, 1e-5, lp, False, p, None)
+    assert not torch.equal(y4, y)
+    # p = 0: the plain kernel, bit for bit
+    y0, _, _ = lo.AddLayerNormFunction.apply(x, r, None, gamma, beta, 1e-5, lp, False, 0.0, bias)
+    y1, _, _ = lo.AddLayerNormFunction.apply(x, r, None, gamma, beta, 1e-5, lp, False)
+    assert torch.equal(y0, y1)
+    d0 = torch.autograd.grad((y0.float() * w).sum(), [x, r, bias])
+    d1 = torch.autograd.grad((y1.float() * w).sum(), [x, r])
+    assert torch.equal(d0[0], d1[0]) and torch.equal(d0[1], d1[1])
+    assert _rel(d0[2], d1[1].float().sum(0)) < (1e-5 if lp == torch.float32 else 4e-3)
+
+
+@pytest.mark.gpu
+def test_layers_bias_gradients_come_out_of_the_norm_steps():
+    """Encoder / decoder layers route the bias gradients of output_proj / out_proj / linear2 through the fused add +
+    LayerNorm backward (no column-sum pass of their own): every parameter still gets its gradient, equal to the plain
+    composition's (dropout 0), and training mode with dropout 0.1 runs with finite, non-zero gradients everywhere."""
+    from kinet_b200.modules import DeformableTransformerDecoderLayer, DeformableTransformerEncoderLayer
+    dev = _dev()
+    torch.manual_seed(3)
+    d, L = 128, 2
+    levels = [(6, 8), (3, 4)]
+    S = sum(h * w for h, w in levels)
+    shapes = torch.as_tensor(levels, device=dev)
+    for p_drop in (0.0, 0.1):
+        enc = DeformableTransformerEncoderLayer(d, 48, p_drop, "relu", L, 8, 2).to(dev).train()
+        dec = DeformableTransformerDecoderLayer(d, 48, p_drop, "relu", L, 8, 2).to(dev).train()
+        with torch.no_grad():
+            for m in (enc, dec):
+                for n_, p_ in m.named_parameters():
+                    if p_.dim() == 1 and "norm" not in n_:
+                        p_.normal_(0, 0.1)
+        src = torch.randn(2, S, d, device=dev, requires_grad=True)
+        pos = torch.randn(2, S, d, device=dev)
+        ref_e = torch.rand(2, S, L, 2, device=dev)
+        tgt = torch.randn(2, 5, d, device=dev)
+        qpos = torch.randn(2, 5, d, device=dev)
+        ref_d = torch.rand(2, 5, L, 2, device=dev)
+        mem = enc(src, pos, ref_e, shapes)
+        out = dec(tgt, qpos, ref_d, mem, shapes)
+        out.square().sum().backward()
+        for m in (enc, dec):
+            for n_, p_ in m.named_parameters():
+                assert p_.grad is not None and torch.isfinite(p_.grad).all(), n_
+                if "sampling_offsets" not in n_ and "attention_weights" not in n_:
+                    assert p_.grad.abs().max() > 0, n_
+        if p_drop == 0.0:
+            # the same layers with every bias gradient computed by its own Linear layer (skip flags off)
+            import kinet_b200.functions.layer_ops as lo
+            got = {n_: p_.grad.clone() for m, tag in ((enc, "e."), (dec, "d.")) for n_, p_ in
+                   ((tag + k, v) for k, v in m.named_parameters())}
+            for m in (enc, dec):
+                m.zero_grad()
+            src.grad = None
+            orig = lo.LinearFunction.forward
+            real_apply = lo.AddLayerNormFunction.apply
+            lo_linear_params = lo.linear_params
+            try:
+                lo.linear_params = lambda x, w, b, relu=False, mirror=None, skip_bias_grad=False: lo_linear_params(x, w, b, relu, mirror, False)
+                import kinet_b200.modules.deformable_transformer as dt
+                dt_norm = dt.add_layer_norm
+                dt.add_layer_norm = lambda x, r, norm, pos=None, lp_dtype=None, want_lp=False, drop_p=0.0, branch_bias=None: \
+                    dt_norm(x, r, norm, pos, lp_dtype, want_lp, drop_p, None)
+                lo_linear = lo.linear
+                mem = enc(src, pos, ref_e, shapes)
+                out = dec(tgt, qpos, ref_d, mem, shapes)
+                out.square().sum().backward()
+            finally:
+                lo.linear_params = lo_linear_params
+                dt.add_layer_norm = dt_norm
+            for m, tag in ((enc, "e."), (dec, "d.")):
+                for n_, p_ in m.named_parameters():
+                    assert _rel(got[tag + n_], p_.grad) < 1e-4, n_
