@@ -100,6 +100,18 @@ int kinet_b200_colsum(const void* a, int32_t a_dtype, int64_t rows, int32_t C,
 int kinet_b200_relu_backward_colsum(const void* dy, const void* h, int32_t dtype, int64_t rows, int32_t C,
                                     void* dh, void* out, int32_t out_dtype, float* partial, void* stream);
 
+/* Dropout without a mask tensor (ABI 3): out = dropout(x, drop_p) elementwise over n elements (n % 4 == 0), the keep / drop
+ * decision hashed from (element index, drop_seed, drop_site, *drop_step) exactly as in the add + LayerNorm kernels.  Meant for
+ * the FFN's inner dropout, linear2(dropout(activation(linear1(x)))) (deformable_transformer.py:283, :362): for a ReLU the
+ * backward needs neither the mask nor the hash, because dropout(relu(a)) is positive exactly where the element survived and
+ * the ReLU was open -- kinet_b200_relu_dropout_backward_colsum(dy, h_dropped, drop_p, ...) writes
+ * dh = dy * (h_dropped > 0) / (1 - p') and its column sums in one pass (in place of PyTorch's masked_scale kernel, the ReLU
+ * backward and the bias-gradient reduction). */
+int kinet_b200_dropout_forward(const void* x, void* out, int32_t dtype, int64_t n, float drop_p, uint32_t drop_site,
+                               uint64_t drop_seed, const int64_t* drop_step, void* stream);
+int kinet_b200_relu_dropout_backward_colsum(const void* dy, const void* h_dropped, float drop_p, int32_t dtype, int64_t rows,
+                                            int32_t C, void* dh, void* out, int32_t out_dtype, float* partial, void* stream);
+
 /* ---- attention core of nn.MultiheadAttention for short sequences: the `kine` path ----
  *
  * Replaces, inside the reference's KinematicTransformer / DualKinematicTransformer

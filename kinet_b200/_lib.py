@@ -38,7 +38,8 @@ EXPORTS = ("msda_b200_abi_version", "msda_b200_error_string", "msda_b200_forward
 # include/kinet_layers_b200.h (glue kernels of the layers that call the op)
 LAYER_EXPORTS = ("kinet_b200_add_layernorm_forward", "kinet_b200_add_layernorm_backward",
                  "kinet_b200_colsum_partial_floats", "kinet_b200_colsum", "kinet_b200_relu_backward_colsum",
-                 "kinet_b200_small_mha_forward", "kinet_b200_small_mha_backward")
+                 "kinet_b200_small_mha_forward", "kinet_b200_small_mha_backward",
+                 "kinet_b200_dropout_forward", "kinet_b200_relu_dropout_backward_colsum")
 MHA_MAX_D = 64                                 # KINET_MHA_MAX_D
 
 
@@ -143,6 +144,12 @@ def load():
     lib.kinet_b200_relu_backward_colsum.restype = i
     lib.kinet_b200_relu_backward_colsum.argtypes = [vp, vp, ctypes.c_int32, ctypes.c_int64, ctypes.c_int32, vp, vp,
                                                     ctypes.c_int32, vp, vp]
+    lib.kinet_b200_dropout_forward.restype = i
+    lib.kinet_b200_dropout_forward.argtypes = [vp, vp, ctypes.c_int32, ctypes.c_int64, ctypes.c_float, ctypes.c_uint32,
+                                               ctypes.c_uint64, vp, vp]
+    lib.kinet_b200_relu_dropout_backward_colsum.restype = i
+    lib.kinet_b200_relu_dropout_backward_colsum.argtypes = [vp, vp, ctypes.c_float, ctypes.c_int32, ctypes.c_int64,
+                                                            ctypes.c_int32, vp, vp, ctypes.c_int32, vp, vp]
     lib.kinet_b200_small_mha_forward.restype = i
     lib.kinet_b200_small_mha_forward.argtypes = [ctypes.POINTER(KinetMhaArgs), vp]
     lib.kinet_b200_small_mha_backward.restype = i

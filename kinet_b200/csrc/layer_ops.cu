@@ -327,7 +327,7 @@ colsum_finalize_kernel(const float* __restrict__ partial, int G, int n, void* ou
 template <bool RELU>
 __global__ void __launch_bounds__(256)
 colsum_kernel(const void* __restrict__ a, const void* __restrict__ h, void* __restrict__ dh, int dtype,
-              int64_t rows, int C, int RL, float* __restrict__ partial)
+              int64_t rows, int C, int RL, float* __restrict__ partial, float scale)
 {
     extern __shared__ float smem[];   // [RL][C]
     const int nvec = C >> 2;
@@ -338,8 +338,8 @@ colsum_kernel(const void* __restrict__ a, const void* __restrict__ h, void* __re
         float4 v = load4(a, dtype, i);
         if constexpr (RELU) {
             const float4 o = load4(h, dtype, i);
-            v.x = o.x > 0.f ? v.x : 0.f; v.y = o.y > 0.f ? v.y : 0.f;
-            v.z = o.z > 0.f ? v.z : 0.f; v.w = o.w > 0.f ? v.w : 0.f;
+            v.x = o.x > 0.f ? v.x * scale : 0.f; v.y = o.y > 0.f ? v.y * scale : 0.f;
+            v.z = o.z > 0.f ? v.z * scale : 0.f; v.w = o.w > 0.f ? v.w * scale : 0.f;
             store4(dh, dtype, i, v);
         }
         return v;
@@ -373,7 +373,7 @@ colsum_kernel(const void* __restrict__ a, const void* __restrict__ h, void* __re
 template <bool RELU>
 __global__ void __launch_bounds__(1024)
 colsum_small_kernel(const void* __restrict__ a, const void* __restrict__ h, void* __restrict__ dh, int dtype,
-                    int rows, int C, void* out, int out_dtype)
+                    int rows, int C, void* out, int out_dtype, float scale)
 {
     __shared__ float tile[32][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -385,8 +385,8 @@ colsum_small_kernel(const void* __restrict__ a, const void* __restrict__ h, void
             float v0 = load1(a, dtype, (size_t)r * C + c);
             float v1 = r1 < rows ? load1(a, dtype, (size_t)r1 * C + c) : 0.f;
             if constexpr (RELU) {
-                v0 = load1(h, dtype, (size_t)r * C + c) > 0.f ? v0 : 0.f;
-                if (r1 < rows) v1 = load1(h, dtype, (size_t)r1 * C + c) > 0.f ? v1 : 0.f;
+                v0 = load1(h, dtype, (size_t)r * C + c) > 0.f ? v0 * scale : 0.f;
+                if (r1 < rows) v1 = load1(h, dtype, (size_t)r1 * C + c) > 0.f ? v1 * scale : 0.f;
                 store1(dh, dtype, (size_t)r * C + c, v0);
                 if (r1 < rows) store1(dh, dtype, (size_t)r1 * C + c, v1);
             }
@@ -402,6 +402,28 @@ colsum_small_kernel(const void* __restrict__ a, const void* __restrict__ h, void
         for (int w = 0; w < 32; ++w) t += tile[w][tx];
         store1(out, out_dtype, c, t);
     }
+}
+
+// out = dropout(x): element e survives when drop_keep4's bit says so (the same hash as the add + LayerNorm kernels, vector
+// index = e / 4), scaled by 1 / (1 - p').  No mask tensor: for the activations of a ReLU the backward needs none either --
+// dropout(relu(a)) > 0 exactly where the element survived AND the ReLU was open (kinet_b200_relu_dropout_backward_colsum).
+__global__ void __launch_bounds__(256)
+dropout_fwd_kernel(const void* __restrict__ x, void* __restrict__ out, int dtype, int64_t nvec, float p, uint32_t site,
+                   uint64_t seed, const int64_t* __restrict__ step)
+{
+    const Drop drop = make_drop(p, site, seed, step);
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < nvec; i += 4 * stride) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = load4(x, dtype, (size_t)(i + u * stride) * 4);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            store4(out, dtype, (size_t)(i + u * stride) * 4, drop_scale4(v[u], drop_keep4(drop, (uint32_t)(i + u * stride)), drop.scale));
+    }
+    for (; i < nvec; i += stride)
+        store4(out, dtype, (size_t)i * 4, drop_scale4(load4(x, dtype, (size_t)i * 4), drop_keep4(drop, (uint32_t)i), drop.scale));
 }
 
 constexpr int kSmallRows = 2048;
@@ -526,7 +548,7 @@ int kinet_b200_add_layernorm_backward(const kinet_ln_bwd_args* args, void* strea
 }
 
 static int colsum_common(const void* a, const void* h, void* dh, int32_t a_dtype, int64_t rows, int32_t C, void* out,
-                         int32_t out_dtype, float* partial, void* stream)
+                         int32_t out_dtype, float* partial, void* stream, float scale = 1.f)
 {
     const bool relu = h != nullptr;
     if (!out || !partial || (rows > 0 && !a)) return MSDA_E_NULL;
@@ -539,8 +561,8 @@ static int colsum_common(const void* a, const void* h, void* dh, int32_t a_dtype
     cudaStream_t st = (cudaStream_t)stream;
     if (rows <= kSmallRows) {
         const int g = (C + 31) / 32;
-        if (relu) colsum_small_kernel<true><<<g, 1024, 0, st>>>(a, h, dh, a_dtype, (int)rows, C, out, out_dtype);
-        else colsum_small_kernel<false><<<g, 1024, 0, st>>>(a, nullptr, nullptr, a_dtype, (int)rows, C, out, out_dtype);
+        if (relu) colsum_small_kernel<true><<<g, 1024, 0, st>>>(a, h, dh, a_dtype, (int)rows, C, out, out_dtype, scale);
+        else colsum_small_kernel<false><<<g, 1024, 0, st>>>(a, nullptr, nullptr, a_dtype, (int)rows, C, out, out_dtype, 1.f);
         return (int)cudaGetLastError();
     }
     const int nvec = C >> 2;
@@ -551,8 +573,8 @@ static int colsum_common(const void* a, const void* h, void* dh, int32_t a_dtype
         const int64_t want = (rows + (int64_t)RL * 8 - 1) / ((int64_t)RL * 8);
         grid = (int)(want < kMaxCtas ? (want > 0 ? want : 1) : kMaxCtas);
         const size_t smem = (size_t)RL * C * sizeof(float);
-        if (relu) colsum_kernel<true><<<grid, 256, smem, st>>>(a, h, dh, a_dtype, rows, C, RL, partial);
-        else colsum_kernel<false><<<grid, 256, smem, st>>>(a, nullptr, nullptr, a_dtype, rows, C, RL, partial);
+        if (relu) colsum_kernel<true><<<grid, 256, smem, st>>>(a, h, dh, a_dtype, rows, C, RL, partial, scale);
+        else colsum_kernel<false><<<grid, 256, smem, st>>>(a, nullptr, nullptr, a_dtype, rows, C, RL, partial, 1.f);
         if (int rc = (int)cudaGetLastError()) return rc;
     }
     colsum_finalize_kernel<<<(C + 31) / 32, 1024, 0, st>>>(partial, grid, C, out, out_dtype);
@@ -570,6 +592,31 @@ int kinet_b200_relu_backward_colsum(const void* dy, const void* h, int32_t dtype
 {
     if (!h) return MSDA_E_NULL;
     return colsum_common(dy, h, dh, dtype, rows, C, out, out_dtype, partial, stream);
+}
+
+int kinet_b200_relu_dropout_backward_colsum(const void* dy, const void* h_dropped, float drop_p, int32_t dtype, int64_t rows,
+                                            int32_t C, void* dh, void* out, int32_t out_dtype, float* partial, void* stream)
+{
+    if (!h_dropped) return MSDA_E_NULL;
+    if (!(drop_p >= 0.f && drop_p < 1.f)) return MSDA_E_SHAPE;
+    const uint32_t thr = drop_p > 0.f ? (uint32_t)fminf(drop_p * 65536.f + 0.5f, 65535.f) : 0u;
+    return colsum_common(dy, h_dropped, dh, dtype, rows, C, out, out_dtype, partial, stream, 65536.f / (float)(65536u - thr));
+}
+
+int kinet_b200_dropout_forward(const void* x, void* out, int32_t dtype, int64_t n, float drop_p, uint32_t drop_site,
+                               uint64_t drop_seed, const int64_t* drop_step, void* stream)
+{
+    if (n < 0 || (n & 3)) return MSDA_E_SHAPE;
+    if (!(drop_p >= 0.f && drop_p < 1.f)) return MSDA_E_SHAPE;
+    if (!ok_dtype(dtype)) return MSDA_E_DTYPE;
+    if (n == 0) return 0;
+    if (!x || !out) return MSDA_E_NULL;
+    if (!aligned_for(x, dtype) || !aligned_for(out, dtype)) return MSDA_E_ALIGN;
+    const int64_t nvec = n >> 2;
+    int64_t grid = (nvec + 256 * 4 - 1) / (256 * 4);
+    if (grid > 148 * 16) grid = 148 * 16;
+    dropout_fwd_kernel<<<(int)grid, 256, 0, (cudaStream_t)stream>>>(x, out, dtype, nvec, drop_p, drop_site, drop_seed, drop_step);
+    return (int)cudaGetLastError();
 }
 
 }  // extern "C"

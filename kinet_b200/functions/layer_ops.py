@@ -215,19 +215,40 @@ def colsum_supported(a2d):
             and a2d.shape[1] % 4 == 0 and 0 < a2d.shape[1] <= MAX_C)
 
 
-def relu_backward_column_sum(dy2d, h2d, out_dtype):
-    """dh = dy * (h > 0) and its column sums in one pass (h = the ReLU's output) -> (dh, sums)."""
+def relu_backward_column_sum(dy2d, h2d, out_dtype, drop_p=0.0):
+    """dh = dy * (h > 0) [/ (1 - p') when h = dropout(relu(a), drop_p), see dropout_] and its column sums in one pass
+    (h = the ReLU's output) -> (dh, sums)."""
     rows, C = dy2d.shape
     lib = _lib.load()
     dh = torch.empty_like(dy2d)
     out = torch.empty(C, dtype=out_dtype, device=dy2d.device)
     partial = torch.empty(lib.kinet_b200_colsum_partial_floats(C), dtype=torch.float32, device=dy2d.device)
     with _lib.device_guard(dy2d.device):
-        rc = lib.kinet_b200_relu_backward_colsum(_ptr(dy2d), _ptr(h2d), _lib.dtype_code(dy2d.dtype), rows, C, _ptr(dh),
-                                                 _ptr(out), _lib.dtype_code(out_dtype), _ptr(partial),
-                                                 _lib.raw_stream(dy2d.device))
-    _lib.check(rc, "kinet_b200_relu_backward_colsum")
+        rc = lib.kinet_b200_relu_dropout_backward_colsum(_ptr(dy2d), _ptr(h2d), float(drop_p), _lib.dtype_code(dy2d.dtype),
+                                                         rows, C, _ptr(dh), _ptr(out), _lib.dtype_code(out_dtype),
+                                                         _ptr(partial), _lib.raw_stream(dy2d.device))
+    _lib.check(rc, "kinet_b200_relu_dropout_backward_colsum")
     return dh, out
+
+
+def dropout_(x, p):
+    """In-place dropout of a contiguous CUDA tensor without a mask tensor (kinet_b200_dropout_forward): the keep / drop
+    decisions are a hash of (element index, seed, call site, device step counter), like the add + LayerNorm kernels'."""
+    if p <= 0.0 or x.numel() == 0:
+        return x
+    if not (x.is_cuda and x.is_contiguous() and x.dtype in _LN_DTYPES and x.numel() % 4 == 0):
+        raise RuntimeError("kinet_b200: dropout_ needs a contiguous fp32 / bf16 / fp16 CUDA tensor of 4 n elements")
+    lib = _lib.load()
+    with _lib.device_guard(x.device):
+        rc = lib.kinet_b200_dropout_forward(_ptr(x), _ptr(x), _lib.dtype_code(x.dtype), x.numel(), float(p), _next_site(),
+                                            _dropout_seed(), _ptr(dropout_step_tensor(x.device)), _lib.raw_stream(x.device))
+    _lib.check(rc, "kinet_b200_dropout_forward")
+    return x
+
+
+def dropout_scale(p):
+    """1 / (1 - p') with p' = p rounded to 1 / 65536, as the kernels apply it."""
+    return 65536.0 / (65536 - min(int(p * 65536 + 0.5), 65535)) if p > 0 else 1.0
 
 
 class LinearFunction(Function):
@@ -238,7 +259,8 @@ class LinearFunction(Function):
     ONE fused pass for the bias gradient (+ the ReLU's backward)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, relu, w_lp, b_lp, skip_bias_grad=False):
+    def forward(ctx, x, weight, bias, relu, w_lp, b_lp, skip_bias_grad=False, drop_p=0.0):
+        """drop_p (with relu): y = dropout(relu(x @ W.T + b), drop_p), the FFN's inner dropout, without a mask tensor."""
         ctx.skip_bias_grad = bool(skip_bias_grad)      # the bias gradient comes out of the next add + LayerNorm's backward
         lp = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else None
         w, b, x_dtype = weight, bias, x.dtype
@@ -253,7 +275,11 @@ class LinearFunction(Function):
                 y2 = torch._addmm_activation(b, x2, w.t(), use_gelu=False)
             else:
                 y2 = torch.addmm(b, x2, w.t())
+        drop_p = float(drop_p) if relu else 0.0
+        if drop_p > 0.0:
+            dropout_(y2, drop_p)               # in place: the backward only needs dropout(relu(.)) (its sign pattern)
         ctx.save_for_backward(x2, w, y2 if relu else None)
+        ctx.drop_p = drop_p
         ctx.meta = (weight.dtype, bias.dtype, x_dtype, x.shape, bool(relu))
         return y2.view(x.shape[:-1] + (w.shape[0],))
 
@@ -269,9 +295,9 @@ class LinearFunction(Function):
         db = None
         if relu:
             if fused:
-                dy2, db = relu_backward_column_sum(dy2, y2, bd)
+                dy2, db = relu_backward_column_sum(dy2, y2, bd, ctx.drop_p)
             else:
-                dy2 = dy2 * (y2 > 0).to(dy2.dtype)
+                dy2 = dy2 * (y2 > 0).to(dy2.dtype) * dropout_scale(ctx.drop_p)
         if ctx.skip_bias_grad:
             db = None
         elif db is None and ctx.needs_input_grad[2]:
@@ -283,7 +309,7 @@ class LinearFunction(Function):
                 dw = torch.mm(dy2.t(), x2, out_dtype=torch.float32)    # fp32 straight out of the GEMM: no cast pass
             else:
                 dw = (dy2.t() @ x2).to(wd)
-        return dx, dw, db if ctx.needs_input_grad[2] else None, None, None, None, None
+        return dx, dw, db if ctx.needs_input_grad[2] else None, None, None, None, None, None
 
 
 def lp_params(owner, weight, bias, dtype):
@@ -321,13 +347,15 @@ def inference_mirror(owner, weight, bias, x):
     return mirror
 
 
-def linear_params(x, weight, bias, relu=False, mirror=None, skip_bias_grad=False):
+def linear_params(x, weight, bias, relu=False, mirror=None, skip_bias_grad=False, drop_p=0.0):
     """act(x @ weight.T + bias) on explicit parameter tensors (e.g. slices of an in_proj_weight).
     mirror: optional (weight, bias) low-precision copies kept current by the caller.  skip_bias_grad: the caller
-    obtains the bias gradient elsewhere (add_layer_norm(..., branch_bias=bias))."""
+    obtains the bias gradient elsewhere (add_layer_norm(..., branch_bias=bias)).  drop_p: dropout behind the ReLU."""
     if x.is_cuda and torch.is_grad_enabled() and bias is not None and (weight.requires_grad or bias.requires_grad):
         w_lp, b_lp = mirror if mirror is not None else (None, None)
-        return LinearFunction.apply(x, weight, bias, relu, w_lp, b_lp, skip_bias_grad and not relu)
+        return LinearFunction.apply(x, weight, bias, relu, w_lp, b_lp, skip_bias_grad and not relu, drop_p if relu else 0.0)
+    if drop_p > 0.0:
+        return F.dropout(linear_params(x, weight, bias, relu, mirror), drop_p, True)
     if mirror is not None and x.is_cuda and torch.is_autocast_enabled("cuda") \
             and mirror[0].dtype == torch.get_autocast_dtype("cuda"):
         weight, bias = mirror
@@ -339,9 +367,9 @@ def linear_params(x, weight, bias, relu=False, mirror=None, skip_bias_grad=False
     return F.relu(y) if relu else y
 
 
-def linear(x, layer, relu=False, skip_bias_grad=False):
+def linear(x, layer, relu=False, skip_bias_grad=False, drop_p=0.0):
     """``act(layer(x))`` for an nn.Linear, act = identity or ReLU.  With parameter gradients: LinearFunction.
     Without (inference): one GEMM (ReLU in its epilogue), under CUDA autocast on low-precision parameter copies
     cached on the layer (or kept current by training.FlatParams)."""
     return linear_params(x, layer.weight, layer.bias, relu, inference_mirror(layer, layer.weight, layer.bias, x),
-                         skip_bias_grad)
+                         skip_bias_grad, drop_p)

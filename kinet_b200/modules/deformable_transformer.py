@@ -83,11 +83,14 @@ def _level_grids(spatial_shapes, device):
     return out
 
 
-def _act_linear(x, layer, activation):
-    """activation(layer(x)); ReLU rides in the GEMM's epilogue (and, in the backward, in the bias-gradient pass)."""
+def _act_linear(x, layer, activation, drop=None):
+    """drop(activation(layer(x))); ReLU rides in the GEMM's epilogue (and, in the backward, in the bias-gradient pass,
+    together with the dropout's backward: no mask tensor, functions/layer_ops.py::dropout_)."""
+    p = drop.p if (drop is not None and drop.training) else 0.0
     if activation is F.relu:
-        return linear(x, layer, relu=True)
-    return activation(linear(x, layer))
+        return linear(x, layer, relu=True, drop_p=p)
+    y = activation(linear(x, layer))
+    return drop(y) if drop is not None else y
 
 
 class _skip_output_bias_grad:
@@ -199,7 +202,7 @@ class DeformableTransformerEncoderLayer(nn.Module):
         return self._ffn(_Stream.start(src, None), None, False).x
 
     def _ffn(self, st, pos, want_pos):
-        h = self.dropout2(_act_linear(st.x_lp, self.linear1, self.activation))
+        h = _act_linear(st.x_lp, self.linear1, self.activation, self.dropout2)
         # dropout3 and linear2's bias gradient ride in the fused add + LayerNorm step
         return _norm_step(st.x, linear(h, self.linear2, skip_bias_grad=True), self.norm2, pos, want_pos,
                           drop=self.dropout3, branch_bias=self.linear2.bias)
@@ -272,7 +275,7 @@ class DeformableTransformerDecoderLayer(nn.Module):
         return self._ffn(_Stream.start(tgt, None), None, False).x
 
     def _ffn(self, st, pos, want_pos):
-        h = self.dropout3(_act_linear(st.x_lp, self.linear1, self.activation))
+        h = _act_linear(st.x_lp, self.linear1, self.activation, self.dropout3)
         return _norm_step(st.x, linear(h, self.linear2, skip_bias_grad=True), self.norm3, pos, want_pos,
                           drop=self.dropout4, branch_bias=self.linear2.bias)
 

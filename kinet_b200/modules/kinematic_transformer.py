@@ -101,10 +101,11 @@ class TransformerEncoderLayer(nn.Module):
     # ---- batch-first streams (what the containers call) ----
     def _post_stream(self, st, pos, mask, last):
         src2 = _attention(self.self_attn, st.xpos_lp, st.xpos_lp, st.x_lp, mask, True)          # :331-333
-        st = _norm_step(st.x, self.dropout1(src2), self.norm1, None, False)                      # :334-335
-        h = self.dropout(_act_linear(st.x_lp, self.linear1, self.activation))                    # :336
-        return _norm_step(st.x, self.dropout2(linear(h, self.linear2)), self.norm2, pos,         # :337-338
-                          pos is not None and not last)
+        # (the branch dropouts are generated inside the fused add + LayerNorm kernels, the FFN's inner one without a mask)
+        st = _norm_step(st.x, src2, self.norm1, None, False, drop=self.dropout1)                 # :334-335
+        h = _act_linear(st.x_lp, self.linear1, self.activation, self.dropout)                    # :336
+        return _norm_step(st.x, linear(h, self.linear2, skip_bias_grad=True), self.norm2, pos,   # :337-338
+                          pos is not None and not last, drop=self.dropout2, branch_bias=self.linear2.bias)
 
     def _pre_bf(self, src, pos, mask):
         src2 = self.norm1(src)                                                                   # :345-352
@@ -148,12 +149,12 @@ class TransformerDecoderLayer(nn.Module):
 
     def _post_stream(self, st, mem_lp, mempos_lp, query_pos, tgt_mask_kp, mem_mask_kp, last):
         tgt2 = _attention(self.self_attn, st.xpos_lp, st.xpos_lp, st.x_lp, tgt_mask_kp, True)    # :393-395
-        st = _norm_step(st.x, self.dropout1(tgt2), self.norm1, query_pos, query_pos is not None)  # :396-397
+        st = _norm_step(st.x, tgt2, self.norm1, query_pos, query_pos is not None, drop=self.dropout1)  # :396-397
         tgt2 = _attention(self.multihead_attn, st.xpos_lp, mempos_lp, mem_lp, mem_mask_kp, False)  # :398-401
-        st = _norm_step(st.x, self.dropout2(tgt2), self.norm2, None, False)                       # :402-403
-        h = self.dropout(_act_linear(st.x_lp, self.linear1, self.activation))                     # :404
-        return _norm_step(st.x, self.dropout3(linear(h, self.linear2)), self.norm3, query_pos,    # :405-406
-                          query_pos is not None and not last)
+        st = _norm_step(st.x, tgt2, self.norm2, None, False, drop=self.dropout2)                  # :402-403
+        h = _act_linear(st.x_lp, self.linear1, self.activation, self.dropout)                     # :404
+        return _norm_step(st.x, linear(h, self.linear2, skip_bias_grad=True), self.norm3, query_pos,   # :405-406
+                          query_pos is not None and not last, drop=self.dropout3, branch_bias=self.linear2.bias)
 
     def _pre_bf(self, tgt, memory, mempos, query_pos, tgt_mask_kp, mem_mask_kp):
         tgt2 = self.norm1(tgt)                                                                    # :416-430

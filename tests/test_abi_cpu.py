@@ -30,7 +30,7 @@ def test_header_symbols_are_exported(lib):
     assert set(_lib.EXPORTS) == declared
     hdr2 = open(os.path.join(ROOT, "include", "kinet_layers_b200.h")).read()
     declared2 = set(re.findall(r"\b(kinet_b200_\w+)\s*\(", hdr2))
-    assert len(declared2) == 7
+    assert len(declared2) == 9
     for name in declared2:
         assert hasattr(lib, name), name
     assert set(_lib.LAYER_EXPORTS) == declared2

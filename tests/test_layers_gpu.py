@@ -592,7 +592,7 @@ def test_layers_bias_gradients_come_out_of_the_norm_steps():
             real_apply = lo.AddLayerNormFunction.apply
             lo_linear_params = lo.linear_params
             try:
-                lo.linear_params = lambda x, w, b, relu=False, mirror=None, skip_bias_grad=False: lo_linear_params(x, w, b, relu, mirror, False)
+                lo.linear_params = lambda x, w, b, relu=False, mirror=None, skip_bias_grad=False, drop_p=0.0: lo_linear_params(x, w, b, relu, mirror, False, drop_p)
                 import kinet_b200.modules.deformable_transformer as dt
                 dt_norm = dt.add_layer_norm
                 dt.add_layer_norm = lambda x, r, norm, pos=None, lp_dtype=None, want_lp=False, drop_p=0.0, branch_bias=None: \
@@ -607,3 +607,36 @@ def test_layers_bias_gradients_come_out_of_the_norm_steps():
             for m, tag in ((enc, "e."), (dec, "d.")):
                 for n_, p_ in m.named_parameters():
                     assert _rel(got[tag + n_], p_.grad) < 1e-4, n_
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_linear_relu_dropout_without_a_mask_tensor(dtype):
+    """y = dropout(relu(x W^T + b)) through LinearFunction: density of the zeros, and the backward -- which only sees
+    y's sign pattern -- against autograd through the same mask."""
+    from kinet_b200.functions import layer_ops as lo
+    dev = _dev()
+    g = torch.Generator().manual_seed(2)
+    rows, cin, cout, p = 2500, 64, 256, 0.1
+    lin = torch.nn.Linear(cin, cout).to(dev)
+    x = torch.randn(rows, cin, generator=g).to(dev).requires_grad_(True)
+    w = torch.randn(rows, cout, generator=g).to(dev)
+    with torch.autocast("cuda", dtype=dtype, enabled=dtype != torch.float32):
+        y = lo.linear(x, lin, relu=True, drop_p=p)
+    gx, gw, gb = torch.autograd.grad((y.float() * w).sum(), [x, lin.weight, lin.bias])
+    with torch.no_grad(), torch.autocast("cuda", dtype=dtype, enabled=dtype != torch.float32):
+        h = torch.relu(lin(x))
+    open_ = h > 0
+    kept = (y != 0) & open_
+    frac = 1.0 - kept.sum().item() / open_.sum().item()
+    assert abs(frac - p) < 5 * (p * (1 - p) / open_.sum().item()) ** 0.5 + 1e-4, frac
+    scale = lo.dropout_scale(p)
+    tol = 2e-5 if dtype == torch.float32 else 1.2e-2
+    assert _rel(y.float(), (h.float() * kept * scale)) < tol
+    xd = x.detach().double().requires_grad_(True)
+    wd, bd = lin.weight.detach().double().requires_grad_(True), lin.bias.detach().double().requires_grad_(True)
+    # (the surviving AND open elements, as y itself shows them: in bf16 the ReLU of a pre-activation within rounding
+    # distance of 0 may open in one arithmetic and not in the other, which is not what this test is about)
+    yd = torch.nn.functional.linear(xd, wd, bd) * (y != 0).double() * scale
+    rx, rw, rb = torch.autograd.grad((yd * w.double()).sum(), [xd, wd, bd])
+    assert _rel(gx, rx) < tol and _rel(gw, rw) < tol and _rel(gb, rb) < tol
