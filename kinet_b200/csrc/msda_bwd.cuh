@@ -276,16 +276,12 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, const FineT
     const int walk_items = ((coarse + d.tile_q - 1) / d.tile_q) * d.N * d.M;
     const int tile_items = split ? ft.total * d.N * d.M : 0;
     bool waited = false;
-    // The next claim is issued BEFORE the current item is processed and read after it: the counter's atomic queues
-    // behind this SM's outstanding reductions (1-2 us), which the item's own work hides.
-    if (threadIdx.x == 0) *s_claim = atomicAdd(split_claim, 1);
-    __syncthreads();
-    int item = *s_claim;
     for (;;) {
-        __syncthreads();                     // every thread has read *s_claim
+        if (threadIdx.x == 0) *s_claim = atomicAdd(split_claim, 1);
+        __syncthreads();
+        const int item = *s_claim;
+        __syncthreads();
         if (item >= walk_items + tile_items) break;
-        int next_claim = 0;
-        if (threadIdx.x == 0) next_claim = atomicAdd(split_claim, 1);
         if (item < walk_items) {
             const int chunk = item / (d.N * d.M);
             const int bm = item - chunk * (d.N * d.M);
@@ -305,19 +301,15 @@ __device__ __forceinline__ void backward_items(const LevelTable& lt, const FineT
             if (!waited) { asm volatile("griddepcontrol.wait;" ::: "memory"); waited = true; }
             // (written by the dense-window grid while THIS grid is already resident: a coherent load -- the read-only
             // data path, which `const __restrict__` invites, may serve a line cached before that grid finished)
-            if (*reinterpret_cast<const volatile uint8_t*>(dense_done + it) == 0) {
-                const int tile = it / (d.N * d.M);
-                const int bm = it - tile * (d.N * d.M);
-                const int b = bm / d.M, m = bm - b * d.M;
-                const TileRect r = fine_tile_rect(ft, lt, tile);
-                backward_rows<VT, AT, VEC, GS, NWARPS, WIDE, FUSED>(
-                    lt, stage_a, stage_dx, stage_b, fold, value, loc, attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa,
-                    b, m, kTileQueries, [&](int i) { return fine_tile_query(ft, lt, r, i, d.Lq); });
-            }
+            if (*reinterpret_cast<const volatile uint8_t*>(dense_done + it) != 0) continue;
+            const int tile = it / (d.N * d.M);
+            const int bm = it - tile * (d.N * d.M);
+            const int b = bm / d.M, m = bm - b * d.M;
+            const TileRect r = fine_tile_rect(ft, lt, tile);
+            backward_rows<VT, AT, VEC, GS, NWARPS, WIDE, FUSED>(
+                lt, stage_a, stage_dx, stage_b, fold, value, loc, attn, grad_out, grad_value_acc, grad_loc, grad_attn, d, fa,
+                b, m, kTileQueries, [&](int i) { return fine_tile_query(ft, lt, r, i, d.Lq); });
         }
-        if (threadIdx.x == 0) *s_claim = next_claim;
-        __syncthreads();
-        item = *s_claim;
     }
     // this grid must not complete before the dense-window kernel has (the rounding pass is ordered behind this grid)
     if (!waited) asm volatile("griddepcontrol.wait;" ::: "memory");
