@@ -75,6 +75,31 @@ def _attention(mha, q_in, k_in, v_in, key_padding_mask, self_attention):
     return linear(o, mha.out_proj)
 
 
+def _two_branches(fn_a, fn_b, device):
+    """(fn_a(), fn_b()) with fn_b on a second CUDA stream.  The detection and the metadata transformer do not see each
+    other until the IntertwinedBranch blocks, and every kernel of either occupies a fraction of the GPU (<= 150 CTAs,
+    2-5 us): side by side -- as two parallel branches of a captured CUDA graph, or two streams in eager mode -- they take
+    little more than one of them.  Inference only (no autograd graph crosses the streams here)."""
+    if device.type != "cuda" or torch.is_grad_enabled():
+        return fn_a(), fn_b()
+    main = torch.cuda.current_stream(device)
+    side = _side_streams.get(device.index)
+    if side is None:
+        side = _side_streams[device.index] = torch.cuda.Stream(device=device)
+    side.wait_stream(main)
+    with torch.cuda.stream(side):
+        b = fn_b()
+    a = fn_a()
+    main.wait_stream(side)
+    for t in (b if isinstance(b, (tuple, list)) else (b,)):
+        if torch.is_tensor(t):
+            t.record_stream(main)           # allocated on the side stream, consumed (and freed) on the main one
+    return a, b
+
+
+_side_streams = {}
+
+
 def _check_no_attn_mask(*masks):
     if any(m is not None for m in masks):
         raise RuntimeError("kinet_b200: attn_mask is not supported on the kine path (the reference passes None)")
@@ -328,10 +353,12 @@ class DualKinematicTransformer(nn.Module):
         (Lq, BS, C).  Returns (hs_det, hs_metadata, hs_without_norm_det) as (layers, BS, Lq, C) and memory_det
         (BS, T, C) -- the reference's ``transpose(1, 2)`` / ``permute(1, 0, 2)`` of its sequence-first tensors."""
         c = lambda t: None if t is None else t.contiguous()
-        hs_det, raw_det, memory_det = self.transformer_det._forward_bf(
-            c(src_boxes), mask, _bf(query_embed_bbox), _bf(tgt_bboxes), c(pos_boxes))
-        hs_meta, _, _ = self.transformer_metadata._forward_bf(
-            c(src_metadata), mask, _bf(query_embed_metadata), _bf(tgt_metadata), c(pos_metadata))
+        (hs_det, raw_det, memory_det), (hs_meta, _, _) = _two_branches(
+            lambda: self.transformer_det._forward_bf(c(src_boxes), mask, _bf(query_embed_bbox), _bf(tgt_bboxes),
+                                                     c(pos_boxes)),
+            lambda: self.transformer_metadata._forward_bf(c(src_metadata), mask, _bf(query_embed_metadata),
+                                                          _bf(tgt_metadata), c(pos_metadata)),
+            src_boxes.device)
         # the concatenation dimension of the reference (3: channels of a (layers, Lq, BS, C) stack) stays the last one
         self.detection_branch.dim_concat = self.metadata_branch.dim_concat = hs_det.dim() - 1
         hs_det = self.detection_branch(hs_det, hs_meta)
@@ -356,8 +383,9 @@ class DualKinematicEncoder(nn.Module):
     def forward(self, src_boxes, src_metadata, mask, pos_boxes=None, pos_metadata=None):
         """(:217-242) returns (hs_det[None], hs_metadata[None]) as (1, BS, T, C) and the two memories as (BS, C, T)."""
         c = lambda t: None if t is None else t.contiguous()
-        memory_det = self.encoder_det._forward_bf(c(src_boxes), mask, c(pos_boxes))
-        memory_meta = self.encoder_meta._forward_bf(c(src_metadata), mask, c(pos_metadata))
+        memory_det, memory_meta = _two_branches(
+            lambda: self.encoder_det._forward_bf(c(src_boxes), mask, c(pos_boxes)),
+            lambda: self.encoder_meta._forward_bf(c(src_metadata), mask, c(pos_metadata)), src_boxes.device)
         hs_det = self.detection_branch(memory_det, memory_meta)
         hs_meta = self.metadata_branch(memory_meta, memory_det)
         return hs_det[None], hs_meta[None], memory_meta.transpose(1, 2), memory_det.transpose(1, 2)
