@@ -112,6 +112,17 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32])
     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
 }
 
+// 4 consecutive fp32 columns (the tail of a D = 36 accumulator row)
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, float (&v)[4])
+{
+    uint32_t r[4];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = __uint_as_float(r[j]);
+}
+
 // ---- operand type helpers --------------------------------------------------------------------------------------
 template <typename T> struct Op16;
 template <> struct Op16<__nv_bfloat16> {
@@ -129,11 +140,23 @@ template <> struct Op16<__half> {
 // All MMA operands are K-major SWIZZLE_NONE; strides are padded by 16 bytes where the owner threads' 2-byte /
 // 4-byte accesses would otherwise fall into the same banks.
 template <int D> struct Plan {
-    static_assert(D % 16 == 0 && D >= 16 && D <= 64, "channels per head: whole K = 16 steps, <= 64 accumulator columns");
-    static constexpr int KCH = D / 8;                       // 16-byte chunks of a channel row
-    // G [128 q][D] and V [128 pix][D]: rows of D channels
-    // (chunk stride 160 / 144 bytes: the D / 8 lanes that store one row's chunks hit different banks)
+    static_assert(D % 4 == 0 && D >= 16 && D <= 64, "channels per head: rows of whole 8-byte pieces, <= 64 accumulator columns");
+    // The tensor core wants K (dot product) and N (scatter product) in steps of 16: D = 36 is padded to DP = 48 -- in shared
+    // memory only (the pad chunks of G and V are zeroed once and never written: they contribute exact zeros).
+    static constexpr int DP = (D + 15) / 16 * 16;
+    static constexpr int KCH = DP / 8;                      // 16-byte chunks of a (padded) channel row
+    // A channel row moves between global and shared memory in pieces of 16 bytes when rows are 16-byte aligned (D % 8 == 0),
+    // else of 8 bytes (D = 36: 72-byte rows); PPR pieces per row, RPI rows per warp instruction, NIT instructions per 32 rows
+    static constexpr int PIECE = (D % 8 == 0) ? 16 : 8;
+    static constexpr int PPR = D * 2 / PIECE, RPI = 32 / PPR, NIT = (32 + RPI - 1) / RPI;
+    // G [128 q][DP] and V [128 pix][DP]: rows of DP channels
+    // (chunk stride 160 / 144 bytes: the lanes that store one row's chunks hit different banks)
     static constexpr uint32_t G_LBO = KCH == 4 ? 160 : 144, G_SBO = KCH * G_LBO, G_BYTES = 16 * G_SBO;
+    // byte offset of piece c of row r inside a G / V image
+    static __device__ __forceinline__ uint32_t piece_off(int r, int c)
+    {
+        return (uint32_t)((r & 7) * 16 + (r >> 3) * G_SBO + ((c * PIECE) >> 4) * G_LBO + ((c * PIECE) & 15));
+    }
     // W [128 pix][128 q]
     static constexpr uint32_t W_LBO = 144, W_SBO = 16 * 144 + 16, W_BYTES = 16 * W_SBO;
     // (the scatter product's B operand is G itself, read MN-major: no transposed copy)
@@ -287,7 +310,7 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                            float* __restrict__ grad_value_acc, AT* __restrict__ grad_loc,
                            AT* __restrict__ grad_attn, const KernelDims d, const FusedArgs fa, const DenseArgs da)
 {
-    static_assert(D % 32 == 0, "accumulator rows are read 32 columns at a time");
+    static_assert(D % 32 == 0 || D % 32 == 4, "accumulator rows are read 32 columns at a time (+ one group of 4)");
     using P = Plan<D>;
     using O = Op16<VT>;
     constexpr int NW = kThreads / 32;
@@ -316,6 +339,8 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
 
     // one-time setup: zero W (the owner threads restore the zeros after every chunk), TMEM, barrier
     for (uint32_t i = tid * 16; i < P::W_BYTES; i += kThreads * 16) *reinterpret_cast<uint4*>(sW + i) = make_uint4(0, 0, 0, 0);
+    if constexpr (P::DP != D)      // padded channels of G and of both V buffers: zero for good
+        for (uint32_t i = tid * 16; i < 3 * P::G_BYTES; i += kThreads * 16) *reinterpret_cast<uint4*>(sG + i) = make_uint4(0, 0, 0, 0);
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(&s_tmem)), "r"((uint32_t)kTmemCols));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
@@ -340,7 +365,7 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
     // B = G as staged for the dot product, [K = 128 query rows][N = D channels]: MN-major (instruction descriptor bit 16);
     // for an MN-major SWIZZLE_NONE operand the descriptor's LBO is the stride between 8-row groups along K and its SBO
     // the stride between 16-byte chunks along N (tools/micro/umma_probe.cu tests 8 / 9, profiles/r2_umma_probe.txt)
-    constexpr uint32_t idesc_gv = umma_idesc(128, D, O::fmt) | (1u << 16);
+    constexpr uint32_t idesc_gv = umma_idesc(128, P::DP, O::fmt) | (1u << 16);
 
     int slot = 0;
     DT_DECL
@@ -513,16 +538,23 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
         DT_MARK(2)
         // ---- G: the item's rows of grad_out -> operand A of the dot product (K-major) and, the same bytes read MN-major,
         // operand B of the scatter product.  D / 8 lanes per row (16 bytes each): a warp instruction reads 32 / (D / 8) whole rows.
-        constexpr int LPRV = P::KCH, RPIV = 32 / LPRV;
         {
 #pragma unroll
-            for (int i = 0; i < LPRV; ++i) {
-                const int rr = i * RPIV + lane / LPRV, c = lane % LPRV;
-                const int qq = __shfl_sync(0xffffffffu, q, rr);
-                uint4 g4 = make_uint4(0, 0, 0, 0);
-                if (qq >= 0) g4 = __ldg(reinterpret_cast<const uint4*>(grad_out + (((size_t)b * d.Lq + qq) * d.M + m) * D) + c);
-                const int trow = warp * 32 + rr;
-                *reinterpret_cast<uint4*>(sG + (trow & 7) * 16 + (trow >> 3) * P::G_SBO + c * P::G_LBO) = g4;
+            for (int i = 0; i < P::NIT; ++i) {
+                const int rl = i * P::RPI + lane / P::PPR, c = lane % P::PPR;      // row inside the warp's 32, piece of the row
+                const bool act = lane / P::PPR < P::RPI && rl < 32;
+                const int qq = __shfl_sync(0xffffffffu, q, rl & 31);
+                const int trow = warp * 32 + rl;
+                const char* src = reinterpret_cast<const char*>(grad_out + (((size_t)b * d.Lq + max(qq, 0)) * d.M + m) * D) + c * P::PIECE;
+                if constexpr (P::PIECE == 16) {
+                    uint4 g4 = make_uint4(0, 0, 0, 0);
+                    if (act && qq >= 0) g4 = __ldg(reinterpret_cast<const uint4*>(src));
+                    if (act) *reinterpret_cast<uint4*>(sG + P::piece_off(trow, c)) = g4;
+                } else {
+                    uint2 g2 = make_uint2(0, 0);
+                    if (act && qq >= 0) g2 = __ldg(reinterpret_cast<const uint2*>(src));
+                    if (act) *reinterpret_cast<uint2*>(sG + P::piece_off(trow, c)) = g2;
+                }
             }
         }
 
@@ -606,28 +638,27 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
             const float inv_ww = 1.f / (float)ww;
             int pwy = (int)(((float)tid + 0.5f) * inv_ww), pwx = tid - pwy * ww;
             const int step_y = (int)(((float)kPix + 0.5f) * inv_ww), step_x = kPix - step_y * ww;
-            int vwy[LPRV], vwx[LPRV];       // ... and of the pixels whose value rows this thread fetches
-#pragma unroll
-            for (int i = 0; i < LPRV; ++i) {
-                const int r = warp * 32 + i * RPIV + lane / LPRV;
-                vwy[i] = (int)(((float)r + 0.5f) * inv_ww);
-                vwx[i] = r - vwy[i] * ww;
-            }
-
-            // value rows of chunk kk -> V buffer kk & 1 (operand B of the dot product): D / 8 lanes per pixel row, 16 bytes
+            // value rows of chunk kk -> V buffer kk & 1 (operand B of the dot product): PPR lanes per pixel row, one piece
             // each, global -> shared without passing through registers; rows beyond the window are zero-filled
             auto fetch_values = [&](int kk) {
                 uint8_t* vb = sV + (kk & 1) * P::G_BYTES;
 #pragma unroll
-                for (int i = 0; i < LPRV; ++i) {
-                    const int trow = warp * 32 + i * RPIV + lane / LPRV;
-                    const bool ok = kk * kPix + trow < npix;
-                    const size_t vp = ok ? (size_t)lt.start[l] + (size_t)(ymin + vwy[i]) * W + (xmin + vwx[i]) : 0;
-                    const uint32_t dst = smem_u32(vb + (trow & 7) * 16 + (trow >> 3) * P::G_SBO + (lane % LPRV) * P::G_LBO);
-                    const void* src = reinterpret_cast<const uint4*>(vbase + vp * pix_stride) + lane % LPRV;
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(ok ? 16 : 0) : "memory");
-                    vwy[i] += step_y; vwx[i] += step_x;
-                    if (vwx[i] >= ww) { vwx[i] -= ww; ++vwy[i]; }
+                for (int i = 0; i < P::NIT; ++i) {
+                    const int rl = i * P::RPI + lane / P::PPR, c = lane % P::PPR;
+                    const int trow = warp * 32 + rl;
+                    const int r = kk * kPix + trow;                               // window-linear pixel
+                    const bool act = lane / P::PPR < P::RPI && rl < 32;
+                    const bool ok = r < npix;
+                    const int wy = (int)(((float)r + 0.5f) * inv_ww), wx = r - wy * ww;
+                    const size_t vp = ok ? (size_t)lt.start[l] + (size_t)(ymin + wy) * W + (xmin + wx) : 0;
+                    const uint32_t dst = smem_u32(vb + P::piece_off(trow, c));
+                    const void* src = reinterpret_cast<const char*>(vbase + vp * pix_stride) + c * P::PIECE;
+                    if (act) {
+                        if constexpr (P::PIECE == 16)
+                            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(ok ? 16 : 0) : "memory");
+                        else
+                            asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" :: "r"(dst), "l"(src), "r"(ok ? 8 : 0) : "memory");
+                    }
                 }
                 asm volatile("cp.async.commit_group;" ::: "memory");
             };
@@ -683,7 +714,7 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                     const uint64_t dg = umma_desc(smem_u32(sG), P::G_LBO, P::G_SBO);
                     const uint64_t dv = umma_desc(smem_u32(sV) + (k & 1) * P::G_BYTES, P::G_LBO, P::G_SBO);
 #pragma unroll
-                    for (int j = 0; j < D / 16; ++j)
+                    for (int j = 0; j < P::DP / 16; ++j)
                         umma(tmem_u, dg + (uint64_t)(j * 2 * P::G_LBO / 16), dv + (uint64_t)(j * 2 * P::G_LBO / 16), idesc_u, j > 0);
                     umma_commit(mbar);
                     const uint64_t dw = umma_desc(smem_u32(sW), P::W_LBO, P::W_SBO);
@@ -732,7 +763,8 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
                 if (r0 + warp * 32 < npix) {         // (warp-uniform) this warp's 32 pixel rows exist
                     float gv[D];
 #pragma unroll
-                    for (int c0 = 0; c0 < D; c0 += 32) tmem_ld32(tmem_gv + lane_sel + c0, *reinterpret_cast<float(*)[32]>(&gv[c0]));
+                    for (int c0 = 0; c0 + 32 <= D; c0 += 32) tmem_ld32(tmem_gv + lane_sel + c0, *reinterpret_cast<float(*)[32]>(&gv[c0]));
+                    if constexpr (D % 32 == 4) tmem_ld4(tmem_gv + lane_sel + (D - 4), *reinterpret_cast<float(*)[4]>(&gv[D - 4]));
                     uint32_t any = 0;
 #pragma unroll
                     for (int j = 0; j < D; ++j) any |= __float_as_uint(gv[j]);
@@ -750,8 +782,8 @@ msda_backward_dense_kernel(const VT* __restrict__ value, const int64_t* __restri
 #pragma unroll
                     for (int i = 0; i < 32; i += RPI) {
                         const int rr = i + lane / LPR;
-                        const unsigned spix = __shfl_sync(0xffffffffu, my_pix, rr);
-                        if ((live >> rr) & 1u) {
+                        const unsigned spix = __shfl_sync(0xffffffffu, my_pix, rr & 31);
+                        if (lane / LPR < RPI && rr < 32 && ((live >> rr) & 1u)) {
                             const float4 x = *reinterpret_cast<const float4*>(wstage + i * P::STAGE_STRIDE);
                             red_add_f32x4(my_dst + (size_t)spix * pix_stride, x.x, x.y, x.z, x.w);
                         }

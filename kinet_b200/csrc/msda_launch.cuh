@@ -363,11 +363,11 @@ int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, 
             acc = (float*)ws;
         }
     }
-    // dense-window tensor-core path: encoder form, 16-bit values, D = 32 / 64, and a workspace with room for
+    // dense-window tensor-core path: encoder form, 16-bit values, D = 32 / 36 / 64, and a workspace with room for
     // the work counter (msda_b200_backward_workspace_bytes)
     bool dense_ok = false;
     if constexpr (sizeof(VT) == 2) {
-        dense_ok = !acc16 && d->Lq == d->S && d->Lq > 0 && d->P <= dense::kMaxP && (d->D == 32 || d->D == 64) &&
+        dense_ok = !acc16 && d->Lq == d->S && d->Lq > 0 && d->P <= dense::kMaxP && (d->D == 32 || d->D == 36 || d->D == 64) &&
                    (!fa || d->L * d->P <= kFusedMaxChunks * chunk_of(d->D / 4)) &&     // the per-row kernel's fused limit
                    ws_bytes >= dense_counter_offset(nval) + dense_extra_bytes(d) && aligned16(value) && aligned16(go) &&
                    aligned16(loc) && aligned16(attn) && aligned16(gl) && aligned16(ga) &&
@@ -387,9 +387,11 @@ int backward_typed(const void* value, const int64_t* shapes, const int64_t* ls, 
                 uint8_t* dense_done = reinterpret_cast<uint8_t*>(claim) + kDenseCounterBytes;
                 if (fa) {
                     if (d->D == 32) rc = launch_backward_dense<VT, AT, 32, true>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, dense_done, d, st, *fa);
+                    else if (d->D == 36) rc = launch_backward_dense<VT, AT, 36, true>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, dense_done, d, st, *fa);
                     else rc = launch_backward_dense<VT, AT, 64, true>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, dense_done, d, st, *fa);
                 } else {
                     if (d->D == 32) rc = launch_backward_dense<VT, AT, 32, false>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, dense_done, d, st, FusedArgs{});
+                    else if (d->D == 36) rc = launch_backward_dense<VT, AT, 36, false>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, dense_done, d, st, FusedArgs{});
                     else rc = launch_backward_dense<VT, AT, 64, false>(value, shapes, ls, loc, attn, go, acc, gl, ga, claim, dense_done, d, st, FusedArgs{});
                 }
                 done = true;

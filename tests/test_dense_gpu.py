@@ -91,6 +91,8 @@ CASES = [
     ("one_level", [(33, 47)], 1, 2, 32, 4),                                 # L = 1: everything is the finest level
     ("tiny", [(3, 5), (2, 2)], 2, 1, 32, 2),                                # less than one tile
     ("finest_last", [(6, 9), (12, 18), (24, 36)], 1, 2, 32, 4),            # the finest level is not level 0
+    ("d36", [(20, 31), (10, 16), (5, 8), (3, 4)], 2, 3, 36, 4),            # D = 36: K / N padded to 48, 8-byte row pieces, odd M
+    ("d36_thin", [(37, 53), (19, 27), (1, 9), (7, 1)], 1, 8, 36, 4),
 ]
 
 
@@ -165,13 +167,14 @@ def test_dense_backward_run_to_run_and_zero_rows():
 
 @pytest.mark.parametrize("ref_dim,masked", [(2, False), (2, True), (4, True)])
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16], ids=["bf16", "f16"])
-def test_dense_fused_prologue_matches_per_row_fused(dtype, ref_dim, masked):
+@pytest.mark.parametrize("D", [32, 36])
+def test_dense_fused_prologue_matches_per_row_fused(dtype, ref_dim, masked, D):
     """The module-prologue entry point (raw offsets, logits, reference points): the dense kernel against the fused
     per-row kernels, and against the unfused PyTorch prologue + autograd in fp32 for the scalar gradients."""
     from kinet_b200.functions import MSDeformAttnFusedFunction
     dev = _dev()
     levels = [(20, 31), (10, 16), (5, 8), (3, 4)]
-    N, M, D, P, L = 2, 2, 32, 4, 4
+    N, M, P, L = 2, 2, 4, 4
     S = sum(h * w for h, w in levels)
     g = torch.Generator(device="cpu").manual_seed(7)
     value = torch.randn(N, S, M, D, generator=g).to(dtype).to(dev)
