@@ -19,7 +19,7 @@ KERNELS = [("dense-window backward, bf16 value / f32 aux, D=32, plain", "msda_ba
            ("add + LayerNorm forward", "add_layernorm_fwd_kernel"),
            ("add + LayerNorm backward", "add_layernorm_bwd_kernel")]
 SHOW = ["UTCHMMA", "UTCBAR", "LDTM", "UTCATOMSWS", "LDGSTS", "REDG.E.ADD.F32x4", "RED.E.ADD", "REDG.E.ADD.BF16x2", "FFMA2", "CCTL", "SYNCS",
-        "FENCE.VIEW.ASYNC", "ATOMG", "LDG.E.128", "STS.128", "LDS.128", "REDUX"]
+        "FENCE.VIEW.ASYNC", "ATOMG", "LDG.E.128", "STS.128", "LDS.128", "REDUX", "ACQBULK", "PREEXIT"]
 for title, sub in KERNELS:
     blocks = [b for b in txt.split("Function : ")[1:] if sub in b.split("\n", 1)[0]]
     if not blocks:
