@@ -48,7 +48,7 @@ def test_workspace_size(lib):
     d = MsdaDims(2, 100, 8, 32, 4, 7, 4)
     assert lib.msda_b200_backward_workspace_bytes(MSDA_F32, ctypes.byref(d)) == 0
     # fp32 accumulator (rounded up to 256 bytes) + the dense-window kernel's work counter (256 bytes) and its
-    # deferred-item flags: one byte per (tile, batch, head), at most Lq / 32 + 64 tiles
+    # done-item flags: one byte per (tile, batch, head), at most Lq / 32 + 64 tiles
     acc = 2 * 100 * 8 * 32 * 4
     flags = (7 // 32 + 64) * 2 * 8
     assert lib.msda_b200_backward_workspace_bytes(MSDA_BF16, ctypes.byref(d)) == (acc + 255) // 256 * 256 + 256 + (flags + 255) // 256 * 256
