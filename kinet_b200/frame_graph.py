@@ -152,6 +152,7 @@ class KineFrameGraphs:
     buffers valid until the next call.  Inference only."""
 
     def __init__(self, transformer, heads, token_bucket=32, track_bucket=1, autocast_dtype=torch.bfloat16, warmup=2):
+        """transformer: modules.kinematic_transformer.DualKinematicTransformer; heads: see __call__."""
         self.transformer, self.heads = transformer, heads
         self.token_bucket, self.track_bucket = int(token_bucket), int(track_bucket)
         self.autocast_dtype, self.warmup = autocast_dtype, int(warmup)
@@ -167,9 +168,11 @@ class KineFrameGraphs:
 
     def __call__(self, src_det, src_meta, pos_det, pos_meta, tgt_det=None, tgt_meta=None):
         """src_* / pos_* (1, T, C) token embeddings; tgt_* (K, 1, C) projected track-query embeddings or None.
-        ``heads(hs_det, hs_meta)`` maps the transformer's (layers, 1, K + num_queries, C) outputs to what the caller
-        wants back.  Returns heads' output computed on the padded problem with the K padding rows removed by the
-        caller's ``heads`` (it receives ``pad_k`` as a keyword)."""
+        ``heads(transformer, bufs, padded_K)`` is the frame's computation as the caller wants it recorded: it reads the
+        static buffers ``bufs`` (src_det, src_meta, pos_det, pos_meta (1, Tp, C); mask (1, Tp) bool; tgt_det, tgt_meta
+        (Kp, 1, C)), calls the transformer and returns whatever should come back (tools/kine_bench.py::make_heads: class
+        logits, boxes and the detection embeddings of the last layer).  Returns (that result -- static buffers, valid
+        until the next call --, number of padding track-query rows at the FRONT of the query dimension)."""
         T, C = src_det.shape[1], src_det.shape[2]
         K = 0 if tgt_det is None else tgt_det.shape[0]
         Tp = -(-T // self.token_bucket) * self.token_bucket
