@@ -422,3 +422,43 @@ def test_kinematic_detector_matches_reference_golden_and_takes_track_queries():
     assert out["pred_logits"].shape == (2, 9, 2) and out["pred_boxes"].shape == (2, 9, 4)
     assert _rel(out["pred_logits"], want_logits) < 2e-5 and _rel(out["pred_boxes"], want_boxes) < 2e-5
     assert _rel(hs_det, hd) < 2e-5
+
+
+@pytest.mark.gpu
+def test_kine_frame_graphs_match_direct_calls_with_varying_sizes():
+    """KineFrameGraphs: token counts padded to a bucket and masked, track queries at their own count (track_bucket = 1):
+    every frame equals the direct call; the graphs are recorded once per (padded tokens, track queries) pair."""
+    import torch.nn.functional as F
+    from kinet_b200.frame_graph import KineFrameGraphs
+    from kinet_b200.modules import kinematic_transformer as kt
+    dev = _dev()
+    d, nq = 72, 6
+    model = _by_name(kt.DualKinematicTransformer(d_model=d, nhead=8, num_encoder_layers=1, num_decoder_layers=1,
+                                                 dim_feedforward=48, dropout=0.0, return_intermediate_dec=True)).to(dev).eval()
+    g = torch.Generator().manual_seed(8)
+    qe_d, qe_m = torch.randn(nq, 1, d, generator=g).to(dev), torch.randn(nq, 1, d, generator=g).to(dev)
+
+    def heads(transformer, bufs, Kp):
+        qd, qm = F.pad(qe_d, (0, 0, 0, 0, Kp, 0)), F.pad(qe_m, (0, 0, 0, 0, Kp, 0))
+        td = F.pad(bufs["tgt_det"], (0, 0, 0, 0, 0, nq)) if Kp else None
+        tm = F.pad(bufs["tgt_meta"], (0, 0, 0, 0, 0, nq)) if Kp else None
+        hs_det, hs_meta, _, _ = transformer(bufs["src_det"], bufs["src_meta"], bufs["mask"], qd, qm, td, tm,
+                                            bufs["pos_det"], bufs["pos_meta"])
+        return hs_det[-1], hs_meta[-1]
+    fg = KineFrameGraphs(model, heads, token_bucket=8, track_bucket=1, autocast_dtype=None)
+    sizes = [(5, 0), (11, 3), (8, 3), (13, 2), (11, 3), (6, 0)]
+    for T, K in sizes:
+        toks = [torch.randn(1, T, d, generator=g).to(dev) for _ in range(4)]
+        tg = [torch.randn(K, 1, d, generator=g).to(dev) for _ in range(2)] if K else [None, None]
+        (hd, hm), pad = fg(*toks, *tg)
+        assert pad == 0
+        with torch.no_grad():
+            qd, qm = F.pad(qe_d, (0, 0, 0, 0, K, 0)), F.pad(qe_m, (0, 0, 0, 0, K, 0))
+            td = F.pad(tg[0], (0, 0, 0, 0, 0, nq)) if K else None
+            tm = F.pad(tg[1], (0, 0, 0, 0, 0, nq)) if K else None
+            want_d, want_m, _, _ = model(toks[0], toks[1], torch.zeros(1, T, dtype=torch.bool, device=dev), qd, qm, td, tm,
+                                         toks[2], toks[3])
+        assert hd.shape == want_d[-1].shape
+        assert _rel(hd, want_d[-1]) < 2e-5 and _rel(hm, want_m[-1]) < 2e-5, (T, K)
+    assert fg.recorded_buckets == [(8, 0), (8, 3), (16, 2), (16, 3)]
+    assert fg.replays == len(sizes)
