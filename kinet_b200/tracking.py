@@ -364,3 +364,176 @@ def synthetic_sequence(levels, d_model, n_frames, device, seed=0, drift=0.05, dt
     for _ in range(n_frames):
         cur = [(1 - drift) * c + drift * torch.randn(c.shape, generator=g) + drift * s for c, s in zip(cur, scene)]
         yield [c.to(device=device, dtype=dtype) for c in cur], masks, pos
+
+
+# =====================================================================================================================
+# The literal KineT tracker: kinematic detector over detection tokens
+# =====================================================================================================================
+class KineSequenceTracker:
+    """Tracks one sequence frame by frame with the `kine` model -- the loop of the reference's ``TrackerKinematic.step``
+    (src/trackformer/models/tracker.py:626-880) around ``kinet_b200.modules.kinematic_detector``:
+
+      * :652-671  every live track hands its TRAIL -- its last ``n_frames`` relative boxes and scores (``TrackKinematic.
+        get_trail``, :1027-1046; a young track repeats its oldest entry) -- to the detector as a track query
+        (``track_query_hs_embeds_det / _meta``; the tracklet encoder is the identity, ``use_encoding_tracklets: False``);
+      * :672-690  detector forward, PostProcess (softmax over classes + no-object, best real class; boxes cxcywh -> xyxy
+        pixels, clipped unless ``overflow_boxes``);
+      * :692-707, :937-955  a track survives while score > ``track_obj_score_thresh`` and its label is class 0 (its trail
+        grows by the new box / score), else it counts a miss and ends after ``steps_termination`` misses; NMS among tracks;
+      * :750, :895-930  object queries above ``detection_obj_score_thresh`` start tracks whose trail is the detection repeated
+        ``n_frames`` times (``generate_pseudo_tracklets``); :820-838 NMS in which existing tracks always win;
+      * :860-880  per-frame results.
+
+    Not covered (as in SequenceTracker): re-identification of inactive tracks, public detections.  The reference's
+    ``add_tracks`` (:882-893) does not run as shipped (it passes ``confidence=`` to a constructor without that parameter,
+    SURVEY.md F7); the evident intent -- a TrackKinematic holding the detection's box, score and pseudo-trail -- is built.
+
+    ``detector``: kinematic_detector.KinematicDetectorTransformer whose backbones accept ``(tokens, pos)`` pairs (e.g. the
+    pass-through in tools/kine_bench.py; the reference's Kinet_Backbone + position encoding are the caller's).  A frame is
+    ``(src_det, src_meta, pos_det, pos_meta)``, each (1, T, C).  ``use_graphs``: replay kinet_b200.frame_graph.KineFrameGraphs
+    (tokens padded to ``token_bucket`` and masked; one graph per (padded T, K)); otherwise the detector runs eagerly through
+    its own forward (``targets`` carrying the trails).  One device -> host read per frame; track state lives on the host
+    (a few dozen boxes) and goes to the device through pinned staging."""
+
+    def __init__(self, detector, img_size, n_frames=5, detection_obj_score_thresh=0.4, track_obj_score_thresh=0.4,
+                 detection_nms_thresh=0.9, track_nms_thresh=0.9, steps_termination=1, n_classes=1, use_graphs=False,
+                 token_bucket=32, autocast_dtype=None):
+        self.detector = detector
+        self.img_h, self.img_w = float(img_size[0]), float(img_size[1])
+        self.n_frames = int(n_frames)
+        self.det_thresh, self.trk_thresh = detection_obj_score_thresh, track_obj_score_thresh
+        self.det_nms, self.trk_nms = detection_nms_thresh, track_nms_thresh
+        self.steps_termination, self.n_classes = steps_termination, n_classes
+        self.use_graphs, self.token_bucket, self.autocast_dtype = use_graphs, token_bucket, autocast_dtype
+        self._graphs = None
+        self.reset()
+
+    def reset(self):
+        self.tracks = []          # dicts: id, box (xyxy px), score, trail (list of cxcywh rel), scores (list), misses
+        self.next_id = 0
+        self.frame_index = 0
+        self.results = {}
+
+    # ---- trails -> track-query inputs (tracker.py:652-671, :1027-1046) ----
+    def _trails(self):
+        n, K = self.n_frames, len(self.tracks)
+        det = np.empty((K, n * 4), np.float32)
+        meta = np.empty((K, n), np.float32)
+        for i, t in enumerate(self.tracks):
+            tr, sc = t["trail"][-n:], t["scores"][-n:]
+            tr = [tr[0]] * (n - len(tr)) + tr
+            sc = [sc[0]] * (n - len(sc)) + sc
+            det[i] = np.concatenate(tr)
+            meta[i] = sc
+        return det, meta
+
+    def _to_device(self, dev, det, meta):
+        """(K, n*4) and (K, n) host arrays -> device tensors through pinned staging (see SequenceTracker._to_device_indices)."""
+        n = det.size + meta.size
+        st = getattr(self, "_stage", None)
+        if st is None or st[0].shape[0] < n:
+            cap = max(4096, 2 * n)
+            st = self._stage = [torch.empty(cap).pin_memory(), torch.empty(cap).pin_memory(), 0]
+        st[2] ^= 1
+        host = st[st[2]]
+        flat = host.numpy()
+        flat[:det.size] = det.ravel()
+        flat[det.size:n] = meta.ravel()
+        d = host[:n].to(dev, non_blocking=True)
+        return d[:det.size].view(det.shape), d[det.size:].view(meta.shape)
+
+    # ---- one detector call -> packed (Lq, 6): score, label, box cx cy w h (relative) ----
+    def _pack(self, logits, boxes):
+        prob = logits.float().softmax(-1)[..., :-1]                     # PostProcess: no-object is the last class
+        scores, labels = prob.max(-1)
+        return torch.cat([scores[0, :, None], labels[0, :, None].to(scores.dtype), boxes[0].float()], -1)
+
+    def _detect_eager(self, frame, det_t, meta_t):
+        from .modules.kinematic_detector import TokenFeatures  # noqa: F401  (the backbones' interface)
+
+        class _S:
+            pass
+        s = _S()
+        s.detections, s.metadata = (frame[0], frame[2]), (frame[1], frame[3])
+        targets = None
+        if det_t is not None:
+            targets = [{"track_query_hs_embeds_det": det_t, "track_query_hs_embeds_meta": meta_t}]
+        with torch.autocast("cuda", dtype=self.autocast_dtype, enabled=self.autocast_dtype is not None):
+            out = self.detector(s, targets)[0]
+        return self._pack(out["pred_logits"], out["pred_boxes"])
+
+    def _detect_graph(self, frame, det_t, meta_t):
+        from .frame_graph import KineFrameGraphs
+        from .functions.layer_ops import linear
+        det = self.detector
+        if self._graphs is None:
+            nq = det.num_queries
+
+            def heads(transformer, bufs, Kp):
+                pad = lambda e: torch.nn.functional.pad(e.weight[:, None], (0, 0, 0, 0, Kp, 0))
+                td = torch.nn.functional.pad(bufs["tgt_det"], (0, 0, 0, 0, 0, nq)) if Kp else None
+                tm = torch.nn.functional.pad(bufs["tgt_meta"], (0, 0, 0, 0, 0, nq)) if Kp else None
+                hs_det, hs_meta, _, _ = transformer(bufs["src_det"], bufs["src_meta"], bufs["mask"], pad(det.query_embed_det),
+                                                    pad(det.query_embed_metadata), td, tm, bufs["pos_det"], bufs["pos_meta"])
+                return self._pack(linear(hs_meta[-1], det.class_embed), det.bbox_embed(hs_det[-1]).sigmoid())
+            self._graphs = KineFrameGraphs(det.transformer, heads, token_bucket=self.token_bucket, track_bucket=1,
+                                           autocast_dtype=self.autocast_dtype)
+        tgt_d = tgt_m = None
+        if det_t is not None:
+            with torch.autocast("cuda", dtype=self.autocast_dtype, enabled=self.autocast_dtype is not None):
+                tgt_d = det.input_proj_tracklets_det(det_t)[:, None].float()
+                tgt_m = det.input_proj_tracklets_metadata(meta_t)[:, None].float()
+        packed, _ = self._graphs(frame[0], frame[1], frame[2], frame[3], tgt_d, tgt_m)
+        return packed
+
+    @torch.no_grad()
+    def step(self, frame):
+        """frame = (src_det, src_meta, pos_det, pos_meta), each (1, T, C) on the device -> {track_id: {"bbox", "score"}}."""
+        dev = frame[0].device
+        K = len(self.tracks)
+        det_t = meta_t = None
+        if K:
+            det_t, meta_t = self._to_device(dev, *self._trails())
+        packed = (self._detect_graph if self.use_graphs else self._detect_eager)(frame, det_t, meta_t)
+        return self._update(packed.cpu().numpy(), K)                      # ONE device -> host read per frame
+
+    def _update(self, packed, K):
+        sc, lb, rel = packed[:, 0], packed[:, 1].astype(np.int64), packed[:, 2:6].astype(np.float64)
+        rel = np.clip(rel, 0.0, 1.0)                                       # relative boxes are clamped (:688-690)
+        wh = np.array([self.img_w, self.img_h, self.img_w, self.img_h])
+        px = np.stack([rel[:, 0] - rel[:, 2] / 2, rel[:, 1] - rel[:, 3] / 2, rel[:, 0] + rel[:, 2] / 2, rel[:, 1] + rel[:, 3] / 2], -1) * wh
+        px = np.minimum(np.clip(px, 0, None), wh)                          # clip_boxes_to_image
+        live = []
+        for j, t in enumerate(self.tracks):                                # manage_active_tracks (:937-955)
+            if sc[j] > self.trk_thresh and lb[j] == 0:
+                t["box"], t["score"], t["misses"] = px[j], float(sc[j]), 0
+                t["trail"].append(rel[j].astype(np.float32))
+                t["scores"].append(np.float32(sc[j]))
+                live.append(t)
+            else:
+                t["misses"] += 1
+                if t["misses"] < self.steps_termination:
+                    live.append(t)
+        if self.trk_nms and live:
+            k = _nms(np.stack([t["box"] for t in live]), np.asarray([t["score"] for t in live]), self.trk_nms)
+            live = [live[i] for i in k]
+        new = []
+        obj = slice(K, None)
+        for i in K + np.flatnonzero((sc[obj] > self.det_thresh) & (lb[obj] < self.n_classes)):     # generate_new_tracks
+            new.append({"id": -1, "box": px[i], "score": float(sc[i]), "misses": 0,
+                        "trail": [rel[i].astype(np.float32)] * self.n_frames, "scores": [np.float32(sc[i])] * self.n_frames})
+        if self.det_nms and (live or new):                                 # existing tracks always win (:820-838)
+            boxes = np.stack([t["box"] for t in live + new])
+            scores = np.asarray([np.inf] * len(live) + [t["score"] for t in new])
+            k = set(_nms(boxes, scores, self.det_nms).tolist())
+            new = [t for j, t in enumerate(new) if j + len(live) in k]
+            live = [t for j, t in enumerate(live) if j in k]
+        for t in new:
+            t["id"] = self.next_id
+            self.next_id += 1
+        self.tracks = live + new
+        frame = {t["id"]: {"bbox": np.array(t["box"], dtype=np.float64), "score": t["score"]} for t in self.tracks}
+        for tid, r in frame.items():
+            self.results.setdefault(tid, {})[self.frame_index] = r
+        self.frame_index += 1
+        return frame

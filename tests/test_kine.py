@@ -462,3 +462,49 @@ def test_kine_frame_graphs_match_direct_calls_with_varying_sizes():
         assert _rel(hd, want_d[-1]) < 2e-5 and _rel(hm, want_m[-1]) < 2e-5, (T, K)
     assert fg.recorded_buckets == [(8, 0), (8, 3), (16, 2), (16, 3)]
     assert fg.replays == len(sizes)
+
+
+@pytest.mark.gpu
+def test_kine_sequence_tracker_graphs_match_eager_detector_over_a_sequence():
+    """KineSequenceTracker (the loop of TrackerKinematic.step: trails -> track queries -> detector -> thresholds / NMS ->
+    births and terminations): replaying KineFrameGraphs gives the same track ids every frame and boxes within 1e-3 px of the
+    eager loop through KinematicDetectorTransformer.forward(samples, targets); tracks are born, carried and terminated."""
+    from kinet_b200.modules import kinematic_transformer as kt
+    from kinet_b200.modules.kinematic_detector import KinematicDetectorTransformer, TokenFeatures
+    from kinet_b200.tracking import KineSequenceTracker
+    dev = _dev()
+    d, nq, n_frames = 72, 12, 5
+    back = [lambda x: ([TokenFeatures(x[0], torch.zeros(x[0].shape[:2], dtype=torch.bool, device=x[0].device))], [x[1]])] * 2
+    transformer = kt.DualKinematicTransformer(d_model=d, nhead=8, num_encoder_layers=1, num_decoder_layers=1,
+                                              dim_feedforward=48, dropout=0.0, return_intermediate_dec=True)
+    det = _by_name(KinematicDetectorTransformer(back, transformer, num_classes=1, num_queries=nq, aux_loss=False,
+                                                dim_tracklets_det=4 * n_frames, dim_tracklets_metadata=n_frames)).to(dev).eval()
+    with torch.no_grad():
+        det.class_embed.weight.mul_(6.0)                      # spread the scores around the thresholds
+        det.bbox_embed.layers[-1].weight.mul_(8.0)            # ... and the boxes over the image (NMS would merge them)
+    g = torch.Generator().manual_seed(21)
+    scene = [torch.randn(1, 20, d, generator=g) for _ in range(4)]
+    frames = []
+    for i in range(24):
+        T = 9 + (7 * i) % 11
+        frames.append(tuple((s[:, :T] + 0.25 * torch.randn(1, T, d, generator=g)).to(dev) for s in scene))
+    kw = dict(img_size=(1080, 1920), n_frames=n_frames, detection_nms_thresh=0.9, track_nms_thresh=0.9)
+    a = KineSequenceTracker(det, use_graphs=True, token_bucket=8, **kw)
+    b = KineSequenceTracker(det, use_graphs=False, **kw)
+    # random weights: put the thresholds where about a third of the object queries fire
+    with torch.no_grad():
+        sc = b._detect_eager(frames[0], None, None)[:, 0]
+    thr = float(torch.quantile(sc, 0.67))
+    for t in (a, b):
+        t.det_thresh, t.trk_thresh = thr, thr - 0.02 * (float(sc.max()) - float(sc.min()))
+    counts = []
+    for f in frames:
+        ra, rb = a.step(f), b.step(f)
+        assert sorted(ra) == sorted(rb)
+        for tid in ra:
+            assert np.abs(ra[tid]["bbox"] - rb[tid]["bbox"]).max() < 1e-3
+            assert abs(ra[tid]["score"] - rb[tid]["score"]) < 1e-5
+        counts.append(len(ra))
+    assert a.next_id == b.next_id and a.next_id > max(counts) > 0          # tracks were started and some ended
+    assert any(len(v) >= 3 for v in a.results.values())                   # some track lived for several frames
+    assert len(a._graphs.recorded_buckets) >= 3
