@@ -509,13 +509,19 @@ def measure_callers(rank, world, dev, frames=120, train_steps=10):
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "tools"))
     import kine_bench
     k = kine_bench.measure(dev, frames=200, seed=rank)
-    ms = reduce_max([k["fused_graphs_ms_per_frame"]], dev, world)[0]
+    kt = kine_bench.measure_tracker(dev, frames=200, seed=rank)
+    ms, ms_tr = reduce_max([kt["tracker_ms_per_frame"], k["fused_graphs_ms_per_frame"]], dev, world)
     out["kine_frames_per_s"] = {
-        "value": world * 1e3 / ms, "ms_per_frame_per_gpu": ms, "graphs_recorded": k["graphs_recorded"],
-        "same_parameters_through_stock_pytorch_modules_ms": {"eager": k["plain_eager_ms"], "one_cuda_graph": k["plain_graph_ms"]},
-        "config": "kinet_b200.modules.kinematic_transformer.DualKinematicTransformer + class / box heads through "
-                  "kinet_b200.frame_graph.KineFrameGraphs: " + k["config"] + ", " + k["dtype"] +
-                  "; token and track-query counts change every frame; one sequence per GPU"}
+        "value": world * 1e3 / ms, "ms_per_frame_per_gpu": ms, "tracks_min_max": kt["tracks_min_max"],
+        "tracks_started": kt["tracks_started"], "graphs_recorded": kt["graphs_recorded"],
+        "transformer_only": {"frames_per_s": world * 1e3 / ms_tr, "ms_per_frame_per_gpu": ms_tr,
+                             "same_parameters_through_stock_pytorch_modules_ms": {"eager": k["plain_eager_ms"],
+                                                                                  "one_cuda_graph": k["plain_graph_ms"]}},
+        "config": "kinet_b200.tracking.KineSequenceTracker (the loop of TrackerKinematic.step: trails -> track queries, "
+                  "detector replay from KineFrameGraphs, one read-back, host thresholds / NMS / births / terminations) over "
+                  "kinet_b200.modules.kinematic_detector.KinematicDetectorTransformer: " + k["config"] + ", " + k["dtype"] +
+                  "; transformer_only: the detector's transformer + heads alone with token and track-query counts that "
+                  "change every frame; one sequence per GPU"}
     return out
 
 

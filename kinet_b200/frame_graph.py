@@ -145,11 +145,11 @@ class KineFrameGraphs:
     A frame brings T detection tokens and K track queries, both changing from frame to frame.  Tokens are padded up to
     a multiple of ``token_bucket`` and switched off with the model's own key-padding ``mask`` (what the reference's
     NestedTensor batching does); track queries are padded up to a multiple of ``track_bucket`` at the FRONT of the
-    query list with rows that nothing reads back -- padded queries still act as keys of the decoder's self-attention,
-    which has no padding mask on this path (transformer.py:393-395 passes tgt_key_padding_mask=None), so exact
-    per-frame parity with an unpadded run needs ``track_bucket=1``; the default buckets trade that for a handful of
-    graphs.  One graph per (padded T, padded K); inputs are copied into static buffers, outputs are views of static
-    buffers valid until the next call.  Inference only."""
+    query list with rows that nothing reads back, flagged in ``bufs["kpad"]`` (1, Kp) -- a ``heads`` function that hands
+    that flag to ``DualKinematicTransformer.forward_masked_queries`` (padded queries masked as keys of the decoder's
+    self-attention) gets exactly the unpadded results for the real queries; one that ignores it lets the padding rows
+    take part as keys.  One graph per (padded T, padded K); inputs are copied into static buffers, outputs are views of
+    static buffers valid until the next call.  Inference only."""
 
     def __init__(self, transformer, heads, token_bucket=32, track_bucket=1, autocast_dtype=torch.bfloat16, warmup=2):
         """transformer: modules.kinematic_transformer.DualKinematicTransformer; heads: see __call__."""
@@ -170,7 +170,7 @@ class KineFrameGraphs:
         """src_* / pos_* (1, T, C) token embeddings; tgt_* (K, 1, C) projected track-query embeddings or None.
         ``heads(transformer, bufs, padded_K)`` is the frame's computation as the caller wants it recorded: it reads the
         static buffers ``bufs`` (src_det, src_meta, pos_det, pos_meta (1, Tp, C); mask (1, Tp) bool; tgt_det, tgt_meta
-        (Kp, 1, C)), calls the transformer and returns whatever should come back (tools/kine_bench.py::make_heads: class
+        (Kp, 1, C); kpad (1, Kp) bool = padding track-query rows), calls the transformer and returns whatever should come back (tools/kine_bench.py::make_heads: class
         logits, boxes and the detection embeddings of the last layer).  Returns (that result -- static buffers, valid
         until the next call --, number of padding track-query rows at the FRONT of the query dimension)."""
         T, C = src_det.shape[1], src_det.shape[2]
@@ -183,6 +183,7 @@ class KineFrameGraphs:
             bufs = dict(src_det=torch.zeros(1, Tp, C, device=dev), src_meta=torch.zeros(1, Tp, C, device=dev),
                         pos_det=torch.zeros(1, Tp, C, device=dev), pos_meta=torch.zeros(1, Tp, C, device=dev),
                         mask=torch.ones(1, Tp, dtype=torch.bool, device=dev),
+                        kpad=torch.zeros(1, Kp, dtype=torch.bool, device=dev),
                         tgt_det=torch.zeros(Kp, 1, C, device=dev), tgt_meta=torch.zeros(Kp, 1, C, device=dev))
 
             def fn():
@@ -208,9 +209,12 @@ class KineFrameGraphs:
         if K:
             bufs["tgt_det"][Kp - K:].copy_(tgt_det, non_blocking=True)
             bufs["tgt_meta"][Kp - K:].copy_(tgt_meta, non_blocking=True)
+        if Kp:
+            bufs["kpad"].fill_(False)
         if Kp > K:
             bufs["tgt_det"][:Kp - K].zero_()
             bufs["tgt_meta"][:Kp - K].zero_()
+            bufs["kpad"][:, :Kp - K] = True
         graph.replay()
         self.replays += 1
         return out, Kp - K

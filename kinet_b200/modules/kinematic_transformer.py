@@ -294,12 +294,15 @@ class KinematicTransformer(nn.Module):
             if p.dim() > 1:
                 nn.init.xavier_uniform_(p)
 
-    def _forward_bf(self, src, mask, query_embed, tgt, pos_src):
-        """src / pos_src (BS, T, C); query_embed / tgt (BS, Lq, C).  Batch-first (hs, hs_without_norm, memory)."""
+    def _forward_bf(self, src, mask, query_embed, tgt, pos_src, query_padding_mask=None):
+        """src / pos_src (BS, T, C); query_embed / tgt (BS, Lq, C).  Batch-first (hs, hs_without_norm, memory).
+        query_padding_mask (BS, Lq) bool: queries that are padding (a caller that pads the query list to a bucket, e.g.
+        KineFrameGraphs) -- masked as KEYS of the decoder's self-attention, so the real queries see exactly what they
+        would see unpadded (the reference passes tgt_key_padding_mask=None: it never pads queries)."""
         if tgt is None:
             tgt = torch.zeros_like(query_embed)
         memory = self.encoder._forward_bf(src, mask, pos_src)
-        hs, raw = self.decoder._forward_bf(tgt, memory, None, mask, pos_src, query_embed)
+        hs, raw = self.decoder._forward_bf(tgt, memory, query_padding_mask, mask, pos_src, query_embed)
         return hs, raw, memory
 
     def forward(self, src, mask, query_embed, tgt=None, pos_src=None):
@@ -352,12 +355,18 @@ class DualKinematicTransformer(nn.Module):
         """Reference layouts (:170-185): src_* / pos_* (BS, T, C), mask (BS, T) bool, query_embed_* / tgt_*
         (Lq, BS, C).  Returns (hs_det, hs_metadata, hs_without_norm_det) as (layers, BS, Lq, C) and memory_det
         (BS, T, C) -- the reference's ``transpose(1, 2)`` / ``permute(1, 0, 2)`` of its sequence-first tensors."""
+        return self.forward_masked_queries(src_boxes, src_metadata, mask, query_embed_bbox, query_embed_metadata,
+                                           tgt_bboxes, tgt_metadata, pos_boxes, pos_metadata, None)
+
+    def forward_masked_queries(self, src_boxes, src_metadata, mask, query_embed_bbox, query_embed_metadata, tgt_bboxes,
+                               tgt_metadata, pos_boxes=None, pos_metadata=None, query_padding_mask=None):
+        """forward() with a (BS, Lq) bool mask of PADDING queries (see KinematicTransformer._forward_bf)."""
         c = lambda t: None if t is None else t.contiguous()
         (hs_det, raw_det, memory_det), (hs_meta, _, _) = _two_branches(
             lambda: self.transformer_det._forward_bf(c(src_boxes), mask, _bf(query_embed_bbox), _bf(tgt_bboxes),
-                                                     c(pos_boxes)),
+                                                     c(pos_boxes), query_padding_mask),
             lambda: self.transformer_metadata._forward_bf(c(src_metadata), mask, _bf(query_embed_metadata),
-                                                          _bf(tgt_metadata), c(pos_metadata)),
+                                                          _bf(tgt_metadata), c(pos_metadata), query_padding_mask),
             src_boxes.device)
         # the concatenation dimension of the reference (3: channels of a (layers, Lq, BS, C) stack) stays the last one
         self.detection_branch.dim_concat = self.metadata_branch.dim_concat = hs_det.dim() - 1

@@ -391,13 +391,13 @@ class KineSequenceTracker:
     ``detector``: kinematic_detector.KinematicDetectorTransformer whose backbones accept ``(tokens, pos)`` pairs (e.g. the
     pass-through in tools/kine_bench.py; the reference's Kinet_Backbone + position encoding are the caller's).  A frame is
     ``(src_det, src_meta, pos_det, pos_meta)``, each (1, T, C).  ``use_graphs``: replay kinet_b200.frame_graph.KineFrameGraphs
-    (tokens padded to ``token_bucket`` and masked; one graph per (padded T, K)); otherwise the detector runs eagerly through
+    (tokens padded to ``token_bucket``, track queries to ``track_bucket``, both masked; one graph per (padded T, padded K)); otherwise the detector runs eagerly through
     its own forward (``targets`` carrying the trails).  One device -> host read per frame; track state lives on the host
     (a few dozen boxes) and goes to the device through pinned staging."""
 
     def __init__(self, detector, img_size, n_frames=5, detection_obj_score_thresh=0.4, track_obj_score_thresh=0.4,
                  detection_nms_thresh=0.9, track_nms_thresh=0.9, steps_termination=1, n_classes=1, use_graphs=False,
-                 token_bucket=32, autocast_dtype=None):
+                 token_bucket=32, track_bucket=8, autocast_dtype=None):
         self.detector = detector
         self.img_h, self.img_w = float(img_size[0]), float(img_size[1])
         self.n_frames = int(n_frames)
@@ -405,27 +405,31 @@ class KineSequenceTracker:
         self.det_nms, self.trk_nms = detection_nms_thresh, track_nms_thresh
         self.steps_termination, self.n_classes = steps_termination, n_classes
         self.use_graphs, self.token_bucket, self.autocast_dtype = use_graphs, token_bucket, autocast_dtype
+        self.track_bucket = track_bucket
         self._graphs = None
         self.reset()
 
     def reset(self):
-        self.tracks = []          # dicts: id, box (xyxy px), score, trail (list of cxcywh rel), scores (list), misses
+        n = self.n_frames
+        # host-side track state, one row per live track (a few dozen): struct of arrays, so a frame costs O(1) numpy calls
+        self.ids = np.empty(0, np.int64)
+        self.boxes = np.empty((0, 4), np.float64)            # xyxy pixels
+        self.scores = np.empty(0, np.float64)
+        self.misses = np.empty(0, np.int64)
+        self.trail = np.empty((0, n, 4), np.float32)         # last n relative boxes (cx, cy, w, h), oldest first
+        self.trail_sc = np.empty((0, n), np.float32)         # ... and scores
         self.next_id = 0
         self.frame_index = 0
         self.results = {}
 
+    @property
+    def tracks(self):
+        return self.ids.tolist()
+
     # ---- trails -> track-query inputs (tracker.py:652-671, :1027-1046) ----
     def _trails(self):
-        n, K = self.n_frames, len(self.tracks)
-        det = np.empty((K, n * 4), np.float32)
-        meta = np.empty((K, n), np.float32)
-        for i, t in enumerate(self.tracks):
-            tr, sc = t["trail"][-n:], t["scores"][-n:]
-            tr = [tr[0]] * (n - len(tr)) + tr
-            sc = [sc[0]] * (n - len(sc)) + sc
-            det[i] = np.concatenate(tr)
-            meta[i] = sc
-        return det, meta
+        K = len(self.ids)
+        return self.trail.reshape(K, -1), self.trail_sc
 
     def _to_device(self, dev, det, meta):
         """(K, n*4) and (K, n) host arrays -> device tensors through pinned staging (see SequenceTracker._to_device_indices)."""
@@ -473,24 +477,26 @@ class KineSequenceTracker:
                 pad = lambda e: torch.nn.functional.pad(e.weight[:, None], (0, 0, 0, 0, Kp, 0))
                 td = torch.nn.functional.pad(bufs["tgt_det"], (0, 0, 0, 0, 0, nq)) if Kp else None
                 tm = torch.nn.functional.pad(bufs["tgt_meta"], (0, 0, 0, 0, 0, nq)) if Kp else None
-                hs_det, hs_meta, _, _ = transformer(bufs["src_det"], bufs["src_meta"], bufs["mask"], pad(det.query_embed_det),
-                                                    pad(det.query_embed_metadata), td, tm, bufs["pos_det"], bufs["pos_meta"])
+                qpad = torch.nn.functional.pad(bufs["kpad"], (0, nq)) if Kp else None      # object queries are never padding
+                hs_det, hs_meta, _, _ = transformer.forward_masked_queries(
+                    bufs["src_det"], bufs["src_meta"], bufs["mask"], pad(det.query_embed_det), pad(det.query_embed_metadata),
+                    td, tm, bufs["pos_det"], bufs["pos_meta"], qpad)
                 return self._pack(linear(hs_meta[-1], det.class_embed), det.bbox_embed(hs_det[-1]).sigmoid())
-            self._graphs = KineFrameGraphs(det.transformer, heads, token_bucket=self.token_bucket, track_bucket=1,
-                                           autocast_dtype=self.autocast_dtype)
+            self._graphs = KineFrameGraphs(det.transformer, heads, token_bucket=self.token_bucket,
+                                           track_bucket=self.track_bucket, autocast_dtype=self.autocast_dtype)
         tgt_d = tgt_m = None
         if det_t is not None:
             with torch.autocast("cuda", dtype=self.autocast_dtype, enabled=self.autocast_dtype is not None):
                 tgt_d = det.input_proj_tracklets_det(det_t)[:, None].float()
                 tgt_m = det.input_proj_tracklets_metadata(meta_t)[:, None].float()
-        packed, _ = self._graphs(frame[0], frame[1], frame[2], frame[3], tgt_d, tgt_m)
-        return packed
+        packed, pad = self._graphs(frame[0], frame[1], frame[2], frame[3], tgt_d, tgt_m)
+        return packed[pad:]                       # the padding track-query rows sit at the front
 
     @torch.no_grad()
     def step(self, frame):
         """frame = (src_det, src_meta, pos_det, pos_meta), each (1, T, C) on the device -> {track_id: {"bbox", "score"}}."""
         dev = frame[0].device
-        K = len(self.tracks)
+        K = len(self.ids)
         det_t = meta_t = None
         if K:
             det_t, meta_t = self._to_device(dev, *self._trails())
@@ -498,41 +504,45 @@ class KineSequenceTracker:
         return self._update(packed.cpu().numpy(), K)                      # ONE device -> host read per frame
 
     def _update(self, packed, K):
-        sc, lb, rel = packed[:, 0], packed[:, 1].astype(np.int64), packed[:, 2:6].astype(np.float64)
+        n = self.n_frames
+        sc, lb, rel = packed[:, 0].astype(np.float64), packed[:, 1].astype(np.int64), packed[:, 2:6].astype(np.float64)
         rel = np.clip(rel, 0.0, 1.0)                                       # relative boxes are clamped (:688-690)
         wh = np.array([self.img_w, self.img_h, self.img_w, self.img_h])
         px = np.stack([rel[:, 0] - rel[:, 2] / 2, rel[:, 1] - rel[:, 3] / 2, rel[:, 0] + rel[:, 2] / 2, rel[:, 1] + rel[:, 3] / 2], -1) * wh
         px = np.minimum(np.clip(px, 0, None), wh)                          # clip_boxes_to_image
-        live = []
-        for j, t in enumerate(self.tracks):                                # manage_active_tracks (:937-955)
-            if sc[j] > self.trk_thresh and lb[j] == 0:
-                t["box"], t["score"], t["misses"] = px[j], float(sc[j]), 0
-                t["trail"].append(rel[j].astype(np.float32))
-                t["scores"].append(np.float32(sc[j]))
-                live.append(t)
-            else:
-                t["misses"] += 1
-                if t["misses"] < self.steps_termination:
-                    live.append(t)
-        if self.trk_nms and live:
-            k = _nms(np.stack([t["box"] for t in live]), np.asarray([t["score"] for t in live]), self.trk_nms)
-            live = [live[i] for i in k]
-        new = []
-        obj = slice(K, None)
-        for i in K + np.flatnonzero((sc[obj] > self.det_thresh) & (lb[obj] < self.n_classes)):     # generate_new_tracks
-            new.append({"id": -1, "box": px[i], "score": float(sc[i]), "misses": 0,
-                        "trail": [rel[i].astype(np.float32)] * self.n_frames, "scores": [np.float32(sc[i])] * self.n_frames})
-        if self.det_nms and (live or new):                                 # existing tracks always win (:820-838)
-            boxes = np.stack([t["box"] for t in live + new])
-            scores = np.asarray([np.inf] * len(live) + [t["score"] for t in new])
-            k = set(_nms(boxes, scores, self.det_nms).tolist())
-            new = [t for j, t in enumerate(new) if j + len(live) in k]
-            live = [t for j, t in enumerate(live) if j in k]
-        for t in new:
-            t["id"] = self.next_id
-            self.next_id += 1
-        self.tracks = live + new
-        frame = {t["id"]: {"bbox": np.array(t["box"], dtype=np.float64), "score": t["score"]} for t in self.tracks}
+        ids, boxes, scores, misses, trail, trail_sc = self.ids, self.boxes, self.scores, self.misses, self.trail, self.trail_sc
+        if K:                                                              # manage_active_tracks (:937-955)
+            keep = (sc[:K] > self.trk_thresh) & (lb[:K] == 0)
+            boxes, scores, misses, trail, trail_sc = boxes.copy(), scores.copy(), misses.copy(), trail.copy(), trail_sc.copy()
+            boxes[keep], scores[keep], misses[keep] = px[:K][keep], sc[:K][keep], 0
+            # a surviving track's trail grows by the new box / score (young tracks repeat their oldest entry: a trail that
+            # starts as n copies of the first detection, shifted left once per frame, is exactly TrackKinematic.get_trail)
+            trail[keep] = np.concatenate([trail[keep][:, 1:], rel[:K][keep][:, None].astype(np.float32)], 1)
+            trail_sc[keep] = np.concatenate([trail_sc[keep][:, 1:], sc[:K][keep][:, None].astype(np.float32)], 1)
+            misses[~keep] += 1
+            alive = keep | (misses < self.steps_termination)
+            ids, boxes, scores, misses, trail, trail_sc = (a[alive] for a in (ids, boxes, scores, misses, trail, trail_sc))
+            if self.trk_nms and len(ids):
+                k = _nms(boxes, scores, self.trk_nms)
+                ids, boxes, scores, misses, trail, trail_sc = (a[k] for a in (ids, boxes, scores, misses, trail, trail_sc))
+        # generate_new_tracks (:895-930): the detection repeated n times is the new track's trail
+        idx = K + np.flatnonzero((sc[K:] > self.det_thresh) & (lb[K:] < self.n_classes))
+        nb, ns = px[idx], sc[idx]
+        nlive = len(ids)
+        if self.det_nms and (nlive or len(idx)):                           # existing tracks always win (:820-838)
+            k = _nms(np.concatenate([boxes, nb]), np.concatenate([np.full(nlive, np.inf), ns]), self.det_nms)
+            kl, kn = k[k < nlive], k[k >= nlive] - nlive
+            ids, boxes, scores, misses, trail, trail_sc = (a[kl] for a in (ids, boxes, scores, misses, trail, trail_sc))
+            idx, nb, ns = idx[kn], nb[kn], ns[kn]
+        m = len(idx)
+        self.ids = np.concatenate([ids, np.arange(self.next_id, self.next_id + m, dtype=np.int64)])
+        self.next_id += m
+        self.boxes = np.concatenate([boxes, nb])
+        self.scores = np.concatenate([scores, ns])
+        self.misses = np.concatenate([misses, np.zeros(m, np.int64)])
+        self.trail = np.concatenate([trail, np.repeat(rel[idx][:, None].astype(np.float32), n, 1)])
+        self.trail_sc = np.concatenate([trail_sc, np.repeat(ns[:, None].astype(np.float32), n, 1)])
+        frame = {int(t): {"bbox": self.boxes[i].copy(), "score": float(self.scores[i])} for i, t in enumerate(self.ids)}
         for tid, r in frame.items():
             self.results.setdefault(tid, {})[self.frame_index] = r
         self.frame_index += 1

@@ -442,16 +442,18 @@ def test_kine_frame_graphs_match_direct_calls_with_varying_sizes():
         qd, qm = F.pad(qe_d, (0, 0, 0, 0, Kp, 0)), F.pad(qe_m, (0, 0, 0, 0, Kp, 0))
         td = F.pad(bufs["tgt_det"], (0, 0, 0, 0, 0, nq)) if Kp else None
         tm = F.pad(bufs["tgt_meta"], (0, 0, 0, 0, 0, nq)) if Kp else None
-        hs_det, hs_meta, _, _ = transformer(bufs["src_det"], bufs["src_meta"], bufs["mask"], qd, qm, td, tm,
-                                            bufs["pos_det"], bufs["pos_meta"])
+        qpad = F.pad(bufs["kpad"], (0, nq)) if Kp else None
+        hs_det, hs_meta, _, _ = transformer.forward_masked_queries(bufs["src_det"], bufs["src_meta"], bufs["mask"], qd, qm,
+                                                                   td, tm, bufs["pos_det"], bufs["pos_meta"], qpad)
         return hs_det[-1], hs_meta[-1]
-    fg = KineFrameGraphs(model, heads, token_bucket=8, track_bucket=1, autocast_dtype=None)
-    sizes = [(5, 0), (11, 3), (8, 3), (13, 2), (11, 3), (6, 0)]
+    fg = KineFrameGraphs(model, heads, token_bucket=8, track_bucket=4, autocast_dtype=None)
+    sizes = [(5, 0), (11, 3), (8, 3), (13, 2), (11, 4), (6, 0), (9, 5)]
     for T, K in sizes:
         toks = [torch.randn(1, T, d, generator=g).to(dev) for _ in range(4)]
         tg = [torch.randn(K, 1, d, generator=g).to(dev) for _ in range(2)] if K else [None, None]
         (hd, hm), pad = fg(*toks, *tg)
-        assert pad == 0
+        assert pad == -K % 4
+        hd, hm = hd[:, pad:], hm[:, pad:]               # padding track-query rows sit at the front
         with torch.no_grad():
             qd, qm = F.pad(qe_d, (0, 0, 0, 0, K, 0)), F.pad(qe_m, (0, 0, 0, 0, K, 0))
             td = F.pad(tg[0], (0, 0, 0, 0, 0, nq)) if K else None
@@ -460,7 +462,7 @@ def test_kine_frame_graphs_match_direct_calls_with_varying_sizes():
                                          toks[2], toks[3])
         assert hd.shape == want_d[-1].shape
         assert _rel(hd, want_d[-1]) < 2e-5 and _rel(hm, want_m[-1]) < 2e-5, (T, K)
-    assert fg.recorded_buckets == [(8, 0), (8, 3), (16, 2), (16, 3)]
+    assert fg.recorded_buckets == [(8, 0), (8, 4), (16, 4), (16, 8)]
     assert fg.replays == len(sizes)
 
 
@@ -489,7 +491,7 @@ def test_kine_sequence_tracker_graphs_match_eager_detector_over_a_sequence():
         T = 9 + (7 * i) % 11
         frames.append(tuple((s[:, :T] + 0.25 * torch.randn(1, T, d, generator=g)).to(dev) for s in scene))
     kw = dict(img_size=(1080, 1920), n_frames=n_frames, detection_nms_thresh=0.9, track_nms_thresh=0.9)
-    a = KineSequenceTracker(det, use_graphs=True, token_bucket=8, **kw)
+    a = KineSequenceTracker(det, use_graphs=True, token_bucket=8, track_bucket=4, **kw)
     b = KineSequenceTracker(det, use_graphs=False, **kw)
     # random weights: put the thresholds where about a third of the object queries fire
     with torch.no_grad():

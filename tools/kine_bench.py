@@ -43,8 +43,9 @@ def make_heads(mods):
         nq = mods["query_embed_det"].weight.shape[0]
         td = F.pad(bufs["tgt_det"], (0, 0, 0, 0, 0, nq)) if Kp else None
         tm = F.pad(bufs["tgt_meta"], (0, 0, 0, 0, 0, nq)) if Kp else None
-        hs_det, hs_meta, _, _ = transformer(bufs["src_det"], bufs["src_meta"], bufs["mask"], qd, qm, td, tm,
-                                            bufs["pos_det"], bufs["pos_meta"])
+        qpad = F.pad(bufs["kpad"], (0, nq)) if Kp else None
+        hs_det, hs_meta, _, _ = transformer.forward_masked_queries(bufs["src_det"], bufs["src_meta"], bufs["mask"], qd, qm,
+                                                                   td, tm, bufs["pos_det"], bufs["pos_meta"], qpad)
         return linear(hs_meta[-1], mods["class_embed"]).float(), mods["bbox_embed"](hs_det[-1]).float().sigmoid(), hs_det[-1]
     return heads
 
@@ -161,6 +162,49 @@ def measure(dev, frames=200, fp32=False, nq=150, d=288, seed=0):
     return res
 
 
+def measure_tracker(dev, frames=200, fp32=False, nq=150, d=288, n_frames=5, seed=0):
+    """Frames/s of kinet_b200.tracking.KineSequenceTracker (the loop of TrackerKinematic.step) over the kine detector at the
+    kinet configuration: per frame T detection tokens (100-150), the live tracks' trails as track queries, one detector
+    replay from KineFrameGraphs, ONE read-back, host thresholds / NMS / births / terminations."""
+    from kinet_b200.modules.kinematic_detector import KinematicDetectorTransformer, TokenFeatures
+    from kinet_b200.modules.kinematic_transformer import DualKinematicTransformer
+    from kinet_b200.tracking import KineSequenceTracker
+    torch.manual_seed(seed)
+    back = [lambda x: ([TokenFeatures(x[0], torch.zeros(x[0].shape[:2], dtype=torch.bool, device=x[0].device))], [x[1]])] * 2
+    tr = DualKinematicTransformer(d_model=d, nhead=8, num_encoder_layers=1, num_decoder_layers=1, dim_feedforward=2048,
+                                  dropout=0.1, return_intermediate_dec=True)
+    det = KinematicDetectorTransformer(back, tr, num_classes=1, num_queries=nq, dim_tracklets_det=4 * n_frames,
+                                       dim_tracklets_metadata=n_frames).to(dev).eval()
+    with torch.no_grad():                       # random weights: spread scores and boxes so that tracks come and go
+        det.class_embed.weight.mul_(4.0)
+        det.bbox_embed.layers[-1].weight.mul_(8.0)
+    g = torch.Generator(device=dev).manual_seed(seed + 1)
+    scene = [torch.randn(1, 160, d, device=dev, generator=g) for _ in range(4)]
+    feeds = []
+    for i in range(16):
+        T = 100 + (37 * i) % 51
+        feeds.append(tuple(s_[:, :T] + 0.3 * torch.randn(1, T, d, device=dev, generator=g) for s_ in scene))
+    trk = KineSequenceTracker(det, img_size=(1080, 1920), n_frames=n_frames, use_graphs=True, token_bucket=32,
+                              autocast_dtype=None if fp32 else torch.bfloat16)
+    with torch.no_grad():
+        sc = trk._detect_eager(feeds[0], None, None)[:, 0].float()
+    trk.det_thresh = float(torch.quantile(sc, 0.85))            # ~ 20 of the 150 object queries fire on the first frame
+    trk.trk_thresh = trk.det_thresh - 0.05 * float(sc.max() - sc.min())
+    for i in range(48):                                         # warm-up: records the graphs of the sizes that occur
+        trk.step(feeds[i & 15])
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    counts = []
+    a.record()
+    for i in range(frames):
+        counts.append(len(trk.step(feeds[i & 15])))
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / frames
+    return dict(tracker_ms_per_frame=ms, tracker_frames_per_s=1e3 / ms, tracks_min_max=[min(counts), max(counts)],
+                tracks_started=trk.next_id, graphs_recorded=len(trk._graphs.recorded_buckets))
+
+
 def profile(dev, fp32):
     """Kernel breakdown (torch profiler, eager) of one fused and one plain frame at T = 150, K = 48."""
     from torch.profiler import ProfilerActivity, profile as prof
@@ -194,4 +238,6 @@ if __name__ == "__main__":
     if a.profile:
         profile(torch.device("cuda:0"), a.fp32)
         sys.exit(0)
-    print(json.dumps(measure(torch.device("cuda:0"), a.frames, a.fp32)))
+    res = measure(torch.device("cuda:0"), a.frames, a.fp32)
+    res["tracker"] = measure_tracker(torch.device("cuda:0"), a.frames, a.fp32)
+    print(json.dumps(res))
