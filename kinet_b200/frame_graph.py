@@ -166,6 +166,76 @@ class KineFrameGraphs:
     def recorded_buckets(self):
         return sorted(self._graphs)
 
+    def _record(self, key, bufs, pre=None):
+        Kp = key[1]
+
+        def fn():
+            with torch.no_grad(), torch.autocast("cuda", dtype=self.autocast_dtype,
+                                                 enabled=self.autocast_dtype is not None):
+                if pre is not None:
+                    pre()
+                return self.heads(self.transformer, bufs, Kp)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(self.warmup):
+                fn()
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            out = fn()
+        self._graphs[key] = (graph, bufs, out)
+
+    def call_with_trails(self, src_det, src_meta, pos_det, pos_meta, trail_det, trail_meta):
+        """The tracking loop's entry: the K track queries arrive as HOST arrays ``trail_det`` (K, Xd) / ``trail_meta``
+        (K, Xm) (numpy float32; K may be 0) and everything that depends on the frame's counts happens inside the graph.
+        The token count, the number of padding rows and the (front-padded) trails travel in ONE pinned block and one
+        host -> device copy straight into the bucket's static buffer; the graph derives ``mask`` / ``kpad`` from the two
+        counts and ``heads`` finds the raw trails in ``bufs["trail_det"]`` (Kp, Xd) / ``bufs["trail_meta"]`` (Kp, Xm) --
+        projecting them to track-query embeddings is part of what it records.  Per frame the host enqueues the four
+        token copies, that block and the replay: 6 launches instead of ~25.  Same return value as __call__."""
+        T, C = src_det.shape[1], src_det.shape[2]
+        K, Xd, Xm = trail_det.shape[0], trail_det.shape[1], trail_meta.shape[1]
+        Tp = -(-T // self.token_bucket) * self.token_bucket
+        Kp = -(-K // self.track_bucket) * self.track_bucket
+        key = (Tp, Kp, Xd, Xm)
+        dev = src_det.device
+        n_block = 2 + Kp * (Xd + Xm)
+        if key not in self._graphs:
+            block = torch.zeros(n_block, device=dev)
+            bufs = dict(src_det=torch.zeros(1, Tp, C, device=dev), src_meta=torch.zeros(1, Tp, C, device=dev),
+                        pos_det=torch.zeros(1, Tp, C, device=dev), pos_meta=torch.zeros(1, Tp, C, device=dev),
+                        block=block, trail_det=block[2:2 + Kp * Xd].view(Kp, Xd),
+                        trail_meta=block[2 + Kp * Xd:].view(Kp, Xm))
+            # (kept in bufs: the recorded graph reads them on every replay, so they must outlive this call)
+            tok = bufs["token_index"] = torch.arange(Tp, device=dev, dtype=torch.float32).view(1, Tp)
+            trk = bufs["track_index"] = torch.arange(Kp, device=dev, dtype=torch.float32).view(1, Kp)
+
+            def pre():
+                bufs["mask"] = tok >= block[0]           # tokens T .. Tp-1 are padding
+                bufs["kpad"] = trk < block[1]            # the first Kp-K track-query rows are padding
+            self._record(key, bufs, pre)
+        graph, bufs, out = self._graphs[key]
+        st = getattr(self, "_stage", None)
+        if st is None or st[0].shape[0] < n_block:
+            st = self._stage = [torch.zeros(max(4096, 2 * n_block)).pin_memory() for _ in range(2)] + [0]
+        st[2] ^= 1                                      # two blocks in turn: the previous frame's copy may still be in flight
+        host = st[st[2]]
+        flat = host.numpy()
+        flat[0], flat[1] = T, Kp - K
+        if Kp:
+            o = 2
+            for a, X in ((trail_det, Xd), (trail_meta, Xm)):
+                flat[o:o + (Kp - K) * X] = 0.0
+                flat[o + (Kp - K) * X:o + Kp * X] = a.ravel()
+                o += Kp * X
+        bufs["block"].copy_(host[:n_block], non_blocking=True)
+        for name, t in (("src_det", src_det), ("src_meta", src_meta), ("pos_det", pos_det), ("pos_meta", pos_meta)):
+            bufs[name][:, :T].copy_(t, non_blocking=True)
+        graph.replay()
+        self.replays += 1
+        return out, Kp - K
+
     def __call__(self, src_det, src_meta, pos_det, pos_meta, tgt_det=None, tgt_meta=None):
         """src_* / pos_* (1, T, C) token embeddings; tgt_* (K, 1, C) projected track-query embeddings or None.
         ``heads(transformer, bufs, padded_K)`` is the frame's computation as the caller wants it recorded: it reads the
@@ -186,20 +256,7 @@ class KineFrameGraphs:
                         kpad=torch.zeros(1, Kp, dtype=torch.bool, device=dev),
                         tgt_det=torch.zeros(Kp, 1, C, device=dev), tgt_meta=torch.zeros(Kp, 1, C, device=dev))
 
-            def fn():
-                with torch.no_grad(), torch.autocast("cuda", dtype=self.autocast_dtype,
-                                                     enabled=self.autocast_dtype is not None):
-                    return self.heads(self.transformer, bufs, Kp)
-            side = torch.cuda.Stream()
-            side.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.stream(side):
-                for _ in range(self.warmup):
-                    fn()
-            torch.cuda.current_stream().wait_stream(side)
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
-                out = fn()
-            self._graphs[key] = (graph, bufs, out)
+            self._record(key, bufs)
         graph, bufs, out = self._graphs[key]
         for name, t in (("src_det", src_det), ("src_meta", src_meta), ("pos_det", pos_det), ("pos_meta", pos_meta)):
             bufs[name][:, :T].copy_(t, non_blocking=True)

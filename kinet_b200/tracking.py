@@ -24,6 +24,8 @@ enter as the multi-scale feature maps the backbone + input projections would pro
 """
 import math
 
+from collections.abc import Mapping
+
 import numpy as np
 import torch
 from torch import nn
@@ -77,13 +79,16 @@ def _nms(boxes, scores, thresh):
     n = len(boxes)
     if n <= 1:
         return np.arange(n, dtype=np.int64)
-    x1, y1, x2, y2 = boxes[:, 0], boxes[:, 1], boxes[:, 2], boxes[:, 3]
-    area = np.clip(x2 - x1, 0, None) * np.clip(y2 - y1, 0, None)
-    iw = np.clip(np.minimum(x2[:, None], x2[None]) - np.maximum(x1[:, None], x1[None]), 0, None)
-    ih = np.clip(np.minimum(y2[:, None], y2[None]) - np.maximum(y1[:, None], y1[None]), 0, None)
-    inter = iw * ih
-    over = inter / np.maximum(area[:, None] + area[None] - inter, 1e-12) > thresh
-    np.fill_diagonal(over, False)
+    x1, y1, x2, y2 = boxes.T
+    area = np.maximum(x2 - x1, 0) * np.maximum(y2 - y1, 0)
+    iw = np.minimum(x2[:, None], x2) - np.maximum(x1[:, None], x1)
+    ih = np.minimum(y2[:, None], y2) - np.maximum(y1[:, None], y1)
+    inter = np.maximum(iw, 0, out=iw)
+    inter *= np.maximum(ih, 0, out=ih)
+    union = area[:, None] + area
+    union -= inter
+    over = inter > thresh * np.maximum(union, 1e-12, out=union)           # IoU > thresh without the division
+    over.flat[::n + 1] = False
     if not over.any():
         return np.arange(n, dtype=np.int64)
     order = np.argsort(-scores, kind="stable")
@@ -369,6 +374,33 @@ def synthetic_sequence(levels, d_model, n_frames, device, seed=0, drift=0.05, dt
 # =====================================================================================================================
 # The literal KineT tracker: kinematic detector over detection tokens
 # =====================================================================================================================
+class FrameTracks(Mapping):
+    """One frame's tracks as the read-only mapping {track_id: {"bbox": xyxy pixels, "score"}} over three parallel
+    arrays (``ids``, ``boxes``, ``scores``); the dicts are made on first access, so a loop that only steps pays nothing."""
+    __slots__ = ("ids", "boxes", "scores", "_d")
+
+    def __init__(self, ids, boxes, scores):
+        self.ids, self.boxes, self.scores, self._d = ids, boxes, scores, None
+
+    def _dict(self):
+        if self._d is None:
+            self._d = {int(t): {"bbox": self.boxes[i].copy(), "score": float(self.scores[i])}
+                       for i, t in enumerate(self.ids)}
+        return self._d
+
+    def __getitem__(self, tid):
+        return self._dict()[tid]
+
+    def __iter__(self):
+        return iter(self._dict())
+
+    def __len__(self):
+        return len(self.ids)
+
+    def __repr__(self):
+        return repr(self._dict())
+
+
 class KineSequenceTracker:
     """Tracks one sequence frame by frame with the `kine` model -- the loop of the reference's ``TrackerKinematic.step``
     (src/trackformer/models/tracker.py:626-880) around ``kinet_b200.modules.kinematic_detector``:
@@ -420,16 +452,26 @@ class KineSequenceTracker:
         self.trail_sc = np.empty((0, n), np.float32)         # ... and scores
         self.next_id = 0
         self.frame_index = 0
-        self.results = {}
+        self._frames = []
 
     @property
     def tracks(self):
         return self.ids.tolist()
 
+    @property
+    def results(self):
+        """{track_id: {frame_index: {"bbox", "score"}}} (the reference's ``get_results``, tracker.py:568-573), built
+        from the per-frame arrays when asked for: the loop itself stores three array references per frame."""
+        res = {}
+        for f, frame in enumerate(self._frames):
+            for tid, r in frame.items():
+                res.setdefault(tid, {})[f] = r
+        return res
+
     # ---- trails -> track-query inputs (tracker.py:652-671, :1027-1046) ----
     def _trails(self):
         K = len(self.ids)
-        return self.trail.reshape(K, -1), self.trail_sc
+        return self.trail.reshape(K, 4 * self.n_frames), self.trail_sc
 
     def _to_device(self, dev, det, meta):
         """(K, n*4) and (K, n) host arrays -> device tensors through pinned staging (see SequenceTracker._to_device_indices)."""
@@ -466,7 +508,9 @@ class KineSequenceTracker:
             out = self.detector(s, targets)[0]
         return self._pack(out["pred_logits"], out["pred_boxes"])
 
-    def _detect_graph(self, frame, det_t, meta_t):
+    def _detect_graph(self, frame, trail_det, trail_meta):
+        """trail_det (K, n*4) / trail_meta (K, n) HOST arrays: KineFrameGraphs.call_with_trails moves them (and the
+        frame's counts) in one pinned block; the trail projections are part of the recorded graph."""
         from .frame_graph import KineFrameGraphs
         from .functions.layer_ops import linear
         det = self.detector
@@ -475,32 +519,35 @@ class KineSequenceTracker:
 
             def heads(transformer, bufs, Kp):
                 pad = lambda e: torch.nn.functional.pad(e.weight[:, None], (0, 0, 0, 0, Kp, 0))
-                td = torch.nn.functional.pad(bufs["tgt_det"], (0, 0, 0, 0, 0, nq)) if Kp else None
-                tm = torch.nn.functional.pad(bufs["tgt_meta"], (0, 0, 0, 0, 0, nq)) if Kp else None
-                qpad = torch.nn.functional.pad(bufs["kpad"], (0, nq)) if Kp else None      # object queries are never padding
+                td = tm = qpad = None
+                if Kp:
+                    td = det.input_proj_tracklets_det(bufs["trail_det"])[:, None].float()
+                    tm = det.input_proj_tracklets_metadata(bufs["trail_meta"])[:, None].float()
+                    td = torch.nn.functional.pad(td, (0, 0, 0, 0, 0, nq))
+                    tm = torch.nn.functional.pad(tm, (0, 0, 0, 0, 0, nq))
+                    qpad = torch.nn.functional.pad(bufs["kpad"], (0, nq))                 # object queries are never padding
                 hs_det, hs_meta, _, _ = transformer.forward_masked_queries(
                     bufs["src_det"], bufs["src_meta"], bufs["mask"], pad(det.query_embed_det), pad(det.query_embed_metadata),
                     td, tm, bufs["pos_det"], bufs["pos_meta"], qpad)
                 return self._pack(linear(hs_meta[-1], det.class_embed), det.bbox_embed(hs_det[-1]).sigmoid())
             self._graphs = KineFrameGraphs(det.transformer, heads, token_bucket=self.token_bucket,
                                            track_bucket=self.track_bucket, autocast_dtype=self.autocast_dtype)
-        tgt_d = tgt_m = None
-        if det_t is not None:
-            with torch.autocast("cuda", dtype=self.autocast_dtype, enabled=self.autocast_dtype is not None):
-                tgt_d = det.input_proj_tracklets_det(det_t)[:, None].float()
-                tgt_m = det.input_proj_tracklets_metadata(meta_t)[:, None].float()
-        packed, pad = self._graphs(frame[0], frame[1], frame[2], frame[3], tgt_d, tgt_m)
+        packed, pad = self._graphs.call_with_trails(frame[0], frame[1], frame[2], frame[3], trail_det, trail_meta)
         return packed[pad:]                       # the padding track-query rows sit at the front
 
     @torch.no_grad()
     def step(self, frame):
-        """frame = (src_det, src_meta, pos_det, pos_meta), each (1, T, C) on the device -> {track_id: {"bbox", "score"}}."""
+        """frame = (src_det, src_meta, pos_det, pos_meta), each (1, T, C) on the device -> {track_id: {"bbox", "score"}}
+        (a read-only mapping built on first access; ``.ids`` / ``.boxes`` / ``.scores`` are the arrays behind it)."""
         dev = frame[0].device
         K = len(self.ids)
-        det_t = meta_t = None
-        if K:
-            det_t, meta_t = self._to_device(dev, *self._trails())
-        packed = (self._detect_graph if self.use_graphs else self._detect_eager)(frame, det_t, meta_t)
+        if self.use_graphs:
+            packed = self._detect_graph(frame, *self._trails())
+        else:
+            det_t = meta_t = None
+            if K:
+                det_t, meta_t = self._to_device(dev, *self._trails())
+            packed = self._detect_eager(frame, det_t, meta_t)
         return self._update(packed.cpu().numpy(), K)                      # ONE device -> host read per frame
 
     def _update(self, packed, K):
@@ -542,8 +589,7 @@ class KineSequenceTracker:
         self.misses = np.concatenate([misses, np.zeros(m, np.int64)])
         self.trail = np.concatenate([trail, np.repeat(rel[idx][:, None].astype(np.float32), n, 1)])
         self.trail_sc = np.concatenate([trail_sc, np.repeat(ns[:, None].astype(np.float32), n, 1)])
-        frame = {int(t): {"bbox": self.boxes[i].copy(), "score": float(self.scores[i])} for i, t in enumerate(self.ids)}
-        for tid, r in frame.items():
-            self.results.setdefault(tid, {})[self.frame_index] = r
+        frame = FrameTracks(self.ids, self.boxes, self.scores)             # the arrays are replaced, never edited in place
+        self._frames.append(frame)
         self.frame_index += 1
         return frame

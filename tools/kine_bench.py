@@ -201,8 +201,24 @@ def measure_tracker(dev, frames=200, fp32=False, nq=150, d=288, n_frames=5, seed
     b.record()
     torch.cuda.synchronize()
     ms = a.elapsed_time(b) / frames
+    # where a frame goes (host clock, a second pass): enqueue (trails -> pinned block, copies, replay) / wait for the
+    # read-back / host update
+    import time
+    ph = [0.0, 0.0, 0.0]
+    for i in range(frames):
+        t0 = time.perf_counter()
+        K = len(trk.ids)
+        packed = trk._detect_graph(feeds[i & 15], *trk._trails())
+        t1 = time.perf_counter()
+        host = packed.cpu().numpy()
+        t2 = time.perf_counter()
+        trk._update(host, K)
+        t3 = time.perf_counter()
+        ph[0] += t1 - t0; ph[1] += t2 - t1; ph[2] += t3 - t2
     return dict(tracker_ms_per_frame=ms, tracker_frames_per_s=1e3 / ms, tracks_min_max=[min(counts), max(counts)],
-                tracks_started=trk.next_id, graphs_recorded=len(trk._graphs.recorded_buckets))
+                tracks_started=trk.next_id, graphs_recorded=len(trk._graphs.recorded_buckets),
+                phases_ms=dict(enqueue=1e3 * ph[0] / frames, wait_and_read_back=1e3 * ph[1] / frames,
+                               host_update=1e3 * ph[2] / frames))
 
 
 def profile(dev, fp32):
