@@ -73,13 +73,9 @@ class DetectionHeads(nn.Module):
         return logits, tmp.sigmoid()
 
 
-def _nms(boxes, scores, thresh):
-    """Indices kept by greedy IoU suppression (torchvision.ops.nms semantics: IoU > thresh suppresses), on the host.
-    One vectorised IoU matrix; the common case (nothing overlaps that much) returns without a Python loop."""
-    n = len(boxes)
-    if n <= 1:
-        return np.arange(n, dtype=np.int64)
-    x1, y1, x2, y2 = boxes.T
+def _iou_matrix(boxes):
+    """(n, n) IoU of xyxy boxes in float32 (what torchvision.ops.nms computes in), from contiguous coordinate rows."""
+    x1, y1, x2, y2 = np.ascontiguousarray(boxes.T, dtype=np.float32)
     area = np.maximum(x2 - x1, 0) * np.maximum(y2 - y1, 0)
     iw = np.minimum(x2[:, None], x2) - np.maximum(x1[:, None], x1)
     ih = np.minimum(y2[:, None], y2) - np.maximum(y1[:, None], y1)
@@ -87,18 +83,32 @@ def _nms(boxes, scores, thresh):
     inter *= np.maximum(ih, 0, out=ih)
     union = area[:, None] + area
     union -= inter
-    over = inter > thresh * np.maximum(union, 1e-12, out=union)           # IoU > thresh without the division
-    over.flat[::n + 1] = False
-    if not over.any():
-        return np.arange(n, dtype=np.int64)
-    order = np.argsort(-scores, kind="stable")
-    dead = np.zeros(n, dtype=bool)
+    return np.divide(inter, np.maximum(union, 1e-12, out=union), out=inter)
+
+
+def _greedy_keep(over, order):
+    """Greedy suppression over a boolean (n, n) 'i suppresses j' matrix (diagonal False) visiting ``order``: the sorted
+    indices kept."""
+    dead = np.zeros(len(over), dtype=bool)
     keep = []
     for i in order:
         if not dead[i]:
             keep.append(i)
             dead |= over[i]
     return np.asarray(sorted(keep), dtype=np.int64)
+
+
+def _nms(boxes, scores, thresh):
+    """Indices kept by greedy IoU suppression (torchvision.ops.nms semantics: IoU > thresh suppresses), on the host.
+    One vectorised IoU matrix; the common case (nothing overlaps that much) returns without a Python loop."""
+    n = len(boxes)
+    if n <= 1:
+        return np.arange(n, dtype=np.int64)
+    over = _iou_matrix(boxes) > thresh
+    over.flat[::n + 1] = False
+    if not over.any():
+        return np.arange(n, dtype=np.int64)
+    return _greedy_keep(over, np.argsort(-scores, kind="stable"))
 
 
 class SequenceTracker:
@@ -432,6 +442,7 @@ class KineSequenceTracker:
                  token_bucket=32, track_bucket=8, autocast_dtype=None):
         self.detector = detector
         self.img_h, self.img_w = float(img_size[0]), float(img_size[1])
+        self._wh = np.array([self.img_w, self.img_h, self.img_w, self.img_h])
         self.n_frames = int(n_frames)
         self.det_thresh, self.trk_thresh = detection_obj_score_thresh, track_obj_score_thresh
         self.det_nms, self.trk_nms = detection_nms_thresh, track_nms_thresh
@@ -551,44 +562,69 @@ class KineSequenceTracker:
         return self._update(packed.cpu().numpy(), K)                      # ONE device -> host read per frame
 
     def _update(self, packed, K):
+        """packed (K + num_queries, 6) float32 from the detector (score, label, relative cx cy w h), track queries first.
+        Every state array is REPLACED (FrameTracks of earlier frames keep theirs); selects are whole-array ``np.where`` /
+        boolean compress, and both suppression passes read one IoU matrix."""
         n = self.n_frames
-        sc, lb, rel = packed[:, 0].astype(np.float64), packed[:, 1].astype(np.int64), packed[:, 2:6].astype(np.float64)
-        rel = np.clip(rel, 0.0, 1.0)                                       # relative boxes are clamped (:688-690)
-        wh = np.array([self.img_w, self.img_h, self.img_w, self.img_h])
-        px = np.stack([rel[:, 0] - rel[:, 2] / 2, rel[:, 1] - rel[:, 3] / 2, rel[:, 0] + rel[:, 2] / 2, rel[:, 1] + rel[:, 3] / 2], -1) * wh
-        px = np.minimum(np.clip(px, 0, None), wh)                          # clip_boxes_to_image
+        p = packed.astype(np.float64)
+        sc, lb = p[:, 0], p[:, 1]
+        rel = np.clip(p[:, 2:6], 0.0, 1.0)                                 # relative boxes are clamped (:688-690)
+        half = rel[:, 2:] * 0.5
+        px = np.concatenate([rel[:, :2] - half, rel[:, :2] + half], 1)
+        px *= self._wh
+        np.clip(px, 0.0, self._wh, out=px)                                 # clip_boxes_to_image
+        rel32 = rel.astype(np.float32)
         ids, boxes, scores, misses, trail, trail_sc = self.ids, self.boxes, self.scores, self.misses, self.trail, self.trail_sc
         if K:                                                              # manage_active_tracks (:937-955)
             keep = (sc[:K] > self.trk_thresh) & (lb[:K] == 0)
-            boxes, scores, misses, trail, trail_sc = boxes.copy(), scores.copy(), misses.copy(), trail.copy(), trail_sc.copy()
-            boxes[keep], scores[keep], misses[keep] = px[:K][keep], sc[:K][keep], 0
+            k1, k2 = keep[:, None], keep[:, None, None]
+            boxes = np.where(k1, px[:K], boxes)
+            scores = np.where(keep, sc[:K], scores)
+            misses = np.where(keep, 0, misses + 1)
             # a surviving track's trail grows by the new box / score (young tracks repeat their oldest entry: a trail that
             # starts as n copies of the first detection, shifted left once per frame, is exactly TrackKinematic.get_trail)
-            trail[keep] = np.concatenate([trail[keep][:, 1:], rel[:K][keep][:, None].astype(np.float32)], 1)
-            trail_sc[keep] = np.concatenate([trail_sc[keep][:, 1:], sc[:K][keep][:, None].astype(np.float32)], 1)
-            misses[~keep] += 1
+            trail = np.where(k2, np.concatenate([trail[:, 1:], rel32[:K, None]], 1), trail)
+            trail_sc = np.where(k1, np.concatenate([trail_sc[:, 1:], sc[:K, None].astype(np.float32)], 1), trail_sc)
             alive = keep | (misses < self.steps_termination)
-            ids, boxes, scores, misses, trail, trail_sc = (a[alive] for a in (ids, boxes, scores, misses, trail, trail_sc))
-            if self.trk_nms and len(ids):
-                k = _nms(boxes, scores, self.trk_nms)
-                ids, boxes, scores, misses, trail, trail_sc = (a[k] for a in (ids, boxes, scores, misses, trail, trail_sc))
-        # generate_new_tracks (:895-930): the detection repeated n times is the new track's trail
+            if not alive.all():
+                ids, boxes, scores, misses, trail, trail_sc = (a[alive] for a in (ids, boxes, scores, misses, trail, trail_sc))
+        # generate_new_tracks (:895-930): object queries above the detection threshold
         idx = K + np.flatnonzero((sc[K:] > self.det_thresh) & (lb[K:] < self.n_classes))
-        nb, ns = px[idx], sc[idx]
-        nlive = len(ids)
-        if self.det_nms and (nlive or len(idx)):                           # existing tracks always win (:820-838)
-            k = _nms(np.concatenate([boxes, nb]), np.concatenate([np.full(nlive, np.inf), ns]), self.det_nms)
-            kl, kn = k[k < nlive], k[k >= nlive] - nlive
-            ids, boxes, scores, misses, trail, trail_sc = (a[kl] for a in (ids, boxes, scores, misses, trail, trail_sc))
-            idx, nb, ns = idx[kn], nb[kn], ns[kn]
-        m = len(idx)
-        self.ids = np.concatenate([ids, np.arange(self.next_id, self.next_id + m, dtype=np.int64)])
-        self.next_id += m
-        self.boxes = np.concatenate([boxes, nb])
-        self.scores = np.concatenate([scores, ns])
-        self.misses = np.concatenate([misses, np.zeros(m, np.int64)])
-        self.trail = np.concatenate([trail, np.repeat(rel[idx][:, None].astype(np.float32), n, 1)])
-        self.trail_sc = np.concatenate([trail_sc, np.repeat(ns[:, None].astype(np.float32), n, 1)])
+        nl, m = len(ids), len(idx)
+        sel_t, sel_n = None, None                                          # None = all kept
+        need_t, need_d = bool(self.trk_nms) and nl > 1, bool(self.det_nms) and nl + m > 1
+        if need_t or need_d:
+            allb = np.concatenate([boxes, px[idx]]) if m else boxes
+            iou = _iou_matrix(allb)
+            iou.flat[::nl + m + 1] = 0.0
+            lo = min(t for t, need in ((self.trk_nms, need_t), (self.det_nms, need_d)) if need)
+            if (iou > lo).any():                                           # rare: something overlaps, run the greedy passes
+                kt, kn = np.arange(nl), np.arange(m)
+                if need_t:                                                 # NMS among the tracks (:733)
+                    kt = _greedy_keep(iou[:nl, :nl] > self.trk_nms, np.argsort(-scores, kind="stable"))
+                if need_d:                                                 # :786-800: tracks, old ones at score inf, and births
+                    sel = np.concatenate([kt, nl + kn])
+                    order = np.concatenate([np.arange(len(kt)), len(kt) + np.argsort(-sc[idx], kind="stable")])
+                    k = _greedy_keep(iou[np.ix_(sel, sel)] > self.det_nms, order)
+                    kt, kn = kt[k[k < len(kt)]], k[k >= len(kt)] - len(kt)
+                sel_t, sel_n = kt, kn
+        if sel_t is not None and len(sel_t) < nl:
+            ids, boxes, scores, misses, trail, trail_sc = (a[sel_t] for a in (ids, boxes, scores, misses, trail, trail_sc))
+        if sel_n is not None and len(sel_n) < m:
+            idx = idx[sel_n]
+            m = len(idx)
+        if m:
+            ns = sc[idx]
+            self.ids = np.concatenate([ids, np.arange(self.next_id, self.next_id + m, dtype=np.int64)])
+            self.next_id += m
+            self.boxes = np.concatenate([boxes, px[idx]])
+            self.scores = np.concatenate([scores, ns])
+            self.misses = np.concatenate([misses, np.zeros(m, np.int64)])
+            # the detection repeated n times is the new track's trail (generate_pseudo_tracklets)
+            self.trail = np.concatenate([trail, np.repeat(rel32[idx][:, None], n, 1)])
+            self.trail_sc = np.concatenate([trail_sc, np.repeat(ns[:, None].astype(np.float32), n, 1)])
+        else:
+            self.ids, self.boxes, self.scores, self.misses, self.trail, self.trail_sc = ids, boxes, scores, misses, trail, trail_sc
         frame = FrameTracks(self.ids, self.boxes, self.scores)             # the arrays are replaced, never edited in place
         self._frames.append(frame)
         self.frame_index += 1
