@@ -46,12 +46,14 @@ ROOFLINE_INPUTS = os.path.join(ROOT, "profiles", "roofline_inputs.json")
 
 
 def csrc_hash():
-    """sha256 over the CUDA sources, the key profiles/roofline_inputs.json was recorded under."""
+    """sha256 over the operator's CUDA sources (csrc/msda_*: the kernels the ncu capture is of; the callers' glue
+    kernels in layer_ops.cu / small_mha.cu are not part of that launch), the key profiles/roofline_inputs.json was
+    recorded under."""
     import hashlib
     h = hashlib.sha256()
     d = os.path.join(ROOT, "kinet_b200", "csrc")
     for name in sorted(os.listdir(d)):
-        if name.endswith((".cu", ".cuh")):
+        if name.startswith("msda_") and name.endswith((".cu", ".cuh")):
             with open(os.path.join(d, name), "rb") as f:
                 h.update(name.encode() + b"\0" + f.read())
     return h.hexdigest()[:16]

@@ -20,6 +20,7 @@ from kinet_b200.workloads import PYRAMIDS  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--top", type=int, default=40)
 ap.add_argument("--dropout", type=float, default=0.1)
+ap.add_argument("--ops", action="store_true", help="aten ops by input shape (where the elementwise tail comes from)")
 args = ap.parse_args()
 dev = torch.device("cuda", 0)
 levels, d = PYRAMIDS["detr_800x1333"], 256
@@ -49,6 +50,13 @@ def step():
 for _ in range(3):
     step()
 torch.cuda.synchronize()
+if args.ops:
+    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_shapes=True) as prof:
+        step()
+        torch.cuda.synchronize()
+    print(prof.key_averages(group_by_input_shape=True).table(sort_by="self_device_time_total", row_limit=args.top,
+                                                             max_name_column_width=50, max_shapes_column_width=90))
+    sys.exit(0)
 with profile(activities=[ProfilerActivity.CUDA]) as prof:
     step()
     torch.cuda.synchronize()
