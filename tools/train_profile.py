@@ -21,6 +21,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--top", type=int, default=40)
 ap.add_argument("--dropout", type=float, default=0.1)
 ap.add_argument("--ops", action="store_true", help="aten ops by input shape (where the elementwise tail comes from)")
+ap.add_argument("--stacks", default="", help="comma-separated aten op names: print the Python call sites of their launches")
 args = ap.parse_args()
 dev = torch.device("cuda", 0)
 levels, d = PYRAMIDS["detr_800x1333"], 256
@@ -50,6 +51,18 @@ def step():
 for _ in range(3):
     step()
 torch.cuda.synchronize()
+if args.stacks:
+    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_shapes=True, with_stack=True) as prof:
+        step()
+        torch.cuda.synchronize()
+    want = set(args.stacks.split(","))
+    rows = [e for e in prof.key_averages(group_by_input_shape=True, group_by_stack_n=12) if e.key in want]
+    for e in sorted(rows, key=lambda e: -e.device_time_total)[:args.top]:
+        print("%-14s x%-3d %8.1f us  %s" % (e.key, e.count, e.device_time_total, str(e.input_shapes)[:100]))
+        for fr in e.stack[:12]:
+            if "kinet_b200" in fr or "tools/" in fr:
+                print("      ", fr[-110:])
+    sys.exit(0)
 if args.ops:
     with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_shapes=True) as prof:
         step()
