@@ -426,7 +426,12 @@ class KineSequenceTracker:
         ``n_frames`` times (``generate_pseudo_tracklets``); :820-838 NMS in which existing tracks always win;
       * :860-880  per-frame results.
 
-    Not covered (as in SequenceTracker): re-identification of inactive tracks, public detections.  The reference's
+      * :630-633, :652, :700-713, :922-931  with ``inactive_patience`` >= 0 (cfgs/track_kinet.yaml:45: 5) a terminated track
+        stays an INACTIVE track query for that many frames (its trail frozen, the last entry repeated once) and comes back
+        under its old id when its query scores above ``reid_score_thresh``; -1 (cfgs/track.yaml) forgets it at once.
+
+    Not covered: public detections (``public_detections: False`` in both tracking configs); the embedding-distance
+    ``reid()`` of the deformable Tracker is commented out in TrackerKinematic.step (:756-762).  The reference's
     ``add_tracks`` (:882-893) does not run as shipped (it passes ``confidence=`` to a constructor without that parameter,
     SURVEY.md F7); the evident intent -- a TrackKinematic holding the detection's box, score and pseudo-trail -- is built.
 
@@ -439,8 +444,9 @@ class KineSequenceTracker:
 
     def __init__(self, detector, img_size, n_frames=5, detection_obj_score_thresh=0.4, track_obj_score_thresh=0.4,
                  detection_nms_thresh=0.9, track_nms_thresh=0.9, steps_termination=1, n_classes=1, use_graphs=False,
-                 token_bucket=32, track_bucket=8, autocast_dtype=None):
+                 token_bucket=32, track_bucket=8, autocast_dtype=None, inactive_patience=-1, reid_score_thresh=0.4):
         self.detector = detector
+        self.inactive_patience, self.reid_thresh = inactive_patience, reid_score_thresh
         self.img_h, self.img_w = float(img_size[0]), float(img_size[1])
         self._wh = np.array([self.img_w, self.img_h, self.img_w, self.img_h])
         self.n_frames = int(n_frames)
@@ -461,6 +467,11 @@ class KineSequenceTracker:
         self.misses = np.empty(0, np.int64)
         self.trail = np.empty((0, n, 4), np.float32)         # last n relative boxes (cx, cy, w, h), oldest first
         self.trail_sc = np.empty((0, n), np.float32)         # ... and scores
+        # terminated tracks kept as track queries for ``inactive_patience`` more frames (re-identification, :630-633):
+        # ids, boxes, scores, trail, trail scores, frames spent inactive
+        self.inactive = (np.empty(0, np.int64), np.empty((0, 4), np.float64), np.empty(0, np.float64),
+                         np.empty((0, n, 4), np.float32), np.empty((0, n), np.float32), np.empty(0, np.int64))
+        self.num_reids = 0
         self.next_id = 0
         self.frame_index = 0
         self._frames = []
@@ -468,6 +479,18 @@ class KineSequenceTracker:
     @property
     def tracks(self):
         return self.ids.tolist()
+
+    @property
+    def inactive_tracks(self):
+        return self.inactive[0].tolist()
+
+    def _prune_inactive(self):
+        """Start of a frame (:630-633): inactive tracks beyond their patience, or without area, are forgotten."""
+        iid, ibox, isc, itr, itsc, icnt = self.inactive
+        if len(iid):
+            ok = (icnt <= self.inactive_patience) & (ibox[:, 2] > ibox[:, 0]) & (ibox[:, 3] > ibox[:, 1])
+            if not ok.all():
+                self.inactive = tuple(a[ok] for a in self.inactive)
 
     @property
     def results(self):
@@ -481,8 +504,11 @@ class KineSequenceTracker:
 
     # ---- trails -> track-query inputs (tracker.py:652-671, :1027-1046) ----
     def _trails(self):
-        K = len(self.ids)
-        return self.trail.reshape(K, 4 * self.n_frames), self.trail_sc
+        """Track queries of the frame: the live tracks, then the inactive ones (``self.tracks + self.inactive_tracks``, :652)."""
+        trail, trail_sc = self.trail, self.trail_sc
+        if len(self.inactive[0]):
+            trail, trail_sc = np.concatenate([trail, self.inactive[3]]), np.concatenate([trail_sc, self.inactive[4]])
+        return trail.reshape(len(trail), 4 * self.n_frames), trail_sc
 
     def _to_device(self, dev, det, meta):
         """(K, n*4) and (K, n) host arrays -> device tensors through pinned staging (see SequenceTracker._to_device_indices)."""
@@ -551,7 +577,8 @@ class KineSequenceTracker:
         """frame = (src_det, src_meta, pos_det, pos_meta), each (1, T, C) on the device -> {track_id: {"bbox", "score"}}
         (a read-only mapping built on first access; ``.ids`` / ``.boxes`` / ``.scores`` are the arrays behind it)."""
         dev = frame[0].device
-        K = len(self.ids)
+        self._prune_inactive()
+        K = len(self.ids) + len(self.inactive[0])
         if self.use_graphs:
             packed = self._detect_graph(frame, *self._trails())
         else:
@@ -562,10 +589,11 @@ class KineSequenceTracker:
         return self._update(packed.cpu().numpy(), K)                      # ONE device -> host read per frame
 
     def _update(self, packed, K):
-        """packed (K + num_queries, 6) float32 from the detector (score, label, relative cx cy w h), track queries first.
-        Every state array is REPLACED (FrameTracks of earlier frames keep theirs); selects are whole-array ``np.where`` /
-        boolean compress, and both suppression passes read one IoU matrix."""
+        """packed (K + num_queries, 6) float32 from the detector (score, label, relative cx cy w h), the K track queries
+        (live tracks, then inactive ones) first.  Every state array is REPLACED (FrameTracks of earlier frames keep theirs);
+        selects are whole-array ``np.where`` / boolean compress, and both suppression passes read one IoU matrix."""
         n = self.n_frames
+        nA = len(self.ids)                                                 # live tracks; rows nA .. K-1 are inactive ones
         p = packed.astype(np.float64)
         sc, lb = p[:, 0], p[:, 1]
         rel = np.clip(p[:, 2:6], 0.0, 1.0)                                 # relative boxes are clamped (:688-690)
@@ -575,19 +603,46 @@ class KineSequenceTracker:
         np.clip(px, 0.0, self._wh, out=px)                                 # clip_boxes_to_image
         rel32 = rel.astype(np.float32)
         ids, boxes, scores, misses, trail, trail_sc = self.ids, self.boxes, self.scores, self.misses, self.trail, self.trail_sc
-        if K:                                                              # manage_active_tracks (:937-955)
-            keep = (sc[:K] > self.trk_thresh) & (lb[:K] == 0)
+        gone = None                                                        # live tracks terminated in this frame
+        if nA:                                                             # manage_active_tracks (:937-955)
+            keep = (sc[:nA] > self.trk_thresh) & (lb[:nA] == 0)
             k1, k2 = keep[:, None], keep[:, None, None]
-            boxes = np.where(k1, px[:K], boxes)
-            scores = np.where(keep, sc[:K], scores)
+            boxes = np.where(k1, px[:nA], boxes)
+            scores = np.where(keep, sc[:nA], scores)
             misses = np.where(keep, 0, misses + 1)
             # a surviving track's trail grows by the new box / score (young tracks repeat their oldest entry: a trail that
             # starts as n copies of the first detection, shifted left once per frame, is exactly TrackKinematic.get_trail)
-            trail = np.where(k2, np.concatenate([trail[:, 1:], rel32[:K, None]], 1), trail)
-            trail_sc = np.where(k1, np.concatenate([trail_sc[:, 1:], sc[:K, None].astype(np.float32)], 1), trail_sc)
+            trail = np.where(k2, np.concatenate([trail[:, 1:], rel32[:nA, None]], 1), trail)
+            trail_sc = np.where(k1, np.concatenate([trail_sc[:, 1:], sc[:nA, None].astype(np.float32)], 1), trail_sc)
             alive = keep | (misses < self.steps_termination)
             if not alive.all():
+                if self.inactive_patience >= 0:
+                    gone = tuple(a[~alive] for a in (ids, boxes, scores, trail, trail_sc))
                 ids, boxes, scores, misses, trail, trail_sc = (a[alive] for a in (ids, boxes, scores, misses, trail, trail_sc))
+        if K > nA or gone is not None:
+            # inactive track queries that score above reid_score_thresh come back (manage_inactive_tracks, :922-931: behind
+            # the live tracks; the reference does not reset their count of inactive frames, :241 is the other re-id path);
+            # the tracks terminated above go inactive with their last state repeated once (move_tracks_to_inactive, :88-94,
+            # whose repeat_last_pos() is TrackKinematic.repeat_last_state -- the name it calls does not exist)
+            iid, ibox, isc, itr, itsc, icnt = self.inactive
+            if K > nA:
+                back = (sc[nA:K] > self.reid_thresh) & (lb[nA:K] == 0)
+                if back.any():
+                    self.num_reids += int(back.sum())
+                    ids = np.concatenate([ids, iid[back]])
+                    boxes = np.concatenate([boxes, px[nA:K][back]])
+                    scores = np.concatenate([scores, sc[nA:K][back]])
+                    misses = np.concatenate([misses, np.zeros(int(back.sum()), np.int64)])
+                    trail = np.concatenate([trail, np.concatenate([itr[back][:, 1:], rel32[nA:K][back][:, None]], 1)])
+                    trail_sc = np.concatenate([trail_sc, np.concatenate([itsc[back][:, 1:], sc[nA:K][back][:, None].astype(np.float32)], 1)])
+                    iid, ibox, isc, itr, itsc, icnt = (a[~back] for a in (iid, ibox, isc, itr, itsc, icnt))
+            if gone is not None:
+                gid, gbox, gsc, gtr, gtsc = gone
+                iid, ibox, isc = np.concatenate([iid, gid]), np.concatenate([ibox, gbox]), np.concatenate([isc, gsc])
+                itr = np.concatenate([itr, np.concatenate([gtr[:, 1:], gtr[:, -1:]], 1)])
+                itsc = np.concatenate([itsc, np.concatenate([gtsc[:, 1:], gtsc[:, -1:]], 1)])
+                icnt = np.concatenate([icnt, np.zeros(len(gid), np.int64)])
+            self.inactive = (iid, ibox, isc, itr, itsc, icnt)
         # generate_new_tracks (:895-930): object queries above the detection threshold
         idx = K + np.flatnonzero((sc[K:] > self.det_thresh) & (lb[K:] < self.n_classes))
         nl, m = len(ids), len(idx)
@@ -625,6 +680,8 @@ class KineSequenceTracker:
             self.trail_sc = np.concatenate([trail_sc, np.repeat(ns[:, None].astype(np.float32), n, 1)])
         else:
             self.ids, self.boxes, self.scores, self.misses, self.trail, self.trail_sc = ids, boxes, scores, misses, trail, trail_sc
+        if len(self.inactive[0]):                                          # :849-850
+            self.inactive = self.inactive[:5] + (self.inactive[5] + 1,)
         frame = FrameTracks(self.ids, self.boxes, self.scores)             # the arrays are replaced, never edited in place
         self._frames.append(frame)
         self.frame_index += 1

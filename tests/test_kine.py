@@ -467,7 +467,8 @@ def test_kine_frame_graphs_match_direct_calls_with_varying_sizes():
 
 
 @pytest.mark.gpu
-def test_kine_sequence_tracker_graphs_match_eager_detector_over_a_sequence():
+@pytest.mark.parametrize("patience", [-1, 3])
+def test_kine_sequence_tracker_graphs_match_eager_detector_over_a_sequence(patience):
     """KineSequenceTracker (the loop of TrackerKinematic.step: trails -> track queries -> detector -> thresholds / NMS ->
     births and terminations): replaying KineFrameGraphs gives the same track ids every frame and boxes within 1e-3 px of the
     eager loop through KinematicDetectorTransformer.forward(samples, targets); tracks are born, carried and terminated."""
@@ -490,7 +491,9 @@ def test_kine_sequence_tracker_graphs_match_eager_detector_over_a_sequence():
     for i in range(24):
         T = 9 + (7 * i) % 11
         frames.append(tuple((s[:, :T] + 0.25 * torch.randn(1, T, d, generator=g)).to(dev) for s in scene))
-    kw = dict(img_size=(1080, 1920), n_frames=n_frames, detection_nms_thresh=0.9, track_nms_thresh=0.9)
+    # patience 3: terminated tracks stay inactive track queries for three frames (re-identification, cfgs/track_kinet.yaml:45)
+    kw = dict(img_size=(1080, 1920), n_frames=n_frames, detection_nms_thresh=0.9, track_nms_thresh=0.9,
+              inactive_patience=patience, reid_score_thresh=0.0)
     a = KineSequenceTracker(det, use_graphs=True, token_bucket=8, track_bucket=4, **kw)
     b = KineSequenceTracker(det, use_graphs=False, **kw)
     # random weights: put the thresholds where about a third of the object queries fire
@@ -499,14 +502,25 @@ def test_kine_sequence_tracker_graphs_match_eager_detector_over_a_sequence():
     thr = float(torch.quantile(sc, 0.67))
     for t in (a, b):
         t.det_thresh, t.trk_thresh = thr, thr - 0.02 * (float(sc.max()) - float(sc.min()))
-    counts = []
-    for f in frames:
+        t.reid_thresh = t.trk_thresh                       # an inactive track comes back when it scores like a live one
+    counts, inactive_seen = [], False
+    trk_thresh = a.trk_thresh
+    for i, f in enumerate(frames):
+        if patience >= 0:
+            # random weights give near-binary scores: drive the inactive path by hand -- every 6th frame all live tracks
+            # are terminated (they stay inactive track queries), two frames later every inactive query is taken back
+            for t in (a, b):
+                t.trk_thresh = float("inf") if i % 6 == 3 else trk_thresh
+                t.reid_thresh = float("-inf") if i % 6 == 5 else float("inf")
         ra, rb = a.step(f), b.step(f)
         assert sorted(ra) == sorted(rb)
         for tid in ra:
             assert np.abs(ra[tid]["bbox"] - rb[tid]["bbox"]).max() < 1e-3
             assert abs(ra[tid]["score"] - rb[tid]["score"]) < 1e-5
+        assert a.inactive_tracks == b.inactive_tracks
         counts.append(len(ra))
+        inactive_seen = inactive_seen or bool(a.inactive_tracks)
+    assert inactive_seen == (patience >= 0) and a.num_reids == b.num_reids and (a.num_reids > 0) == (patience >= 0)
     assert a.next_id == b.next_id and a.next_id > max(counts) > 0          # tracks were started and some ended
     assert any(len(v) >= 3 for v in a.results.values())                   # some track lived for several frames
     assert len(a._graphs.recorded_buckets) >= 3

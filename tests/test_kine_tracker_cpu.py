@@ -113,3 +113,56 @@ def test_iou_matrix_and_nms_semantics():
     assert _nms(boxes, np.array([0.5, 0.9, 0.1, 0.2]), 0.5).tolist() == [0, 1, 2, 3]      # strictly greater suppresses
     over = np.array([[0, 1, 0], [1, 0, 1], [0, 1, 0]], bool)
     assert _greedy_keep(over, [1, 0, 2]).tolist() == [1] and _greedy_keep(over, [0, 1, 2]).tolist() == [0, 2]
+
+
+def _step(t, rows):
+    """One frame through the host logic as KineSequenceTracker.step runs it: prune, build the query list, update."""
+    t._prune_inactive()
+    K = len(t.ids) + len(t.inactive[0])
+    det, meta = t._trails()
+    assert det.shape == (K, 4 * t.n_frames) and meta.shape == (K, t.n_frames)
+    assert len(rows) >= K
+    return t._update(_packed(rows), K), det, meta
+
+
+def test_inactive_track_stays_a_query_and_comes_back_under_its_id():
+    t = _tracker(inactive_patience=2, reid_score_thresh=0.3)
+    _step(t, [_row(0.9, 0.5, 0.5), _row(0.8, 0.2, 0.2)])                        # two births: ids 0, 1
+    out, _, _ = _step(t, [_row(0.9, 0.5, 0.5), _row(0.1, 0.2, 0.2), _row(0.0, 0, 0)])      # track 1 is lost
+    assert sorted(out) == [0] and t.inactive_tracks == [1] and t.inactive[5].tolist() == [1]
+    # its frozen trail (last entry repeated once) is the frame's second track query
+    out, det, _ = _step(t, [_row(0.9, 0.5, 0.5), _row(0.2, 0.2, 0.2), _row(0.0, 0, 0)])    # still below reid_score_thresh
+    np.testing.assert_allclose(det[1].reshape(3, 4), np.tile([0.2, 0.2, 0.1, 0.2], (3, 1)), atol=1e-6)
+    assert sorted(out) == [0] and t.inactive_tracks == [1] and t.inactive[5].tolist() == [2]
+    out, _, _ = _step(t, [_row(0.9, 0.5, 0.5), _row(0.35, 0.25, 0.2), _row(0.0, 0, 0)])    # above it (and below the track threshold)
+    assert sorted(out) == [0, 1] and t.inactive_tracks == [] and t.num_reids == 1 and t.next_id == 2
+    np.testing.assert_allclose(out[1]["bbox"], [200, 50, 300, 150], atol=1e-3)
+    np.testing.assert_allclose(t.trail[1], [[0.2, 0.2, 0.1, 0.2], [0.2, 0.2, 0.1, 0.2], [0.25, 0.2, 0.1, 0.2]], atol=1e-6)
+    assert t.results[1].keys() == {0, 3}                                                  # absent while inactive
+
+
+def test_inactive_track_is_forgotten_after_its_patience_and_default_forgets_at_once():
+    t = _tracker(inactive_patience=1)
+    _step(t, [_row(0.9, 0.5, 0.5)])
+    _step(t, [_row(0.1, 0.5, 0.5), _row(0.0, 0, 0)])                                       # lost: inactive, count 1
+    assert t.inactive_tracks == [0]
+    _step(t, [_row(0.1, 0.5, 0.5), _row(0.0, 0, 0)])                                       # count 1 <= patience: still a query; count 2
+    assert t.inactive_tracks == [0]
+    out, det, _ = _step(t, [_row(0.9, 0.5, 0.5)])                                          # pruned before the frame: one object query only
+    assert det.shape[0] == 0 and t.inactive_tracks == [] and sorted(out) == [1]           # the detection starts a NEW track
+    d = _tracker()                                                                         # inactive_patience = -1 (cfgs/track.yaml)
+    _step(d, [_row(0.9, 0.5, 0.5)])
+    _step(d, [_row(0.1, 0.5, 0.5), _row(0.0, 0, 0)])
+    assert d.inactive_tracks == [] and len(d.ids) == 0
+
+
+def test_a_degenerate_inactive_box_is_dropped_and_reactivated_tracks_take_part_in_nms():
+    t = _tracker(inactive_patience=5, reid_score_thresh=0.3)
+    _step(t, [_row(0.9, 0.5, 0.5, w=0.0), _row(0.9, 0.2, 0.2), _row(0.8, 0.7, 0.7)])       # id 0 has no area
+    _step(t, [_row(0.1, 0.5, 0.5), _row(0.1, 0.2, 0.2), _row(0.9, 0.7, 0.7), _row(0.0, 0, 0)])
+    assert t.inactive_tracks == [0, 1]
+    t._prune_inactive()
+    assert t.inactive_tracks == [1]                                                        # has_positive_area (:631)
+    # track 1 comes back on top of track 2 with the lower score: NMS among the tracks removes it again
+    out, _, _ = _step(t, [_row(0.9, 0.7, 0.7), _row(0.5, 0.701, 0.7), _row(0.0, 0, 0)])
+    assert sorted(out) == [2] and t.num_reids == 1 and t.inactive_tracks == []
