@@ -17,8 +17,9 @@ the encoder, one per bucket of query counts for the decoder): the number of quer
 What is different from the reference, on purpose: track state lives in device tensors (boxes, embeddings) instead
 of one Python object per track holding device scalars, and a frame is read back ONCE (scores, labels, boxes of
 all queries in one packed copy) instead of once per track and field (tracker.py:293, 536-542); thresholding and
-NMS then run on the host on a few hundred boxes.  Not covered: re-identification of inactive tracks
-(``inactive_patience`` >= 0; the reference's cfgs/track.yaml sets -1, i.e. off), public detections, masks,
+NMS then run on the host on a few hundred boxes.  Re-identification through inactive track queries (:273-276,
+:290-304, :367-394; ``inactive_patience`` >= 0 -- cfgs/track.yaml sets -1, i.e. off) is built; not covered: the
+embedding-distance ``reid()`` (:170-267; inert at the configured ``reid_sim_threshold`` 0.0), public detections, masks,
 attention maps -- they contain no MSDeformAttn work.  The backbone is out of scope: frames
 enter as the multi-scale feature maps the backbone + input projections would produce.
 """
@@ -124,8 +125,13 @@ class SequenceTracker:
 
     def __init__(self, transformer, heads, query_embed, img_size, detection_obj_score_thresh=0.4,
                  track_obj_score_thresh=0.4, detection_nms_thresh=0.9, track_nms_thresh=0.9, steps_termination=1,
-                 use_graphs=False, bucket=32, autocast_dtype=None):
+                 use_graphs=False, bucket=32, autocast_dtype=None, inactive_patience=-1, reid_score_thresh=0.4):
         assert not transformer.two_stage and not transformer.multi_frame_attention_separate_encoder
+        # inactive_patience >= 0: a terminated track stays a track query (its last box and embedding) for that many frames
+        # and returns under its id when that query scores above reid_score_thresh (tracker.py:273-276, :290-304, :367-383);
+        # -1 (cfgs/track.yaml:44) forgets it at once.  The embedding-distance reid() (:170-267) is not built: at the
+        # configured reid_sim_threshold 0.0 it never matches.
+        self.inactive_patience, self.reid_thresh = inactive_patience, reid_score_thresh
         self.transformer, self.heads = transformer, heads
         self.query_embed = query_embed
         self.num_object_queries = query_embed.shape[0]
@@ -141,10 +147,13 @@ class SequenceTracker:
         """Start a new sequence (tracker.py:75-95); recorded graphs are kept (same weights, same pyramid)."""
         self.track_ids = []                      # host: ids of the live tracks, in query order
         self.track_misses = []                   # host: consecutive frames below track_obj_score_thresh
-        self.track_boxes = None                  # device (T, 4) xyxy pixels
-        self.track_scores = None                 # host numpy (T,)
-        self._host_boxes = None                  # host numpy (T, 4), the same boxes
-        self.track_hs = None                     # device (T, C)
+        self.inactive_ids = []                   # host: ids of the inactive tracks, in query order behind the live ones
+        self.inactive_count = []                 # host: frames spent inactive
+        self.track_boxes = None                  # device (T + I, 4) xyxy pixels: live tracks, then inactive ones
+        self.track_scores = None                 # host numpy (T + I,)
+        self._host_boxes = None                  # host numpy (T + I, 4), the same boxes
+        self.track_hs = None                     # device (T + I, C)
+        self.num_reids = 0
         self.next_id = 0
         self.frame_index = 0
         self.results = {}
@@ -218,11 +227,32 @@ class SequenceTracker:
     def _targets(self, dev):
         if getattr(self, "_scale", None) is None or self._scale.device != dev:
             self._scale = torch.tensor([self.img_w, self.img_h, self.img_w, self.img_h], device=dev)
-        if not self.track_ids:
+        self._prune_inactive(dev)
+        if not self.track_ids and not self.inactive_ids:
             return None
         b = self.track_boxes                                       # xyxy px -> cxcywh normalised (tracker.py:299-304)
         cxcywh = torch.stack([(b[:, 0] + b[:, 2]) / 2, (b[:, 1] + b[:, 3]) / 2, b[:, 2] - b[:, 0], b[:, 3] - b[:, 1]], -1)
         return [{"track_query_boxes": cxcywh / self._scale, "track_query_hs_embeds": self.track_hs}]
+
+    def _prune_inactive(self, dev):
+        """Start of a frame (tracker.py:273-276): inactive tracks beyond their patience, or without area, are forgotten."""
+        I = len(self.inactive_ids)
+        if not I:
+            return
+        T = len(self.track_ids)
+        hb = self._host_boxes[T:]
+        ok = [self.inactive_count[j] <= self.inactive_patience and hb[j, 2] > hb[j, 0] and hb[j, 3] > hb[j, 1] for j in range(I)]
+        if all(ok):
+            return
+        rows = list(range(T)) + [T + j for j in range(I) if ok[j]]
+        self.inactive_ids = [t for t, k in zip(self.inactive_ids, ok) if k]
+        self.inactive_count = [c for c, k in zip(self.inactive_count, ok) if k]
+        self._host_boxes, self.track_scores = self._host_boxes[rows], self.track_scores[rows]
+        if rows:
+            (idx,) = self._to_device_indices(dev, rows)
+            self.track_boxes, self.track_hs = self.track_boxes[idx], self.track_hs[idx]
+        else:
+            self.track_boxes = self.track_hs = None
 
     @torch.no_grad()
     def step(self, srcs, masks, pos_embeds):
@@ -314,16 +344,30 @@ class SequenceTracker:
     def _update_tracks(self, hs, xyxy, packed):
         """Host side of a frame: packed = (Lq, 6) numpy [score, label, x1, y1, x2, y2] of all queries."""
         dev = hs.device
-        T = len(self.track_ids)
+        T, I = len(self.track_ids), len(self.inactive_ids)
         sc, lb, bx = packed[:, 0], packed[:, 1].astype(np.int64), packed[:, 2:6].astype(np.float64)
 
         # tracks (tracker.py:334-420): entry = [id, misses, query index this frame or -1 (stale), old row, box, score]
-        live = []
+        live, inactive = [], []                  # (inactive entries carry their count of inactive frames in slot 1)
         for j in range(T):
             if sc[j] > self.trk_thresh and lb[j] == 0:
                 live.append([self.track_ids[j], 0, j, j, bx[j], sc[j]])
             elif self.track_misses[j] + 1 < self.steps_termination:      # missed, not yet terminated: keeps its state
                 live.append([self.track_ids[j], self.track_misses[j] + 1, -1, j, self._host_boxes[j], self.track_scores[j]])
+            elif self.inactive_patience >= 0:                             # terminated: inactive, its last state kept (:88-94)
+                inactive.append([self.track_ids[j], 0, -1, j, self._host_boxes[j], self.track_scores[j]])
+        # inactive track queries above reid_score_thresh return, behind the live tracks (:367-383, :391-394; the reference
+        # does not reset their count of inactive frames on this path)
+        stay = []
+        for j in range(I):
+            r = T + j
+            if sc[r] > self.reid_thresh and lb[r] == 0:
+                live.append([self.inactive_ids[j], 0, r, r, bx[r], sc[r]])
+                self.num_reids += 1
+            else:
+                stay.append([self.inactive_ids[j], self.inactive_count[j], -1, r, self._host_boxes[r], self.track_scores[r]])
+        inactive = stay + inactive               # (move_tracks_to_inactive appends behind the inactive tracks already there)
+        T = T + I                                # the object queries follow all track queries
         if self.trk_nms and live:
             k = _nms(np.stack([e[4] for e in live]), np.asarray([e[5] for e in live]), self.trk_nms)
             live = [live[j] for j in k]
@@ -342,11 +386,12 @@ class SequenceTracker:
             e[0] = self.next_id
             self.next_id += 1
         entries = live + new
+        pool = entries + inactive                # next frame's track queries: live tracks, then inactive ones
         # next frame's track state, gathered on the device
-        if entries:
-            stale = [j for j, e in enumerate(entries) if e[2] < 0]
+        if pool:
+            stale = [j for j, e in enumerate(pool) if e[2] < 0]
             q_rows, dst, src_rows = self._to_device_indices(
-                dev, [max(e[2], 0) for e in entries], stale, [entries[j][3] for j in stale])
+                dev, [max(e[2], 0) for e in pool], stale, [pool[j][3] for j in stale])
             new_boxes, new_hs = xyxy[0, q_rows], hs[0, q_rows].float()
             if stale:                                               # a missed frame keeps the previous box / embedding
                 new_boxes[dst] = self.track_boxes[src_rows]
@@ -356,8 +401,10 @@ class SequenceTracker:
             self.track_boxes = self.track_hs = None
         self.track_ids = [e[0] for e in entries]
         self.track_misses = [e[1] for e in entries]
-        self._host_boxes = np.asarray([e[4] for e in entries], dtype=np.float64).reshape(-1, 4)
-        self.track_scores = np.asarray([e[5] for e in entries], dtype=np.float64)
+        self.inactive_ids = [e[0] for e in inactive]
+        self.inactive_count = [e[1] + 1 for e in inactive]           # :549-551
+        self._host_boxes = np.asarray([e[4] for e in pool], dtype=np.float64).reshape(-1, 4)
+        self.track_scores = np.asarray([e[5] for e in pool], dtype=np.float64)
         frame = {e[0]: {"bbox": np.array(e[4], dtype=np.float64), "score": float(e[5])} for e in entries}
         for t, r in frame.items():
             self.results.setdefault(t, {})[self.frame_index] = r

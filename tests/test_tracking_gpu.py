@@ -129,3 +129,51 @@ def test_tracker_termination_and_nms_rules_on_host():
     boxes = np.array([[0, 0, 10, 10], [0.5, 0.5, 10.5, 10.5], [50, 50, 60, 60.]])
     assert _nms(boxes, np.array([0.6, np.inf, 0.9]), 0.5).tolist() == [1, 2]
     assert _nms(boxes, np.array([0.9, 0.8, 0.7]), 0.95).tolist() == [0, 1, 2]
+
+
+def test_tracking_loop_inactive_tracks_return_and_graphs_match_eager():
+    """inactive_patience >= 0 (tracker.py:273-276, :290-304, :367-394): terminated tracks stay track queries (last box +
+    embedding) behind the live ones for that many frames and return under their id when their query scores above
+    reid_score_thresh.  Eager loop, bucketed graphs and the pipelined generator agree frame by frame; with the default
+    (-1) nothing is ever inactive."""
+    from kinet_b200.tracking import SequenceTracker, synthetic_sequence
+    dev = torch.device("cuda:0")
+    tr, heads, qe = _model(dev)
+    kw = dict(img_size=IMG, detection_obj_score_thresh=0.5, track_obj_score_thresh=0.5, inactive_patience=3,
+              reid_score_thresh=0.45)
+
+    def run(tracker, pipelined=False):
+        seq = synthetic_sequence(LEVELS, D, 24, dev, seed=0, drift=0.25)
+        frames, inactive = [], []
+        if pipelined:
+            for f in tracker.run(seq):
+                frames.append(f)
+                inactive.append(list(tracker.inactive_ids))
+        else:
+            for srcs, masks, pos in seq:
+                frames.append(tracker.step(srcs, masks, pos))
+                inactive.append(list(tracker.inactive_ids))
+        return frames, inactive
+
+    eager = SequenceTracker(tr, heads, qe, **kw)
+    fa, ia = run(eager)
+    assert any(ia), "no track ever went inactive"
+    assert all(c <= 3 + 1 for c in eager.inactive_count)
+    assert eager.num_reids > 0, "no inactive track ever returned"
+    # a returned track has a gap in its results: present, absent while inactive, present again under the same id
+    gaps = [t for t, r in eager.results.items() if len(r) >= 2 and max(r) - min(r) + 1 > len(r)]
+    assert gaps
+    # inactive tracks are not reported while inactive
+    for f, ids in zip(fa, ia):
+        assert not (set(f) & set(ids))
+    graphed = SequenceTracker(tr, heads, qe, use_graphs=True, bucket=8, **kw)
+    fb, ib = run(graphed)
+    _compare(fa, fb, 1e-3)
+    assert ia == ib and graphed.num_reids == eager.num_reids
+    graphed.reset()
+    fc, ic = run(graphed, pipelined=True)
+    _compare(fa, fc, 1e-3)
+    assert ia == ic
+    plain = SequenceTracker(tr, heads, qe, **dict(kw, inactive_patience=-1))
+    fd, idd = run(plain)
+    assert not any(idd) and plain.num_reids == 0
