@@ -1,0 +1,91 @@
+"""The `kine` model's token backbones and positional encoding (kinet_b200/modules/kinematic_backbone.py; reference
+src/trackformer/models/backbone.py:110-212, position_encoding.py:152-185) against golden vectors made from the
+reference's own classes (tests/golden/make_golden_kine_backbone.py), and the whole `kine` detector from raw detections."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from test_kine import _by_name, _rel
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _z():
+    with np.load(os.path.join(HERE, "golden", "kine_backbone_f32.npz")) as z:
+        return {k: z[k] for k in z.files}
+
+
+def _backbones(dev, max_det=7, d=72):
+    from kinet_b200.modules.kinematic_backbone import build_kine_backbone
+    back = build_kine_backbone(d, max_number_detection=max_det)
+    for b in back:
+        _by_name(b).to(dev).eval()
+    return back
+
+
+def test_backbones_and_detection_rank_embedding_match_reference_golden_on_cpu():
+    """case f: Joiner(Kinet_Backbone, PositionEmbeddingSineDetections) for detections and metadata, fp32 on the CPU."""
+    from kinet_b200.modules.kinematic_backbone import NestedTensor
+    z = _z()
+    back = _backbones(torch.device("cpu"))
+    mask = torch.from_numpy(z["f:mask"])
+    with torch.no_grad():
+        for name, b, key in (("det", back[0], "boxes"), ("meta", back[1], "conf")):
+            feats, pos = b(NestedTensor(torch.from_numpy(z["f:" + key]), mask))
+            assert len(feats) == 1 and feats[0].mask is mask
+            assert _rel(feats[0].tensors, torch.from_numpy(z["f:tokens_" + name])) < 2e-6, name
+            assert _rel(pos[0], torch.from_numpy(z["f:pos_" + name])) < 2e-6, name
+    # the rank embedding wraps at max_detections and ignores padded detections
+    assert torch.equal(pos[0][0, 0], pos[0][0, 7]) and not torch.equal(pos[0][0, 0], pos[0][0, 1])
+    assert torch.equal(pos[0][1, 5], pos[0][1, 8])               # the padded tail repeats the last real rank
+
+
+def test_backbone_classes_mirror_the_reference():
+    """Same constructor signatures and state_dict keys as the reference's classes (when /root/reference is there)."""
+    import inspect
+    import sys
+    if not os.path.isdir("/root/reference"):
+        pytest.skip("reference sources not present")
+    sys.path.insert(0, os.path.join(HERE, "golden"))
+    import importlib
+    from make_golden_layers import load_reference
+    load_reference()
+    bb = importlib.import_module("trackformer.models.backbone")
+    pe = importlib.import_module("trackformer.models.position_encoding")
+    from kinet_b200.modules import kinematic_backbone as kb
+    for name, ref in (("LayerBackboneFC", bb), ("Kinet_Backbone", bb), ("Joiner", bb), ("PositionEmbeddingSineDetections", pe)):
+        a, b = getattr(kb, name), getattr(ref, name)
+        assert list(inspect.signature(a.__init__).parameters) == list(inspect.signature(b.__init__).parameters), name
+        assert list(inspect.signature(a.forward).parameters) == list(inspect.signature(b.forward).parameters), name
+    ours = kb.Joiner(kb.Kinet_Backbone(4, [256, 512, 72]), kb.PositionEmbeddingSineDetections(36)).state_dict()
+    theirs = bb.Joiner(bb.Kinet_Backbone(4, [256, 512, 72]), pe.PositionEmbeddingSineDetections(36)).state_dict()
+    assert list(ours) == list(theirs) and all(ours[k].shape == theirs[k].shape for k in ours)
+
+
+@pytest.mark.gpu
+def test_whole_kine_model_from_raw_detections_matches_reference_golden():
+    """case g: KinematicDetectorTransformer over the real backbones (boxes + confidences in, logits + boxes out), fp32;
+    and the same call under bf16 autocast stays close."""
+    from kinet_b200.modules import kinematic_transformer as kt
+    from kinet_b200.modules.kinematic_backbone import NestedTensor, NestedTensorKinet
+    from kinet_b200.modules.kinematic_detector import KinematicDetectorTransformer
+    dev = torch.device("cuda:0")
+    z = _z()
+    t = lambda k: torch.from_numpy(z[k]).to(dev)
+    transformer = kt.DualKinematicTransformer(d_model=72, nhead=8, num_encoder_layers=1, num_decoder_layers=2,
+                                              dim_feedforward=48, dropout=0.0, return_intermediate_dec=True)
+    model = KinematicDetectorTransformer(_backbones(dev), transformer, num_classes=1, num_queries=6, aux_loss=True,
+                                         dim_tracklets_det=16, dim_tracklets_metadata=8)
+    _by_name(model).to(dev).eval()
+    smp = NestedTensorKinet(NestedTensor(t("f:boxes"), t("f:mask")), NestedTensor(t("f:conf"), t("f:mask")))
+    with torch.no_grad():
+        out, _, _, src_out, hs_det = model(smp, None)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out_lp = model(smp, None)[0]
+    assert _rel(src_out, t("g:src_out")) < 5e-6
+    for got, k in ((out["pred_logits"], "pred_logits"), (out["pred_boxes"], "pred_boxes"),
+                   (out["aux_outputs"][0]["pred_logits"], "aux_logits"), (hs_det, "hs_det")):
+        assert _rel(got, t("g:" + k)) < 2e-5, k
+    assert _rel(out_lp["pred_boxes"], t("g:pred_boxes")) < 3e-2 and _rel(out_lp["pred_logits"], t("g:pred_logits")) < 6e-2
