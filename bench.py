@@ -544,10 +544,16 @@ def measure_callers(rank, world, dev, frames=120, train_steps=10):
     import kine_bench
     k = kine_bench.measure(dev, frames=200, seed=rank)
     kt = kine_bench.measure_tracker(dev, frames=200, seed=rank)
+    kr = kine_bench.measure_tracker(dev, frames=200, seed=rank, raw=True)
     ms, ms_tr = reduce_max([kt["tracker_ms_per_frame"], k["fused_graphs_ms_per_frame"]], dev, world)
     out["kine_frames_per_s"] = {
         "value": world * 1e3 / ms, "ms_per_frame_per_gpu": ms, "tracks_min_max": kt["tracks_min_max"],
         "tracks_started": kt["tracks_started"], "graphs_recorded": kt["graphs_recorded"],
+        "from_raw_detections": {"ms_per_frame_per_gpu": kr["tracker_ms_per_frame"], "tracks_min_max": kr["tracks_min_max"],
+                                "host_enqueue_ms": kr["phases_ms"]["enqueue"],
+                                "note": "the same loop fed raw boxes + confidences, the model's own backbones "
+                                        "(modules.kinematic_backbone) recorded in the graph: one pinned block + one replay per "
+                                        "frame; with random weights only a few tracks live at a time (a lighter host update)"},
         "transformer_only": {"frames_per_s": world * 1e3 / ms_tr, "ms_per_frame_per_gpu": ms_tr,
                              "same_parameters_through_stock_pytorch_modules_ms": {"eager": k["plain_eager_ms"],
                                                                                   "one_cuda_graph": k["plain_graph_ms"]}},

@@ -195,18 +195,44 @@ class KineFrameGraphs:
         projecting them to track-query embeddings is part of what it records.  Per frame the host enqueues the four
         token copies, that block and the replay: 6 launches instead of ~25.  Same return value as __call__."""
         T, C = src_det.shape[1], src_det.shape[2]
+        graph, bufs, out, pad = self._block_call(src_det.device, T, (), trail_det, trail_meta, tokens_c=C)
+        for name, t in (("src_det", src_det), ("src_meta", src_meta), ("pos_det", pos_det), ("pos_meta", pos_meta)):
+            bufs[name][:, :T].copy_(t, non_blocking=True)
+        graph.replay()
+        self.replays += 1
+        return out, pad
+
+    def call_with_detections(self, device, dets, meta, trail_det, trail_meta):
+        """A frame from its RAW detections: ``dets`` (T, Xb) boxes and ``meta`` (T, Xc) confidences [+ classes] as HOST
+        arrays travel in the same pinned block as the counts and the trails; ``heads`` finds them in ``bufs["det_raw"]``
+        (1, Tp, Xb) / ``bufs["meta_raw"]`` (1, Tp, Xc) next to ``mask`` and runs the model's backbones
+        (modules.kinematic_backbone) as part of the recorded graph.  The host enqueues ONE copy and the replay."""
+        graph, bufs, out, pad = self._block_call(device, dets.shape[0], (dets, meta), trail_det, trail_meta)
+        graph.replay()
+        self.replays += 1
+        return out, pad
+
+    def _block_call(self, dev, T, raw, trail_det, trail_meta, tokens_c=0):
+        """Shared by the two entries above: finds / records the graph of the frame's bucket and sends the pinned block
+        [T, padding track rows | raw detections, raw metadata (Tp rows each, zero-padded at the END) | trails (Kp rows each,
+        zero-padded at the FRONT)].  -> (graph, bufs, out, number of padding track-query rows)."""
         K, Xd, Xm = trail_det.shape[0], trail_det.shape[1], trail_meta.shape[1]
         Tp = -(-T // self.token_bucket) * self.token_bucket
         Kp = -(-K // self.track_bucket) * self.track_bucket
-        key = (Tp, Kp, Xd, Xm)
-        dev = src_det.device
-        n_block = 2 + Kp * (Xd + Xm)
+        Xr = tuple(int(r.shape[1]) for r in raw)
+        key = (Tp, Kp, Xd, Xm) + Xr
+        n_raw = Tp * sum(Xr)
+        n_block = 2 + n_raw + Kp * (Xd + Xm)
         if key not in self._graphs:
             block = torch.zeros(n_block, device=dev)
-            bufs = dict(src_det=torch.zeros(1, Tp, C, device=dev), src_meta=torch.zeros(1, Tp, C, device=dev),
-                        pos_det=torch.zeros(1, Tp, C, device=dev), pos_meta=torch.zeros(1, Tp, C, device=dev),
-                        block=block, trail_det=block[2:2 + Kp * Xd].view(Kp, Xd),
-                        trail_meta=block[2 + Kp * Xd:].view(Kp, Xm))
+            o = 2 + n_raw
+            bufs = dict(block=block, trail_det=block[o:o + Kp * Xd].view(Kp, Xd), trail_meta=block[o + Kp * Xd:].view(Kp, Xm))
+            if raw:
+                bufs["det_raw"] = block[2:2 + Tp * Xr[0]].view(1, Tp, Xr[0])
+                bufs["meta_raw"] = block[2 + Tp * Xr[0]:2 + n_raw].view(1, Tp, Xr[1])
+            else:
+                for name in ("src_det", "src_meta", "pos_det", "pos_meta"):
+                    bufs[name] = torch.zeros(1, Tp, tokens_c, device=dev)
             # (kept in bufs: the recorded graph reads them on every replay, so they must outlive this call)
             tok = bufs["token_index"] = torch.arange(Tp, device=dev, dtype=torch.float32).view(1, Tp)
             trk = bufs["track_index"] = torch.arange(Kp, device=dev, dtype=torch.float32).view(1, Kp)
@@ -223,18 +249,18 @@ class KineFrameGraphs:
         host = st[st[2]]
         flat = host.numpy()
         flat[0], flat[1] = T, Kp - K
+        o = 2
+        for a, X in zip(raw, Xr):
+            flat[o:o + T * X] = a.ravel()
+            flat[o + T * X:o + Tp * X] = 0.0
+            o += Tp * X
         if Kp:
-            o = 2
             for a, X in ((trail_det, Xd), (trail_meta, Xm)):
                 flat[o:o + (Kp - K) * X] = 0.0
                 flat[o + (Kp - K) * X:o + Kp * X] = a.ravel()
                 o += Kp * X
         bufs["block"].copy_(host[:n_block], non_blocking=True)
-        for name, t in (("src_det", src_det), ("src_meta", src_meta), ("pos_det", pos_det), ("pos_meta", pos_meta)):
-            bufs[name][:, :T].copy_(t, non_blocking=True)
-        graph.replay()
-        self.replays += 1
-        return out, Kp - K
+        return graph, bufs, out, Kp - K
 
     def __call__(self, src_det, src_meta, pos_det, pos_meta, tgt_det=None, tgt_meta=None):
         """src_* / pos_* (1, T, C) token embeddings; tgt_* (K, 1, C) projected track-query embeddings or None.

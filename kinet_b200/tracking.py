@@ -431,6 +431,13 @@ def synthetic_sequence(levels, d_model, n_frames, device, seed=0, drift=0.05, dt
 # =====================================================================================================================
 # The literal KineT tracker: kinematic detector over detection tokens
 # =====================================================================================================================
+def _host_f32(a):
+    """numpy float32 view / copy of a host array or tensor."""
+    if isinstance(a, torch.Tensor):
+        a = a.detach().cpu().numpy()
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
 class FrameTracks(Mapping):
     """One frame's tracks as the read-only mapping {track_id: {"bbox": xyxy pixels, "score"}} over three parallel
     arrays (``ids``, ``boxes``, ``scores``); the dicts are made on first access, so a loop that only steps pays nothing."""
@@ -584,7 +591,14 @@ class KineSequenceTracker:
         class _S:
             pass
         s = _S()
-        s.detections, s.metadata = (frame[0], frame[2]), (frame[1], frame[3])
+        if len(frame) == 2:                       # raw detections (T, Xb) / metadata (T, Xc): through the model's backbones
+            from .modules.kinematic_backbone import NestedTensor
+            dev = self.query_device()
+            d, m = (torch.from_numpy(_host_f32(a)).to(dev)[None] for a in frame)
+            mask = torch.zeros(1, d.shape[1], dtype=torch.bool, device=dev)
+            s.detections, s.metadata = NestedTensor(d, mask), NestedTensor(m, mask)
+        else:
+            s.detections, s.metadata = (frame[0], frame[2]), (frame[1], frame[3])
         targets = None
         if det_t is not None:
             targets = [{"track_query_hs_embeds_det": det_t, "track_query_hs_embeds_meta": meta_t}]
@@ -603,6 +617,13 @@ class KineSequenceTracker:
 
             def heads(transformer, bufs, Kp):
                 pad = lambda e: torch.nn.functional.pad(e.weight[:, None], (0, 0, 0, 0, Kp, 0))
+                if "det_raw" in bufs:              # a frame from its raw detections: the backbones are part of the graph
+                    from .modules.kinematic_backbone import NestedTensor
+                    fd, pd = det.backbone_det(NestedTensor(bufs["det_raw"], bufs["mask"]))
+                    fm, pm = det.backbone_metadata(NestedTensor(bufs["meta_raw"], bufs["mask"]))
+                    src_det, src_meta, pos_det, pos_meta = fd[-1].tensors, fm[-1].tensors, pd[0], pm[0]
+                else:
+                    src_det, src_meta, pos_det, pos_meta = bufs["src_det"], bufs["src_meta"], bufs["pos_det"], bufs["pos_meta"]
                 td = tm = qpad = None
                 if Kp:
                     td = det.input_proj_tracklets_det(bufs["trail_det"])[:, None].float()
@@ -611,19 +632,28 @@ class KineSequenceTracker:
                     tm = torch.nn.functional.pad(tm, (0, 0, 0, 0, 0, nq))
                     qpad = torch.nn.functional.pad(bufs["kpad"], (0, nq))                 # object queries are never padding
                 hs_det, hs_meta, _, _ = transformer.forward_masked_queries(
-                    bufs["src_det"], bufs["src_meta"], bufs["mask"], pad(det.query_embed_det), pad(det.query_embed_metadata),
-                    td, tm, bufs["pos_det"], bufs["pos_meta"], qpad)
+                    src_det, src_meta, bufs["mask"], pad(det.query_embed_det), pad(det.query_embed_metadata),
+                    td, tm, pos_det, pos_meta, qpad)
                 return self._pack(linear(hs_meta[-1], det.class_embed), det.bbox_embed(hs_det[-1]).sigmoid())
             self._graphs = KineFrameGraphs(det.transformer, heads, token_bucket=self.token_bucket,
                                            track_bucket=self.track_bucket, autocast_dtype=self.autocast_dtype)
-        packed, pad = self._graphs.call_with_trails(frame[0], frame[1], frame[2], frame[3], trail_det, trail_meta)
+        if len(frame) == 2:
+            dev = self.query_device()
+            packed, pad = self._graphs.call_with_detections(dev, _host_f32(frame[0]), _host_f32(frame[1]), trail_det, trail_meta)
+        else:
+            packed, pad = self._graphs.call_with_trails(frame[0], frame[1], frame[2], frame[3], trail_det, trail_meta)
         return packed[pad:]                       # the padding track-query rows sit at the front
+
+    def query_device(self):
+        return self.detector.query_embed_det.weight.device
 
     @torch.no_grad()
     def step(self, frame):
-        """frame = (src_det, src_meta, pos_det, pos_meta), each (1, T, C) on the device -> {track_id: {"bbox", "score"}}
-        (a read-only mapping built on first access; ``.ids`` / ``.boxes`` / ``.scores`` are the arrays behind it)."""
-        dev = frame[0].device
+        """frame = (src_det, src_meta, pos_det, pos_meta), each (1, T, C) on the device -- or, with a detector built on
+        modules.kinematic_backbone, the frame's RAW detections (boxes (T, 4), metadata (T, 1 or 2)) as host arrays
+        -> {track_id: {"bbox", "score"}} (a read-only mapping built on first access; ``.ids`` / ``.boxes`` / ``.scores``
+        are the arrays behind it)."""
+        dev = self.query_device()
         self._prune_inactive()
         K = len(self.ids) + len(self.inactive[0])
         if self.use_graphs:

@@ -89,3 +89,49 @@ def test_whole_kine_model_from_raw_detections_matches_reference_golden():
                    (out["aux_outputs"][0]["pred_logits"], "aux_logits"), (hs_det, "hs_det")):
         assert _rel(got, t("g:" + k)) < 2e-5, k
     assert _rel(out_lp["pred_boxes"], t("g:pred_boxes")) < 3e-2 and _rel(out_lp["pred_logits"], t("g:pred_logits")) < 6e-2
+
+
+@pytest.mark.gpu
+def test_kine_tracker_from_raw_detections_graphs_match_eager():
+    """KineSequenceTracker fed the frames' RAW detections (boxes + confidences as host arrays): with graphs the frame is one
+    pinned block + one replay (backbones, masks, trail projections, transformer, heads recorded together); same track ids
+    and boxes as the eager loop through KinematicDetectorTransformer.forward(NestedTensorKinet, targets)."""
+    from kinet_b200.modules import kinematic_transformer as kt
+    from kinet_b200.modules.kinematic_detector import KinematicDetectorTransformer
+    from kinet_b200.tracking import KineSequenceTracker
+    dev = torch.device("cuda:0")
+    d, nq, n_frames = 72, 12, 5
+    transformer = kt.DualKinematicTransformer(d_model=d, nhead=8, num_encoder_layers=1, num_decoder_layers=1,
+                                              dim_feedforward=48, dropout=0.0, return_intermediate_dec=True)
+    det = _by_name(KinematicDetectorTransformer(_backbones(dev, max_det=60), transformer, num_classes=1, num_queries=nq,
+                                                dim_tracklets_det=4 * n_frames, dim_tracklets_metadata=n_frames)).to(dev).eval()
+    with torch.no_grad():
+        det.class_embed.weight.mul_(6.0)
+        det.bbox_embed.layers[-1].weight.mul_(8.0)
+    rng = np.random.default_rng(5)
+    scene = rng.random((20, 5)).astype(np.float32)
+    frames = []
+    for i in range(20):
+        T = 9 + (7 * i) % 11
+        f = scene[:T] + 0.02 * rng.standard_normal((T, 5)).astype(np.float32)
+        frames.append((np.clip(f[:, :4], 0, 1), np.clip(f[:, 4:], 0, 1)))
+    kw = dict(img_size=(1080, 1920), n_frames=n_frames, inactive_patience=2)
+    a = KineSequenceTracker(det, use_graphs=True, token_bucket=8, track_bucket=4, **kw)
+    b = KineSequenceTracker(det, use_graphs=False, **kw)
+    with torch.no_grad():
+        sc = b._detect_eager(frames[0], None, None)[:, 0]
+    thr = float(torch.quantile(sc, 0.6))
+    for t in (a, b):
+        t.det_thresh = thr
+    started = 0
+    for i, f in enumerate(frames):
+        for t in (a, b):                       # near-binary scores with random weights: drive terminations / returns by hand
+            t.trk_thresh = float("inf") if i % 5 == 3 else thr - 1.0
+            t.reid_thresh = float("-inf") if i % 5 == 4 else float("inf")
+        ra, rb = a.step(f), b.step(f)
+        assert sorted(ra) == sorted(rb) and a.inactive_tracks == b.inactive_tracks
+        for tid in ra:
+            assert np.abs(ra[tid]["bbox"] - rb[tid]["bbox"]).max() < 1e-3 and abs(ra[tid]["score"] - rb[tid]["score"]) < 1e-5
+        started = max(started, len(ra))
+    assert started > 0 and a.num_reids == b.num_reids > 0 and a.next_id == b.next_id
+    assert len(a._graphs.recorded_buckets) >= 3 and all(len(k) == 6 for k in a._graphs.recorded_buckets)

@@ -162,15 +162,20 @@ def measure(dev, frames=200, fp32=False, nq=150, d=288, seed=0):
     return res
 
 
-def measure_tracker(dev, frames=200, fp32=False, nq=150, d=288, n_frames=5, seed=0):
+def measure_tracker(dev, frames=200, fp32=False, nq=150, d=288, n_frames=5, seed=0, raw=False):
     """Frames/s of kinet_b200.tracking.KineSequenceTracker (the loop of TrackerKinematic.step) over the kine detector at the
     kinet configuration: per frame T detection tokens (100-150), the live tracks' trails as track queries, one detector
-    replay from KineFrameGraphs, ONE read-back, host thresholds / NMS / births / terminations."""
+    replay from KineFrameGraphs, ONE read-back, host thresholds / NMS / births / terminations.
+    raw: the frames are RAW detections (boxes + confidences, host arrays) and the detector carries the model's own
+    backbones (modules.kinematic_backbone): the frame is one pinned block + one replay."""
     from kinet_b200.modules.kinematic_detector import KinematicDetectorTransformer, TokenFeatures
     from kinet_b200.modules.kinematic_transformer import DualKinematicTransformer
     from kinet_b200.tracking import KineSequenceTracker
     torch.manual_seed(seed)
     back = [lambda x: ([TokenFeatures(x[0], torch.zeros(x[0].shape[:2], dtype=torch.bool, device=x[0].device))], [x[1]])] * 2
+    if raw:
+        from kinet_b200.modules.kinematic_backbone import build_kine_backbone
+        back = build_kine_backbone(d, max_number_detection=200)
     tr = DualKinematicTransformer(d_model=d, nhead=8, num_encoder_layers=1, num_decoder_layers=1, dim_feedforward=2048,
                                   dropout=0.1, return_intermediate_dec=True)
     det = KinematicDetectorTransformer(back, tr, num_classes=1, num_queries=nq, dim_tracklets_det=4 * n_frames,
@@ -181,15 +186,39 @@ def measure_tracker(dev, frames=200, fp32=False, nq=150, d=288, n_frames=5, seed
     g = torch.Generator(device=dev).manual_seed(seed + 1)
     scene = [torch.randn(1, 160, d, device=dev, generator=g) for _ in range(4)]
     feeds = []
+    import numpy as np
+    rng = np.random.default_rng(seed + 2)
+    boxes = rng.random((160, 5)).astype(np.float32)
     for i in range(16):
         T = 100 + (37 * i) % 51
-        feeds.append(tuple(s_[:, :T] + 0.3 * torch.randn(1, T, d, device=dev, generator=g) for s_ in scene))
+        if raw:
+            f = np.clip(boxes[:T] + 0.01 * rng.standard_normal((T, 5)).astype(np.float32), 0, 1)
+            feeds.append((np.ascontiguousarray(f[:, :4]), np.ascontiguousarray(f[:, 4:])))
+        else:
+            feeds.append(tuple(s_[:, :T] + 0.3 * torch.randn(1, T, d, device=dev, generator=g) for s_ in scene))
     trk = KineSequenceTracker(det, img_size=(1080, 1920), n_frames=n_frames, use_graphs=True, token_bucket=32,
                               autocast_dtype=None if fp32 else torch.bfloat16)
     with torch.no_grad():
         sc = trk._detect_eager(feeds[0], None, None)[:, 0].float()
     trk.det_thresh = float(torch.quantile(sc, 0.85))            # ~ 20 of the 150 object queries fire on the first frame
     trk.trk_thresh = trk.det_thresh - 0.05 * float(sc.max() - sc.min())
+    if raw:
+        # random weights: what a track query scores has little to do with what started it.  Pilot frames in which no track
+        # ends give the distribution of track-query scores; the track threshold is put at its 30 % quantile and the
+        # detection threshold where ~12 object queries fire, i.e. ~40 live tracks in the steady state.
+        import numpy as np
+        seen, orig = [], trk._update
+
+        def spy(packed, K):
+            if K:
+                seen.append(packed[:K, 0].copy())
+            return orig(packed, K)
+        trk._update, trk.trk_thresh, trk.det_thresh = spy, float("-inf"), float(torch.quantile(sc, 0.92))
+        for i in range(6):
+            trk.step(feeds[i & 15])
+        trk._update = orig
+        trk.trk_thresh = float(np.quantile(np.concatenate(seen), 0.3)) if seen else trk.det_thresh
+        trk.reset()
     for i in range(48):                                         # warm-up: records the graphs of the sizes that occur
         trk.step(feeds[i & 15])
     torch.cuda.synchronize()
@@ -256,4 +285,5 @@ if __name__ == "__main__":
         sys.exit(0)
     res = measure(torch.device("cuda:0"), a.frames, a.fp32)
     res["tracker"] = measure_tracker(torch.device("cuda:0"), a.frames, a.fp32)
+    res["tracker_from_raw_detections"] = measure_tracker(torch.device("cuda:0"), a.frames, a.fp32, raw=True)
     print(json.dumps(res))
