@@ -545,6 +545,8 @@ def measure_callers(rank, world, dev, frames=120, train_steps=10):
     k = kine_bench.measure(dev, frames=200, seed=rank)
     kt = kine_bench.measure_tracker(dev, frames=200, seed=rank)
     kr = kine_bench.measure_tracker(dev, frames=200, seed=rank, raw=True)
+    ktr = kine_bench.measure_training(dev, steps=20)
+    (kms,) = reduce_max([ktr["train_graph_ms_per_step"]], dev, world)
     ms, ms_tr = reduce_max([kt["tracker_ms_per_frame"], k["fused_graphs_ms_per_frame"]], dev, world)
     out["kine_frames_per_s"] = {
         "value": world * 1e3 / ms, "ms_per_frame_per_gpu": ms, "tracks_min_max": kt["tracks_min_max"],
@@ -554,6 +556,12 @@ def measure_callers(rank, world, dev, frames=120, train_steps=10):
                                 "note": "the same loop fed raw boxes + confidences, the model's own backbones "
                                         "(modules.kinematic_backbone) recorded in the graph: one pinned block + one replay per "
                                         "frame; with random weights only a few tracks live at a time (a lighter host update)"},
+        "training": {"samples_per_s": world * ktr["batch"] * 1e3 / kms, "ms_per_step_per_gpu": kms, "batch_per_gpu": ktr["batch"],
+                     "same_parameters_through_stock_pytorch_modules_ms": {"eager": ktr["train_plain_eager_ms"],
+                                                                          "one_cuda_graph": ktr["train_plain_graph_ms"]},
+                     "note": "cfgs/train_kinet.yaml shape (batch 8 x 150 tokens, 150 queries, d 288, 1 + 1 layers, dropout 0.1), "
+                             "synthetic loss, clip 0.1 + AdamW inside kinet_b200.training.GraphedTrainStep (data-parallel: "
+                             "one gradient all-reduce per step when N > 1)"},
         "transformer_only": {"frames_per_s": world * 1e3 / ms_tr, "ms_per_frame_per_gpu": ms_tr,
                              "same_parameters_through_stock_pytorch_modules_ms": {"eager": k["plain_eager_ms"],
                                                                                   "one_cuda_graph": k["plain_graph_ms"]}},

@@ -50,18 +50,21 @@ def make_heads(mods):
     return heads
 
 
-def plain_forward(tr, mods, src_b, src_m, mask, qd, qm, td, tm, pos_b, pos_m):
-    """The reference's arithmetic on the same parameters with stock PyTorch modules (sequence-first inside)."""
+def plain_forward(tr, mods, src_b, src_m, mask, qd, qm, td, tm, pos_b, pos_m, p_drop=0.0):
+    """The reference's arithmetic on the same parameters with stock PyTorch modules (sequence-first inside).
+    p_drop > 0: the residual-branch and FFN dropouts of forward_post (training)."""
+    dp = (lambda x: F.dropout(x, p_drop, True)) if p_drop > 0 else (lambda x: x)
+
     def enc_layer(l, src, pos):
         q = src + pos
-        src = l.norm1(src + l.self_attn(q, q, value=src, key_padding_mask=mask, need_weights=False)[0])
-        return l.norm2(src + l.linear2(F.relu(l.linear1(src))))
+        src = l.norm1(src + dp(l.self_attn(q, q, value=src, key_padding_mask=mask, need_weights=False)[0]))
+        return l.norm2(src + dp(l.linear2(dp(F.relu(l.linear1(src))))))
 
     def dec_layer(l, tgt, mem, pos, qpos):
         q = tgt + qpos
-        tgt = l.norm1(tgt + l.self_attn(q, q, value=tgt, need_weights=False)[0])
-        tgt = l.norm2(tgt + l.multihead_attn(tgt + qpos, mem + pos, value=mem, key_padding_mask=mask, need_weights=False)[0])
-        return l.norm3(tgt + l.linear2(F.relu(l.linear1(tgt))))
+        tgt = l.norm1(tgt + dp(l.self_attn(q, q, value=tgt, need_weights=False)[0]))
+        tgt = l.norm2(tgt + dp(l.multihead_attn(tgt + qpos, mem + pos, value=mem, key_padding_mask=mask, need_weights=False)[0]))
+        return l.norm3(tgt + dp(l.linear2(dp(F.relu(l.linear1(tgt))))))
 
     def one(t, src, pos, qe, tgt):
         src, pos = src.permute(1, 0, 2), pos.permute(1, 0, 2)
@@ -250,6 +253,132 @@ def measure_tracker(dev, frames=200, fp32=False, nq=150, d=288, n_frames=5, seed
                                host_update=1e3 * ph[2] / frames))
 
 
+def measure_training(dev, steps=30, fp32=False, batch=8, T=150, nq=150, d=288):
+    """One training step of the `kine` transformer + heads at the reference's configuration (cfgs/train_kinet.yaml:
+    batch_size 8, hidden_dim 288, 1 + 1 layers, 150 queries, dropout 0.1; AdamW lr 1e-4, clip_max_norm 0.1) on synthetic
+    token embeddings and a synthetic loss (cross-entropy on the class logits + L1 on the boxes; matcher and SetCriterion
+    are out of scope): kinet_b200's modules in kinet_b200.training.GraphedTrainStep (forward + backward + clip + AdamW as
+    two CUDA graphs) and eagerly, against the same parameters through stock PyTorch modules (eager, fused AdamW)."""
+    from kinet_b200.functions.layer_ops import linear
+    from kinet_b200.training import GraphedTrainStep
+    amp = dict(device_type="cuda", dtype=torch.bfloat16, enabled=not fp32)
+    g = torch.Generator(device=dev).manual_seed(3)
+    src_b, src_m, pos_b, pos_m = (torch.randn(batch, T, d, device=dev, generator=g) for _ in range(4))
+    mask = torch.zeros(batch, T, dtype=torch.bool, device=dev)
+    for i in range(batch):
+        mask[i, T - 5 * i:] = True                              # samples with 150, 145, ... detections
+    tgt_cls = torch.randint(0, 2, (batch * nq,), device=dev, generator=g)
+    tgt_box = torch.rand(batch, nq, 4, device=dev, generator=g)
+
+    def loss_of(logits, boxes):
+        return F.cross_entropy(logits.float().flatten(0, 1), tgt_cls) + 5.0 * F.l1_loss(boxes.float(), tgt_box)
+
+    def make(train_mode=True):
+        tr, mods = build(dev, d, nq)
+        net = torch.nn.ModuleList([tr, mods])
+        net.train(train_mode)
+        return tr, mods, net
+
+    def queries(mods):
+        return (mods["query_embed_det"].weight[:, None].expand(-1, batch, -1),
+                mods["query_embed_metadata"].weight[:, None].expand(-1, batch, -1))
+
+    def timed(fn, n):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(n):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / n
+
+    # ---- kinet_b200 modules, two CUDA graphs per step ----
+    tr, mods, net = make()
+
+    def fused_loss(src_b, src_m, pos_b, pos_m):
+        with torch.autocast(**amp):
+            qd, qm = queries(mods)
+            hs_det, hs_meta, _, _ = tr(src_b, src_m, mask, qd, qm, None, None, pos_b, pos_m)
+            return loss_of(linear(hs_meta[-1], mods["class_embed"]), mods["bbox_embed"](hs_det[-1]).sigmoid())
+    step = GraphedTrainStep(net, fused_loss, lambda p: torch.optim.AdamW(p, lr=1e-4, weight_decay=1e-4, fused=True, capturable=True),
+                            (src_b, src_m, pos_b, pos_m), clip_max_norm=0.1,
+                            lp_dtype=torch.float32 if fp32 else torch.bfloat16)
+    graph_ms = timed(lambda: step(src_b, src_m, pos_b, pos_m), steps)
+    loss_graph = float(step.loss)
+
+    # ---- kinet_b200 modules, eager ----
+    tr, mods, net = make()
+    opt = torch.optim.AdamW(net.parameters(), lr=1e-4, weight_decay=1e-4, fused=True)
+
+    def fused_eager():
+        opt.zero_grad(set_to_none=True)
+        fused_loss_eager = None
+        with torch.autocast(**amp):
+            qd, qm = queries(mods)
+            hs_det, hs_meta, _, _ = tr(src_b, src_m, mask, qd, qm, None, None, pos_b, pos_m)
+            fused_loss_eager = loss_of(linear(hs_meta[-1], mods["class_embed"]), mods["bbox_embed"](hs_det[-1]).sigmoid())
+        fused_loss_eager.backward()
+        torch.nn.utils.clip_grad_norm_(net.parameters(), 0.1)
+        opt.step()
+    eager_ms = timed(fused_eager, steps)
+    if os.environ.get("KINE_TRAIN_PROFILE"):                   # kernel breakdown of one fused training step (stderr)
+        from torch.profiler import ProfilerActivity, profile as prof
+        with prof(activities=[ProfilerActivity.CUDA]) as pr:
+            fused_eager()
+            torch.cuda.synchronize()
+        print(pr.key_averages().table(sort_by="cuda_time_total", row_limit=28, max_name_column_width=80), file=sys.stderr)
+
+    # ---- the same parameters through stock PyTorch modules (dropout of the residual branches as the reference applies it) ----
+    tr2, mods2, net2 = make()
+    opt2 = torch.optim.AdamW(net2.parameters(), lr=1e-4, weight_decay=1e-4, fused=True)
+
+    def plain_eager():
+        opt2.zero_grad(set_to_none=True)
+        with torch.autocast(**amp):
+            qd, qm = queries(mods2)
+            logits, boxes, _ = plain_forward(tr2, mods2, src_b, src_m, mask, qd, qm, None, None, pos_b, pos_m, p_drop=0.1)
+            loss = loss_of(logits, boxes)
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(net2.parameters(), 0.1)
+        opt2.step()
+    plain_ms = timed(plain_eager, steps)
+
+    # ---- ... and recorded as ONE CUDA graph per step (PyTorch's whole-network capture recipe, capturable AdamW) ----
+    tr3, mods3, net3 = make()
+    opt3 = torch.optim.AdamW(net3.parameters(), lr=1e-4, weight_decay=1e-4, fused=True, capturable=True)
+
+    def plain_step():
+        with torch.autocast(**amp):
+            qd, qm = queries(mods3)
+            logits, boxes, _ = plain_forward(tr3, mods3, src_b, src_m, mask, qd, qm, None, None, pos_b, pos_m, p_drop=0.1)
+            loss = loss_of(logits, boxes)
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(net3.parameters(), 0.1)
+        opt3.step()
+    plain_graph_ms = None
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                opt3.zero_grad(set_to_none=True)
+                plain_step()
+        torch.cuda.current_stream().wait_stream(side)
+        gr = torch.cuda.CUDAGraph()
+        opt3.zero_grad(set_to_none=True)
+        with torch.cuda.graph(gr):
+            plain_step()
+        plain_graph_ms = timed(gr.replay, steps)
+    except Exception as e:                                    # noqa: BLE001  (reported, not fatal: it is the comparison arm)
+        plain_graph_ms = "capture failed: %s" % str(e)[:120]
+    return dict(train_graph_ms_per_step=graph_ms, train_samples_per_s=batch * 1e3 / graph_ms, train_fused_eager_ms=eager_ms,
+                train_plain_eager_ms=plain_ms, train_plain_graph_ms=plain_graph_ms, loss_after=loss_graph, batch=batch, tokens=T,
+                dtype="fp32" if fp32 else "bf16 autocast")
+
+
 def profile(dev, fp32):
     """Kernel breakdown (torch profiler, eager) of one fused and one plain frame at T = 150, K = 48."""
     from torch.profiler import ProfilerActivity, profile as prof
@@ -286,4 +415,5 @@ if __name__ == "__main__":
     res = measure(torch.device("cuda:0"), a.frames, a.fp32)
     res["tracker"] = measure_tracker(torch.device("cuda:0"), a.frames, a.fp32)
     res["tracker_from_raw_detections"] = measure_tracker(torch.device("cuda:0"), a.frames, a.fp32, raw=True)
+    res["training"] = measure_training(torch.device("cuda:0"), fp32=a.fp32)
     print(json.dumps(res))
