@@ -19,8 +19,7 @@ of one Python object per track holding device scalars, and a frame is read back 
 all queries in one packed copy) instead of once per track and field (tracker.py:293, 536-542); thresholding and
 NMS then run on the host on a few hundred boxes.  Re-identification through inactive track queries (:273-276,
 :290-304, :367-394; ``inactive_patience`` >= 0 -- cfgs/track.yaml sets -1, i.e. off) is built; not covered: the
-embedding-distance ``reid()`` (:170-267; inert at the configured ``reid_sim_threshold`` 0.0), public detections, masks,
-attention maps -- they contain no MSDeformAttn work.  The backbone is out of scope: frames
+embedding-distance ``reid()`` (:170-267; inert at the configured ``reid_sim_threshold`` 0.0), masks, attention maps -- they contain no MSDeformAttn work.  The backbone is out of scope: frames
 enter as the multi-scale feature maps the backbone + input projections would produce.
 """
 import math
@@ -112,6 +111,42 @@ def _nms(boxes, scores, thresh):
     return _greedy_keep(over, np.argsort(-scores, kind="stable"))
 
 
+def public_detections_mask(new_boxes, public_boxes, mode):
+    """The reference's Tracker.public_detections_mask (tracker.py:126-167) on host arrays: which of the frame's new
+    detections (n, 4) xyxy are backed by one of the sequence's PUBLIC detections (m, 4) xyxy.  ``mode``: False / None = all;
+    'center_distance': per public box the nearest unclaimed detection, if the squared centre distance is below that
+    detection's area; 'min_iou_0_5': per public box the unclaimed detection with the largest IoU, if >= 0.5."""
+    n = len(new_boxes)
+    if not mode:
+        return np.ones(n, dtype=bool)
+    mask = np.zeros(n, dtype=bool)
+    if public_boxes is None or not len(public_boxes) or not n:
+        return mask
+    a, b = np.asarray(new_boxes, np.float64), np.asarray(public_boxes, np.float64)
+    if mode == "center_distance":
+        size = ((a[:, 2] - a[:, 0]) * (a[:, 3] - a[:, 1])).astype(np.float32)
+        ca, cb = (a[:, :2] + a[:, 2:]) / 2, (b[:, :2] + b[:, 2:]) / 2
+        dist = ((ca[:, None] - cb[None]) ** 2).sum(2)
+        for j in range(len(b)):
+            i = int(dist[:, j].argmin())
+            if dist[i, j] < size[i]:
+                dist[i, :] = 1e18
+                mask[i] = True
+    elif mode == "min_iou_0_5":
+        lt, rb = np.maximum(a[:, None, :2], b[None, :, :2]), np.minimum(a[:, None, 2:], b[None, :, 2:])
+        inter = np.clip(rb - lt, 0, None).prod(2)
+        area_a, area_b = (a[:, 2] - a[:, 0]) * (a[:, 3] - a[:, 1]), (b[:, 2] - b[:, 0]) * (b[:, 3] - b[:, 1])
+        iou = inter / np.maximum(area_a[:, None] + area_b[None] - inter, 1e-12)
+        for j in range(len(b)):
+            i = int(iou[:, j].argmax())
+            if iou[i, j] >= 0.5:
+                iou[i, :] = 0
+                mask[i] = True
+    else:
+        raise NotImplementedError(mode)
+    return mask
+
+
 class SequenceTracker:
     """Tracks one sequence frame by frame.
 
@@ -125,8 +160,12 @@ class SequenceTracker:
 
     def __init__(self, transformer, heads, query_embed, img_size, detection_obj_score_thresh=0.4,
                  track_obj_score_thresh=0.4, detection_nms_thresh=0.9, track_nms_thresh=0.9, steps_termination=1,
-                 use_graphs=False, bucket=32, autocast_dtype=None, inactive_patience=-1, reid_score_thresh=0.4):
+                 use_graphs=False, bucket=32, autocast_dtype=None, inactive_patience=-1, reid_score_thresh=0.4,
+                 public_detections=False):
         assert not transformer.two_stage and not transformer.multi_frame_attention_separate_encoder
+        # public_detections: False | 'center_distance' | 'min_iou_0_5' (tracker.py:126-167): new tracks only where one of the
+        # frame's public detections (step(..., public_dets=(m, 4) xyxy pixels)) backs the detection
+        self.public_detections = public_detections
         # inactive_patience >= 0: a terminated track stays a track query (its last box and embedding) for that many frames
         # and returns under its id when that query scores above reid_score_thresh (tracker.py:273-276, :290-304, :367-383);
         # -1 (cfgs/track.yaml:44) forgets it at once.  The embedding-distance reid() (:170-267) is not built: at the
@@ -255,23 +294,24 @@ class SequenceTracker:
             self.track_boxes = self.track_hs = None
 
     @torch.no_grad()
-    def step(self, srcs, masks, pos_embeds):
+    def step(self, srcs, masks, pos_embeds, public_dets=None):
         """One frame, start to finish (the device idles while the host reads the results and updates the tracks;
         ``run`` overlaps that with the next frame's encoder)."""
         dev = srcs[0].device
         hs, ref = self._run_transformer(srcs, masks, pos_embeds, self._targets(dev))
         hs, xyxy, packed = self._heads_and_pack(hs, ref)
-        return self._update_tracks(hs, xyxy, packed.cpu().numpy())          # ONE device -> host read per frame
+        return self._update_tracks(hs, xyxy, packed.cpu().numpy(), public_dets)   # ONE device -> host read per frame
 
     @torch.no_grad()
     def run(self, frames):
-        """Generator over a sequence, ``for result in tracker.run(frames)``: like calling step() on every frame, but
+        """(frames: (srcs, masks, pos_embeds) or, with public detections, (srcs, masks, pos_embeds, public_dets).)
+        Generator over a sequence, ``for result in tracker.run(frames)``: like calling step() on every frame, but
         with the CUDA-graph path frame t+1's encoder (which does not depend on the tracks) is enqueued BEFORE the host
         waits for frame t's results, so the read-back, the thresholding / NMS and the launches of the next decoder
         hide behind ~60 % of a frame's device work.  Results are identical to step()'s."""
         if not self.use_graphs:
-            for srcs, masks, pos_embeds in frames:
-                yield self.step(srcs, masks, pos_embeds)
+            for frame in frames:
+                yield self.step(*frame)
             return
         it = iter(frames)
         try:
@@ -282,7 +322,7 @@ class SequenceTracker:
         side = torch.cuda.Stream(device=dev)
         main = torch.cuda.current_stream(dev)
         host_buf = None
-        self._encode_graph(*cur)
+        self._encode_graph(*cur[:3])
         while cur is not None:
             hs, ref = self._decode_graph(self._targets(dev))
             hs, xyxy, packed = self._heads_and_pack(hs, ref)
@@ -298,9 +338,9 @@ class SequenceTracker:
             packed.record_stream(side)
             nxt = next(it, None)
             if nxt is not None:
-                self._encode_graph(*nxt)          # the device keeps working while the host reads frame t back
+                self._encode_graph(*nxt[:3])      # the device keeps working while the host reads frame t back
             copied.synchronize()
-            yield self._update_tracks(hs, xyxy, host_buf[:packed.shape[0]].numpy().copy())
+            yield self._update_tracks(hs, xyxy, host_buf[:packed.shape[0]].numpy().copy(), cur[3] if len(cur) > 3 else None)
             cur = nxt
 
     def _heads_and_pack(self, hs, ref):
@@ -341,7 +381,7 @@ class SequenceTracker:
         st[2][:n].copy_(host[:n], non_blocking=True)
         return [st[2][a:b] for a, b in out]      # (consumed by this frame's gathers, stream-ordered before the next copy)
 
-    def _update_tracks(self, hs, xyxy, packed):
+    def _update_tracks(self, hs, xyxy, packed, public_dets=None):
         """Host side of a frame: packed = (Lq, 6) numpy [score, label, x1, y1, x2, y2] of all queries."""
         dev = hs.device
         T, I = len(self.track_ids), len(self.inactive_ids)
@@ -375,6 +415,9 @@ class SequenceTracker:
         obj = slice(T, T + self.num_object_queries)
         new = [[-1, 0, int(i), -1, bx[i], sc[i]]
                for i in T + np.flatnonzero((sc[obj] > self.det_thresh) & (lb[obj] == 0))]
+        if self.public_detections and new:                             # :446-448
+            ok = public_detections_mask(np.stack([e[4] for e in new]), public_dets, self.public_detections)
+            new = [e for e, k in zip(new, ok) if k]
         # NMS in which existing tracks always win over new ones (:485-505)
         if self.det_nms and (live or new):
             boxes_all = np.stack([e[4] for e in live + new])
@@ -484,7 +527,7 @@ class KineSequenceTracker:
         stays an INACTIVE track query for that many frames (its trail frozen, the last entry repeated once) and comes back
         under its old id when its query scores above ``reid_score_thresh``; -1 (cfgs/track.yaml) forgets it at once.
 
-    Not covered: public detections (``public_detections: False`` in both tracking configs); the embedding-distance
+    ``public_detections`` ('center_distance' / 'min_iou_0_5', :126-167) gates births like in the reference.  Not covered: the embedding-distance
     ``reid()`` of the deformable Tracker is commented out in TrackerKinematic.step (:756-762).  The reference's
     ``add_tracks`` (:882-893) does not run as shipped (it passes ``confidence=`` to a constructor without that parameter,
     SURVEY.md F7); the evident intent -- a TrackKinematic holding the detection's box, score and pseudo-trail -- is built.
@@ -498,8 +541,10 @@ class KineSequenceTracker:
 
     def __init__(self, detector, img_size, n_frames=5, detection_obj_score_thresh=0.4, track_obj_score_thresh=0.4,
                  detection_nms_thresh=0.9, track_nms_thresh=0.9, steps_termination=1, n_classes=1, use_graphs=False,
-                 token_bucket=32, track_bucket=8, autocast_dtype=None, inactive_patience=-1, reid_score_thresh=0.4):
+                 token_bucket=32, track_bucket=8, autocast_dtype=None, inactive_patience=-1, reid_score_thresh=0.4,
+                 public_detections=False):
         self.detector = detector
+        self.public_detections = public_detections       # False | 'center_distance' | 'min_iou_0_5' (:126-167, :905-910)
         self.inactive_patience, self.reid_thresh = inactive_patience, reid_score_thresh
         self.img_h, self.img_w = float(img_size[0]), float(img_size[1])
         self._wh = np.array([self.img_w, self.img_h, self.img_w, self.img_h])
@@ -648,7 +693,7 @@ class KineSequenceTracker:
         return self.detector.query_embed_det.weight.device
 
     @torch.no_grad()
-    def step(self, frame):
+    def step(self, frame, public_dets=None):
         """frame = (src_det, src_meta, pos_det, pos_meta), each (1, T, C) on the device -- or, with a detector built on
         modules.kinematic_backbone, the frame's RAW detections (boxes (T, 4), metadata (T, 1 or 2)) as host arrays
         -> {track_id: {"bbox", "score"}} (a read-only mapping built on first access; ``.ids`` / ``.boxes`` / ``.scores``
@@ -663,9 +708,9 @@ class KineSequenceTracker:
             if K:
                 det_t, meta_t = self._to_device(dev, *self._trails())
             packed = self._detect_eager(frame, det_t, meta_t)
-        return self._update(packed.cpu().numpy(), K)                      # ONE device -> host read per frame
+        return self._update(packed.cpu().numpy(), K, public_dets)         # ONE device -> host read per frame
 
-    def _update(self, packed, K):
+    def _update(self, packed, K, public_dets=None):
         """packed (K + num_queries, 6) float32 from the detector (score, label, relative cx cy w h), the K track queries
         (live tracks, then inactive ones) first.  Every state array is REPLACED (FrameTracks of earlier frames keep theirs);
         selects are whole-array ``np.where`` / boolean compress, and both suppression passes read one IoU matrix."""
@@ -722,6 +767,8 @@ class KineSequenceTracker:
             self.inactive = (iid, ibox, isc, itr, itsc, icnt)
         # generate_new_tracks (:895-930): object queries above the detection threshold
         idx = K + np.flatnonzero((sc[K:] > self.det_thresh) & (lb[K:] < self.n_classes))
+        if self.public_detections and len(idx):
+            idx = idx[public_detections_mask(px[idx], public_dets, self.public_detections)]
         nl, m = len(ids), len(idx)
         sel_t, sel_n = None, None                                          # None = all kept
         need_t, need_d = bool(self.trk_nms) and nl > 1, bool(self.det_nms) and nl + m > 1

@@ -166,3 +166,27 @@ def test_a_degenerate_inactive_box_is_dropped_and_reactivated_tracks_take_part_i
     # track 1 comes back on top of track 2 with the lower score: NMS among the tracks removes it again
     out, _, _ = _step(t, [_row(0.9, 0.7, 0.7), _row(0.5, 0.701, 0.7), _row(0.0, 0, 0)])
     assert sorted(out) == [2] and t.num_reids == 1 and t.inactive_tracks == []
+
+
+def test_public_detections_mask_and_its_use_for_births():
+    """tracker.py:126-167: per public detection the nearest (centre distance below the detection's area) / best
+    overlapping (IoU >= 0.5) unclaimed detection; births only where backed (:905-910)."""
+    from kinet_b200.tracking import public_detections_mask as pdm
+    new = np.array([[0, 0, 10, 10], [20, 20, 30, 30], [0, 0, 9, 9.]])
+    pub = np.array([[1, 1, 11, 11.], [100, 100, 110, 110]])
+    assert pdm(new, pub, False).tolist() == [True, True, True]
+    assert pdm(new, pub, "center_distance").tolist() == [True, False, False]      # one public box claims ONE detection
+    assert pdm(new, pub, "min_iou_0_5").tolist() == [True, False, False]
+    assert pdm(new, np.array([[1, 1, 11, 11.], [0, 0, 9, 9]]), "min_iou_0_5").tolist() == [True, False, True]
+    assert pdm(new, None, "min_iou_0_5").tolist() == [False, False, False] and pdm(new[:0], pub, "center_distance").tolist() == []
+    try:
+        pdm(new, pub, "other")
+        assert False
+    except NotImplementedError:
+        pass
+    t = _tracker(public_detections="min_iou_0_5")
+    rows = [_row(0.9, 0.5, 0.5), _row(0.8, 0.2, 0.2)]                              # pixel boxes [450,200,550,300], [150,0,250,100]
+    out = t._update(_packed(rows), 0, np.array([[445, 195, 545, 295.]]))
+    assert sorted(out) == [0] and abs(out[0]["score"] - 0.9) < 1e-6
+    out = t._update(_packed([_row(0.9, 0.5, 0.5)] + rows), 1, None)              # no public detections: no births, the track stays
+    assert sorted(out) == [0]

@@ -177,3 +177,24 @@ def test_tracking_loop_inactive_tracks_return_and_graphs_match_eager():
     plain = SequenceTracker(tr, heads, qe, **dict(kw, inactive_patience=-1))
     fd, idd = run(plain)
     assert not any(idd) and plain.num_reids == 0
+
+
+def test_tracking_loop_public_detections_gate_births():
+    """public_detections (tracker.py:126-167, :446-448): without a backing public detection no track is born; fed the plain
+    run's own boxes as public detections, the gated loop (eager and pipelined graphs) reproduces the plain run."""
+    from kinet_b200.tracking import SequenceTracker, synthetic_sequence
+    dev = torch.device("cuda:0")
+    tr, heads, qe = _model(dev)
+    kw = dict(img_size=IMG, detection_obj_score_thresh=0.5, track_obj_score_thresh=0.5)
+    plain, _ = _run(SequenceTracker(tr, heads, qe, **kw), 12)
+    gated = SequenceTracker(tr, heads, qe, public_detections="min_iou_0_5", **kw)
+    seq = list(synthetic_sequence(LEVELS, D, 12, dev, seed=0, drift=0.25))
+    none = [gated.step(*f) for f in seq]
+    assert all(len(f) == 0 for f in none) and gated.next_id == 0
+    pub = [np.stack([r["bbox"] for r in f.values()]) if f else None for f in plain]
+    gated.reset()
+    fa = [gated.step(*f, public_dets=p) for f, p in zip(seq, pub)]
+    _compare(plain, fa, 1e-3)
+    graphed = SequenceTracker(tr, heads, qe, public_detections="min_iou_0_5", use_graphs=True, bucket=8, **kw)
+    fb = list(graphed.run([f + (p,) for f, p in zip(seq, pub)]))
+    _compare(plain, fb, 1e-3)
