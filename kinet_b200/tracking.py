@@ -18,8 +18,8 @@ What is different from the reference, on purpose: track state lives in device te
 of one Python object per track holding device scalars, and a frame is read back ONCE (scores, labels, boxes of
 all queries in one packed copy) instead of once per track and field (tracker.py:293, 536-542); thresholding and
 NMS then run on the host on a few hundred boxes.  Re-identification through inactive track queries (:273-276,
-:290-304, :367-394; ``inactive_patience`` >= 0 -- cfgs/track.yaml sets -1, i.e. off) is built; not covered: the
-embedding-distance ``reid()`` (:170-267; inert at the configured ``reid_sim_threshold`` 0.0), masks, attention maps -- they contain no MSDeformAttn work.  The backbone is out of scope: frames
+:290-304, :367-394; ``inactive_patience`` >= 0 -- cfgs/track.yaml sets -1, i.e. off) is built, and so is ``reid()`` (:170-267: greedy centre-distance or embedding-distance Hungarian matching of new
+detections to inactive tracks); not covered: masks, attention maps -- they contain no MSDeformAttn work.  The backbone is out of scope: frames
 enter as the multi-scale feature maps the backbone + input projections would produce.
 """
 import math
@@ -161,8 +161,12 @@ class SequenceTracker:
     def __init__(self, transformer, heads, query_embed, img_size, detection_obj_score_thresh=0.4,
                  track_obj_score_thresh=0.4, detection_nms_thresh=0.9, track_nms_thresh=0.9, steps_termination=1,
                  use_graphs=False, bucket=32, autocast_dtype=None, inactive_patience=-1, reid_score_thresh=0.4,
-                 public_detections=False):
+                 public_detections=False, reid_sim_threshold=0.0, reid_greedy_matching=False):
         assert not transformer.two_stage and not transformer.multi_frame_attention_separate_encoder
+        # reid() (tracker.py:170-267): new detections are first offered to the inactive tracks -- greedily by centre distance
+        # (reid_greedy_matching) or by Hungarian assignment on the distance of the decoder embeddings, accepted below
+        # reid_sim_threshold.  (At the configured threshold 0.0 the embedding variant never accepts; it is skipped then.)
+        self.reid_sim_threshold, self.reid_greedy = reid_sim_threshold, reid_greedy_matching
         # public_detections: False | 'center_distance' | 'min_iou_0_5' (tracker.py:126-167): new tracks only where one of the
         # frame's public detections (step(..., public_dets=(m, 4) xyxy pixels)) backs the detection
         self.public_detections = public_detections
@@ -381,6 +385,41 @@ class SequenceTracker:
         st[2][:n].copy_(host[:n], non_blocking=True)
         return [st[2][a:b] for a, b in out]      # (consumed by this frame's gathers, stream-ordered before the next copy)
 
+    def _reid(self, hs, live, inactive, new):
+        """tracker.py:170-267 on the entry lists of _update_tracks: matched inactive tracks return (this frame's detection
+        is their new state, appended behind the live tracks), their detections start no new track."""
+        ib = np.stack([e[4] for e in inactive])
+        nb = np.stack([e[4] for e in new])
+        if self.reid_greedy:
+            ci, cn = (ib[:, :2] + ib[:, 2:]) / 2, (nb[:, :2] + nb[:, 2:]) / 2
+            dist = ((ci[:, None] - cn[None]) ** 2).sum(2)
+            track_size = (ib[:, 2] - ib[:, 0]) * (ib[:, 3] - ib[:, 1])
+            item_size = (nb[:, 2] - nb[:, 0]) * (nb[:, 3] - nb[:, 1])
+            dist = dist + ((dist > track_size[:, None]) | (dist > item_size[None])) * 1e18
+            pairs = []
+            for i in range(dist.shape[0]):
+                j = int(dist[i].argmin())
+                if dist[i, j] < 1e16:
+                    dist[:, j] = 1e18
+                    dist[i, j] = 0.0
+                    pairs.append((i, j))
+        else:
+            from scipy.optimize import linear_sum_assignment
+            # embeddings: an inactive track's last decoder output (its row of the query pool), a detection's this frame
+            rows_i, rows_n = self._to_device_indices(hs.device, [e[3] for e in inactive], [e[2] for e in new])
+            dist = torch.cdist(self.track_hs[rows_i].float(), hs[0, rows_n].float()).cpu().numpy()
+            pairs = list(zip(*linear_sum_assignment(dist)))
+        taken_i, taken_n = set(), set()
+        for i, j in pairs:
+            if dist[i, j] <= self.reid_sim_threshold:
+                e = new[j]
+                live.append([inactive[i][0], 0, e[2], e[2], e[4], e[5]])
+                taken_i.add(i); taken_n.add(j)
+                self.num_reids += 1
+        inactive = [e for i, e in enumerate(inactive) if i not in taken_i]
+        new = [e for j, e in enumerate(new) if j not in taken_n]
+        return live, inactive, new
+
     def _update_tracks(self, hs, xyxy, packed, public_dets=None):
         """Host side of a frame: packed = (Lq, 6) numpy [score, label, x1, y1, x2, y2] of all queries."""
         dev = hs.device
@@ -418,6 +457,8 @@ class SequenceTracker:
         if self.public_detections and new:                             # :446-448
             ok = public_detections_mask(np.stack([e[4] for e in new]), public_dets, self.public_detections)
             new = [e for e, k in zip(new, ok) if k]
+        if inactive and new and (self.reid_greedy or self.reid_sim_threshold > 0):
+            live, inactive, new = self._reid(hs, live, inactive, new)
         # NMS in which existing tracks always win over new ones (:485-505)
         if self.det_nms and (live or new):
             boxes_all = np.stack([e[4] for e in live + new])

@@ -198,3 +198,26 @@ def test_tracking_loop_public_detections_gate_births():
     graphed = SequenceTracker(tr, heads, qe, public_detections="min_iou_0_5", use_graphs=True, bucket=8, **kw)
     fb = list(graphed.run([f + (p,) for f, p in zip(seq, pub)]))
     _compare(plain, fb, 1e-3)
+
+
+@pytest.mark.parametrize("greedy", [True, False])
+def test_tracking_loop_reid_of_new_detections_with_inactive_tracks(greedy):
+    """reid() (tracker.py:170-267): with the query-based return switched off, inactive tracks come back only by claiming a
+    new detection -- greedily by centre distance, or by Hungarian assignment on the embedding distance below
+    reid_sim_threshold.  A claimed detection starts no track of its own; eager and graphs agree."""
+    from kinet_b200.tracking import SequenceTracker, synthetic_sequence
+    dev = torch.device("cuda:0")
+    tr, heads, qe = _model(dev)
+    kw = dict(img_size=IMG, detection_obj_score_thresh=0.5, track_obj_score_thresh=0.5, inactive_patience=4,
+              reid_score_thresh=float("inf"), reid_greedy_matching=greedy, reid_sim_threshold=0.0 if greedy else 1e9)
+    seq = list(synthetic_sequence(LEVELS, D, 24, dev, seed=0, drift=0.25))
+    eager = SequenceTracker(tr, heads, qe, **kw)
+    fa = [eager.step(*f) for f in seq]
+    assert eager.num_reids > 0
+    plain = SequenceTracker(tr, heads, qe, **dict(kw, inactive_patience=-1))
+    fp = [plain.step(*f) for f in seq]
+    assert plain.num_reids == 0 and eager.next_id < plain.next_id          # returned tracks took detections that were births
+    graphed = SequenceTracker(tr, heads, qe, use_graphs=True, bucket=8, **kw)
+    fb = list(graphed.run(seq))
+    _compare(fa, fb, 1e-3)
+    assert graphed.num_reids == eager.num_reids
