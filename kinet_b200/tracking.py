@@ -672,7 +672,6 @@ class KineSequenceTracker:
         return torch.cat([scores[0, :, None], labels[0, :, None].to(scores.dtype), boxes[0].float()], -1)
 
     def _detect_eager(self, frame, det_t, meta_t):
-        from .modules.kinematic_detector import TokenFeatures  # noqa: F401  (the backbones' interface)
 
         class _S:
             pass
