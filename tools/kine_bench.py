@@ -212,10 +212,10 @@ def measure_tracker(dev, frames=200, fp32=False, nq=150, d=288, n_frames=5, seed
         import numpy as np
         seen, orig = [], trk._update
 
-        def spy(packed, K):
+        def spy(packed, K, *rest):
             if K:
                 seen.append(packed[:K, 0].copy())
-            return orig(packed, K)
+            return orig(packed, K, *rest)
         trk._update, trk.trk_thresh, trk.det_thresh = spy, float("-inf"), float(torch.quantile(sc, 0.92))
         for i in range(6):
             trk.step(feeds[i & 15])
