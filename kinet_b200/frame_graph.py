@@ -217,7 +217,7 @@ class KineFrameGraphs:
         [T, padding track rows | raw detections, raw metadata (Tp rows each, zero-padded at the END) | trails (Kp rows each,
         zero-padded at the FRONT)].  -> (graph, bufs, out, number of padding track-query rows)."""
         K, Xd, Xm = trail_det.shape[0], trail_det.shape[1], trail_meta.shape[1]
-        Tp = -(-T // self.token_bucket) * self.token_bucket
+        Tp = max(-(-T // self.token_bucket), 1) * self.token_bucket       # a frame without detections: one bucket, all masked
         Kp = -(-K // self.track_bucket) * self.track_bucket
         Xr = tuple(int(r.shape[1]) for r in raw)
         key = (Tp, Kp, Xd, Xm) + Xr

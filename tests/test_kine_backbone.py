@@ -135,3 +135,29 @@ def test_kine_tracker_from_raw_detections_graphs_match_eager():
         started = max(started, len(ra))
     assert started > 0 and a.num_reids == b.num_reids > 0 and a.next_id == b.next_id
     assert len(a._graphs.recorded_buckets) >= 3 and all(len(k) == 6 for k in a._graphs.recorded_buckets)
+
+
+@pytest.mark.gpu
+def test_kine_tracker_survives_a_frame_without_detections():
+    """T = 0: the graph path pads to one fully masked token bucket (attention over no keys gives zeros); live tracks are
+    still queried and updated."""
+    from kinet_b200.modules import kinematic_transformer as kt
+    from kinet_b200.modules.kinematic_detector import KinematicDetectorTransformer
+    from kinet_b200.tracking import KineSequenceTracker
+    dev = torch.device("cuda:0")
+    d, nq, n_frames = 72, 12, 5
+    transformer = kt.DualKinematicTransformer(d_model=d, nhead=8, num_encoder_layers=1, num_decoder_layers=1,
+                                              dim_feedforward=48, dropout=0.0, return_intermediate_dec=True)
+    det = _by_name(KinematicDetectorTransformer(_backbones(dev, max_det=60), transformer, num_classes=1, num_queries=nq,
+                                                dim_tracklets_det=4 * n_frames, dim_tracklets_metadata=n_frames)).to(dev).eval()
+    trk = KineSequenceTracker(det, img_size=(1080, 1920), n_frames=n_frames, use_graphs=True, token_bucket=8, track_bucket=4,
+                              detection_obj_score_thresh=-1.0, track_obj_score_thresh=-1.0)
+    rng = np.random.default_rng(0)
+    full = (rng.random((9, 4)).astype(np.float32), rng.random((9, 1)).astype(np.float32))
+    empty = (np.zeros((0, 4), np.float32), np.zeros((0, 1), np.float32))
+    a = trk.step(full)
+    b = trk.step(empty)
+    c = trk.step(full)
+    assert len(a) > 0 and len(b) >= len(a) and len(c) >= len(b)
+    for r in list(b.values()) + list(c.values()):
+        assert np.isfinite(r["bbox"]).all() and np.isfinite(r["score"])
